@@ -1,0 +1,483 @@
+"""Flattened, device-ready road map (setup-time, host side).
+
+Builds, once per scenario, the immutable arrays every kernel reads:
+
+* lanes / roads tables (``SumoRoadNetwork.Lane/Road`` accessors,
+  /root/reference/smarts/core/sumo_road_network.py:261-358, :550-657),
+* the linked lane points of ``LanePoints.from_sumo`` + ``_interpolate_shape_lanepoints``
+  (/root/reference/smarts/core/lanepoints.py:104-227, :376-515) as structure-of-arrays with a
+  CSR ``nexts`` list,
+* lane centre polylines for ``nearest_lanes`` (sumo_road_network.py:675-709),
+* convex road-surface polygons for the DrivableAreaGridMap (sumo_road_network.py:986-1019,
+  utils/geometry.py:31-45) and road boundary segments for the LiDAR,
+* routes (sumo_road_network.py:711-801).
+
+Lane points of one lane are contiguous and lanes of one road are contiguous (ordered by lane
+index), so the reference's three KD-trees (all points / per lane / per road,
+lanepoints.py:85-102) become three index ranges of the same arrays.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from .sumo_net import NetEdge, NetLane, SumoNet
+
+TWO_PI = 2.0 * math.pi
+
+
+def vec_to_radians(x: float, y: float) -> float:
+    """utils/math.py:256-277: +y is 0 rad, counter-clockwise, result in [0, 2pi)."""
+    r = math.atan2(abs(y), abs(x))
+    if x < 0:
+        if y < 0:
+            return (r + 0.5 * math.pi) % TWO_PI
+        return (0.5 * math.pi - r) % TWO_PI
+    elif y < 0:
+        return (1.5 * math.pi - r) % TWO_PI
+    return (r - 0.5 * math.pi) % TWO_PI
+
+
+def wrap_heading(h: float) -> float:
+    """coordinates.py:169-185 (``Heading.__new__``): (-pi, pi]."""
+    h = h % TWO_PI
+    if h > math.pi:
+        h -= TWO_PI
+    return h
+
+
+@dataclass
+class Route:
+    """sumo_road_network.py:884-903."""
+
+    road_ids: List[str]
+    road_indices: List[int]
+    length: float
+
+
+class RoadMapData:
+    """All per-scenario constant arrays.  ``arrays()`` returns the dict handed to the C-ABI
+    (``sb_upload_map``) and, unchanged, to the CPU oracle."""
+
+    def __init__(self, net: SumoNet, lanepoint_spacing: float = 1.0):
+        self.net = net
+        self.spacing = float(lanepoint_spacing)
+        self._build_tables()
+        self._build_lanepoints()
+        self._build_shapes()
+        self._build_polygons()
+
+    @classmethod
+    def from_file(cls, net_file: str, lanepoint_spacing: float = 1.0,
+                  default_lane_width: float = 3.2) -> "RoadMapData":
+        return cls(SumoNet(net_file, default_lane_width), lanepoint_spacing)
+
+    # ------------------------------------------------------------------ tables
+    def _build_tables(self):
+        net = self.net
+        self.roads: List[NetEdge] = list(net.getEdges(True))
+        self.road_index: Dict[str, int] = {e.getID(): i for i, e in enumerate(self.roads)}
+        self.lanes: List[NetLane] = []
+        road_lane_start, road_lane_count = [], []
+        for e in self.roads:
+            road_lane_start.append(len(self.lanes))
+            road_lane_count.append(len(e.getLanes()))
+            self.lanes.extend(e.getLanes())
+        self.lane_index: Dict[str, int] = {l.getID(): i for i, l in enumerate(self.lanes)}
+        nl = len(self.lanes)
+        self.road_lane_start = np.asarray(road_lane_start, np.int32)
+        self.road_lane_count = np.asarray(road_lane_count, np.int32)
+        self.road_is_junction = np.asarray([e.isSpecial() for e in self.roads], np.uint8)
+        self.road_length = np.asarray([e.getLength() for e in self.roads], np.float64)
+        self.lane_road = np.asarray([self.road_index[l.getEdge().getID()] for l in self.lanes], np.int32)
+        self.lane_idx_in_road = np.asarray([l.getIndex() for l in self.lanes], np.int32)
+        self.lane_width = np.asarray([l.getWidth() for l in self.lanes], np.float64)
+        self.lane_speed = np.asarray([l.getSpeed() for l in self.lanes], np.float64)
+        self.lane_length = np.asarray([l.getLength() for l in self.lanes], np.float64)
+        # outgoing lanes: via lane if present else to-lane (sumo_road_network.py:351-358)
+        out_start, out_flat = [0], []
+        for l in self.lanes:
+            for c in l.getOutgoing():
+                out_flat.append(self.lane_index[c.getViaLaneID() or c.getToLane().getID()])
+            out_start.append(len(out_flat))
+        self.lane_out_start = np.asarray(out_start, np.int32)
+        self.lane_out = np.asarray(out_flat if out_flat else [0], np.int32)
+        assert nl == len(self.lane_width)
+
+    def outgoing_lanes(self, li: int) -> List[int]:
+        return list(self.lane_out[self.lane_out_start[li]:self.lane_out_start[li + 1]])
+
+    # -------------------------------------------------------------- lane points
+    def _build_lanepoints(self):
+        """Restates ``LanePoints.from_sumo`` + ``_interpolate_shape_lanepoints``.
+
+        The reference links lanes breadth-first from every non-internal lane and memoises per
+        lane, so each lane ends up with exactly one chain of points:
+        shape vertex, interpolated points every ``spacing`` (with the 0.8*spacing / 1.4 m end
+        rules, lanepoints.py:460-515), next shape vertex, ..., last vertex; the last vertex
+        links to the first point of every outgoing lane (via lane if present,
+        lanepoints.py:202-210), with interpolated points on the *from* lane if there is a gap.
+        Lanes never reached from a non-internal lane get no points (same as the reference).
+        """
+        sp = self.spacing
+        nlanes = len(self.lanes)
+        # reachability in the reference's order (only matters for which lanes exist)
+        reached = [False] * nlanes
+        stack = []
+        for e in self.net.getEdges(False):
+            for l in e.getLanes():
+                stack.append(self.lane_index[l.getID()])
+        while stack:
+            li = stack.pop()
+            if reached[li]:
+                continue
+            reached[li] = True
+            stack.extend(self.outgoing_lanes(li))
+
+        xs: List[float] = []
+        ys: List[float] = []
+        hd: List[float] = []
+        inferred: List[int] = []
+        lane_of: List[int] = []
+        nexts: List[List[int]] = []
+        lane_lp_start = np.zeros(nlanes, np.int32)
+        lane_lp_count = np.zeros(nlanes, np.int32)
+        lane_first = [-1] * nlanes
+        lane_last = [-1] * nlanes
+        pending_links: List[Tuple[int, int]] = []  # (from lane, to lane) resolved after all chains exist
+
+        def add(x, y, h, inf, li):
+            xs.append(float(x)); ys.append(float(y)); hd.append(float(h))
+            inferred.append(int(inf)); lane_of.append(li); nexts.append([])
+            return len(xs) - 1
+
+        def interp(ax, ay, bx, by, curr, li):
+            """lanepoints.py:444-515; returns the last created (or ``curr``)."""
+            vx, vy = bx - ax, by - ay
+            seg_len = math.hypot(vx, vy) if False else float(np.linalg.norm(np.array([vx, vy])))
+            dist = sp
+            while dist < seg_len:
+                p = dist / seg_len
+                px, py = ax + vx * p, ay + vy * p
+                cx, cy = xs[curr], ys[curr]
+                half = float(np.linalg.norm(0.5 * (np.array([cx, cy]) - np.array([bx, by]))))
+                if half < 1.4:
+                    px, py = 0.5 * (bx + cx), 0.5 * (by + cy)
+                d = float(np.linalg.norm(np.array([bx - px, by - py])))
+                if d < 0.8 * sp:
+                    break
+                h = wrap_heading(vec_to_radians(vx, vy))
+                n = add(px, py, h, 1, li)
+                nexts[curr].append(n)
+                curr = n
+                dist += sp
+            return curr
+
+        for li, lane in enumerate(self.lanes):
+            lane_lp_start[li] = len(xs)
+            if not reached[li]:
+                continue
+            shape = lane.getShape(False)
+            assert len(shape) >= 2, repr(shape)
+            nv = len(shape)
+            seg_h = [wrap_heading(vec_to_radians(shape[i + 1][0] - shape[i][0],
+                                                 shape[i + 1][1] - shape[i][1]))
+                     for i in range(nv - 1)]
+            curr = add(shape[0][0], shape[0][1], seg_h[0], 0, li)
+            lane_first[li] = curr
+            for i in range(nv - 1):
+                curr = interp(shape[i][0], shape[i][1], shape[i + 1][0], shape[i + 1][1], curr, li)
+                h = seg_h[i + 1] if i + 1 < nv - 1 else seg_h[nv - 2]
+                n = add(shape[i + 1][0], shape[i + 1][1], h, 0, li)
+                nexts[curr].append(n)
+                curr = n
+            lane_last[li] = curr
+            for lo in self.outgoing_lanes(li):
+                pending_links.append((li, lo))
+            lane_lp_count[li] = len(xs) - lane_lp_start[li]
+
+        # cross-lane links (gap interpolation keeps lane points contiguous only when there is
+        # no gap; gaps are appended after the main chains and get their own contiguous block
+        # accounted to the from-lane through ``lp_lane`` -- the per-lane *range* then excludes
+        # them, which matches the maps shipped with the reference: all gaps are < spacing).
+        self.gap_points = 0
+        for li, lo in pending_links:
+            a, b = lane_last[li], lane_first[lo]
+            if b < 0:
+                continue
+            before = len(xs)
+            curr = interp(xs[a], ys[a], xs[b], ys[b], a, li)
+            self.gap_points += len(xs) - before
+            nexts[curr].append(b)
+
+        self.lp_x = np.asarray(xs, np.float64)
+        self.lp_y = np.asarray(ys, np.float64)
+        self.lp_heading = np.asarray(hd, np.float64)
+        self.lp_inferred = np.asarray(inferred, np.uint8)
+        self.lp_lane = np.asarray(lane_of, np.int32)
+        start, flat = [0], []
+        for n in nexts:
+            flat.extend(n)
+            start.append(len(flat))
+        self.lp_next_start = np.asarray(start, np.int32)
+        self.lp_next = np.asarray(flat if flat else [0], np.int32)
+        self.lane_lp_start = lane_lp_start
+        self.lane_lp_count = lane_lp_count
+        assert self.gap_points == 0, (
+            "map has lane-to-lane gaps >= lanepoint spacing; gap lane points would fall outside "
+            "the per-lane index range")
+        # per road range = union of its (contiguous) lanes
+        rs, rc = [], []
+        for r in range(len(self.roads)):
+            l0 = self.road_lane_start[r]
+            l1 = l0 + self.road_lane_count[r]
+            rs.append(lane_lp_start[l0] if l1 > l0 else 0)
+            rc.append(int(lane_lp_count[l0:l1].sum()))
+        self.road_lp_start = np.asarray(rs, np.int32)
+        self.road_lp_count = np.asarray(rc, np.int32)
+
+    # -------------------------------------------------------------- polylines
+    def _build_shapes(self):
+        sx, sy, start = [], [], [0]
+        for l in self.lanes:
+            for x, y in l.getShape(False):
+                sx.append(x); sy.append(y)
+            start.append(len(sx))
+        self.shape_x = np.asarray(sx, np.float64)
+        self.shape_y = np.asarray(sy, np.float64)
+        self.lane_shape_start = np.asarray(start, np.int32)
+
+    # ---------------------------------------------------------------- polygons
+    def _build_polygons(self):
+        """Convex pieces whose union is the drivable surface.
+
+        The reference buffers every lane centre line by ``width/2`` with flat caps and round
+        joins at one segment per quarter circle (utils/geometry.py:31-45) and adds every
+        junction shape with > 2 vertices (sumo_road_network.py:1009-1017).  GEOS/shapely and
+        Panda3D are unavailable on this box, so the surface is restated as: one rectangle per
+        centre-line segment, one join fan per interior vertex (the GEOS fillet: the arc between
+        the two offset points on the outer side, subdivided at multiples of pi/2 measured from
+        the first offset direction), and the junction polygons triangulated by ear clipping.
+        The ``snap`` passes (sumo_road_network.py:1021-1139) are not restated (documented
+        deviation).
+        """
+        polys: List[np.ndarray] = []  # each [n,2] CCW convex
+        edges: List[Tuple[float, float, float, float]] = []
+
+        def ccw(p):
+            p = np.asarray(p, np.float64)
+            a = 0.0
+            for i in range(len(p)):
+                j = (i + 1) % len(p)
+                a += p[i, 0] * p[j, 1] - p[j, 0] * p[i, 1]
+            return p if a >= 0 else p[::-1].copy()
+
+        for l in self.lanes:
+            shp = l.getShape()
+            hw = 0.5 * l.getWidth()
+            pts = [shp[0]]
+            for p in shp[1:]:
+                if p != pts[-1]:
+                    pts.append(p)
+            if len(pts) < 2:
+                continue
+            offs = []
+            for i in range(len(pts) - 1):
+                (ax, ay), (bx, by) = pts[i], pts[i + 1]
+                dx, dy = bx - ax, by - ay
+                ln = math.hypot(dx, dy)
+                nx, ny = -dy / ln * hw, dx / ln * hw  # left normal * hw
+                polys.append(ccw([(ax + nx, ay + ny), (ax - nx, ay - ny), (bx - nx, by - ny), (bx + nx, by + ny)]))
+                offs.append((nx, ny))
+            for i in range(1, len(pts) - 1):
+                (n0x, n0y), (n1x, n1y) = offs[i - 1], offs[i]
+                cross = n0x * n1y - n0y * n1x
+                if abs(cross) < 1e-12 * hw * hw:
+                    continue
+                s = -1.0 if cross > 0 else 1.0  # left turn -> outer side is the right
+                cx, cy = pts[i]
+                a0 = math.atan2(s * n0y, s * n0x)
+                a1 = math.atan2(s * n1y, s * n1x)
+                da = a1 - a0
+                while da > math.pi:
+                    da -= TWO_PI
+                while da < -math.pi:
+                    da += TWO_PI
+                fan = [(cx, cy), (cx + s * n0x, cy + s * n0y)]
+                nseg = int(abs(da) / (0.5 * math.pi) + 0.5)
+                if nseg >= 1:
+                    inc = da / nseg
+                    for k in range(1, nseg):
+                        fan.append((cx + hw * math.cos(a0 + k * inc), cy + hw * math.sin(a0 + k * inc)))
+                fan.append((cx + s * n1x, cy + s * n1y))
+                polys.append(ccw(fan))
+            # boundary segments of the outer-most lanes feed the LiDAR "road edge" walls
+        for e in self.roads:
+            if e.isSpecial():
+                continue
+            lanes = e.getLanes()
+            for lane, side in ((lanes[0], -1.0), (lanes[-1], 1.0)):
+                shp = lane.getShape()
+                hw = 0.5 * lane.getWidth()
+                for i in range(len(shp) - 1):
+                    (ax, ay), (bx, by) = shp[i], shp[i + 1]
+                    dx, dy = bx - ax, by - ay
+                    ln = math.hypot(dx, dy)
+                    if ln == 0:
+                        continue
+                    nx, ny = -dy / ln * hw * side, dx / ln * hw * side
+                    edges.append((ax + nx, ay + ny, bx + nx, by + ny))
+
+        for node in self.net.getNodes():
+            line = node.getShape()
+            if len(line) <= 2 or len(set(line)) == 1:
+                continue
+            for tri in _ear_clip(line):
+                polys.append(ccw(tri))
+
+        vx, vy, start = [], [], [0]
+        for p in polys:
+            vx.extend(p[:, 0]); vy.extend(p[:, 1])
+            start.append(len(vx))
+        self.poly_x = np.asarray(vx, np.float64)
+        self.poly_y = np.asarray(vy, np.float64)
+        self.poly_start = np.asarray(start, np.int32)
+        self.road_edges = np.asarray(edges if edges else np.zeros((0, 4)), np.float64).reshape(-1, 4)
+
+    # ------------------------------------------------------------------ routes
+    def road_by_id(self, road_id: str) -> int:
+        return self.road_index[road_id]
+
+    def generate_route(self, start_road: str, end_road: str,
+                       via: Optional[Sequence[str]] = None) -> Route:
+        """sumo_road_network.py:711-801 (max_to_gen == 1)."""
+        net = self.net
+        roads = [start_road] + list(via or [])
+        if end_road != start_road:
+            roads.append(end_road)
+        edges = []
+        for cur, nxt in zip(roads, roads[1:] + [None]):
+            if nxt is None:
+                edges.append(net.getEdge(cur))
+                break
+            sub = net.getShortestPath(net.getEdge(cur), net.getEdge(nxt))[0] or []
+            if len(sub) < 2:
+                return Route([], [], 0.0)
+            edges.extend(sub[:-1])
+        if len(edges) == 1:
+            ids = [edges[0].getID()]
+        else:
+            used = []
+            for ce, ne in zip(edges, edges[1:]):
+                for conn in ce.getOutgoing()[ne]:
+                    conn_route = [ce]
+                    via_id = conn.getViaLaneID()
+                    while via_id:
+                        via_edge = net.getLane(via_id).getEdge()
+                        conn_route.append(via_edge)
+                        nxt_ids = set(c.getViaLaneID() for c in via_edge.getOutgoing()[ne])
+                        assert len(nxt_ids) == 1
+                        via_id = list(nxt_ids)[0]
+                    conn_route.append(ne)
+                    used.extend(conn_route)
+            ids = []
+            seen = set()
+            for e in used:  # first-occurrence order == np.unique(return_index) + sorted(indices)
+                if e.getID() not in seen:
+                    seen.add(e.getID())
+                    ids.append(e.getID())
+        idx = [self.road_index[i] for i in ids]
+        return Route(ids, idx, float(sum(self.road_length[i] for i in idx)))
+
+    # ------------------------------------------------------------------ export
+    def arrays(self) -> Dict[str, np.ndarray]:
+        keys = [
+            "road_lane_start", "road_lane_count", "road_is_junction", "road_lp_start", "road_lp_count",
+            "lane_road", "lane_idx_in_road", "lane_width", "lane_speed", "lane_length",
+            "lane_out_start", "lane_out", "lane_lp_start", "lane_lp_count", "lane_shape_start",
+            "lp_x", "lp_y", "lp_heading", "lp_inferred", "lp_lane", "lp_next_start", "lp_next",
+            "shape_x", "shape_y", "poly_x", "poly_y", "poly_start", "road_edges",
+        ]
+        return {k: np.ascontiguousarray(getattr(self, k)) for k in keys}
+
+    @property
+    def lane_ids(self) -> List[str]:
+        return [l.getID() for l in self.lanes]
+
+    @property
+    def road_ids(self) -> List[str]:
+        return [e.getID() for e in self.roads]
+
+    def lane_start_pose(self, road_id: str, lane_idx: int, offset: float) -> Tuple[float, float, float]:
+        """Centre-line pose at ``offset`` metres along a lane (mission start poses,
+        scenarios/*/scenario.py ``Route(begin=(edge, lane, offset))``)."""
+        lane = self.net.getEdge(road_id).getLanes()[lane_idx]
+        shp = lane.getShape(False)
+        seen = 0.0
+        for (ax, ay), (bx, by) in zip(shp, shp[1:]):
+            ln = math.hypot(bx - ax, by - ay)
+            if seen + ln > offset or (bx, by) == shp[-1]:
+                t = min(max((offset - seen) / ln, 0.0), 1.0) if ln > 0 else 0.0
+                return (ax + (bx - ax) * t, ay + (by - ay) * t,
+                        wrap_heading(vec_to_radians(bx - ax, by - ay)))
+            seen += ln
+        raise ValueError("empty lane shape")
+
+
+def _ear_clip(line: Sequence[Tuple[float, float]]) -> List[List[Tuple[float, float]]]:
+    """Triangulate a simple polygon (junction shape) into triangles."""
+    pts = []
+    for p in line:
+        if not pts or p != pts[-1]:
+            pts.append(p)
+    if len(pts) > 1 and pts[0] == pts[-1]:
+        pts.pop()
+    if len(pts) < 3:
+        return []
+    area = 0.0
+    for i in range(len(pts)):
+        j = (i + 1) % len(pts)
+        area += pts[i][0] * pts[j][1] - pts[j][0] * pts[i][1]
+    if area < 0:
+        pts = pts[::-1]
+    idx = list(range(len(pts)))
+    tris = []
+
+    def cross(o, a, b):
+        return (a[0] - o[0]) * (b[1] - o[1]) - (a[1] - o[1]) * (b[0] - o[0])
+
+    guard = 0
+    while len(idx) > 3 and guard < 10000:
+        guard += 1
+        n = len(idx)
+        clipped = False
+        for k in range(n):
+            i0, i1, i2 = idx[(k - 1) % n], idx[k], idx[(k + 1) % n]
+            a, b, c = pts[i0], pts[i1], pts[i2]
+            cr = cross(a, b, c)
+            if cr < 0:
+                continue
+            ok = True
+            for m in idx:
+                if m in (i0, i1, i2):
+                    continue
+                p = pts[m]
+                if cross(a, b, p) > 0 and cross(b, c, p) > 0 and cross(c, a, p) > 0:
+                    ok = False
+                    break
+            if ok:
+                if cr > 0:
+                    tris.append([a, b, c])
+                idx.pop(k)
+                clipped = True
+                break
+        if not clipped:
+            break
+    if len(idx) == 3:
+        a, b, c = pts[idx[0]], pts[idx[1]], pts[idx[2]]
+        if cross(a, b, c) > 0:
+            tris.append([a, b, c])
+    return tris
