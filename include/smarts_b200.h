@@ -1,0 +1,222 @@
+/*
+ * smarts_b200 C-ABI: the batched per-tick multi-agent step (controllers + vehicle dynamics +
+ * observation sensors) for E independent environments on one B200.
+ *
+ * The reference (fahmyadan/SMARTS, 100% Python) has no FFI boundary; the entry points below are
+ * what a binding of its hot path would call.  Each one names the reference interface it replaces
+ * (paths relative to /root/reference).  All pointers are plain host or device addresses; there
+ * are no torch / C++ types in any signature.  INTEGRATION.md shows the ctypes stub.
+ *
+ * Conventions
+ *   - E envs, A agent slots per env, M social slots per env, V = A + M vehicle slots per env.
+ *     Vehicle arrays are indexed [e*V + slot]; slots 0..A-1 are agents.  Agent arrays are
+ *     indexed [e*A + a].
+ *   - Frames/angles follow smarts/core/coordinates.py:169-185: heading in radians, 0 = +y,
+ *     counter-clockwise, wrapped to (-pi, pi].
+ *   - Every function returns 0 on success, a negative SB_E* code otherwise; sb_last_error()
+ *     gives the message.  CUDA errors are sticky per handle.  No exceptions cross the ABI.
+ *   - Calls on one handle are not re-entrant.  sb_step/sb_observe only enqueue work on the
+ *     given stream (0 = legacy default stream) and return; the caller synchronises.
+ */
+#ifndef SMARTS_B200_H
+#define SMARTS_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SB_ABI_VERSION 1
+
+/* error codes */
+#define SB_OK 0
+#define SB_EINVAL (-1)   /* bad argument / config */
+#define SB_ECUDA (-2)    /* CUDA runtime error (sticky) */
+#define SB_ESTATE (-3)   /* call order: map / rays not uploaded, handle destroyed */
+#define SB_ENOMEM (-4)
+
+/* ActionSpaceType values, smarts/core/controllers/__init__.py:42-54 */
+#define SB_ACTION_CONTINUOUS 0
+#define SB_ACTION_LANE 1
+#define SB_ACTION_ACTUATOR_DYNAMIC 2
+#define SB_ACTION_LANE_WITH_CONTINUOUS_SPEED 3
+#define SB_ACTION_TRAJECTORY 5
+
+/* Lane action command codes (strings in the reference, controllers/__init__.py:136-143) */
+#define SB_LANE_KEEP 0
+#define SB_LANE_SLOW_DOWN 1
+#define SB_LANE_CHANGE_LEFT 2
+#define SB_LANE_CHANGE_RIGHT 3
+
+/* internal caps (status bit SB_STATUS_PATH_OVERFLOW is raised when exceeded) */
+#define SB_MAX_PATHS 16
+#define SB_MAX_LOOKAHEAD 64
+#define SB_MAX_TRAJ 32
+
+#define SB_STATUS_PATH_OVERFLOW 1u
+#define SB_STATUS_NO_WAYPOINTS 2u
+
+typedef struct SbHandle_ *SbHandle;
+
+/* Compiled from AgentInterface (smarts/core/agent_interface.py:209-277) + HiWayEnv kwargs
+ * (smarts/env/hiway_env.py:43-65).  One interface for all agents of a batch. */
+typedef struct SbConfig {
+  int32_t abi_version;     /* SB_ABI_VERSION */
+  int32_t device;          /* CUDA device ordinal */
+  int32_t n_envs;          /* E */
+  int32_t n_agents;        /* A */
+  int32_t n_social;        /* M */
+  double dt;               /* fixed_timestep_sec, hiway_env.py:112-113 */
+  int32_t substeps;        /* dynamics substeps per tick; 0 -> int(dt*240) (smarts.py:607-615) */
+  int32_t action_space;    /* SB_ACTION_* */
+  int32_t traj_len;        /* N points per Trajectory action (<= SB_MAX_TRAJ) */
+  int32_t route_cap;       /* max roads per agent route */
+  /* NeighborhoodVehicles (agent_interface.py:88-93, sensors.py:950-969) */
+  int32_t nbr_enable;
+  int32_t nbr_cap;         /* neighbours written per agent (StdObs: 10, format_obs.py:41) */
+  double nbr_radius;       /* < 0  ==  radius=None (all vehicles) */
+  /* Waypoints (agent_interface.py:74-79, sensors.py:972-988) */
+  int32_t wp_enable;
+  int32_t wp_lookahead;    /* sensor lookahead (default 32) */
+  int32_t wp_out_paths;    /* paths written per agent (StdObs: 4) */
+  int32_t wp_out_len;      /* waypoints written per path (StdObs: 20; raw: lookahead+1) */
+  /* Lidar (agent_interface.py:64-71, lidar.py, sensors.py:797-827) */
+  int32_t lidar_enable;
+  int32_t lidar_rays;      /* R, must equal the uploaded table */
+  int32_t lidar_miss_inf;  /* 1: miss -> (inf,inf,inf) as lidar.py:131; 0: zeros as format_obs.py:437-443 */
+  double lidar_wall_height;/* road-edge wall height in metres; 0 disables edges (reference has none) */
+  /* OGM / DrivableAreaGridMap (agent_interface.py:36-62, sensors.py:675-758) */
+  int32_t ogm_enable, ogm_width, ogm_height;
+  double ogm_resolution;
+  int32_t dagm_enable, dagm_width, dagm_height;
+  double dagm_resolution;
+} SbConfig;
+
+/* Per-scenario constant road map (host pointers, copied once).  Built by
+ * smarts_b200/road_map.py from a SUMO net.xml; restates SumoRoadNetwork + LanePoints
+ * (smarts/core/sumo_road_network.py, smarts/core/lanepoints.py). */
+typedef struct SbMap {
+  int32_t n_roads, n_lanes, n_lanepoints, n_shape_pts, n_polys, n_poly_verts, n_edges;
+  int32_t n_lane_out, n_lp_next;
+  double lanepoint_spacing;
+  /* roads */
+  const int32_t *road_lane_start, *road_lane_count;   /* [n_roads] lanes of a road are contiguous */
+  const uint8_t *road_is_junction;                     /* [n_roads] Edge.isSpecial() */
+  const int32_t *road_lp_start, *road_lp_count;        /* [n_roads] lane-point range */
+  const int32_t *road_first_out;                       /* [n_roads] first outgoing road or -1 (Road.outgoing_roads[0]) */
+  /* lanes */
+  const int32_t *lane_road, *lane_idx_in_road;         /* [n_lanes] */
+  const double *lane_width, *lane_speed, *lane_length; /* [n_lanes] */
+  const int32_t *lane_out_start;                       /* [n_lanes+1] CSR into lane_out */
+  const int32_t *lane_out;                             /* [n_lane_out] outgoing lane (via or to) */
+  const int32_t *lane_lp_start, *lane_lp_count;        /* [n_lanes] */
+  const int32_t *lane_shape_start;                     /* [n_lanes+1] CSR into shape_x/y */
+  /* lane points */
+  const double *lp_x, *lp_y, *lp_heading;              /* [n_lanepoints] */
+  const uint8_t *lp_inferred;                          /* [n_lanepoints] */
+  const int32_t *lp_lane;                              /* [n_lanepoints] */
+  const int32_t *lp_next_start;                        /* [n_lanepoints+1] CSR into lp_next */
+  const int32_t *lp_next;                              /* [n_lp_next] */
+  /* lane centre polylines */
+  const double *shape_x, *shape_y;                     /* [n_shape_pts] */
+  /* drivable-area convex polygons (3 or 4 vertices each) and road boundary segments */
+  const int32_t *poly_start;                           /* [n_polys+1] CSR into poly_x/y */
+  const double *poly_x, *poly_y;                       /* [n_poly_verts] */
+  const double *road_edges;                            /* [n_edges,4] ax,ay,bx,by */
+} SbMap;
+
+/* Device pointers owned by the library (valid until sb_destroy). */
+typedef struct SbStatePtrs {
+  /* vehicles [E*V]  (VehicleState, smarts/core/vehicle.py:53-80) */
+  double *pos_x, *pos_y, *pos_z, *heading, *speed, *yaw_rate;
+  double *length, *width, *height;
+  double *cos_h, *sin_h;     /* of heading, by the deterministic sincos of include/sb_detmath.h */
+  uint8_t *alive;
+  /* agents [E*A]  (AckermannChassis read-backs, smarts/core/chassis.py:493-566) */
+  double *steering;          /* chassis.steering (rad, clockwise positive) */
+  double *v_long, *v_lat;    /* longitudinal_lateral_speed */
+  double *ctrl;              /* [E*A, SB_CTRL_STATE] controller state */
+  double *last_control;      /* [E*A, 3] throttle, brake, steering applied this tick */
+  int32_t *route;            /* [E*A, route_cap] road indices, -1 padded */
+  int32_t *route_len;        /* [E*A] */
+  uint32_t *status;          /* [E*A] SB_STATUS_* bits, sticky until sb_reset */
+} SbStatePtrs;
+
+#define SB_CTRL_STATE 12
+
+/* Observation buffers (device, owned by the library).  Layouts are StdObs
+ * (smarts/env/wrappers/format_obs.py:45-197) so a Python view is zero-copy. */
+typedef struct SbObsPtrs {
+  /* ego (EgoVehicleObservation, sensors.py:65-101) */
+  int32_t *ego_lane;           /* [E*A] nearest lane index into the map or -1 (sensors.py:277-285) */
+  /* neighbours */
+  int32_t *nbr_count;          /* [E*A] total vehicles within radius (uncapped) */
+  int32_t *nbr_id;             /* [E*A, cap] vehicle slot within env, -1 padded */
+  double *nbr_pos;             /* [E*A, cap, 3] */
+  float *nbr_box;              /* [E*A, cap, 3] length,width,height */
+  float *nbr_heading;          /* [E*A, cap] */
+  float *nbr_speed;            /* [E*A, cap] */
+  int32_t *nbr_lane;           /* [E*A, cap] map lane index or -1 (sensors.py:244-254) */
+  int8_t *nbr_lane_index;      /* [E*A, cap] */
+  /* waypoints */
+  int32_t *wp_n_paths;         /* [E*A] total paths found (uncapped) */
+  int32_t *wp_len;             /* [E*A, P] */
+  double *wp_pos;              /* [E*A, P, L, 3] */
+  float *wp_heading;           /* [E*A, P, L] */
+  float *wp_lane_width;        /* [E*A, P, L] */
+  float *wp_speed_limit;       /* [E*A, P, L] */
+  int32_t *wp_lane;            /* [E*A, P, L] map lane index (lane_id) */
+  int8_t *wp_lane_index;       /* [E*A, P, L] */
+  /* lidar */
+  double *lidar_points;        /* [E*A, R, 3] */
+  int8_t *lidar_hits;          /* [E*A, R] */
+  /* grids */
+  uint8_t *ogm;                /* [E*A, H, W] */
+  uint8_t *dagm;               /* [E*A, H, W] */
+} SbObsPtrs;
+
+/* Initial / reset state for a set of envs (host pointers).  Replaces SMARTS.reset ->
+ * setup -> vehicle creation (smarts/core/smarts.py:365-460, vehicle.py:344-457). */
+typedef struct SbResetState {
+  const double *agent_x, *agent_y, *agent_heading, *agent_speed; /* [n, A] */
+  const int32_t *route;      /* [n, A, route_cap] or NULL (no route) */
+  const int32_t *route_len;  /* [n, A] or NULL */
+} SbResetState;
+
+/* HiWayEnv.__init__ -> SMARTS.__init__ (smarts/env/hiway_env.py:166-173, smarts/core/smarts.py:96-185) */
+int sb_create(const SbConfig *cfg, SbHandle *out);
+/* HiWayEnv.close / SMARTS.destroy (hiway_env.py:287-291, smarts.py:688-703) */
+void sb_destroy(SbHandle h);
+/* SMARTS.setup -> road map load (smarts.py:440-460; SumoRoadNetwork.from_spec, sumo_road_network.py:145-176) */
+int sb_upload_map(SbHandle h, const SbMap *map);
+/* Lidar._compute_rays base table (smarts/core/lidar.py:89-106); host [R,3] direction*max_distance */
+int sb_upload_lidar_rays(SbHandle h, const double *base_rays, int32_t n_rays);
+/* SMARTS.reset for a subset of envs (smarts.py:365-438); env_ids host [n] or NULL = all envs */
+int sb_reset(SbHandle h, const int32_t *env_ids, int32_t n, const SbResetState *init);
+/* Provider state injection (ExternalProvider.state_update, smarts/core/external_provider.py:44-51 ->
+ * BoxChassis.control, chassis.py:211-217).  dev_states: device [E, M, 8] doubles
+ * (x, y, heading, speed, length, width, height, alive) for this tick. */
+int sb_set_social(SbHandle h, const double *dev_states, void *stream);
+/* SMARTS._step_providers: Controllers.perform_action + chassis step (smarts.py:1048-1110,
+ * controllers/__init__.py:61-152).  dev_actions layout by action space:
+ *   LANE: int32 [E*A] command;  LANE_WITH_CONTINUOUS_SPEED: double [E*A,2] (speed, lane_change);
+ *   CONTINUOUS / ACTUATOR_DYNAMIC: double [E*A,3];  TRAJECTORY: double [E*A,4,N] (x,y,heading,speed). */
+int sb_step(SbHandle h, const void *dev_actions, void *stream);
+/* AgentManager.observe -> Sensors.observe for every agent (agent_manager.py:161-240, sensors.py:238-396) */
+int sb_observe(SbHandle h, void *stream);
+/* Convenience: the reference-facing call with HOST buffers (hiway_env.py:216-263 step()):
+ * copies actions and social states in, runs sb_set_social + sb_step + sb_observe, synchronises. */
+int sb_step_host(SbHandle h, const void *host_actions, int64_t action_bytes,
+                 const double *host_social);
+int sb_get_obs(SbHandle h, SbObsPtrs *out);
+int sb_get_state(SbHandle h, SbStatePtrs *out);
+/* number of kernel launches issued by this handle so far (bench gpu_launches) */
+int64_t sb_launch_count(SbHandle h);
+const char *sb_last_error(SbHandle h);
+int sb_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SMARTS_B200_H */

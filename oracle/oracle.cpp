@@ -1,0 +1,835 @@
+/*
+ * oracle.cpp -- second half of the CPU oracle: controllers, chassis, sensors and the C entry
+ * points used by tests/ and bench.py (ctypes).  TEST INFRASTRUCTURE ONLY -- see the header of
+ * oracle_core.hpp for what may call this and for the parity status of each part.
+ */
+#include "oracle_core.hpp"
+
+#include <atomic>
+#include <thread>
+
+namespace {
+
+// envs are independent, so the CPU baseline runs them on plain std::threads (dynamic chunks)
+template <class F>
+void parallel_for(int n, int threads, int chunk, F fn) {
+  if (threads <= 1 || n <= chunk) {
+    for (int i = 0; i < n; ++i) fn(i);
+    return;
+  }
+  std::atomic<int> next(0);
+  std::vector<std::thread> pool;
+  for (int t = 0; t < threads; ++t)
+    pool.emplace_back([&]() {
+      for (;;) {
+        int b = next.fetch_add(chunk);
+        if (b >= n) break;
+        int e = b + chunk < n ? b + chunk : n;
+        for (int i = b; i < e; ++i) fn(i);
+      }
+    });
+  for (auto& th : pool) th.join();
+}
+
+constexpr double kMaxSteeringWheel = 12.56 / 17.4;  // chassis.py:628-631, controller_parameters.yaml:23-25
+constexpr double kSteerLimit = 0.8727;              // models/vehicle.urdf:101
+constexpr double kWheelRadius = 0.31265, kMaxTorque = 1600.0, kMaxBrakeTorque = 1400.0;
+// 1 + 2356 + 2*1 + 4*15 kg (vehicle.urdf) plus the wheels' rotational inertia 4*Izz/r^2
+constexpr double kEffMass = 2419.0 + 4.0 * 2.0 / (kWheelRadius * kWheelRadius);
+constexpr double kRearAxleToCg = 1.5;  // wheels at y = +-1.5 (vehicle.urdf:96-135)
+
+struct Ego {
+  double x, y, h, speed, yaw_rate, v_long, v_lat;
+};
+
+// AckermannChassis.control, chassis.py:678-718: brake is dropped below 1/36 m/s.
+inline void apply_control(const Ego& v, double thr, double brake, double steer, double* out3) {
+  if (brake > 0 && v.v_long < 1.0 / 36.0) brake = 0;
+  out3[0] = thr;
+  out3[1] = brake;
+  out3[2] = steer;
+}
+
+// lane_following_controller.py:63-365.  st: [0] lateral_integral_error [1] integral_speed_error
+// [2] steering_state [3] throttle_state [4] speed_error [5,6] min_curvature_location [7] valid.
+// _update_target_lane_if_reached_end_of_lane (:439-473) only rewrites state.target_lane_id, which
+// feeds nothing but itself, so it is not restated.
+uint32_t lane_following(const Map& mp, const Ego& v, const int32_t* route, int route_len, double target_speed,
+                        int lane_change, double dt, double* st, double* out3) {
+  static thread_local PathSet ps;
+  waypoint_paths(mp, v.x, v.y, v.h, 16, 5.0, route, route_len, &ps);
+  uint32_t status = ps.overflow ? SB_STATUS_PATH_OVERFLOW : 0u;
+  if (ps.n == 0) {
+    apply_control(v, 0, 0, 0, out3);
+    return status | SB_STATUS_NO_WAYPOINTS;
+  }
+  // find_current_lane, :367-374
+  int current = 0;
+  double bd = 0;
+  for (int i = 0; i < ps.n; ++i) {
+    double dx = ps.wp[i][0].x - v.x, dy = ps.wp[i][0].y - v.y;
+    double d = std::sqrt(dx * dx + dy * dy);
+    if (i == 0 || d < bd) {
+      current = i;
+      bd = d;
+    }
+  }
+  int sel = current + lane_change;
+  sel = sel < 0 ? 0 : (sel > ps.n - 1 ? ps.n - 1 : sel);
+  const Waypoint* wp = ps.wp[sel];
+  const int L = ps.len[sel];
+
+  double ewma = 0.0;
+  for (int i = L - 2; i >= 0; --i)
+    ewma = lerp(ewma, degrees(std::fabs(wrap_heading(wp[i].heading - wp[i + 1].heading))), 0.03);
+  double curv = clipd(ewma / 2.5, 0, 1);
+  int npts = L < 10 ? L : 10;
+  double tx[10], ty[10], th[10];
+  for (int i = 0; i < npts; ++i) {
+    tx[i] = wp[i].x;
+    ty[i] = wp[i].y;
+    th[i] = wp[i].heading;
+  }
+  double lac = std::fabs(curvature_calculation(tx, ty, th, npts, 4));
+  if (lac <= 2) {
+    st[5] = wp[4].x;
+    st[6] = wp[4].y;
+    st[7] = 1.0;
+  }
+  int la = curv > 0.5 ? 3 : 4;
+  if (la > L - 1) la = L - 1;
+  double ref_h = wp[0].heading;
+  double ddx = wp[la].x - v.x, ddy = wp[la].y - v.y;
+  double lad = std::sqrt(ddx * ddx + ddy * ddy);
+  double sh, ch;
+  sb_sincos(v.h, &sh, &ch);
+  double lx = v.x - lad * sh, ly = v.y + lad * ch;
+
+  double raw;
+  if (curv < 0.3) {
+    raw = -3.6 * 1.8 * (v.speed - target_speed);
+  } else if (curv > 0.3 && curv < 0.8) {
+    raw = -0.6 * 3.6 * (v.speed - clipd(target_speed, 0, 6.94));
+  } else {
+    raw = -0.6 * 3.6 * (v.speed - clipd(target_speed, 0, 5.56));
+  }
+  double speed_error = v.speed - target_speed;
+  st[1] += speed_error * dt;
+  double damping = (speed_error - st[4]) / dt;
+  double lfc = 1.5;
+  if (v.speed < 8 || target_speed < 6) lfc = 0;
+  raw += (-0.2 * damping - 0.1 * st[1]) + std::fabs(lfc * sb_sin(st[2] * kMaxSteeringWheel));
+  st[4] = speed_error;
+  if (st[7] != 0.0) {
+    double mx = v.x - st[5], my = v.y - st[6];
+    if (std::sqrt(mx * mx + my * my) < 2) ref_h = wp[la].heading;
+  }
+  double Kh, Kl;
+  lateral_gains(target_speed, &Kh, &Kl);
+  double dvx, dvy;
+  radians_to_vec(wp[la].heading, &dvx, &dvy);
+  double lat_err = signed_dist_to_line(lx, ly, wp[la].x, wp[la].y, dvx, dvy);
+  double Rc = curvature_calculation(tx, ty, th, npts);
+  double brake = 0, thr;
+  if (raw < 0) {
+    brake = clipd(-raw, 0, 1);
+    thr = 0;
+  } else {
+    double tg;
+    if (v.speed > 70 / 3.6 && std::fabs(Rc) <= 1e3)
+      tg = 4.5;
+    else if (40 / 3.6 <= v.speed && v.speed <= 70 / 3.6 && std::fabs(Rc) <= 3)
+      tg = 2.5;
+    else
+      tg = 0.5;
+    thr = clipd(raw - tg * 3.6 * std::fabs(v.v_lat), 0, 1);
+  }
+  st[0] += dt * lat_err;
+  double ffg = std::fabs(Rc) < 7 ? 0.45 : 0.15;
+  double ff = 1 * ffg * (1 / Rc) * (v.speed * v.speed);
+  double ns = clipd(v.speed * 3.6 / 100, 0, 1);
+  double hsg = -lerp(0.5, 14, ns);
+  double yrg = lerp(5.75, 11.75, ns);
+  double lsg = clipd(lerp(-1, 14, ns), 1, 2);
+  double max_s = 1;
+  if (std::fabs(Rc) > 1e7 && lane_change != 0) {
+    hsg = -4.95;
+    yrg = 1;
+    lsg = 0.22;
+    max_s = 0.12;
+  }
+  double herr = angdiff(sb_pymod(v.h, kTwoPi), ref_h);
+  double steer = clipd(-hsg * degrees(Kh) * herr + lsg * Kl * lat_err + yrg * v.yaw_rate + 0.3 * st[0] - ff, -max_s,
+                       max_s);
+  st[2] = low_pass(steer, st[2], 5.5, dt);
+  st[3] = low_pass(thr, st[3], 2, dt, 0);
+  apply_control(v, st[3], brake, st[2], out3);
+  return status;
+}
+
+// trajectory_tracking_controller.py:176-331 with the sedan parameters of
+// models/controller_parameters.yaml:3-16.  st: [0] heading_error [1] lateral_error
+// [2] velocity_error [3] integral_velocity_error [4] integral_windup_error [5] steering_state
+// [6] throttle_state.  traj = x[N], y[N], heading[N], speed[N].
+void trajectory_tracking(const Ego& v, const double* traj, int N, double dt, double* st, double* out3) {
+  const double* tx = traj;
+  const double* ty = traj + N;
+  const double* th = traj + 2 * N;
+  const double* tv = traj + 3 * N;
+  const double final_steering_filter_constant = 23.5;
+  double throttle_filter_constant = 22.5;
+  const double velocity_gain = 5.1, velocity_integral_gain = 0, traction_gain = 6;
+  const double initial_look_ahead_distant = 6, derivative_activation = 1;
+  const bool speed_reduction = true;
+  const double velocity_damping_gain = 0.001, windup_gain = 0.01;
+
+  double lateral_gain = 0.61, heading_gain = 0.01, led_gain = 0.15, hed_gain = 0.5;
+  double ns = clipd((3.6 * tv[0] - 20) / (80 - 20), 0, 1);
+  if (v.speed > 70 / 3.6) {
+    lateral_gain = 1.51;
+    hed_gain = 0.1;
+  }
+  double steering_filter_constant = lerp(12, final_steering_filter_constant, ns);
+  if (std::fabs(angdiff(th[N - 1], th[0])) > 2) throttle_filter_constant = 2.5;
+  if (std::fabs(curvature_calculation(tx, ty, th, N, 0, 3)) < 150) {
+    heading_gain = 0.05;
+    led_gain = 0.015;
+    hed_gain = 0.05;
+  }
+  // calculate_heading_lateral_error, :397-441
+  double heading_error = angdiff(sb_pymod(v.h, kTwoPi), th[0]);
+  double look_dist = initial_look_ahead_distant;
+  int look_pts = (int)initial_look_ahead_distant;
+  double ahead_curv = std::fabs(curvature_calculation(tx, ty, th, N, 4));
+  if (ahead_curv < 30 && speed_reduction) {
+    look_dist = 1;
+    look_pts = 1;
+  }
+  int j = look_pts < N - 1 ? look_pts : N - 1;
+  double pvx, pvy;
+  radians_to_vec(th[j], &pvx, &pvy);
+  double sh, ch;
+  sb_sincos(v.h, &sh, &ch);
+  double lx = v.x - look_dist * sh, ly = v.y + look_dist * ch;
+  double lateral_error = signed_dist_to_line(lx, ly, tx[j], ty[j], pvx, pvy);
+
+  double Rc = curvature_calculation(tx, ty, th, N);
+  double derivative_term = hed_gain * v.yaw_rate + led_gain * (lateral_error - st[1]) / dt;
+  double ff = 0.1 * (1 / Rc) * (v.speed * v.speed);
+  double steering_raw = clipd(
+      derivative_activation * derivative_term + degrees(heading_gain * heading_error) + 1 * lateral_gain * lateral_error - ff,
+      -1, 1);
+  st[5] = low_pass(steering_raw, st[5], steering_filter_constant, dt);
+
+  // calculate_raw_throttle_feedback, :333-395
+  double desired_speed = tv[N - 1];
+  if (ahead_curv < 30 && speed_reduction)
+    desired_speed = clipd(0.8 * desired_speed, 0, 8.3);
+  else if (ahead_curv < 100 && speed_reduction)
+    desired_speed *= 0.8;
+  double velocity_error = v.speed - desired_speed;
+  double ved = (velocity_error - st[2]) / dt;
+  double raw_throttle = 3.6 * (-0.5 * velocity_gain * velocity_error -
+                               velocity_integral_gain * (st[3] + windup_gain * st[4]) - velocity_damping_gain * ved);
+  st[2] = velocity_error;
+  st[4] = clipd(raw_throttle, -1, 1) - raw_throttle;
+  st[6] = low_pass(raw_throttle, st[6], throttle_filter_constant, dt, -1, -traction_gain * std::fabs(v.v_lat));
+  double thr, brake;
+  if (st[6] > 0) {
+    brake = 0;
+    thr = clipd(st[6], 0, 1);
+  } else {
+    brake = clipd(-st[6], 0, 1);
+    thr = 0;
+  }
+  st[0] = heading_error;
+  st[1] = lateral_error;
+  st[3] += (v.speed - desired_speed) * dt;
+  apply_control(v, thr, brake, st[5], out3);
+}
+
+// Kinematic stand-in for the pybullet AckermannChassis step (DESIGN.md
+// "Vehicle model"): CG-referenced kinematic bicycle, `substeps` explicit Euler sub-steps.
+void chassis_step(World& w, int ai, int vi) {
+  const double* c = &w.last_control[(size_t)ai * 3];
+  double delta = -c[2] * kMaxSteeringWheel;  // chassis.py:790-793 (joint angle, left positive)
+  delta = clipd(delta, -kSteerLimit, kSteerLimit);
+  double acc = 4.0 * (c[0] * kMaxTorque - c[1] * kMaxBrakeTorque) / kWheelRadius / kEffMass;
+  double sd, cd;
+  sb_sincos(delta, &sd, &cd);
+  double beta = sb_atan2(0.5 * sd, cd);
+  double sbeta, cbeta;
+  sb_sincos(beta, &sbeta, &cbeta);
+  const int n = w.substeps;
+  const double hdt = w.cfg.dt / (double)n;
+  double x = w.pos_x[vi], y = w.pos_y[vi], h = w.heading[vi], v = w.speed[vi];
+  double omega = 0.0;
+  for (int k = 0; k < n; ++k) {
+    v = v + acc * hdt;
+    if (v < 0) v = 0;
+    double s, cc;
+    sb_sincos(h + beta, &s, &cc);
+    x = x - (v * s) * hdt;
+    y = y + (v * cc) * hdt;
+    omega = (v / kRearAxleToCg) * sbeta;
+    h = h + omega * hdt;
+  }
+  h = wrap_heading(h);
+  w.pos_x[vi] = x;
+  w.pos_y[vi] = y;
+  w.heading[vi] = h;
+  w.speed[vi] = v;
+  w.yaw_rate[vi] = omega;
+  sb_sincos(h, &w.sin_h[vi], &w.cos_h[vi]);
+  w.steering[ai] = -delta;  // chassis.py:513-528
+  w.v_long[ai] = v * cbeta; // chassis.py:558-566
+  w.v_lat[ai] = -(v * sbeta);
+}
+
+// ---------------------------------------------------------------- sensors
+// smarts.py:1191-1208 + sensors.py:241-266
+void observe_neighbors(World& w, int e, int a) {
+  const int V = w.V, cap = w.cfg.nbr_cap;
+  const int ai = e * w.A + a, vi = e * V + a;
+  int cnt = 0;
+  for (int k = 0; k < cap; ++k) {
+    size_t o = (size_t)ai * cap + k;
+    w.nbr_id[o] = -1;
+    w.nbr_lane[o] = -1;
+    w.nbr_lane_index[o] = 0;
+    w.nbr_heading[o] = 0;
+    w.nbr_speed[o] = 0;
+    for (int c = 0; c < 3; ++c) {
+      w.nbr_pos[o * 3 + c] = 0;
+      w.nbr_box[o * 3 + c] = 0;
+    }
+  }
+  for (int j = 0; j < V; ++j) {
+    if (j == a) continue;
+    int vj = e * V + j;
+    if (!w.alive[vj]) continue;
+    if (w.cfg.nbr_radius >= 0) {
+      double dx = w.pos_x[vj] - w.pos_x[vi], dy = w.pos_y[vj] - w.pos_y[vi], dz = w.pos_z[vj] - w.pos_z[vi];
+      double d = std::sqrt((dx * dx + dy * dy) + dz * dz);
+      if (!(d <= w.cfg.nbr_radius)) continue;
+    }
+    if (cnt < cap) {
+      size_t o = (size_t)ai * cap + cnt;
+      w.nbr_id[o] = j;
+      w.nbr_pos[o * 3 + 0] = w.pos_x[vj];
+      w.nbr_pos[o * 3 + 1] = w.pos_y[vj];
+      w.nbr_pos[o * 3 + 2] = w.pos_z[vj];
+      w.nbr_box[o * 3 + 0] = (float)w.length[vj];
+      w.nbr_box[o * 3 + 1] = (float)w.width[vj];
+      w.nbr_box[o * 3 + 2] = (float)w.height[vj];
+      w.nbr_heading[o] = (float)w.heading[vj];
+      w.nbr_speed[o] = (float)w.speed[vj];
+      int lane = nearest_lane(w.map, w.pos_x[vj], w.pos_y[vj], w.length[vi]);
+      w.nbr_lane[o] = lane;
+      w.nbr_lane_index[o] = lane >= 0 ? (int8_t)w.map.lane_idx_in_road[lane] : 0;
+    }
+    ++cnt;
+  }
+  w.nbr_count[ai] = cnt;
+}
+
+// sensors.py:972-988 -> waypoint_paths; StdObs layout format_obs.py:546-604
+void observe_waypoints(World& w, int e, int a) {
+  static thread_local PathSet ps;
+  const int ai = e * w.A + a, vi = e * w.V + a;
+  const int P = w.cfg.wp_out_paths, L = w.cfg.wp_out_len;
+  waypoint_paths(w.map, w.pos_x[vi], w.pos_y[vi], w.heading[vi], w.cfg.wp_lookahead, 5.0,
+                 &w.route[(size_t)ai * w.cfg.route_cap], w.route_len[ai], &ps);
+  if (ps.overflow) w.status[ai] |= SB_STATUS_PATH_OVERFLOW;
+  w.wp_n_paths[ai] = ps.total;
+  for (int p = 0; p < P; ++p) {
+    int len = p < ps.n ? std::min(ps.len[p], L) : 0;
+    w.wp_len[(size_t)ai * P + p] = len;
+    for (int i = 0; i < L; ++i) {
+      size_t o = ((size_t)ai * P + p) * L + i;
+      if (i < len) {
+        const Waypoint& q = ps.wp[p][i];
+        w.wp_pos[o * 3 + 0] = q.x;
+        w.wp_pos[o * 3 + 1] = q.y;
+        w.wp_pos[o * 3 + 2] = 0.0;
+        w.wp_heading[o] = (float)q.heading;
+        w.wp_lane_width[o] = (float)q.lane_width;
+        w.wp_speed_limit[o] = (float)q.speed_limit;
+        w.wp_lane[o] = q.lane;
+        w.wp_lane_index[o] = (int8_t)q.lane_index;
+      } else {
+        w.wp_pos[o * 3 + 0] = w.wp_pos[o * 3 + 1] = w.wp_pos[o * 3 + 2] = 0.0;
+        w.wp_heading[o] = w.wp_lane_width[o] = w.wp_speed_limit[o] = 0.f;
+        w.wp_lane[o] = -1;
+        w.wp_lane_index[o] = 0;
+      }
+    }
+  }
+}
+
+// lidar.py:74-134 + sensors.py:797-827.  Hittable set: ground plane z = 0
+// (plane.urdf), every other alive vehicle's box (agents z in [0.1, 1.1] above their base,
+// vehicle.urdf:12-16; social boxes z in [0.2, 0.2 + height], utils/bullet.py:169-177) and,
+// when lidar_wall_height > 0, vertical walls on the road boundary segments.
+void observe_lidar(World& w, int e, int a) {
+  const int R = w.cfg.lidar_rays, V = w.V;
+  const int ai = e * w.A + a, vi = e * V + a;
+  const double ox = w.pos_x[vi], oy = w.pos_y[vi], oz = w.pos_z[vi] + 1.0;
+  const double inf = std::numeric_limits<double>::infinity();
+  const double miss = w.cfg.lidar_miss_inf ? inf : 0.0;
+  for (int r = 0; r < R; ++r) {
+    const double dx = w.rays[r * 3 + 0], dy = w.rays[r * 3 + 1], dz = w.rays[r * 3 + 2];
+    double tbest = 2.0;
+    if (dz < 0.0) {
+      double t = (0.0 - oz) / dz;
+      if (t >= 0.0 && t <= 1.0) tbest = t;
+    }
+    for (int j = 0; j < V; ++j) {
+      if (j == a) continue;
+      int vj = e * V + j;
+      if (!w.alive[vj]) continue;
+      double c = w.cos_h[vj], s = w.sin_h[vj];
+      double rx = ox - w.pos_x[vj], ry = oy - w.pos_y[vj];
+      // box frame: u = right (width), f = forward (length)
+      double lo_[3], ld_[3], mn[3], mx[3];
+      lo_[0] = rx * c + ry * s;
+      lo_[1] = ry * c - rx * s;
+      lo_[2] = oz;
+      ld_[0] = dx * c + dy * s;
+      ld_[1] = dy * c - dx * s;
+      ld_[2] = dz;
+      double hw = 0.5 * w.width[vj], hl = 0.5 * w.length[vj];
+      double z0 = w.pos_z[vj] + (j < w.A ? 0.1 : 0.2);
+      mn[0] = -hw; mx[0] = hw;
+      mn[1] = -hl; mx[1] = hl;
+      mn[2] = z0;  mx[2] = z0 + w.height[vj];
+      double t0 = -inf, t1 = inf;
+      bool ok = true;
+      for (int k = 0; k < 3 && ok; ++k) {
+        if (ld_[k] == 0.0) {
+          if (lo_[k] < mn[k] || lo_[k] > mx[k]) ok = false;
+        } else {
+          double ta = (mn[k] - lo_[k]) / ld_[k], tb = (mx[k] - lo_[k]) / ld_[k];
+          if (ta > tb) std::swap(ta, tb);
+          if (ta > t0) t0 = ta;
+          if (tb < t1) t1 = tb;
+        }
+      }
+      if (!ok || t0 > t1 || t0 < 0.0 || t0 > 1.0) continue;  // origin inside a box: no hit
+      if (t0 < tbest) tbest = t0;
+    }
+    if (w.cfg.lidar_wall_height > 0.0) {
+      const int NE = w.map.m.n_edges;
+      for (int k = 0; k < NE; ++k) {
+        const double* ed = &w.map.road_edges[(size_t)k * 4];
+        double ex = ed[2] - ed[0], ey = ed[3] - ed[1];
+        double den = dx * ey - dy * ex;
+        if (den == 0.0) continue;
+        double qx = ed[0] - ox, qy = ed[1] - oy;
+        double t = (qx * ey - qy * ex) / den;
+        double u = (qx * dy - qy * dx) / den;
+        if (t < 0.0 || t > 1.0 || u < 0.0 || u > 1.0) continue;
+        double z = oz + t * dz;
+        if (z < 0.0 || z > w.cfg.lidar_wall_height) continue;
+        if (t < tbest) tbest = t;
+      }
+    }
+    size_t o = (size_t)ai * R + r;
+    if (tbest <= 1.0) {
+      w.lidar_hits[o] = 1;
+      w.lidar_points[o * 3 + 0] = ox + tbest * dx;
+      w.lidar_points[o * 3 + 1] = oy + tbest * dy;
+      w.lidar_points[o * 3 + 2] = oz + tbest * dz;
+    } else {
+      w.lidar_hits[o] = 0;
+      w.lidar_points[o * 3 + 0] = w.lidar_points[o * 3 + 1] = w.lidar_points[o * 3 + 2] = miss;
+    }
+  }
+}
+
+// Raster contract (DESIGN.md "Grid maps"): camera = renderer.py:325-336, :383-386 (orthographic,
+// film W*res x H*res centred on the ego, rotated by the ego heading, rows flipped so row 0 is
+// ahead: sensors.py:706, :748).  World vertices go to pixel space in binary64, are snapped to
+// 1/256 px (round-half-even), and a pixel is covered iff its centre satisfies every edge function
+// of the convex polygon (inclusive), evaluated in exact integer arithmetic.
+struct Cam {
+  double px, py, c, s, res, halfw, halfh;
+};
+inline void to_pixel(const Cam& cam, double x, double y, int64_t* U, int64_t* Vv) {
+  double dx = x - cam.px, dy = y - cam.py;
+  double xr = dx * cam.c + dy * cam.s;
+  double yr = dy * cam.c - dx * cam.s;
+  double u = xr / cam.res + cam.halfw;
+  double v = cam.halfh - yr / cam.res;
+  double su = rint(u * 256.0), sv = rint(v * 256.0);
+  const double lim = 1073741824.0;
+  su = su > lim ? lim : (su < -lim ? -lim : su);
+  sv = sv > lim ? lim : (sv < -lim ? -lim : sv);
+  *U = (int64_t)su;
+  *Vv = (int64_t)sv;
+}
+
+void fill_convex(uint8_t* img, int W, int H, const int64_t* U, const int64_t* Vv, int n) {
+  int64_t area2 = 0;
+  for (int i = 0; i < n; ++i) {
+    int j = (i + 1) % n;
+    area2 += U[i] * Vv[j] - U[j] * Vv[i];
+  }
+  if (area2 == 0) return;
+  int64_t sg = area2 > 0 ? 1 : -1;
+  int64_t umin = U[0], umax = U[0], vmin = Vv[0], vmax = Vv[0];
+  for (int i = 1; i < n; ++i) {
+    umin = std::min(umin, U[i]); umax = std::max(umax, U[i]);
+    vmin = std::min(vmin, Vv[i]); vmax = std::max(vmax, Vv[i]);
+  }
+  // pixel centre c*256+128 within [min,max]
+  auto lo = [](int64_t m) { int64_t t = m - 128; return t <= 0 ? (int64_t)0 : (t + 255) / 256; };
+  auto hi = [](int64_t m) { int64_t t = m - 128; return t < 0 ? (int64_t)-1 : t / 256; };
+  int64_t c0 = lo(umin), c1 = std::min<int64_t>(hi(umax), W - 1);
+  int64_t r0 = lo(vmin), r1 = std::min<int64_t>(hi(vmax), H - 1);
+  for (int64_t r = r0; r <= r1; ++r) {
+    int64_t py = r * 256 + 128;
+    for (int64_t c = c0; c <= c1; ++c) {
+      int64_t px = c * 256 + 128;
+      bool in = true;
+      for (int i = 0; i < n && in; ++i) {
+        int j = (i + 1) % n;
+        int64_t ev = (U[j] - U[i]) * (py - Vv[i]) - (Vv[j] - Vv[i]) * (px - U[i]);
+        if (sg * ev < 0) in = false;
+      }
+      if (in) img[r * W + c] = 255;
+    }
+  }
+}
+
+// sensors.py:719-758 (vehicles only, ego included: test_observations.py:179-187)
+void observe_ogm(World& w, int e, int a) {
+  const int W = w.cfg.ogm_width, H = w.cfg.ogm_height, V = w.V;
+  const int ai = e * w.A + a, vi = e * V + a;
+  uint8_t* img = &w.ogm[(size_t)ai * W * H];
+  std::memset(img, 0, (size_t)W * H);
+  Cam cam{w.pos_x[vi], w.pos_y[vi], w.cos_h[vi], w.sin_h[vi], w.cfg.ogm_resolution, 0.5 * W, 0.5 * H};
+  for (int j = 0; j < V; ++j) {
+    int vj = e * V + j;
+    if (!w.alive[vj]) continue;
+    double c = w.cos_h[vj], s = w.sin_h[vj];
+    double hw = 0.5 * w.width[vj], hl = 0.5 * w.length[vj];
+    const double sa[4] = {-hw, hw, hw, -hw}, sb_[4] = {-hl, -hl, hl, hl};
+    int64_t U[4], Vv[4];
+    for (int k = 0; k < 4; ++k) {
+      double x = w.pos_x[vj] + (sa[k] * c - sb_[k] * s);
+      double y = w.pos_y[vj] + (sa[k] * s + sb_[k] * c);
+      to_pixel(cam, x, y, &U[k], &Vv[k]);
+    }
+    fill_convex(img, W, H, U, Vv, 4);
+  }
+}
+
+// sensors.py:675-716 (road surface only)
+void observe_dagm(World& w, int e, int a) {
+  const int W = w.cfg.dagm_width, H = w.cfg.dagm_height;
+  const int ai = e * w.A + a, vi = e * w.V + a;
+  uint8_t* img = &w.dagm[(size_t)ai * W * H];
+  std::memset(img, 0, (size_t)W * H);
+  Cam cam{w.pos_x[vi], w.pos_y[vi], w.cos_h[vi], w.sin_h[vi], w.cfg.dagm_resolution, 0.5 * W, 0.5 * H};
+  const Map& mp = w.map;
+  for (int p = 0; p < mp.m.n_polys; ++p) {
+    int s = mp.poly_start[p], n = mp.poly_start[p + 1] - s;
+    if (n < 3 || n > 8) continue;
+    int64_t U[8], Vv[8];
+    for (int k = 0; k < n; ++k) to_pixel(cam, mp.poly_x[s + k], mp.poly_y[s + k], &U[k], &Vv[k]);
+    fill_convex(img, W, H, U, Vv, n);
+  }
+}
+
+void observe_agent(World& w, int e, int a) {
+  const int ai = e * w.A + a, vi = e * w.V + a;
+  // sensors.py:277-285, radius None -> max(10, 2 * default lane width) (sumo_road_network.py:679-680)
+  w.ego_lane[ai] = nearest_lane(w.map, w.pos_x[vi], w.pos_y[vi], std::max(10.0, 2 * 3.2));
+  if (w.cfg.nbr_enable) observe_neighbors(w, e, a);
+  if (w.cfg.wp_enable) observe_waypoints(w, e, a);
+  if (w.cfg.lidar_enable) observe_lidar(w, e, a);
+  if (w.cfg.ogm_enable) observe_ogm(w, e, a);
+  if (w.cfg.dagm_enable) observe_dagm(w, e, a);
+}
+
+}  // namespace
+
+// ==================================================================== C entry points (ctypes)
+extern "C" {
+
+void* or_create(const SbConfig* cfg, const SbMap* m, const double* base_rays, int n_rays) {
+  World* w = new World();
+  w->cfg = *cfg;
+  Map& mp = w->map;
+  mp.m = *m;
+  cp(mp.road_lane_start, m->road_lane_start, m->n_roads);
+  cp(mp.road_lane_count, m->road_lane_count, m->n_roads);
+  cp(mp.road_is_junction, m->road_is_junction, m->n_roads);
+  cp(mp.road_lp_start, m->road_lp_start, m->n_roads);
+  cp(mp.road_lp_count, m->road_lp_count, m->n_roads);
+  cp(mp.road_first_out, m->road_first_out, m->n_roads);
+  cp(mp.lane_road, m->lane_road, m->n_lanes);
+  cp(mp.lane_idx_in_road, m->lane_idx_in_road, m->n_lanes);
+  cp(mp.lane_width, m->lane_width, m->n_lanes);
+  cp(mp.lane_speed, m->lane_speed, m->n_lanes);
+  cp(mp.lane_length, m->lane_length, m->n_lanes);
+  cp(mp.lane_out_start, m->lane_out_start, m->n_lanes + 1);
+  cp(mp.lane_out, m->lane_out, std::max(m->n_lane_out, 1));
+  cp(mp.lane_lp_start, m->lane_lp_start, m->n_lanes);
+  cp(mp.lane_lp_count, m->lane_lp_count, m->n_lanes);
+  cp(mp.lane_shape_start, m->lane_shape_start, m->n_lanes + 1);
+  cp(mp.lp_x, m->lp_x, m->n_lanepoints);
+  cp(mp.lp_y, m->lp_y, m->n_lanepoints);
+  cp(mp.lp_heading, m->lp_heading, m->n_lanepoints);
+  cp(mp.lp_inferred, m->lp_inferred, m->n_lanepoints);
+  cp(mp.lp_lane, m->lp_lane, m->n_lanepoints);
+  cp(mp.lp_next_start, m->lp_next_start, m->n_lanepoints + 1);
+  cp(mp.lp_next, m->lp_next, std::max(m->n_lp_next, 1));
+  cp(mp.shape_x, m->shape_x, m->n_shape_pts);
+  cp(mp.shape_y, m->shape_y, m->n_shape_pts);
+  cp(mp.poly_start, m->poly_start, m->n_polys + 1);
+  cp(mp.poly_x, m->poly_x, m->n_poly_verts);
+  cp(mp.poly_y, m->poly_y, m->n_poly_verts);
+  cp(mp.road_edges, m->road_edges, (size_t)m->n_edges * 4);
+  if (base_rays && n_rays > 0) w->rays.assign(base_rays, base_rays + (size_t)n_rays * 3);
+  w->E = cfg->n_envs;
+  w->A = cfg->n_agents;
+  w->M = cfg->n_social;
+  w->V = w->A + w->M;
+  w->substeps = cfg->substeps > 0 ? cfg->substeps : std::max(1, (int)(cfg->dt * 240));
+  size_t nv = (size_t)w->E * w->V, na = (size_t)w->E * w->A;
+  for (auto* v : {&w->pos_x, &w->pos_y, &w->pos_z, &w->heading, &w->speed, &w->yaw_rate, &w->length, &w->width,
+                  &w->height, &w->cos_h, &w->sin_h})
+    v->assign(nv, 0.0);
+  for (size_t i = 0; i < nv; ++i) w->cos_h[i] = 1.0;
+  w->alive.assign(nv, 0);
+  w->steering.assign(na, 0.0);
+  w->v_long.assign(na, 0.0);
+  w->v_lat.assign(na, 0.0);
+  w->ctrl.assign(na * SB_CTRL_STATE, 0.0);
+  w->last_control.assign(na * 3, 0.0);
+  w->route.assign(na * std::max(cfg->route_cap, 1), -1);
+  w->route_len.assign(na, 0);
+  w->status.assign(na, 0);
+  w->ego_lane.assign(na, -1);
+  if (cfg->nbr_enable) {
+    size_t n = na * cfg->nbr_cap;
+    w->nbr_count.assign(na, 0);
+    w->nbr_id.assign(n, -1);
+    w->nbr_lane.assign(n, -1);
+    w->nbr_pos.assign(n * 3, 0);
+    w->nbr_box.assign(n * 3, 0);
+    w->nbr_heading.assign(n, 0);
+    w->nbr_speed.assign(n, 0);
+    w->nbr_lane_index.assign(n, 0);
+  }
+  if (cfg->wp_enable) {
+    size_t np = na * cfg->wp_out_paths, n = np * cfg->wp_out_len;
+    w->wp_n_paths.assign(na, 0);
+    w->wp_len.assign(np, 0);
+    w->wp_pos.assign(n * 3, 0);
+    w->wp_heading.assign(n, 0);
+    w->wp_lane_width.assign(n, 0);
+    w->wp_speed_limit.assign(n, 0);
+    w->wp_lane.assign(n, -1);
+    w->wp_lane_index.assign(n, 0);
+  }
+  if (cfg->lidar_enable) {
+    w->lidar_points.assign(na * cfg->lidar_rays * 3, 0);
+    w->lidar_hits.assign(na * cfg->lidar_rays, 0);
+  }
+  if (cfg->ogm_enable) w->ogm.assign(na * cfg->ogm_width * cfg->ogm_height, 0);
+  if (cfg->dagm_enable) w->dagm.assign(na * cfg->dagm_width * cfg->dagm_height, 0);
+  return w;
+}
+
+void or_destroy(void* h) { delete static_cast<World*>(h); }
+void or_set_threads(void* h, int n) { static_cast<World*>(h)->threads = n < 1 ? 1 : n; }
+
+// SMARTS.reset for a subset of envs: agents placed at their mission start, sedan chassis
+// dimensions (vehicle.urdf:12-16), social slots cleared.
+void or_reset(void* h, const int32_t* env_ids, int n, const SbResetState* init) {
+  World& w = *static_cast<World*>(h);
+  if (!env_ids) n = w.E;
+  for (int i = 0; i < n; ++i) {
+    int e = env_ids ? env_ids[i] : i;
+    for (int a = 0; a < w.A; ++a) {
+      int ai = e * w.A + a, vi = e * w.V + a;
+      size_t src = (size_t)i * w.A + a;
+      w.pos_x[vi] = init->agent_x[src];
+      w.pos_y[vi] = init->agent_y[src];
+      w.pos_z[vi] = 0.0;
+      w.heading[vi] = wrap_heading(init->agent_heading[src]);
+      w.speed[vi] = init->agent_speed[src];
+      w.yaw_rate[vi] = 0.0;
+      w.length[vi] = 3.68;
+      w.width[vi] = 1.47;
+      w.height[vi] = 1.0;
+      sb_sincos(w.heading[vi], &w.sin_h[vi], &w.cos_h[vi]);
+      w.alive[vi] = 1;
+      w.steering[ai] = 0.0;
+      w.v_long[ai] = w.speed[vi];
+      w.v_lat[ai] = 0.0;
+      for (int k = 0; k < SB_CTRL_STATE; ++k) w.ctrl[(size_t)ai * SB_CTRL_STATE + k] = 0.0;
+      for (int k = 0; k < 3; ++k) w.last_control[(size_t)ai * 3 + k] = 0.0;
+      w.status[ai] = 0;
+      int rc = w.cfg.route_cap;
+      for (int k = 0; k < rc; ++k) w.route[(size_t)ai * rc + k] = init->route ? init->route[src * rc + k] : -1;
+      w.route_len[ai] = init->route_len ? init->route_len[src] : 0;
+    }
+    for (int j = w.A; j < w.V; ++j) {
+      int vj = e * w.V + j;
+      w.alive[vj] = 0;
+      w.pos_x[vj] = w.pos_y[vj] = w.pos_z[vj] = w.heading[vj] = w.speed[vj] = w.yaw_rate[vj] = 0.0;
+      w.length[vj] = w.width[vj] = w.height[vj] = 0.0;
+      w.cos_h[vj] = 1.0;
+      w.sin_h[vj] = 0.0;
+    }
+  }
+}
+
+// BoxChassis.control + yaw_rate, chassis.py:211-217, :302-308.  states: host [E, M, 8].
+void or_set_social(void* h, const double* states) {
+  World& w = *static_cast<World*>(h);
+  for (int e = 0; e < w.E; ++e)
+    for (int m = 0; m < w.M; ++m) {
+      const double* s = &states[((size_t)e * w.M + m) * 8];
+      int vj = e * w.V + w.A + m;
+      bool was = w.alive[vj] != 0;
+      bool now = s[7] != 0.0;
+      double hn = wrap_heading(s[2]);
+      w.yaw_rate[vj] = (was && now) ? angdiff(hn, w.heading[vj]) / w.cfg.dt : 0.0;
+      w.pos_x[vj] = s[0];
+      w.pos_y[vj] = s[1];
+      w.pos_z[vj] = 0.0;
+      w.heading[vj] = hn;
+      w.speed[vj] = s[3];
+      w.length[vj] = s[4];
+      w.width[vj] = s[5];
+      w.height[vj] = s[6];
+      w.alive[vj] = now ? 1 : 0;
+      sb_sincos(hn, &w.sin_h[vj], &w.cos_h[vj]);
+    }
+}
+
+// SMARTS._step_providers: controllers then the chassis step (smarts.py:1048-1110)
+void or_step(void* h, const void* actions) {
+  World& w = *static_cast<World*>(h);
+  const int as = w.cfg.action_space;
+  parallel_for(w.E, w.threads, 4, [&](int e) {
+    for (int a = 0; a < w.A; ++a) {
+      int ai = e * w.A + a, vi = e * w.V + a;
+      Ego v{w.pos_x[vi], w.pos_y[vi], w.heading[vi], w.speed[vi], w.yaw_rate[vi], w.v_long[ai], w.v_lat[ai]};
+      double* st = &w.ctrl[(size_t)ai * SB_CTRL_STATE];
+      double* out3 = &w.last_control[(size_t)ai * 3];
+      const int32_t* route = &w.route[(size_t)ai * w.cfg.route_cap];
+      if (as == SB_ACTION_LANE) {
+        int cmd = static_cast<const int32_t*>(actions)[ai];
+        // controllers/__init__.py:125-144
+        double ts = 15;
+        int lc = 0;
+        if (cmd == SB_LANE_SLOW_DOWN) ts = 0;
+        else if (cmd == SB_LANE_CHANGE_LEFT) { ts = 12.5; lc = 1; }
+        else if (cmd == SB_LANE_CHANGE_RIGHT) { ts = 12.5; lc = -1; }
+        w.status[ai] |= lane_following(w.map, v, route, w.route_len[ai], ts, lc, w.cfg.dt, st, out3);
+      } else if (as == SB_ACTION_LANE_WITH_CONTINUOUS_SPEED) {
+        const double* ac = static_cast<const double*>(actions) + (size_t)ai * 2;
+        w.status[ai] |= lane_following(w.map, v, route, w.route_len[ai], ac[0], (int)ac[1], w.cfg.dt, st, out3);
+      } else if (as == SB_ACTION_TRAJECTORY) {
+        const int N = w.cfg.traj_len;
+        trajectory_tracking(v, static_cast<const double*>(actions) + (size_t)ai * 4 * N, N, w.cfg.dt, st, out3);
+      } else if (as == SB_ACTION_CONTINUOUS) {
+        const double* ac = static_cast<const double*>(actions) + (size_t)ai * 3;
+        apply_control(v, clipd(ac[0], 0, 1), clipd(ac[1], 0, 1), clipd(ac[2], -1, 1), out3);
+      } else if (as == SB_ACTION_ACTUATOR_DYNAMIC) {
+        // actuator_dynamic_controller.py:51-80
+        const double* ac = static_cast<const double*>(actions) + (size_t)ai * 3;
+        double steering = clipd((1 - 0.001) * st[0] + clipd(ac[2], -1, 1) * w.cfg.dt, -1, 1);
+        apply_control(v, clipd(ac[0], 0, 1), clipd(ac[1], 0, 1), steering, out3);
+        st[0] = steering;
+      }
+      chassis_step(w, ai, vi);
+    }
+  });
+}
+
+void or_observe(void* h) {
+  World& w = *static_cast<World*>(h);
+  parallel_for(w.E * w.A, w.threads, 1, [&](int i) { observe_agent(w, i / w.A, i % w.A); });
+}
+
+void or_get_state(void* h, SbStatePtrs* o) {
+  World& w = *static_cast<World*>(h);
+  o->pos_x = w.pos_x.data(); o->pos_y = w.pos_y.data(); o->pos_z = w.pos_z.data();
+  o->heading = w.heading.data(); o->speed = w.speed.data(); o->yaw_rate = w.yaw_rate.data();
+  o->length = w.length.data(); o->width = w.width.data(); o->height = w.height.data();
+  o->cos_h = w.cos_h.data(); o->sin_h = w.sin_h.data(); o->alive = w.alive.data();
+  o->steering = w.steering.data(); o->v_long = w.v_long.data(); o->v_lat = w.v_lat.data();
+  o->ctrl = w.ctrl.data(); o->last_control = w.last_control.data();
+  o->route = w.route.data(); o->route_len = w.route_len.data(); o->status = w.status.data();
+}
+
+void or_get_obs(void* h, SbObsPtrs* o) {
+  World& w = *static_cast<World*>(h);
+  std::memset(o, 0, sizeof(*o));
+  o->ego_lane = w.ego_lane.data();
+  o->nbr_count = w.nbr_count.data(); o->nbr_id = w.nbr_id.data(); o->nbr_pos = w.nbr_pos.data();
+  o->nbr_box = w.nbr_box.data(); o->nbr_heading = w.nbr_heading.data(); o->nbr_speed = w.nbr_speed.data();
+  o->nbr_lane = w.nbr_lane.data(); o->nbr_lane_index = w.nbr_lane_index.data();
+  o->wp_n_paths = w.wp_n_paths.data(); o->wp_len = w.wp_len.data(); o->wp_pos = w.wp_pos.data();
+  o->wp_heading = w.wp_heading.data(); o->wp_lane_width = w.wp_lane_width.data();
+  o->wp_speed_limit = w.wp_speed_limit.data(); o->wp_lane = w.wp_lane.data();
+  o->wp_lane_index = w.wp_lane_index.data();
+  o->lidar_points = w.lidar_points.data(); o->lidar_hits = w.lidar_hits.data();
+  o->ogm = w.ogm.data(); o->dagm = w.dagm.data();
+}
+
+// ---- unit-level probes used to pin the oracle against the reference's golden vectors ----
+// RoadMap.waypoint_paths.  Outputs: n paths (return), lens[SB_MAX_PATHS], wp[SB_MAX_PATHS][65][7]
+// (x, y, heading, lane_width, speed_limit, lane, lane_index).
+int or_waypoint_paths(void* h, double x, double y, double heading, int lookahead, double within_radius,
+                      const int32_t* route, int route_len, int32_t* lens, double* wp_out) {
+  World& w = *static_cast<World*>(h);
+  static thread_local PathSet ps;
+  waypoint_paths(w.map, x, y, heading, lookahead, within_radius, route, route_len, &ps);
+  for (int p = 0; p < ps.n; ++p) {
+    lens[p] = ps.len[p];
+    for (int i = 0; i < ps.len[p]; ++i) {
+      double* o = &wp_out[((size_t)p * (SB_MAX_LOOKAHEAD + 1) + i) * 7];
+      const Waypoint& q = ps.wp[p][i];
+      o[0] = q.x; o[1] = q.y; o[2] = q.heading; o[3] = q.lane_width; o[4] = q.speed_limit;
+      o[5] = q.lane; o[6] = q.lane_index;
+    }
+  }
+  return ps.n;
+}
+
+int or_nearest_lane(void* h, double x, double y, double radius, double* dist) {
+  return nearest_lane(static_cast<World*>(h)->map, x, y, radius, dist);
+}
+
+void or_lateral_gains(double target_speed, double* heading_gain, double* lateral_gain) {
+  lateral_gains(target_speed, heading_gain, lateral_gain);
+}
+
+// one controller call on an explicit vehicle state (golden checks vs the reference controllers)
+uint32_t or_lane_following(void* h, const double* veh7, const int32_t* route, int route_len, double target_speed,
+                           int lane_change, double dt, double* st, double* out3) {
+  Ego v{veh7[0], veh7[1], veh7[2], veh7[3], veh7[4], veh7[5], veh7[6]};
+  return lane_following(static_cast<World*>(h)->map, v, route, route_len, target_speed, lane_change, dt, st, out3);
+}
+
+void or_trajectory_tracking(const double* veh7, const double* traj, int N, double dt, double* st, double* out3) {
+  Ego v{veh7[0], veh7[1], veh7[2], veh7[3], veh7[4], veh7[5], veh7[6]};
+  trajectory_tracking(v, traj, N, dt, st, out3);
+}
+
+void or_sincos(const double* x, int n, double* s, double* c) {
+  for (int i = 0; i < n; ++i) sb_sincos(x[i], &s[i], &c[i]);
+}
+void or_atan2(const double* y, const double* x, int n, double* out) {
+  for (int i = 0; i < n; ++i) out[i] = sb_atan2(y[i], x[i]);
+}
+
+}  // extern "C"

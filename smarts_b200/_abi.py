@@ -1,0 +1,150 @@
+"""ctypes mirror of ``include/smarts_b200.h`` (struct layouts and constants only)."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict
+
+import numpy as np
+
+SB_ABI_VERSION = 1
+
+SB_ACTION_CONTINUOUS = 0
+SB_ACTION_LANE = 1
+SB_ACTION_ACTUATOR_DYNAMIC = 2
+SB_ACTION_LANE_WITH_CONTINUOUS_SPEED = 3
+SB_ACTION_TRAJECTORY = 5
+
+SB_LANE_KEEP, SB_LANE_SLOW_DOWN, SB_LANE_CHANGE_LEFT, SB_LANE_CHANGE_RIGHT = 0, 1, 2, 3
+
+SB_MAX_PATHS = 16
+SB_MAX_LOOKAHEAD = 64
+SB_MAX_TRAJ = 32
+SB_CTRL_STATE = 12
+SB_STATUS_PATH_OVERFLOW = 1
+SB_STATUS_NO_WAYPOINTS = 2
+
+_i32, _f64, _u8 = C.c_int32, C.c_double, C.c_uint8
+_pi32, _pf64, _pu8 = C.POINTER(C.c_int32), C.POINTER(C.c_double), C.POINTER(C.c_uint8)
+_pf32, _pi8, _pu32 = C.POINTER(C.c_float), C.POINTER(C.c_int8), C.POINTER(C.c_uint32)
+
+
+class SbConfig(C.Structure):
+    _fields_ = [
+        ("abi_version", _i32), ("device", _i32), ("n_envs", _i32), ("n_agents", _i32), ("n_social", _i32),
+        ("dt", _f64), ("substeps", _i32), ("action_space", _i32), ("traj_len", _i32), ("route_cap", _i32),
+        ("nbr_enable", _i32), ("nbr_cap", _i32), ("nbr_radius", _f64),
+        ("wp_enable", _i32), ("wp_lookahead", _i32), ("wp_out_paths", _i32), ("wp_out_len", _i32),
+        ("lidar_enable", _i32), ("lidar_rays", _i32), ("lidar_miss_inf", _i32), ("lidar_wall_height", _f64),
+        ("ogm_enable", _i32), ("ogm_width", _i32), ("ogm_height", _i32), ("ogm_resolution", _f64),
+        ("dagm_enable", _i32), ("dagm_width", _i32), ("dagm_height", _i32), ("dagm_resolution", _f64),
+    ]
+
+
+_MAP_PTRS = [
+    ("road_lane_start", _pi32), ("road_lane_count", _pi32), ("road_is_junction", _pu8),
+    ("road_lp_start", _pi32), ("road_lp_count", _pi32), ("road_first_out", _pi32),
+    ("lane_road", _pi32), ("lane_idx_in_road", _pi32),
+    ("lane_width", _pf64), ("lane_speed", _pf64), ("lane_length", _pf64),
+    ("lane_out_start", _pi32), ("lane_out", _pi32), ("lane_lp_start", _pi32), ("lane_lp_count", _pi32),
+    ("lane_shape_start", _pi32),
+    ("lp_x", _pf64), ("lp_y", _pf64), ("lp_heading", _pf64), ("lp_inferred", _pu8), ("lp_lane", _pi32),
+    ("lp_next_start", _pi32), ("lp_next", _pi32),
+    ("shape_x", _pf64), ("shape_y", _pf64),
+    ("poly_start", _pi32), ("poly_x", _pf64), ("poly_y", _pf64), ("road_edges", _pf64),
+]
+
+
+class SbMap(C.Structure):
+    _fields_ = [
+        ("n_roads", _i32), ("n_lanes", _i32), ("n_lanepoints", _i32), ("n_shape_pts", _i32),
+        ("n_polys", _i32), ("n_poly_verts", _i32), ("n_edges", _i32), ("n_lane_out", _i32), ("n_lp_next", _i32),
+        ("lanepoint_spacing", _f64),
+    ] + _MAP_PTRS
+
+
+class SbStatePtrs(C.Structure):
+    _fields_ = [(n, _pf64) for n in
+                ("pos_x", "pos_y", "pos_z", "heading", "speed", "yaw_rate", "length", "width", "height",
+                 "cos_h", "sin_h")] + [("alive", _pu8)] + [(n, _pf64) for n in
+                ("steering", "v_long", "v_lat", "ctrl", "last_control")] + [
+                ("route", _pi32), ("route_len", _pi32), ("status", _pu32)]
+
+
+class SbObsPtrs(C.Structure):
+    _fields_ = [
+        ("ego_lane", _pi32),
+        ("nbr_count", _pi32), ("nbr_id", _pi32), ("nbr_pos", _pf64), ("nbr_box", _pf32),
+        ("nbr_heading", _pf32), ("nbr_speed", _pf32), ("nbr_lane", _pi32), ("nbr_lane_index", _pi8),
+        ("wp_n_paths", _pi32), ("wp_len", _pi32), ("wp_pos", _pf64), ("wp_heading", _pf32),
+        ("wp_lane_width", _pf32), ("wp_speed_limit", _pf32), ("wp_lane", _pi32), ("wp_lane_index", _pi8),
+        ("lidar_points", _pf64), ("lidar_hits", _pi8),
+        ("ogm", _pu8), ("dagm", _pu8),
+    ]
+
+
+class SbResetState(C.Structure):
+    _fields_ = [("agent_x", _pf64), ("agent_y", _pf64), ("agent_heading", _pf64), ("agent_speed", _pf64),
+                ("route", _pi32), ("route_len", _pi32)]
+
+
+_NP = {_pi32: np.int32, _pf64: np.float64, _pu8: np.uint8, _pf32: np.float32, _pi8: np.int8, _pu32: np.uint32}
+
+
+def make_map_struct(arrays: Dict[str, np.ndarray], spacing: float):
+    """Fill an SbMap from ``RoadMapData.arrays()``.  Returns (struct, keepalive list)."""
+    m = SbMap()
+    keep = []
+    for name, ptype in _MAP_PTRS:
+        a = np.ascontiguousarray(arrays[name], dtype=_NP[ptype])
+        keep.append(a)
+        setattr(m, name, a.ctypes.data_as(ptype))
+    m.n_roads = len(arrays["road_lane_start"])
+    m.n_lanes = len(arrays["lane_road"])
+    m.n_lanepoints = len(arrays["lp_x"])
+    m.n_shape_pts = len(arrays["shape_x"])
+    m.n_polys = len(arrays["poly_start"]) - 1
+    m.n_poly_verts = len(arrays["poly_x"])
+    m.n_edges = len(arrays["road_edges"])
+    m.n_lane_out = int(arrays["lane_out_start"][-1])
+    m.n_lp_next = int(arrays["lp_next_start"][-1])
+    m.lanepoint_spacing = float(spacing)
+    return m, keep
+
+
+def obs_shapes(cfg: SbConfig) -> Dict[str, tuple]:
+    """Shapes (without the leading E*A) and dtypes of every SbObsPtrs field enabled by cfg."""
+    out = {"ego_lane": ((), np.int32)}
+    if cfg.nbr_enable:
+        c = cfg.nbr_cap
+        out.update(nbr_count=((), np.int32), nbr_id=((c,), np.int32), nbr_pos=((c, 3), np.float64),
+                   nbr_box=((c, 3), np.float32), nbr_heading=((c,), np.float32), nbr_speed=((c,), np.float32),
+                   nbr_lane=((c,), np.int32), nbr_lane_index=((c,), np.int8))
+    if cfg.wp_enable:
+        p, l = cfg.wp_out_paths, cfg.wp_out_len
+        out.update(wp_n_paths=((), np.int32), wp_len=((p,), np.int32), wp_pos=((p, l, 3), np.float64),
+                   wp_heading=((p, l), np.float32), wp_lane_width=((p, l), np.float32),
+                   wp_speed_limit=((p, l), np.float32), wp_lane=((p, l), np.int32),
+                   wp_lane_index=((p, l), np.int8))
+    if cfg.lidar_enable:
+        r = cfg.lidar_rays
+        out.update(lidar_points=((r, 3), np.float64), lidar_hits=((r,), np.int8))
+    if cfg.ogm_enable:
+        out.update(ogm=((cfg.ogm_height, cfg.ogm_width), np.uint8))
+    if cfg.dagm_enable:
+        out.update(dagm=((cfg.dagm_height, cfg.dagm_width), np.uint8))
+    return out
+
+
+def state_shapes(cfg: SbConfig) -> Dict[str, tuple]:
+    """(per-what, trailing shape, dtype): 'v' = per vehicle slot [E*V], 'a' = per agent [E*A]."""
+    out = {n: ("v", (), np.float64) for n in
+           ("pos_x", "pos_y", "pos_z", "heading", "speed", "yaw_rate", "length", "width", "height", "cos_h", "sin_h")}
+    out["alive"] = ("v", (), np.uint8)
+    for n in ("steering", "v_long", "v_lat"):
+        out[n] = ("a", (), np.float64)
+    out["ctrl"] = ("a", (SB_CTRL_STATE,), np.float64)
+    out["last_control"] = ("a", (3,), np.float64)
+    out["route"] = ("a", (max(cfg.route_cap, 1),), np.int32)
+    out["route_len"] = ("a", (), np.int32)
+    out["status"] = ("a", (), np.uint32)
+    return out

@@ -62,18 +62,52 @@ class RoadMapData:
     """All per-scenario constant arrays.  ``arrays()`` returns the dict handed to the C-ABI
     (``sb_upload_map``) and, unchanged, to the CPU oracle."""
 
-    def __init__(self, net: SumoNet, lanepoint_spacing: float = 1.0):
+    _SAVE_KEYS = ["road_length", "conn_from", "conn_to", "conn_via"]
+
+    def __init__(self, net: Optional[SumoNet], lanepoint_spacing: float = 1.0):
         self.net = net
         self.spacing = float(lanepoint_spacing)
-        self._build_tables()
-        self._build_lanepoints()
-        self._build_shapes()
-        self._build_polygons()
+        if net is not None:
+            self._build_tables()
+            self._build_lanepoints()
+            self._build_shapes()
+            self._build_polygons()
 
     @classmethod
     def from_file(cls, net_file: str, lanepoint_spacing: float = 1.0,
                   default_lane_width: float = 3.2) -> "RoadMapData":
+        """``net_file``: a SUMO ``*.net.xml`` (or a scenario directory holding ``map.net.xml``,
+        sumo_road_network.py:191-196) or a ``*.npz`` written by :meth:`save`."""
+        import os
+        if os.path.isdir(net_file):
+            net_file = os.path.join(net_file, "map.net.xml")
+        if net_file.endswith(".npz"):
+            return cls.load(net_file)
         return cls(SumoNet(net_file, default_lane_width), lanepoint_spacing)
+
+    def save(self, path: str):
+        """Write the flattened map (this repo's own format; no reference content)."""
+        d = self.arrays()
+        for k in self._SAVE_KEYS:
+            d[k] = getattr(self, k)
+        d["lane_ids"] = np.asarray(self._lane_ids)
+        d["road_ids"] = np.asarray(self._road_ids)
+        d["spacing"] = np.asarray(self.spacing)
+        np.savez_compressed(path, **d)
+
+    @classmethod
+    def load(cls, path: str) -> "RoadMapData":
+        z = np.load(path, allow_pickle=False)
+        self = cls(None, float(z["spacing"]))
+        for k in z.files:
+            if k in ("lane_ids", "road_ids", "spacing"):
+                continue
+            setattr(self, k, z[k])
+        self._lane_ids = [str(s) for s in z["lane_ids"]]
+        self._road_ids = [str(s) for s in z["road_ids"]]
+        self.lane_index = {s: i for i, s in enumerate(self._lane_ids)}
+        self.road_index = {s: i for i, s in enumerate(self._road_ids)}
+        return self
 
     # ------------------------------------------------------------------ tables
     def _build_tables(self):
@@ -92,6 +126,10 @@ class RoadMapData:
         self.road_lane_count = np.asarray(road_lane_count, np.int32)
         self.road_is_junction = np.asarray([e.isSpecial() for e in self.roads], np.uint8)
         self.road_length = np.asarray([e.getLength() for e in self.roads], np.float64)
+        # Road.outgoing_roads[0] (sumo_road_network.py:578-583), used by _resolve_in_junction
+        self.road_first_out = np.asarray(
+            [self.road_index[next(iter(e.getOutgoing().keys())).getID()] if e.getOutgoing() else -1
+             for e in self.roads], np.int32)
         self.lane_road = np.asarray([self.road_index[l.getEdge().getID()] for l in self.lanes], np.int32)
         self.lane_idx_in_road = np.asarray([l.getIndex() for l in self.lanes], np.int32)
         self.lane_width = np.asarray([l.getWidth() for l in self.lanes], np.float64)
@@ -106,6 +144,18 @@ class RoadMapData:
         self.lane_out_start = np.asarray(out_start, np.int32)
         self.lane_out = np.asarray(out_flat if out_flat else [0], np.int32)
         assert nl == len(self.lane_width)
+        # <connection> table in file order (from lane, to lane, via lane or -1): all the routing
+        # code needs, so a map saved with ``save()`` can route without the net.xml.
+        cf, ct, cv = [], [], []
+        for c in net.connections:
+            cf.append(self.lane_index[c.getFromLane().getID()])
+            ct.append(self.lane_index[c.getToLane().getID()])
+            cv.append(self.lane_index[c.getViaLaneID()] if c.getViaLaneID() else -1)
+        self.conn_from = np.asarray(cf, np.int32)
+        self.conn_to = np.asarray(ct, np.int32)
+        self.conn_via = np.asarray(cv, np.int32)
+        self._lane_ids = [l.getID() for l in self.lanes]
+        self._road_ids = [e.getID() for e in self.roads]
 
     def outgoing_lanes(self, li: int) -> List[int]:
         return list(self.lane_out[self.lane_out_start[li]:self.lane_out_start[li + 1]])
@@ -313,7 +363,8 @@ class RoadMapData:
                     for k in range(1, nseg):
                         fan.append((cx + hw * math.cos(a0 + k * inc), cy + hw * math.sin(a0 + k * inc)))
                 fan.append((cx + s * n1x, cy + s * n1y))
-                polys.append(ccw(fan))
+                for k in range(1, len(fan) - 1):  # triangles: every piece has <= 4 vertices
+                    polys.append(ccw([fan[0], fan[k], fan[k + 1]]))
             # boundary segments of the outer-most lanes feed the LiDAR "road edge" walls
         for e in self.roads:
             if e.isSpecial():
@@ -353,49 +404,80 @@ class RoadMapData:
 
     def generate_route(self, start_road: str, end_road: str,
                        via: Optional[Sequence[str]] = None) -> Route:
-        """sumo_road_network.py:711-801 (max_to_gen == 1)."""
-        net = self.net
-        roads = [start_road] + list(via or [])
+        """sumo_road_network.py:711-801 (max_to_gen == 1), on the <connection> table."""
+        g = self._route_graph()
+        ri = self.road_index
+        roads = [ri[start_road]] + [ri[v] for v in (via or [])]
         if end_road != start_road:
-            roads.append(end_road)
-        edges = []
+            roads.append(ri[end_road])
+        edges: List[int] = []
         for cur, nxt in zip(roads, roads[1:] + [None]):
             if nxt is None:
-                edges.append(net.getEdge(cur))
+                edges.append(cur)
                 break
-            sub = net.getShortestPath(net.getEdge(cur), net.getEdge(nxt))[0] or []
+            sub = self._shortest_path(g, cur, nxt) or []
             if len(sub) < 2:
                 return Route([], [], 0.0)
             edges.extend(sub[:-1])
         if len(edges) == 1:
-            ids = [edges[0].getID()]
+            idx = [edges[0]]
         else:
-            used = []
+            used: List[int] = []
             for ce, ne in zip(edges, edges[1:]):
-                for conn in ce.getOutgoing()[ne]:
+                for via_lane in g[ce][ne]:  # one entry per connection ce -> ne
                     conn_route = [ce]
-                    via_id = conn.getViaLaneID()
-                    while via_id:
-                        via_edge = net.getLane(via_id).getEdge()
-                        conn_route.append(via_edge)
-                        nxt_ids = set(c.getViaLaneID() for c in via_edge.getOutgoing()[ne])
-                        assert len(nxt_ids) == 1
-                        via_id = list(nxt_ids)[0]
+                    v = via_lane
+                    while v >= 0:
+                        via_road = int(self.lane_road[v])
+                        conn_route.append(via_road)
+                        nxt_ids = set(g[via_road][ne])
+                        assert len(nxt_ids) == 1, nxt_ids
+                        v = list(nxt_ids)[0]
                     conn_route.append(ne)
                     used.extend(conn_route)
-            ids = []
-            seen = set()
-            for e in used:  # first-occurrence order == np.unique(return_index) + sorted(indices)
-                if e.getID() not in seen:
-                    seen.add(e.getID())
-                    ids.append(e.getID())
-        idx = [self.road_index[i] for i in ids]
+            idx, seen = [], set()
+            for r in used:  # first-occurrence order == np.unique(return_index) + sorted(indices)
+                if r not in seen:
+                    seen.add(r)
+                    idx.append(r)
+        ids = [self._road_ids[i] for i in idx]
         return Route(ids, idx, float(sum(self.road_length[i] for i in idx)))
+
+    def _route_graph(self) -> Dict[int, Dict[int, List[int]]]:
+        """road -> {to road -> [via lane (or -1) per connection]}, insertion-ordered like
+        sumolib's ``Edge.getOutgoing()``."""
+        if getattr(self, "_rg", None) is None:
+            g: Dict[int, Dict[int, List[int]]] = {r: {} for r in range(len(self._road_ids))}
+            for f, t, v in zip(self.conn_from, self.conn_to, self.conn_via):
+                g[int(self.lane_road[f])].setdefault(int(self.lane_road[t]), []).append(int(v))
+            self._rg = g
+        return self._rg
+
+    def _shortest_path(self, g, src: int, dst: int) -> Optional[List[int]]:
+        """Dijkstra over non-junction roads weighted by road length
+        (sumolib.net.Net.getShortestPath as used at sumo_road_network.py:733-738)."""
+        import heapq
+        seen = set()
+        q = [(float(self.road_length[src]), 0, src, (src,))]
+        tie = 1
+        while q:
+            cost, _, r, path = heapq.heappop(q)
+            if r in seen:
+                continue
+            seen.add(r)
+            if r == dst:
+                return list(path)
+            for nr in g[r].keys():
+                if self.road_is_junction[nr] or nr in seen:
+                    continue
+                heapq.heappush(q, (cost + float(self.road_length[nr]), tie, nr, path + (nr,)))
+                tie += 1
+        return None
 
     # ------------------------------------------------------------------ export
     def arrays(self) -> Dict[str, np.ndarray]:
         keys = [
-            "road_lane_start", "road_lane_count", "road_is_junction", "road_lp_start", "road_lp_count",
+            "road_lane_start", "road_lane_count", "road_is_junction", "road_lp_start", "road_lp_count", "road_first_out",
             "lane_road", "lane_idx_in_road", "lane_width", "lane_speed", "lane_length",
             "lane_out_start", "lane_out", "lane_lp_start", "lane_lp_count", "lane_shape_start",
             "lp_x", "lp_y", "lp_heading", "lp_inferred", "lp_lane", "lp_next_start", "lp_next",
@@ -405,21 +487,28 @@ class RoadMapData:
 
     @property
     def lane_ids(self) -> List[str]:
-        return [l.getID() for l in self.lanes]
+        return self._lane_ids
 
     @property
     def road_ids(self) -> List[str]:
-        return [e.getID() for e in self.roads]
+        return self._road_ids
+
+    def lane_of_road(self, road_id: str, lane_idx: int) -> int:
+        r = self.road_index[road_id]
+        assert 0 <= lane_idx < self.road_lane_count[r]
+        return int(self.road_lane_start[r]) + lane_idx
 
     def lane_start_pose(self, road_id: str, lane_idx: int, offset: float) -> Tuple[float, float, float]:
         """Centre-line pose at ``offset`` metres along a lane (mission start poses,
         scenarios/*/scenario.py ``Route(begin=(edge, lane, offset))``)."""
-        lane = self.net.getEdge(road_id).getLanes()[lane_idx]
-        shp = lane.getShape(False)
+        li = self.lane_of_road(road_id, lane_idx)
+        s, e = int(self.lane_shape_start[li]), int(self.lane_shape_start[li + 1])
+        shp = [(float(self.shape_x[i]), float(self.shape_y[i])) for i in range(s, e)]
         seen = 0.0
-        for (ax, ay), (bx, by) in zip(shp, shp[1:]):
+        for k in range(len(shp) - 1):
+            (ax, ay), (bx, by) = shp[k], shp[k + 1]
             ln = math.hypot(bx - ax, by - ay)
-            if seen + ln > offset or (bx, by) == shp[-1]:
+            if seen + ln > offset or k == len(shp) - 2:
                 t = min(max((offset - seen) / ln, 0.0), 1.0) if ln > 0 else 0.0
                 return (ax + (bx - ax) * t, ay + (by - ay) * t,
                         wrap_heading(vec_to_radians(bx - ax, by - ay)))

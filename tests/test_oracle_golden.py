@@ -1,0 +1,166 @@
+"""Pin the CPU oracle to the reference: every check here compares oracle/ (and the host-side
+map code) against fixtures that were produced by running the reference's own Python
+(tests/golden/gen_golden.py).  CPU only."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, load_map, make_cfg, oracle_world
+from oracle import oracle_py
+from smarts_b200 import lidar_params
+
+MAPS = ["loop", "figure_eight", "4lane", "straight", "6lane"]
+
+
+def test_detmath_sincos_matches_libm():
+    rng = np.random.default_rng(0)
+    x = np.concatenate([rng.uniform(-10, 10, 200000), rng.uniform(-1e5, 1e5, 50000),
+                        np.linspace(-np.pi, np.pi, 10001), [0.0, np.pi / 2, -np.pi / 2, np.pi]])
+    s, c = oracle_py.det_sincos(x)
+    ulp = np.spacing(1.0)
+    assert np.max(np.abs(s - np.sin(x))) <= 2 * ulp
+    assert np.max(np.abs(c - np.cos(x))) <= 2 * ulp
+
+
+def test_detmath_atan2_matches_libm():
+    rng = np.random.default_rng(1)
+    y = rng.normal(0, 3, 200000)
+    x = rng.normal(0, 3, 200000)
+    a = oracle_py.det_atan2(y, x)
+    ref = np.arctan2(y, x)
+    assert np.max(np.abs(a - ref) / np.maximum(np.abs(ref), 1e-300)) < 1e-15 or np.max(np.abs(a - ref)) < 9e-16
+    assert oracle_py.det_atan2(np.array([0.0]), np.array([0.0]))[0] == 0.0
+
+
+@pytest.mark.parametrize("name", MAPS)
+def test_waypoint_paths_match_reference(name):
+    """RoadMap.waypoint_paths (sumo_road_network.py:815-882): path count, per-path length, lane
+    ids / lane indices exact; positions, headings within 1e-9."""
+    rm = load_map(name)
+    q = np.load(os.path.join(GOLDEN, f"queries_{name}.npz"))
+    w = oracle_world(rm, make_cfg(E=1, A=1, M=0))
+    routes = [[rm.road_index[r] for r in s.split(";")] for s in q["routes"] if s]
+    meta, rows = q["wp_meta"], q["wp_rows"].reshape(-1, 7)
+    # group reference paths per query
+    groups = {}
+    for i, look, mode, p, n, off in meta:
+        groups.setdefault((i, look, mode), []).append(rows[off:off + n])
+    assert groups
+    n_checked = 0
+    for (i, look, mode), ref_paths in groups.items():
+        route = None if mode == 0 else ([] if mode == 1 else routes[mode - 2])
+        got = w.waypoint_paths(q["x"][i], q["y"][i], q["h"][i], int(look), route)
+        assert len(got) == len(ref_paths), (name, i, look, mode)
+        for g, r in zip(got, ref_paths):
+            assert g.shape == r.shape
+            assert np.array_equal(g[:, 5], r[:, 5]), "lane ids differ"
+            assert np.array_equal(g[:, 6], r[:, 6]), "lane indices differ"
+            np.testing.assert_allclose(g[:, :2], r[:, :2], rtol=0, atol=1e-9)
+            dh = np.abs(g[:, 2] - r[:, 2])
+            dh = np.minimum(dh, np.abs(dh - 2 * np.pi))
+            assert dh.max() < 1e-9
+            np.testing.assert_allclose(g[:, 3:5], r[:, 3:5], rtol=1e-12)
+            n_checked += 1
+    assert n_checked == len(meta)
+
+
+@pytest.mark.parametrize("name", MAPS)
+def test_nearest_lane_matches_reference(name):
+    rm = load_map(name)
+    q = np.load(os.path.join(GOLDEN, f"queries_{name}.npz"))
+    w = oracle_world(rm, make_cfg(E=1, A=1, M=0))
+    for i in range(len(q["x"])):
+        for k, radius in enumerate((3.68, 10.0)):
+            lane, d = w.nearest_lane(q["x"][i], q["y"][i], radius)
+            assert lane == q["nl_lane"][i, k], (name, i, radius)
+            if lane >= 0:
+                assert abs(d - q["nl_dist"][i, k]) < 1e-12
+
+
+def test_sensor_test_known_answer():
+    """smarts/core/tests/test_sensors.py:83-99: 3 waypoint paths at (33, -65) on 6lane."""
+    rm = load_map("6lane")
+    w = oracle_world(rm, make_cfg(E=1, A=1, M=0))
+    route = rm.generate_route("edge-west-WE", "edge-east-WE").road_indices
+    paths = w.waypoint_paths(33.0, -65.0, 0.0, 32, route)
+    assert len(paths) == 3
+
+
+def test_lateral_gains_match_place_poles():
+    g = np.load(os.path.join(GOLDEN, "controllers.npz"))["gains"]
+    for v, k0, k1, hg, lg in g:
+        h, l = oracle_py.lateral_gains(float(v))
+        assert abs(h - hg) < 1e-9 and abs(l - lg) < 1e-9
+    assert oracle_py.lateral_gains(0.0) == (0.01, 0.36)
+
+
+@pytest.mark.parametrize("key,mapname", [("lane_4lane", "4lane"), ("lane_loop", "loop")])
+def test_lane_following_matches_reference(key, mapname):
+    rec = np.load(os.path.join(GOLDEN, "controllers.npz"))[key]
+    rm = load_map(mapname)
+    q = np.load(os.path.join(GOLDEN, f"queries_{mapname}.npz"))
+    routes = [[rm.road_index[r] for r in s.split(";")] for s in q["routes"] if s]
+    w = oracle_world(rm, make_cfg(E=1, A=1, M=0))
+    for r in rec:
+        ridx, ts, lc = int(r[0]), float(r[1]), int(r[2])
+        veh = r[3:10]
+        st = np.zeros(12)
+        st[:8] = r[10:18]
+        out, st2, status = w.lane_following(veh, routes[ridx], ts, lc, 0.1, st)
+        assert status == 0
+        np.testing.assert_allclose(st2[:5], r[18:23], rtol=1e-9, atol=1e-10)
+        assert st2[7] == r[25]
+        if r[25]:
+            np.testing.assert_allclose(st2[5:7], r[23:25], atol=1e-9)
+        # brake is zeroed inside AckermannChassis.control below 1/36 m/s, the mock records it raw
+        exp_brake = 0.0 if (r[27] > 0 and r[8] < 1 / 36) else r[27]
+        np.testing.assert_allclose(out, [r[26], exp_brake, r[28]], rtol=1e-9, atol=1e-10)
+
+
+def test_trajectory_tracking_matches_reference():
+    g = np.load(os.path.join(GOLDEN, "controllers.npz"))
+    for r, traj in zip(g["traj_rec"], g["trajs"]):
+        st = np.zeros(12)
+        st[:7] = r[7:14]
+        out, st2 = oracle_py.trajectory_tracking(r[0:7], traj, 0.1, st)
+        np.testing.assert_allclose(st2[:7], r[14:21], rtol=1e-9, atol=1e-10)
+        exp_brake = 0.0 if (r[22] > 0 and r[5] < 1 / 36) else r[22]
+        np.testing.assert_allclose(out, [r[21], exp_brake, r[23]], rtol=1e-9, atol=1e-10)
+
+
+def test_lidar_ray_table_matches_reference():
+    g = np.load(os.path.join(GOLDEN, "controllers.npz"))
+    for key, params in (("rays_basic", lidar_params.BasicLidar), ("rays_hdl32e", lidar_params.VelodyneHDL32E)):
+        mine = lidar_params.base_rays(params)
+        assert mine.shape == g[key].shape
+        np.testing.assert_allclose(mine, g[key], atol=1e-12)
+    assert lidar_params.base_rays(lidar_params.BasicLidar).shape == (300, 3)
+
+
+def test_neighbors_match_cdist():
+    """smarts.py:1191-1208: 3-D euclidean cdist <= radius, ego excluded."""
+    from scipy.spatial.distance import cdist
+    rm = load_map("4lane")
+    rng = np.random.default_rng(5)
+    E, A, M = 8, 4, 20
+    cfg = make_cfg(E=E, A=A, M=M, nbr=True, nbr_radius=25.0, nbr_cap=24)
+    w = oracle_world(rm, cfg)
+    ax = rng.uniform(100, 200, (E, A)); ay = rng.uniform(-110, -10, (E, A))
+    w.reset(ax, ay, np.zeros((E, A)), np.zeros((E, A)))
+    soc = np.zeros((E, M, 8))
+    soc[..., 0] = rng.uniform(100, 200, (E, M)); soc[..., 1] = rng.uniform(-110, -10, (E, M))
+    soc[..., 4:7] = [3.68, 1.47, 1.4]
+    soc[..., 7] = rng.uniform(size=(E, M)) > 0.2
+    w.set_social(soc)
+    w.observe()
+    obs, st = w.obs(), w.state()
+    for e in range(E):
+        pos = np.stack([st["pos_x"][e], st["pos_y"][e], st["pos_z"][e]], 1)
+        for a in range(A):
+            others = [j for j in range(A + M) if j != a and st["alive"][e, j]]
+            d = cdist(pos[others], pos[a:a + 1]).reshape(-1)
+            want = [others[i] for i in np.argwhere(d <= 25.0).flatten()]
+            n = obs["nbr_count"][e, a]
+            assert n == len(want)
+            assert list(obs["nbr_id"][e, a, :n]) == want
