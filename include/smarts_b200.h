@@ -209,6 +209,9 @@ int sb_observe(SbHandle h, void *stream);
  * copies actions and social states in, runs sb_set_social + sb_step + sb_observe, synchronises. */
 int sb_step_host(SbHandle h, const void *host_actions, int64_t action_bytes,
                  const double *host_social);
+/* The other half of the host-buffer call: copy every enabled observation buffer to the HOST
+ * pointers in *host_dst (NULL members are skipped) and synchronise.  Layouts as SbObsPtrs. */
+int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs *host_dst);
 int sb_get_obs(SbHandle h, SbObsPtrs *out);
 int sb_get_state(SbHandle h, SbStatePtrs *out);
 /* number of kernel launches issued by this handle so far (bench gpu_launches) */

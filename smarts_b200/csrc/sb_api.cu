@@ -1,0 +1,486 @@
+// sb_api.cu -- the C-ABI of include/smarts_b200.h over the kernels of sb_kernels.cuh.
+// Compiled for sm_100a only (-gencode arch=compute_100a,code=sm_100a -fmad=false).  There is no
+// CPU path in this library: every entry point that computes launches CUDA kernels.
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "sb_kernels.cuh"
+
+struct SbHandle_ {
+  SbConfig cfg;
+  DCfg dc;
+  DMap dmap;
+  DState st;
+  DObs ob;
+  bool have_map = false, have_rays = false;
+  double* d_rays = nullptr;
+  std::vector<void*> allocs;
+  void* d_actions = nullptr;  // staging for sb_step_host
+  size_t actions_cap = 0;
+  double* d_social = nullptr;
+  int64_t launches = 0;
+  int cuda_err = 0;
+  std::string err;
+  size_t raster_smem = 0;
+};
+
+namespace {
+
+int fail(SbHandle h, int code, const std::string& msg) {
+  if (h) h->err = msg;
+  return code;
+}
+
+bool cuda_ok(SbHandle h, cudaError_t e, const char* what) {
+  if (e == cudaSuccess) return true;
+  h->cuda_err = (int)e;
+  h->err = std::string(what) + ": " + cudaGetErrorString(e);
+  return false;
+}
+
+template <class T>
+bool dev_alloc(SbHandle h, T** p, size_t n, bool zero = true) {
+  void* q = nullptr;
+  size_t bytes = (n ? n : 1) * sizeof(T);
+  if (!cuda_ok(h, cudaMalloc(&q, bytes), "cudaMalloc")) return false;
+  if (zero && !cuda_ok(h, cudaMemset(q, 0, bytes), "cudaMemset")) return false;
+  h->allocs.push_back(q);
+  *p = static_cast<T*>(q);
+  return true;
+}
+
+template <class T>
+bool dev_upload(SbHandle h, const T** dst, const T* src, size_t n) {
+  T* q = nullptr;
+  if (!dev_alloc(h, &q, n, false)) return false;
+  if (n && !cuda_ok(h, cudaMemcpy(q, src, n * sizeof(T), cudaMemcpyHostToDevice), "cudaMemcpy(map)")) return false;
+  *dst = q;
+  return true;
+}
+
+__global__ void k_fill(double* p, size_t n, double v) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
+
+// SMARTS.reset for a list of envs: agents at their mission start with the sedan chassis box
+// (models/vehicle.urdf:12-16), social slots cleared.
+__global__ void k_reset(DCfg c, DState s, const int32_t* env_ids, int n, const double* ax, const double* ay,
+                        const double* ah, const double* av, const int32_t* route, const int32_t* route_len) {
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n * c.V) return;
+  int i = t / c.V, slot = t - i * c.V;
+  int e = env_ids ? env_ids[i] : i;
+  int vi = e * c.V + slot;
+  if (slot < c.A) {
+    int ai = e * c.A + slot;
+    size_t src = (size_t)i * c.A + slot;
+    double h = d_wrap_heading(ah[src]);
+    s.pos_x[vi] = ax[src];
+    s.pos_y[vi] = ay[src];
+    s.pos_z[vi] = 0.0;
+    s.heading[vi] = h;
+    s.speed[vi] = av[src];
+    s.yaw_rate[vi] = 0.0;
+    s.length[vi] = 3.68;
+    s.width[vi] = 1.47;
+    s.height[vi] = 1.0;
+    sb_sincos(h, &s.sin_h[vi], &s.cos_h[vi]);
+    s.alive[vi] = 1;
+    s.steering[ai] = 0.0;
+    s.v_long[ai] = av[src];
+    s.v_lat[ai] = 0.0;
+    for (int k = 0; k < SB_CTRL_STATE; ++k) s.ctrl[(size_t)ai * SB_CTRL_STATE + k] = 0.0;
+    for (int k = 0; k < 3; ++k) s.last_control[(size_t)ai * 3 + k] = 0.0;
+    s.status[ai] = 0;
+    for (int k = 0; k < c.route_cap; ++k)
+      s.route[(size_t)ai * c.route_cap + k] = route ? route[src * c.route_cap + k] : -1;
+    s.route_len[ai] = route_len ? route_len[src] : 0;
+  } else {
+    s.alive[vi] = 0;
+    s.pos_x[vi] = s.pos_y[vi] = s.pos_z[vi] = s.heading[vi] = s.speed[vi] = s.yaw_rate[vi] = 0.0;
+    s.length[vi] = s.width[vi] = s.height[vi] = 0.0;
+    s.cos_h[vi] = 1.0;
+    s.sin_h[vi] = 0.0;
+  }
+}
+
+size_t action_bytes(const SbConfig& c) {
+  size_t na = (size_t)c.n_envs * c.n_agents;
+  switch (c.action_space) {
+    case SB_ACTION_LANE: return na * sizeof(int32_t);
+    case SB_ACTION_LANE_WITH_CONTINUOUS_SPEED: return na * 2 * sizeof(double);
+    case SB_ACTION_TRAJECTORY: return na * 4 * (size_t)c.traj_len * sizeof(double);
+    default: return na * 3 * sizeof(double);
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+int sb_abi_version(void) { return SB_ABI_VERSION; }
+
+const char* sb_last_error(SbHandle h) { return h ? h->err.c_str() : "null handle"; }
+
+int64_t sb_launch_count(SbHandle h) { return h ? h->launches : 0; }
+
+int sb_create(const SbConfig* cfg, SbHandle* out) {
+  if (!cfg || !out) return SB_EINVAL;
+  *out = nullptr;
+  SbHandle h = new SbHandle_();
+  h->cfg = *cfg;
+  *out = h;  // returned even on failure so sb_last_error works; caller must sb_destroy
+  const SbConfig& c = h->cfg;
+  if (c.abi_version != SB_ABI_VERSION) return fail(h, SB_EINVAL, "abi_version mismatch");
+  if (c.n_envs < 1 || c.n_agents < 1 || c.n_social < 0) return fail(h, SB_EINVAL, "n_envs/n_agents/n_social");
+  if (!(c.dt > 0)) return fail(h, SB_EINVAL, "dt must be > 0");
+  switch (c.action_space) {
+    case SB_ACTION_CONTINUOUS: case SB_ACTION_LANE: case SB_ACTION_ACTUATOR_DYNAMIC:
+    case SB_ACTION_LANE_WITH_CONTINUOUS_SPEED: break;
+    case SB_ACTION_TRAJECTORY:
+      if (c.traj_len < 2 || c.traj_len > SB_MAX_TRAJ) return fail(h, SB_EINVAL, "traj_len out of range");
+      break;
+    default: return fail(h, SB_EINVAL, "unsupported action_space");
+  }
+  if (c.route_cap < 1) return fail(h, SB_EINVAL, "route_cap must be >= 1");
+  if (c.nbr_enable && c.nbr_cap < 1) return fail(h, SB_EINVAL, "nbr_cap");
+  if (c.wp_enable && (c.wp_lookahead < 1 || c.wp_lookahead > SB_MAX_LOOKAHEAD || c.wp_out_paths < 1 ||
+                      c.wp_out_paths > SB_MAX_PATHS || c.wp_out_len < 1 || c.wp_out_len > SB_MAX_LOOKAHEAD + 1))
+    return fail(h, SB_EINVAL, "waypoint sensor limits");
+  if (c.lidar_enable && c.lidar_rays < 1) return fail(h, SB_EINVAL, "lidar_rays");
+  auto grid_ok = [](int w, int hh, double r) { return w >= 32 && hh >= 1 && (w % 32) == 0 && r > 0 && w <= 1024 && hh <= 1024; };
+  if (c.ogm_enable && !grid_ok(c.ogm_width, c.ogm_height, c.ogm_resolution))
+    return fail(h, SB_EINVAL, "ogm: width must be a multiple of 32, <= 1024; resolution > 0");
+  if (c.dagm_enable && !grid_ok(c.dagm_width, c.dagm_height, c.dagm_resolution))
+    return fail(h, SB_EINVAL, "dagm: width must be a multiple of 32, <= 1024; resolution > 0");
+  if (c.n_agents + c.n_social > SB_LIDAR_MAX_BOXES + 1 && c.lidar_enable)
+    return fail(h, SB_EINVAL, "lidar: too many vehicles per env");
+
+  if (!cuda_ok(h, cudaSetDevice(c.device), "cudaSetDevice")) return SB_ECUDA;
+  DCfg& d = h->dc;
+  d.E = c.n_envs; d.A = c.n_agents; d.M = c.n_social; d.V = d.A + d.M;
+  d.dt = c.dt;
+  d.substeps = c.substeps > 0 ? c.substeps : ((int)(c.dt * 240) > 1 ? (int)(c.dt * 240) : 1);
+  d.action_space = c.action_space; d.traj_len = c.traj_len; d.route_cap = c.route_cap;
+  d.nbr_enable = c.nbr_enable; d.nbr_cap = c.nbr_cap; d.nbr_radius = c.nbr_radius;
+  d.wp_enable = c.wp_enable; d.wp_lookahead = c.wp_lookahead; d.wp_out_paths = c.wp_out_paths;
+  d.wp_out_len = c.wp_out_len;
+  d.lidar_enable = c.lidar_enable; d.lidar_rays = c.lidar_rays; d.lidar_miss_inf = c.lidar_miss_inf;
+  d.lidar_wall_height = c.lidar_wall_height;
+  d.ogm_enable = c.ogm_enable; d.ogm_w = c.ogm_width; d.ogm_h = c.ogm_height; d.ogm_res = c.ogm_resolution;
+  d.dagm_enable = c.dagm_enable; d.dagm_w = c.dagm_width; d.dagm_h = c.dagm_height; d.dagm_res = c.dagm_resolution;
+
+  const size_t nv = (size_t)d.E * d.V, na = (size_t)d.E * d.A;
+  DState& s = h->st;
+  bool ok = dev_alloc(h, &s.pos_x, nv) && dev_alloc(h, &s.pos_y, nv) && dev_alloc(h, &s.pos_z, nv) &&
+            dev_alloc(h, &s.heading, nv) && dev_alloc(h, &s.speed, nv) && dev_alloc(h, &s.yaw_rate, nv) &&
+            dev_alloc(h, &s.length, nv) && dev_alloc(h, &s.width, nv) && dev_alloc(h, &s.height, nv) &&
+            dev_alloc(h, &s.cos_h, nv) && dev_alloc(h, &s.sin_h, nv) && dev_alloc(h, &s.alive, nv) &&
+            dev_alloc(h, &s.steering, na) && dev_alloc(h, &s.v_long, na) && dev_alloc(h, &s.v_lat, na) &&
+            dev_alloc(h, &s.ctrl, na * SB_CTRL_STATE) && dev_alloc(h, &s.last_control, na * 3) &&
+            dev_alloc(h, &s.route, na * c.route_cap) && dev_alloc(h, &s.route_len, na) &&
+            dev_alloc(h, &s.status, na);
+  if (!ok) return SB_ENOMEM;
+  k_fill<<<(unsigned)((nv + 255) / 256), 256>>>(s.cos_h, nv, 1.0);
+  cudaMemset(s.route, 0xff, na * c.route_cap * sizeof(int32_t));
+  DObs& o = h->ob;
+  std::memset(&o, 0, sizeof(o));
+  ok = dev_alloc(h, &o.ego_lane, na);
+  if (ok && c.nbr_enable) {
+    size_t n = na * c.nbr_cap;
+    ok = dev_alloc(h, &o.nbr_count, na) && dev_alloc(h, &o.nbr_id, n) && dev_alloc(h, &o.nbr_pos, n * 3) &&
+         dev_alloc(h, &o.nbr_box, n * 3) && dev_alloc(h, &o.nbr_heading, n) && dev_alloc(h, &o.nbr_speed, n) &&
+         dev_alloc(h, &o.nbr_lane, n) && dev_alloc(h, &o.nbr_lane_index, n);
+  }
+  if (ok && c.wp_enable) {
+    size_t np = na * c.wp_out_paths, n = np * c.wp_out_len;
+    ok = dev_alloc(h, &o.wp_n_paths, na) && dev_alloc(h, &o.wp_len, np) && dev_alloc(h, &o.wp_pos, n * 3) &&
+         dev_alloc(h, &o.wp_heading, n) && dev_alloc(h, &o.wp_lane_width, n) && dev_alloc(h, &o.wp_speed_limit, n) &&
+         dev_alloc(h, &o.wp_lane, n) && dev_alloc(h, &o.wp_lane_index, n);
+  }
+  if (ok && c.lidar_enable)
+    ok = dev_alloc(h, &o.lidar_points, na * c.lidar_rays * 3) && dev_alloc(h, &o.lidar_hits, na * c.lidar_rays);
+  // the grids are the bulk of the memory (E*A*W*H bytes each); written in full every tick
+  if (ok && c.ogm_enable) ok = dev_alloc(h, &o.ogm, na * c.ogm_width * c.ogm_height, false);
+  if (ok && c.dagm_enable) ok = dev_alloc(h, &o.dagm, na * c.dagm_width * c.dagm_height, false);
+  if (!ok) return SB_ENOMEM;
+  if (!dev_alloc(h, &h->d_social, (size_t)d.E * (d.M ? d.M : 1) * 8)) return SB_ENOMEM;
+  h->actions_cap = action_bytes(c);
+  void* da = nullptr;
+  if (!cuda_ok(h, cudaMalloc(&da, h->actions_cap), "cudaMalloc(actions)")) return SB_ENOMEM;
+  h->allocs.push_back(da);
+  h->d_actions = da;
+  size_t b0 = c.ogm_enable ? (size_t)c.ogm_width * c.ogm_height / 8 : 0;
+  size_t b1 = c.dagm_enable ? (size_t)c.dagm_width * c.dagm_height / 8 : 0;
+  h->raster_smem = b0 > b1 ? b0 : b1;
+  if (h->raster_smem > 200 * 1024) return fail(h, SB_EINVAL, "grid too large for the shared-memory bit image");
+  if (h->raster_smem > 24 * 1024) {
+    if (!cuda_ok(h, cudaFuncSetAttribute(k_raster, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->raster_smem),
+                 "cudaFuncSetAttribute"))
+      return SB_ECUDA;
+  }
+  if (!cuda_ok(h, cudaDeviceSynchronize(), "sb_create sync")) return SB_ECUDA;
+  return SB_OK;
+}
+
+void sb_destroy(SbHandle h) {
+  if (!h) return;
+  cudaSetDevice(h->cfg.device);
+  cudaDeviceSynchronize();
+  for (void* p : h->allocs) cudaFree(p);
+  delete h;
+}
+
+int sb_upload_map(SbHandle h, const SbMap* mp) {
+  if (!h || !mp) return SB_EINVAL;
+  if (h->cuda_err) return SB_ECUDA;
+  if (h->have_map) return fail(h, SB_ESTATE, "map already uploaded");
+  if (mp->n_lanes < 1 || mp->n_lanepoints < 1) return fail(h, SB_EINVAL, "empty map");
+  cudaSetDevice(h->cfg.device);
+  DMap& m = h->dmap;
+  m.n_roads = mp->n_roads; m.n_lanes = mp->n_lanes; m.n_lanepoints = mp->n_lanepoints;
+  m.n_shape_pts = mp->n_shape_pts; m.n_polys = mp->n_polys; m.n_poly_verts = mp->n_poly_verts;
+  m.n_edges = mp->n_edges; m.lanepoint_spacing = mp->lanepoint_spacing;
+  // derived host tables: lane of every shape vertex; polygon AABBs (float, rounded outwards)
+  std::vector<int32_t> shape_lane(mp->n_shape_pts);
+  for (int l = 0; l < mp->n_lanes; ++l)
+    for (int i = mp->lane_shape_start[l]; i < mp->lane_shape_start[l + 1]; ++i) shape_lane[i] = l;
+  std::vector<float> bbox((size_t)mp->n_polys * 4);
+  for (int p = 0; p < mp->n_polys; ++p) {
+    int s = mp->poly_start[p], n = mp->poly_start[p + 1] - s;
+    if (n > 4) return fail(h, SB_EINVAL, "drivable-area polygons must have <= 4 vertices");
+    double x0 = 1e300, y0 = 1e300, x1 = -1e300, y1 = -1e300;
+    for (int k = 0; k < n; ++k) {
+      x0 = fmin(x0, mp->poly_x[s + k]); x1 = fmax(x1, mp->poly_x[s + k]);
+      y0 = fmin(y0, mp->poly_y[s + k]); y1 = fmax(y1, mp->poly_y[s + k]);
+    }
+    bbox[p * 4 + 0] = nextafterf((float)x0, -INFINITY);
+    bbox[p * 4 + 1] = nextafterf((float)y0, -INFINITY);
+    bbox[p * 4 + 2] = nextafterf((float)x1, INFINITY);
+    bbox[p * 4 + 3] = nextafterf((float)y1, INFINITY);
+  }
+  const size_t R = mp->n_roads, L = mp->n_lanes, P = mp->n_lanepoints;
+  bool ok = dev_upload(h, &m.road_lane_start, mp->road_lane_start, R) &&
+            dev_upload(h, &m.road_lane_count, mp->road_lane_count, R) &&
+            dev_upload(h, &m.road_is_junction, mp->road_is_junction, R) &&
+            dev_upload(h, &m.road_lp_start, mp->road_lp_start, R) &&
+            dev_upload(h, &m.road_lp_count, mp->road_lp_count, R) &&
+            dev_upload(h, &m.road_first_out, mp->road_first_out, R) &&
+            dev_upload(h, &m.lane_road, mp->lane_road, L) &&
+            dev_upload(h, &m.lane_idx_in_road, mp->lane_idx_in_road, L) &&
+            dev_upload(h, &m.lane_width, mp->lane_width, L) && dev_upload(h, &m.lane_speed, mp->lane_speed, L) &&
+            dev_upload(h, &m.lane_out_start, mp->lane_out_start, L + 1) &&
+            dev_upload(h, &m.lane_out, mp->lane_out, (size_t)(mp->n_lane_out > 0 ? mp->n_lane_out : 1)) &&
+            dev_upload(h, &m.lane_lp_start, mp->lane_lp_start, L) &&
+            dev_upload(h, &m.lane_lp_count, mp->lane_lp_count, L) &&
+            dev_upload(h, &m.lane_shape_start, mp->lane_shape_start, L + 1) &&
+            dev_upload(h, &m.lp_x, mp->lp_x, P) && dev_upload(h, &m.lp_y, mp->lp_y, P) &&
+            dev_upload(h, &m.lp_heading, mp->lp_heading, P) && dev_upload(h, &m.lp_inferred, mp->lp_inferred, P) &&
+            dev_upload(h, &m.lp_lane, mp->lp_lane, P) && dev_upload(h, &m.lp_next_start, mp->lp_next_start, P + 1) &&
+            dev_upload(h, &m.lp_next, mp->lp_next, (size_t)(mp->n_lp_next > 0 ? mp->n_lp_next : 1)) &&
+            dev_upload(h, &m.shape_x, mp->shape_x, (size_t)mp->n_shape_pts) &&
+            dev_upload(h, &m.shape_y, mp->shape_y, (size_t)mp->n_shape_pts) &&
+            dev_upload(h, &m.shape_lane, shape_lane.data(), shape_lane.size()) &&
+            dev_upload(h, &m.poly_start, mp->poly_start, (size_t)mp->n_polys + 1) &&
+            dev_upload(h, &m.poly_x, mp->poly_x, (size_t)mp->n_poly_verts) &&
+            dev_upload(h, &m.poly_y, mp->poly_y, (size_t)mp->n_poly_verts) &&
+            dev_upload(h, &m.poly_bbox, bbox.data(), bbox.size()) &&
+            dev_upload(h, &m.road_edges, mp->road_edges, (size_t)mp->n_edges * 4);
+  if (!ok) return SB_ECUDA;
+  h->have_map = true;
+  return SB_OK;
+}
+
+int sb_upload_lidar_rays(SbHandle h, const double* base_rays, int32_t n_rays) {
+  if (!h || !base_rays) return SB_EINVAL;
+  if (h->cuda_err) return SB_ECUDA;
+  if (n_rays != h->cfg.lidar_rays) return fail(h, SB_EINVAL, "n_rays != cfg.lidar_rays");
+  cudaSetDevice(h->cfg.device);
+  const double* d = nullptr;
+  if (!dev_upload(h, &d, base_rays, (size_t)n_rays * 3)) return SB_ECUDA;
+  h->d_rays = const_cast<double*>(d);
+  h->have_rays = true;
+  return SB_OK;
+}
+
+int sb_reset(SbHandle h, const int32_t* env_ids, int32_t n, const SbResetState* init) {
+  if (!h || !init || !init->agent_x || !init->agent_y || !init->agent_heading || !init->agent_speed) return SB_EINVAL;
+  if (h->cuda_err) return SB_ECUDA;
+  if (!h->have_map) return fail(h, SB_ESTATE, "sb_reset before sb_upload_map");
+  const DCfg& c = h->dc;
+  if (!env_ids) n = c.E;
+  if (n < 1 || n > c.E) return fail(h, SB_EINVAL, "n out of range");
+  if (env_ids)
+    for (int i = 0; i < n; ++i)
+      if (env_ids[i] < 0 || env_ids[i] >= c.E) return fail(h, SB_EINVAL, "env id out of range");
+  cudaSetDevice(h->cfg.device);
+  size_t na = (size_t)n * c.A;
+  // one staging buffer: ids | x | y | h | v | route | route_len
+  size_t off_ids = 0, off_x = ((size_t)n * 4 + 7) / 8 * 8, off_y = off_x + na * 8, off_h = off_y + na * 8,
+         off_v = off_h + na * 8, off_r = off_v + na * 8, off_rl = off_r + na * c.route_cap * 4,
+         total = off_rl + na * 4;
+  std::vector<unsigned char> host(total, 0);
+  if (env_ids) std::memcpy(&host[off_ids], env_ids, (size_t)n * 4);
+  std::memcpy(&host[off_x], init->agent_x, na * 8);
+  std::memcpy(&host[off_y], init->agent_y, na * 8);
+  std::memcpy(&host[off_h], init->agent_heading, na * 8);
+  std::memcpy(&host[off_v], init->agent_speed, na * 8);
+  if (init->route) std::memcpy(&host[off_r], init->route, na * c.route_cap * 4);
+  if (init->route_len) std::memcpy(&host[off_rl], init->route_len, na * 4);
+  unsigned char* dev = nullptr;
+  if (!cuda_ok(h, cudaMalloc(&dev, total), "cudaMalloc(reset)")) return SB_ECUDA;
+  bool ok = cuda_ok(h, cudaMemcpy(dev, host.data(), total, cudaMemcpyHostToDevice), "cudaMemcpy(reset)");
+  if (ok) {
+    int threads = n * c.V;
+    k_reset<<<(threads + 127) / 128, 128>>>(
+        c, h->st, env_ids ? reinterpret_cast<const int32_t*>(dev + off_ids) : nullptr, n,
+        reinterpret_cast<const double*>(dev + off_x), reinterpret_cast<const double*>(dev + off_y),
+        reinterpret_cast<const double*>(dev + off_h), reinterpret_cast<const double*>(dev + off_v),
+        init->route ? reinterpret_cast<const int32_t*>(dev + off_r) : nullptr,
+        init->route_len ? reinterpret_cast<const int32_t*>(dev + off_rl) : nullptr);
+    h->launches++;
+    ok = cuda_ok(h, cudaDeviceSynchronize(), "k_reset");
+  }
+  cudaFree(dev);
+  return ok ? SB_OK : SB_ECUDA;
+}
+
+int sb_set_social(SbHandle h, const double* dev_states, void* stream) {
+  if (!h) return SB_EINVAL;
+  if (h->cuda_err) return SB_ECUDA;
+  const DCfg& c = h->dc;
+  if (c.M == 0) return SB_OK;
+  if (!dev_states) return fail(h, SB_EINVAL, "dev_states is null");
+  int n = c.E * c.M;
+  k_set_social<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(c, h->st, dev_states);
+  h->launches++;
+  return cuda_ok(h, cudaGetLastError(), "k_set_social") ? SB_OK : SB_ECUDA;
+}
+
+int sb_step(SbHandle h, const void* dev_actions, void* stream) {
+  if (!h || !dev_actions) return SB_EINVAL;
+  if (h->cuda_err) return SB_ECUDA;
+  if (!h->have_map) return fail(h, SB_ESTATE, "sb_step before sb_upload_map");
+  const DCfg& c = h->dc;
+  int na = c.E * c.A;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (c.action_space == SB_ACTION_LANE || c.action_space == SB_ACTION_LANE_WITH_CONTINUOUS_SPEED) {
+    k_control_lane<<<(na + SB_CTRL_WARPS - 1) / SB_CTRL_WARPS, SB_CTRL_WARPS * 32, 0, st>>>(c, h->dmap, h->st,
+                                                                                          dev_actions);
+  } else {
+    k_control_simple<<<(na + 127) / 128, 128, 0, st>>>(c, h->st, static_cast<const double*>(dev_actions));
+  }
+  h->launches++;
+  return cuda_ok(h, cudaGetLastError(), "k_control") ? SB_OK : SB_ECUDA;
+}
+
+int sb_observe(SbHandle h, void* stream) {
+  if (!h) return SB_EINVAL;
+  if (h->cuda_err) return SB_ECUDA;
+  if (!h->have_map) return fail(h, SB_ESTATE, "sb_observe before sb_upload_map");
+  const DCfg& c = h->dc;
+  if (c.lidar_enable && !h->have_rays) return fail(h, SB_ESTATE, "lidar enabled but no ray table uploaded");
+  int na = c.E * c.A;
+  cudaStream_t st = (cudaStream_t)stream;
+  k_observe<<<(na + SB_OBS_WARPS - 1) / SB_OBS_WARPS, SB_OBS_WARPS * 32, 0, st>>>(c, h->dmap, h->st, h->ob);
+  h->launches++;
+  if (c.lidar_enable) {
+    k_lidar<<<na, SB_LIDAR_THREADS, 0, st>>>(c, h->dmap, h->st, h->ob, h->d_rays);
+    h->launches++;
+  }
+  if (c.ogm_enable || c.dagm_enable) {
+    k_raster<<<na, SB_RASTER_THREADS, h->raster_smem, st>>>(c, h->dmap, h->st, h->ob);
+    h->launches++;
+  }
+  return cuda_ok(h, cudaGetLastError(), "k_observe") ? SB_OK : SB_ECUDA;
+}
+
+int sb_step_host(SbHandle h, const void* host_actions, int64_t n_bytes, const double* host_social) {
+  if (!h || !host_actions) return SB_EINVAL;
+  if (h->cuda_err) return SB_ECUDA;
+  if ((size_t)n_bytes != h->actions_cap) return fail(h, SB_EINVAL, "action_bytes does not match the action space");
+  const DCfg& c = h->dc;
+  cudaSetDevice(h->cfg.device);
+  if (!cuda_ok(h, cudaMemcpyAsync(h->d_actions, host_actions, h->actions_cap, cudaMemcpyHostToDevice, 0), "H2D actions"))
+    return SB_ECUDA;
+  if (c.M > 0) {
+    if (!host_social) return fail(h, SB_EINVAL, "host_social is null");
+    if (!cuda_ok(h, cudaMemcpyAsync(h->d_social, host_social, (size_t)c.E * c.M * 8 * sizeof(double),
+                                    cudaMemcpyHostToDevice, 0), "H2D social"))
+      return SB_ECUDA;
+    int rc = sb_set_social(h, h->d_social, nullptr);
+    if (rc) return rc;
+  }
+  int rc = sb_step(h, h->d_actions, nullptr);
+  if (rc) return rc;
+  rc = sb_observe(h, nullptr);
+  if (rc) return rc;
+  return cuda_ok(h, cudaStreamSynchronize(0), "sb_step_host sync") ? SB_OK : SB_ECUDA;
+}
+
+int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs* dst) {
+  if (!h || !dst) return SB_EINVAL;
+  if (h->cuda_err) return SB_ECUDA;
+  const SbConfig& c = h->cfg;
+  const DObs& o = h->ob;
+  size_t na = (size_t)c.n_envs * c.n_agents;
+  cudaSetDevice(c.device);
+  bool ok = true;
+  auto cpy = [&](void* d, const void* s, size_t bytes) {
+    if (ok && d && s && bytes) ok = cuda_ok(h, cudaMemcpyAsync(d, s, bytes, cudaMemcpyDeviceToHost, 0), "D2H obs");
+  };
+  cpy(dst->ego_lane, o.ego_lane, na * 4);
+  if (c.nbr_enable) {
+    size_t n = na * c.nbr_cap;
+    cpy(dst->nbr_count, o.nbr_count, na * 4); cpy(dst->nbr_id, o.nbr_id, n * 4); cpy(dst->nbr_pos, o.nbr_pos, n * 24);
+    cpy(dst->nbr_box, o.nbr_box, n * 12); cpy(dst->nbr_heading, o.nbr_heading, n * 4);
+    cpy(dst->nbr_speed, o.nbr_speed, n * 4); cpy(dst->nbr_lane, o.nbr_lane, n * 4);
+    cpy(dst->nbr_lane_index, o.nbr_lane_index, n);
+  }
+  if (c.wp_enable) {
+    size_t np = na * c.wp_out_paths, n = np * c.wp_out_len;
+    cpy(dst->wp_n_paths, o.wp_n_paths, na * 4); cpy(dst->wp_len, o.wp_len, np * 4); cpy(dst->wp_pos, o.wp_pos, n * 24);
+    cpy(dst->wp_heading, o.wp_heading, n * 4); cpy(dst->wp_lane_width, o.wp_lane_width, n * 4);
+    cpy(dst->wp_speed_limit, o.wp_speed_limit, n * 4); cpy(dst->wp_lane, o.wp_lane, n * 4);
+    cpy(dst->wp_lane_index, o.wp_lane_index, n);
+  }
+  if (c.lidar_enable) {
+    cpy(dst->lidar_points, o.lidar_points, na * c.lidar_rays * 24);
+    cpy(dst->lidar_hits, o.lidar_hits, na * c.lidar_rays);
+  }
+  if (c.ogm_enable) cpy(dst->ogm, o.ogm, na * c.ogm_width * c.ogm_height);
+  if (c.dagm_enable) cpy(dst->dagm, o.dagm, na * c.dagm_width * c.dagm_height);
+  if (!ok) return SB_ECUDA;
+  return cuda_ok(h, cudaStreamSynchronize(0), "D2H obs sync") ? SB_OK : SB_ECUDA;
+}
+
+int sb_get_obs(SbHandle h, SbObsPtrs* out) {
+  if (!h || !out) return SB_EINVAL;
+  const DObs& o = h->ob;
+  out->ego_lane = o.ego_lane;
+  out->nbr_count = o.nbr_count; out->nbr_id = o.nbr_id; out->nbr_pos = o.nbr_pos; out->nbr_box = o.nbr_box;
+  out->nbr_heading = o.nbr_heading; out->nbr_speed = o.nbr_speed; out->nbr_lane = o.nbr_lane;
+  out->nbr_lane_index = o.nbr_lane_index;
+  out->wp_n_paths = o.wp_n_paths; out->wp_len = o.wp_len; out->wp_pos = o.wp_pos; out->wp_heading = o.wp_heading;
+  out->wp_lane_width = o.wp_lane_width; out->wp_speed_limit = o.wp_speed_limit; out->wp_lane = o.wp_lane;
+  out->wp_lane_index = o.wp_lane_index;
+  out->lidar_points = o.lidar_points; out->lidar_hits = o.lidar_hits;
+  out->ogm = o.ogm; out->dagm = o.dagm;
+  return SB_OK;
+}
+
+int sb_get_state(SbHandle h, SbStatePtrs* out) {
+  if (!h || !out) return SB_EINVAL;
+  const DState& s = h->st;
+  out->pos_x = s.pos_x; out->pos_y = s.pos_y; out->pos_z = s.pos_z; out->heading = s.heading; out->speed = s.speed;
+  out->yaw_rate = s.yaw_rate; out->length = s.length; out->width = s.width; out->height = s.height;
+  out->cos_h = s.cos_h; out->sin_h = s.sin_h; out->alive = s.alive;
+  out->steering = s.steering; out->v_long = s.v_long; out->v_lat = s.v_lat; out->ctrl = s.ctrl;
+  out->last_control = s.last_control; out->route = s.route; out->route_len = s.route_len; out->status = s.status;
+  return SB_OK;
+}
+
+}  // extern "C"

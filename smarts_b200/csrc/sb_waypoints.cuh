@@ -1,0 +1,314 @@
+// sb_waypoints.cuh -- warp-cooperative RoadMap.waypoint_paths
+// (smarts/core/sumo_road_network.py:815-882, :1278-1437; smarts/core/lanepoints.py:517-692).
+//
+// One warp serves one agent.  The three KD-tree queries of the reference become strided argmin
+// scans over index ranges of the lane-point arrays (all 32 lanes), the branch enumeration is a
+// depth-first walk on lane 0 (same leaf order as the reference's level-by-level expansion), and
+// the equal-arc-length re-spacing runs one path per lane.
+#pragma once
+
+#include "sb_device.cuh"
+
+struct WarpPaths {
+  int32_t lp[SB_MAX_PATHS][SB_MAX_LOOKAHEAD + 1];  // lane-point indices of each path
+  int32_t len[SB_MAX_PATHS];
+  int32_t n;         // paths stored
+  int32_t total;     // paths found
+  int32_t overflow;  // more than SB_MAX_PATHS
+  int32_t jr[2];     // junction route of _resolve_in_junction
+};
+
+struct DWaypoint {
+  double x, y, heading, lane_width, speed_limit;
+  int32_t lane, lane_index;
+};
+
+__device__ __forceinline__ double wp_sqdist(const DMap& m, int i, double x, double y) {
+  double dx = m.lp_x[i] - x, dy = m.lp_y[i] - y;
+  return dx * dx + dy * dy;
+}
+
+// KD-tree k=1 over [start, start+count): lowest index wins ties.  All lanes return the result.
+__device__ int wp_closest_in_range(const DMap& m, int start, int count, double x, double y, int lane) {
+  double bd = 1e300;
+  int bi = 0x7fffffff;
+  for (int i = start + lane; i < start + count; i += 32) {
+    double d = wp_sqdist(m, i, x, y);
+    if (d < bd) {
+      bd = d;
+      bi = i;
+    }
+  }
+  warp_argmin(bd, bi);
+  return bi == 0x7fffffff ? -1 : bi;
+}
+
+// lanepoints.py:526-623: closest_lanepoints([pose], within_radius, maximum_count=10)[0]
+__device__ int wp_closest_with_pose(const DMap& m, double x, double y, double h, double within_radius, int lane) {
+  const int P = m.n_lanepoints;
+  const int k = P < 10 ? P : 10;
+  int idx[10];
+  double d2[10];
+  int n = 0;
+  double last_d = -1.0;
+  int last_i = -1;
+  for (int r = 0; r < k; ++r) {
+    double bd = 1e300;
+    int bi = 0x7fffffff;
+    for (int i = lane; i < P; i += 32) {
+      double d = wp_sqdist(m, i, x, y);
+      bool after = (d > last_d) || (d == last_d && i > last_i);
+      if (r > 0 && !after) continue;
+      if (d < bd) {
+        bd = d;
+        bi = i;
+      }
+    }
+    warp_argmin(bd, bi);
+    if (bi == 0x7fffffff) break;
+    idx[n] = bi;
+    d2[n] = bd;
+    ++n;
+    last_d = bd;
+    last_i = bi;
+  }
+  // every lane holds the same list; finish redundantly (tiny)
+  int best = -1;
+  double bk = 0.0;
+  double r2 = within_radius * within_radius;
+  for (int i = 0; i < n; ++i) {
+    if (within_radius >= 0.0 && !(d2[i] <= r2 || i == 0)) continue;
+    double rel = d_wrap_heading(h - m.lp_heading[idx[i]]);
+    double key = d2[i] + fabs(rel);
+    if (best < 0 || key < bk) {
+      best = idx[i];
+      bk = key;
+    }
+  }
+  return best;
+}
+
+__device__ __forceinline__ bool wp_in_route(const int32_t* route, int n, int road) {
+  for (int i = 0; i < n; ++i)
+    if (route[i] == road) return true;
+  return false;
+}
+
+// lanepoints.py:646-692 as a depth-first walk (lane 0 only).  Appends to wpaths.
+__device__ void wp_enumerate_paths(const DMap& m, int start, int lookahead, const int32_t* filt, int nf,
+                                   WarpPaths* wp) {
+  int32_t node[SB_MAX_LOOKAHEAD + 1];
+  int32_t cursor[SB_MAX_LOOKAHEAD + 1];
+  uint8_t had_child[SB_MAX_LOOKAHEAD + 1];
+  int d = 0;
+  node[0] = start;
+  cursor[0] = m.lp_next_start[start];
+  had_child[0] = 0;
+  while (d >= 0) {
+    bool emit = false;
+    if (d == lookahead) {
+      emit = true;
+    } else {
+      bool found = false;
+      int end = m.lp_next_start[node[d] + 1];
+      while (cursor[d] < end) {
+        int nlp = m.lp_next[cursor[d]++];
+        int nlane = m.lp_lane[nlp];
+        int road = m.lane_road[nlane];
+        if (nf > 0) {
+          if (!wp_in_route(filt, nf, road)) continue;
+          if (road != filt[nf - 1]) {
+            bool any = false;
+            for (int o = m.lane_out_start[nlane]; o < m.lane_out_start[nlane + 1]; ++o)
+              if (wp_in_route(filt, nf, m.lane_road[m.lane_out[o]])) any = true;
+            if (!any) continue;
+          }
+        }
+        had_child[d] = 1;
+        ++d;
+        node[d] = nlp;
+        cursor[d] = m.lp_next_start[nlp];
+        had_child[d] = 0;
+        found = true;
+        break;
+      }
+      if (found) continue;
+      if (!had_child[d]) emit = true;
+    }
+    if (emit) {
+      wp->total++;
+      if (wp->n < SB_MAX_PATHS) {
+        int k = wp->n++;
+        wp->len[k] = d + 1;
+        for (int i = 0; i <= d; ++i) wp->lp[k][i] = node[i];
+      } else {
+        wp->overflow = 1;
+      }
+    }
+    --d;
+  }
+}
+
+// Lane._waypoint_paths_at for every lane of `road` (sumo_road_network.py:429-446, :838-839, :880-881)
+__device__ void wp_paths_on_road(const DMap& m, int road, double x, double y, int lookahead, const int32_t* filt,
+                                 int nf, WarpPaths* wp, int lane) {
+  int l0 = m.road_lane_start[road], l1 = l0 + m.road_lane_count[road];
+  for (int l = l0; l < l1; ++l) {
+    int cnt = m.lane_lp_count[l];
+    if (cnt <= 0) continue;
+    int lp = wp_closest_in_range(m, m.lane_lp_start[l], cnt, x, y, lane);
+    if (lane == 0) wp_enumerate_paths(m, lp, lookahead, filt, nf, wp);
+    __syncwarp();
+  }
+}
+
+// RoadMap.waypoint_paths: fills wp (shared memory, one per warp).  route_len < 0: no route
+// object; == 0: empty Route (-> _resolve_in_junction).
+__device__ void wp_waypoint_paths(const DMap& m, double x, double y, double h, int lookahead, double within_radius,
+                                  const int32_t* route, int route_len, WarpPaths* wp, int lane) {
+  if (lane == 0) {
+    wp->n = 0;
+    wp->total = 0;
+    wp->overflow = 0;
+  }
+  __syncwarp();
+  const int32_t* roads = route;
+  int nr = route_len;
+  if (route_len == 0) {
+    int lp = wp_closest_with_pose(m, x, y, h, -1.0, lane);
+    nr = 0;
+    if (lp >= 0) {
+      int road = m.lane_road[m.lp_lane[lp]];
+      if (m.road_is_junction[road]) {
+        int fo = m.road_first_out[road];
+        if (lane == 0) {
+          wp->jr[0] = road;
+          wp->jr[1] = fo;
+        }
+        nr = fo >= 0 ? 2 : 1;
+      }
+    }
+    __syncwarp();
+    roads = wp->jr;
+  }
+  if (route_len >= 0 && nr > 0) {
+    int best = -1;
+    double bd = 0.0;
+    for (int r = 0; r < nr; ++r) {
+      int road = roads[r];
+      int cnt = m.road_lp_count[road];
+      if (cnt <= 0) continue;
+      int lp = wp_closest_in_range(m, m.road_lp_start[road], cnt, x, y, lane);
+      double d = sqrt(wp_sqdist(m, lp, x, y));
+      if (best < 0 || d < bd) {
+        best = lp;
+        bd = d;
+      }
+    }
+    if (best >= 0) {
+      wp_paths_on_road(m, m.lane_road[m.lp_lane[best]], x, y, lookahead, roads, nr, wp, lane);
+      return;
+    }
+  }
+  int lp = wp_closest_with_pose(m, x, y, h, within_radius, lane);
+  if (lp < 0) return;
+  wp_paths_on_road(m, m.lane_road[m.lp_lane[lp]], x, y, lookahead, nullptr, 0, wp, lane);
+}
+
+// rank of path k after sorted(paths, key=first waypoint's lane_index) (stable)
+__device__ __forceinline__ int wp_rank(const DMap& m, const WarpPaths* wp, int k) {
+  int key = m.lane_idx_in_road[m.lp_lane[wp->lp[k][0]]];
+  int rank = 0;
+  for (int j = 0; j < wp->n; ++j) {
+    int kj = m.lane_idx_in_road[m.lp_lane[wp->lp[j][0]]];
+    if (kj < key || (kj == key && j < k)) ++rank;
+  }
+  return rank;
+}
+
+// sumo_road_network.py:1312-1437, one path, executed by a single lane.  Calls emit(i, waypoint)
+// for the first min(n_out, n) waypoints.  MAXN bounds the path length (lookahead + 1).
+template <int MAXN, class Emit>
+__device__ int wp_equally_spaced(const DMap& m, const int32_t* path, int n, double vx, double vy, int n_out,
+                                 Emit emit) {
+  double rx[MAXN], ry[MAXN], rh[MAXN], cum[MAXN];
+  int32_t rlane[MAXN];
+  int mm = 0;
+  for (int i = 0; i < n; ++i) {
+    int lp = path[i];
+    if (m.lp_inferred[lp] && 0 < i && i < n - 1) continue;
+    rx[mm] = m.lp_x[lp];
+    ry[mm] = m.lp_y[lp];
+    rh[mm] = m.lp_heading[lp];
+    rlane[mm] = m.lp_lane[lp];
+    ++mm;
+  }
+  {  // inplace_unwrap, utils/math.py:537-550
+    double acc = 0.0, prev = rh[0];
+    for (int i = 1; i < mm; ++i) {
+      double cur = rh[i];
+      double dd = cur - prev;
+      double ddmod = sb_pymod(dd + SB_PI, SB_TWO_PI) - SB_PI;
+      if (ddmod == -SB_PI && dd > 0) ddmod = SB_PI;
+      double corr = ddmod - dd;
+      if (fabs(dd) < SB_PI) corr = 0.0;
+      acc += corr;
+      prev = cur;
+      rh[i] = cur + acc;
+    }
+  }
+  double hvx, hvy;
+  d_radians_to_vec(rh[0], &hvx, &hvy);
+  int lp0 = path[0];
+  double lx = m.lp_x[lp0], ly = m.lp_y[lp0];
+  double proj = (vx - lx) * hvx + (vy - ly) * hvy;
+  rx[0] = lx + proj * hvx;
+  ry[0] = ly + proj * hvy;
+  cum[0] = 0.0;
+  for (int i = 1; i < mm; ++i) {
+    double dx = rx[i] - rx[i - 1], dy = ry[i] - ry[i - 1];
+    cum[i] = cum[i - 1] + sqrt(dx * dx + dy * dy);
+  }
+  if ((double)mm <= m.lanepoint_spacing) {  // sic (:1379)
+    int lane = m.lp_lane[lp0];
+    DWaypoint w{lx, ly, m.lp_heading[lp0], m.lane_width[lane], m.lane_speed[lane], lane, m.lane_idx_in_road[lane]};
+    if (n_out > 0) emit(0, w);
+    return 1;
+  }
+  double total = cum[mm - 1];
+  double step = total / (double)(n - 1);
+  int jd = 0, j = 0;
+  int lim = n < n_out ? n : n_out;
+  for (int i = 0; i < lim; ++i) {
+    double s = (i == n - 1) ? total : (double)i * step;
+    if (s > cum[mm - 1]) {
+      j = mm - 1;
+    } else {
+      while (j + 1 < mm && cum[j + 1] <= s) ++j;  // s is non-decreasing in i
+    }
+    DWaypoint w;
+    if (j >= mm - 1 || cum[j] == s) {
+      int l = rlane[j];
+      w.x = rx[j];
+      w.y = ry[j];
+      w.heading = rh[j];
+      w.lane_width = m.lane_width[l];
+      w.speed_limit = m.lane_speed[l];
+    } else {
+      double den = cum[j + 1] - cum[j], ds = s - cum[j];
+      int la = rlane[j], lb = rlane[j + 1];
+      w.x = ((rx[j + 1] - rx[j]) / den) * ds + rx[j];
+      w.y = ((ry[j + 1] - ry[j]) / den) * ds + ry[j];
+      w.heading = ((rh[j + 1] - rh[j]) / den) * ds + rh[j];
+      double wa = m.lane_width[la], wb = m.lane_width[lb], sa = m.lane_speed[la], sb_ = m.lane_speed[lb];
+      w.lane_width = ((wb - wa) / den) * ds + wa;
+      w.speed_limit = ((sb_ - sa) / den) * ds + sa;
+    }
+    w.heading = d_wrap_heading(w.heading);
+    while (jd + 1 < mm && s > cum[jd + 1]) ++jd;
+    w.lane = rlane[jd];
+    w.lane_index = m.lane_idx_in_road[w.lane];
+    emit(i, w);
+  }
+  return n;
+}

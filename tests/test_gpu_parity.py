@@ -1,0 +1,245 @@
+"""GPU parity: the CUDA path (through the C-ABI, via smarts_b200.engine's ctypes loader) against
+the CPU oracle on identical seeded inputs.  Everything is compared BIT-EXACT -- integers and
+bytes by contract, floating point because both sides evaluate the same binary64 operation
+sequences without FMA contraction (include/sb_detmath.h); the 1e-4 relative tolerance BASELINE
+allows for poses / speeds / LiDAR distances is therefore met with zero error."""
+import numpy as np
+import pytest
+
+from conftest import load_map, make_cfg, oracle_world
+from smarts_b200 import _abi, lidar_params, scenario_gen
+
+pytestmark = pytest.mark.gpu
+
+MISSIONS_4LANE = [("edge-south-SN", 1, 10.0, "edge-west-EW"), ("edge-west-WE", 0, 10.0, "edge-east-WE"),
+                  ("edge-north-NS", 0, 10.0, "edge-south-NS"), ("edge-east-EW", 1, 10.0, "edge-west-EW")]
+MISSIONS_LOOP = [("445633931", 0, 10.0, "445633932"), ("445633931", 2, 40.0, "445633932")]
+MISSIONS_F8 = [("gneE20", 0, 5.0, "gneE27"), ("gneE36", 1, 5.0, "gneE25"), ("gneE20", 2, 25.0, "gneE27"),
+               ("gneE36", 0, 30.0, "gneE25")]
+
+
+def engine(rm, cfg):
+    from smarts_b200.engine import Engine
+    return Engine(cfg, rm, lidar_params.base_rays(lidar_params.BasicLidar))
+
+
+def assert_same(got: dict, want: dict, keys=None):
+    for k in (keys or want.keys()):
+        g, w = got[k], want[k]
+        assert g.shape == w.shape, k
+        if g.dtype.kind == "f":
+            same = (g.view(np.uint8) == w.view(np.uint8)).all() or np.array_equal(g, w)  # -0.0 == 0.0 tolerated
+        else:
+            same = np.array_equal(g.view(w.dtype) if g.dtype != w.dtype else g, w)
+        if not same:
+            bad = np.argwhere(g != w)
+            raise AssertionError(f"{k}: {len(bad)} mismatches, first at {bad[0]}: got {g[tuple(bad[0])]} want {w[tuple(bad[0])]}")
+
+
+def run_pair(rm, cfg, missions, ticks, seed, action_fn, jitter=20.0, check_every=1, social_alive=0.9):
+    import torch
+    E, M = cfg.n_envs, cfg.n_social
+    x, y, h, v, route, rlen = scenario_gen.agent_starts(rm, E, missions, cfg.route_cap, seed, jitter=jitter, speed=5.0)
+    traffic = scenario_gen.SocialTraffic(rm, E, M, seed + 1, p_alive=social_alive) if M else None
+    eng = engine(rm, cfg)
+    ora = oracle_world(rm, cfg, threads=8)
+    eng.reset(x, y, h, v, route, rlen)
+    ora.reset(x, y, h, v, route, rlen)
+    for t in range(ticks):
+        act = action_fn(t, ora)
+        if traffic is not None:
+            soc = traffic.states(t)
+            eng.set_social(torch.from_numpy(soc).cuda())
+            ora.set_social(soc)
+        eng.step(torch.from_numpy(act).cuda())
+        ora.step(act)
+        if t % check_every == 0 or t == ticks - 1:
+            eng.observe()
+            ora.observe()
+            assert_same(eng.state_numpy(), ora.state())
+            assert_same(eng.obs_numpy(), ora.obs())
+    return eng, ora
+
+
+def lane_actions(E, A, seed):
+    rng = np.random.default_rng(seed)
+
+    def fn(t, _):
+        return rng.integers(0, 4, (E, A)).astype(np.int32)
+    return fn
+
+
+def test_config2_figure_eight_neighbors_waypoints():
+    """BASELINE configs[1] shape: 4 agents x envs, NeighborhoodVehicles + Waypoints, recorded traffic."""
+    rm = load_map("figure_eight")
+    E, A, M = 24, 4, 20
+    cfg = make_cfg(E=E, A=A, M=M, nbr=True, nbr_radius=50.0, wp=True, wp_lookahead=32, route_cap=24)
+    run_pair(rm, cfg, MISSIONS_F8, ticks=40, seed=7, action_fn=lane_actions(E, A, 3))
+
+
+def test_config3_4lane_lidar_ogm_dagm():
+    """BASELINE configs[2] shape: LiDAR 300 rays + OGM + DAGM 256x256 @ 0.1 m/px (few envs)."""
+    rm = load_map("4lane")
+    E, A, M = 6, 4, 20
+    cfg = make_cfg(E=E, A=A, M=M, lidar=True, wall=1.5, ogm=(256, 256, 0.1), dagm=(256, 256, 0.1), route_cap=16)
+    eng, ora = run_pair(rm, cfg, MISSIONS_4LANE, ticks=30, seed=11, action_fn=lane_actions(E, A, 5), check_every=5)
+    o = ora.obs()
+    assert o["ogm"].max() == 255 and o["dagm"].max() == 255 and o["lidar_hits"].sum() > 0
+    assert 0.05 < (o["dagm"] == 255).mean() < 0.95
+
+
+def test_config1_loop_laner_full_suite():
+    """BASELINE configs[0] shape: Laner agent, keep_lane, waypoints + LiDAR + OGM 64x64 @ 50/64."""
+    rm = load_map("loop")
+    E, A, M = 4, 2, 20
+    cfg = make_cfg(E=E, A=A, M=M, nbr=True, wp=True, lidar=True, lidar_miss_inf=1, ogm=(64, 64, 50 / 64),
+                   dagm=(64, 64, 50 / 64), route_cap=8)
+
+    def keep(t, _):
+        return np.zeros((E, A), np.int32)
+    run_pair(rm, cfg, MISSIONS_LOOP, ticks=120, seed=42, action_fn=keep, check_every=10)
+
+
+def test_lane_with_continuous_speed_and_rollout_stays_on_road():
+    rm = load_map("4lane")
+    E, A = 8, 4
+    cfg = make_cfg(E=E, A=A, M=0, action_space=_abi.SB_ACTION_LANE_WITH_CONTINUOUS_SPEED, wp=True, route_cap=16)
+    rng = np.random.default_rng(1)
+
+    def fn(t, _):
+        a = np.zeros((E, A, 2))
+        a[..., 0] = rng.uniform(0, 14, (E, A))
+        a[..., 1] = rng.integers(-1, 2, (E, A))
+        return a
+    run_pair(rm, cfg, MISSIONS_4LANE, ticks=60, seed=2, action_fn=fn, check_every=6)
+
+
+def test_trajectory_tracking_action_space():
+    """BASELINE configs[3] shape: Trajectory action = first 10 waypoints of path 0 at 50/3.6 m/s
+    (examples/trajectory_tracking_agent.py:16-37), fed back from the oracle's own observation."""
+    rm = load_map("figure_eight")
+    E, A, N = 6, 4, 10
+    cfg = make_cfg(E=E, A=A, M=10, action_space=_abi.SB_ACTION_TRAJECTORY, traj_len=N, wp=True, wp_len=20,
+                   route_cap=24)
+    ora0 = oracle_world(rm, cfg)
+    x, y, h, v, route, rlen = scenario_gen.agent_starts(rm, E, MISSIONS_F8, cfg.route_cap, 13, jitter=20.0, speed=5.0)
+    ora0.reset(x, y, h, v, route, rlen)
+    ora0.observe()
+
+    def fn(t, ora):
+        ora.observe()
+        o = ora.obs()
+        act = np.zeros((E, A, 4, N))
+        act[:, :, 0] = o["wp_pos"][:, :, 0, :N, 0]
+        act[:, :, 1] = o["wp_pos"][:, :, 0, :N, 1]
+        act[:, :, 2] = o["wp_heading"][:, :, 0, :N].astype(np.float64)
+        act[:, :, 3] = 50 / 3.6
+        return act
+    run_pair(rm, cfg, MISSIONS_F8, ticks=50, seed=13, action_fn=fn, check_every=5)
+
+
+@pytest.mark.parametrize("space", [_abi.SB_ACTION_CONTINUOUS, _abi.SB_ACTION_ACTUATOR_DYNAMIC])
+def test_continuous_action_spaces(space):
+    rm = load_map("straight")
+    E, A = 16, 3
+    cfg = make_cfg(E=E, A=A, M=6, action_space=space, nbr=True, nbr_radius=-1.0, wp=True, ogm=(64, 64, 0.5),
+                   route_cap=4)
+    rng = np.random.default_rng(9)
+    missions = [("west", 0, 5.0, "east"), ("west", 1, 15.0, "east"), ("west", 2, 25.0, "east")]
+
+    def fn(t, _):
+        a = rng.uniform(-0.2, 1.2, (E, A, 3))
+        a[..., 2] = rng.uniform(-1.3, 1.3, (E, A))
+        return a
+    run_pair(rm, cfg, missions, ticks=40, seed=17, action_fn=fn, check_every=4)
+
+
+def test_edge_cases_empty_social_dead_slots_and_partial_reset():
+    import torch
+    rm = load_map("4lane")
+    E, A, M = 5, 4, 8
+    cfg = make_cfg(E=E, A=A, M=M, nbr=True, nbr_radius=30.0, nbr_cap=3, wp=True, lidar=True,
+                   ogm=(128, 64, 0.25), dagm=(64, 128, 0.25), route_cap=16)
+    x, y, h, v, route, rlen = scenario_gen.agent_starts(rm, E, MISSIONS_4LANE, cfg.route_cap, 3, jitter=30.0, speed=8.0)
+    eng, ora = engine(rm, cfg), oracle_world(rm, cfg)
+    for w in (eng, ora):
+        w.reset(x, y, h, v, route, rlen)
+    # no social set at all: every social slot dead
+    eng.observe(); ora.observe()
+    assert_same(eng.obs_numpy(), ora.obs())
+    assert (ora.obs()["nbr_count"] <= A - 1).all()
+    # ragged: some slots alive, vehicles stacked on the ego (lidar origin inside a box, OGM overlap)
+    soc = scenario_gen.SocialTraffic(rm, E, M, 5, p_alive=0.5).states(0)
+    soc[0, 0, :3] = [x[0, 0], y[0, 0], h[0, 0]]
+    soc[0, 0, 7] = 1.0
+    soc[1, :, 7] = 0.0
+    act = np.zeros((E, A), np.int32)
+    for t in range(3):
+        eng.set_social(torch.from_numpy(soc).cuda()); ora.set_social(soc)
+        eng.step(torch.from_numpy(act).cuda()); ora.step(act)
+    eng.observe(); ora.observe()
+    assert_same(eng.state_numpy(), ora.state())
+    assert_same(eng.obs_numpy(), ora.obs())
+    # partial reset of two envs (auto-reset path of ParallelEnv, parallel_env.py:267-326)
+    ids = np.array([3, 1], np.int32)
+    for w in (eng, ora):
+        w.reset(x[ids], y[ids], h[ids], v[ids], route[ids], rlen[ids], env_ids=ids)
+    eng.observe(); ora.observe()
+    assert_same(eng.state_numpy(), ora.state())
+    assert_same(eng.obs_numpy(), ora.obs())
+
+
+def test_off_map_and_no_route_agents():
+    """Agents far from any lane and agents with an empty Route (-> _resolve_in_junction /
+    closest_lanepoints fallback, sumo_road_network.py:822-840)."""
+    import torch
+    rm = load_map("4lane")
+    E, A = 6, 4
+    cfg = make_cfg(E=E, A=A, M=0, nbr=True, wp=True, dagm=(64, 64, 0.5), route_cap=16)
+    rng = np.random.default_rng(4)
+    x = rng.uniform(100, 200, (E, A)); y = rng.uniform(-110, -10, (E, A))
+    x[0, :] = [500.0, -300.0, 150.0, 150.0]; y[0, :] = [500.0, 40.0, -60.0, -59.0]
+    h = rng.uniform(-3.1, 3.1, (E, A)); v = np.zeros((E, A))
+    eng, ora = engine(rm, cfg), oracle_world(rm, cfg)
+    for w in (eng, ora):
+        w.reset(x, y, h, v, None, None)
+    act = np.zeros((E, A), np.int32)
+    for t in range(5):
+        eng.step(torch.from_numpy(act).cuda()); ora.step(act)
+        eng.observe(); ora.observe()
+        assert_same(eng.state_numpy(), ora.state())
+        assert_same(eng.obs_numpy(), ora.obs())
+
+
+def test_full_size_grid_properties():
+    """At BASELINE's full grid size the oracle is too slow for many envs, so check size-independent
+    properties on a larger batch: determinism (two runs bit-identical), OGM == 255 at the ego's
+    own projected centre (test_observations.py:179-187), DAGM covers the ego when on road, and
+    translation invariance (shifting nothing but env index leaves results unchanged)."""
+    import torch
+    rm = load_map("4lane")
+    E, A, M = 256, 4, 20
+    cfg = make_cfg(E=E, A=A, M=M, lidar=True, ogm=(256, 256, 0.1), dagm=(256, 256, 0.1), route_cap=16)
+    x, y, h, v, route, rlen = scenario_gen.agent_starts(rm, E, MISSIONS_4LANE, cfg.route_cap, 21, jitter=25.0, speed=6.0)
+    # env e and env e + E/2 are identical copies
+    half = E // 2
+    for arr in (x, y, h, v, route, rlen):
+        arr[half:] = arr[:half]
+    soc = scenario_gen.SocialTraffic(rm, E, M, 22).states(0)
+    soc[half:] = soc[:half]
+    outs = []
+    for rep in range(2):
+        eng = engine(rm, cfg)
+        eng.reset(x, y, h, v, route, rlen)
+        eng.set_social(torch.from_numpy(soc).cuda())
+        eng.step(torch.zeros((E, A), dtype=torch.int32, device="cuda"))
+        eng.observe()
+        outs.append(eng.obs_numpy())
+        eng.close()
+    for k in outs[0]:
+        assert np.array_equal(outs[0][k], outs[1][k]), k
+        assert np.array_equal(outs[0][k][:half], outs[0][k][half:]), k
+    ogm, dagm = outs[0]["ogm"], outs[0]["dagm"]
+    assert (ogm[:, :, 127:129, 127:129] == 255).all()
+    assert (dagm[:, :, 127:129, 127:129] == 255).all()
+    assert set(np.unique(ogm)) <= {0, 255} and set(np.unique(dagm)) <= {0, 255}
