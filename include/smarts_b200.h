@@ -216,6 +216,18 @@ int sb_get_obs(SbHandle h, SbObsPtrs *out);
 int sb_get_state(SbHandle h, SbStatePtrs *out);
 /* number of kernel launches issued by this handle so far (bench gpu_launches) */
 int64_t sb_launch_count(SbHandle h);
+/* Per-kernel device timing (the tracing hook; the reference wraps SMARTS.step in a `timeit`
+ * logger, smarts/core/utils/logging.py:29-43).  With timing on, every kernel launch is bracketed
+ * by CUDA events on its stream; sb_collect_timing synchronises and returns, per kernel kind,
+ * the summed milliseconds and the number of launches since the last collect. */
+#define SB_K_SOCIAL 0
+#define SB_K_CONTROL 1
+#define SB_K_OBSERVE 2
+#define SB_K_LIDAR 3
+#define SB_K_RASTER 4
+#define SB_K_COUNT 5
+int sb_set_timing(SbHandle h, int on);
+int sb_collect_timing(SbHandle h, double *ms_sum /*[SB_K_COUNT]*/, int64_t *count /*[SB_K_COUNT]*/);
 const char *sb_last_error(SbHandle h);
 int sb_abi_version(void);
 

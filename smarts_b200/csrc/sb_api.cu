@@ -21,6 +21,12 @@ struct SbHandle_ {
   size_t actions_cap = 0;
   double* d_social = nullptr;
   int64_t launches = 0;
+  // optional per-kernel CUDA-event timing (sb_set_timing / sb_collect_timing)
+  bool timing = false;
+  std::vector<cudaEvent_t> ev_pool;
+  size_t ev_used = 0;
+  struct Span { int kind; cudaEvent_t a, b; };
+  std::vector<Span> spans;
   int cuda_err = 0;
   std::string err;
   size_t raster_smem = 0;
@@ -106,6 +112,37 @@ __global__ void k_reset(DCfg c, DState s, const int32_t* env_ids, int n, const d
     s.sin_h[vi] = 0.0;
   }
 }
+
+cudaEvent_t next_event(SbHandle h) {
+  if (h->ev_used == h->ev_pool.size()) {
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    h->ev_pool.push_back(e);
+  }
+  return h->ev_pool[h->ev_used++];
+}
+
+// brackets one kernel launch with events on its stream when timing is enabled
+struct LaunchScope {
+  SbHandle h;
+  cudaStream_t st;
+  cudaEvent_t a = nullptr, b = nullptr;
+  int kind;
+  LaunchScope(SbHandle h_, int kind_, cudaStream_t st_) : h(h_), st(st_), kind(kind_) {
+    h->launches++;
+    if (h->timing) {
+      a = next_event(h);
+      b = next_event(h);
+      cudaEventRecord(a, st);
+    }
+  }
+  ~LaunchScope() {
+    if (h->timing) {
+      cudaEventRecord(b, st);
+      h->spans.push_back({kind, a, b});
+    }
+  }
+};
 
 size_t action_bytes(const SbConfig& c) {
   size_t na = (size_t)c.n_envs * c.n_agents;
@@ -355,8 +392,10 @@ int sb_set_social(SbHandle h, const double* dev_states, void* stream) {
   if (c.M == 0) return SB_OK;
   if (!dev_states) return fail(h, SB_EINVAL, "dev_states is null");
   int n = c.E * c.M;
-  k_set_social<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(c, h->st, dev_states);
-  h->launches++;
+  {
+    LaunchScope ls(h, SB_K_SOCIAL, (cudaStream_t)stream);
+    k_set_social<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(c, h->st, dev_states);
+  }
   return cuda_ok(h, cudaGetLastError(), "k_set_social") ? SB_OK : SB_ECUDA;
 }
 
@@ -367,13 +406,15 @@ int sb_step(SbHandle h, const void* dev_actions, void* stream) {
   const DCfg& c = h->dc;
   int na = c.E * c.A;
   cudaStream_t st = (cudaStream_t)stream;
-  if (c.action_space == SB_ACTION_LANE || c.action_space == SB_ACTION_LANE_WITH_CONTINUOUS_SPEED) {
-    k_control_lane<<<(na + SB_CTRL_WARPS - 1) / SB_CTRL_WARPS, SB_CTRL_WARPS * 32, 0, st>>>(c, h->dmap, h->st,
-                                                                                          dev_actions);
-  } else {
-    k_control_simple<<<(na + 127) / 128, 128, 0, st>>>(c, h->st, static_cast<const double*>(dev_actions));
+  {
+    LaunchScope ls(h, SB_K_CONTROL, st);
+    if (c.action_space == SB_ACTION_LANE || c.action_space == SB_ACTION_LANE_WITH_CONTINUOUS_SPEED) {
+      k_control_lane<<<(na + SB_CTRL_WARPS - 1) / SB_CTRL_WARPS, SB_CTRL_WARPS * 32, 0, st>>>(c, h->dmap, h->st,
+                                                                                            dev_actions);
+    } else {
+      k_control_simple<<<(na + 127) / 128, 128, 0, st>>>(c, h->st, static_cast<const double*>(dev_actions));
+    }
   }
-  h->launches++;
   return cuda_ok(h, cudaGetLastError(), "k_control") ? SB_OK : SB_ECUDA;
 }
 
@@ -385,15 +426,17 @@ int sb_observe(SbHandle h, void* stream) {
   if (c.lidar_enable && !h->have_rays) return fail(h, SB_ESTATE, "lidar enabled but no ray table uploaded");
   int na = c.E * c.A;
   cudaStream_t st = (cudaStream_t)stream;
-  k_observe<<<(na + SB_OBS_WARPS - 1) / SB_OBS_WARPS, SB_OBS_WARPS * 32, 0, st>>>(c, h->dmap, h->st, h->ob);
-  h->launches++;
+  {
+    LaunchScope ls(h, SB_K_OBSERVE, st);
+    k_observe<<<(na + SB_OBS_WARPS - 1) / SB_OBS_WARPS, SB_OBS_WARPS * 32, 0, st>>>(c, h->dmap, h->st, h->ob);
+  }
   if (c.lidar_enable) {
+    LaunchScope ls(h, SB_K_LIDAR, st);
     k_lidar<<<na, SB_LIDAR_THREADS, 0, st>>>(c, h->dmap, h->st, h->ob, h->d_rays);
-    h->launches++;
   }
   if (c.ogm_enable || c.dagm_enable) {
+    LaunchScope ls(h, SB_K_RASTER, st);
     k_raster<<<na, SB_RASTER_THREADS, h->raster_smem, st>>>(c, h->dmap, h->st, h->ob);
-    h->launches++;
   }
   return cuda_ok(h, cudaGetLastError(), "k_observe") ? SB_OK : SB_ECUDA;
 }
@@ -455,6 +498,34 @@ int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs* dst) {
   if (c.dagm_enable) cpy(dst->dagm, o.dagm, na * c.dagm_width * c.dagm_height);
   if (!ok) return SB_ECUDA;
   return cuda_ok(h, cudaStreamSynchronize(0), "D2H obs sync") ? SB_OK : SB_ECUDA;
+}
+
+int sb_set_timing(SbHandle h, int on) {
+  if (!h) return SB_EINVAL;
+  h->timing = on != 0;
+  h->spans.clear();
+  h->ev_used = 0;
+  return SB_OK;
+}
+
+int sb_collect_timing(SbHandle h, double* ms_sum, int64_t* count) {
+  if (!h || !ms_sum || !count) return SB_EINVAL;
+  cudaSetDevice(h->cfg.device);
+  if (!cuda_ok(h, cudaDeviceSynchronize(), "sb_collect_timing sync")) return SB_ECUDA;
+  for (int k = 0; k < SB_K_COUNT; ++k) {
+    ms_sum[k] = 0.0;
+    count[k] = 0;
+  }
+  for (auto& s : h->spans) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, s.a, s.b) == cudaSuccess) {
+      ms_sum[s.kind] += ms;
+      count[s.kind]++;
+    }
+  }
+  h->spans.clear();
+  h->ev_used = 0;
+  return SB_OK;
 }
 
 int sb_get_obs(SbHandle h, SbObsPtrs* out) {

@@ -21,8 +21,9 @@ _LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libsmartsb
 EXPORTS = [
     "sb_abi_version", "sb_create", "sb_destroy", "sb_upload_map", "sb_upload_lidar_rays", "sb_reset",
     "sb_set_social", "sb_step", "sb_observe", "sb_step_host", "sb_copy_obs_to_host", "sb_get_obs",
-    "sb_get_state", "sb_launch_count", "sb_last_error",
+    "sb_get_state", "sb_launch_count", "sb_last_error", "sb_set_timing", "sb_collect_timing",
 ]
+KERNEL_KINDS = ["k_set_social", "k_control", "k_observe", "k_lidar", "k_raster"]
 
 
 class SmartsB200Error(RuntimeError):
@@ -59,6 +60,10 @@ def load_library(path: Optional[str] = None):
     L.sb_launch_count.restype = C.c_int64
     L.sb_last_error.argtypes = [H]
     L.sb_last_error.restype = C.c_char_p
+    L.sb_set_timing.argtypes = [H, C.c_int]
+    L.sb_set_timing.restype = C.c_int
+    L.sb_collect_timing.argtypes = [H, C.POINTER(C.c_double), C.POINTER(C.c_int64)]
+    L.sb_collect_timing.restype = C.c_int
     for f in ("sb_create", "sb_upload_map", "sb_upload_lidar_rays", "sb_reset", "sb_set_social", "sb_step",
               "sb_observe", "sb_step_host", "sb_copy_obs_to_host", "sb_get_obs", "sb_get_state"):
         getattr(L, f).restype = C.c_int
@@ -136,6 +141,16 @@ class Engine:
     @property
     def launch_count(self) -> int:
         return int(self._lib.sb_launch_count(self._h))
+
+    def set_timing(self, on: bool):
+        self._check(self._lib.sb_set_timing(self._h, int(on)), "sb_set_timing")
+
+    def collect_timing(self) -> Dict[str, tuple]:
+        """{kernel: (total ms, launches)} since the last collect (synchronises)."""
+        ms = (C.c_double * len(KERNEL_KINDS))()
+        cnt = (C.c_int64 * len(KERNEL_KINDS))()
+        self._check(self._lib.sb_collect_timing(self._h, ms, cnt), "sb_collect_timing")
+        return {k: (ms[i], int(cnt[i])) for i, k in enumerate(KERNEL_KINDS)}
 
     def _stream_ptr(self):
         return C.c_void_p(self._torch.cuda.current_stream(self.device).cuda_stream)

@@ -22,10 +22,10 @@ _MAPS = {}
 
 
 def load_map(name: str) -> RoadMapData:
-    """Flattened maps committed under tests/golden/maps (written by gen_golden.py from the
+    """Flattened maps committed under maps/ (written by tests/golden/gen_golden.py from the
     reference's own net.xml files; /root/reference is never read at test time)."""
     if name not in _MAPS:
-        _MAPS[name] = RoadMapData.load(os.path.join(GOLDEN, "maps", name + ".npz"))
+        _MAPS[name] = RoadMapData.load(os.path.join(ROOT, "maps", name + ".npz"))
     return _MAPS[name]
 
 

@@ -93,7 +93,7 @@ def sample_poses(mine: RoadMapData, rng, n):
 def gen_map_queries(name, rel, rng, n=60):
     rm, net = ref_shims.reference_road_map(REF + rel)
     mine = RoadMapData(net)
-    mine.save(os.path.join(HERE, "maps", name + ".npz"))
+    mine.save(os.path.join(ROOT, "maps", name + ".npz"))
     if name == "minicity":
         return None, mine
     routes = []
@@ -279,7 +279,7 @@ def gen_neighbors(rng):
 
 
 def main():
-    os.makedirs(os.path.join(HERE, "maps"), exist_ok=True)
+    os.makedirs(os.path.join(ROOT, "maps"), exist_ok=True)
     rng = np.random.default_rng(20241104)
     keep = {}
     for name, rel in MAPS.items():
