@@ -56,6 +56,7 @@ extern "C" {
 
 #define SB_STATUS_PATH_OVERFLOW 1u
 #define SB_STATUS_NO_WAYPOINTS 2u
+#define SB_STATUS_LIDAR_OVERFLOW 4u  /* more candidate boxes / edges near one agent than the kernel stages */
 
 typedef struct SbHandle_ *SbHandle;
 

@@ -462,7 +462,7 @@ inline void to_pixel(const Cam& cam, double x, double y, int64_t* U, int64_t* Vv
   double u = xr / cam.res + cam.halfw;
   double v = cam.halfh - yr / cam.res;
   double su = rint(u * 256.0), sv = rint(v * 256.0);
-  const double lim = 1073741824.0;
+  const double lim = 16777216.0;  // 2^24 units = 65536 px
   su = su > lim ? lim : (su < -lim ? -lim : su);
   sv = sv > lim ? lim : (sv < -lim ? -lim : sv);
   *U = (int64_t)su;

@@ -16,6 +16,7 @@ struct SbHandle_ {
   DObs ob;
   bool have_map = false, have_rays = false;
   double* d_rays = nullptr;
+  float ray_reach = 0.f;
   std::vector<void*> allocs;
   void* d_actions = nullptr;  // staging for sb_step_host
   size_t actions_cap = 0;
@@ -250,8 +251,9 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
   if (!cuda_ok(h, cudaMalloc(&da, h->actions_cap), "cudaMalloc(actions)")) return SB_ENOMEM;
   h->allocs.push_back(da);
   h->d_actions = da;
-  size_t b0 = c.ogm_enable ? (size_t)c.ogm_width * c.ogm_height / 8 : 0;
-  size_t b1 = c.dagm_enable ? (size_t)c.dagm_width * c.dagm_height / 8 : 0;
+  auto rows256 = [](int hh) { return (size_t)(hh < SB_RASTER_THREADS ? hh : SB_RASTER_THREADS); };
+  size_t b0 = c.ogm_enable ? (size_t)c.ogm_width * rows256(c.ogm_height) / 8 : 0;
+  size_t b1 = c.dagm_enable ? (size_t)c.dagm_width * rows256(c.dagm_height) / 8 : 0;
   h->raster_smem = b0 > b1 ? b0 : b1;
   if (h->raster_smem > 200 * 1024) return fail(h, SB_EINVAL, "grid too large for the shared-memory bit image");
   if (h->raster_smem > 24 * 1024) {
@@ -339,6 +341,10 @@ int sb_upload_lidar_rays(SbHandle h, const double* base_rays, int32_t n_rays) {
   const double* d = nullptr;
   if (!dev_upload(h, &d, base_rays, (size_t)n_rays * 3)) return SB_ECUDA;
   h->d_rays = const_cast<double*>(d);
+  double reach = 0.0;
+  for (int i = 0; i < n_rays; ++i)
+    reach = fmax(reach, sqrt(base_rays[i * 3] * base_rays[i * 3] + base_rays[i * 3 + 1] * base_rays[i * 3 + 1]));
+  h->ray_reach = (float)(reach * 1.0001 + 0.01);
   h->have_rays = true;
   return SB_OK;
 }
@@ -432,7 +438,7 @@ int sb_observe(SbHandle h, void* stream) {
   }
   if (c.lidar_enable) {
     LaunchScope ls(h, SB_K_LIDAR, st);
-    k_lidar<<<na, SB_LIDAR_THREADS, 0, st>>>(c, h->dmap, h->st, h->ob, h->d_rays);
+    k_lidar<<<na, SB_LIDAR_THREADS, 0, st>>>(c, h->dmap, h->st, h->ob, h->d_rays, h->ray_reach);
   }
   if (c.ogm_enable || c.dagm_enable) {
     LaunchScope ls(h, SB_K_RASTER, st);
