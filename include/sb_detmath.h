@@ -13,7 +13,7 @@
  *
  * This header is shared by the CUDA kernels (smarts_b200/csrc) and by the CPU oracle
  * (oracle/); it contains only libm-level primitives, none of the reference's algorithms.
- * Accuracy (checked in tests/test_detmath.py against numpy): <= 2 ulp for sin/cos on
+ * Accuracy (checked in tests/test_oracle_golden.py against numpy): <= 2 ulp for sin/cos on
  * |x| <= 1e5 and for atan2.
  */
 #ifndef SB_DETMATH_H
