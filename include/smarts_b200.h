@@ -53,6 +53,7 @@ extern "C" {
 #define SB_MAX_PATHS 16
 #define SB_MAX_LOOKAHEAD 64
 #define SB_MAX_TRAJ 32
+#define SB_MAX_POLY_VERTS 8 /* drivable-area polygons: convex, counter-clockwise, 3..8 vertices */
 
 #define SB_STATUS_PATH_OVERFLOW 1u
 #define SB_STATUS_NO_WAYPOINTS 2u
@@ -121,7 +122,7 @@ typedef struct SbMap {
   const int32_t *lp_next;                              /* [n_lp_next] */
   /* lane centre polylines */
   const double *shape_x, *shape_y;                     /* [n_shape_pts] */
-  /* drivable-area convex polygons (3 or 4 vertices each) and road boundary segments */
+  /* drivable-area convex CCW polygons (3..SB_MAX_POLY_VERTS vertices each) and road boundary segments */
   const int32_t *poly_start;                           /* [n_polys+1] CSR into poly_x/y */
   const double *poly_x, *poly_y;                       /* [n_poly_verts] */
   const double *road_edges;                            /* [n_edges,4] ax,ay,bx,by */

@@ -31,6 +31,7 @@ struct SbHandle_ {
   int cuda_err = 0;
   std::string err;
   size_t raster_smem = 0;
+  int raster_bits_off = 0;
 };
 
 namespace {
@@ -251,12 +252,22 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
   if (!cuda_ok(h, cudaMalloc(&da, h->actions_cap), "cudaMalloc(actions)")) return SB_ENOMEM;
   h->allocs.push_back(da);
   h->d_actions = da;
-  auto rows256 = [](int hh) { return (size_t)(hh < SB_RASTER_THREADS ? hh : SB_RASTER_THREADS); };
-  size_t b0 = c.ogm_enable ? (size_t)c.ogm_width * rows256(c.ogm_height) / 8 : 0;
-  size_t b1 = c.dagm_enable ? (size_t)c.dagm_width * rows256(c.dagm_height) / 8 : 0;
-  h->raster_smem = b0 > b1 ? b0 : b1;
-  if (h->raster_smem > 200 * 1024) return fail(h, SB_EINVAL, "grid too large for the shared-memory bit image");
-  if (h->raster_smem > 24 * 1024) {
+  {  // k_raster shared memory: table | staging area, bit images aliased onto it when no grid is wider than 256
+    auto rows256 = [](int hh) { return (size_t)(hh < SB_RASTER_THREADS ? hh : SB_RASTER_THREADS); };
+    size_t b0 = c.ogm_enable ? ((size_t)c.ogm_width / 32 + 1) * 4 * rows256(c.ogm_height) : 0;
+    size_t b1 = c.dagm_enable ? ((size_t)c.dagm_width / 32 + 1) * 4 * rows256(c.dagm_height) : 0;
+    int wmax = 0;
+    if (c.ogm_enable) wmax = c.ogm_width;
+    if (c.dagm_enable && c.dagm_width > wmax) wmax = c.dagm_width;
+    size_t stage = (sizeof(RasterStage) + 15) / 16 * 16;
+    if (wmax <= 256) {
+      h->raster_bits_off = SB_RASTER_LUT_BYTES;
+      h->raster_smem = SB_RASTER_LUT_BYTES + (stage > b0 + b1 ? stage : b0 + b1);
+    } else {
+      h->raster_bits_off = (int)(SB_RASTER_LUT_BYTES + stage);
+      h->raster_smem = SB_RASTER_LUT_BYTES + stage + b0 + b1;
+    }
+    if (h->raster_smem > 200 * 1024) return fail(h, SB_EINVAL, "grid too large for the shared-memory bit image");
     if (!cuda_ok(h, cudaFuncSetAttribute(k_raster, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->raster_smem),
                  "cudaFuncSetAttribute"))
       return SB_ECUDA;
@@ -290,7 +301,7 @@ int sb_upload_map(SbHandle h, const SbMap* mp) {
   std::vector<float> bbox((size_t)mp->n_polys * 4);
   for (int p = 0; p < mp->n_polys; ++p) {
     int s = mp->poly_start[p], n = mp->poly_start[p + 1] - s;
-    if (n > 4) return fail(h, SB_EINVAL, "drivable-area polygons must have <= 4 vertices");
+    if (n > SB_MAX_POLY_VERTS) return fail(h, SB_EINVAL, "drivable-area polygons must have <= SB_MAX_POLY_VERTS vertices");
     double x0 = 1e300, y0 = 1e300, x1 = -1e300, y1 = -1e300;
     for (int k = 0; k < n; ++k) {
       x0 = fmin(x0, mp->poly_x[s + k]); x1 = fmax(x1, mp->poly_x[s + k]);
@@ -442,7 +453,7 @@ int sb_observe(SbHandle h, void* stream) {
   }
   if (c.ogm_enable || c.dagm_enable) {
     LaunchScope ls(h, SB_K_RASTER, st);
-    k_raster<<<na, SB_RASTER_THREADS, h->raster_smem, st>>>(c, h->dmap, h->st, h->ob);
+    k_raster<<<na, SB_RASTER_THREADS, h->raster_smem, st>>>(c, h->dmap, h->st, h->ob, h->raster_bits_off);
   }
   return cuda_ok(h, cudaGetLastError(), "k_observe") ? SB_OK : SB_ECUDA;
 }

@@ -1,41 +1,65 @@
-// sb_raster.cuh -- OGM + DrivableAreaGridMap rasterisation (block per agent).
+// sb_raster.cuh -- OGM + DrivableAreaGridMap rasterisation (block per agent, thread per row).
 //   OGMSensor / DrivableAreaGridMapSensor      smarts/core/sensors.py:675-758
 //   camera (orthographic, ego-centred, ego-heading-aligned, rows flipped)
 //                                               smarts/core/renderer.py:325-336, :383-386
 //
-// Contract (DESIGN.md "Grid maps"; identical in oracle/oracle.cpp): polygon vertices go to pixel
-// space in binary64, are snapped to 1/256 px (round-half-even) and clamped to +-2^24; a pixel is
-// set iff its centre (256c+128, 256r+128) satisfies every edge function of the convex polygon
-// (inclusive), in exact integer arithmetic.
+// Contract (DESIGN.md "Grid maps"; the oracle evaluates it pixel by pixel): polygon vertices go
+// to pixel space in binary64, are snapped to 1/256 px (round-half-even) and clamped to +-2^24; a
+// pixel (c, r) is set iff its centre (256c+128, 256r+128) satisfies every edge function
+//     F_e(c, r) = A_e (256c+128) + D_e (256r) + B0_e >= 0          (all integers, |F| < 2^52)
+// of some polygon.  The result is a set of integers, so HOW a row's covered span is found is
+// free; this file finds it without divisions in the per-row loop.  Both grids of an agent are
+// produced by one pass:
 //
-// Implementation: one thread owns one image row.  Polygons are staged in shared memory as
-// per-edge linear coefficients; for each polygon whose row range contains its row the thread
-// solves the <= 4 edge inequalities for the covered column span and ORs the span into the row's
-// bit words held in registers -- no atomics, no cross-thread dependence.  All quantities are
-// integers below 2^52 carried in binary64, where +, -, * are exact and a correctly-rounded
-// division followed by floor/ceil gives the exact integer quotient (|num| < 2^52: the rounding
-// error of num/den is below 1/(2 den), less than the distance of a non-integer quotient to the
-// nearest integer).  The bit image then goes through shared memory so that the 0/255 byte image
-// is written with fully coalesced 16-byte streaming stores.
+//   cull    (thread = source)  vehicles (OGM) and map polygons (DAGM) that can touch the film;
+//   vertex  (thread = polygon vertex)  world -> snapped pixel coordinates, int32 in shared memory;
+//   edge    (thread = polygon edge)  A, D, B0 as integers, plus a 32.32 fixed-point line
+//           x*(r) = e0 + ek r for the real column where F_e changes sign along a row;
+//   rows    (thread = image row)  k = round(x*(r)) by integer multiply-adds, then ONE exact
+//           evaluation of F_e(k, r) in 64-bit integers decides between k and k+-1 (the estimate
+//           is within 2^-20 of the true crossing, so the answer is always one of the two); the
+//           span [max lower bounds, min upper bounds] is OR-ed into the row's bit words held in
+//           registers -- no atomics, no cross-thread dependence;
+//   store   bit image -> 0/255 bytes through a 256-entry byte-expansion table in shared memory,
+//           32 pixels per thread per 256-bit store (STG.256), rows fully coalesced.
+//
+// An edge that is horizontal in pixel space (A == 0) is a per-row yes/no.  A polygon whose
+// crossing line leaves the +-2^29 px range inside the image (nearly horizontal edge) takes an
+// exact binary64-division path instead (flag SLOW; the branch is warp-uniform).
 #pragma once
 
 #include "sb_device.cuh"
 
 #define SB_RASTER_THREADS 256
-#define SB_RASTER_MAX_POLYS 256
-#define SB_RASTER_CLAMP 16777216.0  // 2^24 units = 65536 px
+#define SB_RASTER_ROUND 64  // polygons staged per round (2 vertex / edge slots per thread)
+#define SB_RASTER_LIST (SB_RASTER_THREADS + SB_RASTER_ROUND)
+#define SB_RASTER_CLAMP 16777216.0        // 2^24 units = 65536 px
+#define SB_RASTER_FAST_LIMIT 536870912.0  // 2^29
 
-struct REdge {
-  double A, B0, B1;  // A*px + (B0 + B1*row) >= 0
+struct __align__(16) REdgeI {
+  int32_t A, D;      // F = A*(256c+128) + D*(256r) + B0
+  long long B0;
+  long long e0, ek;  // 32.32 fixed point: (x* + 0.5) at r = 0, and d x*/d r
 };
-struct RPoly {
-  int32_t r0, r1;  // first / last row whose centre can be covered (r1 < r0: nothing)
-  int32_t pad0, pad1;
-  REdge e[4];
+struct __align__(8) RPolyI {
+  int16_t r0, r1;  // rows whose centre can be covered (r1 < r0: nothing)
+  uint8_t n;       // edges
+  uint8_t img;     // 0 = OGM, 1 = DAGM
+  uint8_t slow;    // exact-division path
+  uint8_t pad;
 };
 
 struct Cam {
   double px, py, c, s, res, halfw, halfh;
+};
+
+// staging area; the bit images alias it once the last round's rows are done
+struct RasterStage {
+  REdgeI edges[SB_RASTER_ROUND][SB_MAX_POLY_VERTS];
+  int32_t U[SB_RASTER_ROUND][SB_MAX_POLY_VERTS], V[SB_RASTER_ROUND][SB_MAX_POLY_VERTS];
+  RPolyI hdr[SB_RASTER_ROUND];
+  int32_t list[SB_RASTER_LIST];
+  int32_t n_list;
 };
 
 __device__ __forceinline__ void d_to_pixel(const Cam& cam, double x, double y, double* U, double* V) {
@@ -50,83 +74,178 @@ __device__ __forceinline__ void d_to_pixel(const Cam& cam, double x, double y, d
   *V = sv > lim ? lim : (sv < -lim ? -lim : sv);
 }
 
-// snapped vertices -> row range + edge coefficients (all values exact integers in binary64)
-__device__ __forceinline__ void d_make_rpoly(const double* U, const double* V, int n, int W, int H, RPoly* out) {
-  double area2 = 0.0;
-  double umin = U[0], umax = U[0], vmin = V[0], vmax = V[0];
-  for (int i = 0; i < n; ++i) {
-    int j = (i + 1 == n) ? 0 : i + 1;
-    area2 += U[i] * V[j] - U[j] * V[i];
-    umin = fmin(umin, U[i]);
-    umax = fmax(umax, U[i]);
-    vmin = fmin(vmin, V[i]);
-    vmax = fmax(vmax, V[i]);
-  }
-  RPoly P;
-  P.pad0 = P.pad1 = 0;
-  double r0 = ceil((vmin - 128.0) / 256.0), r1 = floor((vmax - 128.0) / 256.0);
-  double c0 = ceil((umin - 128.0) / 256.0), c1 = floor((umax - 128.0) / 256.0);
-  if (r0 < 0.0) r0 = 0.0;
-  if (r1 > (double)(H - 1)) r1 = (double)(H - 1);
-  if (area2 == 0.0 || r0 > r1 || c1 < 0.0 || c0 > (double)(W - 1)) {
-    P.r0 = 1;
-    P.r1 = 0;
-  } else {
-    P.r0 = (int)r0;
-    P.r1 = (int)r1;
-  }
-  const double sg = area2 > 0.0 ? 1.0 : -1.0;
-  for (int i = 0; i < 4; ++i) {
-    if (i < n) {
-      int j = (i + 1 == n) ? 0 : i + 1;
-      double dxe = U[j] - U[i], dye = V[j] - V[i];
-      P.e[i].A = -(sg * dye);
-      P.e[i].B1 = sg * (dxe * 256.0);
-      P.e[i].B0 = sg * (dxe * (128.0 - V[i]) + dye * U[i]);
-    } else {
-      P.e[i].A = 0.0;
-      P.e[i].B0 = 0.0;
-      P.e[i].B1 = 0.0;
-    }
-  }
-  *out = P;
-}
+struct RasterJob {
+  Cam cam[2];          // [0] OGM, [1] DAGM
+  int W[2], H[2];
+  bool on[2];
+  int n_veh;           // sources [0, n_veh) are the env's vehicles, [n_veh, n_veh + n_polys) map polygons
+  int n_src;
+};
 
-// OR the staged polygons' spans on row `r` (columns [cb, cb+256)) into the thread's row bits
-__device__ __forceinline__ void d_row_spans(const RPoly* polys, int np, int r, int cb, int W, unsigned long long* w4) {
-  const double rr = (double)r;
-  const double wlast = (double)(W - 1);
-  for (int p = 0; p < np; ++p) {
-    const RPoly& P = polys[p];
-    if (r < P.r0 || r > P.r1) continue;
-    double c0 = 0.0, c1 = wlast;
-    bool empty = false;
+// vertex phase: slot = (list entry, vertex); world -> snapped pixel coordinates
+__device__ __forceinline__ void d_vertex_phase(const DCfg& c, const DMap& m, const DState& s, int e,
+                                               const RasterJob& job, RasterStage* st, int first, int count) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const double A = P.e[i].A;
-      const double bb = P.e[i].B0 + P.e[i].B1 * rr;
-      if (A > 0.0) {
-        double lo = ceil((-bb - 128.0 * A) / (256.0 * A));
-        c0 = fmax(c0, lo);
-      } else if (A < 0.0) {
-        double hi = floor((bb + 128.0 * A) / (-256.0 * A));
-        c1 = fmin(c1, hi);
-      } else if (bb < 0.0) {
-        empty = true;
+  for (int it = 0; it < (SB_RASTER_ROUND * SB_MAX_POLY_VERTS) / SB_RASTER_THREADS; ++it) {
+    const int slot = threadIdx.x + it * SB_RASTER_THREADS;
+    const int li = slot / SB_MAX_POLY_VERTS, k = slot % SB_MAX_POLY_VERTS;
+    if (li >= count) continue;
+    const int src = st->list[first + li];
+    double x, y;
+    int n, img;
+    if (src < job.n_veh) {
+      img = 0;
+      n = 4;
+      if (k < 4) {
+        const int vj = e * c.V + src;
+        const double cc = s.cos_h[vj], ss = s.sin_h[vj];
+        const double hw = 0.5 * s.width[vj], hl = 0.5 * s.length[vj];
+        const double sa = (k == 1 || k == 2) ? hw : -hw, sb = (k >= 2) ? hl : -hl;
+        x = s.pos_x[vj] + (sa * cc - sb * ss);
+        y = s.pos_y[vj] + (sa * ss + sb * cc);
+      }
+    } else {
+      img = 1;
+      const int p = src - job.n_veh;
+      const int p0 = m.poly_start[p];
+      n = m.poly_start[p + 1] - p0;
+      if (k < n) {
+        x = m.poly_x[p0 + k];
+        y = m.poly_y[p0 + k];
       }
     }
-    if (empty || c0 > c1) continue;
-    int lo = (int)c0 - cb, hi = (int)c1 - cb;
-    if (lo < 0) lo = 0;
-    if (hi > 255) hi = 255;
-    if (lo > hi) continue;
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      int wl = lo - 64 * k, wh = hi - 64 * k;
-      if (wl < 0) wl = 0;
-      if (wh > 63) wh = 63;
-      if (wl <= wh) w4[k] |= (~0ull << wl) & (~0ull >> (63 - wh));
+    if (k < n) {
+      double U, V;
+      d_to_pixel(job.cam[img], x, y, &U, &V);
+      st->U[li][k] = (int32_t)U;
+      st->V[li][k] = (int32_t)V;
     }
+    if (k == 0) {
+      RPolyI P;
+      P.r0 = 1;
+      P.r1 = 0;
+      P.n = (uint8_t)n;
+      P.img = (uint8_t)img;
+      P.slow = 0;
+      P.pad = 0;
+      st->hdr[li] = P;
+    }
+  }
+}
+
+// edge phase: slot = (list entry, edge k -> k+1); integer edge function + fixed-point crossing line
+__device__ __forceinline__ void d_edge_phase(const RasterJob& job, RasterStage* st, int count) {
+#pragma unroll
+  for (int it = 0; it < (SB_RASTER_ROUND * SB_MAX_POLY_VERTS) / SB_RASTER_THREADS; ++it) {
+    const int slot = threadIdx.x + it * SB_RASTER_THREADS;
+    const int li = slot / SB_MAX_POLY_VERTS, k = slot % SB_MAX_POLY_VERTS;
+    if (li >= count) continue;
+    const int n = st->hdr[li].n, img = st->hdr[li].img;
+    if (k >= n) continue;
+    const int32_t* U = st->U[li];
+    const int32_t* V = st->V[li];
+    long long area2 = 0;
+    int umin = U[0], umax = U[0], vmin = V[0], vmax = V[0];
+    for (int i = 0; i < n; ++i) {
+      const int j = (i + 1 == n) ? 0 : i + 1;
+      area2 += (long long)U[i] * V[j] - (long long)U[j] * V[i];
+      umin = min(umin, U[i]);
+      umax = max(umax, U[i]);
+      vmin = min(vmin, V[i]);
+      vmax = max(vmax, V[i]);
+    }
+    const int W = job.W[img], H = job.H[img];
+    int r0 = (vmin - 128 + 255) >> 8, r1 = (vmax - 128) >> 8;  // rows with vmin <= 256r+128 <= vmax
+    const int c0 = (umin - 128 + 255) >> 8, c1 = (umax - 128) >> 8;
+    r0 = max(r0, 0);
+    r1 = min(r1, H - 1);
+    const bool valid = area2 != 0 && r0 <= r1 && c1 >= 0 && c0 <= W - 1;
+    if (k == 0 && valid) {
+      st->hdr[li].r0 = (int16_t)r0;
+      st->hdr[li].r1 = (int16_t)r1;
+    }
+    if (!valid) continue;
+    const int sg = area2 > 0 ? 1 : -1;
+    const int j = (k + 1 == n) ? 0 : k + 1;
+    const int dxe = U[j] - U[k], dye = V[j] - V[k];
+    REdgeI q;
+    q.A = -sg * dye;
+    q.D = sg * dxe;
+    q.B0 = (long long)sg * ((long long)dxe * (128 - V[k]) + (long long)dye * U[k]);
+    q.e0 = 0;
+    q.ek = 0;
+    if (q.A != 0) {
+      const double A = (double)q.A;
+      const double e0 = -((double)(q.B0 + 128ll * q.A)) / (256.0 * A), ek = -(double)q.D / A;
+      if (fabs(e0) + fabs(ek) * (double)H < SB_RASTER_FAST_LIMIT) {
+        q.e0 = __double2ll_rn((e0 + 0.5) * 4294967296.0);
+        q.ek = __double2ll_rn(ek * 4294967296.0);
+      } else {
+        st->hdr[li].slow = 1;
+      }
+    }
+    st->edges[li][k] = q;
+  }
+}
+
+// low `t` bits set, t clamped to [0, 32]
+__device__ __forceinline__ uint32_t d_ones_below(int t) {
+  return __funnelshift_lc(0xffffffffu, 0u, (uint32_t)max(t, 0));
+}
+
+// Column span [c0, c1] of staged polygon `li` on row r (c0 > c1: empty).
+__device__ __forceinline__ void d_poly_span(const RasterStage* st, int li, const RPolyI P, int r, int W, int* c0o,
+                                            int* c1o) {
+  const int r256 = r << 8;
+  const REdgeI* e = st->edges[li];
+  int c0 = 0, c1 = W - 1;
+  if (!P.slow) {
+    for (int i = 0; i < P.n; ++i) {
+      const REdgeI q = e[i];
+      const long long base = (long long)q.D * (long long)r256 + q.B0;
+      if (q.A == 0) {  // horizontal edge: the row is in or out (same branch for every lane)
+        if (base < 0) c1 = -1;
+        continue;
+      }
+      int k = (int)((q.e0 + q.ek * (long long)r) >> 32);
+      k = min(max(k, -2), 1025);
+      const long long F = (long long)q.A * (long long)(k * 256 + 128) + base;
+      if (q.A > 0) c0 = max(c0, k + (F < 0 ? 1 : 0));  // smallest c with F >= 0
+      else c1 = min(c1, k - (F < 0 ? 1 : 0));          // largest c with F >= 0
+    }
+  } else {  // exact binary64 division (|numerator| < 2^52: floor/ceil of the rounded quotient is exact)
+    double d0 = 0.0, d1 = (double)(W - 1);
+    for (int i = 0; i < P.n; ++i) {
+      const REdgeI q = e[i];
+      const double A = (double)q.A, bb = (double)q.B0 + (double)q.D * (double)r256;
+      if (A > 0.0) d0 = fmax(d0, ceil((-bb - 128.0 * A) / (256.0 * A)));
+      else if (A < 0.0) d1 = fmin(d1, floor((bb + 128.0 * A) / (-256.0 * A)));
+      else if (bb < 0.0) d1 = -1.0;
+    }
+    c0 = (int)d0;
+    c1 = (int)d1;
+  }
+  *c0o = c0;
+  *c1o = c1;
+}
+
+__device__ __forceinline__ void d_or_span(uint32_t (&w)[8], int lo, int hi1) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j) w[j] |= d_ones_below(hi1 - 32 * j) & ~d_ones_below(lo - 32 * j);
+}
+
+// OR the staged polygons' spans on row `r` (columns [cb, cb+256)) into the row's bit words.
+__device__ __forceinline__ void d_row_spans(const RasterJob& job, const RasterStage* st, int np, int r, int cb,
+                                            uint32_t (&w0)[8], uint32_t (&w1)[8]) {
+  for (int p = 0; p < np; ++p) {
+    const RPolyI P = st->hdr[p];
+    if (r < P.r0 || r > P.r1) continue;
+    int c0, c1;
+    d_poly_span(st, p, P, r, job.W[P.img], &c0, &c1);
+    const int lo = max(c0 - cb, 0), hi1 = min(c1 - cb, 255) + 1;
+    if (lo >= hi1) continue;
+    if (P.img == 0) d_or_span(w0, lo, hi1);  // warp-uniform
+    else d_or_span(w1, lo, hi1);
   }
 }
 
@@ -134,107 +253,124 @@ __device__ __forceinline__ uint32_t d_expand4(uint32_t b) {  // low 4 bits -> 4 
   return ((b * 0x00204081u) & 0x01010101u) * 255u;
 }
 
-// rows x W bit image (wpr words per row) -> byte image, 16 pixels per thread per step
-__device__ __forceinline__ void d_store_rows(const uint32_t* bits, uint8_t* dst, int n_pixels) {
-  const int n16 = n_pixels >> 4;
-  uint4* out = reinterpret_cast<uint4*>(dst);
-  for (int i = threadIdx.x; i < n16; i += SB_RASTER_THREADS) {
-    uint32_t word = bits[i >> 1];
-    uint32_t hw = (i & 1) ? (word >> 16) : word;
-    uint4 v;
-    v.x = d_expand4(hw & 15u);
-    v.y = d_expand4((hw >> 4) & 15u);
-    v.z = d_expand4((hw >> 8) & 15u);
-    v.w = d_expand4((hw >> 12) & 15u);
-    __stcs(out + i, v);
+// rows x W bit image (stride words per row in shared memory) -> byte image; one 32-pixel word
+// per thread per step, written with a single 256-bit store.
+__device__ __forceinline__ void d_store_rows(const uint32_t* bits, const uint2* lut, uint8_t* dst, int rows, int wpr,
+                                             int stride) {
+  const int n_words = rows * wpr;
+  const bool pow2 = (wpr & (wpr - 1)) == 0;
+  const int sh = 31 - __clz(wpr);
+  for (int i = threadIdx.x; i < n_words; i += SB_RASTER_THREADS) {
+    const int row = pow2 ? (i >> sh) : (i / wpr);
+    const int j = i - row * wpr;
+    const uint32_t word = bits[row * stride + j];
+    const uint2 a = lut[word & 0xffu], b = lut[(word >> 8) & 0xffu], c = lut[(word >> 16) & 0xffu], d = lut[word >> 24];
+    uint8_t* p = dst + (size_t)i * 32;
+    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(a.x), "r"(a.y), "r"(b.x),
+                 "r"(b.y), "r"(c.x), "r"(c.y), "r"(d.x), "r"(d.y)
+                 : "memory");
   }
 }
 
-// One grid (OGM when `vehicles`, DAGM otherwise) of agent `ai`.
-template <bool VEHICLES>
-__device__ void d_raster_grid(const DCfg& c, const DMap& m, const DState& s, int e, const Cam& cam, int W, int H,
-                              uint8_t* dst, uint32_t* bits, RPoly* polys, int* n_staged) {
-  const int wpr = W >> 5;
-  const int n_src = VEHICLES ? c.V : m.n_polys;
-  const float rad = 0.5f * (float)cam.res * sqrtf((float)W * (float)W + (float)H * (float)H) + 1.0f;
-  const float fx = (float)cam.px, fy = (float)cam.py;
-  for (int rg = 0; rg < H; rg += SB_RASTER_THREADS) {
-    const int r = rg + threadIdx.x;
-    const int rows = H - rg < SB_RASTER_THREADS ? H - rg : SB_RASTER_THREADS;
-    for (int cb = 0; cb < W; cb += 256) {
-      unsigned long long w4[4] = {0ull, 0ull, 0ull, 0ull};
-      for (int base = 0; base < n_src; base += SB_RASTER_MAX_POLYS) {
-        __syncthreads();  // previous round's readers are done
-        if (threadIdx.x == 0) *n_staged = 0;
-        __syncthreads();
-        const int p = base + threadIdx.x;
-        if (p < n_src) {
-          double U[4], V[4];
-          int n = 0;
-          if (VEHICLES) {
-            const int vj = e * c.V + p;
-            if (s.alive[vj]) {
-              const double cc = s.cos_h[vj], ss = s.sin_h[vj];
-              const double hw = 0.5 * s.width[vj], hl = 0.5 * s.length[vj];
-              const double sa[4] = {-hw, hw, hw, -hw}, sbv[4] = {-hl, -hl, hl, hl};
-              n = 4;
-#pragma unroll
-              for (int k = 0; k < 4; ++k) {
-                double x = s.pos_x[vj] + (sa[k] * cc - sbv[k] * ss);
-                double y = s.pos_y[vj] + (sa[k] * ss + sbv[k] * cc);
-                d_to_pixel(cam, x, y, &U[k], &V[k]);
-              }
-            }
-          } else {
-            const float* bb = m.poly_bbox + (size_t)p * 4;
-            if (!(bb[0] > fx + rad || bb[2] < fx - rad || bb[1] > fy + rad || bb[3] < fy - rad)) {
-              const int st = m.poly_start[p];
-              n = m.poly_start[p + 1] - st;
-              if (n < 3 || n > 4) n = 0;
-              for (int k = 0; k < n; ++k) d_to_pixel(cam, m.poly_x[st + k], m.poly_y[st + k], &U[k], &V[k]);
-            }
-          }
-          if (n) {
-            RPoly P;
-            d_make_rpoly(U, V, n, W, H, &P);
-            if (P.r0 <= P.r1) polys[atomicAdd(n_staged, 1)] = P;  // order is irrelevant (OR)
-          }
-        }
-        __syncthreads();
-        if (r < H) d_row_spans(polys, *n_staged, r, cb, W, w4);
-      }
-      if (r < H) {
-        uint32_t* row = bits + threadIdx.x * wpr + (cb >> 5);
-        const int nw = (W - cb) >= 256 ? 8 : ((W - cb) >> 5);
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          if (2 * k < nw) row[2 * k] = (uint32_t)w4[k];
-          if (2 * k + 1 < nw) row[2 * k + 1] = (uint32_t)(w4[k] >> 32);
-        }
-      }
-    }
-    __syncthreads();
-    d_store_rows(bits, dst + (size_t)rg * W, rows * W);
-    __syncthreads();
-  }
-}
+#define SB_RASTER_LUT_BYTES 2048
 
-// dynamic shared memory: bit image of one 256-row group, min(H,256) * W / 8 bytes
-__global__ void __launch_bounds__(SB_RASTER_THREADS) k_raster(DCfg c, DMap m, DState s, DObs o) {
-  extern __shared__ uint32_t bits[];
-  __shared__ RPoly polys[SB_RASTER_MAX_POLYS];
-  __shared__ int n_staged;
+// Dynamic shared memory: [byte-expansion table | staging area], and the two bit images at
+// `bits_off` -- on top of the staging area when no grid is wider than 256 (they are written only
+// after the last rows pass), behind it otherwise.  Sized by sb_raster_smem_bytes() in sb_api.cu.
+__global__ void __launch_bounds__(SB_RASTER_THREADS, 4) k_raster(DCfg c, DMap m, DState s, DObs o, int bits_off) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  uint2* lut = reinterpret_cast<uint2*>(smem);
+  RasterStage* st = reinterpret_cast<RasterStage*>(smem + SB_RASTER_LUT_BYTES);
   const int ai = blockIdx.x;
   const int e = ai / c.A, a = ai - e * c.A, vi = e * c.V + a;
   const double px = s.pos_x[vi], py = s.pos_y[vi], ch = s.cos_h[vi], sh = s.sin_h[vi];
-  if (c.ogm_enable) {  // sensors.py:719-758: vehicles only, ego included
-    Cam cam{px, py, ch, sh, c.ogm_res, 0.5 * c.ogm_w, 0.5 * c.ogm_h};
-    d_raster_grid<true>(c, m, s, e, cam, c.ogm_w, c.ogm_h, o.ogm + (size_t)ai * c.ogm_w * c.ogm_h, bits, polys,
-                        &n_staged);
-  }
-  if (c.dagm_enable) {  // sensors.py:675-716: road surface only
-    Cam cam{px, py, ch, sh, c.dagm_res, 0.5 * c.dagm_w, 0.5 * c.dagm_h};
-    d_raster_grid<false>(c, m, s, e, cam, c.dagm_w, c.dagm_h, o.dagm + (size_t)ai * c.dagm_w * c.dagm_h, bits,
-                         polys, &n_staged);
+  RasterJob job;
+  job.on[0] = c.ogm_enable != 0;   // sensors.py:719-758: vehicles only, ego included
+  job.on[1] = c.dagm_enable != 0;  // sensors.py:675-716: road surface only
+  job.W[0] = job.on[0] ? c.ogm_w : 0;
+  job.H[0] = job.on[0] ? c.ogm_h : 0;
+  job.W[1] = job.on[1] ? c.dagm_w : 0;
+  job.H[1] = job.on[1] ? c.dagm_h : 0;
+  job.cam[0] = Cam{px, py, ch, sh, c.ogm_res, 0.5 * c.ogm_w, 0.5 * c.ogm_h};
+  job.cam[1] = Cam{px, py, ch, sh, c.dagm_res, 0.5 * c.dagm_w, 0.5 * c.dagm_h};
+  job.n_veh = job.on[0] ? c.V : 0;
+  job.n_src = job.n_veh + (job.on[1] ? m.n_polys : 0);
+  const int Hmax = max(job.H[0], job.H[1]), Wmax = max(job.W[0], job.W[1]);
+  const int wpr0 = job.W[0] >> 5, wpr1 = job.W[1] >> 5;
+  const int rows0 = min(job.H[0], SB_RASTER_THREADS), rows1 = min(job.H[1], SB_RASTER_THREADS);
+  uint32_t* bits0 = reinterpret_cast<uint32_t*>(smem + bits_off);
+  uint32_t* bits1 = bits0 + rows0 * (wpr0 + 1);
+  // conservative world-space cull radii: the film's half diagonal + 1 m
+  const float rad0 = 0.5f * (float)c.ogm_res * sqrtf((float)job.W[0] * job.W[0] + (float)job.H[0] * job.H[0]) + 1.0f;
+  const float rad1 = 0.5f * (float)c.dagm_res * sqrtf((float)job.W[1] * job.W[1] + (float)job.H[1] * job.H[1]) + 1.0f;
+  const float fx = (float)px, fy = (float)py;
+  lut[threadIdx.x] = make_uint2(d_expand4(threadIdx.x & 15u), d_expand4(threadIdx.x >> 4));
+
+  for (int rg = 0; rg < Hmax; rg += SB_RASTER_THREADS) {
+    const int r = rg + threadIdx.x;
+    for (int cb = 0; cb < Wmax; cb += 256) {
+      uint32_t w0[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u}, w1[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+      if (threadIdx.x == 0) st->n_list = 0;
+      __syncthreads();
+      for (int base = 0; base < job.n_src; base += SB_RASTER_THREADS) {
+        const int p = base + threadIdx.x;
+        bool keep = false;
+        if (p < job.n_veh) {
+          const int vj = e * c.V + p;
+          if (s.alive[vj]) {
+            const float dx = (float)s.pos_x[vj] - fx, dy = (float)s.pos_y[vj] - fy;
+            const float fl = (float)s.length[vj], fw = (float)s.width[vj];
+            const float lim = rad0 + 0.5f * sqrtf(fl * fl + fw * fw) + 0.5f;
+            keep = dx * dx + dy * dy <= lim * lim;
+          }
+        } else if (p < job.n_src) {
+          const int q = p - job.n_veh;
+          const float4 bb = reinterpret_cast<const float4*>(m.poly_bbox)[q];
+          const int n = m.poly_start[q + 1] - m.poly_start[q];
+          keep = !(bb.x > fx + rad1 || bb.z < fx - rad1 || bb.y > fy + rad1 || bb.w < fy - rad1) && n >= 3 &&
+                 n <= SB_MAX_POLY_VERTS;
+        }
+        if (keep) st->list[atomicAdd(&st->n_list, 1)] = p;
+        __syncthreads();
+        // stage + rasterise in rounds; a remainder < ROUND waits for the next cull pass
+        const bool last = base + SB_RASTER_THREADS >= job.n_src;
+        int n_list = st->n_list;
+        while (n_list >= SB_RASTER_ROUND || (last && n_list > 0)) {
+          const int count = min(n_list, SB_RASTER_ROUND);
+          d_vertex_phase(c, m, s, e, job, st, n_list - count, count);
+          __syncthreads();
+          d_edge_phase(job, st, count);
+          __syncthreads();
+          d_row_spans(job, st, count, r, cb, w0, w1);
+          n_list -= count;
+          __syncthreads();
+        }
+        if (threadIdx.x == 0) st->n_list = n_list;
+        __syncthreads();
+      }
+      // every thread is past the last rows pass: the staging area may now be overwritten
+      if (r < job.H[0] && cb < job.W[0]) {
+        uint32_t* row = bits0 + threadIdx.x * (wpr0 + 1) + (cb >> 5);
+        const int nw = min(8, wpr0 - (cb >> 5));
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          if (k < nw) row[k] = w0[k];
+      }
+      if (r < job.H[1] && cb < job.W[1]) {
+        uint32_t* row = bits1 + threadIdx.x * (wpr1 + 1) + (cb >> 5);
+        const int nw = min(8, wpr1 - (cb >> 5));
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          if (k < nw) row[k] = w1[k];
+      }
+    }
+    __syncthreads();
+    if (rg < job.H[0])
+      d_store_rows(bits0, lut, o.ogm + (size_t)ai * job.W[0] * job.H[0] + (size_t)rg * job.W[0],
+                   min(job.H[0] - rg, SB_RASTER_THREADS), wpr0, wpr0 + 1);
+    if (rg < job.H[1])
+      d_store_rows(bits1, lut, o.dagm + (size_t)ai * job.W[1] * job.H[1] + (size_t)rg * job.W[1],
+                   min(job.H[1] - rg, SB_RASTER_THREADS), wpr1, wpr1 + 1);
+    __syncthreads();
   }
 }

@@ -389,6 +389,8 @@ class RoadMapData:
             for tri in _ear_clip(line):
                 polys.append(ccw(tri))
 
+        self.n_polys_raw = len(polys)
+        polys = simplify_polygons(polys, MAX_POLY_VERTS)
         vx, vy, start = [], [], [0]
         for p in polys:
             vx.extend(p[:, 0]); vy.extend(p[:, 1])
@@ -514,6 +516,284 @@ class RoadMapData:
                         wrap_heading(vec_to_radians(bx - ax, by - ay)))
             seen += ln
         raise ValueError("empty lane shape")
+
+
+MAX_POLY_VERTS = 8  # SB_MAX_POLY_VERTS of include/smarts_b200.h
+
+
+def _cross(o, a, b) -> float:
+    return (a[0] - o[0]) * (b[1] - o[1]) - (a[1] - o[1]) * (b[0] - o[0])
+
+
+def _clean_ring(pts: List[Tuple[float, float]], tol: float) -> List[Tuple[float, float]]:
+    """Drop repeated vertices (closer than 1e-6 m) and vertices within ``tol`` metres of the
+    line through their neighbours (when they lie between them) of a CCW ring."""
+    out = list(pts)
+    changed = True
+    while changed and len(out) >= 3:
+        changed = False
+        n = len(out)
+        for i in range(n):
+            a, b, c = out[i - 1], out[i], out[(i + 1) % n]
+            lab = math.hypot(b[0] - a[0], b[1] - a[1])
+            lbc = math.hypot(c[0] - b[0], c[1] - b[1])
+            lac = math.hypot(c[0] - a[0], c[1] - a[1])
+            if lab <= 1e-6 or lbc <= 1e-6:
+                out.pop(i)
+                changed = True
+                break
+            if n > 3 and abs(_cross(a, b, c)) <= tol * lac and \
+                    (b[0] - a[0]) * (c[0] - b[0]) + (b[1] - a[1]) * (c[1] - b[1]) > 0:
+                out.pop(i)
+                changed = True
+                break
+    return out
+
+
+def _is_convex(pts: Sequence[Tuple[float, float]], tol: float) -> bool:
+    """Strictly simple convex CCW ring: every turn is left (to within ``tol`` metres of
+    deviation) and the turning angles add up to one revolution."""
+    n = len(pts)
+    if n < 3:
+        return False
+    total = 0.0
+    for i in range(n):
+        a, b, c = pts[i - 1], pts[i], pts[(i + 1) % n]
+        lab = math.hypot(b[0] - a[0], b[1] - a[1])
+        lbc = math.hypot(c[0] - b[0], c[1] - b[1])
+        if lab <= 1e-6 or lbc <= 1e-6:
+            return False
+        cr = _cross(a, b, c)
+        if cr < -tol * max(lab, lbc):
+            return False
+        total += math.atan2(cr, (b[0] - a[0]) * (c[0] - b[0]) + (b[1] - a[1]) * (c[1] - b[1]))
+    return abs(total - TWO_PI) < 1e-3 and _ring_area(pts) > 0.0
+
+
+def simplify_polygons(polys: Sequence[np.ndarray], max_verts: int = MAX_POLY_VERTS,
+                      tol: float = 1e-6) -> List[np.ndarray]:
+    """Union-preserving reduction of a list of convex CCW polygons (setup time, host side).
+
+    The DrivableAreaGridMap shows the *union* of the road pieces (sensors.py:675-716 renders the
+    merged road mesh), so any polygon list with the same union is an equally valid restatement;
+    fewer, larger pieces make the rasteriser cheaper for both the CUDA kernel and the oracle
+    (both consume this list unchanged).  Two exact steps, repeated to a fixed point:
+
+    1. merge two polygons that share a full edge when the result is convex and has at most
+       ``max_verts`` vertices (Hertel-Mehlhorn style; adjacent lane strips of one edge, the
+       ear-clipped triangles of a junction shape);
+    2. drop a polygon whose vertices all lie inside (or on) one other convex polygon.
+    """
+    rings: List[Optional[List[Tuple[float, float]]]] = []
+    for p in polys:
+        r = _clean_ring([(float(x), float(y)) for x, y in np.asarray(p, np.float64)], tol)
+        if len(r) >= 3 and _is_convex(r, tol):
+            rings.append(r)
+        elif len(r) >= 3 and abs(_ring_area(r)) > 1e-9:
+            raise ValueError("simplify_polygons expects convex counter-clockwise polygons")
+        # else: zero-area input (repeated shape points) covers nothing
+    q = 1e-5
+
+    def key(pt):
+        return (round(pt[0] / q), round(pt[1] / q))
+
+    def try_merge_pass() -> bool:
+        edge_owner: Dict[Tuple, Tuple[int, int]] = {}
+        for pi, r in enumerate(rings):
+            if r is None:
+                continue
+            for i in range(len(r)):
+                edge_owner[(key(r[i]), key(r[(i + 1) % len(r)]))] = (pi, i)
+        merged_any = False
+        dirty = set()
+        for pi, r in enumerate(rings):
+            if r is None or pi in dirty:
+                continue
+            n = len(r)
+            for i in range(n):
+                rev = (key(r[(i + 1) % n]), key(r[i]))
+                if rev[0] == rev[1]:
+                    continue
+                hit = edge_owner.get(rev)
+                if hit is None:
+                    continue
+                pj, j = hit
+                if pj == pi or rings[pj] is None or pj in dirty:
+                    continue
+                s = rings[pj]
+                m = len(s)
+                # r: ... r[i] -> r[i+1] ...; s: ... s[j] (= r[i+1]) -> s[j+1] (= r[i]) ...
+                cand = [r[(i + 1 + k) % n] for k in range(n)]          # starts at r[i+1], ends at r[i]
+                cand += [s[(j + 2 + k) % m] for k in range(m - 2)]     # s after s[j+1] up to before s[j]
+                cand = _clean_ring(cand, tol)
+                if 3 <= len(cand) <= max_verts and _is_convex(cand, tol) and \
+                        abs(_ring_area(cand) - _ring_area(r) - _ring_area(s)) <= 1e-6 * (1.0 + _ring_area(cand)):
+                    rings[pi] = cand
+                    rings[pj] = None
+                    dirty.add(pi); dirty.add(pj)
+                    merged_any = True
+                    break
+        return merged_any
+
+    def drop_contained() -> bool:
+        live = [i for i, r in enumerate(rings) if r is not None]
+        if not live:
+            return False
+        bb = np.array([[min(p[0] for p in rings[i]), min(p[1] for p in rings[i]),
+                        max(p[0] for p in rings[i]), max(p[1] for p in rings[i])] for i in live])
+        area = np.array([0.5 * sum(rings[i][k][0] * rings[i][(k + 1) % len(rings[i])][1] -
+                                   rings[i][(k + 1) % len(rings[i])][0] * rings[i][k][1]
+                                   for k in range(len(rings[i]))) for i in live])
+        order = np.argsort(area)  # small first: try to drop the small ones
+        dropped = False
+        alive = np.ones(len(live), bool)
+        eps = 1e-9
+        for a in order:
+            cand = np.nonzero(alive & (bb[:, 0] <= bb[a, 0] + eps) & (bb[:, 1] <= bb[a, 1] + eps) &
+                              (bb[:, 2] >= bb[a, 2] - eps) & (bb[:, 3] >= bb[a, 3] - eps))[0]
+            ra = rings[live[a]]
+            for b in cand:
+                if b == a:
+                    continue
+                rb = rings[live[b]]
+                inside = True
+                for k in range(len(rb)):
+                    p0, p1 = rb[k], rb[(k + 1) % len(rb)]
+                    ln = math.hypot(p1[0] - p0[0], p1[1] - p0[1])
+                    for v in ra:
+                        if _cross(p0, p1, v) < -eps * max(ln, 1.0):
+                            inside = False
+                            break
+                    if not inside:
+                        break
+                if inside and (area[b] > area[a] or (area[b] == area[a] and b < a)):
+                    alive[a] = False
+                    rings[live[a]] = None
+                    dropped = True
+                    break
+        return dropped
+
+    def drop_covered() -> bool:
+        """Step 3: drop a polygon covered by the union of the others (its area minus every
+        overlapping polygon, tracked as convex pieces, falls below 1e-9 m^2)."""
+        live = [i for i, r in enumerate(rings) if r is not None]
+        if len(live) < 2:
+            return False
+        bb = np.array([[min(p[0] for p in rings[i]), min(p[1] for p in rings[i]),
+                        max(p[0] for p in rings[i]), max(p[1] for p in rings[i])] for i in live])
+        area = np.array([_ring_area(rings[i]) for i in live])
+        alive = np.ones(len(live), bool)
+        dropped = False
+        for a in np.argsort(area):
+            cand = np.nonzero(alive & (bb[:, 0] < bb[a, 2]) & (bb[:, 2] > bb[a, 0]) &
+                              (bb[:, 1] < bb[a, 3]) & (bb[:, 3] > bb[a, 1]))[0]
+            cand = [b for b in cand if b != a]
+            if not cand:
+                continue
+            rest = [rings[live[a]]]
+            for b in sorted(cand, key=lambda k: -area[k]):
+                nxt = []
+                for piece in rest:
+                    nxt.extend(_convex_minus(piece, rings[live[b]]))
+                rest = nxt
+                if not rest:
+                    break
+            if sum(_ring_area(r) for r in rest) < 1e-9:
+                alive[a] = False
+                rings[live[a]] = None
+                dropped = True
+        return dropped
+
+    def fixed_point():
+        for _ in range(64):
+            a = False
+            while try_merge_pass():
+                a = True
+            b = drop_contained()
+            c = drop_covered()
+            if not (a or b or c):
+                break
+
+    fixed_point()
+    # Step 4: make the pieces disjoint (largest first; every later polygon keeps only the convex
+    # pieces of itself outside what is already there, slivers under 1e-9 m^2 dropped), so that a
+    # raster row meets each part of the surface once; then merge again.
+    rings[:] = _disjoint_pieces([r for r in rings if r is not None], max_verts, tol)
+    fixed_point()
+    return [np.asarray(r, np.float64) for r in rings if r is not None]
+
+
+def _disjoint_pieces(rings, max_verts: int, tol: float):
+    rings = sorted(rings, key=lambda r: -_ring_area(r))
+    acc: List[List[Tuple[float, float]]] = []
+    bbs: List[Tuple[float, float, float, float]] = []
+
+    def bbox(r):
+        return (min(p[0] for p in r), min(p[1] for p in r), max(p[0] for p in r), max(p[1] for p in r))
+
+    for r in rings:
+        rest = [r]
+        bb = bbox(r)
+        for q, qb in zip(acc, bbs):
+            if qb[0] >= bb[2] or qb[2] <= bb[0] or qb[1] >= bb[3] or qb[3] <= bb[1]:
+                continue
+            nxt = []
+            for piece in rest:
+                nxt.extend(_convex_minus(piece, q))
+            rest = nxt
+            if not rest:
+                break
+        for piece in rest:
+            piece = _clean_ring(piece, tol)
+            if len(piece) < 3 or _ring_area(piece) <= 1e-9 or not _is_convex(piece, tol):
+                continue
+            stack = [piece]
+            while stack:  # split rings with too many vertices along a diagonal (stays convex)
+                g = stack.pop()
+                if len(g) <= max_verts:
+                    acc.append(g)
+                    bbs.append(bbox(g))
+                else:
+                    h = len(g) // 2
+                    stack.append(g[:h + 1])
+                    stack.append(g[h:] + g[:1])
+    return acc
+
+
+def _ring_area(r: Sequence[Tuple[float, float]]) -> float:
+    return 0.5 * sum(r[k][0] * r[(k + 1) % len(r)][1] - r[(k + 1) % len(r)][0] * r[k][1] for k in range(len(r)))
+
+
+def _clip_halfplane(ring, p0, p1, keep_left: bool):
+    """Part of a convex ring on the left (or right) of the directed line p0 -> p1."""
+    out = []
+    n = len(ring)
+    sgn = 1.0 if keep_left else -1.0
+    d = [sgn * _cross(p0, p1, v) for v in ring]
+    for i in range(n):
+        a, b, da, db = ring[i], ring[(i + 1) % n], d[i], d[(i + 1) % n]
+        if da >= 0:
+            out.append(a)
+        if (da > 0 and db < 0) or (da < 0 and db > 0):
+            t = da / (da - db)
+            out.append((a[0] + (b[0] - a[0]) * t, a[1] + (b[1] - a[1]) * t))
+    return out
+
+
+def _convex_minus(p, q):
+    """Convex pieces of P minus Q (both convex, CCW): for each edge of Q, the part of what is
+    left of P outside that edge; what remains inside all edges is P intersect Q (discarded)."""
+    pieces = []
+    rest = list(p)
+    for k in range(len(q)):
+        if len(rest) < 3:
+            break
+        p0, p1 = q[k], q[(k + 1) % len(q)]
+        outside = _clip_halfplane(rest, p0, p1, keep_left=False)
+        if len(outside) >= 3 and _ring_area(outside) > 1e-12:
+            pieces.append(outside)
+        rest = _clip_halfplane(rest, p0, p1, keep_left=True)
+    return pieces
 
 
 def _ear_clip(line: Sequence[Tuple[float, float]]) -> List[List[Tuple[float, float]]]:
