@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libsmartsb200.so")
 SOURCES = ["sb_api.cu"]
-DEPS = ["sb_api.cu", "sb_kernels.cuh", "sb_control.cuh", "sb_waypoints.cuh", "sb_device.cuh", "sb_raster.cuh",
+DEPS = ["sb_api.cu", "sb_lidar.cuh", "sb_kernels.cuh", "sb_control.cuh", "sb_waypoints.cuh", "sb_device.cuh", "sb_raster.cuh",
         os.path.join("..", "..", "include", "smarts_b200.h"), os.path.join("..", "..", "include", "sb_detmath.h")]
 
 

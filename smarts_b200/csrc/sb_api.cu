@@ -2,6 +2,8 @@
 // Compiled for sm_100a only (-gencode arch=compute_100a,code=sm_100a -fmad=false).  There is no
 // CPU path in this library: every entry point that computes launches CUDA kernels.
 #include <cstdio>
+#include <algorithm>
+#include <cmath>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -16,6 +18,8 @@ struct SbHandle_ {
   DObs ob;
   bool have_map = false, have_rays = false;
   double* d_rays = nullptr;
+  int32_t* d_ray_order = nullptr;   // rays in azimuth order (k_lidar's thread -> ray map)
+  LSector* d_ray_sectors = nullptr; // bounding sector of every 32 consecutive rays of that order
   float ray_reach = 0.f;
   std::vector<void*> allocs;
   void* d_actions = nullptr;  // staging for sb_step_host
@@ -189,7 +193,7 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
   if (c.wp_enable && (c.wp_lookahead < 1 || c.wp_lookahead > SB_MAX_LOOKAHEAD || c.wp_out_paths < 1 ||
                       c.wp_out_paths > SB_MAX_PATHS || c.wp_out_len < 1 || c.wp_out_len > SB_MAX_LOOKAHEAD + 1))
     return fail(h, SB_EINVAL, "waypoint sensor limits");
-  if (c.lidar_enable && c.lidar_rays < 1) return fail(h, SB_EINVAL, "lidar_rays");
+  if (c.lidar_enable && (c.lidar_rays < 1 || c.lidar_rays > SB_LIDAR_MAX_RAYS)) return fail(h, SB_EINVAL, "lidar_rays");
   auto grid_ok = [](int w, int hh, double r) { return w >= 32 && hh >= 1 && (w % 32) == 0 && r > 0 && w <= 1024 && hh <= 1024; };
   if (c.ogm_enable && !grid_ok(c.ogm_width, c.ogm_height, c.ogm_resolution))
     return fail(h, SB_EINVAL, "ogm: width must be a multiple of 32, <= 1024; resolution > 0");
@@ -349,6 +353,7 @@ int sb_upload_lidar_rays(SbHandle h, const double* base_rays, int32_t n_rays) {
   if (h->cuda_err) return SB_ECUDA;
   if (n_rays != h->cfg.lidar_rays) return fail(h, SB_EINVAL, "n_rays != cfg.lidar_rays");
   cudaSetDevice(h->cfg.device);
+  if (n_rays > SB_LIDAR_MAX_RAYS) return fail(h, SB_EINVAL, "lidar: too many rays");
   const double* d = nullptr;
   if (!dev_upload(h, &d, base_rays, (size_t)n_rays * 3)) return SB_ECUDA;
   h->d_rays = const_cast<double*>(d);
@@ -356,6 +361,49 @@ int sb_upload_lidar_rays(SbHandle h, const double* base_rays, int32_t n_rays) {
   for (int i = 0; i < n_rays; ++i)
     reach = fmax(reach, sqrt(base_rays[i * 3] * base_rays[i * 3] + base_rays[i * 3 + 1] * base_rays[i * 3 + 1]));
   h->ray_reach = (float)(reach * 1.0001 + 0.01);
+  // Thread -> ray map of k_lidar: rays sorted by azimuth (vertical rays last) so that a warp's 32
+  // rays fan a narrow sector, and the bounding sector of every chunk of 32.  Used for culling
+  // only (conservative: a chunk that is not narrow is marked "wide" and culls nothing).
+  std::vector<int32_t> order(n_rays);
+  std::vector<double> az(n_rays);
+  for (int i = 0; i < n_rays; ++i) {
+    order[i] = i;
+    double hx = base_rays[i * 3], hy = base_rays[i * 3 + 1];
+    az[i] = (hx * hx + hy * hy > 1e-18) ? atan2(hy, hx) : 1e9;
+  }
+  std::stable_sort(order.begin(), order.end(), [&](int32_t p, int32_t q) { return az[p] < az[q]; });
+  const int n_chunks = (n_rays + 31) / 32;
+  std::vector<LSector> sectors(n_chunks);
+  for (int ch = 0; ch < n_chunks; ++ch) {
+    double sx = 0, sy = 0;
+    int cnt = 0;
+    for (int i = ch * 32; i < n_rays && i < ch * 32 + 32; ++i) {
+      int r = order[i];
+      if (az[r] > 1e8) continue;
+      sx += cos(az[r]);
+      sy += sin(az[r]);
+      ++cnt;
+    }
+    LSector q{1.f, 0.f, -2.f, 0.f};  // wide
+    double nrm = sqrt(sx * sx + sy * sy);
+    if (cnt > 0 && nrm > 0.5 * cnt) {
+      double ucx = sx / nrm, ucy = sy / nrm, cmin = 1.0;
+      for (int i = ch * 32; i < n_rays && i < ch * 32 + 32; ++i) {
+        int r = order[i];
+        if (az[r] > 1e8) continue;
+        cmin = fmin(cmin, cos(az[r]) * ucx + sin(az[r]) * ucy);
+      }
+      double half = acos(fmax(-1.0, fmin(1.0, cmin))) + 1e-3;  // margin for the float arithmetic of the cull
+      if (half < 1.3) q = LSector{(float)ucx, (float)ucy, (float)cos(half), (float)sin(half)};
+    }
+    sectors[ch] = q;
+  }
+  const int32_t* d_order = nullptr;
+  const LSector* d_sec = nullptr;
+  if (!dev_upload(h, &d_order, order.data(), order.size()) || !dev_upload(h, &d_sec, sectors.data(), sectors.size()))
+    return SB_ECUDA;
+  h->d_ray_order = const_cast<int32_t*>(d_order);
+  h->d_ray_sectors = const_cast<LSector*>(d_sec);
   h->have_rays = true;
   return SB_OK;
 }
@@ -449,7 +497,8 @@ int sb_observe(SbHandle h, void* stream) {
   }
   if (c.lidar_enable) {
     LaunchScope ls(h, SB_K_LIDAR, st);
-    k_lidar<<<na, SB_LIDAR_THREADS, 0, st>>>(c, h->dmap, h->st, h->ob, h->d_rays, h->ray_reach);
+    k_lidar<<<na, SB_LIDAR_THREADS, (size_t)c.lidar_rays * sizeof(double), st>>>(c, h->dmap, h->st, h->ob, h->d_rays,
+                                                                                     h->d_ray_order, h->d_ray_sectors, h->ray_reach);
   }
   if (c.ogm_enable || c.dagm_enable) {
     LaunchScope ls(h, SB_K_RASTER, st);

@@ -322,334 +322,9 @@ __global__ void __launch_bounds__(SB_OBS_WARPS * 32) k_observe(DCfg c, DMap m, D
 }
 
 // --------------------------------------------------------------------------------- lidar
-#define SB_LIDAR_THREADS 320
-#define SB_LIDAR_MAX_BOXES 160
-#define SB_LIDAR_MAX_EDGES 256
-
-struct LBox {
-  double x, y, c, s, hw, hl, z0, z1;
-};
-
-// lidar.py:74-134: closest hit of every ray against ground plane, vehicle boxes, edge walls.
-__global__ void __launch_bounds__(SB_LIDAR_THREADS)
-k_lidar(DCfg c, DMap m, DState s, DObs o, const double* __restrict__ rays, float reach_xy) {
-  // reach_xy: longest horizontal extent of any table ray (+ margin), for conservative culling
-  __shared__ LBox boxes[SB_LIDAR_MAX_BOXES];
-  __shared__ double edges[SB_LIDAR_MAX_EDGES][4];
-  __shared__ int n_boxes, n_edges;
-  const int ai = blockIdx.x;
-  const int e = ai / c.A, a = ai - e * c.A, vi = e * c.V + a;
-  const double ox = s.pos_x[vi], oy = s.pos_y[vi], oz = s.pos_z[vi] + 1.0;
-  if (threadIdx.x == 0) {
-    n_boxes = 0;
-    n_edges = 0;
-  }
-  __syncthreads();
-  // stage the env's other vehicles (order is irrelevant: the result is a minimum)
-  for (int j = threadIdx.x; j < c.V; j += blockDim.x) {
-    int vj = e * c.V + j;
-    if (j == a || !s.alive[vj]) continue;
-    {  // a hit lies within reach_xy of the origin and within the half diagonal of the box centre
-      float bx = (float)(s.pos_x[vj] - ox), by = (float)(s.pos_y[vj] - oy);
-      float fw = (float)s.width[vj], fl = (float)s.length[vj];
-      float lim = reach_xy + 0.5f * sqrtf(fw * fw + fl * fl) + 0.25f;
-      if (bx * bx + by * by > lim * lim) continue;
-    }
-    int k = atomicAdd(&n_boxes, 1);
-    if (k < SB_LIDAR_MAX_BOXES) {
-      double z0 = s.pos_z[vj] + (j < c.A ? 0.1 : 0.2);
-      boxes[k] = LBox{s.pos_x[vj], s.pos_y[vj], s.cos_h[vj], s.sin_h[vj], 0.5 * s.width[vj], 0.5 * s.length[vj],
-                      z0,          z0 + s.height[vj]};
-    }
-  }
-  if (c.lidar_wall_height > 0.0) {
-    // conservative cull: segments whose bounding circle reaches the 20 m + margin disc
-    for (int k = threadIdx.x; k < m.n_edges; k += blockDim.x) {
-      const double* ed = m.road_edges + (size_t)k * 4;
-      float mx = 0.5f * (float)(ed[0] + ed[2]) - (float)ox, my = 0.5f * (float)(ed[1] + ed[3]) - (float)oy;
-      float hx = 0.5f * (float)(ed[2] - ed[0]), hy = 0.5f * (float)(ed[3] - ed[1]);
-      float reach = sqrtf(hx * hx + hy * hy) + reach_xy + 0.25f;
-      if (mx * mx + my * my > reach * reach) continue;
-      int q = atomicAdd(&n_edges, 1);
-      if (q < SB_LIDAR_MAX_EDGES) {
-        edges[q][0] = ed[0];
-        edges[q][1] = ed[1];
-        edges[q][2] = ed[2];
-        edges[q][3] = ed[3];
-      }
-    }
-  }
-  __syncthreads();
-  const int nb = n_boxes < SB_LIDAR_MAX_BOXES ? n_boxes : SB_LIDAR_MAX_BOXES;
-  const int ne = n_edges < SB_LIDAR_MAX_EDGES ? n_edges : SB_LIDAR_MAX_EDGES;
-  if (threadIdx.x == 0 && (n_boxes > SB_LIDAR_MAX_BOXES || n_edges > SB_LIDAR_MAX_EDGES))
-    s.status[ai] |= SB_STATUS_LIDAR_OVERFLOW;
-  const double inf = __longlong_as_double(0x7ff0000000000000LL);
-  const double miss = c.lidar_miss_inf ? inf : 0.0;
-  for (int r = threadIdx.x; r < c.lidar_rays; r += blockDim.x) {
-    const double dx = rays[r * 3 + 0], dy = rays[r * 3 + 1], dz = rays[r * 3 + 2];
-    double tbest = 2.0;
-    if (dz < 0.0) {
-      double t = (0.0 - oz) / dz;
-      if (t >= 0.0 && t <= 1.0) tbest = t;
-    }
-    for (int k = 0; k < nb; ++k) {
-      const LBox b = boxes[k];
-      double rx = ox - b.x, ry = oy - b.y;
-      double lo[3] = {rx * b.c + ry * b.s, ry * b.c - rx * b.s, oz};
-      double ld[3] = {dx * b.c + dy * b.s, dy * b.c - dx * b.s, dz};
-      double mn[3] = {-b.hw, -b.hl, b.z0}, mxv[3] = {b.hw, b.hl, b.z1};
-      double t0 = -inf, t1 = inf;
-      bool ok = true;
-#pragma unroll
-      for (int q = 0; q < 3; ++q) {
-        if (ld[q] == 0.0) {
-          if (lo[q] < mn[q] || lo[q] > mxv[q]) ok = false;
-        } else {
-          double ta = (mn[q] - lo[q]) / ld[q], tb = (mxv[q] - lo[q]) / ld[q];
-          if (ta > tb) {
-            double t = ta;
-            ta = tb;
-            tb = t;
-          }
-          if (ta > t0) t0 = ta;
-          if (tb < t1) t1 = tb;
-        }
-      }
-      if (!ok || t0 > t1 || t0 < 0.0 || t0 > 1.0) continue;
-      if (t0 < tbest) tbest = t0;
-    }
-    for (int k = 0; k < ne; ++k) {
-      double ex = edges[k][2] - edges[k][0], ey = edges[k][3] - edges[k][1];
-      double den = dx * ey - dy * ex;
-      if (den == 0.0) continue;
-      double qx = edges[k][0] - ox, qy = edges[k][1] - oy;
-      double t = (qx * ey - qy * ex) / den;
-      double u = (qx * dy - qy * dx) / den;
-      if (t < 0.0 || t > 1.0 || u < 0.0 || u > 1.0) continue;
-      double zz = oz + t * dz;
-      if (zz < 0.0 || zz > c.lidar_wall_height) continue;
-      if (t < tbest) tbest = t;
-    }
-    size_t q = (size_t)ai * c.lidar_rays + r;
-    if (tbest <= 1.0) {
-      o.lidar_hits[q] = 1;
-      o.lidar_points[q * 3 + 0] = ox + tbest * dx;
-      o.lidar_points[q * 3 + 1] = oy + tbest * dy;
-      o.lidar_points[q * 3 + 2] = oz + tbest * dz;
-    } else {
-      o.lidar_hits[q] = 0;
-      o.lidar_points[q * 3 + 0] = miss;
-      o.lidar_points[q * 3 + 1] = miss;
-      o.lidar_points[q * 3 + 2] = miss;
-    }
-  }
-}
+// k_lidar lives in sb_lidar.cuh (azimuth-sorted warps, sector / per-ray culls, exact binary64 tests).
+#include "sb_lidar.cuh"
 
 // --------------------------------------------------------------------------------- raster
-// k_raster lives in sb_raster.cuh (row-per-thread spans).  The first-generation version below
-// (warp per polygon, int64 divisions, atomicOr) is kept for reference only; profiles/README.md
-// has its numbers (1.80 ms/step at 16384 agents, 18 % of HBM peak, barrier-stall bound).
+// k_raster lives in sb_raster.cuh (row-per-thread exact integer spans).
 #include "sb_raster.cuh"
-#if 0
-// Contract (DESIGN.md "Grid maps"): vertices -> pixel space in binary64, snapped to 1/256 px; a
-// pixel is set iff its centre satisfies all edge functions of the convex polygon (inclusive),
-// in exact integer arithmetic.  Here each (polygon, row) task solves the edge inequalities for
-// the covered column span with exact integer division and ORs the span into a 1-bit image in
-// shared memory; the image is then expanded to 0/255 bytes with 16-byte streaming stores.
-#define SB_RASTER_THREADS 256
-#define SB_RASTER_MAX_POLYS 256
-
-struct PixPoly {
-  long long U[4], V[4];
-  int n;
-  long long sg;  // orientation sign, 0 = degenerate
-};
-
-struct Cam {
-  double px, py, c, s, res, halfw, halfh;
-};
-
-__device__ __forceinline__ void d_to_pixel(const Cam& cam, double x, double y, long long* U, long long* V) {
-  double dx = x - cam.px, dy = y - cam.py;
-  double xr = dx * cam.c + dy * cam.s;
-  double yr = dy * cam.c - dx * cam.s;
-  double u = xr / cam.res + cam.halfw;
-  double v = cam.halfh - yr / cam.res;
-  double su = rint(u * 256.0), sv = rint(v * 256.0);
-  const double lim = 1073741824.0;
-  su = su > lim ? lim : (su < -lim ? -lim : su);
-  sv = sv > lim ? lim : (sv < -lim ? -lim : sv);
-  *U = (long long)su;
-  *V = (long long)sv;
-}
-
-__device__ __forceinline__ long long d_floor_div(long long a, long long b) {  // b > 0
-  long long q = a / b;
-  if ((a % b) != 0 && a < 0) --q;
-  return q;
-}
-__device__ __forceinline__ long long d_ceil_div(long long a, long long b) {  // b > 0
-  long long q = a / b;
-  if ((a % b) != 0 && a > 0) ++q;
-  return q;
-}
-
-__device__ __forceinline__ void d_finish_poly(PixPoly& p) {
-  long long area2 = 0;
-  for (int i = 0; i < p.n; ++i) {
-    int j = (i + 1 == p.n) ? 0 : i + 1;
-    area2 += p.U[i] * p.V[j] - p.U[j] * p.V[i];
-  }
-  p.sg = area2 > 0 ? 1 : (area2 < 0 ? -1 : 0);
-}
-
-// rasterise the polygons staged in shared memory into the bit image (W/32 words per row)
-__device__ void d_fill_polys(const PixPoly* polys, int np, uint32_t* bits, int W, int H) {
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
-  const int wpr = W >> 5;
-  for (int p = warp; p < np; p += nwarps) {
-    const PixPoly& P = polys[p];
-    if (P.sg == 0) continue;
-    long long vmin = P.V[0], vmax = P.V[0], umin = P.U[0], umax = P.U[0];
-    for (int i = 1; i < P.n; ++i) {
-      vmin = P.V[i] < vmin ? P.V[i] : vmin;
-      vmax = P.V[i] > vmax ? P.V[i] : vmax;
-      umin = P.U[i] < umin ? P.U[i] : umin;
-      umax = P.U[i] > umax ? P.U[i] : umax;
-    }
-    long long r0 = d_ceil_div(vmin - 128, 256), r1 = d_floor_div(vmax - 128, 256);
-    if (r0 < 0) r0 = 0;
-    if (r1 > H - 1) r1 = H - 1;
-    if (d_floor_div(umax - 128, 256) < 0 || d_ceil_div(umin - 128, 256) > W - 1) continue;
-    for (long long r = r0 + lane; r <= r1; r += 32) {
-      long long py = r * 256 + 128;
-      long long c0 = 0, c1 = W - 1;
-      bool empty = false;
-      for (int i = 0; i < P.n; ++i) {
-        int j = (i + 1 == P.n) ? 0 : i + 1;
-        long long dxe = P.U[j] - P.U[i], dye = P.V[j] - P.V[i];
-        // sg * (dxe*(py-Vi) - dye*(px-Ui)) >= 0   <=>   a*px + b >= 0
-        long long aa = -P.sg * dye;
-        long long bb = P.sg * (dxe * (py - P.V[i]) + dye * P.U[i]);
-        if (aa > 0) {
-          long long lo = d_ceil_div(-bb - 128 * aa, 256 * aa);
-          if (lo > c0) c0 = lo;
-        } else if (aa < 0) {
-          long long hi = d_floor_div(bb + 128 * aa, -256 * aa);
-          if (hi < c1) c1 = hi;
-        } else if (bb < 0) {
-          empty = true;
-        }
-      }
-      if (empty || c0 > c1) continue;
-      int w0 = (int)(c0 >> 5), w1 = (int)(c1 >> 5);
-      uint32_t* row = bits + (int)r * wpr;
-      for (int w = w0; w <= w1; ++w) {
-        uint32_t msk = 0xffffffffu;
-        if (w == w0) msk &= 0xffffffffu << (c0 & 31);
-        if (w == w1) msk &= 0xffffffffu >> (31 - (c1 & 31));
-        atomicOr(&row[w], msk);
-      }
-    }
-  }
-}
-
-__device__ __forceinline__ uint32_t d_expand4(uint32_t b) {  // 4 bits -> 4 bytes of 0/255
-  uint32_t x = (b & 1u) | ((b & 2u) << 7) | ((b & 4u) << 14) | ((b & 8u) << 21);
-  return x * 255u;
-}
-
-// write the H x W byte image from the bit image, 16 pixels (one uint4) per thread per step
-__device__ void d_store_image(const uint32_t* bits, uint8_t* dst, int W, int H) {
-  const int n16 = (W * H) >> 4;
-  uint4* out = reinterpret_cast<uint4*>(dst);
-  for (int i = threadIdx.x; i < n16; i += blockDim.x) {
-    uint32_t word = bits[i >> 1];
-    uint32_t hw = (i & 1) ? (word >> 16) : (word & 0xffffu);
-    uint4 v;
-    v.x = d_expand4(hw & 15u);
-    v.y = d_expand4((hw >> 4) & 15u);
-    v.z = d_expand4((hw >> 8) & 15u);
-    v.w = d_expand4((hw >> 12) & 15u);
-    __stcs(out + i, v);
-  }
-}
-
-// dynamic shared memory: bit image (max(ogm, dagm) W*H/8 bytes)
-__global__ void __launch_bounds__(SB_RASTER_THREADS) k_raster(DCfg c, DMap m, DState s, DObs o) {
-  extern __shared__ uint32_t bits[];
-  __shared__ PixPoly polys[SB_RASTER_MAX_POLYS];
-  __shared__ int n_polys;
-  const int ai = blockIdx.x;
-  const int e = ai / c.A, a = ai - e * c.A, vi = e * c.V + a;
-  const double px = s.pos_x[vi], py = s.pos_y[vi], ch = s.cos_h[vi], sh = s.sin_h[vi];
-
-  if (c.ogm_enable) {  // sensors.py:719-758: vehicles only, ego included
-    const int W = c.ogm_w, H = c.ogm_h;
-    Cam cam{px, py, ch, sh, c.ogm_res, 0.5 * W, 0.5 * H};
-    for (int i = threadIdx.x; i < (W * H) >> 5; i += blockDim.x) bits[i] = 0u;
-    for (int base = 0; base < c.V; base += SB_RASTER_MAX_POLYS) {
-      int cntp = c.V - base < SB_RASTER_MAX_POLYS ? c.V - base : SB_RASTER_MAX_POLYS;
-      __syncthreads();
-      for (int t = threadIdx.x; t < cntp; t += blockDim.x) {
-        int vj = e * c.V + base + t;
-        PixPoly P;
-        P.n = 4;
-        if (s.alive[vj]) {
-          double cc = s.cos_h[vj], ss = s.sin_h[vj];
-          double hw = 0.5 * s.width[vj], hl = 0.5 * s.length[vj];
-          const double sa[4] = {-hw, hw, hw, -hw}, sbv[4] = {-hl, -hl, hl, hl};
-          for (int k = 0; k < 4; ++k) {
-            double x = s.pos_x[vj] + (sa[k] * cc - sbv[k] * ss);
-            double y = s.pos_y[vj] + (sa[k] * ss + sbv[k] * cc);
-            d_to_pixel(cam, x, y, &P.U[k], &P.V[k]);
-          }
-          d_finish_poly(P);
-        } else {
-          P.sg = 0;
-        }
-        polys[t] = P;
-      }
-      __syncthreads();
-      d_fill_polys(polys, cntp, bits, W, H);
-    }
-    __syncthreads();
-    d_store_image(bits, o.ogm + (size_t)ai * W * H, W, H);
-    __syncthreads();
-  }
-
-  if (c.dagm_enable) {  // sensors.py:675-716: road surface only
-    const int W = c.dagm_w, H = c.dagm_h;
-    Cam cam{px, py, ch, sh, c.dagm_res, 0.5 * W, 0.5 * H};
-    for (int i = threadIdx.x; i < (W * H) >> 5; i += blockDim.x) bits[i] = 0u;
-    // conservative world-space cull radius: half diagonal of the film + 1 m
-    const float rad = 0.5f * (float)c.dagm_res * sqrtf((float)(W * W + H * H)) + 1.0f;
-    const float fx = (float)px, fy = (float)py;
-    for (int base = 0; base < m.n_polys; base += blockDim.x) {
-      if (threadIdx.x == 0) n_polys = 0;
-      __syncthreads();
-      int p = base + threadIdx.x;
-      if (p < m.n_polys) {
-        const float* bb = m.poly_bbox + (size_t)p * 4;
-        bool hit = !(bb[0] > fx + rad || bb[2] < fx - rad || bb[1] > fy + rad || bb[3] < fy - rad);
-        if (hit) {
-          int st = m.poly_start[p], n = m.poly_start[p + 1] - st;
-          if (n >= 3 && n <= 4) {
-            PixPoly P;
-            P.n = n;
-            for (int k = 0; k < n; ++k) d_to_pixel(cam, m.poly_x[st + k], m.poly_y[st + k], &P.U[k], &P.V[k]);
-            d_finish_poly(P);
-            int q = atomicAdd(&n_polys, 1);
-            polys[q] = P;  // at most blockDim.x == SB_RASTER_MAX_POLYS per round
-          }
-        }
-      }
-      __syncthreads();
-      d_fill_polys(polys, n_polys, bits, W, H);
-      __syncthreads();
-    }
-    d_store_image(bits, o.dagm + (size_t)ai * W * H, W, H);
-  }
-}
-#endif  // first-generation rasteriser

@@ -284,25 +284,35 @@ __global__ void __launch_bounds__(SB_RASTER_THREADS, 4) k_raster(DCfg c, DMap m,
   const int ai = blockIdx.x;
   const int e = ai / c.A, a = ai - e * c.A, vi = e * c.V + a;
   const double px = s.pos_x[vi], py = s.pos_y[vi], ch = s.cos_h[vi], sh = s.sin_h[vi];
-  RasterJob job;
-  job.on[0] = c.ogm_enable != 0;   // sensors.py:719-758: vehicles only, ego included
-  job.on[1] = c.dagm_enable != 0;  // sensors.py:675-716: road surface only
-  job.W[0] = job.on[0] ? c.ogm_w : 0;
-  job.H[0] = job.on[0] ? c.ogm_h : 0;
-  job.W[1] = job.on[1] ? c.dagm_w : 0;
-  job.H[1] = job.on[1] ? c.dagm_h : 0;
-  job.cam[0] = Cam{px, py, ch, sh, c.ogm_res, 0.5 * c.ogm_w, 0.5 * c.ogm_h};
-  job.cam[1] = Cam{px, py, ch, sh, c.dagm_res, 0.5 * c.dagm_w, 0.5 * c.dagm_h};
-  job.n_veh = job.on[0] ? c.V : 0;
-  job.n_src = job.n_veh + (job.on[1] ? m.n_polys : 0);
-  const int Hmax = max(job.H[0], job.H[1]), Wmax = max(job.W[0], job.W[1]);
-  const int wpr0 = job.W[0] >> 5, wpr1 = job.W[1] >> 5;
-  const int rows0 = min(job.H[0], SB_RASTER_THREADS), rows1 = min(job.H[1], SB_RASTER_THREADS);
+  // the job record is indexed by image at run time: it lives in shared memory (a per-thread copy
+  // would go to local memory -- 144 B x 256 threads x 16 384 CTAs of extra DRAM write traffic)
+  __shared__ RasterJob sjob;
+  if (threadIdx.x == 0) {
+    RasterJob& j = sjob;
+    j.on[0] = c.ogm_enable != 0;   // sensors.py:719-758: vehicles only, ego included
+    j.on[1] = c.dagm_enable != 0;  // sensors.py:675-716: road surface only
+    j.W[0] = j.on[0] ? c.ogm_w : 0;
+    j.H[0] = j.on[0] ? c.ogm_h : 0;
+    j.W[1] = j.on[1] ? c.dagm_w : 0;
+    j.H[1] = j.on[1] ? c.dagm_h : 0;
+    j.cam[0] = Cam{px, py, ch, sh, c.ogm_res, 0.5 * c.ogm_w, 0.5 * c.ogm_h};
+    j.cam[1] = Cam{px, py, ch, sh, c.dagm_res, 0.5 * c.dagm_w, 0.5 * c.dagm_h};
+    j.n_veh = j.on[0] ? c.V : 0;
+    j.n_src = j.n_veh + (j.on[1] ? m.n_polys : 0);
+  }
+  __syncthreads();
+  const RasterJob& job = sjob;
+  const int W0 = c.ogm_enable ? c.ogm_w : 0, H0 = c.ogm_enable ? c.ogm_h : 0;
+  const int W1 = c.dagm_enable ? c.dagm_w : 0, H1 = c.dagm_enable ? c.dagm_h : 0;
+  const int n_veh = c.ogm_enable ? c.V : 0, n_src = n_veh + (c.dagm_enable ? m.n_polys : 0);
+  const int Hmax = max(H0, H1), Wmax = max(W0, W1);
+  const int wpr0 = W0 >> 5, wpr1 = W1 >> 5;
+  const int rows0 = min(H0, SB_RASTER_THREADS), rows1 = min(H1, SB_RASTER_THREADS);
   uint32_t* bits0 = reinterpret_cast<uint32_t*>(smem + bits_off);
   uint32_t* bits1 = bits0 + rows0 * (wpr0 + 1);
   // conservative world-space cull radii: the film's half diagonal + 1 m
-  const float rad0 = 0.5f * (float)c.ogm_res * sqrtf((float)job.W[0] * job.W[0] + (float)job.H[0] * job.H[0]) + 1.0f;
-  const float rad1 = 0.5f * (float)c.dagm_res * sqrtf((float)job.W[1] * job.W[1] + (float)job.H[1] * job.H[1]) + 1.0f;
+  const float rad0 = 0.5f * (float)c.ogm_res * sqrtf((float)W0 * W0 + (float)H0 * H0) + 1.0f;
+  const float rad1 = 0.5f * (float)c.dagm_res * sqrtf((float)W1 * W1 + (float)H1 * H1) + 1.0f;
   const float fx = (float)px, fy = (float)py;
   lut[threadIdx.x] = make_uint2(d_expand4(threadIdx.x & 15u), d_expand4(threadIdx.x >> 4));
 
@@ -312,10 +322,10 @@ __global__ void __launch_bounds__(SB_RASTER_THREADS, 4) k_raster(DCfg c, DMap m,
       uint32_t w0[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u}, w1[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
       if (threadIdx.x == 0) st->n_list = 0;
       __syncthreads();
-      for (int base = 0; base < job.n_src; base += SB_RASTER_THREADS) {
+      for (int base = 0; base < n_src; base += SB_RASTER_THREADS) {
         const int p = base + threadIdx.x;
         bool keep = false;
-        if (p < job.n_veh) {
+        if (p < n_veh) {
           const int vj = e * c.V + p;
           if (s.alive[vj]) {
             const float dx = (float)s.pos_x[vj] - fx, dy = (float)s.pos_y[vj] - fy;
@@ -323,8 +333,8 @@ __global__ void __launch_bounds__(SB_RASTER_THREADS, 4) k_raster(DCfg c, DMap m,
             const float lim = rad0 + 0.5f * sqrtf(fl * fl + fw * fw) + 0.5f;
             keep = dx * dx + dy * dy <= lim * lim;
           }
-        } else if (p < job.n_src) {
-          const int q = p - job.n_veh;
+        } else if (p < n_src) {
+          const int q = p - n_veh;
           const float4 bb = reinterpret_cast<const float4*>(m.poly_bbox)[q];
           const int n = m.poly_start[q + 1] - m.poly_start[q];
           keep = !(bb.x > fx + rad1 || bb.z < fx - rad1 || bb.y > fy + rad1 || bb.w < fy - rad1) && n >= 3 &&
@@ -333,7 +343,7 @@ __global__ void __launch_bounds__(SB_RASTER_THREADS, 4) k_raster(DCfg c, DMap m,
         if (keep) st->list[atomicAdd(&st->n_list, 1)] = p;
         __syncthreads();
         // stage + rasterise in rounds; a remainder < ROUND waits for the next cull pass
-        const bool last = base + SB_RASTER_THREADS >= job.n_src;
+        const bool last = base + SB_RASTER_THREADS >= n_src;
         int n_list = st->n_list;
         while (n_list >= SB_RASTER_ROUND || (last && n_list > 0)) {
           const int count = min(n_list, SB_RASTER_ROUND);
@@ -349,14 +359,14 @@ __global__ void __launch_bounds__(SB_RASTER_THREADS, 4) k_raster(DCfg c, DMap m,
         __syncthreads();
       }
       // every thread is past the last rows pass: the staging area may now be overwritten
-      if (r < job.H[0] && cb < job.W[0]) {
+      if (r < H0 && cb < W0) {
         uint32_t* row = bits0 + threadIdx.x * (wpr0 + 1) + (cb >> 5);
         const int nw = min(8, wpr0 - (cb >> 5));
 #pragma unroll
         for (int k = 0; k < 8; ++k)
           if (k < nw) row[k] = w0[k];
       }
-      if (r < job.H[1] && cb < job.W[1]) {
+      if (r < H1 && cb < W1) {
         uint32_t* row = bits1 + threadIdx.x * (wpr1 + 1) + (cb >> 5);
         const int nw = min(8, wpr1 - (cb >> 5));
 #pragma unroll
@@ -365,12 +375,12 @@ __global__ void __launch_bounds__(SB_RASTER_THREADS, 4) k_raster(DCfg c, DMap m,
       }
     }
     __syncthreads();
-    if (rg < job.H[0])
-      d_store_rows(bits0, lut, o.ogm + (size_t)ai * job.W[0] * job.H[0] + (size_t)rg * job.W[0],
-                   min(job.H[0] - rg, SB_RASTER_THREADS), wpr0, wpr0 + 1);
-    if (rg < job.H[1])
-      d_store_rows(bits1, lut, o.dagm + (size_t)ai * job.W[1] * job.H[1] + (size_t)rg * job.W[1],
-                   min(job.H[1] - rg, SB_RASTER_THREADS), wpr1, wpr1 + 1);
+    if (rg < H0)
+      d_store_rows(bits0, lut, o.ogm + (size_t)ai * W0 * H0 + (size_t)rg * W0,
+                   min(H0 - rg, SB_RASTER_THREADS), wpr0, wpr0 + 1);
+    if (rg < H1)
+      d_store_rows(bits1, lut, o.dagm + (size_t)ai * W1 * H1 + (size_t)rg * W1,
+                   min(H1 - rg, SB_RASTER_THREADS), wpr1, wpr1 + 1);
     __syncthreads();
   }
 }
