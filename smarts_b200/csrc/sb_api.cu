@@ -474,7 +474,7 @@ int sb_step(SbHandle h, const void* dev_actions, void* stream) {
   {
     LaunchScope ls(h, SB_K_CONTROL, st);
     if (c.action_space == SB_ACTION_LANE || c.action_space == SB_ACTION_LANE_WITH_CONTINUOUS_SPEED) {
-      k_control_lane<<<(na + SB_CTRL_WARPS - 1) / SB_CTRL_WARPS, SB_CTRL_WARPS * 32, 0, st>>>(c, h->dmap, h->st,
+      k_control_lane<<<(na + SB_CTRL_GROUP - 1) / SB_CTRL_GROUP, SB_CTRL_WARPS * 32, 0, st>>>(c, h->dmap, h->st,
                                                                                             dev_actions);
     } else {
       k_control_simple<<<(na + 127) / 128, 128, 0, st>>>(c, h->st, static_cast<const double*>(dev_actions));

@@ -67,65 +67,109 @@ __global__ void k_set_social(DCfg c, DState s, const double* __restrict__ in) {
 }
 
 // --------------------------------------------------------------------------------- control
-#define SB_CTRL_WARPS 4
+// Two phases in one launch.  Phase A (warp per agent, 4 agents per warp in turn): the waypoint
+// path search -- strided argmin scans + branch enumeration -- and the choice of the lane to
+// follow; the chosen path's lane points go to shared memory.  Phase B (thread per agent): the
+// inherently serial part -- re-spacing of that one path, the steering / throttle law, the
+// substepped chassis -- so its ~10 k dependent instructions are issued once per agent instead of
+// once per warp with 31 lanes idle.
+#define SB_CTRL_WARPS 8
+#define SB_CTRL_GROUP 32  // agents per block
+#define SB_CTRL_LOOKAHEAD 16
+
+struct CtrlPick {
+  int32_t lp[SB_CTRL_LOOKAHEAD + 1];
+  int32_t len;  // 0: no waypoints found
+};
+
+// controllers/__init__.py:125-152: Lane strings / LaneWithContinuousSpeed tuple -> (target speed, lane change)
+__device__ __forceinline__ void d_lane_action(const DCfg& c, const void* actions, int ai, double* ts, int* lc) {
+  *ts = 15;
+  *lc = 0;
+  if (c.action_space == SB_ACTION_LANE) {
+    int cmd = static_cast<const int32_t*>(actions)[ai];
+    if (cmd == SB_LANE_SLOW_DOWN) *ts = 0;
+    else if (cmd == SB_LANE_CHANGE_LEFT) { *ts = 12.5; *lc = 1; }
+    else if (cmd == SB_LANE_CHANGE_RIGHT) { *ts = 12.5; *lc = -1; }
+  } else {
+    const double* ac = static_cast<const double*>(actions) + (size_t)ai * 2;
+    *ts = ac[0];
+    *lc = (int)ac[1];
+  }
+}
 
 __global__ void __launch_bounds__(SB_CTRL_WARPS * 32)
 k_control_lane(DCfg c, DMap m, DState s, const void* __restrict__ actions) {
   __shared__ WarpPaths wps[SB_CTRL_WARPS];
+  __shared__ CtrlPick picks[SB_CTRL_GROUP];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int ai = blockIdx.x * SB_CTRL_WARPS + warp;
-  if (ai >= c.E * c.A) return;
+  const int a0 = blockIdx.x * SB_CTRL_GROUP, na = c.E * c.A;
+  WarpPaths* wp = &wps[warp];
+  for (int g = warp; g < SB_CTRL_GROUP; g += SB_CTRL_WARPS) {  // phase A
+    const int ai = a0 + g;
+    if (ai >= na) break;
+    const int e = ai / c.A, a = ai - e * c.A, vi = e * c.V + a;
+    const double vx = s.pos_x[vi], vy = s.pos_y[vi], vh = s.heading[vi];
+    double ts;
+    int lc;
+    d_lane_action(c, actions, ai, &ts, &lc);
+    wp_waypoint_paths(m, vx, vy, vh, SB_CTRL_LOOKAHEAD, 5.0, s.route + (size_t)ai * c.route_cap, s.route_len[ai], wp,
+                      lane);
+    __syncwarp();
+    const int n = wp->n;
+    if (lane == 0) {
+      uint32_t bits = (wp->overflow ? SB_STATUS_PATH_OVERFLOW : 0u) | (n == 0 ? SB_STATUS_NO_WAYPOINTS : 0u);
+      if (bits) s.status[ai] |= bits;
+      if (n == 0) picks[g].len = 0;
+    }
+    if (n > 0) {
+      int rank = 0x7fffffff;
+      double d0 = 1e300;
+      if (lane < n) {  // find_current_lane, lane_following_controller.py:367-374
+        double fx, fy;
+        wp_first_point(m, wp->lp[lane], wp->len[lane], vx, vy, &fx, &fy);
+        rank = wp_rank(m, wp, lane);
+        double dx = fx - vx, dy = fy - vy;
+        d0 = sqrt(dx * dx + dy * dy);
+      }
+      double dmin = d0;
+      int cur = rank;
+      warp_argmin(dmin, cur);
+      int sel = cur + lc;
+      sel = sel < 0 ? 0 : (sel > n - 1 ? n - 1 : sel);
+      if (rank == sel) {
+        const int len = wp->len[lane];
+        picks[g].len = len;
+        for (int i = 0; i < len; ++i) picks[g].lp[i] = wp->lp[lane][i];
+      }
+    }
+    __syncwarp();
+  }
+  __syncthreads();
+  if (threadIdx.x >= SB_CTRL_GROUP) return;
+  const int ai = a0 + threadIdx.x;  // phase B
+  if (ai >= na) return;
   const int e = ai / c.A, a = ai - e * c.A, vi = e * c.V + a;
   DEgo v{s.pos_x[vi], s.pos_y[vi], s.heading[vi], s.speed[vi], s.yaw_rate[vi], s.v_long[ai], s.v_lat[ai]};
-  double ts = 15;
-  int lc = 0;
-  if (c.action_space == SB_ACTION_LANE) {  // controllers/__init__.py:125-144
-    int cmd = static_cast<const int32_t*>(actions)[ai];
-    if (cmd == SB_LANE_SLOW_DOWN) ts = 0;
-    else if (cmd == SB_LANE_CHANGE_LEFT) { ts = 12.5; lc = 1; }
-    else if (cmd == SB_LANE_CHANGE_RIGHT) { ts = 12.5; lc = -1; }
-  } else {
-    const double* ac = static_cast<const double*>(actions) + (size_t)ai * 2;
-    ts = ac[0];
-    lc = (int)ac[1];
-  }
-  WarpPaths* wp = &wps[warp];
-  wp_waypoint_paths(m, v.x, v.y, v.h, 16, 5.0, s.route + (size_t)ai * c.route_cap, s.route_len[ai], wp, lane);
-  __syncwarp();
-  const int n = wp->n;
   double* st = s.ctrl + (size_t)ai * SB_CTRL_STATE;
   double* out3 = s.last_control + (size_t)ai * 3;
-  if (lane == 0 && wp->overflow) s.status[ai] |= SB_STATUS_PATH_OVERFLOW;
-  if (n == 0) {
-    if (lane == 0) {
-      s.status[ai] |= SB_STATUS_NO_WAYPOINTS;
-      d_apply_control(v, 0, 0, 0, out3);
-      d_chassis_step(s, ai, vi, c.dt, c.substeps);
-    }
-    return;
-  }
-  double wx[17], wy[17], wh[17];
-  int L = 0, rank = 0x7fffffff;
-  double d0 = 1e300;
-  if (lane < n) {
-    L = wp_equally_spaced<17>(m, wp->lp[lane], wp->len[lane], v.x, v.y, 17, [&](int i, const DWaypoint& w) {
-      wx[i] = w.x;
-      wy[i] = w.y;
-      wh[i] = w.heading;
-    });
-    rank = wp_rank(m, wp, lane);
-    double dx = wx[0] - v.x, dy = wy[0] - v.y;
-    d0 = sqrt(dx * dx + dy * dy);  // find_current_lane, :367-374
-  }
-  double dmin = d0;
-  int cur = rank;
-  warp_argmin(dmin, cur);
-  int sel = cur + lc;
-  sel = sel < 0 ? 0 : (sel > n - 1 ? n - 1 : sel);
-  if (rank == sel) {
+  const CtrlPick& pk = picks[threadIdx.x];
+  if (pk.len == 0) {
+    d_apply_control(v, 0, 0, 0, out3);
+  } else {
+    double ts;
+    int lc;
+    d_lane_action(c, actions, ai, &ts, &lc);
+    double wx[SB_CTRL_LOOKAHEAD + 1], wy[SB_CTRL_LOOKAHEAD + 1], wh[SB_CTRL_LOOKAHEAD + 1];
+    const int L = wp_equally_spaced<SB_CTRL_LOOKAHEAD + 1>(m, pk.lp, pk.len, v.x, v.y, SB_CTRL_LOOKAHEAD + 1,
+                                                         [&](int i, const DWaypoint& w) {
+                                                           wx[i] = w.x;
+                                                           wy[i] = w.y;
+                                                           wh[i] = w.heading;
+                                                         });
     d_lane_following_law(v, wx, wy, wh, L, ts, lc, c.dt, st, out3);
-    d_chassis_step(s, ai, vi, c.dt, c.substeps);
   }
+  d_chassis_step(s, ai, vi, c.dt, c.substeps);
 }
 
 __global__ void k_control_simple(DCfg c, DState s, const double* __restrict__ actions) {

@@ -100,7 +100,8 @@ __device__ void wp_enumerate_paths(const DMap& m, int start, int lookahead, cons
   int32_t node[SB_MAX_LOOKAHEAD + 1];
   int32_t cursor[SB_MAX_LOOKAHEAD + 1];
   uint8_t had_child[SB_MAX_LOOKAHEAD + 1];
-  int d = 0;
+  int d = 0, memo_lane = -1;
+  bool memo_ok = false;
   node[0] = start;
   cursor[0] = m.lp_next_start[start];
   had_child[0] = 0;
@@ -114,15 +115,21 @@ __device__ void wp_enumerate_paths(const DMap& m, int start, int lookahead, cons
       while (cursor[d] < end) {
         int nlp = m.lp_next[cursor[d]++];
         int nlane = m.lp_lane[nlp];
-        int road = m.lane_road[nlane];
         if (nf > 0) {
-          if (!wp_in_route(filt, nf, road)) continue;
-          if (road != filt[nf - 1]) {
-            bool any = false;
-            for (int o = m.lane_out_start[nlane]; o < m.lane_out_start[nlane + 1]; ++o)
-              if (wp_in_route(filt, nf, m.lane_road[m.lane_out[o]])) any = true;
-            if (!any) continue;
+          // the filter is a function of the lane only: successive lane points of one lane reuse it
+          if (nlane != memo_lane) {
+            int road = m.lane_road[nlane];
+            bool ok = wp_in_route(filt, nf, road);
+            if (ok && road != filt[nf - 1]) {
+              bool any = false;
+              for (int o = m.lane_out_start[nlane]; o < m.lane_out_start[nlane + 1]; ++o)
+                if (wp_in_route(filt, nf, m.lane_road[m.lane_out[o]])) any = true;
+              ok = any;
+            }
+            memo_lane = nlane;
+            memo_ok = ok;
           }
+          if (!memo_ok) continue;
         }
         had_child[d] = 1;
         ++d;
@@ -224,6 +231,27 @@ __device__ __forceinline__ int wp_rank(const DMap& m, const WarpPaths* wp, int k
     if (kj < key || (kj == key && j < k)) ++rank;
   }
   return rank;
+}
+
+// First waypoint of wp_equally_spaced() for `path` without building the rest (find_current_lane,
+// lane_following_controller.py:367-374, only needs this one): the vehicle's projection on the
+// first lane point's heading line, or the lane point itself for a path of <= spacing points.
+__device__ void wp_first_point(const DMap& m, const int32_t* path, int n, double vx, double vy, double* x, double* y) {
+  int mm = 0;
+  for (int i = 0; i < n; ++i)
+    if (!(m.lp_inferred[path[i]] && 0 < i && i < n - 1)) ++mm;
+  const int lp0 = path[0];
+  const double lx = m.lp_x[lp0], ly = m.lp_y[lp0];
+  if ((double)mm <= m.lanepoint_spacing) {
+    *x = lx;
+    *y = ly;
+    return;
+  }
+  double hvx, hvy;
+  d_radians_to_vec(m.lp_heading[lp0], &hvx, &hvy);
+  const double proj = (vx - lx) * hvx + (vy - ly) * hvy;
+  *x = lx + proj * hvx;
+  *y = ly + proj * hvy;
 }
 
 // sumo_road_network.py:1312-1437, one path, executed by a single lane.  Calls emit(i, waypoint)
