@@ -33,8 +33,23 @@
 
 /* Python's float % for b > 0 (used by Heading.__new__, coordinates.py:175-181, and
  * min_angles_difference_signed, utils/math.py:447-449). fmod is exact in IEEE arithmetic. */
+/* fmod(a, b) for finite b > 0, bit-identical to the libm function: for |a| < 4b the quotient is
+ * 0..3 and every subtraction below is exact (Sterbenz: y/2 <= x <= 2y), so the result is the
+ * exact remainder that fmod returns -- without libm's iterative long division, which dominated
+ * the angle-wrapping-heavy controller code on the GPU.  Larger |a|, inf and NaN go to fmod. */
+SB_HD double sb_fmod_pos(double a, double b) {
+  double r = fabs(a);
+  if (r < b) return a;
+  if (r < 4.0 * b) {
+    if (r >= 2.0 * b) r -= 2.0 * b;
+    if (r >= b) r -= b;
+    return copysign(r, a);
+  }
+  return fmod(a, b);
+}
+
 SB_HD double sb_pymod(double a, double b) {
-  double m = fmod(a, b);
+  double m = sb_fmod_pos(a, b);
   if (m != 0.0 && m < 0.0) m += b;
   return m;
 }

@@ -22,6 +22,7 @@ struct SbHandle_ {
   LSector* d_ray_sectors = nullptr; // bounding sector of every 32 consecutive rays of that order
   float ray_reach = 0.f;
   std::vector<void*> allocs;
+  CtrlPick* d_picks = nullptr;  // k_control_paths -> k_control_law
   void* d_actions = nullptr;  // staging for sb_step_host
   size_t actions_cap = 0;
   double* d_social = nullptr;
@@ -250,6 +251,7 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
   if (ok && c.ogm_enable) ok = dev_alloc(h, &o.ogm, na * c.ogm_width * c.ogm_height, false);
   if (ok && c.dagm_enable) ok = dev_alloc(h, &o.dagm, na * c.dagm_width * c.dagm_height, false);
   if (!ok) return SB_ENOMEM;
+  if (!dev_alloc(h, &h->d_picks, na)) return SB_ENOMEM;
   if (!dev_alloc(h, &h->d_social, (size_t)d.E * (d.M ? d.M : 1) * 8)) return SB_ENOMEM;
   h->actions_cap = action_bytes(c);
   void* da = nullptr;
@@ -298,6 +300,19 @@ int sb_upload_map(SbHandle h, const SbMap* mp) {
   m.n_roads = mp->n_roads; m.n_lanes = mp->n_lanes; m.n_lanepoints = mp->n_lanepoints;
   m.n_shape_pts = mp->n_shape_pts; m.n_polys = mp->n_polys; m.n_poly_verts = mp->n_poly_verts;
   m.n_edges = mp->n_edges; m.lanepoint_spacing = mp->lanepoint_spacing;
+  {  // chained lane points?  (enables the lane-level path walk of sb_waypoints.cuh)
+    bool chained = true;
+    for (int l = 0; l < mp->n_lanes && chained; ++l) {
+      const int s0 = mp->lane_lp_start[l], cnt = mp->lane_lp_count[l];
+      for (int i = s0; i < s0 + cnt; ++i) {
+        if (mp->lp_lane[i] != l) chained = false;
+        if (i + 1 < s0 + cnt && !(mp->lp_next_start[i + 1] - mp->lp_next_start[i] == 1 &&
+                                  mp->lp_next[mp->lp_next_start[i]] == i + 1))
+          chained = false;
+      }
+    }
+    m.lp_chained = chained ? 1 : 0;
+  }
   // derived host tables: lane of every shape vertex; polygon AABBs (float, rounded outwards)
   std::vector<int32_t> shape_lane(mp->n_shape_pts);
   for (int l = 0; l < mp->n_lanes; ++l)
@@ -474,8 +489,11 @@ int sb_step(SbHandle h, const void* dev_actions, void* stream) {
   {
     LaunchScope ls(h, SB_K_CONTROL, st);
     if (c.action_space == SB_ACTION_LANE || c.action_space == SB_ACTION_LANE_WITH_CONTINUOUS_SPEED) {
-      k_control_lane<<<(na + SB_CTRL_GROUP - 1) / SB_CTRL_GROUP, SB_CTRL_WARPS * 32, 0, st>>>(c, h->dmap, h->st,
-                                                                                            dev_actions);
+      k_control_paths<<<(na + SB_CTRL_WARPS - 1) / SB_CTRL_WARPS, SB_CTRL_WARPS * 32, 0, st>>>(c, h->dmap, h->st,
+                                                                                             dev_actions, h->d_picks);
+      h->launches++;
+      k_control_law<<<(na + SB_CTRL_LAW_THREADS - 1) / SB_CTRL_LAW_THREADS, SB_CTRL_LAW_THREADS, 0, st>>>(
+          c, h->dmap, h->st, dev_actions, h->d_picks);
     } else {
       k_control_simple<<<(na + 127) / 128, 128, 0, st>>>(c, h->st, static_cast<const double*>(dev_actions));
     }

@@ -16,6 +16,7 @@
 // world-space AABBs of the drivable-area polygons for culling).
 struct DMap {
   int32_t n_roads, n_lanes, n_lanepoints, n_shape_pts, n_polys, n_poly_verts, n_edges;
+  int32_t lp_chained;  // every lane point but the last of its lane has the single successor index + 1
   double lanepoint_spacing;
   const int32_t *road_lane_start, *road_lane_count, *road_lp_start, *road_lp_count, *road_first_out;
   const uint8_t* road_is_junction;

@@ -1,7 +1,8 @@
 // sb_kernels.cuh -- the per-tick kernels.
 //
 //   k_set_social      BoxChassis.control for injected traffic             (chassis.py:211-217, :302-308)
-//   k_control_lane    Lane / LaneWithContinuousSpeed action path + chassis (warp per agent)
+//   k_control_paths   Lane / LaneWithContinuousSpeed: waypoint path search    (warp per agent)
+//   k_control_law     ... re-spacing, steering/throttle law, chassis           (thread per agent)
 //   k_control_simple  Trajectory / Continuous / ActuatorDynamic + chassis  (thread per agent)
 //   k_observe         ego lane, NeighborhoodVehicles, Waypoints            (warp per agent)
 //   k_lidar           LidarSensor ray casting                              (block per agent)
@@ -67,14 +68,14 @@ __global__ void k_set_social(DCfg c, DState s, const double* __restrict__ in) {
 }
 
 // --------------------------------------------------------------------------------- control
-// Two phases in one launch.  Phase A (warp per agent, 4 agents per warp in turn): the waypoint
-// path search -- strided argmin scans + branch enumeration -- and the choice of the lane to
-// follow; the chosen path's lane points go to shared memory.  Phase B (thread per agent): the
-// inherently serial part -- re-spacing of that one path, the steering / throttle law, the
-// substepped chassis -- so its ~10 k dependent instructions are issued once per agent instead of
-// once per warp with 31 lanes idle.
-#define SB_CTRL_WARPS 8
-#define SB_CTRL_GROUP 32  // agents per block
+// Lane / LaneWithContinuousSpeed in two launches.  k_control_paths (warp per agent): the
+// waypoint path search -- strided argmin scans, lane-level branch enumeration -- and the choice
+// of the lane to follow; the chosen path's lane points go to a small global record.
+// k_control_law (thread per agent): the inherently serial part -- re-spacing of that one path,
+// the steering / throttle law, the substepped chassis -- so its dependent instruction chain is
+// issued once per agent instead of once per warp with 31 lanes idle.
+#define SB_CTRL_WARPS 4
+#define SB_CTRL_LAW_THREADS 32
 #define SB_CTRL_LOOKAHEAD 16
 
 struct CtrlPick {
@@ -99,61 +100,58 @@ __device__ __forceinline__ void d_lane_action(const DCfg& c, const void* actions
 }
 
 __global__ void __launch_bounds__(SB_CTRL_WARPS * 32)
-k_control_lane(DCfg c, DMap m, DState s, const void* __restrict__ actions) {
+k_control_paths(DCfg c, DMap m, DState s, const void* __restrict__ actions, CtrlPick* __restrict__ picks) {
   __shared__ WarpPaths wps[SB_CTRL_WARPS];
-  __shared__ CtrlPick picks[SB_CTRL_GROUP];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int a0 = blockIdx.x * SB_CTRL_GROUP, na = c.E * c.A;
+  const int ai = blockIdx.x * SB_CTRL_WARPS + warp;
+  if (ai >= c.E * c.A) return;
   WarpPaths* wp = &wps[warp];
-  for (int g = warp; g < SB_CTRL_GROUP; g += SB_CTRL_WARPS) {  // phase A
-    const int ai = a0 + g;
-    if (ai >= na) break;
-    const int e = ai / c.A, a = ai - e * c.A, vi = e * c.V + a;
-    const double vx = s.pos_x[vi], vy = s.pos_y[vi], vh = s.heading[vi];
-    double ts;
-    int lc;
-    d_lane_action(c, actions, ai, &ts, &lc);
-    wp_waypoint_paths(m, vx, vy, vh, SB_CTRL_LOOKAHEAD, 5.0, s.route + (size_t)ai * c.route_cap, s.route_len[ai], wp,
-                      lane);
-    __syncwarp();
-    const int n = wp->n;
-    if (lane == 0) {
-      uint32_t bits = (wp->overflow ? SB_STATUS_PATH_OVERFLOW : 0u) | (n == 0 ? SB_STATUS_NO_WAYPOINTS : 0u);
-      if (bits) s.status[ai] |= bits;
-      if (n == 0) picks[g].len = 0;
-    }
-    if (n > 0) {
-      int rank = 0x7fffffff;
-      double d0 = 1e300;
-      if (lane < n) {  // find_current_lane, lane_following_controller.py:367-374
-        double fx, fy;
-        wp_first_point(m, wp->lp[lane], wp->len[lane], vx, vy, &fx, &fy);
-        rank = wp_rank(m, wp, lane);
-        double dx = fx - vx, dy = fy - vy;
-        d0 = sqrt(dx * dx + dy * dy);
-      }
-      double dmin = d0;
-      int cur = rank;
-      warp_argmin(dmin, cur);
-      int sel = cur + lc;
-      sel = sel < 0 ? 0 : (sel > n - 1 ? n - 1 : sel);
-      if (rank == sel) {
-        const int len = wp->len[lane];
-        picks[g].len = len;
-        for (int i = 0; i < len; ++i) picks[g].lp[i] = wp->lp[lane][i];
-      }
-    }
-    __syncwarp();
+  const int e = ai / c.A, a = ai - e * c.A, vi = e * c.V + a;
+  const double vx = s.pos_x[vi], vy = s.pos_y[vi], vh = s.heading[vi];
+  double ts;
+  int lc;
+  d_lane_action(c, actions, ai, &ts, &lc);
+  wp_waypoint_paths(m, vx, vy, vh, SB_CTRL_LOOKAHEAD, 5.0, s.route + (size_t)ai * c.route_cap, s.route_len[ai], wp,
+                    lane);
+  __syncwarp();
+  const int n = wp->n;
+  if (lane == 0) {
+    uint32_t bits = (wp->overflow ? SB_STATUS_PATH_OVERFLOW : 0u) | (n == 0 ? SB_STATUS_NO_WAYPOINTS : 0u);
+    if (bits) s.status[ai] |= bits;
+    if (n == 0) picks[ai].len = 0;
   }
-  __syncthreads();
-  if (threadIdx.x >= SB_CTRL_GROUP) return;
-  const int ai = a0 + threadIdx.x;  // phase B
-  if (ai >= na) return;
+  if (n == 0) return;
+  int rank = 0x7fffffff;
+  double d0 = 1e300;
+  if (lane < n) {  // find_current_lane, lane_following_controller.py:367-374
+    double fx, fy;
+    wp_first_point(m, wp->lp[lane], wp->len[lane], vx, vy, &fx, &fy);
+    rank = wp_rank(m, wp, lane);
+    double dx = fx - vx, dy = fy - vy;
+    d0 = sqrt(dx * dx + dy * dy);
+  }
+  double dmin = d0;
+  int cur = rank;
+  warp_argmin(dmin, cur);
+  int sel = cur + lc;
+  sel = sel < 0 ? 0 : (sel > n - 1 ? n - 1 : sel);
+  // the lane holding the selected path hands it to the others; all 32 write it out
+  const unsigned who = __ballot_sync(SB_FULL_MASK, rank == sel);
+  const int src = __ffs(who) - 1;
+  const int len = wp->len[src];
+  if (lane < len) picks[ai].lp[lane] = wp->lp[src][lane];
+  if (lane == 0) picks[ai].len = len;
+}
+
+__global__ void __launch_bounds__(SB_CTRL_LAW_THREADS)
+k_control_law(DCfg c, DMap m, DState s, const void* __restrict__ actions, const CtrlPick* __restrict__ picks) {
+  const int ai = blockIdx.x * SB_CTRL_LAW_THREADS + threadIdx.x;
+  if (ai >= c.E * c.A) return;
   const int e = ai / c.A, a = ai - e * c.A, vi = e * c.V + a;
   DEgo v{s.pos_x[vi], s.pos_y[vi], s.heading[vi], s.speed[vi], s.yaw_rate[vi], s.v_long[ai], s.v_lat[ai]};
   double* st = s.ctrl + (size_t)ai * SB_CTRL_STATE;
   double* out3 = s.last_control + (size_t)ai * 3;
-  const CtrlPick& pk = picks[threadIdx.x];
+  const CtrlPick& pk = picks[ai];
   if (pk.len == 0) {
     d_apply_control(v, 0, 0, 0, out3);
   } else {

@@ -16,6 +16,10 @@ struct WarpPaths {
   int32_t total;     // paths found
   int32_t overflow;  // more than SB_MAX_PATHS
   int32_t jr[2];     // junction route of _resolve_in_junction
+  // lane-level walk stack of wp_enumerate_chained (depth counts lanes, not lane points)
+  int32_t seg_first[SB_MAX_LOOKAHEAD + 1], seg_cnt[SB_MAX_LOOKAHEAD + 1], seg_before[SB_MAX_LOOKAHEAD + 1],
+      seg_cursor[SB_MAX_LOOKAHEAD + 1];
+  uint8_t seg_had[SB_MAX_LOOKAHEAD + 1];
 };
 
 struct DWaypoint {
@@ -156,6 +160,94 @@ __device__ void wp_enumerate_paths(const DMap& m, int start, int lookahead, cons
   }
 }
 
+// route filter of paths_starting_at_lanepoint (lanepoints.py:665-679) for a lane
+__device__ __forceinline__ bool wp_lane_ok(const DMap& m, const int32_t* filt, int nf, int nlane) {
+  const int road = m.lane_road[nlane];
+  if (!wp_in_route(filt, nf, road)) return false;
+  if (road == filt[nf - 1]) return true;
+  for (int o = m.lane_out_start[nlane]; o < m.lane_out_start[nlane + 1]; ++o)
+    if (wp_in_route(filt, nf, m.lane_road[m.lane_out[o]])) return true;
+  return false;
+}
+
+// Same enumeration on a "chained" map (every lane point but the last of its lane has exactly one
+// successor, the next index -- checked on the host at upload; true of every map built by
+// road_map.py): a path is a run of consecutive lane points per lane, so the walk branches per
+// LANE (2-4 steps for a 16 m lookahead) instead of per lane point.  Leaf order and leaf rule are
+// those of the point-level walk above.  Executed by the whole warp uniformly; the lanes share
+// the work of writing a path out.
+__device__ void wp_enumerate_chained(const DMap& m, int start, int lookahead, const int32_t* filt, int nf,
+                                     WarpPaths* wp, int lane) {
+  int n = wp->n, total = wp->total, overflow = wp->overflow;
+  const int need = lookahead + 1;
+  int d = 0;
+  bool entering = true;
+  wp->seg_first[0] = start;
+  wp->seg_before[0] = 0;
+  while (d >= 0) {
+    bool emit = false;
+    const int first = wp->seg_first[d], before = wp->seg_before[d];
+    if (entering) {
+      const int l = m.lp_lane[first];
+      const int avail = m.lane_lp_start[l] + m.lane_lp_count[l] - first;
+      int take = min(avail, need - before);
+      // the start lane itself is never filtered, but its next lane point (same lane) is
+      const bool blocked = d == 0 && nf > 0 && avail > 1 && need > 1 && !wp_lane_ok(m, filt, nf, l);
+      if (blocked) take = 1;
+      wp->seg_cnt[d] = take;
+      entering = false;
+      if (blocked || before + take == need) {
+        emit = true;
+      } else {
+        wp->seg_cursor[d] = m.lp_next_start[first + take - 1];
+        wp->seg_had[d] = 0;
+      }
+    }
+    if (!emit) {
+      const int cnt = wp->seg_cnt[d];
+      const int endc = m.lp_next_start[first + cnt];
+      int cur = wp->seg_cursor[d];
+      bool found = false;
+      while (cur < endc) {
+        const int child = m.lp_next[cur++];
+        if (nf > 0 && !wp_lane_ok(m, filt, nf, m.lp_lane[child])) continue;
+        found = true;
+        wp->seg_cursor[d] = cur;
+        wp->seg_had[d] = 1;
+        ++d;
+        wp->seg_first[d] = child;
+        wp->seg_before[d] = before + cnt;
+        entering = true;
+        break;
+      }
+      if (found) continue;
+      if (!wp->seg_had[d]) emit = true;
+    }
+    if (emit) {
+      ++total;
+      if (n < SB_MAX_PATHS) {
+        const int len = wp->seg_before[d] + wp->seg_cnt[d];
+        for (int j = lane; j < len; j += 32) {
+          int i = 0;
+          while (i < d && j >= wp->seg_before[i] + wp->seg_cnt[i]) ++i;
+          wp->lp[n][j] = wp->seg_first[i] + (j - wp->seg_before[i]);
+        }
+        if (lane == 0) wp->len[n] = len;
+        ++n;
+      } else {
+        overflow = 1;
+      }
+    }
+    --d;
+  }
+  __syncwarp();
+  if (lane == 0) {
+    wp->n = n;
+    wp->total = total;
+    wp->overflow = overflow;
+  }
+}
+
 // Lane._waypoint_paths_at for every lane of `road` (sumo_road_network.py:429-446, :838-839, :880-881)
 __device__ void wp_paths_on_road(const DMap& m, int road, double x, double y, int lookahead, const int32_t* filt,
                                  int nf, WarpPaths* wp, int lane) {
@@ -164,7 +256,11 @@ __device__ void wp_paths_on_road(const DMap& m, int road, double x, double y, in
     int cnt = m.lane_lp_count[l];
     if (cnt <= 0) continue;
     int lp = wp_closest_in_range(m, m.lane_lp_start[l], cnt, x, y, lane);
-    if (lane == 0) wp_enumerate_paths(m, lp, lookahead, filt, nf, wp);
+    if (m.lp_chained) {
+      wp_enumerate_chained(m, lp, lookahead, filt, nf, wp, lane);
+    } else if (lane == 0) {
+      wp_enumerate_paths(m, lp, lookahead, filt, nf, wp);
+    }
     __syncwarp();
   }
 }
