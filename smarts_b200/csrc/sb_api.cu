@@ -258,7 +258,7 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
   if (!cuda_ok(h, cudaMalloc(&da, h->actions_cap), "cudaMalloc(actions)")) return SB_ENOMEM;
   h->allocs.push_back(da);
   h->d_actions = da;
-  {  // k_raster shared memory: table | staging area, bit images aliased onto it when no grid is wider than 256
+  {  // k_raster shared memory: table | staging area | bit image 0 | bit image 1
     auto rows256 = [](int hh) { return (size_t)(hh < SB_RASTER_THREADS ? hh : SB_RASTER_THREADS); };
     size_t b0 = c.ogm_enable ? ((size_t)c.ogm_width / 32 + 1) * 4 * rows256(c.ogm_height) : 0;
     size_t b1 = c.dagm_enable ? ((size_t)c.dagm_width / 32 + 1) * 4 * rows256(c.dagm_height) : 0;
@@ -266,13 +266,9 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
     if (c.ogm_enable) wmax = c.ogm_width;
     if (c.dagm_enable && c.dagm_width > wmax) wmax = c.dagm_width;
     size_t stage = (sizeof(RasterStage) + 15) / 16 * 16;
-    if (wmax <= 256) {
-      h->raster_bits_off = SB_RASTER_LUT_BYTES;
-      h->raster_smem = SB_RASTER_LUT_BYTES + (stage > b0 + b1 ? stage : b0 + b1);
-    } else {
-      h->raster_bits_off = (int)(SB_RASTER_LUT_BYTES + stage);
-      h->raster_smem = SB_RASTER_LUT_BYTES + stage + b0 + b1;
-    }
+    (void)wmax;
+    h->raster_bits_off = (int)(SB_RASTER_LUT_BYTES + stage);
+    h->raster_smem = SB_RASTER_LUT_BYTES + stage + b0 + b1;
     if (h->raster_smem > 200 * 1024) return fail(h, SB_EINVAL, "grid too large for the shared-memory bit image");
     if (!cuda_ok(h, cudaFuncSetAttribute(k_raster, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->raster_smem),
                  "cudaFuncSetAttribute"))

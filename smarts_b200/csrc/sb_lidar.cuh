@@ -71,7 +71,7 @@ __device__ __forceinline__ bool d_sector_segment(const LSector& q, const LEdgeF&
 }
 
 // dynamic shared memory: double tbest[R]
-__global__ void __launch_bounds__(SB_LIDAR_THREADS)
+__global__ void __launch_bounds__(SB_LIDAR_THREADS, 4)
 k_lidar(DCfg c, DMap m, DState s, DObs o, const double* __restrict__ rays, const int32_t* __restrict__ order,
         const LSector* __restrict__ sectors, float reach_xy) {
   // reach_xy: longest horizontal extent of any table ray (+ margin), for the block-level cull
@@ -80,6 +80,7 @@ k_lidar(DCfg c, DMap m, DState s, DObs o, const double* __restrict__ rays, const
   __shared__ LBoxF boxf[SB_LIDAR_MAX_BOXES];
   __shared__ double edges[SB_LIDAR_MAX_EDGES][4];
   __shared__ LEdgeF edgef[SB_LIDAR_MAX_EDGES];
+  __shared__ float2 edged[SB_LIDAR_MAX_EDGES];
   __shared__ int n_boxes, n_edges;
   const int ai = blockIdx.x;
   const int e = ai / c.A, a = ai - e * c.A, vi = e * c.V + a;
@@ -90,40 +91,46 @@ k_lidar(DCfg c, DMap m, DState s, DObs o, const double* __restrict__ rays, const
     n_edges = 0;
   }
   __syncthreads();
-  // stage the env's other vehicles (order is irrelevant: the result is a minimum)
+  // stage the env's other vehicles (order is irrelevant: the result is a minimum); every field is
+  // loaded before the cull decision so that the block pays one round of global-load latency
   for (int j = threadIdx.x; j < c.V; j += blockDim.x) {
     const int vj = e * c.V + j;
-    if (j == a || !s.alive[vj]) continue;
+    const bool alive = s.alive[vj] != 0;
+    const double vx = s.pos_x[vj], vy = s.pos_y[vj], vz = s.pos_z[vj], vc = s.cos_h[vj], vs = s.sin_h[vj];
+    const double vw = s.width[vj], vl = s.length[vj], vhh = s.height[vj];
+    if (j == a || !alive) continue;
     // a hit lies within reach_xy of the origin and within the half diagonal of the box centre
-    const float bx = (float)(s.pos_x[vj] - ox), by = (float)(s.pos_y[vj] - oy);
-    const float fw = (float)s.width[vj], fl = (float)s.length[vj];
+    const float bx = (float)(vx - ox), by = (float)(vy - oy);
+    const float fw = (float)vw, fl = (float)vl;
     const float hd = 0.5f * sqrtf(fw * fw + fl * fl);
     const float lim = reach_xy + hd + 0.25f;
     if (bx * bx + by * by > lim * lim) continue;
     const int k = atomicAdd(&n_boxes, 1);
     if (k < SB_LIDAR_MAX_BOXES) {
-      const double z0 = s.pos_z[vj] + (j < c.A ? 0.1 : 0.2);
-      boxes[k] = LBox{s.pos_x[vj], s.pos_y[vj], s.cos_h[vj], s.sin_h[vj], 0.5 * s.width[vj], 0.5 * s.length[vj],
-                      z0,          z0 + s.height[vj]};
+      const double z0 = vz + (j < c.A ? 0.1 : 0.2);
+      boxes[k] = LBox{vx, vy, vc, vs, 0.5 * vw, 0.5 * vl, z0, z0 + vhh};
       boxf[k] = LBoxF{bx, by, hd * 1.0001f + SB_LIDAR_MARGIN, 0.f};
     }
   }
   if (c.lidar_wall_height > 0.0) {
-    // segments whose bounding circle reaches the disc
-    for (int k = threadIdx.x; k < m.n_edges; k += blockDim.x) {
-      const double* ed = m.road_edges + (size_t)k * 4;
-      const float ax = (float)(ed[0] - ox), ay = (float)(ed[1] - oy), bx = (float)(ed[2] - ox),
-                  by = (float)(ed[3] - oy);
+    // segments whose bounding circle reaches the disc; taken from the far end of the block so
+    // that they are staged by other warps than the vehicles, at the same time
+    for (int k = blockDim.x - 1 - threadIdx.x; k < m.n_edges; k += blockDim.x) {
+      const double4 ed = reinterpret_cast<const double4*>(m.road_edges)[k];
+      const float ax = (float)(ed.x - ox), ay = (float)(ed.y - oy), bx = (float)(ed.z - ox), by = (float)(ed.w - oy);
       const float mx = 0.5f * (ax + bx), my = 0.5f * (ay + by), hx = 0.5f * (bx - ax), hy = 0.5f * (by - ay);
-      const float reach = sqrtf(hx * hx + hy * hy) + reach_xy + 0.25f;
+      const float hl = sqrtf(hx * hx + hy * hy);
+      const float reach = hl + reach_xy + 0.25f;
       if (mx * mx + my * my > reach * reach) continue;
       const int q = atomicAdd(&n_edges, 1);
       if (q < SB_LIDAR_MAX_EDGES) {
-        edges[q][0] = ed[0];
-        edges[q][1] = ed[1];
-        edges[q][2] = ed[2];
-        edges[q][3] = ed[3];
+        edges[q][0] = ed.x;
+        edges[q][1] = ed.y;
+        edges[q][2] = ed.z;
+        edges[q][3] = ed.w;
         edgef[q] = LEdgeF{ax, ay, bx, by};
+        const float il = hl > 1e-12f ? 1.0f / hl : 0.f;  // unit direction (0 for a degenerate segment: no cull)
+        edged[q] = make_float2(hx * il, hy * il);
       }
     }
   }
@@ -199,10 +206,20 @@ k_lidar(DCfg c, DMap m, DState s, DObs o, const double* __restrict__ rays, const
         mask &= mask - 1;
         const LEdgeF f = edgef[k];
         if (!act) continue;
-        if (flat) {  // both end points strictly on one side of the ray's line
+        if (flat) {
+          // both end points strictly on one side of the ray's line
           const float s0 = ux * f.ay - uy * f.ax, s1 = ux * f.by - uy * f.bx;
           if ((s0 > SB_LIDAR_MARGIN && s1 > SB_LIDAR_MARGIN) || (s0 < -SB_LIDAR_MARGIN && s1 < -SB_LIDAR_MARGIN))
             continue;
+          // the ray meets the segment's line behind the origin or beyond its reach:
+          // distance along the ray = tn / dn (tn: origin-to-line distance, dn: sine of the angle)
+          const float2 ed = edged[k];
+          float tn = f.ax * ed.y - f.ay * ed.x, dn = ux * ed.y - uy * ed.x;
+          if (dn < 0.f) {
+            tn = -tn;
+            dn = -dn;
+          }
+          if ((ed.x != 0.f || ed.y != 0.f) && (tn < -SB_LIDAR_MARGIN || tn > len * dn + SB_LIDAR_MARGIN)) continue;
         }
         double ex = edges[k][2] - edges[k][0], ey = edges[k][3] - edges[k][1];
         double den = dx * ey - dy * ex;

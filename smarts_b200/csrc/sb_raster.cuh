@@ -33,6 +33,7 @@
 #define SB_RASTER_THREADS 256
 #define SB_RASTER_ROUND 64  // polygons staged per round (2 vertex / edge slots per thread)
 #define SB_RASTER_LIST (SB_RASTER_THREADS + SB_RASTER_ROUND)
+#define SB_RASTER_SMALL_ROWS 64  // polygons up to this many rows go warp-per-polygon, taller ones row-per-thread
 #define SB_RASTER_CLAMP 16777216.0        // 2^24 units = 65536 px
 #define SB_RASTER_FAST_LIMIT 536870912.0  // 2^29
 
@@ -53,13 +54,14 @@ struct Cam {
   double px, py, c, s, res, halfw, halfh;
 };
 
-// staging area; the bit images alias it once the last round's rows are done
+// staging area of one round of polygons
 struct RasterStage {
   REdgeI edges[SB_RASTER_ROUND][SB_MAX_POLY_VERTS];
-  int32_t U[SB_RASTER_ROUND][SB_MAX_POLY_VERTS], V[SB_RASTER_ROUND][SB_MAX_POLY_VERTS];
   RPolyI hdr[SB_RASTER_ROUND];
   int32_t list[SB_RASTER_LIST];
+  int32_t big[SB_RASTER_ROUND];  // staged polygons tall enough for the row-per-thread pass
   int32_t n_list;
+  int32_t n_big[2];  // by round parity: the other one is zeroed while a round is being rasterised
 };
 
 __device__ __forceinline__ void d_to_pixel(const Cam& cam, double x, double y, double* U, double* V) {
@@ -82,109 +84,108 @@ struct RasterJob {
   int n_src;
 };
 
-// vertex phase: slot = (list entry, vertex); world -> snapped pixel coordinates
-__device__ __forceinline__ void d_vertex_phase(const DCfg& c, const DMap& m, const DState& s, int e,
-                                               const RasterJob& job, RasterStage* st, int first, int count) {
+// Stage phase: slot = (list entry, vertex k).  The 8 slots of a polygon are 8 consecutive lanes of
+// one warp, so the polygon never leaves the register file: world -> snapped pixel coordinates
+// per lane, neighbour vertex / signed area / bounding box by shuffles inside the group of 8, then
+// each lane writes the record of edge k -> k+1 (integer edge function + 32.32 crossing line).
+__device__ __forceinline__ void d_stage_phase(const DCfg& c, const DMap& m, const DState& s, int e,
+                                              const RasterJob& job, RasterStage* st, int first, int count, int par) {
+  const int lane = threadIdx.x & 31, gbase = lane & ~7;
 #pragma unroll
   for (int it = 0; it < (SB_RASTER_ROUND * SB_MAX_POLY_VERTS) / SB_RASTER_THREADS; ++it) {
     const int slot = threadIdx.x + it * SB_RASTER_THREADS;
     const int li = slot / SB_MAX_POLY_VERTS, k = slot % SB_MAX_POLY_VERTS;
-    if (li >= count) continue;
-    const int src = st->list[first + li];
-    double x, y;
-    int n, img;
-    if (src < job.n_veh) {
-      img = 0;
-      n = 4;
-      if (k < 4) {
-        const int vj = e * c.V + src;
-        const double cc = s.cos_h[vj], ss = s.sin_h[vj];
-        const double hw = 0.5 * s.width[vj], hl = 0.5 * s.length[vj];
-        const double sa = (k == 1 || k == 2) ? hw : -hw, sb = (k >= 2) ? hl : -hl;
-        x = s.pos_x[vj] + (sa * cc - sb * ss);
-        y = s.pos_y[vj] + (sa * ss + sb * cc);
-      }
-    } else {
-      img = 1;
-      const int p = src - job.n_veh;
-      const int p0 = m.poly_start[p];
-      n = m.poly_start[p + 1] - p0;
-      if (k < n) {
-        x = m.poly_x[p0 + k];
-        y = m.poly_y[p0 + k];
+    int n = 0, img = 0;
+    double x = 0.0, y = 0.0;
+    if (li < count) {
+      const int src = st->list[first + li];
+      if (src < job.n_veh) {
+        n = 4;
+        if (k < 4) {
+          const int vj = e * c.V + src;
+          const double cc = s.cos_h[vj], ss = s.sin_h[vj];
+          const double hw = 0.5 * s.width[vj], hl = 0.5 * s.length[vj];
+          const double sa = (k == 1 || k == 2) ? hw : -hw, sb = (k >= 2) ? hl : -hl;
+          x = s.pos_x[vj] + (sa * cc - sb * ss);
+          y = s.pos_y[vj] + (sa * ss + sb * cc);
+        }
+      } else {
+        img = 1;
+        const int p = src - job.n_veh;
+        const int p0 = m.poly_start[p];
+        n = m.poly_start[p + 1] - p0;
+        if (k < n) {
+          x = m.poly_x[p0 + k];
+          y = m.poly_y[p0 + k];
+        }
       }
     }
+    int U = 0, V = 0;
     if (k < n) {
-      double U, V;
-      d_to_pixel(job.cam[img], x, y, &U, &V);
-      st->U[li][k] = (int32_t)U;
-      st->V[li][k] = (int32_t)V;
+      double Ud, Vd;
+      d_to_pixel(job.cam[img], x, y, &Ud, &Vd);
+      U = (int32_t)Ud;
+      V = (int32_t)Vd;
     }
-    if (k == 0) {
-      RPolyI P;
-      P.r0 = 1;
-      P.r1 = 0;
-      P.n = (uint8_t)n;
-      P.img = (uint8_t)img;
-      P.slow = 0;
-      P.pad = 0;
-      st->hdr[li] = P;
+    // lanes past the last vertex mirror vertex 0: neutral for min / max, zero area term
+    const int U0 = __shfl_sync(SB_FULL_MASK, U, gbase), V0 = __shfl_sync(SB_FULL_MASK, V, gbase);
+    if (k >= n) {
+      U = U0;
+      V = V0;
     }
-  }
-}
-
-// edge phase: slot = (list entry, edge k -> k+1); integer edge function + fixed-point crossing line
-__device__ __forceinline__ void d_edge_phase(const RasterJob& job, RasterStage* st, int count) {
+    const int nxt = (k + 1 >= n) ? gbase : lane + 1;
+    const int Uj = __shfl_sync(SB_FULL_MASK, U, nxt), Vj = __shfl_sync(SB_FULL_MASK, V, nxt);
+    long long area2 = (k < n) ? (long long)U * Vj - (long long)Uj * V : 0ll;
+    int umin = U, umax = U, vmin = V, vmax = V;
 #pragma unroll
-  for (int it = 0; it < (SB_RASTER_ROUND * SB_MAX_POLY_VERTS) / SB_RASTER_THREADS; ++it) {
-    const int slot = threadIdx.x + it * SB_RASTER_THREADS;
-    const int li = slot / SB_MAX_POLY_VERTS, k = slot % SB_MAX_POLY_VERTS;
-    if (li >= count) continue;
-    const int n = st->hdr[li].n, img = st->hdr[li].img;
-    if (k >= n) continue;
-    const int32_t* U = st->U[li];
-    const int32_t* V = st->V[li];
-    long long area2 = 0;
-    int umin = U[0], umax = U[0], vmin = V[0], vmax = V[0];
-    for (int i = 0; i < n; ++i) {
-      const int j = (i + 1 == n) ? 0 : i + 1;
-      area2 += (long long)U[i] * V[j] - (long long)U[j] * V[i];
-      umin = min(umin, U[i]);
-      umax = max(umax, U[i]);
-      vmin = min(vmin, V[i]);
-      vmax = max(vmax, V[i]);
+    for (int off = 1; off < 8; off <<= 1) {
+      area2 += __shfl_xor_sync(SB_FULL_MASK, area2, off);
+      umin = min(umin, __shfl_xor_sync(SB_FULL_MASK, umin, off));
+      umax = max(umax, __shfl_xor_sync(SB_FULL_MASK, umax, off));
+      vmin = min(vmin, __shfl_xor_sync(SB_FULL_MASK, vmin, off));
+      vmax = max(vmax, __shfl_xor_sync(SB_FULL_MASK, vmax, off));
     }
     const int W = job.W[img], H = job.H[img];
     int r0 = (vmin - 128 + 255) >> 8, r1 = (vmax - 128) >> 8;  // rows with vmin <= 256r+128 <= vmax
     const int c0 = (umin - 128 + 255) >> 8, c1 = (umax - 128) >> 8;
     r0 = max(r0, 0);
     r1 = min(r1, H - 1);
-    const bool valid = area2 != 0 && r0 <= r1 && c1 >= 0 && c0 <= W - 1;
-    if (k == 0 && valid) {
-      st->hdr[li].r0 = (int16_t)r0;
-      st->hdr[li].r1 = (int16_t)r1;
-    }
-    if (!valid) continue;
-    const int sg = area2 > 0 ? 1 : -1;
-    const int j = (k + 1 == n) ? 0 : k + 1;
-    const int dxe = U[j] - U[k], dye = V[j] - V[k];
-    REdgeI q;
-    q.A = -sg * dye;
-    q.D = sg * dxe;
-    q.B0 = (long long)sg * ((long long)dxe * (128 - V[k]) + (long long)dye * U[k]);
-    q.e0 = 0;
-    q.ek = 0;
-    if (q.A != 0) {
-      const double A = (double)q.A;
-      const double e0 = -((double)(q.B0 + 128ll * q.A)) / (256.0 * A), ek = -(double)q.D / A;
-      if (fabs(e0) + fabs(ek) * (double)H < SB_RASTER_FAST_LIMIT) {
-        q.e0 = __double2ll_rn((e0 + 0.5) * 4294967296.0);
-        q.ek = __double2ll_rn(ek * 4294967296.0);
-      } else {
-        st->hdr[li].slow = 1;
+    const bool valid = li < count && n >= 3 && area2 != 0 && r0 <= r1 && c1 >= 0 && c0 <= W - 1;
+    bool slow = false;
+    if (valid && k < n) {
+      const int sg = area2 > 0 ? 1 : -1;
+      const int dxe = Uj - U, dye = Vj - V;
+      REdgeI q;
+      q.A = -sg * dye;
+      q.D = sg * dxe;
+      q.B0 = (long long)sg * ((long long)dxe * (128 - V) + (long long)dye * U);
+      q.e0 = 0;
+      q.ek = 0;
+      if (q.A != 0) {
+        const double A = (double)q.A;
+        const double e0 = -((double)(q.B0 + 128ll * q.A)) / (256.0 * A), ek = -(double)q.D / A;
+        if (fabs(e0) + fabs(ek) * (double)H < SB_RASTER_FAST_LIMIT) {
+          q.e0 = __double2ll_rn((e0 + 0.5) * 4294967296.0);
+          q.ek = __double2ll_rn(ek * 4294967296.0);
+        } else {
+          slow = true;
+        }
       }
+      st->edges[li][k] = q;
     }
-    st->edges[li][k] = q;
+    // any edge of the polygon on the exact-division path puts the whole polygon there
+    const unsigned slow_mask = __ballot_sync(SB_FULL_MASK, slow);
+    if (k == 0 && li < count) {
+      RPolyI P;
+      P.r0 = (int16_t)(valid ? r0 : 1);
+      P.r1 = (int16_t)(valid ? r1 : 0);
+      P.n = (uint8_t)n;
+      P.img = (uint8_t)img;
+      P.slow = (uint8_t)(((slow_mask >> gbase) & 0xffu) != 0u);
+      P.pad = 0;
+      st->hdr[li] = P;
+      if (valid && r1 - r0 + 1 > SB_RASTER_SMALL_ROWS) st->big[atomicAdd(&st->n_big[par], 1)] = li;
+    }
   }
 }
 
@@ -234,10 +235,13 @@ __device__ __forceinline__ void d_or_span(uint32_t (&w)[8], int lo, int hi1) {
   for (int j = 0; j < 8; ++j) w[j] |= d_ones_below(hi1 - 32 * j) & ~d_ones_below(lo - 32 * j);
 }
 
-// OR the staged polygons' spans on row `r` (columns [cb, cb+256)) into the row's bit words.
-__device__ __forceinline__ void d_row_spans(const RasterJob& job, const RasterStage* st, int np, int r, int cb,
-                                            uint32_t (&w0)[8], uint32_t (&w1)[8]) {
-  for (int p = 0; p < np; ++p) {
+// Tall polygons: OR their spans on row `r` (columns [cb, cb+256)) into the row's bit words held
+// in registers (every thread owns a row: no atomics).
+__device__ __forceinline__ void d_big_rows(const RasterJob& job, const RasterStage* st, int par, int r, int cb,
+                                           uint32_t (&w0)[8], uint32_t (&w1)[8]) {
+  const int nbig = st->n_big[par];
+  for (int i = 0; i < nbig; ++i) {
+    const int p = st->big[i];
     const RPolyI P = st->hdr[p];
     if (r < P.r0 || r > P.r1) continue;
     int c0, c1;
@@ -246,6 +250,34 @@ __device__ __forceinline__ void d_row_spans(const RasterJob& job, const RasterSt
     if (lo >= hi1) continue;
     if (P.img == 0) d_or_span(w0, lo, hi1);  // warp-uniform
     else d_or_span(w1, lo, hi1);
+  }
+}
+
+// Short polygons (vehicles, junction slivers): one warp per polygon, lane = row, the span goes
+// into the shared-memory bit image with atomicOr (1-2 words for a vehicle).  Rows [rg, rg+rows),
+// columns [cb, cb+256).
+__device__ __forceinline__ void d_small_polys(const RasterJob& job, const RasterStage* st, int count, int rg, int cb,
+                                              uint32_t* bits0, uint32_t* bits1, int stride0, int stride1) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int p = warp; p < count; p += SB_RASTER_THREADS / 32) {
+    const RPolyI P = st->hdr[p];
+    if (P.r1 < P.r0 || P.r1 - P.r0 + 1 > SB_RASTER_SMALL_ROWS) continue;
+    uint32_t* bits = P.img == 0 ? bits0 : bits1;
+    const int stride = P.img == 0 ? stride0 : stride1, W = job.W[P.img];
+    const int rlo = max((int)P.r0, rg), rhi = min((int)P.r1, rg + SB_RASTER_THREADS - 1);
+    for (int r = rlo + lane; r <= rhi; r += 32) {
+      int c0, c1;
+      d_poly_span(st, p, P, r, W, &c0, &c1);
+      c0 = max(c0, cb);
+      c1 = min(c1, cb + 255);
+      if (c0 > c1) continue;
+      uint32_t* row = bits + (r - rg) * stride;
+      const int j0 = c0 >> 5, j1 = c1 >> 5;
+      for (int j = j0; j <= j1; ++j) {
+        const uint32_t mk = d_ones_below(c1 + 1 - 32 * j) & ~d_ones_below(c0 - 32 * j);
+        atomicOr(&row[j], mk);
+      }
+    }
   }
 }
 
@@ -274,10 +306,9 @@ __device__ __forceinline__ void d_store_rows(const uint32_t* bits, const uint2* 
 
 #define SB_RASTER_LUT_BYTES 2048
 
-// Dynamic shared memory: [byte-expansion table | staging area], and the two bit images at
-// `bits_off` -- on top of the staging area when no grid is wider than 256 (they are written only
-// after the last rows pass), behind it otherwise.  Sized by sb_raster_smem_bytes() in sb_api.cu.
-__global__ void __launch_bounds__(SB_RASTER_THREADS, 4) k_raster(DCfg c, DMap m, DState s, DObs o, int bits_off) {
+// Dynamic shared memory: [byte-expansion table | staging area | bit image 0 | bit image 1]
+// (bit images: min(H, 256) rows of W/32 + 1 words).  Sized by sb_create in sb_api.cu.
+__global__ void __launch_bounds__(SB_RASTER_THREADS, 5) k_raster(DCfg c, DMap m, DState s, DObs o, int bits_off) {
   extern __shared__ __align__(16) unsigned char smem[];
   uint2* lut = reinterpret_cast<uint2*>(smem);
   RasterStage* st = reinterpret_cast<RasterStage*>(smem + SB_RASTER_LUT_BYTES);
@@ -300,7 +331,6 @@ __global__ void __launch_bounds__(SB_RASTER_THREADS, 4) k_raster(DCfg c, DMap m,
     j.n_veh = j.on[0] ? c.V : 0;
     j.n_src = j.n_veh + (j.on[1] ? m.n_polys : 0);
   }
-  __syncthreads();
   const RasterJob& job = sjob;
   const int W0 = c.ogm_enable ? c.ogm_w : 0, H0 = c.ogm_enable ? c.ogm_h : 0;
   const int W1 = c.dagm_enable ? c.dagm_w : 0, H1 = c.dagm_enable ? c.dagm_h : 0;
@@ -310,6 +340,7 @@ __global__ void __launch_bounds__(SB_RASTER_THREADS, 4) k_raster(DCfg c, DMap m,
   const int rows0 = min(H0, SB_RASTER_THREADS), rows1 = min(H1, SB_RASTER_THREADS);
   uint32_t* bits0 = reinterpret_cast<uint32_t*>(smem + bits_off);
   uint32_t* bits1 = bits0 + rows0 * (wpr0 + 1);
+  const int n_bit_words = rows0 * (wpr0 + 1) + rows1 * (wpr1 + 1);
   // conservative world-space cull radii: the film's half diagonal + 1 m
   const float rad0 = 0.5f * (float)c.ogm_res * sqrtf((float)W0 * W0 + (float)H0 * H0) + 1.0f;
   const float rad1 = 0.5f * (float)c.dagm_res * sqrtf((float)W1 * W1 + (float)H1 * H1) + 1.0f;
@@ -318,21 +349,25 @@ __global__ void __launch_bounds__(SB_RASTER_THREADS, 4) k_raster(DCfg c, DMap m,
 
   for (int rg = 0; rg < Hmax; rg += SB_RASTER_THREADS) {
     const int r = rg + threadIdx.x;
+    for (int i = threadIdx.x; i < n_bit_words; i += SB_RASTER_THREADS) bits0[i] = 0u;
     for (int cb = 0; cb < Wmax; cb += 256) {
       uint32_t w0[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u}, w1[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
-      if (threadIdx.x == 0) st->n_list = 0;
+      if (threadIdx.x == 0) {
+        st->n_list = 0;
+        st->n_big[0] = 0;
+      }
       __syncthreads();
+      int par = 0;
       for (int base = 0; base < n_src; base += SB_RASTER_THREADS) {
         const int p = base + threadIdx.x;
         bool keep = false;
         if (p < n_veh) {
           const int vj = e * c.V + p;
-          if (s.alive[vj]) {
-            const float dx = (float)s.pos_x[vj] - fx, dy = (float)s.pos_y[vj] - fy;
-            const float fl = (float)s.length[vj], fw = (float)s.width[vj];
-            const float lim = rad0 + 0.5f * sqrtf(fl * fl + fw * fw) + 0.5f;
-            keep = dx * dx + dy * dy <= lim * lim;
-          }
+          const bool alive = s.alive[vj] != 0;  // every field loaded up front: one round of load latency
+          const float dx = (float)s.pos_x[vj] - fx, dy = (float)s.pos_y[vj] - fy;
+          const float fl = (float)s.length[vj], fw = (float)s.width[vj];
+          const float lim = rad0 + 0.5f * sqrtf(fl * fl + fw * fw) + 0.5f;
+          keep = alive && dx * dx + dy * dy <= lim * lim;
         } else if (p < n_src) {
           const int q = p - n_veh;
           const float4 bb = reinterpret_cast<const float4*>(m.poly_bbox)[q];
@@ -347,40 +382,43 @@ __global__ void __launch_bounds__(SB_RASTER_THREADS, 4) k_raster(DCfg c, DMap m,
         int n_list = st->n_list;
         while (n_list >= SB_RASTER_ROUND || (last && n_list > 0)) {
           const int count = min(n_list, SB_RASTER_ROUND);
-          d_vertex_phase(c, m, s, e, job, st, n_list - count, count);
+          d_stage_phase(c, m, s, e, job, st, n_list - count, count, par);
           __syncthreads();
-          d_edge_phase(job, st, count);
-          __syncthreads();
-          d_row_spans(job, st, count, r, cb, w0, w1);
+          if (threadIdx.x == 0) st->n_big[par ^ 1] = 0;
+          d_small_polys(job, st, count, rg, cb, bits0, bits1, wpr0 + 1, wpr1 + 1);
+          d_big_rows(job, st, par, r, cb, w0, w1);
           n_list -= count;
+          par ^= 1;
           __syncthreads();
         }
-        if (threadIdx.x == 0) st->n_list = n_list;
-        __syncthreads();
+        if (!last) {  // carry the remainder over to the next cull pass
+          if (threadIdx.x == 0) st->n_list = n_list;
+          __syncthreads();
+        }
       }
-      // every thread is past the last rows pass: the staging area may now be overwritten
+      // merge the register rows of the tall polygons (all atomics are behind the last barrier)
       if (r < H0 && cb < W0) {
         uint32_t* row = bits0 + threadIdx.x * (wpr0 + 1) + (cb >> 5);
         const int nw = min(8, wpr0 - (cb >> 5));
 #pragma unroll
         for (int k = 0; k < 8; ++k)
-          if (k < nw) row[k] = w0[k];
+          if (k < nw && w0[k]) row[k] |= w0[k];
       }
       if (r < H1 && cb < W1) {
         uint32_t* row = bits1 + threadIdx.x * (wpr1 + 1) + (cb >> 5);
         const int nw = min(8, wpr1 - (cb >> 5));
 #pragma unroll
         for (int k = 0; k < 8; ++k)
-          if (k < nw) row[k] = w1[k];
+          if (k < nw && w1[k]) row[k] |= w1[k];
       }
     }
     __syncthreads();
     if (rg < H0)
-      d_store_rows(bits0, lut, o.ogm + (size_t)ai * W0 * H0 + (size_t)rg * W0,
-                   min(H0 - rg, SB_RASTER_THREADS), wpr0, wpr0 + 1);
+      d_store_rows(bits0, lut, o.ogm + (size_t)ai * W0 * H0 + (size_t)rg * W0, min(H0 - rg, SB_RASTER_THREADS), wpr0,
+                   wpr0 + 1);
     if (rg < H1)
-      d_store_rows(bits1, lut, o.dagm + (size_t)ai * W1 * H1 + (size_t)rg * W1,
-                   min(H1 - rg, SB_RASTER_THREADS), wpr1, wpr1 + 1);
-    __syncthreads();
+      d_store_rows(bits1, lut, o.dagm + (size_t)ai * W1 * H1 + (size_t)rg * W1, min(H1 - rg, SB_RASTER_THREADS), wpr1,
+                   wpr1 + 1);
+    if (rg + SB_RASTER_THREADS < Hmax) __syncthreads();
   }
 }
