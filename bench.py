@@ -209,6 +209,8 @@ def main():
     ap.add_argument("--envs", type=int, default=0, help="override envs per GPU")
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-kernel-timing", action="store_true",
+                    help="do not bracket every kernel with CUDA events inside the timed region (no roofline object)")
     args = ap.parse_args()
     w = dict(WORKLOADS[args.workload])
     if args.envs:
@@ -250,7 +252,7 @@ def main():
         dist.barrier()
     torch.cuda.synchronize()
     sampler.start()
-    eng.set_timing(True)
+    eng.set_timing(not args.no_kernel_timing)
     l0 = eng.launch_count
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
@@ -311,7 +313,7 @@ def main():
             per_launch = raster_bytes_per_agent(cfg, A + M) * E * A
         else:
             per_launch = algorithmic_bytes_per_agent_step(cfg, M, A) * E * A
-        achieved = per_launch / (d_ms / max(d_n, 1) * 1e-3) / 1e9
+        achieved = per_launch / (d_ms / d_n * 1e-3) / 1e9 if d_n and d_ms > 0 else float('nan')
         step_bytes = algorithmic_bytes_per_agent_step(cfg, M, A)
         step_gbs = step_bytes * (E * A * K) / (ms * 1e-3) / 1e9  # this rank's share (weak scaling: per GPU)
         line = {

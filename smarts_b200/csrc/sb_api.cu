@@ -2,6 +2,7 @@
 // Compiled for sm_100a only (-gencode arch=compute_100a,code=sm_100a -fmad=false).  There is no
 // CPU path in this library: every entry point that computes launches CUDA kernels.
 #include <cstdio>
+#include <cstdlib>
 #include <algorithm>
 #include <cmath>
 #include <cstring>
@@ -36,7 +37,7 @@ struct SbHandle_ {
   int cuda_err = 0;
   std::string err;
   size_t raster_smem = 0;
-  int raster_bits_off = 0;
+  RasterDims raster_dims{};
 };
 
 namespace {
@@ -267,8 +268,22 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
     if (c.dagm_enable && c.dagm_width > wmax) wmax = c.dagm_width;
     size_t stage = (sizeof(RasterStage) + 15) / 16 * 16;
     (void)wmax;
-    h->raster_bits_off = (int)(SB_RASTER_LUT_BYTES + stage);
     h->raster_smem = SB_RASTER_LUT_BYTES + stage + b0 + b1;
+    RasterDims& g = h->raster_dims;
+    g.W0 = c.ogm_enable ? c.ogm_width : 0;
+    g.H0 = c.ogm_enable ? c.ogm_height : 0;
+    g.W1 = c.dagm_enable ? c.dagm_width : 0;
+    g.H1 = c.dagm_enable ? c.dagm_height : 0;
+    g.wpr0 = g.W0 / 32;
+    g.wpr1 = g.W1 / 32;
+    g.rows0 = (int)rows256(g.H0);
+    g.rows1 = (int)rows256(g.H1);
+    g.n_veh = c.ogm_enable ? d.V : 0;
+    g.n_src = g.n_veh;  // + map polygons once the map is uploaded (sb_upload_map)
+    g.bits_off = (int)(SB_RASTER_LUT_BYTES + stage);
+    g.n_bit_words = g.rows0 * (g.wpr0 + 1) + g.rows1 * (g.wpr1 + 1);
+    g.rad0 = 0.5f * (float)c.ogm_resolution * sqrtf((float)g.W0 * g.W0 + (float)g.H0 * g.H0) + 1.0f;
+    g.rad1 = 0.5f * (float)c.dagm_resolution * sqrtf((float)g.W1 * g.W1 + (float)g.H1 * g.H1) + 1.0f;
     if (h->raster_smem > 200 * 1024) return fail(h, SB_EINVAL, "grid too large for the shared-memory bit image");
     if (!cuda_ok(h, cudaFuncSetAttribute(k_raster, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->raster_smem),
                  "cudaFuncSetAttribute"))
@@ -355,6 +370,7 @@ int sb_upload_map(SbHandle h, const SbMap* mp) {
             dev_upload(h, &m.poly_bbox, bbox.data(), bbox.size()) &&
             dev_upload(h, &m.road_edges, mp->road_edges, (size_t)mp->n_edges * 4);
   if (!ok) return SB_ECUDA;
+  h->raster_dims.n_src = h->raster_dims.n_veh + (h->cfg.dagm_enable ? mp->n_polys : 0);
   h->have_map = true;
   return SB_OK;
 }
@@ -516,7 +532,7 @@ int sb_observe(SbHandle h, void* stream) {
   }
   if (c.ogm_enable || c.dagm_enable) {
     LaunchScope ls(h, SB_K_RASTER, st);
-    k_raster<<<na, SB_RASTER_THREADS, h->raster_smem, st>>>(c, h->dmap, h->st, h->ob, h->raster_bits_off);
+    k_raster<<<na, SB_RASTER_THREADS, h->raster_smem, st>>>(c, h->dmap, h->st, h->ob, h->raster_dims);
   }
   return cuda_ok(h, cudaGetLastError(), "k_observe") ? SB_OK : SB_ECUDA;
 }

@@ -31,7 +31,7 @@
 #include "sb_device.cuh"
 
 #define SB_RASTER_THREADS 256
-#define SB_RASTER_ROUND 64  // polygons staged per round (2 vertex / edge slots per thread)
+#define SB_RASTER_ROUND 96  // polygons staged per round: one round in the common case
 #define SB_RASTER_LIST (SB_RASTER_THREADS + SB_RASTER_ROUND)
 #define SB_RASTER_SMALL_ROWS 64  // polygons up to this many rows go warp-per-polygon, taller ones row-per-thread
 #define SB_RASTER_CLAMP 16777216.0        // 2^24 units = 65536 px
@@ -54,14 +54,27 @@ struct Cam {
   double px, py, c, s, res, halfw, halfh;
 };
 
+// Grid geometry, derived once on the host (sb_create) and passed by value: plain constant-bank
+// operands in the kernel instead of selects on the config re-evaluated inside its loops.
+struct RasterDims {
+  int32_t W0, H0, W1, H1;        // 0 when the grid is disabled
+  int32_t wpr0, wpr1;            // 32-pixel words per row
+  int32_t rows0, rows1;          // rows per pass: min(H, 256)
+  int32_t n_veh, n_src;          // OGM sources (vehicle slots), all sources (+ map polygons)
+  int32_t bits_off, n_bit_words; // byte offset of bit image 0 in dynamic shared memory; words of both images
+  float rad0, rad1;              // world-space cull radii: the film's half diagonal + 1 m
+};
+
 // staging area of one round of polygons
 struct RasterStage {
   REdgeI edges[SB_RASTER_ROUND][SB_MAX_POLY_VERTS];
   RPolyI hdr[SB_RASTER_ROUND];
   int32_t list[SB_RASTER_LIST];
   int32_t big[SB_RASTER_ROUND];  // staged polygons tall enough for the row-per-thread pass
+  int32_t pre[SB_RASTER_ROUND + 1];  // exclusive prefix of the short polygons' row counts ((polygon, row) pairs)
   int32_t n_list;
   int32_t n_big[2];  // by round parity: the other one is zeroed while a round is being rasterised
+  int32_t wide;      // a kept polygon has more than 4 vertices: stage with 8 lanes per polygon instead of 4
 };
 
 __device__ __forceinline__ void d_to_pixel(const Cam& cam, double x, double y, double* U, double* V) {
@@ -84,17 +97,18 @@ struct RasterJob {
   int n_src;
 };
 
-// Stage phase: slot = (list entry, vertex k).  The 8 slots of a polygon are 8 consecutive lanes of
-// one warp, so the polygon never leaves the register file: world -> snapped pixel coordinates
+// Stage phase: slot = (list entry, vertex k).  The G slots of a polygon (4 when every kept polygon
+// has at most 4 vertices -- vehicles, and the maps built by road_map.py -- else 8) are G
+// consecutive lanes of one warp, so the polygon never leaves the register file: world -> snapped pixel coordinates
 // per lane, neighbour vertex / signed area / bounding box by shuffles inside the group of 8, then
 // each lane writes the record of edge k -> k+1 (integer edge function + 32.32 crossing line).
+template <int G>
 __device__ __forceinline__ void d_stage_phase(const DCfg& c, const DMap& m, const DState& s, int e,
                                               const RasterJob& job, RasterStage* st, int first, int count, int par) {
-  const int lane = threadIdx.x & 31, gbase = lane & ~7;
-#pragma unroll
-  for (int it = 0; it < (SB_RASTER_ROUND * SB_MAX_POLY_VERTS) / SB_RASTER_THREADS; ++it) {
+  const int lane = threadIdx.x & 31, gbase = lane & ~(G - 1);
+  for (int it = 0; it * SB_RASTER_THREADS < count * G; ++it) {
     const int slot = threadIdx.x + it * SB_RASTER_THREADS;
-    const int li = slot / SB_MAX_POLY_VERTS, k = slot % SB_MAX_POLY_VERTS;
+    const int li = slot / G, k = slot % G;
     int n = 0, img = 0;
     double x = 0.0, y = 0.0;
     if (li < count) {
@@ -138,7 +152,7 @@ __device__ __forceinline__ void d_stage_phase(const DCfg& c, const DMap& m, cons
     long long area2 = (k < n) ? (long long)U * Vj - (long long)Uj * V : 0ll;
     int umin = U, umax = U, vmin = V, vmax = V;
 #pragma unroll
-    for (int off = 1; off < 8; off <<= 1) {
+    for (int off = 1; off < G; off <<= 1) {
       area2 += __shfl_xor_sync(SB_FULL_MASK, area2, off);
       umin = min(umin, __shfl_xor_sync(SB_FULL_MASK, umin, off));
       umax = max(umax, __shfl_xor_sync(SB_FULL_MASK, umax, off));
@@ -181,7 +195,7 @@ __device__ __forceinline__ void d_stage_phase(const DCfg& c, const DMap& m, cons
       P.r1 = (int16_t)(valid ? r1 : 0);
       P.n = (uint8_t)n;
       P.img = (uint8_t)img;
-      P.slow = (uint8_t)(((slow_mask >> gbase) & 0xffu) != 0u);
+      P.slow = (uint8_t)(((slow_mask >> gbase) & ((1u << G) - 1u)) != 0u);
       P.pad = 0;
       st->hdr[li] = P;
       if (valid && r1 - r0 + 1 > SB_RASTER_SMALL_ROWS) st->big[atomicAdd(&st->n_big[par], 1)] = li;
@@ -236,13 +250,16 @@ __device__ __forceinline__ void d_or_span(uint32_t (&w)[8], int lo, int hi1) {
 }
 
 // Tall polygons: OR their spans on row `r` (columns [cb, cb+256)) into the row's bit words held
-// in registers (every thread owns a row: no atomics).
-__device__ __forceinline__ void d_big_rows(const RasterJob& job, const RasterStage* st, int par, int r, int cb,
-                                           uint32_t (&w0)[8], uint32_t (&w1)[8]) {
+// in registers (every thread owns a row: no atomics).  Returns the images touched (bit per image;
+// uniform over the block).
+__device__ __forceinline__ int d_big_rows(const RasterJob& job, const RasterStage* st, int par, int r, int cb,
+                                          uint32_t (&w0)[8], uint32_t (&w1)[8]) {
   const int nbig = st->n_big[par];
+  int touched = 0;
   for (int i = 0; i < nbig; ++i) {
     const int p = st->big[i];
     const RPolyI P = st->hdr[p];
+    touched |= 1 << P.img;
     if (r < P.r0 || r > P.r1) continue;
     int c0, c1;
     d_poly_span(st, p, P, r, job.W[P.img], &c0, &c1);
@@ -251,33 +268,68 @@ __device__ __forceinline__ void d_big_rows(const RasterJob& job, const RasterSta
     if (P.img == 0) d_or_span(w0, lo, hi1);  // warp-uniform
     else d_or_span(w1, lo, hi1);
   }
+  return touched;
 }
 
-// Short polygons (vehicles, junction slivers): one warp per polygon, lane = row, the span goes
-// into the shared-memory bit image with atomicOr (1-2 words for a vehicle).  Rows [rg, rg+rows),
-// columns [cb, cb+256).
-__device__ __forceinline__ void d_small_polys(const RasterJob& job, const RasterStage* st, int count, int rg, int cb,
+// Short polygons (vehicles, junction slivers) are flattened into (polygon, row) pairs so that
+// every lane has a row to do: each warp builds the exclusive prefix of the row counts (all warps
+// write the same values: no block barrier), takes a contiguous chunk of the pairs and walks the
+// prefix forward as its pair index grows.  A span goes into the shared-memory bit image with
+// atomicOr (1-2 words for a vehicle).  Rows [rg, rg+256), columns [cb, cb+256).
+__device__ __forceinline__ void d_small_pairs(const RasterJob& job, RasterStage* st, int count, int rg, int cb,
                                               uint32_t* bits0, uint32_t* bits1, int stride0, int stride1) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int p = warp; p < count; p += SB_RASTER_THREADS / 32) {
-    const RPolyI P = st->hdr[p];
-    if (P.r1 < P.r0 || P.r1 - P.r0 + 1 > SB_RASTER_SMALL_ROWS) continue;
-    uint32_t* bits = P.img == 0 ? bits0 : bits1;
-    const int stride = P.img == 0 ? stride0 : stride1, W = job.W[P.img];
-    const int rlo = max((int)P.r0, rg), rhi = min((int)P.r1, rg + SB_RASTER_THREADS - 1);
-    for (int r = rlo + lane; r <= rhi; r += 32) {
+  int total = 0;
+  for (int b = 0; b < count; b += 32) {
+    const int li = b + lane;
+    int rows = 0;
+    if (li < count) {
+      const RPolyI P = st->hdr[li];
+      if (P.r1 >= P.r0 && P.r1 - P.r0 + 1 <= SB_RASTER_SMALL_ROWS)
+        rows = max(min((int)P.r1, rg + SB_RASTER_THREADS - 1) - max((int)P.r0, rg) + 1, 0);
+    }
+    int inc = rows;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const int t = __shfl_up_sync(SB_FULL_MASK, inc, off);
+      if (lane >= off) inc += t;
+    }
+    if (li < count) st->pre[li] = total + inc - rows;
+    total += __shfl_sync(SB_FULL_MASK, inc, 31);
+  }
+  if (lane == 0) st->pre[count] = total;
+  __syncwarp();
+  if (total == 0) return;
+  const int chunk = (((total + SB_RASTER_THREADS / 32 - 1) / (SB_RASTER_THREADS / 32)) + 31) & ~31;
+  const int t_begin = warp * chunk, t_end = min(total, t_begin + chunk);
+  if (t_begin >= t_end) return;
+  int cursor = 0;  // largest li with pre[li] <= t_begin
+  for (int step = 64; step >= 1; step >>= 1) {
+    const int q = cursor + step;
+    if (q < count && st->pre[q] <= t_begin) cursor = q;
+  }
+  for (int t0 = t_begin; t0 < t_end; t0 += 32) {
+    const int t = t0 + lane;
+    const bool act = t < t_end;
+    int li = cursor;
+    if (act) {
+      while (st->pre[li + 1] <= t) ++li;  // t < total = pre[count]: stops at li <= count - 1
+      const RPolyI P = st->hdr[li];
+      const int r = max((int)P.r0, rg) + (t - st->pre[li]);
       int c0, c1;
-      d_poly_span(st, p, P, r, W, &c0, &c1);
+      d_poly_span(st, li, P, r, job.W[P.img], &c0, &c1);
       c0 = max(c0, cb);
       c1 = min(c1, cb + 255);
-      if (c0 > c1) continue;
-      uint32_t* row = bits + (r - rg) * stride;
-      const int j0 = c0 >> 5, j1 = c1 >> 5;
-      for (int j = j0; j <= j1; ++j) {
-        const uint32_t mk = d_ones_below(c1 + 1 - 32 * j) & ~d_ones_below(c0 - 32 * j);
-        atomicOr(&row[j], mk);
+      if (c0 <= c1) {
+        uint32_t* row = (P.img == 0 ? bits0 + (r - rg) * stride0 : bits1 + (r - rg) * stride1);
+        const int j0 = c0 >> 5, j1 = c1 >> 5;
+        for (int j = j0; j <= j1; ++j) {
+          const uint32_t mk = d_ones_below(c1 + 1 - 32 * j) & ~d_ones_below(c0 - 32 * j);
+          atomicOr(&row[j], mk);
+        }
       }
     }
+    cursor = __shfl_sync(SB_FULL_MASK, li, 31);
   }
 }
 
@@ -286,21 +338,36 @@ __device__ __forceinline__ uint32_t d_expand4(uint32_t b) {  // low 4 bits -> 4 
 }
 
 // rows x W bit image (stride words per row in shared memory) -> byte image; one 32-pixel word
-// per thread per step, written with a single 256-bit store.
+// per thread per step, written with a single 256-bit store.  A warp whose 32 words are all
+// 0 or all ~0 (most of an occupancy grid) skips the table.
 __device__ __forceinline__ void d_store_rows(const uint32_t* bits, const uint2* lut, uint8_t* dst, int rows, int wpr,
                                              int stride) {
   const int n_words = rows * wpr;
-  const bool pow2 = (wpr & (wpr - 1)) == 0;
-  const int sh = 31 - __clz(wpr);
-  for (int i = threadIdx.x; i < n_words; i += SB_RASTER_THREADS) {
-    const int row = pow2 ? (i >> sh) : (i / wpr);
-    const int j = i - row * wpr;
-    const uint32_t word = bits[row * stride + j];
-    const uint2 a = lut[word & 0xffu], b = lut[(word >> 8) & 0xffu], c = lut[(word >> 16) & 0xffu], d = lut[word >> 24];
-    uint8_t* p = dst + (size_t)i * 32;
-    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(a.x), "r"(a.y), "r"(b.x),
-                 "r"(b.y), "r"(c.x), "r"(c.y), "r"(d.x), "r"(d.y)
-                 : "memory");
+  // running (row, word-in-row) of this thread's word: 256 words further every step
+  int row = threadIdx.x / wpr, j = threadIdx.x - row * wpr;
+  const int drow = SB_RASTER_THREADS / wpr, dj = SB_RASTER_THREADS - drow * wpr;
+  const uint32_t* src = bits + row * stride + j;
+  const int dsrc = drow * stride + dj;
+  uint8_t* p = dst + (size_t)threadIdx.x * 32;
+  for (int i = threadIdx.x; i - (int)threadIdx.x < n_words; i += SB_RASTER_THREADS) {
+    const bool act = i < n_words;
+    const uint32_t word = act ? *src : 0u;
+    if (__all_sync(SB_FULL_MASK, word + 1u <= 1u)) {
+      if (act)
+        asm volatile("st.global.v8.b32 [%0], {%1,%1,%1,%1,%1,%1,%1,%1};" ::"l"(p), "r"(word) : "memory");
+    } else if (act) {
+      const uint2 a = lut[word & 0xffu], b = lut[(word >> 8) & 0xffu], c = lut[(word >> 16) & 0xffu], d = lut[word >> 24];
+      asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(a.x), "r"(a.y), "r"(b.x),
+                   "r"(b.y), "r"(c.x), "r"(c.y), "r"(d.x), "r"(d.y)
+                   : "memory");
+    }
+    p += SB_RASTER_THREADS * 32;
+    j += dj;
+    src += dsrc;
+    if (j >= wpr) {  // carry into the next row (never taken when wpr divides 256)
+      j -= wpr;
+      src += stride - wpr;
+    }
   }
 }
 
@@ -308,7 +375,8 @@ __device__ __forceinline__ void d_store_rows(const uint32_t* bits, const uint2* 
 
 // Dynamic shared memory: [byte-expansion table | staging area | bit image 0 | bit image 1]
 // (bit images: min(H, 256) rows of W/32 + 1 words).  Sized by sb_create in sb_api.cu.
-__global__ void __launch_bounds__(SB_RASTER_THREADS, 5) k_raster(DCfg c, DMap m, DState s, DObs o, int bits_off) {
+__global__ void __launch_bounds__(SB_RASTER_THREADS, 4)
+k_raster(DCfg c, DMap m, DState s, DObs o, RasterDims g) {
   extern __shared__ __align__(16) unsigned char smem[];
   uint2* lut = reinterpret_cast<uint2*>(smem);
   RasterStage* st = reinterpret_cast<RasterStage*>(smem + SB_RASTER_LUT_BYTES);
@@ -320,30 +388,25 @@ __global__ void __launch_bounds__(SB_RASTER_THREADS, 5) k_raster(DCfg c, DMap m,
   __shared__ RasterJob sjob;
   if (threadIdx.x == 0) {
     RasterJob& j = sjob;
-    j.on[0] = c.ogm_enable != 0;   // sensors.py:719-758: vehicles only, ego included
-    j.on[1] = c.dagm_enable != 0;  // sensors.py:675-716: road surface only
-    j.W[0] = j.on[0] ? c.ogm_w : 0;
-    j.H[0] = j.on[0] ? c.ogm_h : 0;
-    j.W[1] = j.on[1] ? c.dagm_w : 0;
-    j.H[1] = j.on[1] ? c.dagm_h : 0;
+    j.on[0] = g.W0 != 0;  // sensors.py:719-758: vehicles only, ego included
+    j.on[1] = g.W1 != 0;  // sensors.py:675-716: road surface only
+    j.W[0] = g.W0;
+    j.H[0] = g.H0;
+    j.W[1] = g.W1;
+    j.H[1] = g.H1;
     j.cam[0] = Cam{px, py, ch, sh, c.ogm_res, 0.5 * c.ogm_w, 0.5 * c.ogm_h};
     j.cam[1] = Cam{px, py, ch, sh, c.dagm_res, 0.5 * c.dagm_w, 0.5 * c.dagm_h};
-    j.n_veh = j.on[0] ? c.V : 0;
-    j.n_src = j.n_veh + (j.on[1] ? m.n_polys : 0);
+    j.n_veh = g.n_veh;
+    j.n_src = g.n_src;
   }
   const RasterJob& job = sjob;
-  const int W0 = c.ogm_enable ? c.ogm_w : 0, H0 = c.ogm_enable ? c.ogm_h : 0;
-  const int W1 = c.dagm_enable ? c.dagm_w : 0, H1 = c.dagm_enable ? c.dagm_h : 0;
-  const int n_veh = c.ogm_enable ? c.V : 0, n_src = n_veh + (c.dagm_enable ? m.n_polys : 0);
+  const int W0 = g.W0, H0 = g.H0, W1 = g.W1, H1 = g.H1, n_veh = g.n_veh, n_src = g.n_src;
   const int Hmax = max(H0, H1), Wmax = max(W0, W1);
-  const int wpr0 = W0 >> 5, wpr1 = W1 >> 5;
-  const int rows0 = min(H0, SB_RASTER_THREADS), rows1 = min(H1, SB_RASTER_THREADS);
-  uint32_t* bits0 = reinterpret_cast<uint32_t*>(smem + bits_off);
-  uint32_t* bits1 = bits0 + rows0 * (wpr0 + 1);
-  const int n_bit_words = rows0 * (wpr0 + 1) + rows1 * (wpr1 + 1);
-  // conservative world-space cull radii: the film's half diagonal + 1 m
-  const float rad0 = 0.5f * (float)c.ogm_res * sqrtf((float)W0 * W0 + (float)H0 * H0) + 1.0f;
-  const float rad1 = 0.5f * (float)c.dagm_res * sqrtf((float)W1 * W1 + (float)H1 * H1) + 1.0f;
+  const int wpr0 = g.wpr0, wpr1 = g.wpr1;
+  uint32_t* bits0 = reinterpret_cast<uint32_t*>(smem + g.bits_off);
+  uint32_t* bits1 = bits0 + g.rows0 * (wpr0 + 1);
+  const int n_bit_words = g.n_bit_words;
+  const float rad0 = g.rad0, rad1 = g.rad1;
   const float fx = (float)px, fy = (float)py;
   lut[threadIdx.x] = make_uint2(d_expand4(threadIdx.x & 15u), d_expand4(threadIdx.x >> 4));
 
@@ -355,9 +418,10 @@ __global__ void __launch_bounds__(SB_RASTER_THREADS, 5) k_raster(DCfg c, DMap m,
       if (threadIdx.x == 0) {
         st->n_list = 0;
         st->n_big[0] = 0;
+        st->wide = 0;
       }
       __syncthreads();
-      int par = 0;
+      int par = 0, touched = 0;
       for (int base = 0; base < n_src; base += SB_RASTER_THREADS) {
         const int p = base + threadIdx.x;
         bool keep = false;
@@ -376,17 +440,19 @@ __global__ void __launch_bounds__(SB_RASTER_THREADS, 5) k_raster(DCfg c, DMap m,
                  n <= SB_MAX_POLY_VERTS;
         }
         if (keep) st->list[atomicAdd(&st->n_list, 1)] = p;
+        if (keep && p >= n_veh && m.poly_start[p - n_veh + 1] - m.poly_start[p - n_veh] > 4) st->wide = 1;
         __syncthreads();
         // stage + rasterise in rounds; a remainder < ROUND waits for the next cull pass
         const bool last = base + SB_RASTER_THREADS >= n_src;
         int n_list = st->n_list;
         while (n_list >= SB_RASTER_ROUND || (last && n_list > 0)) {
           const int count = min(n_list, SB_RASTER_ROUND);
-          d_stage_phase(c, m, s, e, job, st, n_list - count, count, par);
+          if (st->wide) d_stage_phase<8>(c, m, s, e, job, st, n_list - count, count, par);
+          else d_stage_phase<4>(c, m, s, e, job, st, n_list - count, count, par);
           __syncthreads();
           if (threadIdx.x == 0) st->n_big[par ^ 1] = 0;
-          d_small_polys(job, st, count, rg, cb, bits0, bits1, wpr0 + 1, wpr1 + 1);
-          d_big_rows(job, st, par, r, cb, w0, w1);
+          d_small_pairs(job, st, count, rg, cb, bits0, bits1, wpr0 + 1, wpr1 + 1);
+          touched |= d_big_rows(job, st, par, r, cb, w0, w1);
           n_list -= count;
           par ^= 1;
           __syncthreads();
@@ -397,14 +463,14 @@ __global__ void __launch_bounds__(SB_RASTER_THREADS, 5) k_raster(DCfg c, DMap m,
         }
       }
       // merge the register rows of the tall polygons (all atomics are behind the last barrier)
-      if (r < H0 && cb < W0) {
+      if ((touched & 1) && r < H0 && cb < W0) {
         uint32_t* row = bits0 + threadIdx.x * (wpr0 + 1) + (cb >> 5);
         const int nw = min(8, wpr0 - (cb >> 5));
 #pragma unroll
         for (int k = 0; k < 8; ++k)
           if (k < nw && w0[k]) row[k] |= w0[k];
       }
-      if (r < H1 && cb < W1) {
+      if ((touched & 2) && r < H1 && cb < W1) {
         uint32_t* row = bits1 + threadIdx.x * (wpr1 + 1) + (cb >> 5);
         const int nw = min(8, wpr1 - (cb >> 5));
 #pragma unroll

@@ -390,7 +390,7 @@ class RoadMapData:
                 polys.append(ccw(tri))
 
         self.n_polys_raw = len(polys)
-        polys = simplify_polygons(polys, MAX_POLY_VERTS)
+        polys = split_polygons(simplify_polygons(polys, MAX_POLY_VERTS), STAGE_POLY_VERTS)
         vx, vy, start = [], [], [0]
         for p in polys:
             vx.extend(p[:, 0]); vy.extend(p[:, 1])
@@ -519,6 +519,26 @@ class RoadMapData:
 
 
 MAX_POLY_VERTS = 8  # SB_MAX_POLY_VERTS of include/smarts_b200.h
+STAGE_POLY_VERTS = 4  # k_raster stages a polygon on 4 lanes when no kept polygon has more vertices
+
+
+def split_polygons(polys: Sequence[np.ndarray], max_verts: int = STAGE_POLY_VERTS) -> List[np.ndarray]:
+    """Fan-split convex polygons with more than ``max_verts`` vertices from their first vertex into
+    pieces of at most ``max_verts`` (same union: the pieces share full diagonals)."""
+    out: List[np.ndarray] = []
+    for p in polys:
+        p = np.asarray(p, np.float64)
+        n = len(p)
+        if n <= max_verts:
+            out.append(p)
+            continue
+        i = 1
+        while i < n - 1:
+            j = min(i + max_verts - 2, n - 1)
+            out.append(np.concatenate([p[:1], p[i:j + 1]], axis=0))
+            i = j
+    return out
+
 
 
 def _cross(o, a, b) -> float:

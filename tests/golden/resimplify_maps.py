@@ -12,7 +12,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
-from smarts_b200.road_map import RoadMapData, simplify_polygons  # noqa: E402
+from smarts_b200.road_map import RoadMapData, simplify_polygons, split_polygons  # noqa: E402
 
 
 def main(names):
@@ -22,7 +22,7 @@ def main(names):
         ps, px, py = rm.poly_start, rm.poly_x, rm.poly_y
         polys = [np.stack([px[ps[p]:ps[p + 1]], py[ps[p]:ps[p + 1]]], 1) for p in range(len(ps) - 1)]
         t = time.time()
-        out = simplify_polygons(polys)
+        out = split_polygons(simplify_polygons(polys))
         vx, vy, st = [], [], [0]
         for q in out:
             vx.extend(q[:, 0]); vy.extend(q[:, 1]); st.append(len(vx))
