@@ -314,6 +314,10 @@ def main():
         else:
             per_launch = algorithmic_bytes_per_agent_step(cfg, M, A) * E * A
         achieved = per_launch / (d_ms / d_n * 1e-3) / 1e9 if d_n and d_ms > 0 else float('nan')
+        traffic = None  # dram__bytes_read + write per launch of that kernel, from the last committed ncu capture
+        cur = os.path.join(ROOT, "profiles", "current.json")
+        if os.path.exists(cur) and args.workload == "4lane_lidar_ogm_dagm_256" and not args.envs:
+            traffic = json.load(open(cur)).get("kernels", {}).get(dom, {}).get("dram_bytes")
         step_bytes = algorithmic_bytes_per_agent_step(cfg, M, A)
         step_gbs = step_bytes * (E * A * K) / (ms * 1e-3) / 1e9  # this rank's share (weak scaling: per GPU)
         line = {
@@ -326,7 +330,7 @@ def main():
                        "step_hbm_gbs_per_gpu": step_gbs, "step_frac_of_peak": step_gbs / peak,
                        "kernel_ms_per_step": {k: v[0] / max(v[1], 1) for k, v in ktimes.items() if v[1]}},
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                          "bytes_per_launch": per_launch, "ms_per_launch": d_ms / max(d_n, 1)},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "steps": Ke},
