@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define SB_ABI_VERSION 1
+#define SB_ABI_VERSION 2
 
 /* error codes */
 #define SB_OK 0
@@ -58,6 +58,19 @@ extern "C" {
 #define SB_STATUS_PATH_OVERFLOW 1u
 #define SB_STATUS_NO_WAYPOINTS 2u
 #define SB_STATUS_LIDAR_OVERFLOW 4u  /* more candidate boxes / edges near one agent than the kernel stages */
+
+/* Events bits (smarts/core/events.py:23-34) in SbObsPtrs.ev_events and SbConfig.done_mask
+ * (DoneCriteria, smarts/core/agent_interface.py:185-206). */
+#define SB_EV_COLLISION 1u
+#define SB_EV_OFF_ROAD 2u
+#define SB_EV_OFF_ROUTE 4u
+#define SB_EV_ON_SHOULDER 8u
+#define SB_EV_WRONG_WAY 16u
+#define SB_EV_NOT_MOVING 32u
+#define SB_EV_REACHED_GOAL 64u          /* always ends the episode (sensors.py:464-474) */
+#define SB_EV_REACHED_MAX_STEPS 128u    /* always ends the episode */
+#define SB_EV_AGENTS_ALIVE_DONE 256u    /* multi-agent alive criteria: evaluated by the host layer */
+#define SB_DRIVEN_PATH_MAX 500          /* DrivenPathSensor deque length, sensors.py:838-840 */
 
 typedef struct SbHandle_ *SbHandle;
 
@@ -93,6 +106,12 @@ typedef struct SbConfig {
   double ogm_resolution;
   int32_t dagm_enable, dagm_width, dagm_height;
   double dagm_resolution;
+  /* Events / done criteria / trip-meter reward (sensors.py:443-594, :830-947; agent_manager.py:233-234) */
+  int32_t events_enable;
+  uint32_t done_mask;          /* SB_EV_* bits that end an agent's episode (DoneCriteria) */
+  int32_t max_episode_steps;   /* AgentInterface.max_episode_steps; <= 0: None */
+  double not_moving_time;      /* EventConfiguration, agent_interface.py:174-182 (60 s) */
+  double not_moving_distance;  /* (1 m) */
 } SbConfig;
 
 /* Per-scenario constant road map (host pointers, copied once).  Built by
@@ -176,6 +195,14 @@ typedef struct SbObsPtrs {
   /* grids */
   uint8_t *ogm;                /* [E*A, H, W] */
   uint8_t *dagm;               /* [E*A, H, W] */
+  /* events / reward (events_enable) */
+  uint32_t *ev_events;         /* [E*A] SB_EV_* bits (Events, events.py:23-34) */
+  uint8_t *ev_done;            /* [E*A] Sensors._is_done_with_events, sensors.py:464-474 */
+  int32_t *ev_n_collisions;    /* [E*A] vehicles in contact (smarts.py:1270-1291) */
+  int32_t *ev_collidee;        /* [E*A] lowest colliding vehicle slot or -1 */
+  double *ev_distance;         /* [E*A] TripMeterSensor(), sensors.py:880-947 (Observation.distance_travelled) */
+  double *ev_reward;           /* [E*A] TripMeterSensor(increment=True), agent_manager.py:233-234 */
+  int32_t *ev_steps;           /* [E*A] SensorState.steps_completed, sensors.py:609-637 */
 } SbObsPtrs;
 
 /* Initial / reset state for a set of envs (host pointers).  Replaces SMARTS.reset ->
@@ -184,6 +211,8 @@ typedef struct SbResetState {
   const double *agent_x, *agent_y, *agent_heading, *agent_speed; /* [n, A] */
   const int32_t *route;      /* [n, A, route_cap] or NULL (no route) */
   const int32_t *route_len;  /* [n, A] or NULL */
+  /* PositionalGoal (plan.py:95-124): goal_radius < 0 or NULL pointers = EndlessGoal */
+  const double *goal_x, *goal_y, *goal_radius; /* [n, A] or NULL */
 } SbResetState;
 
 /* HiWayEnv.__init__ -> SMARTS.__init__ (smarts/env/hiway_env.py:166-173, smarts/core/smarts.py:96-185) */
@@ -227,7 +256,8 @@ int64_t sb_launch_count(SbHandle h);
 #define SB_K_OBSERVE 2
 #define SB_K_LIDAR 3
 #define SB_K_RASTER 4
-#define SB_K_COUNT 5
+#define SB_K_EVENTS 5
+#define SB_K_COUNT 6
 int sb_set_timing(SbHandle h, int on);
 int sb_collect_timing(SbHandle h, double *ms_sum /*[SB_K_COUNT]*/, int64_t *count /*[SB_K_COUNT]*/);
 const char *sb_last_error(SbHandle h);

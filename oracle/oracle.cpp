@@ -333,6 +333,20 @@ void observe_neighbors(World& w, int e, int a) {
   w.nbr_count[ai] = cnt;
 }
 
+// waypoint_paths[0][0] feeds TripMeterSensor.append_waypoint_if_new (sensors.py:340-341)
+void stash_trip_waypoint(World& w, int ai, const PathSet& ps) {
+  double* tw = &w.trip_wp[(size_t)ai * 4];
+  if (ps.n == 0 || ps.len[0] == 0) {
+    tw[3] = -1.0;
+    return;
+  }
+  const Waypoint& q = ps.wp[0][0];
+  tw[0] = q.x;
+  tw[1] = q.y;
+  tw[2] = q.heading;
+  tw[3] = (double)q.lane;
+}
+
 // sensors.py:972-988 -> waypoint_paths; StdObs layout format_obs.py:546-604
 void observe_waypoints(World& w, int e, int a) {
   static thread_local PathSet ps;
@@ -342,6 +356,7 @@ void observe_waypoints(World& w, int e, int a) {
                  &w.route[(size_t)ai * w.cfg.route_cap], w.route_len[ai], &ps);
   if (ps.overflow) w.status[ai] |= SB_STATUS_PATH_OVERFLOW;
   w.wp_n_paths[ai] = ps.total;
+  if (w.cfg.events_enable) stash_trip_waypoint(w, ai, ps);
   for (int p = 0; p < P; ++p) {
     int len = p < ps.n ? std::min(ps.len[p], L) : 0;
     w.wp_len[(size_t)ai * P + p] = len;
@@ -542,12 +557,278 @@ void observe_dagm(World& w, int e, int a) {
   }
 }
 
+// ---------------------------------------------------------------- events
+// sumolib 1.10.0 geomhelper restatements (package not vendored in the reference, setup.py:28)
+inline double line_offset(double px, double py, double ax, double ay, double bx, double by) {
+  double dx = ax - bx, dy = ay - by;
+  double d = std::sqrt(dx * dx + dy * dy);
+  double u = ((px - ax) * (bx - ax)) + ((py - ay) * (by - ay));
+  if (d == 0.0 || u < 0.0 || u > d * d) return u < 0.0 ? 0.0 : d;
+  return u / d;
+}
+inline bool geo_isclose(double a, double b) { return std::fabs(a - b) <= 1e-9 * std::max(std::fabs(a), std::fabs(b)); }
+inline void position_at_offset(double ax, double ay, double bx, double by, double off, double* x, double* y) {
+  if (geo_isclose(off, 0.0)) { *x = ax; *y = ay; return; }
+  double dx = ax - bx, dy = ay - by;
+  double dist = std::sqrt(dx * dx + dy * dy);
+  if (geo_isclose(dist, off)) { *x = bx; *y = by; return; }
+  *x = ax + (bx - ax) * (off / dist);
+  *y = ay + (by - ay) * (off / dist);
+}
+// Lane.offset_along_lane, sumo_road_network.py:476-491
+double offset_along_lane(const Map& mp, int lane, double px, double py) {
+  int s = mp.lane_shape_start[lane], e = mp.lane_shape_start[lane + 1];
+  double seen = 0.0, min_dist = 1e300, min_off = -1.0;
+  for (int i = s; i + 1 < e; ++i) {
+    double ax = mp.shape_x[i], ay = mp.shape_y[i], bx = mp.shape_x[i + 1], by = mp.shape_y[i + 1];
+    double pos = line_offset(px, py, ax, ay, bx, by);
+    double qx, qy;
+    position_at_offset(ax, ay, bx, by, pos, &qx, &qy);
+    double ex = px - qx, ey = py - qy;
+    double dist = std::sqrt(ex * ex + ey * ey);
+    if (dist < min_dist) {
+      min_dist = dist;
+      min_off = pos + seen;
+    }
+    double dx = ax - bx, dy = ay - by;
+    seen += std::sqrt(dx * dx + dy * dy);
+  }
+  return min_off;
+}
+// Lane.from_lane_coord, sumo_road_network.py:502-506
+void from_lane_coord(const Map& mp, int lane, double off, double* x, double* y) {
+  int s = mp.lane_shape_start[lane], e = mp.lane_shape_start[lane + 1];
+  double seen = 0.0;
+  for (int i = s; i + 1 < e; ++i) {
+    double ax = mp.shape_x[i], ay = mp.shape_y[i], bx = mp.shape_x[i + 1], by = mp.shape_y[i + 1];
+    double dx = ax - bx, dy = ay - by;
+    double len = std::sqrt(dx * dx + dy * dy);
+    if (seen + len > off) {
+      position_at_offset(ax, ay, bx, by, off - seen, x, y);
+      return;
+    }
+    seen += len;
+  }
+  *x = mp.shape_x[e - 1];
+  *y = mp.shape_y[e - 1];
+}
+// RoadMap.Lane.vector_at_offset, road_map.py:377-388
+void vector_at_offset(const Map& mp, int lane, double off, double* vx, double* vy) {
+  double len = mp.lane_length[lane], s0, s1;
+  if (off >= len) {
+    s0 = len - 1;
+    s1 = len;
+  } else {
+    s0 = off;
+    s1 = off + 1;
+  }
+  s0 = s0 > 0 ? s0 : 0;
+  double x0, y0, x1, y1;
+  from_lane_coord(mp, lane, s0, &x0, &y0);
+  from_lane_coord(mp, lane, s1, &x1, &y1);
+  *vx = x1 - x0;
+  *vy = y1 - y0;
+}
+// utils/math.py:256-277
+double vec_to_radians(double x, double y) {
+  double r = sb_atan2(std::fabs(y), std::fabs(x));
+  if (x < 0) {
+    if (y < 0) return sb_pymod(r + 0.5 * kPi, kTwoPi);
+    return sb_pymod(0.5 * kPi - r, kTwoPi);
+  } else if (y < 0) {
+    return sb_pymod(1.5 * kPi - r, kTwoPi);
+  }
+  return sb_pymod(r - 0.5 * kPi, kTwoPi);
+}
+// sumo_road_network.py:703-709
+bool road_with_point(const Map& mp, double px, double py) {
+  const double radius = std::max(5.0, 2 * 3.2);
+  for (int l = 0; l < mp.m.n_lanes; ++l) {
+    double d = dist_point_to_polyline(mp, l, px, py);
+    if (d < 0.0 || !(d < radius)) continue;
+    if (d < 0.5 * mp.lane_width[l] + 1e-1) return true;
+  }
+  return false;
+}
+// vehicle-vehicle contact: smarts.py:1270-1291 with the 0.05 m leeway of chassis.py:76-79,
+// as a 2-D separating-axis test on the heading-aligned boxes
+bool boxes_touch(double ax, double ay, double ac, double as, double al, double aw, double bx, double by, double bc,
+                 double bs, double bl, double bw) {
+  const double afx = -as, afy = ac, asx = ac, asy = as;
+  const double bfx = -bs, bfy = bc, bsx = bc, bsy = bs;
+  const double dx = bx - ax, dy = by - ay;
+  const double hal = 0.5 * al, haw = 0.5 * aw, hbl = 0.5 * bl, hbw = 0.5 * bw;
+  const double leeway = 0.05;
+  const double ff = std::fabs(afx * bfx + afy * bfy), fs = std::fabs(afx * bsx + afy * bsy);
+  const double sf = std::fabs(asx * bfx + asy * bfy), ss = std::fabs(asx * bsx + asy * bsy);
+  if (std::fabs(dx * afx + dy * afy) > (hal + (hbl * ff + hbw * fs)) + leeway) return false;
+  if (std::fabs(dx * asx + dy * asy) > (haw + (hbl * sf + hbw * ss)) + leeway) return false;
+  if (std::fabs(dx * bfx + dy * bfy) > (hbl + (hal * ff + haw * sf)) + leeway) return false;
+  if (std::fabs(dx * bsx + dy * bsy) > (hbw + (hal * fs + haw * ss)) + leeway) return false;
+  return true;
+}
+
+// Sensors.observe tail: trip meter, driven path, _is_done_with_events (sensors.py:340-396, :443-594)
+void observe_events(World& w, int e, int a, bool ticked) {
+  const Map& mp = w.map;
+  const int ai = e * w.A + a, vi = e * w.V + a;
+  const double px = w.pos_x[vi], py = w.pos_y[vi], ph = w.heading[vi];
+  const double len = w.length[vi], wid = w.width[vi], ch = w.cos_h[vi], sh = w.sin_h[vi];
+  const int32_t* route = &w.route[(size_t)ai * w.cfg.route_cap];
+  const int route_len = w.route_len[ai];
+  uint32_t bits = 0;
+  const int steps = w.steps[ai] + (ticked ? 1 : 0);
+  w.steps[ai] = steps;
+  w.ev_steps[ai] = steps;
+  {  // TripMeterSensor, sensors.py:880-947
+    const double* tw = &w.trip_wp[(size_t)ai * 4];
+    const int tlane = (int)tw[3];
+    double dist = w.trip_dist[ai], last = w.trip_last[ai];
+    if (tlane >= 0) {
+      if (!w.trip_init[ai]) {
+        w.trip_init[ai] = 1;
+        w.trip_has[ai] = 1;
+        w.trip_x[ai] = tw[0];
+        w.trip_y[ai] = tw[1];
+        w.trip_h[ai] = tw[2];
+      }
+      last = dist;
+      const bool fixed_route = w.goal_r[ai] >= 0.0;
+      const bool count = !fixed_route || in_route(route, route_len, mp.lane_road[tlane]);
+      if (!w.trip_has[ai]) {
+        if (count) {
+          w.trip_has[ai] = 1;
+          w.trip_x[ai] = tw[0];
+          w.trip_y[ai] = tw[1];
+          w.trip_h[ai] = tw[2];
+        }
+      } else {
+        double ddx = tw[0] - w.trip_x[ai], ddy = tw[1] - w.trip_y[ai];
+        double d = std::sqrt(ddx * ddx + ddy * ddy);
+        if (d > 0.5 && count) {
+          double hvx, hvy;
+          radians_to_vec(w.trip_h[ai], &hvx, &hvy);
+          double dot = hvx * ddx + hvy * ddy;
+          double sg = dot > 0 ? 1.0 : (dot < 0 ? -1.0 : 0.0);
+          dist += sg * d;
+          w.trip_x[ai] = tw[0];
+          w.trip_y[ai] = tw[1];
+          w.trip_h[ai] = tw[2];
+        }
+      }
+    } else if (!w.trip_init[ai]) {
+      w.trip_init[ai] = 1;
+    }
+    w.trip_dist[ai] = dist;
+    w.trip_last[ai] = last;
+    w.ev_distance[ai] = dist;
+    w.ev_reward[ai] = dist - last;
+  }
+  {  // DrivenPathSensor + _vehicle_is_not_moving, sensors.py:830-877, :509-524
+    const int n = w.path_n[ai];
+    double* ring = &w.path_cum[(size_t)ai * w.ring];
+    double cum = 0.0;
+    if (n > 0) {
+      double qx = px - w.last_px[ai], qy = py - w.last_py[ai];
+      cum = ring[(n - 1) % w.ring] + std::sqrt(qx * qx + qy * qy);
+    }
+    ring[n % w.ring] = cum;
+    w.path_n[ai] = n + 1;
+    w.last_px[ai] = px;
+    w.last_py[ai] = py;
+    if (!((double)steps * w.cfg.dt < w.cfg.not_moving_time)) {
+      int back = std::min(w.ring - 1, n);
+      double moved = cum - ring[(n - back) % w.ring];
+      if (moved < w.cfg.not_moving_distance) bits |= SB_EV_NOT_MOVING;
+    }
+  }
+  if (w.goal_r[ai] >= 0.0) {  // plan.py:117-121
+    double gx = px - w.goal_x[ai], gy = py - w.goal_y[ai];
+    if (gx * gx + gy * gy <= w.goal_r[ai] * w.goal_r[ai]) bits |= SB_EV_REACHED_GOAL;
+  }
+  if (w.cfg.max_episode_steps > 0 && steps >= w.cfg.max_episode_steps) bits |= SB_EV_REACHED_MAX_STEPS;
+  {  // contacts
+    int cnt = 0, first = -1;
+    for (int j = 0; j < w.V; ++j) {
+      int vj = e * w.V + j;
+      if (j == a || !w.alive[vj]) continue;
+      if (boxes_touch(px, py, ch, sh, len, wid, w.pos_x[vj], w.pos_y[vj], w.cos_h[vj], w.sin_h[vj], w.length[vj],
+                      w.width[vj])) {
+        if (first < 0) first = j;
+        ++cnt;
+      }
+    }
+    w.ev_n_collisions[ai] = cnt;
+    w.ev_collidee[ai] = first;
+    if (cnt) bits |= SB_EV_COLLISION;
+  }
+  {  // off road / on shoulder: sensors.py:496-507; corners vehicle.py:316-332, utils/math.py:436-444
+    if (!road_with_point(mp, px, py)) bits |= SB_EV_OFF_ROAD;
+    const double cw[4] = {-0.5, 0.5, 0.5, -0.5}, cl[4] = {0.5, 0.5, -0.5, -0.5};
+    bool shoulder = false;
+    for (int k = 0; k < 4; ++k) {
+      double ox = (px + cw[k] * wid) - px, oy = (py + cl[k] * len) - py;
+      double qx = (px + ch * ox) + sh * oy;
+      double qy = (py + (-sh) * ox) + ch * oy;
+      if (!road_with_point(mp, qx, qy)) shoulder = true;
+    }
+    if (shoulder) bits |= SB_EV_ON_SHOULDER;
+  }
+  {  // sensors.py:526-594
+    double radius = std::sqrt(len * len + wid * wid) * 0.5 + 5;
+    int nl = nearest_lane(mp, px, py, radius);
+    if (nl < 0) {
+      bits |= SB_EV_OFF_ROUTE;
+    } else {
+      int road = mp.lane_road[nl];
+      bool in_j = mp.road_is_junction[road] != 0;
+      double off = offset_along_lane(mp, nl, px, py), mvx, mvy;
+      vector_at_offset(mp, nl, off, &mvx, &mvy);
+      if (!in_j) {
+        double th = wrap_heading(vec_to_radians(mvx, mvy));
+        double rel = wrap_heading(ph - th);
+        if (std::fabs(rel) > 0.5 * kPi) bits |= SB_EV_WRONG_WAY;
+      }
+      if (!(route_len <= 0 || in_route(route, route_len, road) || in_j)) {
+        // oncoming_lanes_at_offset, sumo_road_network.py:371-396
+        double cx, cy;
+        from_lane_coord(mp, nl, off, &cx, &cy);
+        double near_r = 1.1 * mp.lane_width[nl];
+        double my_norm = std::sqrt(mvx * mvx + mvy * mvy);
+        bool found = false;
+        if (my_norm != 0.0) {
+          for (int l = 0; l < mp.m.n_lanes && !found; ++l) {
+            if (l == nl) continue;
+            double d = dist_point_to_polyline(mp, l, cx, cy);
+            if (d < 0.0 || !(d < near_r)) continue;
+            double sl = offset_along_lane(mp, l, cx, cy), lvx, lvy;
+            vector_at_offset(mp, l, sl, &lvx, &lvy);
+            double lv_norm = std::sqrt(lvx * lvx + lvy * lvy);
+            if (lv_norm == 0.0) continue;
+            double ang = (mvx * lvx + mvy * lvy) / (my_norm * lv_norm);
+            if (ang < -0.995562 && in_route(route, route_len, mp.lane_road[l])) found = true;
+          }
+        }
+        if (!found) bits |= SB_EV_OFF_ROUTE;
+      }
+    }
+  }
+  w.ev_events[ai] = bits;
+  const uint32_t mask = w.cfg.done_mask | SB_EV_REACHED_GOAL | SB_EV_REACHED_MAX_STEPS;
+  w.ev_done[ai] = (ticked && (bits & mask)) ? 1 : 0;
+}
+
 void observe_agent(World& w, int e, int a) {
   const int ai = e * w.A + a, vi = e * w.V + a;
   // sensors.py:277-285, radius None -> max(10, 2 * default lane width) (sumo_road_network.py:679-680)
   w.ego_lane[ai] = nearest_lane(w.map, w.pos_x[vi], w.pos_y[vi], std::max(10.0, 2 * 3.2));
   if (w.cfg.nbr_enable) observe_neighbors(w, e, a);
   if (w.cfg.wp_enable) observe_waypoints(w, e, a);
+  if (!w.cfg.wp_enable && w.cfg.events_enable) {  // sensors.py:289-295
+    static thread_local PathSet ps;
+    waypoint_paths(w.map, w.pos_x[vi], w.pos_y[vi], w.heading[vi], 1, w.length[vi], nullptr, -1, &ps);
+    stash_trip_waypoint(w, ai, ps);
+  }
   if (w.cfg.lidar_enable) observe_lidar(w, e, a);
   if (w.cfg.ogm_enable) observe_ogm(w, e, a);
   if (w.cfg.dagm_enable) observe_dagm(w, e, a);
@@ -639,6 +920,21 @@ void* or_create(const SbConfig* cfg, const SbMap* m, const double* base_rays, in
     w->lidar_points.assign(na * cfg->lidar_rays * 3, 0);
     w->lidar_hits.assign(na * cfg->lidar_rays, 0);
   }
+  if (cfg->events_enable) {
+    double win = std::floor(cfg->not_moving_time / cfg->dt + 1e-9);
+    w->ring = (int)(win < SB_DRIVEN_PATH_MAX - 1 ? win : SB_DRIVEN_PATH_MAX - 1) + 1;
+    w->trip_init.assign(na, 0);
+    w->trip_has.assign(na, 0);
+    w->ev_done.assign(na, 0);
+    for (auto* v : {&w->trip_x, &w->trip_y, &w->trip_h, &w->trip_dist, &w->trip_last, &w->last_px, &w->last_py,
+                    &w->goal_x, &w->goal_y, &w->ev_distance, &w->ev_reward})
+      v->assign(na, 0.0);
+    w->goal_r.assign(na, -1.0);
+    w->trip_wp.assign(na * 4, 0.0);
+    w->path_cum.assign(na * w->ring, 0.0);
+    for (auto* v : {&w->steps, &w->path_n, &w->ev_n_collisions, &w->ev_collidee, &w->ev_steps}) v->assign(na, 0);
+    w->ev_events.assign(na, 0);
+  }
   if (cfg->ogm_enable) w->ogm.assign(na * cfg->ogm_width * cfg->ogm_height, 0);
   if (cfg->dagm_enable) w->dagm.assign(na * cfg->dagm_width * cfg->dagm_height, 0);
   return w;
@@ -677,6 +973,17 @@ void or_reset(void* h, const int32_t* env_ids, int n, const SbResetState* init) 
       int rc = w.cfg.route_cap;
       for (int k = 0; k < rc; ++k) w.route[(size_t)ai * rc + k] = init->route ? init->route[src * rc + k] : -1;
       w.route_len[ai] = init->route_len ? init->route_len[src] : 0;
+      if (w.cfg.events_enable) {
+        w.trip_init[ai] = w.trip_has[ai] = 0;
+        w.trip_x[ai] = w.trip_y[ai] = w.trip_h[ai] = w.trip_dist[ai] = w.trip_last[ai] = 0.0;
+        w.trip_wp[(size_t)ai * 4 + 3] = -1.0;
+        w.steps[ai] = w.path_n[ai] = 0;
+        w.last_px[ai] = w.last_py[ai] = 0.0;
+        const bool goals = init->goal_x && init->goal_y && init->goal_radius;
+        w.goal_x[ai] = goals ? init->goal_x[src] : 0.0;
+        w.goal_y[ai] = goals ? init->goal_y[src] : 0.0;
+        w.goal_r[ai] = goals ? init->goal_radius[src] : -1.0;
+      }
     }
     for (int j = w.A; j < w.V; ++j) {
       int vj = e * w.V + j;
@@ -752,11 +1059,17 @@ void or_step(void* h, const void* actions) {
       chassis_step(w, ai, vi);
     }
   });
+  w.stepped = true;
 }
 
 void or_observe(void* h) {
   World& w = *static_cast<World*>(h);
   parallel_for(w.E * w.A, w.threads, 1, [&](int i) { observe_agent(w, i / w.A, i % w.A); });
+  if (w.cfg.events_enable) {
+    const bool ticked = w.stepped;
+    parallel_for(w.E * w.A, w.threads, 1, [&](int i) { observe_events(w, i / w.A, i % w.A, ticked); });
+    w.stepped = false;
+  }
 }
 
 void or_get_state(void* h, SbStatePtrs* o) {
@@ -783,6 +1096,9 @@ void or_get_obs(void* h, SbObsPtrs* o) {
   o->wp_lane_index = w.wp_lane_index.data();
   o->lidar_points = w.lidar_points.data(); o->lidar_hits = w.lidar_hits.data();
   o->ogm = w.ogm.data(); o->dagm = w.dagm.data();
+  o->ev_events = w.ev_events.data(); o->ev_done = w.ev_done.data(); o->ev_n_collisions = w.ev_n_collisions.data();
+  o->ev_collidee = w.ev_collidee.data(); o->ev_distance = w.ev_distance.data(); o->ev_reward = w.ev_reward.data();
+  o->ev_steps = w.ev_steps.data();
 }
 
 // ---- unit-level probes used to pin the oracle against the reference's golden vectors ----

@@ -109,6 +109,14 @@ struct World {
   std::vector<float> nbr_box, nbr_heading, nbr_speed, wp_heading, wp_lane_width, wp_speed_limit;
   std::vector<int8_t> nbr_lane_index, wp_lane_index, lidar_hits;
   std::vector<uint8_t> ogm, dagm;
+  // events / trip meter / driven path (sensors.py:443-594, :830-947)
+  std::vector<uint8_t> trip_init, trip_has, ev_done;
+  std::vector<double> trip_x, trip_y, trip_h, trip_dist, trip_last, trip_wp, path_cum, last_px, last_py, goal_x,
+      goal_y, goal_r, ev_distance, ev_reward;
+  std::vector<int32_t> steps, path_n, ev_n_collisions, ev_collidee, ev_steps;
+  std::vector<uint32_t> ev_events;
+  int ring = 1;
+  bool stepped = false;
   int threads = 1;
 };
 

@@ -115,7 +115,7 @@ class OracleWorld:
         except Exception:
             pass
 
-    def reset(self, x, y, heading, speed, route=None, route_len=None, env_ids=None):
+    def reset(self, x, y, heading, speed, route=None, route_len=None, env_ids=None, goal=None):
         x, y, heading, speed = (np.ascontiguousarray(v, np.float64) for v in (x, y, heading, speed))
         rs = _abi.SbResetState()
         rs.agent_x, rs.agent_y, rs.agent_heading, rs.agent_speed = _dp(x), _dp(y), _dp(heading), _dp(speed)
@@ -125,6 +125,10 @@ class OracleWorld:
             route_len = np.ascontiguousarray(route_len, np.int32)
             keep = [route, route_len]
             rs.route, rs.route_len = _ip(route), _ip(route_len)
+        if goal is not None:
+            goal = [np.ascontiguousarray(g, np.float64) for g in goal]
+            keep += goal
+            rs.goal_x, rs.goal_y, rs.goal_radius = (_dp(g) for g in goal)
         ids = None
         n = self.E
         if env_ids is not None:

@@ -6,7 +6,7 @@ from typing import Dict
 
 import numpy as np
 
-SB_ABI_VERSION = 1
+SB_ABI_VERSION = 2
 
 SB_ACTION_CONTINUOUS = 0
 SB_ACTION_LANE = 1
@@ -22,6 +22,12 @@ SB_MAX_TRAJ = 32
 SB_CTRL_STATE = 12
 SB_STATUS_PATH_OVERFLOW = 1
 SB_STATUS_NO_WAYPOINTS = 2
+SB_STATUS_LIDAR_OVERFLOW = 4
+
+SB_EV_COLLISION, SB_EV_OFF_ROAD, SB_EV_OFF_ROUTE, SB_EV_ON_SHOULDER = 1, 2, 4, 8
+SB_EV_WRONG_WAY, SB_EV_NOT_MOVING, SB_EV_REACHED_GOAL, SB_EV_REACHED_MAX_STEPS = 16, 32, 64, 128
+SB_EV_AGENTS_ALIVE_DONE = 256
+SB_DRIVEN_PATH_MAX = 500
 
 _i32, _f64, _u8 = C.c_int32, C.c_double, C.c_uint8
 _pi32, _pf64, _pu8 = C.POINTER(C.c_int32), C.POINTER(C.c_double), C.POINTER(C.c_uint8)
@@ -37,6 +43,8 @@ class SbConfig(C.Structure):
         ("lidar_enable", _i32), ("lidar_rays", _i32), ("lidar_miss_inf", _i32), ("lidar_wall_height", _f64),
         ("ogm_enable", _i32), ("ogm_width", _i32), ("ogm_height", _i32), ("ogm_resolution", _f64),
         ("dagm_enable", _i32), ("dagm_width", _i32), ("dagm_height", _i32), ("dagm_resolution", _f64),
+        ("events_enable", _i32), ("done_mask", C.c_uint32), ("max_episode_steps", _i32),
+        ("not_moving_time", _f64), ("not_moving_distance", _f64),
     ]
 
 
@@ -79,12 +87,15 @@ class SbObsPtrs(C.Structure):
         ("wp_lane_width", _pf32), ("wp_speed_limit", _pf32), ("wp_lane", _pi32), ("wp_lane_index", _pi8),
         ("lidar_points", _pf64), ("lidar_hits", _pi8),
         ("ogm", _pu8), ("dagm", _pu8),
+        ("ev_events", _pu32), ("ev_done", _pu8), ("ev_n_collisions", _pi32), ("ev_collidee", _pi32),
+        ("ev_distance", _pf64), ("ev_reward", _pf64), ("ev_steps", _pi32),
     ]
 
 
 class SbResetState(C.Structure):
     _fields_ = [("agent_x", _pf64), ("agent_y", _pf64), ("agent_heading", _pf64), ("agent_speed", _pf64),
-                ("route", _pi32), ("route_len", _pi32)]
+                ("route", _pi32), ("route_len", _pi32),
+                ("goal_x", _pf64), ("goal_y", _pf64), ("goal_radius", _pf64)]
 
 
 _NP = {_pi32: np.int32, _pf64: np.float64, _pu8: np.uint8, _pf32: np.float32, _pi8: np.int8, _pu32: np.uint32}
@@ -132,6 +143,10 @@ def obs_shapes(cfg: SbConfig) -> Dict[str, tuple]:
         out.update(ogm=((cfg.ogm_height, cfg.ogm_width), np.uint8))
     if cfg.dagm_enable:
         out.update(dagm=((cfg.dagm_height, cfg.dagm_width), np.uint8))
+    if cfg.events_enable:
+        out.update(ev_events=((), np.uint32), ev_done=((), np.uint8), ev_n_collisions=((), np.int32),
+                   ev_collidee=((), np.int32), ev_distance=((), np.float64), ev_reward=((), np.float64),
+                   ev_steps=((), np.int32))
     return out
 
 

@@ -17,6 +17,9 @@ struct SbHandle_ {
   DMap dmap;
   DState st;
   DObs ob;
+  DEvents ev{};
+  DEvOut evo{};
+  bool stepped = false;  // a sb_step since the last sb_observe (SensorState.step; `sim.resetting` otherwise)
   bool have_map = false, have_rays = false;
   double* d_rays = nullptr;
   int32_t* d_ray_order = nullptr;   // rays in azimuth order (k_lidar's thread -> ray map)
@@ -81,8 +84,9 @@ __global__ void k_fill(double* p, size_t n, double v) {
 
 // SMARTS.reset for a list of envs: agents at their mission start with the sedan chassis box
 // (models/vehicle.urdf:12-16), social slots cleared.
-__global__ void k_reset(DCfg c, DState s, const int32_t* env_ids, int n, const double* ax, const double* ay,
-                        const double* ah, const double* av, const int32_t* route, const int32_t* route_len) {
+__global__ void k_reset(DCfg c, DState s, DEvents ev, const int32_t* env_ids, int n, const double* ax,
+                        const double* ay, const double* ah, const double* av, const int32_t* route,
+                        const int32_t* route_len, const double* gx, const double* gy, const double* gr) {
   int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n * c.V) return;
   int i = t / c.V, slot = t - i * c.V;
@@ -112,6 +116,18 @@ __global__ void k_reset(DCfg c, DState s, const int32_t* env_ids, int n, const d
     for (int k = 0; k < c.route_cap; ++k)
       s.route[(size_t)ai * c.route_cap + k] = route ? route[src * c.route_cap + k] : -1;
     s.route_len[ai] = route_len ? route_len[src] : 0;
+    if (c.events_enable) {  // new SensorState / TripMeterSensor / DrivenPathSensor (vehicle.py:344-457)
+      ev.trip_init[ai] = 0;
+      ev.trip_has[ai] = 0;
+      ev.trip_x[ai] = ev.trip_y[ai] = ev.trip_h[ai] = ev.trip_dist[ai] = ev.trip_last[ai] = 0.0;
+      ev.trip_wp[(size_t)ai * 4 + 3] = -1.0;
+      ev.steps[ai] = 0;
+      ev.path_n[ai] = 0;
+      ev.last_px[ai] = ev.last_py[ai] = 0.0;
+      ev.goal_x[ai] = gx ? gx[src] : 0.0;
+      ev.goal_y[ai] = gy ? gy[src] : 0.0;
+      ev.goal_r[ai] = gr ? gr[src] : -1.0;
+    }
   } else {
     s.alive[vi] = 0;
     s.pos_x[vi] = s.pos_y[vi] = s.pos_z[vi] = s.heading[vi] = s.speed[vi] = s.yaw_rate[vi] = 0.0;
@@ -217,6 +233,9 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
   d.lidar_wall_height = c.lidar_wall_height;
   d.ogm_enable = c.ogm_enable; d.ogm_w = c.ogm_width; d.ogm_h = c.ogm_height; d.ogm_res = c.ogm_resolution;
   d.dagm_enable = c.dagm_enable; d.dagm_w = c.dagm_width; d.dagm_h = c.dagm_height; d.dagm_res = c.dagm_resolution;
+  d.events_enable = c.events_enable; d.max_steps = c.max_episode_steps; d.done_mask = c.done_mask;
+  d.nm_time = c.not_moving_time; d.nm_dist = c.not_moving_distance;
+  if (c.events_enable && !(c.not_moving_time >= 0)) return fail(h, SB_EINVAL, "not_moving_time must be >= 0");
 
   const size_t nv = (size_t)d.E * d.V, na = (size_t)d.E * d.A;
   DState& s = h->st;
@@ -252,6 +271,24 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
   if (ok && c.ogm_enable) ok = dev_alloc(h, &o.ogm, na * c.ogm_width * c.ogm_height, false);
   if (ok && c.dagm_enable) ok = dev_alloc(h, &o.dagm, na * c.dagm_width * c.dagm_height, false);
   if (!ok) return SB_ENOMEM;
+  if (c.events_enable) {
+    DEvents& v = h->ev;
+    DEvOut& q = h->evo;
+    // DrivenPathSensor keeps 500 entries (sensors.py:838-840); the not-moving window needs
+    // floor(not_moving_time / dt) intervals of them
+    double win = floor(c.not_moving_time / c.dt + 1e-9);
+    v.ring = (int)(win < SB_DRIVEN_PATH_MAX - 1 ? win : SB_DRIVEN_PATH_MAX - 1) + 1;
+    ok = dev_alloc(h, &v.trip_init, na) && dev_alloc(h, &v.trip_has, na) && dev_alloc(h, &v.trip_x, na) &&
+         dev_alloc(h, &v.trip_y, na) && dev_alloc(h, &v.trip_h, na) && dev_alloc(h, &v.trip_dist, na) &&
+         dev_alloc(h, &v.trip_last, na) && dev_alloc(h, &v.trip_wp, na * 4) && dev_alloc(h, &v.steps, na) &&
+         dev_alloc(h, &v.path_n, na) && dev_alloc(h, &v.path_cum, na * v.ring) && dev_alloc(h, &v.last_px, na) &&
+         dev_alloc(h, &v.last_py, na) && dev_alloc(h, &v.goal_x, na) && dev_alloc(h, &v.goal_y, na) &&
+         dev_alloc(h, &v.goal_r, na) && dev_alloc(h, &q.events, na) && dev_alloc(h, &q.done, na) &&
+         dev_alloc(h, &q.n_collisions, na) && dev_alloc(h, &q.collidee, na) && dev_alloc(h, &q.distance, na) &&
+         dev_alloc(h, &q.reward, na) && dev_alloc(h, &q.steps, na);
+    if (!ok) return SB_ENOMEM;
+    k_fill<<<(unsigned)((na + 255) / 256), 256>>>(v.goal_r, na, -1.0);
+  }
   if (!dev_alloc(h, &h->d_picks, na)) return SB_ENOMEM;
   if (!dev_alloc(h, &h->d_social, (size_t)d.E * (d.M ? d.M : 1) * 8)) return SB_ENOMEM;
   h->actions_cap = action_bytes(c);
@@ -352,6 +389,7 @@ int sb_upload_map(SbHandle h, const SbMap* mp) {
             dev_upload(h, &m.lane_road, mp->lane_road, L) &&
             dev_upload(h, &m.lane_idx_in_road, mp->lane_idx_in_road, L) &&
             dev_upload(h, &m.lane_width, mp->lane_width, L) && dev_upload(h, &m.lane_speed, mp->lane_speed, L) &&
+            dev_upload(h, &m.lane_length, mp->lane_length, L) &&
             dev_upload(h, &m.lane_out_start, mp->lane_out_start, L + 1) &&
             dev_upload(h, &m.lane_out, mp->lane_out, (size_t)(mp->n_lane_out > 0 ? mp->n_lane_out : 1)) &&
             dev_upload(h, &m.lane_lp_start, mp->lane_lp_start, L) &&
@@ -449,14 +487,20 @@ int sb_reset(SbHandle h, const int32_t* env_ids, int32_t n, const SbResetState* 
   size_t na = (size_t)n * c.A;
   // one staging buffer: ids | x | y | h | v | route | route_len
   size_t off_ids = 0, off_x = ((size_t)n * 4 + 7) / 8 * 8, off_y = off_x + na * 8, off_h = off_y + na * 8,
-         off_v = off_h + na * 8, off_r = off_v + na * 8, off_rl = off_r + na * c.route_cap * 4,
-         total = off_rl + na * 4;
+         off_v = off_h + na * 8, off_gx = off_v + na * 8, off_gy = off_gx + na * 8, off_gr = off_gy + na * 8,
+         off_r = off_gr + na * 8, off_rl = off_r + na * c.route_cap * 4, total = off_rl + na * 4;
+  const bool goals = init->goal_x && init->goal_y && init->goal_radius;
   std::vector<unsigned char> host(total, 0);
   if (env_ids) std::memcpy(&host[off_ids], env_ids, (size_t)n * 4);
   std::memcpy(&host[off_x], init->agent_x, na * 8);
   std::memcpy(&host[off_y], init->agent_y, na * 8);
   std::memcpy(&host[off_h], init->agent_heading, na * 8);
   std::memcpy(&host[off_v], init->agent_speed, na * 8);
+  if (goals) {
+    std::memcpy(&host[off_gx], init->goal_x, na * 8);
+    std::memcpy(&host[off_gy], init->goal_y, na * 8);
+    std::memcpy(&host[off_gr], init->goal_radius, na * 8);
+  }
   if (init->route) std::memcpy(&host[off_r], init->route, na * c.route_cap * 4);
   if (init->route_len) std::memcpy(&host[off_rl], init->route_len, na * 4);
   unsigned char* dev = nullptr;
@@ -465,11 +509,14 @@ int sb_reset(SbHandle h, const int32_t* env_ids, int32_t n, const SbResetState* 
   if (ok) {
     int threads = n * c.V;
     k_reset<<<(threads + 127) / 128, 128>>>(
-        c, h->st, env_ids ? reinterpret_cast<const int32_t*>(dev + off_ids) : nullptr, n,
+        c, h->st, h->ev, env_ids ? reinterpret_cast<const int32_t*>(dev + off_ids) : nullptr, n,
         reinterpret_cast<const double*>(dev + off_x), reinterpret_cast<const double*>(dev + off_y),
         reinterpret_cast<const double*>(dev + off_h), reinterpret_cast<const double*>(dev + off_v),
         init->route ? reinterpret_cast<const int32_t*>(dev + off_r) : nullptr,
-        init->route_len ? reinterpret_cast<const int32_t*>(dev + off_rl) : nullptr);
+        init->route_len ? reinterpret_cast<const int32_t*>(dev + off_rl) : nullptr,
+        goals ? reinterpret_cast<const double*>(dev + off_gx) : nullptr,
+        goals ? reinterpret_cast<const double*>(dev + off_gy) : nullptr,
+        goals ? reinterpret_cast<const double*>(dev + off_gr) : nullptr);
     h->launches++;
     ok = cuda_ok(h, cudaDeviceSynchronize(), "k_reset");
   }
@@ -510,6 +557,7 @@ int sb_step(SbHandle h, const void* dev_actions, void* stream) {
       k_control_simple<<<(na + 127) / 128, 128, 0, st>>>(c, h->st, static_cast<const double*>(dev_actions));
     }
   }
+  h->stepped = true;
   return cuda_ok(h, cudaGetLastError(), "k_control") ? SB_OK : SB_ECUDA;
 }
 
@@ -523,7 +571,8 @@ int sb_observe(SbHandle h, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   {
     LaunchScope ls(h, SB_K_OBSERVE, st);
-    k_observe<<<(na + SB_OBS_WARPS - 1) / SB_OBS_WARPS, SB_OBS_WARPS * 32, 0, st>>>(c, h->dmap, h->st, h->ob);
+    k_observe<<<(na + SB_OBS_WARPS - 1) / SB_OBS_WARPS, SB_OBS_WARPS * 32, 0, st>>>(c, h->dmap, h->st, h->ob,
+                                                                                    h->ev.trip_wp);
   }
   if (c.lidar_enable) {
     LaunchScope ls(h, SB_K_LIDAR, st);
@@ -533,6 +582,12 @@ int sb_observe(SbHandle h, void* stream) {
   if (c.ogm_enable || c.dagm_enable) {
     LaunchScope ls(h, SB_K_RASTER, st);
     k_raster<<<na, SB_RASTER_THREADS, h->raster_smem, st>>>(c, h->dmap, h->st, h->ob, h->raster_dims);
+  }
+  if (c.events_enable) {
+    LaunchScope ls(h, SB_K_EVENTS, st);
+    k_events<<<(na + SB_EV_WARPS - 1) / SB_EV_WARPS, SB_EV_WARPS * 32, 0, st>>>(c, h->dmap, h->st, h->ev, h->evo,
+                                                                              h->stepped ? 1 : 0);
+    h->stepped = false;
   }
   return cuda_ok(h, cudaGetLastError(), "k_observe") ? SB_OK : SB_ECUDA;
 }
@@ -592,6 +647,12 @@ int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs* dst) {
   }
   if (c.ogm_enable) cpy(dst->ogm, o.ogm, na * c.ogm_width * c.ogm_height);
   if (c.dagm_enable) cpy(dst->dagm, o.dagm, na * c.dagm_width * c.dagm_height);
+  if (c.events_enable) {
+    const DEvOut& q = h->evo;
+    cpy(dst->ev_events, q.events, na * 4); cpy(dst->ev_done, q.done, na); cpy(dst->ev_n_collisions, q.n_collisions, na * 4);
+    cpy(dst->ev_collidee, q.collidee, na * 4); cpy(dst->ev_distance, q.distance, na * 8);
+    cpy(dst->ev_reward, q.reward, na * 8); cpy(dst->ev_steps, q.steps, na * 4);
+  }
   if (!ok) return SB_ECUDA;
   return cuda_ok(h, cudaStreamSynchronize(0), "D2H obs sync") ? SB_OK : SB_ECUDA;
 }
@@ -636,6 +697,9 @@ int sb_get_obs(SbHandle h, SbObsPtrs* out) {
   out->wp_lane_index = o.wp_lane_index;
   out->lidar_points = o.lidar_points; out->lidar_hits = o.lidar_hits;
   out->ogm = o.ogm; out->dagm = o.dagm;
+  const DEvOut& q = h->evo;
+  out->ev_events = q.events; out->ev_done = q.done; out->ev_n_collisions = q.n_collisions;
+  out->ev_collidee = q.collidee; out->ev_distance = q.distance; out->ev_reward = q.reward; out->ev_steps = q.steps;
   return SB_OK;
 }
 

@@ -22,7 +22,7 @@ struct DMap {
   const uint8_t* road_is_junction;
   const int32_t *lane_road, *lane_idx_in_road, *lane_out_start, *lane_out, *lane_lp_start, *lane_lp_count,
       *lane_shape_start;
-  const double *lane_width, *lane_speed;
+  const double *lane_width, *lane_speed, *lane_length;
   const double *lp_x, *lp_y, *lp_heading;
   const uint8_t* lp_inferred;
   const int32_t *lp_lane, *lp_next_start, *lp_next;

@@ -7,6 +7,7 @@
 //   k_observe         ego lane, NeighborhoodVehicles, Waypoints            (warp per agent)
 //   k_lidar           LidarSensor ray casting                              (block per agent)
 //   k_raster          OGM + DrivableAreaGridMap                            (block per agent)
+//   k_events          Events / done / trip-meter reward / contacts         (warp per agent, sb_events.cuh)
 #pragma once
 
 #include "sb_control.cuh"
@@ -42,6 +43,9 @@ struct DCfg {
   double ogm_res;
   int32_t dagm_enable, dagm_w, dagm_h;
   double dagm_res;
+  int32_t events_enable, max_steps;
+  uint32_t done_mask;
+  double nm_time, nm_dist;
 };
 
 // --------------------------------------------------------------------------------- social
@@ -239,7 +243,8 @@ __device__ int d_nearest_lane_warp(const DMap& m, double px, double py, double r
 
 #define SB_OBS_WARPS 4
 
-__global__ void __launch_bounds__(SB_OBS_WARPS * 32) k_observe(DCfg c, DMap m, DState s, DObs o) {
+__global__ void __launch_bounds__(SB_OBS_WARPS * 32)
+k_observe(DCfg c, DMap m, DState s, DObs o, double* __restrict__ trip_wp) {
   __shared__ WarpPaths wps[SB_OBS_WARPS];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int ai = blockIdx.x * SB_OBS_WARPS + warp;
@@ -311,6 +316,24 @@ __global__ void __launch_bounds__(SB_OBS_WARPS * 32) k_observe(DCfg c, DMap m, D
     }
   }
 
+  if (!c.wp_enable && c.events_enable) {
+    // TripMeterSensor without a waypoints sensor (sensors.py:289-295): lookahead 1, within the
+    // vehicle's length, no route; only path 0's first waypoint is needed.
+    WarpPaths* wp = &wps[warp];
+    wp_waypoint_paths(m, x, y, h, 1, s.length[vi], nullptr, -1, wp, lane);
+    __syncwarp();
+    const int n = wp->n;
+    double* tw = trip_wp + (size_t)ai * 4;
+    if (n == 0 && lane == 0) tw[3] = -1.0;
+    if (lane < n && wp_rank(m, wp, lane) == 0)
+      wp_equally_spaced<SB_MAX_LOOKAHEAD + 1>(m, wp->lp[lane], wp->len[lane], x, y, 1, [&](int, const DWaypoint& w) {
+        tw[0] = w.x;
+        tw[1] = w.y;
+        tw[2] = w.heading;
+        tw[3] = (double)w.lane;
+      });
+  }
+
   if (c.wp_enable) {  // sensors.py:972-988
     WarpPaths* wp = &wps[warp];
     const int P = c.wp_out_paths, L = c.wp_out_len;
@@ -321,12 +344,21 @@ __global__ void __launch_bounds__(SB_OBS_WARPS * 32) k_observe(DCfg c, DMap m, D
     if (lane == 0) {
       o.wp_n_paths[ai] = wp->total;
       if (wp->overflow) s.status[ai] |= SB_STATUS_PATH_OVERFLOW;
+      if (c.events_enable && n == 0) trip_wp[(size_t)ai * 4 + 3] = -1.0;
     }
     int rank = lane < n ? wp_rank(m, wp, lane) : 0x7fffffff;
     if (rank < P) {
       size_t row = ((size_t)ai * P + rank) * L;
+      const bool stash = c.events_enable && rank == 0;  // waypoint_paths[0][0] feeds the trip meter (sensors.py:340-341)
       int got = wp_equally_spaced<SB_MAX_LOOKAHEAD + 1>(
           m, wp->lp[lane], wp->len[lane], x, y, L, [&](int i, const DWaypoint& w) {
+            if (stash && i == 0) {
+              double* tw = trip_wp + (size_t)ai * 4;
+              tw[0] = w.x;
+              tw[1] = w.y;
+              tw[2] = w.heading;
+              tw[3] = (double)w.lane;
+            }
             size_t q = row + i;
             o.wp_pos[q * 3 + 0] = w.x;
             o.wp_pos[q * 3 + 1] = w.y;
@@ -362,6 +394,9 @@ __global__ void __launch_bounds__(SB_OBS_WARPS * 32) k_observe(DCfg c, DMap m, D
     }
   }
 }
+
+// --------------------------------------------------------------------------------- events
+#include "sb_events.cuh"
 
 // --------------------------------------------------------------------------------- lidar
 // k_lidar lives in sb_lidar.cuh (azimuth-sorted warps, sector / per-ray culls, exact binary64 tests).

@@ -23,7 +23,7 @@ EXPORTS = [
     "sb_set_social", "sb_step", "sb_observe", "sb_step_host", "sb_copy_obs_to_host", "sb_get_obs",
     "sb_get_state", "sb_launch_count", "sb_last_error", "sb_set_timing", "sb_collect_timing",
 ]
-KERNEL_KINDS = ["k_set_social", "k_control", "k_observe", "k_lidar", "k_raster"]
+KERNEL_KINDS = ["k_set_social", "k_control", "k_observe", "k_lidar", "k_raster", "k_events"]
 
 
 class SmartsB200Error(RuntimeError):
@@ -156,8 +156,9 @@ class Engine:
         return C.c_void_p(self._torch.cuda.current_stream(self.device).cuda_stream)
 
     # -- the step ------------------------------------------------------------------------
-    def reset(self, x, y, heading, speed, route=None, route_len=None, env_ids=None):
-        """Place agents (arrays [n, A]); ``route`` int32 [n, A, route_cap] road indices (-1 pad)."""
+    def reset(self, x, y, heading, speed, route=None, route_len=None, env_ids=None, goal=None):
+        """Place agents (arrays [n, A]); ``route`` int32 [n, A, route_cap] road indices (-1 pad);
+        ``goal`` = (x, y, radius) arrays [n, A] of PositionalGoals (radius < 0: EndlessGoal)."""
         f = lambda a: np.ascontiguousarray(a, np.float64)  # noqa: E731
         x, y, heading, speed = f(x), f(y), f(heading), f(speed)
         dp = lambda a: a.ctypes.data_as(C.POINTER(C.c_double))  # noqa: E731
@@ -168,6 +169,10 @@ class Engine:
             route = np.ascontiguousarray(route, np.int32)
             route_len = np.ascontiguousarray(route_len, np.int32)
             rs.route, rs.route_len = ip(route), ip(route_len)
+        if goal is not None:
+            gx, gy, gr = (f(g) for g in goal)
+            assert gx.size == gy.size == gr.size == x.size
+            rs.goal_x, rs.goal_y, rs.goal_radius = dp(gx), dp(gy), dp(gr)
         ids, n = None, self.E
         if env_ids is not None:
             env_ids = np.ascontiguousarray(env_ids, np.int32)

@@ -1,0 +1,484 @@
+"""``hiway-v0`` on the B200 step: the gym-style environment the reference registers as
+``smarts.env:hiway-v0`` (/root/reference/smarts/env/hiway_env.py:43-291, smarts/env/__init__.py:20-23)
+and its batched form ``ParallelEnv`` (/root/reference/smarts/env/wrappers/parallel_env.py:129-262),
+both driving ONE ``Engine`` handle (E environments on one GPU) instead of E simulator processes.
+
+    env = HiWayEnv(scenarios=[Scenario("4lane", missions={...})], agent_specs={"A0": spec, ...})
+    obs = env.reset();  obs, rewards, dones, infos = env.step({"A0": "keep_lane", ...})
+
+    envs = BatchedHiWayEnv(scenario, agent_specs, n_envs=4096)            # ParallelEnv surface
+    obs_tensors = envs.step_tensor(action_tensor)                          # zero-copy device tensors
+
+What the reference builds from a scenario directory (sstudio pickles, SUMO route files) is given
+here explicitly as a ``Scenario`` record: the flattened map, one ``Mission`` per agent and the
+social-traffic source (SUMO stays out of the kernel path, BASELINE.json north_star).  There is no
+CPU fallback: constructing either class without the CUDA library or a GPU raises.
+"""
+from __future__ import annotations
+
+import math
+import os
+from dataclasses import dataclass, field
+from typing import Any, Callable, Dict, List, Optional, Sequence, Tuple, Union
+
+import numpy as np
+
+from . import _abi, lidar_params
+from .agent_interface import ActionSpaceType, AgentInterface, AgentSpec, compile_config
+from .observation import (Collision, Dimensions, DrivableAreaGridMap, EgoVehicleObservation, Events,
+                          GridMapMetadata, Mission, Observation, OccupancyGridMap, VehicleObservation, Vias,
+                          Waypoint)
+from .road_map import RoadMapData
+
+_MAPS_DIR = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "maps")
+_LANE_COMMANDS = {"keep_lane": _abi.SB_LANE_KEEP, "slow_down": _abi.SB_LANE_SLOW_DOWN,
+                  "change_lane_left": _abi.SB_LANE_CHANGE_LEFT, "change_lane_right": _abi.SB_LANE_CHANGE_RIGHT}
+
+
+class SMARTSNotSetupError(Exception):
+    """step() before reset() (smarts/core/smarts.py:207-208)."""
+
+
+class SMARTSDestroyedError(Exception):
+    """use after close() (smarts/core/smarts.py:705-709)."""
+
+
+@dataclass
+class Scenario:
+    """One scenario: map + agent missions + social traffic source.
+
+    ``map`` is a ``RoadMapData``, the name of a flattened map under ``maps/`` ("4lane", "loop" ...)
+    or the path of a SUMO ``map.net.xml``.  ``traffic`` is ``None`` (no social vehicles), a
+    ``[T, E, M, 8]`` recording, or a callable ``t -> [E, M, 8]`` (the ``ExternalProvider`` record,
+    external_provider.py:44-51)."""
+    map: Union[str, RoadMapData]
+    missions: Dict[str, Mission] = field(default_factory=dict)
+    traffic: Any = None
+    n_social: int = 0
+
+    def road_map(self) -> RoadMapData:
+        if isinstance(self.map, RoadMapData):
+            return self.map
+        p = self.map
+        if p.endswith(".net.xml"):
+            return RoadMapData.from_file(p)
+        if not p.endswith(".npz"):
+            p = os.path.join(_MAPS_DIR, os.path.basename(p.rstrip("/")) + ".npz")
+        return RoadMapData.load(p)
+
+
+def encode_actions(space: ActionSpaceType, actions: Sequence[Any], traj_len: int) -> np.ndarray:
+    """Reference action values -> the flat array ``sb_step`` takes (include/smarts_b200.h).
+    Lane strings as in controllers/__init__.py:125-144; Trajectory = 4 sequences x, y, heading, speed."""
+    n = len(actions)
+    if space == ActionSpaceType.Lane:
+        out = np.zeros(n, np.int32)
+        for i, a in enumerate(actions):
+            if isinstance(a, str):
+                if a not in _LANE_COMMANDS:
+                    raise ValueError(f"unknown lane action {a!r}")
+                out[i] = _LANE_COMMANDS[a]
+            else:
+                out[i] = int(a)
+        return out
+    if space == ActionSpaceType.LaneWithContinuousSpeed:
+        return np.asarray([[float(a[0]), float(a[1])] for a in actions], np.float64).reshape(n, 2)
+    if space in (ActionSpaceType.Continuous, ActionSpaceType.ActuatorDynamic):
+        return np.asarray([[float(a[0]), float(a[1]), float(a[2])] for a in actions], np.float64).reshape(n, 3)
+    if space == ActionSpaceType.Trajectory:
+        out = np.zeros((n, 4, traj_len), np.float64)
+        for i, a in enumerate(actions):
+            t = np.asarray(a, np.float64)
+            if t.shape[0] != 4 or t.shape[1] < 2:
+                raise ValueError("Trajectory action must be 4 sequences (x, y, heading, speed) of >= 2 points")
+            k = min(traj_len, t.shape[1])
+            out[i, :, :k] = t[:, :k]
+            out[i, :, k:] = t[:, k - 1:k]  # pad by repeating the last point
+        return out
+    raise NotImplementedError(space)
+
+
+class BatchedHiWayEnv:
+    """E copies of one scenario on one GPU behind the ``ParallelEnv`` surface
+    (parallel_env.py:129-262): ``step(Sequence[Dict])``, ``reset()``, ``seed()``, ``batch_size``,
+    auto-reset of an env when its ``dones["__all__"]`` is raised.  ``step_tensor`` is the same step
+    without leaving the device."""
+
+    def __init__(self, scenario: Scenario, agent_specs: Dict[str, AgentSpec], n_envs: int = 1, *,
+                 fixed_timestep_sec: float = 0.1, seed: int = 42, headless: bool = True, device: int = 0,
+                 auto_reset: bool = True, start_jitter: float = 0.0, route_cap: int = 16, traj_len: int = 10,
+                 lidar_wall_height: float = 0.0, wp_out_len: Optional[int] = None, sim_name: Optional[str] = None,
+                 **_ignored_reference_kwargs):
+        from .engine import Engine  # raises without the CUDA library / a GPU: no CPU fallback
+        if not agent_specs:
+            raise ValueError("agent_specs is empty")
+        self._agent_specs = dict(agent_specs)
+        self.agent_ids = list(agent_specs.keys())
+        itfs = [s.interface for s in agent_specs.values()]
+        if any(i is None for i in itfs):
+            raise ValueError("every AgentSpec needs an interface")
+        if any(i is not itfs[0] and repr(i) != repr(itfs[0]) for i in itfs[1:]):
+            raise NotImplementedError("one AgentInterface per batch (SbConfig is per handle); "
+                                      "use one env per interface")
+        self.interface: AgentInterface = itfs[0]
+        self.scenario = scenario
+        self.road_map = scenario.road_map()
+        missing = [a for a in self.agent_ids if a not in scenario.missions]
+        if missing:
+            raise ValueError(f"scenario has no mission for agents {missing}")
+        self.E, self.A, self.M = int(n_envs), len(self.agent_ids), int(scenario.n_social)
+        self.dt = float(fixed_timestep_sec)
+        self._seed = int(seed)
+        self._jitter = float(start_jitter)
+        self._auto_reset = auto_reset
+        self.cfg = compile_config(self.interface, self.E, self.A, self.M, self.dt, device=device,
+                                  route_cap=route_cap, traj_len=traj_len, lidar_wall_height=lidar_wall_height,
+                                  wp_out_len=wp_out_len)
+        rays = lidar_params.base_rays(self.interface.lidar.sensor_params) if self.interface.lidar else None
+        self._base_rays = rays
+        self._engine: Optional[Engine] = Engine(self.cfg, self.road_map, rays)
+        self._torch = self._engine._torch
+        self._start = self._build_starts(self._seed)
+        self._setup = False
+        self._tick = np.zeros(self.E, np.int64)           # per-env step_count
+        self._global_tick = 0
+        self._done_agents = np.zeros((self.E, self.A), bool)
+        self._host: Dict[str, np.ndarray] = {}
+
+    # -- gym-ish surface -------------------------------------------------------------------
+    @property
+    def batch_size(self) -> int:
+        return self.E
+
+    def seed(self, seed: int) -> List[int]:
+        """parallel_env.py:246-256: env i gets seed + i."""
+        self._seed = int(seed)
+        self._start = self._build_starts(self._seed)
+        return [seed + i for i in range(self.E)]
+
+    def close(self, terminate: bool = False):
+        if self._engine is not None:
+            self._engine.close()
+            self._engine = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def engine(self):
+        if self._engine is None:
+            raise SMARTSDestroyedError("environment was closed")
+        return self._engine
+
+    # -- scenario -> reset arrays ------------------------------------------------------------
+    def _build_starts(self, seed: int):
+        rm, E, A = self.road_map, self.E, self.A
+        rng = np.random.default_rng(seed)
+        rc = self.cfg.route_cap
+        x = np.zeros((E, A)); y = np.zeros((E, A)); h = np.zeros((E, A)); v = np.zeros((E, A))
+        gx = np.zeros((E, A)); gy = np.zeros((E, A)); gr = np.full((E, A), -1.0)
+        route = np.full((E, A, rc), -1, np.int32)
+        rlen = np.zeros((E, A), np.int32)
+        for a, aid in enumerate(self.agent_ids):
+            m = self.scenario.missions[aid]
+            r = rm.generate_route(m.begin_road, m.end_road)
+            if not 0 < len(r.road_indices) <= rc:
+                raise ValueError(f"route of {aid}: {len(r.road_indices)} roads (route_cap {rc})")
+            route[:, a, :len(r.road_indices)] = r.road_indices
+            rlen[:, a] = len(r.road_indices)
+            offs = m.begin_offset + (rng.uniform(0, self._jitter, E) if self._jitter > 0 else np.zeros(E))
+            for e in range(E):
+                x[e, a], y[e, a], h[e, a] = rm.lane_start_pose(m.begin_road, m.begin_lane, float(offs[e]))
+            v[:, a] = m.start_speed
+            if not m.endless:
+                lane = rm.lane_of_road(m.end_road, m.end_lane)
+                off = 0.5 * float(rm.lane_length[lane]) if m.end_offset is None else m.end_offset
+                px, py, _ = rm.lane_start_pose(m.end_road, m.end_lane, off)
+                gx[:, a], gy[:, a], gr[:, a] = px, py, m.goal_radius
+        return dict(x=x, y=y, h=h, v=v, route=route, rlen=rlen, goal=(gx, gy, gr))
+
+    def _social(self, t: int) -> Optional[np.ndarray]:
+        tr = self.scenario.traffic
+        if self.M == 0 or tr is None:
+            return None
+        if callable(tr):
+            s = tr(t)
+        elif hasattr(tr, "states"):
+            s = tr.states(t)
+        else:
+            s = tr[t % len(tr)]
+        return np.ascontiguousarray(s, np.float64)
+
+    def _reset_envs(self, env_ids: Optional[np.ndarray]):
+        s = self._start
+        sel = slice(None) if env_ids is None else env_ids
+        self.engine.reset(s["x"][sel], s["y"][sel], s["h"][sel], s["v"][sel], s["route"][sel], s["rlen"][sel],
+                          env_ids=env_ids, goal=tuple(g[sel] for g in s["goal"]))
+        self._tick[sel] = 0
+        self._done_agents[sel] = False
+
+    # -- device-resident step (the scalable API) ----------------------------------------------
+    def reset_tensor(self) -> Dict[str, Any]:
+        self._reset_envs(None)
+        self._global_tick = 0
+        soc = self._social(0)
+        if soc is not None:
+            self.engine.set_social(self._torch.from_numpy(soc).to(self.engine.device))
+        self.engine.observe()
+        self._setup = True
+        return self.engine.obs()
+
+    def step_tensor(self, actions, social=None) -> Dict[str, Any]:
+        """actions: CUDA tensor in the ``sb_step`` layout; social: CUDA ``[E, M, 8]`` f64 or None (then the
+        scenario's traffic source is uploaded).  Returns the zero-copy observation tensors
+        (``ev_reward`` / ``ev_done`` included); envs whose agents are all done are reset in place when
+        ``auto_reset`` is on, after the returned views were filled for this tick."""
+        if not self._setup:
+            raise SMARTSNotSetupError("reset() must be called before step()")
+        eng = self.engine
+        if social is None:
+            soc = self._social(self._global_tick)
+            if soc is not None:
+                social = self._torch.from_numpy(soc).to(eng.device)
+        if social is not None:
+            eng.set_social(social)
+        eng.step(actions)
+        eng.observe()
+        self._global_tick += 1
+        self._tick += 1
+        return eng.obs()
+
+    def auto_reset_done_envs(self) -> np.ndarray:
+        """Reset every env whose agents are all done (parallel_env.py:300-326); returns their ids."""
+        done = self.engine.obs()["ev_done"]
+        self._torch.cuda.synchronize(self.engine.device)
+        d = done.cpu().numpy().astype(bool) | self._done_agents
+        self._done_agents = d
+        ids = np.nonzero(d.all(axis=1))[0].astype(np.int32)
+        if len(ids) and self._auto_reset:
+            self._reset_envs(ids)
+            self.engine.observe()
+        return ids
+
+    # -- host-side Observation objects ---------------------------------------------------------
+    def _fetch(self):
+        self._host = self.engine.obs_numpy()
+        self._host_state = self.engine.state_numpy()
+
+    def _vehicle_id(self, e: int, slot: int) -> str:
+        return self.agent_ids[slot] if slot < self.A else f"social-{slot - self.A}"
+
+    def _observation(self, e: int, a: int) -> Observation:
+        o, s, itf, rm = self._host, self._host_state, self.interface, self.road_map
+        px, py, pz = s["pos_x"][e, a], s["pos_y"][e, a], s["pos_z"][e, a]
+        hd, sp = float(s["heading"][e, a]), float(s["speed"][e, a])
+        el = int(o["ego_lane"][e, a])
+        lane_id = rm.lane_ids[el] if el >= 0 else None
+        road_id = rm.road_ids[int(rm.lane_road[el])] if el >= 0 else None
+        lane_index = int(rm.lane_idx_in_road[el]) if el >= 0 else None
+        ego = EgoVehicleObservation(
+            id=self.agent_ids[a], position=np.array([px, py, pz]),
+            bounding_box=Dimensions(float(s["length"][e, a]), float(s["width"][e, a]), float(s["height"][e, a])),
+            heading=hd, speed=sp, steering=float(s["steering"][e, a]), yaw_rate=float(s["yaw_rate"][e, a]),
+            road_id=road_id, lane_id=lane_id, lane_index=lane_index, mission=self.scenario.missions[self.agent_ids[a]],
+            linear_velocity=np.array([-math.sin(hd) * sp, math.cos(hd) * sp, 0.0]),
+            angular_velocity=np.array([0.0, 0.0, float(s["yaw_rate"][e, a])]),
+            linear_acceleration=None, angular_acceleration=None, linear_jerk=None, angular_jerk=None)
+        nbrs = None
+        if itf.neighborhood_vehicles:
+            nbrs = []
+            for k in range(min(int(o["nbr_count"][e, a]), self.cfg.nbr_cap)):
+                nl = int(o["nbr_lane"][e, a, k])
+                nbrs.append(VehicleObservation(
+                    id=self._vehicle_id(e, int(o["nbr_id"][e, a, k])), position=tuple(o["nbr_pos"][e, a, k]),
+                    bounding_box=Dimensions(*[float(t) for t in o["nbr_box"][e, a, k]]),
+                    heading=float(o["nbr_heading"][e, a, k]), speed=float(o["nbr_speed"][e, a, k]),
+                    road_id=rm.road_ids[int(rm.lane_road[nl])] if nl >= 0 else None,
+                    lane_id=rm.lane_ids[nl] if nl >= 0 else None,
+                    lane_index=int(o["nbr_lane_index"][e, a, k]) if nl >= 0 else None))
+        wps = None
+        if itf.waypoints:
+            wps = []
+            for p in range(self.cfg.wp_out_paths):
+                n = int(o["wp_len"][e, a, p])
+                if n == 0:
+                    continue
+                wps.append([Waypoint(pos=o["wp_pos"][e, a, p, i, :2].copy(), heading=float(o["wp_heading"][e, a, p, i]),
+                                     lane_id=rm.lane_ids[int(o["wp_lane"][e, a, p, i])],
+                                     lane_width=float(o["wp_lane_width"][e, a, p, i]),
+                                     speed_limit=float(o["wp_speed_limit"][e, a, p, i]),
+                                     lane_index=int(o["wp_lane_index"][e, a, p, i])) for i in range(n)])
+        lidar = None
+        if itf.lidar:  # (points, hits, [(origin, end)]) as lidar.py:115-134
+            origin = np.array([px, py, pz + 1.0])
+            pts = o["lidar_points"][e, a]
+            hits = o["lidar_hits"][e, a].astype(bool)
+            lidar = ([p for p in pts], [bool(t) for t in hits], [(origin, origin + r) for r in self._base_rays])
+
+        def grid(key, cfg_w, cfg_h, res, cls):
+            meta = GridMapMetadata(created_at=int(self._tick[e]), resolution=res, width=cfg_w, height=cfg_h,
+                                   camera_pos=(px, py, 20.0 * max(s["length"][e, a], s["width"][e, a], s["height"][e, a])),
+                                   camera_heading_in_degrees=math.degrees(hd))
+            return cls(metadata=meta, data=o[key][e, a][..., None])
+        ogm = grid("ogm", itf.ogm.width, itf.ogm.height, itf.ogm.resolution, OccupancyGridMap) if itf.ogm else None
+        dagm = (grid("dagm", itf.drivable_area_grid_map.width, itf.drivable_area_grid_map.height,
+                     itf.drivable_area_grid_map.resolution, DrivableAreaGridMap)
+                if itf.drivable_area_grid_map else None)
+        bits = int(o["ev_events"][e, a])
+        cols = []
+        if bits & _abi.SB_EV_COLLISION:
+            cols = [Collision(collidee_id=self._vehicle_id(e, int(o["ev_collidee"][e, a])))]
+        events = Events(collisions=cols, off_road=bool(bits & _abi.SB_EV_OFF_ROAD),
+                        off_route=bool(bits & _abi.SB_EV_OFF_ROUTE), on_shoulder=bool(bits & _abi.SB_EV_ON_SHOULDER),
+                        wrong_way=bool(bits & _abi.SB_EV_WRONG_WAY), not_moving=bool(bits & _abi.SB_EV_NOT_MOVING),
+                        reached_goal=bool(bits & _abi.SB_EV_REACHED_GOAL),
+                        reached_max_episode_steps=bool(bits & _abi.SB_EV_REACHED_MAX_STEPS), agents_alive_done=False)
+        return Observation(dt=self.dt, step_count=int(self._tick[e]), elapsed_sim_time=float(self._tick[e]) * self.dt,
+                           events=events, ego_vehicle_state=ego, neighborhood_vehicle_states=nbrs,
+                           waypoint_paths=wps, distance_travelled=float(o["ev_distance"][e, a]),
+                           lidar_point_cloud=lidar, drivable_area_grid_map=dagm, occupancy_grid_map=ogm,
+                           top_down_rgb=None, road_waypoints=None, via_data=Vias([], []))
+
+    def _env_observations(self, e: int) -> Dict[str, Observation]:
+        return {aid: self._observation(e, a) for a, aid in enumerate(self.agent_ids) if not self._done_agents[e, a]}
+
+    # -- ParallelEnv surface -------------------------------------------------------------------
+    def reset(self) -> List[Dict[str, Any]]:
+        self.reset_tensor()
+        self._fetch()
+        return [{aid: self._agent_specs[aid].observation_adapter(ob) for aid, ob in self._env_observations(e).items()}
+                for e in range(self.E)]
+
+    def step(self, actions: Sequence[Dict[str, Any]]):
+        """actions: one ``{agent_id: action}`` dict per env.  Returns (observations, rewards, dones, infos),
+        each a list over envs (parallel_env.py:188-216).  Agents that are done drop out of the dicts
+        (agent_manager.py:161-240); an env whose agents are all done raises ``dones["__all__"]`` and,
+        with ``auto_reset``, restarts -- its observation entry is then the reset observation."""
+        if self._engine is None:
+            raise SMARTSDestroyedError("environment was closed")
+        if not self._setup:
+            raise SMARTSNotSetupError("reset() must be called before step()")
+        if len(actions) != self.E:
+            raise ValueError(f"expected {self.E} action dicts, got {len(actions)}")
+        space = self.interface.action
+        flat: List[Any] = []
+        default = {ActionSpaceType.Lane: "keep_lane", ActionSpaceType.LaneWithContinuousSpeed: (0.0, 0)}.get(space)
+        for e, env_act in enumerate(actions):
+            assert isinstance(env_act, dict) and all(isinstance(k, str) for k in env_act), "Expected Dict[str, any]"
+            for a, aid in enumerate(self.agent_ids):
+                if aid in env_act:
+                    flat.append(self._agent_specs[aid].action_adapter(env_act[aid]))
+                elif self._done_agents[e, a] or default is not None:
+                    flat.append(default if default is not None else self._neutral_action())
+                else:
+                    raise KeyError(f"env {e}: no action for live agent {aid}")
+        arr = encode_actions(space, flat, self.cfg.traj_len)
+        try:
+            self.step_tensor(self._torch.from_numpy(arr).to(self.engine.device))
+            self._fetch()
+        except Exception:
+            self.close()  # smarts.py:214-227: tear down, re-raise
+            raise
+        obs_l, rew_l, done_l, info_l = [], [], [], []
+        newly = self._host["ev_done"].astype(bool) & ~self._done_agents
+        for e in range(self.E):
+            obs_e, rew_e, done_e, info_e = {}, {}, {}, {}
+            for a, aid in enumerate(self.agent_ids):
+                if self._done_agents[e, a]:
+                    continue
+                spec = self._agent_specs[aid]
+                ob = self._observation(e, a)
+                r = float(self._host["ev_reward"][e, a])
+                info = {"score": float(self._host["ev_distance"][e, a]), "env_obs": ob}
+                rew_e[aid] = spec.reward_adapter(ob, r)
+                obs_e[aid] = spec.observation_adapter(ob)
+                info_e[aid] = spec.info_adapter(ob, r, info)
+                done_e[aid] = bool(newly[e, a])
+            self._done_agents[e] |= newly[e]
+            done_e["__all__"] = bool(self._done_agents[e].all())
+            obs_l.append(obs_e); rew_l.append(rew_e); done_l.append(done_e); info_l.append(info_e)
+        # done agents leave the simulation (vehicle removed, agent_manager teardown)
+        if newly.any():
+            alive = self.engine.state()["alive"]
+            idx = np.argwhere(newly)
+            dev = self.engine.device
+            alive[self._torch.as_tensor(idx[:, 0]).to(dev), self._torch.as_tensor(idx[:, 1]).to(dev)] = 0
+        finished = np.nonzero(self._done_agents.all(axis=1))[0].astype(np.int32)
+        if len(finished) and self._auto_reset:
+            self._reset_envs(finished)
+            self.engine.observe()
+            self._fetch()
+            for e in finished:
+                obs_l[e] = {aid: self._agent_specs[aid].observation_adapter(ob)
+                            for aid, ob in self._env_observations(int(e)).items()}
+        return obs_l, rew_l, done_l, info_l
+
+    def _neutral_action(self):
+        if self.interface.action == ActionSpaceType.Trajectory:
+            return np.zeros((4, self.cfg.traj_len))
+        return (0.0, 0.0, 0.0)
+
+
+class HiWayEnv:
+    """The single-environment ``hiway-v0`` surface (hiway_env.py:43-291): dict in, dicts out."""
+
+    metadata = {"render.modes": ["human"]}
+
+    def __init__(self, scenarios: Sequence[Scenario], agent_specs: Dict[str, AgentSpec], sim_name: Optional[str] = None,
+                 shuffle_scenarios: bool = True, headless: bool = True, fixed_timestep_sec: Optional[float] = None,
+                 seed: int = 42, timestep_sec: Optional[float] = None, **kwargs):
+        if not scenarios:
+            raise ValueError("scenarios is empty")
+        if len(scenarios) > 1:
+            raise NotImplementedError("one scenario per env (the map is uploaded once per handle)")
+        dt = fixed_timestep_sec or timestep_sec or 0.1  # hiway_env.py:112-113
+        self._agent_specs = agent_specs
+        self._batched: Optional[BatchedHiWayEnv] = BatchedHiWayEnv(
+            scenarios[0], agent_specs, n_envs=1, fixed_timestep_sec=dt, seed=seed, auto_reset=False, **kwargs)
+        self._dones_registered = 0
+
+    @property
+    def agent_specs(self):
+        return self._agent_specs
+
+    @property
+    def batched(self) -> BatchedHiWayEnv:
+        if self._batched is None:
+            raise SMARTSDestroyedError("environment was closed")
+        return self._batched
+
+    def seed(self, seed: int) -> int:
+        self.batched.seed(seed)
+        return seed
+
+    def reset(self) -> Dict[str, Any]:
+        self._dones_registered = 0
+        return self.batched.reset()[0]
+
+    def step(self, agent_actions: Dict[str, Any]):
+        obs, rew, done, info = self.batched.step([agent_actions])
+        observations, rewards, dones, infos = obs[0], rew[0], done[0], info[0]
+        dones.pop("__all__", None)
+        for d in dones.values():
+            self._dones_registered += 1 if d else 0
+        dones["__all__"] = self._dones_registered >= len(self._agent_specs)  # hiway_env.py:258-261
+        return observations, rewards, dones, infos
+
+    def render(self, mode="human"):
+        pass
+
+    def close(self):
+        if self._batched is not None:
+            self._batched.close()
+            self._batched = None
+
+
+def make(id: str = "smarts.env:hiway-v0", **kwargs) -> HiWayEnv:
+    """``gym.make("smarts.env:hiway-v0", scenarios=..., agent_specs=...)`` (smarts/env/__init__.py:20-23);
+    gym itself is not needed for the call."""
+    if id.split(":")[-1] != "hiway-v0":
+        raise ValueError(f"unknown environment id {id!r}")
+    return HiWayEnv(**kwargs)

@@ -243,3 +243,85 @@ def test_full_size_grid_properties():
     assert (ogm[:, :, 127:129, 127:129] == 255).all()
     assert (dagm[:, :, 127:129, 127:129] == 255).all()
     assert set(np.unique(ogm)) <= {0, 255} and set(np.unique(dagm)) <= {0, 255}
+
+
+def _goals(rm, E, missions, radius=3.0):
+    """PositionalGoal at the middle of lane 0 of each mission's end road (plan.py:95-115)."""
+    A = len(missions)
+    gx = np.zeros((E, A)); gy = np.zeros((E, A)); gr = np.full((E, A), radius)
+    for a, (_, _, _, end) in enumerate(missions):
+        lane = rm.lane_of_road(end, 0)
+        px, py, _ = rm.lane_start_pose(end, 0, 0.5 * float(rm.lane_length[lane]))
+        gx[:, a], gy[:, a] = px, py
+    return gx, gy, gr
+
+
+@pytest.mark.parametrize("wp", [True, False])
+def test_events_rewards_dones_match_oracle(wp):
+    """Events bits, done flags, trip-meter reward / distance, contacts --
+    bit-exact against the oracle over a rollout with random lane commands (agents drift off route,
+    collide with traffic, some reach their goal, all hit max_episode_steps)."""
+    import torch
+    rm = load_map("4lane")
+    E, A, M = 24, 4, 12
+    cfg = make_cfg(E=E, A=A, M=M, wp=wp, nbr=True, route_cap=16, events=True, max_episode_steps=55,
+                   not_moving_time=2.0, not_moving_distance=1.0,
+                   done_mask=_abi.SB_EV_COLLISION | _abi.SB_EV_OFF_ROAD | _abi.SB_EV_OFF_ROUTE | _abi.SB_EV_WRONG_WAY)
+    x, y, h, v, route, rlen = scenario_gen.agent_starts(rm, E, MISSIONS_4LANE, cfg.route_cap, 31, jitter=40.0, speed=7.0)
+    goal = _goals(rm, E, MISSIONS_4LANE)
+    goal[2][E // 2:] = -1.0  # half the envs: endless missions
+    traffic = scenario_gen.SocialTraffic(rm, E, M, 32, p_alive=0.9)
+    eng, ora = engine(rm, cfg), oracle_world(rm, cfg, threads=8)
+    for w in (eng, ora):
+        w.reset(x, y, h, v, route, rlen, goal=goal)
+    eng.observe(); ora.observe()  # the reset observation: no tick, nobody done
+    assert_same(eng.obs_numpy(), ora.obs())
+    assert not ora.obs()["ev_done"].any()
+    rng = np.random.default_rng(33)
+    seen = 0
+    for t in range(60):
+        act = rng.integers(0, 4, (E, A)).astype(np.int32)
+        act[:, 3] = _abi.SB_LANE_SLOW_DOWN if t > 20 else _abi.SB_LANE_KEEP  # agent 3 stops: not_moving
+        soc = traffic.states(t)
+        eng.set_social(torch.from_numpy(soc).cuda()); ora.set_social(soc)
+        eng.step(torch.from_numpy(act).cuda()); ora.step(act)
+        eng.observe(); ora.observe()
+        got, want = eng.obs_numpy(), ora.obs()
+        assert_same(got, want)
+        seen |= int(np.bitwise_or.reduce(want["ev_events"].ravel()))
+        if t == 20:  # partial reset restarts the trip meter / step counter of those envs
+            ids = np.array([2, 5], np.int32)
+            for w in (eng, ora):
+                w.reset(x[ids], y[ids], h[ids], v[ids], route[ids], rlen[ids], env_ids=ids,
+                        goal=tuple(g[ids] for g in goal))
+    want = ora.obs()
+    assert (want["ev_steps"].ravel() >= 39).all()
+    assert want["ev_done"][want["ev_steps"] >= 55].all()  # max_episode_steps reached (envs 2, 5 restarted at t = 20)
+    assert want["ev_distance"].max() > 20.0
+    for bit in (_abi.SB_EV_COLLISION, _abi.SB_EV_NOT_MOVING, _abi.SB_EV_REACHED_MAX_STEPS):
+        assert seen & bit, f"rollout never raised event bit {bit}"
+
+
+def test_events_off_road_and_wrong_way_poses():
+    """Hand-placed poses: on the lane, on the shoulder, off the road, facing against the lane."""
+    rm = load_map("4lane")
+    E, A = 2, 4
+    cfg = make_cfg(E=E, A=A, M=0, route_cap=16, events=True)
+    x0, y0, h0 = rm.lane_start_pose("edge-south-SN", 0, 30.0)
+    fx, fy = -np.sin(h0), np.cos(h0)      # forward
+    rx, ry = np.cos(h0), np.sin(h0)        # "side" axis
+    x = np.array([[x0, x0 - 1.2 * rx, x0 - 30 * rx, x0]] * E)
+    y = np.array([[y0, y0 - 1.2 * ry, y0 - 30 * ry, y0]] * E)
+    h = np.array([[h0, h0, h0, h0 + np.pi]] * E)
+    v = np.zeros((E, A))
+    eng, ora = engine(rm, cfg), oracle_world(rm, cfg)
+    for w in (eng, ora):
+        w.reset(x, y, h, v, None, None)
+        w.observe()
+    got, want = eng.obs_numpy(), ora.obs()
+    assert_same(got, want)
+    ev = want["ev_events"][0]
+    assert not ev[0] & (_abi.SB_EV_OFF_ROAD | _abi.SB_EV_WRONG_WAY)
+    assert ev[2] & _abi.SB_EV_OFF_ROAD and ev[2] & _abi.SB_EV_ON_SHOULDER
+    assert ev[3] & _abi.SB_EV_WRONG_WAY
+    _ = fx, fy

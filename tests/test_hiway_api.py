@@ -1,0 +1,173 @@
+"""Host-side mirror of the reference's agent / environment API: AgentInterface presets,
+AgentSpec, action encoding, AgentInterface -> SbConfig; plus (gpu) the hiway-v0 step() contract."""
+import numpy as np
+import pytest
+
+from conftest import load_map
+from smarts_b200 import _abi, scenario_gen
+from smarts_b200.agent_interface import (OGM, Agent, AgentInterface, AgentSpec, AgentType, ActionSpaceType,
+                                         DoneCriteria, DrivableAreaGridMap, Lidar, NeighborhoodVehicles, Waypoints,
+                                         compile_config)
+from smarts_b200.hiway_env import (BatchedHiWayEnv, HiWayEnv, Scenario, SMARTSDestroyedError, SMARTSNotSetupError,
+                                   encode_actions, make)
+from smarts_b200.observation import Mission, Observation
+
+MISSIONS = {"A0": Mission("edge-south-SN", 1, 10.0, "edge-west-EW", start_speed=5.0),
+            "A1": Mission("edge-west-WE", 0, 10.0, "edge-east-WE", start_speed=5.0),
+            "A2": Mission("edge-north-NS", 0, 10.0, "edge-south-NS", start_speed=5.0),
+            "A3": Mission("edge-east-EW", 1, 10.0, "edge-west-EW", endless=True, start_speed=5.0)}
+
+
+def test_agent_type_presets_match_reference_table():
+    # agent_interface.py:299-392
+    laner = AgentInterface.from_type(AgentType.Laner)
+    assert laner.waypoints == Waypoints(32) and laner.action == ActionSpaceType.Lane and not laner.lidar
+    full = AgentInterface.from_type(AgentType.Full, max_episode_steps=7)
+    assert full.ogm == OGM() and full.lidar and full.rgb and full.max_episode_steps == 7
+    assert AgentInterface.from_type(AgentType.Tracker).action == ActionSpaceType.Trajectory
+    assert AgentInterface.from_type(AgentType.Standard).action == ActionSpaceType.ActuatorDynamic
+    assert AgentInterface.from_type(AgentType.LanerWithSpeed).action == ActionSpaceType.LaneWithContinuousSpeed
+    assert AgentInterface(waypoints=True).waypoints.lookahead == 32
+    assert AgentInterface(waypoints=17).waypoints is False  # _resolve_config: neither True nor the type
+    assert laner.replace(ogm=True).ogm.resolution == 50 / 256 and laner.ogm is False
+    assert [t.value for t in ActionSpaceType][:6] == [0, 1, 2, 3, 4, 5]  # controllers/__init__.py:42-54
+    with pytest.raises(Exception):
+        AgentInterface.from_type(99)
+
+
+def test_compile_config_from_interface():
+    itf = AgentInterface.from_type(AgentType.Laner, lidar=True, ogm=OGM(64, 64, 50 / 64),
+                                   neighborhood_vehicles=NeighborhoodVehicles(radius=50), max_episode_steps=100,
+                                   done_criteria=DoneCriteria(off_route=False, wrong_way=True))
+    c = compile_config(itf, 8, 2, 20, 0.1)
+    assert (c.n_envs, c.n_agents, c.n_social, c.action_space) == (8, 2, 20, _abi.SB_ACTION_LANE)
+    assert (c.wp_enable, c.wp_lookahead, c.wp_out_paths, c.wp_out_len) == (1, 32, 4, 33)
+    assert (c.lidar_enable, c.lidar_rays) == (1, 300)      # BasicLidar: 6 azimuths x 50 lasers
+    assert (c.ogm_enable, c.ogm_width, c.ogm_height) == (1, 64, 64) and c.ogm_resolution == 50 / 64
+    assert c.dagm_enable == 0 and c.nbr_radius == 50.0 and c.nbr_cap == 10
+    assert c.done_mask == _abi.SB_EV_COLLISION | _abi.SB_EV_OFF_ROAD | _abi.SB_EV_WRONG_WAY
+    assert c.max_episode_steps == 100 and c.not_moving_time == 60.0
+    assert compile_config(AgentInterface.from_type(AgentType.Tagger), 1, 1, 0, 0.1).nbr_radius == -1.0  # radius=None
+    for bad in (AgentType.Full, AgentType.MPCTracker, AgentType.Boid, AgentType.Buddha):
+        with pytest.raises((NotImplementedError, ValueError)):
+            compile_config(AgentInterface.from_type(bad), 1, 1, 0, 0.1)
+
+
+def test_encode_actions_layouts():
+    a = encode_actions(ActionSpaceType.Lane, ["keep_lane", "slow_down", "change_lane_left", "change_lane_right"], 10)
+    assert a.dtype == np.int32 and a.tolist() == [0, 1, 2, 3]
+    with pytest.raises(ValueError):
+        encode_actions(ActionSpaceType.Lane, ["fly"], 10)
+    a = encode_actions(ActionSpaceType.LaneWithContinuousSpeed, [(12.5, -1), (3, 0)], 10)
+    assert a.shape == (2, 2) and a.dtype == np.float64 and a[0].tolist() == [12.5, -1.0]
+    a = encode_actions(ActionSpaceType.Continuous, [np.array([0.5, 0.0, -0.2])], 10)
+    assert a.shape == (1, 3)
+    traj = [np.arange(4), np.arange(4) * 2.0, np.zeros(4), np.full(4, 13.9)]
+    a = encode_actions(ActionSpaceType.Trajectory, [traj], 6)
+    assert a.shape == (1, 4, 6) and a[0, 0].tolist() == [0, 1, 2, 3, 3, 3] and a[0, 3, 5] == 13.9
+
+
+def test_agent_spec_build_agent_variants():
+    class P(Agent):
+        def __init__(self, k=1, j=2):
+            self.k, self.j = k, j
+
+        def act(self, obs):
+            return self.k
+    assert AgentSpec(agent_builder=P).build_agent().k == 1
+    assert AgentSpec(agent_builder=P, agent_params=(5, 6)).build_agent().j == 6
+    assert AgentSpec(agent_builder=P, agent_params={"k": 9, "zzz": 0}).build_agent().k == 9  # unknown keys dropped
+    assert AgentSpec(agent_builder=Agent.from_function, agent_params=lambda _: "keep_lane").build_agent().act(None) == "keep_lane"
+    with pytest.raises(ValueError):
+        AgentSpec().build_agent()
+    spec = AgentSpec(interface=AgentInterface.from_type(AgentType.Laner))
+    assert spec.observation_adapter(3) == 3 and spec.reward_adapter(None, 2.0) == 2.0
+    assert spec.info_adapter(None, 0, {"a": 1}) == {"a": 1}
+
+
+def test_env_requires_gpu_and_valid_specs():
+    import torch
+    spec = AgentSpec(interface=AgentInterface.from_type(AgentType.Laner))
+    with pytest.raises(ValueError):
+        BatchedHiWayEnv(Scenario("4lane", missions={}), {"A0": spec})
+    if not torch.cuda.is_available():
+        from smarts_b200.engine import SmartsB200Error
+        with pytest.raises(SmartsB200Error):  # no CPU fallback
+            HiWayEnv([Scenario("4lane", missions=MISSIONS)], {"A0": spec})
+    with pytest.raises(ValueError):
+        make("smarts.env:other-v0")
+
+
+def _specs(itf, ids=("A0", "A1", "A2", "A3")):
+    return {i: AgentSpec(interface=itf, agent_builder=Agent.from_function, agent_params=lambda _: "keep_lane",
+                         reward_adapter=lambda obs, r: 2.0 * r) for i in ids}
+
+
+@pytest.mark.gpu
+def test_hiway_env_step_contract():
+    """reset()/step() return shapes, adapters, dones["__all__"], close() idempotence, errors."""
+    rm = load_map("4lane")
+    itf = AgentInterface.from_type(AgentType.Laner, neighborhood_vehicles=True, lidar=True, ogm=OGM(64, 64, 0.5),
+                                   drivable_area_grid_map=DrivableAreaGridMap(64, 64, 0.5), max_episode_steps=12)
+    specs = _specs(itf)
+    traffic = scenario_gen.SocialTraffic(rm, 1, 10, 3)
+    env = make("smarts.env:hiway-v0", scenarios=[Scenario(rm, MISSIONS, traffic, n_social=10)], agent_specs=specs)
+    with pytest.raises(SMARTSNotSetupError):
+        env.step({})
+    obs = env.reset()
+    assert set(obs) == set(specs) and all(isinstance(o, Observation) for o in obs.values())
+    o = obs["A0"]
+    assert o.step_count == 0 and o.ego_vehicle_state.lane_id is not None and o.ego_vehicle_state.road_id == "edge-south-SN"
+    assert len(o.waypoint_paths) >= 1 and max(len(p) for p in o.waypoint_paths) == 33   # lookahead 32 + 1
+    assert o.occupancy_grid_map.data.shape == (64, 64, 1) and o.occupancy_grid_map.data[32, 32, 0] == 255
+    assert o.drivable_area_grid_map.metadata.resolution == 0.5
+    pts, hits, rays = o.lidar_point_cloud
+    assert len(pts) == len(hits) == len(rays) == 300
+    agents = {i: s.build_agent() for i, s in specs.items()}
+    total = {i: 0.0 for i in specs}
+    for t in range(12):
+        acts = {i: agents[i].act(obs[i]) for i in obs}
+        obs, rewards, dones, infos = env.step(acts)
+        for i, r in rewards.items():
+            total[i] += r
+            assert infos[i]["env_obs"].step_count == t + 1
+    assert dones["__all__"] and all(dones[i] for i in specs)                        # max_episode_steps
+    assert obs["A0"].events.reached_max_episode_steps
+    for i in specs:  # reward adapter doubled the trip-meter increments; score is the trip meter
+        assert total[i] == pytest.approx(2.0 * infos[i]["score"], rel=1e-12) and infos[i]["score"] > 3.0
+    env.close(); env.close()
+    with pytest.raises(SMARTSDestroyedError):
+        env.step({})
+
+
+@pytest.mark.gpu
+def test_batched_env_auto_reset_and_tensor_path_agree():
+    """ParallelEnv surface: per-env dicts, auto-reset on dones['__all__']; the device-tensor path gives the
+    same rewards as the dict path."""
+    import torch
+    rm = load_map("4lane")
+    itf = AgentInterface.from_type(AgentType.LanerWithSpeed, max_episode_steps=5)
+    E = 6
+    sc = Scenario(rm, MISSIONS, None, 0)
+    env = BatchedHiWayEnv(sc, _specs(itf), n_envs=E, start_jitter=20.0, seed=5)
+    assert env.batch_size == E and env.seed(5) == [5 + i for i in range(E)]
+    obs = env.reset()
+    assert len(obs) == E and set(obs[0]) == set(MISSIONS)
+    rew_hist = []
+    for t in range(5):
+        obs, rew, dones, infos = env.step([{i: (8.0, 0) for i in ob} for ob in obs])
+        rew_hist.append(np.array([[rew[e][i] for i in MISSIONS] for e in range(E)]))
+    assert all(d["__all__"] for d in dones)
+    assert all(ob["A0"].step_count == 0 for ob in obs)            # auto-reset: fresh observations
+    obs, rew, dones, infos = env.step([{i: (8.0, 0) for i in ob} for ob in obs])
+    assert not any(d["__all__"] for d in dones) and obs[0]["A1"].step_count == 1
+    env.close()
+    env2 = BatchedHiWayEnv(sc, _specs(itf), n_envs=E, start_jitter=20.0, seed=5)
+    env2.reset_tensor()
+    act = torch.tensor([[8.0, 0.0]], dtype=torch.float64, device="cuda").repeat(E * 4, 1)
+    for t in range(5):
+        out = env2.step_tensor(act)
+        torch.cuda.synchronize()
+        assert np.array_equal(2.0 * out["ev_reward"].cpu().numpy(), rew_hist[t])
+    assert len(env2.auto_reset_done_envs()) == E
+    env2.close()
