@@ -176,14 +176,13 @@ def run_reference(args, w):
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    E_s = max(threads, 16)
-    # calibrate the per-step sample so steps+warmup finish within ~2 minutes
-    rate, _ = cpu_run(w, E_s, 2, threads)
-    per_step_agents = E_s * w["A"]
-    budget = 90.0 / max(args.steps + args.warmup, 1)
-    while per_step_agents / rate > budget and E_s > threads:
+    # each step = the whole workload (every env of the per-GPU batch, one tick) unless that would not fit a
+    # few minutes on this host, in which case the per-step sample is halved until it does
+    E_s = w["E"]
+    rate, _ = cpu_run(w, max(threads, 16), 2, threads)
+    budget = 150.0 / max(args.steps + args.warmup, 1)
+    while E_s * w["A"] / rate > budget and E_s > threads:
         E_s //= 2
-        per_step_agents = E_s * w["A"]
     cpu_run(w, E_s, max(args.warmup, 1), threads)
     value, dt = cpu_run(w, E_s, args.steps, threads)
     sample = f"{E_s} envs x {w['A']} agents per step, {args.steps} steps, oracle port on {threads} threads"
@@ -284,7 +283,10 @@ def main():
     act_host = torch.zeros((E, A), dtype=torch.int32).pin_memory()
     soc_host = torch.from_numpy(rec_host).pin_memory()
     h2d = act_host.numel() * 4 + soc_host[0].numel() * 8
-    d2h = sum(t.numel() * t.element_size() for t in host_obs.values())
+    obs_host_bytes = sum(t.numel() * t.element_size() for t in host_obs.values())
+    # bytes that cross PCIe: the 0/255 grids travel as 1 bit per pixel (sb_copy_obs_to_host) and are widened
+    # to the uint8 StdObs layout by host threads inside the call; every other buffer is copied as is
+    d2h = sum(t.numel() * t.element_size() // (8 if k in ("ogm", "dagm") else 1) for k, t in host_obs.items())
     eng.step_host(act_host.numpy(), soc_host[0].numpy()); eng.copy_obs_to_host(host_obs)  # warm
     torch.cuda.synchronize()
     if world > 1:
@@ -325,7 +327,7 @@ def main():
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": w["desc"], "envs_per_gpu": E, "agents_per_env": A, "social_per_env": M,
-                       "l2": "outputs (%.2f GB/step/GPU) exceed the 126 MB L2, no flush needed" % (d2h / 1e9),
+                       "l2": "outputs (%.2f GB/step/GPU) exceed the 126 MB L2, no flush needed" % (obs_host_bytes / 1e9),
                        "algorithmic_bytes_per_agent_step": step_bytes,
                        "step_hbm_gbs_per_gpu": step_gbs, "step_frac_of_peak": step_gbs / peak,
                        "kernel_ms_per_step": {k: v[0] / max(v[1], 1) for k, v in ktimes.items() if v[1]}},
@@ -333,14 +335,15 @@ def main():
                          "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                          "bytes_per_launch": per_launch, "ms_per_launch": d_ms / max(d_n, 1)},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "steps": Ke},
+                    "host_obs_bytes_per_step": obs_host_bytes, "steps": Ke,
+                    "transport": "grids bit-packed over PCIe, widened to uint8 in host memory by the library"},
             "gpu_launches": int(launches), "clocks": clocks,
         }
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
-            E_s = max(threads, 16)
-            rate, _ = cpu_run(w, E_s, 2, threads)
-            ticks = int(min(max(12.0 * rate / (E_s * A), 3), 200))
+            rate, _ = cpu_run(w, max(threads, 16), 2, threads)
+            ticks = 20  # ~15 s of CPU work: as many envs of the workload as that allows, 20 ticks each
+            E_s = int(min(max(15.0 * rate / (A * ticks), threads), E))
             v, dt = cpu_run(w, E_s, ticks, threads)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
                                     "sample": f"{E_s} envs x {A} agents x {ticks} ticks of the same workload "

@@ -241,7 +241,9 @@ int sb_observe(SbHandle h, void *stream);
 int sb_step_host(SbHandle h, const void *host_actions, int64_t action_bytes,
                  const double *host_social);
 /* The other half of the host-buffer call: copy every enabled observation buffer to the HOST
- * pointers in *host_dst (NULL members are skipped) and synchronise.  Layouts as SbObsPtrs. */
+ * pointers in *host_dst (NULL members are skipped) and synchronise.  Layouts as SbObsPtrs.
+ * The grids (0 / 255 pixels) cross PCIe as 1 bit per pixel and are widened to uint8 by a pool of
+ * host threads while later chunks are still in flight; every other buffer is a plain copy. */
 int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs *host_dst);
 int sb_get_obs(SbHandle h, SbObsPtrs *out);
 int sb_get_state(SbHandle h, SbStatePtrs *out);
@@ -257,7 +259,8 @@ int64_t sb_launch_count(SbHandle h);
 #define SB_K_LIDAR 3
 #define SB_K_RASTER 4
 #define SB_K_EVENTS 5
-#define SB_K_COUNT 6
+#define SB_K_PACK 6    /* k_pack_bits: grid transport of sb_copy_obs_to_host */
+#define SB_K_COUNT 7
 int sb_set_timing(SbHandle h, int on);
 int sb_collect_timing(SbHandle h, double *ms_sum /*[SB_K_COUNT]*/, int64_t *count /*[SB_K_COUNT]*/);
 const char *sb_last_error(SbHandle h);

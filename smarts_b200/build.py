@@ -14,7 +14,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libsmartsb200.so")
 SOURCES = ["sb_api.cu"]
-DEPS = ["sb_api.cu", "sb_lidar.cuh", "sb_kernels.cuh", "sb_control.cuh", "sb_waypoints.cuh", "sb_device.cuh", "sb_raster.cuh",
+HOST_SOURCES = ["sb_hostxfer.cpp"]  # g++ (AVX-512 target attributes), linked into the same library
+DEPS = ["sb_api.cu", "sb_hostxfer.cpp", "sb_events.cuh", "sb_lidar.cuh", "sb_kernels.cuh", "sb_control.cuh", "sb_waypoints.cuh", "sb_device.cuh", "sb_raster.cuh",
         os.path.join("..", "..", "include", "smarts_b200.h"), os.path.join("..", "..", "include", "sb_detmath.h")]
 
 
@@ -35,12 +36,21 @@ def is_stale() -> bool:
 def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not is_stale():
         return OUT
+    objs = []
+    for src in HOST_SOURCES:
+        obj = os.path.join(CSRC, os.path.splitext(src)[0] + ".o")
+        res = subprocess.run(["g++", "-O3", "-std=c++17", "-fPIC", "-pthread", "-c", os.path.join(CSRC, src), "-o", obj],
+                             capture_output=True, text=True)
+        if res.returncode != 0:
+            sys.stderr.write(res.stdout + res.stderr)
+            raise RuntimeError("g++ failed")
+        objs.append(obj)
     cmd = [
         nvcc_path(), "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
         "-fmad=false", "--expt-extended-lambda", "-Xcompiler", "-fPIC", "-shared",
         "-Xptxas", "-v" if verbose else "-O3",
         "-o", OUT,
-    ] + [os.path.join(CSRC, s) for s in SOURCES]
+    ] + [os.path.join(CSRC, s) for s in SOURCES] + objs
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:
         sys.stderr.write(res.stdout + res.stderr)

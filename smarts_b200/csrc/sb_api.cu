@@ -9,7 +9,19 @@
 #include <string>
 #include <vector>
 
+#include <chrono>
+#include <thread>
+
 #include "sb_kernels.cuh"
+
+// sb_hostxfer.cpp (g++): host threads that widen bit-packed grids back to uint8
+extern "C" {
+void* sbx_pool_create(int threads);
+void sbx_pool_destroy(void* p);
+void sbx_pool_submit(void* p, const uint8_t* bits, uint8_t* out, size_t n_bytes_in, size_t piece);
+void sbx_pool_wait(void* p);
+int sbx_pool_threads(void* p);
+}
 
 struct SbHandle_ {
   SbConfig cfg;
@@ -41,6 +53,12 @@ struct SbHandle_ {
   std::string err;
   size_t raster_smem = 0;
   RasterDims raster_dims{};
+  // grid transport of sb_copy_obs_to_host: device bit image, pinned staging, expansion pool
+  uint32_t* d_bits = nullptr;
+  uint8_t* h_bits = nullptr;
+  size_t bits_bytes = 0;
+  void* pool = nullptr;
+  std::vector<cudaEvent_t> xfer_ev;
 };
 
 namespace {
@@ -75,6 +93,19 @@ bool dev_upload(SbHandle h, const T** dst, const T* src, size_t n) {
   if (n && !cuda_ok(h, cudaMemcpy(q, src, n * sizeof(T), cudaMemcpyHostToDevice), "cudaMemcpy(map)")) return false;
   *dst = q;
   return true;
+}
+
+// One bit per grid pixel (pixels are 0 / 255): thread t packs bytes [32 t, 32 t + 32) into word t,
+// bit i = byte 32 t + i.  Pure streaming: 256-bit loads, 1/8 of that written.
+__global__ void __launch_bounds__(256) k_pack_bits(const uint8_t* __restrict__ src, uint32_t* __restrict__ dst,
+                                                   size_t n_words) {
+  size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n_words) return;
+  const uint4* p = reinterpret_cast<const uint4*>(src) + t * 2;
+  const uint4 a = __ldcs(p), b = __ldcs(p + 1);
+  auto nib = [](uint32_t w) { return ((w & 0x01010101u) * 0x01020408u) >> 24; };
+  dst[t] = nib(a.x) | (nib(a.y) << 4) | (nib(a.z) << 8) | (nib(a.w) << 12) | (nib(b.x) << 16) | (nib(b.y) << 20) |
+           (nib(b.z) << 24) | (nib(b.w) << 28);
 }
 
 __global__ void k_fill(double* p, size_t n, double v) {
@@ -335,6 +366,10 @@ void sb_destroy(SbHandle h) {
   cudaSetDevice(h->cfg.device);
   cudaDeviceSynchronize();
   for (void* p : h->allocs) cudaFree(p);
+  if (h->pool) sbx_pool_destroy(h->pool);
+  if (h->h_bits) cudaFreeHost(h->h_bits);
+  for (auto e : h->xfer_ev) cudaEventDestroy(e);
+  for (auto e : h->ev_pool) cudaEventDestroy(e);
   delete h;
 }
 
@@ -626,6 +661,57 @@ int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs* dst) {
   auto cpy = [&](void* d, const void* s, size_t bytes) {
     if (ok && d && s && bytes) ok = cuda_ok(h, cudaMemcpyAsync(d, s, bytes, cudaMemcpyDeviceToHost, 0), "D2H obs");
   };
+  // Grids: packed to 1 bit / pixel on the device, copied in chunks, widened by host threads while
+  // the next chunk is in flight (8x fewer PCIe bytes than the byte image).
+  struct Sent { size_t off, len; uint8_t* host; };
+  std::vector<Sent> sent;
+  struct GridJob { const uint8_t* dev; uint8_t* host; size_t bytes; };
+  GridJob jobs[2];
+  int nj = 0;
+  if (c.ogm_enable && dst->ogm) jobs[nj++] = {o.ogm, dst->ogm, na * c.ogm_width * c.ogm_height};
+  if (c.dagm_enable && dst->dagm) jobs[nj++] = {o.dagm, dst->dagm, na * c.dagm_width * c.dagm_height};
+  if (ok && nj) {
+    size_t need = 0;
+    for (int j = 0; j < nj; ++j) need += jobs[j].bytes / 8;  // widths are multiples of 32
+    if (h->bits_bytes < need) {
+      if (h->h_bits) cudaFreeHost(h->h_bits);
+      h->h_bits = nullptr;
+      void* q = nullptr;
+      if (!cuda_ok(h, cudaMalloc(&q, need), "cudaMalloc(bits)")) return SB_ENOMEM;
+      h->allocs.push_back(q);
+      h->d_bits = static_cast<uint32_t*>(q);
+      if (!cuda_ok(h, cudaHostAlloc(&q, need, cudaHostAllocDefault), "cudaHostAlloc(bits)")) return SB_ENOMEM;
+      h->h_bits = static_cast<uint8_t*>(q);
+      h->bits_bytes = need;
+    }
+    if (!h->pool) {
+      unsigned hc = std::thread::hardware_concurrency();
+      h->pool = sbx_pool_create((int)(hc == 0 ? 4 : (hc > 32 ? 32 : hc)));
+    }
+    const size_t chunk = (size_t)8 << 20;  // bytes of bits per D2H chunk (64 MB of pixels)
+    size_t off = 0, n_ev = 0;
+    for (int j = 0; j < nj && ok; ++j) {
+      const size_t words = jobs[j].bytes / 32;
+      {
+        LaunchScope ls(h, SB_K_PACK, 0);
+        k_pack_bits<<<(unsigned)((words + 255) / 256), 256>>>(jobs[j].dev, h->d_bits + off / 4, words);
+      }
+      for (size_t c0 = 0; c0 < words * 4 && ok; c0 += chunk) {
+        const size_t len = words * 4 - c0 < chunk ? words * 4 - c0 : chunk;
+        ok = cuda_ok(h, cudaMemcpyAsync(h->h_bits + off + c0, reinterpret_cast<const uint8_t*>(h->d_bits) + off + c0,
+                                        len, cudaMemcpyDeviceToHost, 0), "D2H grid bits");
+        if (n_ev == h->xfer_ev.size()) {
+          cudaEvent_t e;
+          cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+          h->xfer_ev.push_back(e);
+        }
+        cudaEventRecord(h->xfer_ev[n_ev++], 0);
+        sent.push_back({off + c0, len, jobs[j].host + c0 * 8});
+      }
+      off += words * 4;
+    }
+  }
+  // everything else: plain copies, queued behind the grid chunks so that widening starts at once
   cpy(dst->ego_lane, o.ego_lane, na * 4);
   if (c.nbr_enable) {
     size_t n = na * c.nbr_cap;
@@ -645,16 +731,32 @@ int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs* dst) {
     cpy(dst->lidar_points, o.lidar_points, na * c.lidar_rays * 24);
     cpy(dst->lidar_hits, o.lidar_hits, na * c.lidar_rays);
   }
-  if (c.ogm_enable) cpy(dst->ogm, o.ogm, na * c.ogm_width * c.ogm_height);
-  if (c.dagm_enable) cpy(dst->dagm, o.dagm, na * c.dagm_width * c.dagm_height);
   if (c.events_enable) {
     const DEvOut& q = h->evo;
     cpy(dst->ev_events, q.events, na * 4); cpy(dst->ev_done, q.done, na); cpy(dst->ev_n_collisions, q.n_collisions, na * 4);
     cpy(dst->ev_collidee, q.collidee, na * 4); cpy(dst->ev_distance, q.distance, na * 8);
     cpy(dst->ev_reward, q.reward, na * 8); cpy(dst->ev_steps, q.steps, na * 4);
   }
+  static const bool debug = getenv("SB_DEBUG_XFER") != nullptr;
+  const auto t0 = std::chrono::steady_clock::now();
+  auto ms_since = [&] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); };
+  double t_first = 0, t_last = 0, t_pool = 0;
+  if (ok && !sent.empty()) {
+    for (size_t k = 0; k < sent.size() && ok; ++k) {
+      ok = cuda_ok(h, cudaEventSynchronize(h->xfer_ev[k]), "D2H grid bits wait");
+      if (k == 0) t_first = ms_since();
+      if (ok) sbx_pool_submit(h->pool, h->h_bits + sent[k].off, sent[k].host, sent[k].len, (size_t)128 << 10);
+    }
+    t_last = ms_since();
+    sbx_pool_wait(h->pool);
+    t_pool = ms_since();
+  }
   if (!ok) return SB_ECUDA;
-  return cuda_ok(h, cudaStreamSynchronize(0), "D2H obs sync") ? SB_OK : SB_ECUDA;
+  ok = cuda_ok(h, cudaStreamSynchronize(0), "D2H obs sync");
+  if (debug)
+    fprintf(stderr, "[sb xfer] first chunk %.2f ms, last chunk %.2f ms, widened %.2f ms, all copies %.2f ms (%d threads)\n",
+            t_first, t_last, t_pool, ms_since(), h->pool ? sbx_pool_threads(h->pool) : 0);
+  return ok ? SB_OK : SB_ECUDA;
 }
 
 int sb_set_timing(SbHandle h, int on) {

@@ -1,0 +1,157 @@
+// sb_hostxfer.cpp -- host half of the grid transport of sb_copy_obs_to_host.
+//
+// OGM / DrivableAreaGridMap pixels are 0 or 255 (sensors.py:702-716, :744-758), so the grids
+// cross PCIe as 1 bit per pixel (k_pack_bits in sb_api.cu) and are widened back to the uint8
+// layout of StdObs (format_obs.py:108-110, :176-178) here, by a small pool of host threads that
+// works on chunk c while chunk c + 1 is still in flight.  This is transport decoding only: no
+// observation is computed on the CPU.
+//
+// Compiled by g++ (not nvcc) so that the AVX-512 body can use target attributes.
+#include <atomic>
+#include <condition_variable>
+#include <cstdint>
+#include <cstring>
+#include <mutex>
+#include <thread>
+#include <vector>
+
+#if defined(__x86_64__)
+#include <immintrin.h>
+#endif
+
+namespace {
+
+typedef void (*ExpandFn)(const uint8_t* bits, uint8_t* out, size_t n_bytes_in);
+
+uint64_t g_lut[256];
+std::once_flag g_lut_once;
+
+void init_lut() {
+  for (int v = 0; v < 256; ++v) {
+    uint64_t w = 0;
+    for (int b = 0; b < 8; ++b)
+      if (v & (1 << b)) w |= (uint64_t)0xff << (8 * b);
+    g_lut[v] = w;
+  }
+}
+
+// portable body: one 8-byte store per input byte
+void expand_lut(const uint8_t* bits, uint8_t* out, size_t n) {
+  uint64_t* o = reinterpret_cast<uint64_t*>(out);
+  for (size_t i = 0; i < n; ++i) o[i] = g_lut[bits[i]];
+}
+
+#if defined(__x86_64__)
+// 64 pixels per instruction: mask -> byte vector, written with non-temporal stores (the output is
+// not read again by this thread and is 8x the input, so it should not displace the cache)
+__attribute__((target("avx512f,avx512bw"))) void expand_avx512(const uint8_t* bits, uint8_t* out, size_t n) {
+  size_t i = 0;
+  if ((reinterpret_cast<uintptr_t>(out) & 63) == 0) {
+    for (; i + 8 <= n; i += 8) {
+      uint64_t m;
+      std::memcpy(&m, bits + i, 8);
+      _mm512_stream_si512(reinterpret_cast<__m512i*>(out + i * 8), _mm512_movm_epi8((__mmask64)m));
+    }
+    _mm_sfence();
+  } else {
+    for (; i + 8 <= n; i += 8) {
+      uint64_t m;
+      std::memcpy(&m, bits + i, 8);
+      _mm512_storeu_si512(out + i * 8, _mm512_movm_epi8((__mmask64)m));
+    }
+  }
+  if (i < n) expand_lut(bits + i, out + i * 8, n - i);
+}
+#endif
+
+ExpandFn pick_expand() {
+  std::call_once(g_lut_once, init_lut);
+#if defined(__x86_64__)
+  if (__builtin_cpu_supports("avx512bw") && __builtin_cpu_supports("avx512f")) return expand_avx512;
+#endif
+  return expand_lut;
+}
+
+struct Piece {
+  const uint8_t* bits;
+  uint8_t* out;
+  size_t n;
+};
+
+}  // namespace
+
+// A fixed pool; submit() queues pieces, wait() blocks until every queued piece is done.
+class SbExpandPool {
+ public:
+  explicit SbExpandPool(int threads) : fn_(pick_expand()) {
+    if (threads < 1) threads = 1;
+    for (int i = 0; i < threads; ++i) workers_.emplace_back([this] { run(); });
+  }
+  ~SbExpandPool() {
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      stop_ = true;
+    }
+    cv_.notify_all();
+    for (auto& t : workers_) t.join();
+  }
+  void submit(const uint8_t* bits, uint8_t* out, size_t n, size_t piece) {
+    std::lock_guard<std::mutex> lk(mu_);
+    for (size_t off = 0; off < n; off += piece) {
+      queue_.push_back(Piece{bits + off, out + off * 8, n - off < piece ? n - off : piece});
+      ++pending_;
+    }
+    cv_.notify_all();
+  }
+  void wait() {
+    std::unique_lock<std::mutex> lk(mu_);
+    done_cv_.wait(lk, [this] { return pending_ == 0; });
+  }
+  int threads() const { return (int)workers_.size(); }
+
+ private:
+  void run() {
+    for (;;) {
+      Piece p;
+      {
+        std::unique_lock<std::mutex> lk(mu_);
+        cv_.wait(lk, [this] { return stop_ || head_ < queue_.size(); });
+        if (stop_ && head_ >= queue_.size()) return;
+        p = queue_[head_++];
+      }
+      fn_(p.bits, p.out, p.n);
+      {
+        std::lock_guard<std::mutex> lk(mu_);
+        if (--pending_ == 0) {
+          queue_.clear();
+          head_ = 0;
+          done_cv_.notify_all();
+        }
+      }
+    }
+  }
+  ExpandFn fn_;
+  std::vector<std::thread> workers_;
+  std::vector<Piece> queue_;
+  size_t head_ = 0, pending_ = 0;
+  bool stop_ = false;
+  std::mutex mu_;
+  std::condition_variable cv_, done_cv_;
+};
+
+// C-linkage handles for sb_api.cu (which nvcc compiles)
+#define SBX_LOCAL __attribute__((visibility("hidden")))
+extern "C" {
+SBX_LOCAL void* sbx_pool_create(int threads);
+SBX_LOCAL void sbx_pool_destroy(void* p);
+SBX_LOCAL void sbx_pool_submit(void* p, const uint8_t* bits, uint8_t* out, size_t n_bytes_in, size_t piece);
+SBX_LOCAL void sbx_pool_wait(void* p);
+SBX_LOCAL int sbx_pool_threads(void* p);
+void* sbx_pool_create(int threads) { return new SbExpandPool(threads); }
+void sbx_pool_destroy(void* p) { delete static_cast<SbExpandPool*>(p); }
+void sbx_pool_submit(void* p, const uint8_t* bits, uint8_t* out, size_t n_bytes_in, size_t piece) {
+  static_cast<SbExpandPool*>(p)->submit(bits, out, n_bytes_in, piece);
+}
+void sbx_pool_wait(void* p) { static_cast<SbExpandPool*>(p)->wait(); }
+int sbx_pool_threads(void* p) { return static_cast<SbExpandPool*>(p)->threads(); }
+}

@@ -325,3 +325,36 @@ def test_events_off_road_and_wrong_way_poses():
     assert ev[2] & _abi.SB_EV_OFF_ROAD and ev[2] & _abi.SB_EV_ON_SHOULDER
     assert ev[3] & _abi.SB_EV_WRONG_WAY
     _ = fx, fy
+
+
+@pytest.mark.parametrize("pinned", [True, False])
+def test_host_buffer_call_matches_device_views(pinned):
+    """sb_step_host + sb_copy_obs_to_host (the reference-facing call with HOST buffers) against the
+    zero-copy device views and the oracle: the grids cross PCIe bit-packed and are widened on the
+    host, every other buffer is copied as is -- results must be identical, for pinned and for
+    unaligned pageable destinations, on grids whose size is not a multiple of the chunking."""
+    import torch
+    rm = load_map("4lane")
+    E, A, M = 37, 4, 9
+    cfg = make_cfg(E=E, A=A, M=M, nbr=True, wp=True, lidar=True, wall=1.5, ogm=(96, 40, 0.3), dagm=(160, 72, 0.2),
+                   route_cap=16, events=True)
+    x, y, h, v, route, rlen = scenario_gen.agent_starts(rm, E, MISSIONS_4LANE, cfg.route_cap, 41, jitter=30.0, speed=6.0)
+    traffic = scenario_gen.SocialTraffic(rm, E, M, 42)
+    eng, ora = engine(rm, cfg), oracle_world(rm, cfg, threads=8)
+    for w in (eng, ora):
+        w.reset(x, y, h, v, route, rlen)
+    bufs = eng.host_obs_buffers(pinned=pinned)
+    if not pinned:  # misaligned destinations: views one byte into a larger buffer
+        for k in ("ogm", "dagm"):
+            raw = torch.empty(bufs[k].numel() + 1, dtype=torch.uint8)
+            bufs[k] = raw[1:].view(bufs[k].shape)
+    act = np.random.default_rng(43).integers(0, 4, (E, A)).astype(np.int32)
+    for t in range(4):
+        soc = traffic.states(t)
+        eng.step_host(act, soc)
+        eng.copy_obs_to_host(bufs)
+        ora.set_social(soc); ora.step(act); ora.observe()
+    got = {k: t.numpy() for k, t in bufs.items()}
+    assert_same(got, ora.obs())
+    assert_same(got, eng.obs_numpy())
+    assert got["ogm"].any() and got["dagm"].any()
