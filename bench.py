@@ -50,6 +50,18 @@ WORKLOADS = {
                   ("gneE36", 0, 30.0, "gneE25")],
         cfg=dict(nbr=True, nbr_radius=50.0, wp=True, wp_lookahead=32, route_cap=24),
         desc="scenarios/figure_eight, 4 agents x 256 envs, NeighborhoodVehicles + Waypoints"),
+    # BASELINE.json configs[3] (Lane action here: the Trajectory policy needs the previous observation on the host)
+    "minicity_wp_100_social": dict(
+        map="minicity", E=1024, A=32, M=100, seed=13, missions="random",
+        cfg=dict(wp=True, wp_lookahead=32, route_cap=32),
+        desc="scenarios/minicity, 32 agents x 1024 envs, Waypoints obs, 100 synthetic BoxChassis social vehicles/env"),
+    # BASELINE.json configs[4], one point of the sweep
+    "straight_full_suite_64": dict(
+        map="straight", E=4096, A=16, M=16, seed=17,
+        missions=[("west", k % 3, 4.0 + 5.5 * k, "east") for k in range(16)],
+        cfg=dict(nbr=True, nbr_radius=50.0, wp=True, wp_lookahead=32, lidar=True, wall=1.5, ogm=(64, 64, 50 / 64),
+                 dagm=(64, 64, 50 / 64), route_cap=4),
+        desc="synthetic straight road, 16 agents x 4096 envs + 16 social/env, nbr + wp + LiDAR + OGM + DAGM 64x64"),
 }
 
 
@@ -142,6 +154,8 @@ class ClockSampler(threading.Thread):
 
 def build_inputs(w, E, seed_shift=0):
     rm = RoadMapData.load(os.path.join(ROOT, "maps", w["map"] + ".npz"))
+    if w["missions"] == "random":
+        w = dict(w, missions=scenario_gen.random_missions(rm, w["A"], w["seed"], w["cfg"].get("route_cap", 16)))
     x, y, h, v, route, rlen = scenario_gen.agent_starts(rm, E, w["missions"], w["cfg"].get("route_cap", 16),
                                                          w["seed"] + seed_shift, jitter=25.0, speed=8.0)
     traffic = scenario_gen.SocialTraffic(rm, E, w["M"], w["seed"] + 1 + seed_shift)

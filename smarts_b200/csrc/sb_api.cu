@@ -443,6 +443,57 @@ int sb_upload_map(SbHandle h, const SbMap* mp) {
             dev_upload(h, &m.poly_bbox, bbox.data(), bbox.size()) &&
             dev_upload(h, &m.road_edges, mp->road_edges, (size_t)mp->n_edges * 4);
   if (!ok) return SB_ECUDA;
+  m.seg_nx = m.seg_ny = 0;
+  m.seg_x0 = m.seg_y0 = m.seg_inv_cell = m.seg_rmax = 0.0;
+  m.seg_cell_start = m.seg_items = nullptr;
+  if (mp->n_shape_pts > 256) {  // uniform grid over the lane-centre segments (small maps: the full scan is one pass)
+    const double rmax = 12.0, cell = 16.0, eps = 1e-6;
+    double x0 = 1e300, y0 = 1e300, x1 = -1e300, y1 = -1e300;
+    for (int i = 0; i < mp->n_shape_pts; ++i) {
+      x0 = fmin(x0, mp->shape_x[i]); x1 = fmax(x1, mp->shape_x[i]);
+      y0 = fmin(y0, mp->shape_y[i]); y1 = fmax(y1, mp->shape_y[i]);
+    }
+    x0 -= rmax + eps; y0 -= rmax + eps; x1 += rmax + eps; y1 += rmax + eps;
+    const int nx = (int)floor((x1 - x0) / cell) + 1, ny = (int)floor((y1 - y0) / cell) + 1;
+    if ((long long)nx * ny <= (1 << 22)) {
+      const double inv = 1.0 / cell;
+      auto span = [&](double lo, double hi, double o, int n, int* c0, int* c1) {
+        *c0 = std::max(0, (int)floor((lo - rmax - eps - o) * inv));
+        *c1 = std::min(n - 1, (int)floor((hi + rmax + eps - o) * inv));
+      };
+      std::vector<int32_t> cnt((size_t)nx * ny + 1, 0);
+      for (int pass = 0; pass < 2; ++pass) {
+        std::vector<int32_t> fill;
+        std::vector<int32_t> items;
+        if (pass == 1) {
+          for (size_t c2 = 0, acc = 0; c2 <= (size_t)nx * ny; ++c2) {  // exclusive prefix
+            int32_t v = cnt[c2];
+            cnt[c2] = (int32_t)acc;
+            acc += v;
+          }
+          fill.assign(cnt.begin(), cnt.end() - 1);
+          items.resize(cnt.back());
+        }
+        for (int i = 0; i + 1 < mp->n_shape_pts; ++i) {
+          if (shape_lane[i] != shape_lane[i + 1]) continue;
+          int cx0, cx1, cy0, cy1;
+          span(fmin(mp->shape_x[i], mp->shape_x[i + 1]), fmax(mp->shape_x[i], mp->shape_x[i + 1]), x0, nx, &cx0, &cx1);
+          span(fmin(mp->shape_y[i], mp->shape_y[i + 1]), fmax(mp->shape_y[i], mp->shape_y[i + 1]), y0, ny, &cy0, &cy1);
+          for (int cy = cy0; cy <= cy1; ++cy)
+            for (int cx = cx0; cx <= cx1; ++cx) {
+              if (pass == 0) cnt[(size_t)cy * nx + cx]++;
+              else items[fill[(size_t)cy * nx + cx]++] = i;  // ascending segment index within a cell
+            }
+        }
+        if (pass == 1) {
+          if (!dev_upload(h, &m.seg_cell_start, cnt.data(), cnt.size()) ||
+              !dev_upload(h, &m.seg_items, items.data(), items.size()))
+            return SB_ECUDA;
+          m.seg_nx = nx; m.seg_ny = ny; m.seg_x0 = x0; m.seg_y0 = y0; m.seg_inv_cell = inv; m.seg_rmax = rmax;
+        }
+      }
+    }
+  }
   h->raster_dims.n_src = h->raster_dims.n_veh + (h->cfg.dagm_enable ? mp->n_polys : 0);
   h->have_map = true;
   return SB_OK;
@@ -684,9 +735,12 @@ int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs* dst) {
       h->h_bits = static_cast<uint8_t*>(q);
       h->bits_bytes = need;
     }
-    if (!h->pool) {
+    if (!h->pool) {  // host threads: the cores of this box shared by the ranks of a torchrun launch
       unsigned hc = std::thread::hardware_concurrency();
-      h->pool = sbx_pool_create((int)(hc == 0 ? 4 : (hc > 32 ? 32 : hc)));
+      const char* lws = getenv("LOCAL_WORLD_SIZE");
+      const int ranks = lws && atoi(lws) > 0 ? atoi(lws) : 1;
+      int nt = (int)(hc == 0 ? 4 : hc) / ranks;
+      h->pool = sbx_pool_create(nt < 2 ? 2 : (nt > 32 ? 32 : nt));
     }
     const size_t chunk = (size_t)8 << 20;  // bytes of bits per D2H chunk (64 MB of pixels)
     size_t off = 0, n_ev = 0;

@@ -32,6 +32,12 @@ struct DMap {
   const double *poly_x, *poly_y;
   const float* poly_bbox;  // [n_polys,4] xmin,ymin,xmax,ymax rounded outwards
   const double* road_edges;
+  // Uniform grid over the lane-centre segments (built in sb_upload_map): cell (cx, cy) lists every
+  // segment whose bounding box comes within seg_rmax of the cell, so a nearest-lane query of
+  // radius <= seg_rmax reads one list.  seg_nx == 0: no grid (small maps scan everything).
+  double seg_x0, seg_y0, seg_inv_cell, seg_rmax;
+  int32_t seg_nx, seg_ny;
+  const int32_t *seg_cell_start, *seg_items;
 };
 
 struct DState {

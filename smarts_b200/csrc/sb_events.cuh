@@ -292,15 +292,31 @@ k_events(DCfg c, DMap m, DState s, DEvents ev, DEvOut o, int ticked) {
     }
     unsigned on = 0;  // bit k: point k lies on some road
     const double rad = 6.4;  // max(5, 2 * default lane width 3.2), sumo_road_network.py:705
-    for (int i = lane; i + 1 < m.n_shape_pts; i += 32) {
-      const int l = m.shape_lane[i];
-      if (l != m.shape_lane[i + 1]) continue;
-      const double thr = 0.5 * m.lane_width[l] + 1e-1;
-      const double ax = m.shape_x[i], ay = m.shape_y[i], bx = m.shape_x[i + 1], by = m.shape_y[i + 1];
+    if (m.seg_nx != 0 && rad <= m.seg_rmax) {
+      for (int k = 0; k < 5; ++k) {  // each point reads the segment list of its own grid cell
+        const int32_t* items;
+        int n;
+        d_seg_candidates(m, qx[k], qy[k], rad, &items, &n);
+        for (int t = lane; t < n; t += 32) {
+          const int i = items ? items[t] : t;
+          const int l = m.shape_lane[i];
+          if (l != m.shape_lane[i + 1]) continue;
+          const double d = d_dist_point_to_segment(qx[k], qy[k], m.shape_x[i], m.shape_y[i], m.shape_x[i + 1],
+                                                   m.shape_y[i + 1]);
+          if (d < rad && d < 0.5 * m.lane_width[l] + 1e-1) on |= 1u << k;
+        }
+      }
+    } else {
+      for (int i = lane; i + 1 < m.n_shape_pts; i += 32) {
+        const int l = m.shape_lane[i];
+        if (l != m.shape_lane[i + 1]) continue;
+        const double thr = 0.5 * m.lane_width[l] + 1e-1;
+        const double ax = m.shape_x[i], ay = m.shape_y[i], bx = m.shape_x[i + 1], by = m.shape_y[i + 1];
 #pragma unroll
-      for (int k = 0; k < 5; ++k) {
-        const double d = d_dist_point_to_segment(qx[k], qy[k], ax, ay, bx, by);
-        if (d < rad && d < thr) on |= 1u << k;
+        for (int k = 0; k < 5; ++k) {
+          const double d = d_dist_point_to_segment(qx[k], qy[k], ax, ay, bx, by);
+          if (d < rad && d < thr) on |= 1u << k;
+        }
       }
     }
     on = __reduce_or_sync(SB_FULL_MASK, on);

@@ -222,12 +222,35 @@ __device__ __forceinline__ double d_dist_point_to_segment(double px, double py, 
   return sqrt(ex * ex + ey * ey);
 }
 
+// Segment range a query at (px, py) with `radius` has to look at: the whole table, the list of
+// the point's grid cell, or nothing (the point is further than the radius from every segment).
+// Conservative by construction, so results equal the full scan's.
+__device__ __forceinline__ void d_seg_candidates(const DMap& m, double px, double py, double radius,
+                                                 const int32_t** items, int* n) {
+  *items = nullptr;
+  *n = m.n_shape_pts - 1;
+  if (m.seg_nx == 0 || !(radius <= m.seg_rmax)) return;
+  const double gx = (px - m.seg_x0) * m.seg_inv_cell, gy = (py - m.seg_y0) * m.seg_inv_cell;
+  if (!(gx >= 0.0 && gy >= 0.0 && gx < (double)m.seg_nx && gy < (double)m.seg_ny)) {
+    *n = 0;  // the grid covers every segment's box grown by seg_rmax
+    return;
+  }
+  const int cell = (int)gy * m.seg_nx + (int)gx;
+  const int s0 = m.seg_cell_start[cell];
+  *items = m.seg_items + s0;
+  *n = m.seg_cell_start[cell + 1] - s0;
+}
+
 // nearest_lanes(point, radius)[0] (sumo_road_network.py:675-701): the minimum over lanes of the
 // minimum over segments is the minimum over all segments; ties go to the lowest lane index.
 __device__ int d_nearest_lane_warp(const DMap& m, double px, double py, double radius, int lane) {
   double bd = 1e300;
   int bl = 0x7fffffff;
-  for (int i = lane; i + 1 < m.n_shape_pts; i += 32) {
+  const int32_t* items;
+  int n;
+  d_seg_candidates(m, px, py, radius, &items, &n);
+  for (int t = lane; t < n; t += 32) {
+    const int i = items ? items[t] : t;
     int l = m.shape_lane[i];
     if (l != m.shape_lane[i + 1]) continue;
     double d = d_dist_point_to_segment(px, py, m.shape_x[i], m.shape_y[i], m.shape_x[i + 1], m.shape_y[i + 1]);

@@ -89,3 +89,25 @@ def agent_starts(rm: RoadMapData, E: int, missions: Sequence[Tuple[str, int, flo
         for e in range(E):
             x[e, a], y[e, a], h[e, a] = rm.lane_start_pose(road, lane_idx, float(offs[e]))
     return x, y, h, v, route, rlen
+
+
+def random_missions(rm: RoadMapData, A: int, seed: int, route_cap: int, min_len: float = 30.0,
+                    tries: int = 4000) -> List[Tuple[str, int, float, str]]:
+    """A begin/end pairs joined by a route of at most ``route_cap`` roads, on lanes long enough to start
+    10 m in -- stands in for the random missions of large scenarios (scenarios/minicity/scenario.py)."""
+    rng = np.random.default_rng(seed)
+    normal = [r for r in range(len(rm.road_ids)) if not rm.road_is_junction[r]
+              and rm.lane_length[int(rm.road_lane_start[r])] >= min_len and rm.road_lp_count[r] > 0]
+    out: List[Tuple[str, int, float, str]] = []
+    for _ in range(tries):
+        if len(out) == A:
+            break
+        b, e = (int(t) for t in rng.choice(normal, 2, replace=False))
+        r = rm.generate_route(rm.road_ids[b], rm.road_ids[e])
+        if not 1 < len(r.road_indices) <= route_cap:
+            continue
+        lane = int(rng.integers(0, rm.road_lane_count[b]))
+        out.append((rm.road_ids[b], lane, 10.0, rm.road_ids[e]))
+    if len(out) < A:
+        raise RuntimeError(f"only {len(out)} of {A} missions found")
+    return out

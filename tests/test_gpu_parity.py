@@ -358,3 +358,51 @@ def test_host_buffer_call_matches_device_views(pinned):
     assert_same(got, ora.obs())
     assert_same(got, eng.obs_numpy())
     assert got["ogm"].any() and got["dagm"].any()
+
+
+def test_config4_minicity_trajectory_tracking_100_social():
+    """BASELINE configs[3] shape: minicity (52 k lane points), 32 TrajectoryTracking agents per env with
+    100 BoxChassis social vehicles; action = first 10 waypoints of path 0 at 50/3.6 m/s
+    (examples/trajectory_tracking_agent.py:16-37)."""
+    rm = load_map("minicity")
+    E, A, M, N = 2, 32, 100, 10
+    cfg = make_cfg(E=E, A=A, M=M, action_space=_abi.SB_ACTION_TRAJECTORY, traj_len=N, wp=True, wp_len=20,
+                   nbr=True, route_cap=32, events=True)
+    missions = scenario_gen.random_missions(rm, A, 13, cfg.route_cap)
+
+    import torch
+    x, y, h, v, route, rlen = scenario_gen.agent_starts(rm, E, missions, cfg.route_cap, 13, jitter=5.0, speed=5.0)
+    traffic = scenario_gen.SocialTraffic(rm, E, M, 14, p_alive=0.9)
+    eng, ora = engine(rm, cfg), oracle_world(rm, cfg, threads=8)
+    for w in (eng, ora):
+        w.reset(x, y, h, v, route, rlen)
+        w.observe()  # both sides observe exactly once per tick: the trip meter / step counter are stateful
+    for t in range(24):
+        o = ora.obs()
+        act = np.zeros((E, A, 4, N))
+        act[:, :, 0] = o["wp_pos"][:, :, 0, :N, 0]
+        act[:, :, 1] = o["wp_pos"][:, :, 0, :N, 1]
+        act[:, :, 2] = o["wp_heading"][:, :, 0, :N].astype(np.float64)
+        act[:, :, 3] = 50 / 3.6
+        soc = traffic.states(t)
+        eng.set_social(torch.from_numpy(soc).cuda()); ora.set_social(soc)
+        eng.step(torch.from_numpy(act).cuda()); ora.step(act)
+        eng.observe(); ora.observe()
+        assert_same(eng.state_numpy(), ora.state())
+        assert_same(eng.obs_numpy(), ora.obs())
+    assert (ora.obs()["wp_len"][:, :, 0] == 20).mean() > 0.8 and ora.obs()["ev_distance"].mean() > 5.0
+
+
+def test_config5_straight_full_sensor_suite():
+    """BASELINE configs[4] shape: straight road, 16 agents + 16 social per env, every sensor on
+    (nbr r=50, wp 32, LiDAR 300, OGM + DAGM at 64x64 and at 256x256)."""
+    rm = load_map("straight")
+    E, A, M = 6, 16, 16
+    missions = [("west", k % 3, 4.0 + 5.5 * k, "east") for k in range(A)]
+    for grid in ((64, 64, 50 / 64), (256, 256, 0.1)):
+        cfg = make_cfg(E=E, A=A, M=M, nbr=True, nbr_radius=50.0, wp=True, wp_lookahead=32, lidar=True, wall=1.5,
+                       ogm=grid, dagm=grid, route_cap=4, events=True)
+        eng, ora = run_pair(rm, cfg, missions, ticks=12, seed=17, action_fn=lane_actions(E, A, 6), jitter=2.0,
+                            check_every=4)
+        o = ora.obs()
+        assert (o["nbr_count"] > 0).all() and o["lidar_hits"].sum() > 0 and (o["dagm"] == 255).any()
