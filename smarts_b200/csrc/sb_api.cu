@@ -59,6 +59,8 @@ struct SbHandle_ {
   size_t bits_bytes = 0;
   void* pool = nullptr;
   std::vector<cudaEvent_t> xfer_ev;
+  cudaEvent_t xfer_t0 = nullptr, xfer_t1 = nullptr;
+  double xfer_frac = 1.0;  // share of the agents whose grids take the bit-packed path (adapted per call)
 };
 
 namespace {
@@ -709,8 +711,12 @@ int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs* dst) {
   size_t na = (size_t)c.n_envs * c.n_agents;
   cudaSetDevice(c.device);
   bool ok = true;
+  size_t link_total = 0;  // bytes queued on the PCIe link by this call
   auto cpy = [&](void* d, const void* s, size_t bytes) {
-    if (ok && d && s && bytes) ok = cuda_ok(h, cudaMemcpyAsync(d, s, bytes, cudaMemcpyDeviceToHost, 0), "D2H obs");
+    if (ok && d && s && bytes) {
+      ok = cuda_ok(h, cudaMemcpyAsync(d, s, bytes, cudaMemcpyDeviceToHost, 0), "D2H obs");
+      link_total += bytes;
+    }
   };
   // Grids: packed to 1 bit / pixel on the device, copied in chunks, widened by host threads while
   // the next chunk is in flight (8x fewer PCIe bytes than the byte image).
@@ -719,11 +725,21 @@ int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs* dst) {
   struct GridJob { const uint8_t* dev; uint8_t* host; size_t bytes; };
   GridJob jobs[2];
   int nj = 0;
-  if (c.ogm_enable && dst->ogm) jobs[nj++] = {o.ogm, dst->ogm, na * c.ogm_width * c.ogm_height};
-  if (c.dagm_enable && dst->dagm) jobs[nj++] = {o.dagm, dst->dagm, na * c.dagm_width * c.dagm_height};
-  if (ok && nj) {
+  // The first n_packed agents' grids go bit-packed + widened by host threads, the rest as plain byte
+  // copies by the DMA engine, both at once; the split follows the measured rates of the two paths
+  // (host cores and memory bandwidth are shared by the ranks of a box, PCIe links are not).
+  const size_t n_packed = std::min(na, (size_t)llround(h->xfer_frac * (double)na));
+  if (c.ogm_enable && dst->ogm) jobs[nj++] = {o.ogm, dst->ogm, n_packed * c.ogm_width * c.ogm_height};
+  if (c.dagm_enable && dst->dagm) jobs[nj++] = {o.dagm, dst->dagm, n_packed * c.dagm_width * c.dagm_height};
+  if (!h->xfer_t0) {
+    cudaEventCreate(&h->xfer_t0);
+    cudaEventCreate(&h->xfer_t1);
+  }
+  cudaEventRecord(h->xfer_t0, 0);
+  const auto t0 = std::chrono::steady_clock::now();
+  if (ok && nj && n_packed) {
     size_t need = 0;
-    for (int j = 0; j < nj; ++j) need += jobs[j].bytes / 8;  // widths are multiples of 32
+    for (int j = 0; j < nj; ++j) need += (jobs[j].bytes / n_packed) * na / 8;  // room for every agent; widths are multiples of 32
     if (h->bits_bytes < need) {
       if (h->h_bits) cudaFreeHost(h->h_bits);
       h->h_bits = nullptr;
@@ -760,6 +776,7 @@ int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs* dst) {
           h->xfer_ev.push_back(e);
         }
         cudaEventRecord(h->xfer_ev[n_ev++], 0);
+        link_total += len;
         sent.push_back({off + c0, len, jobs[j].host + c0 * 8});
       }
       off += words * 4;
@@ -791,8 +808,14 @@ int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs* dst) {
     cpy(dst->ev_collidee, q.collidee, na * 4); cpy(dst->ev_distance, q.distance, na * 8);
     cpy(dst->ev_reward, q.reward, na * 8); cpy(dst->ev_steps, q.steps, na * 4);
   }
+  size_t direct_bytes = 0;
+  if (n_packed < na) {  // the byte-image share, behind everything else on the link
+    const size_t g0 = (size_t)c.ogm_width * c.ogm_height, g1 = (size_t)c.dagm_width * c.dagm_height;
+    if (c.ogm_enable && dst->ogm) { cpy(dst->ogm + n_packed * g0, o.ogm + n_packed * g0, (na - n_packed) * g0); direct_bytes += (na - n_packed) * g0; }
+    if (c.dagm_enable && dst->dagm) { cpy(dst->dagm + n_packed * g1, o.dagm + n_packed * g1, (na - n_packed) * g1); direct_bytes += (na - n_packed) * g1; }
+  }
+  cudaEventRecord(h->xfer_t1, 0);
   static const bool debug = getenv("SB_DEBUG_XFER") != nullptr;
-  const auto t0 = std::chrono::steady_clock::now();
   auto ms_since = [&] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); };
   double t_first = 0, t_last = 0, t_pool = 0;
   if (ok && !sent.empty()) {
@@ -807,6 +830,27 @@ int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs* dst) {
   }
   if (!ok) return SB_ECUDA;
   ok = cuda_ok(h, cudaStreamSynchronize(0), "D2H obs sync");
+  if (ok && nj) {  // move the split towards the point where both paths finish together
+    float t_link = 0.f;
+    cudaEventElapsedTime(&t_link, h->xfer_t0, h->xfer_t1);
+    size_t grid_bytes = 0, packed_bytes = 0;
+    for (int j = 0; j < nj; ++j) {
+      packed_bytes += jobs[j].bytes;
+      grid_bytes += n_packed ? (jobs[j].bytes / n_packed) * na : 0;
+    }
+    if (!n_packed) grid_bytes = direct_bytes;
+    const double f = h->xfer_frac;
+    if (t_link > 0.05f && grid_bytes) {
+      // link time ~ l0 - l1 f (7/8 of a packed agent's bytes stay off the link), widening time ~ w f
+      const double per_byte = t_link / (double)(link_total > 0 ? link_total : 1);
+      const double l1 = per_byte * grid_bytes * (7.0 / 8.0), l0 = t_link + l1 * f;
+      const double w = (n_packed && t_pool > 0.05) ? t_pool / f : l0;  // no sample yet: assume parity
+      double f_eq = l0 / (w + l1);
+      f_eq = f_eq < 0.05 ? 0.05 : (f_eq > 1.0 ? 1.0 : f_eq);
+      h->xfer_frac = f + 0.5 * (f_eq - f);
+    }
+    if (debug) fprintf(stderr, "[sb xfer] packed share %.3f -> %.3f, link %.2f ms\n", f, h->xfer_frac, t_link);
+  }
   if (debug)
     fprintf(stderr, "[sb xfer] first chunk %.2f ms, last chunk %.2f ms, widened %.2f ms, all copies %.2f ms (%d threads)\n",
             t_first, t_last, t_pool, ms_since(), h->pool ? sbx_pool_threads(h->pool) : 0);
