@@ -59,8 +59,7 @@ struct SbHandle_ {
   size_t bits_bytes = 0;
   void* pool = nullptr;
   std::vector<cudaEvent_t> xfer_ev;
-  cudaEvent_t xfer_t0 = nullptr, xfer_t1 = nullptr;
-  double xfer_frac = 1.0;  // share of the agents whose grids take the bit-packed path (adapted per call)
+  double xfer_frac = 1.0;  // share of the agents whose grids take the bit-packed path (SB_XFER_PACKED_SHARE)
 };
 
 namespace {
@@ -726,16 +725,16 @@ int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs* dst) {
   GridJob jobs[2];
   int nj = 0;
   // The first n_packed agents' grids go bit-packed + widened by host threads, the rest as plain byte
-  // copies by the DMA engine, both at once; the split follows the measured rates of the two paths
-  // (host cores and memory bandwidth are shared by the ranks of a box, PCIe links are not).
+  // copies by the DMA engine, both at once.  Default: everything packed -- on the B200 hosts measured the
+  // call is bound by host-memory write bandwidth either way (profiles/README.md), and packing keeps the
+  // PCIe link free; SB_XFER_PACKED_SHARE=0..1 moves the split for hosts with few cores per GPU.
+  if (const char* sh = getenv("SB_XFER_PACKED_SHARE")) {
+    const double v = atof(sh);
+    h->xfer_frac = v < 0.0 ? 0.0 : (v > 1.0 ? 1.0 : v);
+  }
   const size_t n_packed = std::min(na, (size_t)llround(h->xfer_frac * (double)na));
   if (c.ogm_enable && dst->ogm) jobs[nj++] = {o.ogm, dst->ogm, n_packed * c.ogm_width * c.ogm_height};
   if (c.dagm_enable && dst->dagm) jobs[nj++] = {o.dagm, dst->dagm, n_packed * c.dagm_width * c.dagm_height};
-  if (!h->xfer_t0) {
-    cudaEventCreate(&h->xfer_t0);
-    cudaEventCreate(&h->xfer_t1);
-  }
-  cudaEventRecord(h->xfer_t0, 0);
   const auto t0 = std::chrono::steady_clock::now();
   if (ok && nj && n_packed) {
     size_t need = 0;
@@ -755,7 +754,11 @@ int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs* dst) {
       unsigned hc = std::thread::hardware_concurrency();
       const char* lws = getenv("LOCAL_WORLD_SIZE");
       const int ranks = lws && atoi(lws) > 0 ? atoi(lws) : 1;
+      // every hardware thread of this rank's share: measured best on the B200 host (16 threads 15.0 ms,
+      // 8 threads 17.0 ms, 4 threads 19.7 ms per 2.15 GB of grids); SB_XFER_THREADS overrides
       int nt = (int)(hc == 0 ? 4 : hc) / ranks;
+      const char* forced = getenv("SB_XFER_THREADS");
+      if (forced && atoi(forced) > 0) nt = atoi(forced);
       h->pool = sbx_pool_create(nt < 2 ? 2 : (nt > 32 ? 32 : nt));
     }
     const size_t chunk = (size_t)8 << 20;  // bytes of bits per D2H chunk (64 MB of pixels)
@@ -808,13 +811,11 @@ int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs* dst) {
     cpy(dst->ev_collidee, q.collidee, na * 4); cpy(dst->ev_distance, q.distance, na * 8);
     cpy(dst->ev_reward, q.reward, na * 8); cpy(dst->ev_steps, q.steps, na * 4);
   }
-  size_t direct_bytes = 0;
   if (n_packed < na) {  // the byte-image share, behind everything else on the link
     const size_t g0 = (size_t)c.ogm_width * c.ogm_height, g1 = (size_t)c.dagm_width * c.dagm_height;
-    if (c.ogm_enable && dst->ogm) { cpy(dst->ogm + n_packed * g0, o.ogm + n_packed * g0, (na - n_packed) * g0); direct_bytes += (na - n_packed) * g0; }
-    if (c.dagm_enable && dst->dagm) { cpy(dst->dagm + n_packed * g1, o.dagm + n_packed * g1, (na - n_packed) * g1); direct_bytes += (na - n_packed) * g1; }
+    if (c.ogm_enable && dst->ogm) { cpy(dst->ogm + n_packed * g0, o.ogm + n_packed * g0, (na - n_packed) * g0); }
+    if (c.dagm_enable && dst->dagm) { cpy(dst->dagm + n_packed * g1, o.dagm + n_packed * g1, (na - n_packed) * g1); }
   }
-  cudaEventRecord(h->xfer_t1, 0);
   static const bool debug = getenv("SB_DEBUG_XFER") != nullptr;
   auto ms_since = [&] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); };
   double t_first = 0, t_last = 0, t_pool = 0;
@@ -830,30 +831,10 @@ int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs* dst) {
   }
   if (!ok) return SB_ECUDA;
   ok = cuda_ok(h, cudaStreamSynchronize(0), "D2H obs sync");
-  if (ok && nj) {  // move the split towards the point where both paths finish together
-    float t_link = 0.f;
-    cudaEventElapsedTime(&t_link, h->xfer_t0, h->xfer_t1);
-    size_t grid_bytes = 0, packed_bytes = 0;
-    for (int j = 0; j < nj; ++j) {
-      packed_bytes += jobs[j].bytes;
-      grid_bytes += n_packed ? (jobs[j].bytes / n_packed) * na : 0;
-    }
-    if (!n_packed) grid_bytes = direct_bytes;
-    const double f = h->xfer_frac;
-    if (t_link > 0.05f && grid_bytes) {
-      // link time ~ l0 - l1 f (7/8 of a packed agent's bytes stay off the link), widening time ~ w f
-      const double per_byte = t_link / (double)(link_total > 0 ? link_total : 1);
-      const double l1 = per_byte * grid_bytes * (7.0 / 8.0), l0 = t_link + l1 * f;
-      const double w = (n_packed && t_pool > 0.05) ? t_pool / f : l0;  // no sample yet: assume parity
-      double f_eq = l0 / (w + l1);
-      f_eq = f_eq < 0.05 ? 0.05 : (f_eq > 1.0 ? 1.0 : f_eq);
-      h->xfer_frac = f + 0.5 * (f_eq - f);
-    }
-    if (debug) fprintf(stderr, "[sb xfer] packed share %.3f -> %.3f, link %.2f ms\n", f, h->xfer_frac, t_link);
-  }
   if (debug)
-    fprintf(stderr, "[sb xfer] first chunk %.2f ms, last chunk %.2f ms, widened %.2f ms, all copies %.2f ms (%d threads)\n",
-            t_first, t_last, t_pool, ms_since(), h->pool ? sbx_pool_threads(h->pool) : 0);
+    fprintf(stderr, "[sb xfer] first chunk %.2f ms, last chunk %.2f ms, widened %.2f ms, all copies %.2f ms "
+            "(%d threads, %.1f MB over the link, packed share %.2f)\n",
+            t_first, t_last, t_pool, ms_since(), h->pool ? sbx_pool_threads(h->pool) : 0, link_total / 1e6, h->xfer_frac);
   return ok ? SB_OK : SB_ECUDA;
 }
 

@@ -327,13 +327,15 @@ def test_events_off_road_and_wrong_way_poses():
     _ = fx, fy
 
 
-@pytest.mark.parametrize("pinned", [True, False])
-def test_host_buffer_call_matches_device_views(pinned):
+@pytest.mark.parametrize("pinned,share", [(True, None), (False, None), (True, "0.4"), (True, "0")])
+def test_host_buffer_call_matches_device_views(pinned, share, monkeypatch):
     """sb_step_host + sb_copy_obs_to_host (the reference-facing call with HOST buffers) against the
     zero-copy device views and the oracle: the grids cross PCIe bit-packed and are widened on the
     host, every other buffer is copied as is -- results must be identical, for pinned and for
     unaligned pageable destinations, on grids whose size is not a multiple of the chunking."""
     import torch
+    if share is not None:  # part of the agents' grids as plain byte copies, the rest packed
+        monkeypatch.setenv("SB_XFER_PACKED_SHARE", share)
     rm = load_map("4lane")
     E, A, M = 37, 4, 9
     cfg = make_cfg(E=E, A=A, M=M, nbr=True, wp=True, lidar=True, wall=1.5, ogm=(96, 40, 0.3), dagm=(160, 72, 0.2),
