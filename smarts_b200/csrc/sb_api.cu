@@ -663,7 +663,7 @@ int sb_observe(SbHandle h, void* stream) {
   }
   if (c.lidar_enable) {
     LaunchScope ls(h, SB_K_LIDAR, st);
-    k_lidar<<<na, SB_LIDAR_THREADS, (size_t)c.lidar_rays * sizeof(double), st>>>(c, h->dmap, h->st, h->ob, h->d_rays,
+    k_lidar<<<na, SB_LIDAR_THREADS, 0, st>>>(c, h->dmap, h->st, h->ob, h->d_rays,
                                                                                      h->d_ray_order, h->d_ray_sectors, h->ray_reach);
   }
   if (c.ogm_enable || c.dagm_enable) {

@@ -17,8 +17,8 @@
 //   ray     distance from the box centre to the ray's line / both edge end points on one side
 //           of it (float, a handful of FMAs) before the binary64 test with its divisions.
 //
-// Best t per ray goes to shared memory under the ORIGINAL ray index; a second pass forms the
-// points and writes them with consecutive threads on consecutive rays (24 B apart: coalesced).
+// Every thread writes its own ray's point and hit flag as soon as it is known (no block barrier
+// after the ray loop: a warp that is done retires instead of waiting for the slowest one).
 #pragma once
 
 #include "sb_device.cuh"
@@ -26,7 +26,7 @@
 #define SB_LIDAR_THREADS 320
 #define SB_LIDAR_MAX_BOXES 160
 #define SB_LIDAR_MAX_EDGES 256
-#define SB_LIDAR_MAX_RAYS 4096  // best-t staging: 8 B per ray of dynamic shared memory
+#define SB_LIDAR_MAX_RAYS 4096
 
 struct LBox {
   double x, y, c, s, hw, hl, z0, z1;
@@ -70,12 +70,10 @@ __device__ __forceinline__ bool d_sector_segment(const LSector& q, const LEdgeF&
   return true;
 }
 
-// dynamic shared memory: double tbest[R]
 __global__ void __launch_bounds__(SB_LIDAR_THREADS, 4)
 k_lidar(DCfg c, DMap m, DState s, DObs o, const double* __restrict__ rays, const int32_t* __restrict__ order,
         const LSector* __restrict__ sectors, float reach_xy) {
   // reach_xy: longest horizontal extent of any table ray (+ margin), for the block-level cull
-  extern __shared__ __align__(16) double tbest_sm[];
   __shared__ LBox boxes[SB_LIDAR_MAX_BOXES];
   __shared__ LBoxF boxf[SB_LIDAR_MAX_BOXES];
   __shared__ double edges[SB_LIDAR_MAX_EDGES][4];
@@ -141,6 +139,7 @@ k_lidar(DCfg c, DMap m, DState s, DObs o, const double* __restrict__ rays, const
     s.status[ai] |= SB_STATUS_LIDAR_OVERFLOW;
   const double inf = __longlong_as_double(0x7ff0000000000000LL);
   const int R = c.lidar_rays;
+  const double miss = c.lidar_miss_inf ? inf : 0.0;
 
   for (int base = 0; base < R; base += blockDim.x) {  // blockDim is a multiple of 32: chunks stay warp-aligned
     const int si = base + threadIdx.x;
@@ -233,23 +232,22 @@ k_lidar(DCfg c, DMap m, DState s, DObs o, const double* __restrict__ rays, const
         if (t < tbest) tbest = t;
       }
     }
-    if (act) tbest_sm[r] = tbest;
-  }
-  __syncthreads();
-  const double miss = c.lidar_miss_inf ? inf : 0.0;
-  for (int r = threadIdx.x; r < R; r += blockDim.x) {
-    const double tb = tbest_sm[r];
-    const size_t q = (size_t)ai * R + r;
-    if (tb <= 1.0) {
-      o.lidar_hits[q] = 1;
-      o.lidar_points[q * 3 + 0] = ox + tb * rays[r * 3 + 0];
-      o.lidar_points[q * 3 + 1] = oy + tb * rays[r * 3 + 1];
-      o.lidar_points[q * 3 + 2] = oz + tb * rays[r * 3 + 2];
-    } else {
-      o.lidar_hits[q] = 0;
-      o.lidar_points[q * 3 + 0] = miss;
-      o.lidar_points[q * 3 + 1] = miss;
-      o.lidar_points[q * 3 + 2] = miss;
+    // each warp writes its own rays as soon as they are done: no block barrier, no staging of t;
+    // the agent's 7.5 KB of points fill whole L2 lines within the block's lifetime, so the stride-6
+    // ray order of an azimuth-sorted warp costs L2 transactions, not DRAM traffic
+    if (act) {
+      const size_t q = (size_t)ai * R + r;
+      if (tbest <= 1.0) {
+        o.lidar_hits[q] = 1;
+        o.lidar_points[q * 3 + 0] = ox + tbest * dx;
+        o.lidar_points[q * 3 + 1] = oy + tbest * dy;
+        o.lidar_points[q * 3 + 2] = oz + tbest * dz;
+      } else {
+        o.lidar_hits[q] = 0;
+        o.lidar_points[q * 3 + 0] = miss;
+        o.lidar_points[q * 3 + 1] = miss;
+        o.lidar_points[q * 3 + 2] = miss;
+      }
     }
   }
 }

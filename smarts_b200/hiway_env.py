@@ -263,6 +263,63 @@ class BatchedHiWayEnv:
             self.engine.observe()
         return ids
 
+    # -- StdObs: the dense, batched observation of format_obs.py, on the device -------------------
+    def std_obs(self) -> Dict[str, Any]:
+        """The current observation of every agent as ``StdObs`` (smarts/env/wrappers/format_obs.py:45-197):
+        same keys, dtypes and trailing shapes, with a leading ``[E, A]`` batch and every tensor resident on the
+        GPU.  The big members (grids, lidar point cloud, waypoints, neighbours) are the library's own buffers,
+        not copies; the small ``ego`` / ``events`` members are assembled by a few torch ops.  Use
+        ``wp_out_len=20`` at construction for the 4 x 20 waypoint block of StdObs."""
+        t = self._torch
+        o, s, itf, A = self.engine.obs(), self.engine.state(), self.interface, self.A
+        ego = {k: s[k][:, :A] for k in ("pos_x", "pos_y", "pos_z", "heading", "speed", "yaw_rate", "length", "width", "height")}
+        f32 = t.float32
+        zeros3 = t.zeros((self.E, A, 3), dtype=f32, device=self.engine.device)
+        lane = o["ego_lane"].long()
+        lane_idx = t.as_tensor(self.road_map.lane_idx_in_road, device=self.engine.device)
+        ev = o["ev_events"]
+        bit = lambda b: ((ev & b) != 0).to(t.int8)  # noqa: E731
+        out: Dict[str, Any] = {
+            "dist": o["ev_distance"].to(f32),
+            "ego": {
+                "angular_acceleration": zeros3, "angular_jerk": zeros3, "linear_acceleration": zeros3, "linear_jerk": zeros3,
+                "angular_velocity": t.stack([t.zeros_like(ego["yaw_rate"]), t.zeros_like(ego["yaw_rate"]), ego["yaw_rate"]], -1).to(f32),
+                "box": t.stack([ego["length"], ego["width"], ego["height"]], -1).to(f32),
+                "heading": ego["heading"].to(f32),
+                "lane_index": t.where(lane >= 0, lane_idx[lane.clamp(min=0)], t.zeros_like(lane)).to(t.int8),
+                "linear_velocity": t.stack([-t.sin(ego["heading"]) * ego["speed"], t.cos(ego["heading"]) * ego["speed"],
+                                            t.zeros_like(ego["speed"])], -1).to(f32),
+                "pos": t.stack([ego["pos_x"], ego["pos_y"], ego["pos_z"]], -1),
+                "speed": ego["speed"].to(f32), "steering": s["steering"].to(f32), "yaw_rate": ego["yaw_rate"].to(f32),
+            },
+            "events": {"agents_alive_done": t.zeros_like(ev, dtype=t.int8), "collisions": bit(_abi.SB_EV_COLLISION),
+                       "not_moving": bit(_abi.SB_EV_NOT_MOVING), "off_road": bit(_abi.SB_EV_OFF_ROAD),
+                       "off_route": bit(_abi.SB_EV_OFF_ROUTE), "on_shoulder": bit(_abi.SB_EV_ON_SHOULDER),
+                       "reached_goal": bit(_abi.SB_EV_REACHED_GOAL),
+                       "reached_max_episode_steps": bit(_abi.SB_EV_REACHED_MAX_STEPS), "wrong_way": bit(_abi.SB_EV_WRONG_WAY)},
+        }
+        if itf.drivable_area_grid_map:
+            out["dagm"] = o["dagm"].unsqueeze(-1)
+        if itf.ogm:
+            out["ogm"] = o["ogm"].unsqueeze(-1)
+        if itf.lidar:  # misses are zeros in StdObs (format_obs.py:437-443): construct with lidar_miss_inf=0 or clean here
+            pc = o["lidar_points"]
+            if self.cfg.lidar_miss_inf:
+                pc = t.nan_to_num(pc, nan=0.0, posinf=0.0, neginf=0.0)
+            origin = out["ego"]["pos"].clone()
+            origin[..., 2] += 1.0
+            rays = t.as_tensor(self._base_rays, device=self.engine.device)
+            n = rays.shape[0]
+            org = origin.unsqueeze(2).expand(self.E, A, n, 3)
+            out["lidar"] = {"hit": o["lidar_hits"], "point_cloud": pc, "ray_origin": org, "ray_vector": org + rays}
+        if itf.neighborhood_vehicles:
+            out["neighbors"] = {"box": o["nbr_box"], "heading": o["nbr_heading"], "lane_index": o["nbr_lane_index"],
+                                "pos": o["nbr_pos"], "speed": o["nbr_speed"]}
+        if itf.waypoints:
+            out["waypoints"] = {"heading": o["wp_heading"], "lane_index": o["wp_lane_index"], "lane_width": o["wp_lane_width"],
+                                "pos": o["wp_pos"], "speed_limit": o["wp_speed_limit"]}
+        return out
+
     # -- host-side Observation objects ---------------------------------------------------------
     def _fetch(self):
         self._host = self.engine.obs_numpy()

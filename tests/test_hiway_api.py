@@ -171,3 +171,52 @@ def test_batched_env_auto_reset_and_tensor_path_agree():
         assert np.array_equal(2.0 * out["ev_reward"].cpu().numpy(), rew_hist[t])
     assert len(env2.auto_reset_done_envs()) == E
     env2.close()
+
+
+@pytest.mark.gpu
+def test_std_obs_layout_matches_format_obs():
+    """StdObs keys / dtypes / trailing shapes (format_obs.py:45-197, :313-376) on the device, and agreement
+    with the per-agent Observation objects of the dict path."""
+    import torch
+    rm = load_map("4lane")
+    itf = AgentInterface.from_type(AgentType.Laner, neighborhood_vehicles=NeighborhoodVehicles(radius=50), lidar=True,
+                                   ogm=OGM(64, 64, 0.5), drivable_area_grid_map=DrivableAreaGridMap(64, 64, 0.5))
+    E = 3
+    env = BatchedHiWayEnv(Scenario(rm, MISSIONS, scenario_gen.SocialTraffic(rm, E, 12, 8), n_social=12), _specs(itf),
+                          n_envs=E, wp_out_len=20, start_jitter=10.0)
+    obs = env.reset()
+    for _ in range(3):
+        obs, _, _, _ = env.step([{i: "keep_lane" for i in ob} for ob in obs])
+    so = env.std_obs()
+    torch.cuda.synchronize()
+    A = 4
+    want = {"dist": ((), torch.float32), "dagm": ((64, 64, 1), torch.uint8), "ogm": ((64, 64, 1), torch.uint8)}
+    for k, (shp, dt) in want.items():
+        assert tuple(so[k].shape) == (E, A) + shp and so[k].dtype == dt, k
+    ego = {"angular_acceleration": (3,), "angular_jerk": (3,), "angular_velocity": (3,), "box": (3,), "heading": (),
+           "lane_index": (), "linear_acceleration": (3,), "linear_jerk": (3,), "linear_velocity": (3,), "pos": (3,),
+           "speed": (), "steering": (), "yaw_rate": ()}
+    assert set(so["ego"]) == set(ego)
+    for k, shp in ego.items():
+        dt = torch.float64 if k == "pos" else (torch.int8 if k == "lane_index" else torch.float32)
+        assert tuple(so["ego"][k].shape) == (E, A) + shp and so["ego"][k].dtype == dt, k
+    assert set(so["events"]) == {"agents_alive_done", "collisions", "not_moving", "off_road", "off_route", "on_shoulder",
+                                 "reached_goal", "reached_max_episode_steps", "wrong_way"}
+    assert all(v.dtype == torch.int8 and tuple(v.shape) == (E, A) for v in so["events"].values())
+    lid = so["lidar"]
+    assert tuple(lid["hit"].shape) == (E, A, 300) and lid["hit"].dtype == torch.int8
+    for k in ("point_cloud", "ray_origin", "ray_vector"):
+        assert tuple(lid[k].shape) == (E, A, 300, 3) and lid[k].dtype == torch.float64
+    assert torch.isfinite(lid["point_cloud"]).all()
+    nb = so["neighbors"]
+    assert tuple(nb["pos"].shape) == (E, A, 10, 3) and nb["pos"].dtype == torch.float64 and nb["lane_index"].dtype == torch.int8
+    wp = so["waypoints"]
+    assert tuple(wp["pos"].shape) == (E, A, 4, 20, 3) and tuple(wp["heading"].shape) == (E, A, 4, 20)
+    # agreement with the Observation objects
+    o = obs[1]["A2"]
+    assert np.allclose(so["ego"]["pos"][1, 2].cpu().numpy(), o.ego_vehicle_state.position)
+    assert so["ego"]["lane_index"][1, 2].item() == o.ego_vehicle_state.lane_index
+    assert np.float32(o.distance_travelled) == so["dist"][1, 2].item()
+    assert np.array_equal(so["ogm"][1, 2].cpu().numpy(), o.occupancy_grid_map.data)
+    assert np.allclose(lid["ray_vector"][1, 2, 7].cpu().numpy(), o.lidar_point_cloud[2][7][1])
+    env.close()
