@@ -81,6 +81,11 @@ def make_cfg(E, A, M, device, **kw):
         c.ogm_enable, c.ogm_width, c.ogm_height, c.ogm_resolution = (1,) + tuple(kw["ogm"])
     if kw.get("dagm"):
         c.dagm_enable, c.dagm_width, c.dagm_height, c.dagm_resolution = (1,) + tuple(kw["dagm"])
+    if kw.get("events"):  # Events + done flags + trip-meter reward, DoneCriteria defaults (agent_interface.py:185-206)
+        c.events_enable = 1
+        c.done_mask = _abi.SB_EV_COLLISION | _abi.SB_EV_OFF_ROAD | _abi.SB_EV_OFF_ROUTE
+        c.max_episode_steps = 0
+        c.not_moving_time, c.not_moving_distance = 60.0, 1.0
     return c
 
 
@@ -222,12 +227,16 @@ def main():
     ap.add_argument("--envs", type=int, default=0, help="override envs per GPU")
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--events", action="store_true", help="also compute Events / dones / trip-meter rewards (k_events)")
     ap.add_argument("--no-kernel-timing", action="store_true",
                     help="do not bracket every kernel with CUDA events inside the timed region (no roofline object)")
     args = ap.parse_args()
     w = dict(WORKLOADS[args.workload])
     if args.envs:
         w["E"] = args.envs
+    if args.events:
+        w["cfg"] = dict(w["cfg"], events=True)
+        w["desc"] += ", events + rewards"
     if args.impl == "reference":
         return run_reference(args, w)
 
@@ -316,6 +325,29 @@ def main():
         dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
     e2e_value = world * E * A * Ke / float(e2e_t.item())
 
+    # ---- informational: the same step with Events / dones / trip-meter rewards also computed (k_events)
+    ms_events = None
+    if not args.events and world == 1:
+        cfg_e = make_cfg(E, A, M, local, **dict(w["cfg"], events=True))
+        eng_e = Engine(cfg_e, rm, lidar_params.base_rays(lidar_params.BasicLidar))
+        eng_e.reset(*init)
+
+        def tick_e(t):
+            eng_e.set_social(rec[t % T])
+            eng_e.step(actions)
+            eng_e.observe()
+        for t in range(W_):
+            tick_e(t)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for t in range(10):
+            tick_e(W_ + t)
+        e1.record()
+        torch.cuda.synchronize()
+        ms_events = e0.elapsed_time(e1) / 10
+        eng_e.close()
+
     if rank == 0:
         peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
         if os.path.exists(peaks_path):
@@ -344,7 +376,8 @@ def main():
                        "l2": "outputs (%.2f GB/step/GPU) exceed the 126 MB L2, no flush needed" % (obs_host_bytes / 1e9),
                        "algorithmic_bytes_per_agent_step": step_bytes,
                        "step_hbm_gbs_per_gpu": step_gbs, "step_frac_of_peak": step_gbs / peak,
-                       "kernel_ms_per_step": {k: v[0] / max(v[1], 1) for k, v in ktimes.items() if v[1]}},
+                       "kernel_ms_per_step": {k: v[0] / max(v[1], 1) for k, v in ktimes.items() if v[1]},
+                       "ms_per_step_with_events_and_rewards": ms_events},
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                          "bytes_per_launch": per_launch, "ms_per_launch": d_ms / max(d_n, 1)},

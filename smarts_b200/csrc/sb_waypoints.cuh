@@ -9,6 +9,8 @@
 
 #include "sb_device.cuh"
 
+#define SB_WP_CAND 64
+
 struct WarpPaths {
   int32_t lp[SB_MAX_PATHS][SB_MAX_LOOKAHEAD + 1];  // lane-point indices of each path
   int32_t len[SB_MAX_PATHS];
@@ -20,6 +22,9 @@ struct WarpPaths {
   int32_t seg_first[SB_MAX_LOOKAHEAD + 1], seg_cnt[SB_MAX_LOOKAHEAD + 1], seg_before[SB_MAX_LOOKAHEAD + 1],
       seg_cursor[SB_MAX_LOOKAHEAD + 1];
   uint8_t seg_had[SB_MAX_LOOKAHEAD + 1];
+  // candidate set of wp_closest_with_pose (lane points within a small disc around the nearest one)
+  double cand_d[SB_WP_CAND];
+  int32_t cand_i[SB_WP_CAND];
 };
 
 struct DWaypoint {
@@ -47,25 +52,78 @@ __device__ int wp_closest_in_range(const DMap& m, int start, int count, double x
   return bi == 0x7fffffff ? -1 : bi;
 }
 
-// lanepoints.py:526-623: closest_lanepoints([pose], within_radius, maximum_count=10)[0]
-__device__ int wp_closest_with_pose(const DMap& m, double x, double y, double h, double within_radius, int lane) {
+// lanepoints.py:526-623: closest_lanepoints([pose], within_radius, maximum_count=10)[0].
+// The KD-tree's k = 10 query is the 10 smallest (distance, index) pairs.  One scan finds the nearest
+// point, a second one gathers every point within 4 m more than that into shared memory (ballot
+// compaction); when that set holds at least k points the k smallest are among them, and the ten
+// selection rounds run on <= 64 candidates instead of the whole table.  Otherwise (sparse or very
+// dense neighbourhood) the rounds scan the table, as before.  Same distances, same ties: same result.
+__device__ int wp_closest_with_pose(const DMap& m, double x, double y, double h, double within_radius, int lane,
+                                    WarpPaths* wp) {
   const int P = m.n_lanepoints;
   const int k = P < 10 ? P : 10;
   int idx[10];
   double d2[10];
   int n = 0;
+  int n_cand = -1;  // < 0: scan the table
+  {
+    double bd = 1e300;
+    int bi = 0x7fffffff;
+    for (int i = lane; i < P; i += 32) {
+      double d = wp_sqdist(m, i, x, y);
+      if (d < bd) {
+        bd = d;
+        bi = i;
+      }
+    }
+    warp_argmin(bd, bi);
+    if (bi == 0x7fffffff) return -1;
+    const double reach = sqrt(bd) + 4.0, T = reach * reach;
+    int cnt = 0;
+    for (int i0 = 0; i0 < P; i0 += 32) {
+      const int i = i0 + lane;
+      double d = 0.0;
+      bool in = false;
+      if (i < P) {
+        d = wp_sqdist(m, i, x, y);
+        in = d <= T;
+      }
+      const unsigned bal = __ballot_sync(SB_FULL_MASK, in);
+      const int pos = cnt + __popc(bal & ((1u << lane) - 1u));
+      if (in && pos < SB_WP_CAND) {
+        wp->cand_d[pos] = d;
+        wp->cand_i[pos] = i;
+      }
+      cnt += __popc(bal);
+    }
+    __syncwarp();
+    if (cnt >= k && cnt <= SB_WP_CAND) n_cand = cnt;
+  }
   double last_d = -1.0;
   int last_i = -1;
   for (int r = 0; r < k; ++r) {
     double bd = 1e300;
     int bi = 0x7fffffff;
-    for (int i = lane; i < P; i += 32) {
-      double d = wp_sqdist(m, i, x, y);
-      bool after = (d > last_d) || (d == last_d && i > last_i);
-      if (r > 0 && !after) continue;
-      if (d < bd) {
-        bd = d;
-        bi = i;
+    if (n_cand >= 0) {
+      for (int t = lane; t < n_cand; t += 32) {
+        const double d = wp->cand_d[t];
+        const int i = wp->cand_i[t];
+        const bool after = (d > last_d) || (d == last_d && i > last_i);
+        if (r > 0 && !after) continue;
+        if (d < bd || (d == bd && i < bi)) {
+          bd = d;
+          bi = i;
+        }
+      }
+    } else {
+      for (int i = lane; i < P; i += 32) {
+        double d = wp_sqdist(m, i, x, y);
+        bool after = (d > last_d) || (d == last_d && i > last_i);
+        if (r > 0 && !after) continue;
+        if (d < bd) {
+          bd = d;
+          bi = i;
+        }
       }
     }
     warp_argmin(bd, bi);
@@ -76,6 +134,7 @@ __device__ int wp_closest_with_pose(const DMap& m, double x, double y, double h,
     last_d = bd;
     last_i = bi;
   }
+  __syncwarp();
   // every lane holds the same list; finish redundantly (tiny)
   int best = -1;
   double bk = 0.0;
@@ -278,7 +337,7 @@ __device__ void wp_waypoint_paths(const DMap& m, double x, double y, double h, i
   const int32_t* roads = route;
   int nr = route_len;
   if (route_len == 0) {
-    int lp = wp_closest_with_pose(m, x, y, h, -1.0, lane);
+    int lp = wp_closest_with_pose(m, x, y, h, -1.0, lane, wp);
     nr = 0;
     if (lp >= 0) {
       int road = m.lane_road[m.lp_lane[lp]];
@@ -313,7 +372,7 @@ __device__ void wp_waypoint_paths(const DMap& m, double x, double y, double h, i
       return;
     }
   }
-  int lp = wp_closest_with_pose(m, x, y, h, within_radius, lane);
+  int lp = wp_closest_with_pose(m, x, y, h, within_radius, lane, wp);
   if (lp < 0) return;
   wp_paths_on_road(m, m.lane_road[m.lp_lane[lp]], x, y, lookahead, nullptr, 0, wp, lane);
 }
