@@ -408,3 +408,28 @@ def test_config5_straight_full_sensor_suite():
                             check_every=4)
         o = ora.obs()
         assert (o["nbr_count"] > 0).all() and o["lidar_hits"].sum() > 0 and (o["dagm"] == 255).any()
+
+
+def test_maximum_grid_sizes_and_multi_pass_rows():
+    """Grids at the limits of the rasteriser: 1024 columns (four 256-column passes), more than 256 rows (several
+    row passes), the narrowest legal width, very coarse and very fine resolutions -- bit-exact against the oracle."""
+    import torch
+    rm = load_map("4lane")
+    E, A, M = 2, 4, 20
+    x, y, h, v, route, rlen = scenario_gen.agent_starts(rm, E, MISSIONS_4LANE, 16, 51, jitter=60.0, speed=9.0)
+    soc = scenario_gen.SocialTraffic(rm, E, M, 52).states(3)
+    act = np.zeros((E, A), np.int32)
+    for ogm, dagm in (((1024, 300, 0.05), (32, 1024, 0.4)), ((512, 513, 0.11), (1024, 1024, 0.03)),
+                      ((32, 1, 2.0), (64, 700, 1.7))):
+        cfg = make_cfg(E=E, A=A, M=M, ogm=ogm, dagm=dagm, route_cap=16)
+        eng, ora = engine(rm, cfg), oracle_world(rm, cfg, threads=8)
+        for w in (eng, ora):
+            w.reset(x, y, h, v, route, rlen)
+        eng.set_social(torch.from_numpy(soc).cuda()); ora.set_social(soc)
+        for t in range(2):
+            eng.step(torch.from_numpy(act).cuda()); ora.step(act)
+        eng.observe(); ora.observe()
+        got, want = eng.obs_numpy(), ora.obs()
+        assert_same(got, want)
+        assert want["dagm"].any()
+        eng.close(); ora.close()
