@@ -147,7 +147,7 @@ class ClockSampler(threading.Thread):
                         self.reasons.add(name)
             except Exception:
                 pass
-            time.sleep(0.05)
+            time.sleep(0.004)
 
     def stop(self):
         self._stop_evt.set()

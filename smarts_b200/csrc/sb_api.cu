@@ -444,10 +444,22 @@ int sb_upload_map(SbHandle h, const SbMap* mp) {
             dev_upload(h, &m.poly_bbox, bbox.data(), bbox.size()) &&
             dev_upload(h, &m.road_edges, mp->road_edges, (size_t)mp->n_edges * 4);
   if (!ok) return SB_ECUDA;
+  {  // bounding box of every road's lane points: lower bound for the "closest lane point per route road" search
+    std::vector<double> rb((size_t)mp->n_roads * 4);
+    for (int r = 0; r < mp->n_roads; ++r) {
+      double x0 = 1e300, y0 = 1e300, x1 = -1e300, y1 = -1e300;
+      for (int i = mp->road_lp_start[r]; i < mp->road_lp_start[r] + mp->road_lp_count[r]; ++i) {
+        x0 = fmin(x0, mp->lp_x[i]); x1 = fmax(x1, mp->lp_x[i]);
+        y0 = fmin(y0, mp->lp_y[i]); y1 = fmax(y1, mp->lp_y[i]);
+      }
+      rb[r * 4 + 0] = x0; rb[r * 4 + 1] = y0; rb[r * 4 + 2] = x1; rb[r * 4 + 3] = y1;
+    }
+    if (!dev_upload(h, &m.road_lp_bbox, rb.data(), rb.size())) return SB_ECUDA;
+  }
   m.seg_nx = m.seg_ny = 0;
   m.seg_x0 = m.seg_y0 = m.seg_inv_cell = m.seg_rmax = 0.0;
   m.seg_cell_start = m.seg_items = nullptr;
-  if (mp->n_shape_pts > 256) {  // uniform grid over the lane-centre segments (small maps: the full scan is one pass)
+  if (mp->n_shape_pts > 32) {  // uniform grid over the lane-centre segments (small maps: the full scan is one pass)
     const double rmax = 12.0, cell = 16.0, eps = 1e-6;
     double x0 = 1e300, y0 = 1e300, x1 = -1e300, y1 = -1e300;
     for (int i = 0; i < mp->n_shape_pts; ++i) {

@@ -38,6 +38,7 @@ struct DMap {
   double seg_x0, seg_y0, seg_inv_cell, seg_rmax;
   int32_t seg_nx, seg_ny;
   const int32_t *seg_cell_start, *seg_items;
+  const double* road_lp_bbox;  // [n_roads,4] xmin, ymin, xmax, ymax of the road's lane points
 };
 
 struct DState {

@@ -354,12 +354,44 @@ __device__ void wp_waypoint_paths(const DMap& m, double x, double y, double h, i
     roads = wp->jr;
   }
   if (route_len >= 0 && nr > 0) {
+    // The reference queries one KD-tree per route road and keeps the first road with the smallest
+    // distance.  Roads whose lane-point bounding box is further away than a distance already achieved
+    // cannot win (nor tie), so they are not scanned: squared box distances go to shared memory, the road
+    // with the smallest one is scanned first for an upper bound, then the roads are visited in order.
+    double ub = 1e300;
+    const bool prune = nr > 1 && nr <= SB_WP_CAND;
+    if (prune) {
+      double lb_best = 1e300;
+      int r_best = 0x7fffffff;
+      for (int r = lane; r < nr; r += 32) {
+        const int road = roads[r];
+        double lb = 1e300;
+        if (m.road_lp_count[road] > 0) {
+          const double* bb = m.road_lp_bbox + (size_t)road * 4;
+          const double ex = fmax(fmax(bb[0] - x, x - bb[2]), 0.0), ey = fmax(fmax(bb[1] - y, y - bb[3]), 0.0);
+          lb = ex * ex + ey * ey;
+        }
+        wp->cand_d[r] = lb;
+        if (lb < lb_best) {
+          lb_best = lb;
+          r_best = r;
+        }
+      }
+      warp_argmin(lb_best, r_best);
+      __syncwarp();
+      if (r_best != 0x7fffffff && lb_best < 1e299) {
+        const int road = roads[r_best];
+        const int lp = wp_closest_in_range(m, m.road_lp_start[road], m.road_lp_count[road], x, y, lane);
+        ub = wp_sqdist(m, lp, x, y) * (1.0 + 1e-9);  // guard: bounds and distances round independently
+      }
+    }
     int best = -1;
     double bd = 0.0;
     for (int r = 0; r < nr; ++r) {
       int road = roads[r];
       int cnt = m.road_lp_count[road];
       if (cnt <= 0) continue;
+      if (prune && wp->cand_d[r] > ub) continue;
       int lp = wp_closest_in_range(m, m.road_lp_start[road], cnt, x, y, lane);
       double d = sqrt(wp_sqdist(m, lp, x, y));
       if (best < 0 || d < bd) {
