@@ -343,6 +343,30 @@ __device__ __forceinline__ uint32_t d_expand4(uint32_t b) {  // low 4 bits -> 4 
 __device__ __forceinline__ void d_store_rows(const uint32_t* bits, const uint2* lut, uint8_t* dst, int rows, int wpr,
                                              int stride) {
   const int n_words = rows * wpr;
+  if ((wpr & (wpr - 1)) == 0 && wpr <= SB_RASTER_THREADS && (n_words & (SB_RASTER_THREADS - 1)) == 0) {
+    // Common shapes (W a power of two up to 8192 px, rows * W/32 a multiple of 256): this thread's word keeps
+    // its column and moves 256 / wpr rows per step, every thread is active in every step -- no index
+    // carry, no tail predicate, and four steps' shared-memory loads are issued before their stores.
+    const int sh = __ffs(wpr) - 1;
+    const uint32_t* src = bits + (threadIdx.x >> sh) * stride + (threadIdx.x & (wpr - 1));
+    const int dsrc = (SB_RASTER_THREADS >> sh) * stride;
+    uint8_t* p = dst + (size_t)threadIdx.x * 32;
+    const int iters = n_words / SB_RASTER_THREADS;
+#pragma unroll 4
+    for (int k = 0; k < iters; ++k) {
+      const uint32_t word = src[k * dsrc];
+      uint8_t* q = p + (size_t)k * (SB_RASTER_THREADS * 32);
+      if (__all_sync(SB_FULL_MASK, word + 1u <= 1u)) {
+        asm volatile("st.global.v8.b32 [%0], {%1,%1,%1,%1,%1,%1,%1,%1};" ::"l"(q), "r"(word) : "memory");
+      } else {
+        const uint2 a = lut[word & 0xffu], b = lut[(word >> 8) & 0xffu], c = lut[(word >> 16) & 0xffu], d = lut[word >> 24];
+        asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(q), "r"(a.x), "r"(a.y), "r"(b.x),
+                     "r"(b.y), "r"(c.x), "r"(c.y), "r"(d.x), "r"(d.y)
+                     : "memory");
+      }
+    }
+    return;
+  }
   // running (row, word-in-row) of this thread's word: 256 words further every step
   int row = threadIdx.x / wpr, j = threadIdx.x - row * wpr;
   const int drow = SB_RASTER_THREADS / wpr, dj = SB_RASTER_THREADS - drow * wpr;
