@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define SB_ABI_VERSION 2
+#define SB_ABI_VERSION 3
 
 /* error codes */
 #define SB_OK 0
@@ -58,6 +58,8 @@ extern "C" {
 #define SB_STATUS_PATH_OVERFLOW 1u
 #define SB_STATUS_NO_WAYPOINTS 2u
 #define SB_STATUS_LIDAR_OVERFLOW 4u  /* more candidate boxes / edges near one agent than the kernel stages */
+#define SB_STATUS_TTC_TRUNCATED 8u   /* lane_ttc saw a capped neighbour / path / waypoint block (or a lane index
+                                        beyond the path list, an IndexError in the reference) */
 
 /* Events bits (smarts/core/events.py:23-34) in SbObsPtrs.ev_events and SbConfig.done_mask
  * (DoneCriteria, smarts/core/agent_interface.py:185-206). */
@@ -112,6 +114,9 @@ typedef struct SbConfig {
   int32_t max_episode_steps;   /* AgentInterface.max_episode_steps; <= 0: None */
   double not_moving_time;      /* EventConfiguration, agent_interface.py:174-182 (60 s) */
   double not_moving_distance;  /* (1 m) */
+  /* lane_ttc (smarts/env/custom_observations.py:148-290), the `ttc` member of StdObs (format_obs.py:546-556);
+   * needs nbr_enable and wp_enable */
+  int32_t ttc_enable;
 } SbConfig;
 
 /* Per-scenario constant road map (host pointers, copied once).  Built by
@@ -203,6 +208,12 @@ typedef struct SbObsPtrs {
   double *ev_distance;         /* [E*A] TripMeterSensor(), sensors.py:880-947 (Observation.distance_travelled) */
   double *ev_reward;           /* [E*A] TripMeterSensor(increment=True), agent_manager.py:233-234 */
   int32_t *ev_steps;           /* [E*A] SensorState.steps_completed, sensors.py:609-637 */
+  /* lane_ttc (ttc_enable): StdObs `ttc` (format_obs.py:546-556) */
+  float *ttc_angle_error;      /* [E*A] */
+  float *ttc_distance_from_center; /* [E*A] */
+  float *ttc_dtc;              /* [E*A, 3] right / current / left lane */
+  float *ttc_ttc;              /* [E*A, 3] */
+  uint8_t *ttc_valid;          /* [E*A] 0: no neighbours or no waypoint paths (the reference returns None) */
 } SbObsPtrs;
 
 /* Initial / reset state for a set of envs (host pointers).  Replaces SMARTS.reset ->
@@ -260,7 +271,8 @@ int64_t sb_launch_count(SbHandle h);
 #define SB_K_RASTER 4
 #define SB_K_EVENTS 5
 #define SB_K_PACK 6    /* k_pack_bits: grid transport of sb_copy_obs_to_host */
-#define SB_K_COUNT 7
+#define SB_K_TTC 7
+#define SB_K_COUNT 8
 int sb_set_timing(SbHandle h, int on);
 int sb_collect_timing(SbHandle h, double *ms_sum /*[SB_K_COUNT]*/, int64_t *count /*[SB_K_COUNT]*/);
 const char *sb_last_error(SbHandle h);

@@ -818,6 +818,99 @@ void observe_events(World& w, int e, int a, bool ticked) {
   w.ev_done[ai] = (ticked && (bits & mask)) ? 1 : 0;
 }
 
+// lane_ttc, smarts/env/custom_observations.py:148-290 (the `ttc` member of StdObs, format_obs.py:546-556),
+// on the agent's own observation buffers.
+void observe_ttc(World& w, int e, int a) {
+  const int ai = e * w.A + a, vi = e * w.V + a;
+  const int P = w.cfg.wp_out_paths, L = w.cfg.wp_out_len, cap = w.cfg.nbr_cap;
+  const double ex = w.pos_x[vi], ey = w.pos_y[vi], eh = w.heading[vi], espeed = w.speed[vi];
+  const int total_paths = w.wp_n_paths[ai];
+  const int n = std::min(std::min(total_paths, P), 32);
+  const int cnt = w.nbr_count[ai], nv = std::min(cnt, cap);
+  bool truncated = total_paths > P || cnt > cap;
+  auto row = [&](int p) { return ((size_t)ai * P + p) * L; };
+  auto plen = [&](int p) { return w.wp_len[(size_t)ai * P + p]; };
+  bool any_path = false;
+  for (int p = 0; p < n; ++p) {
+    if (plen(p) > 0) any_path = true;
+    if (plen(p) == L && L < w.cfg.wp_lookahead + 1) truncated = true;
+  }
+  w.ttc_valid[ai] = 0;
+  w.ttc_angle_error[ai] = w.ttc_dist_center[ai] = 0.f;
+  for (int k = 0; k < 3; ++k) w.ttc_dtc[(size_t)ai * 3 + k] = w.ttc_ttc[(size_t)ai * 3 + k] = 0.f;
+  if (cnt == 0 || n == 0 || !any_path) return;
+  // closest first waypoint (first minimum wins)
+  int p0 = -1;
+  double d0 = 0.0;
+  for (int p = 0; p < n; ++p) {
+    if (plen(p) <= 0) continue;
+    double dx = w.wp_pos[row(p) * 3 + 0] - ex, dy = w.wp_pos[row(p) * 3 + 1] - ey;
+    double d = std::sqrt(dx * dx + dy * dy);
+    if (p0 < 0 || d < d0) {
+      p0 = p;
+      d0 = d;
+    }
+  }
+  const size_t crow = row(p0);
+  const double cwx = w.wp_pos[crow * 3 + 0], cwy = w.wp_pos[crow * 3 + 1], cwh = (double)w.wp_heading[crow];
+  const int li = (int)w.wp_lane_index[crow];
+  double hvx, hvy;
+  radians_to_vec(cwh, &hvx, &hvy);
+  const double signed_dist = signed_dist_to_line(ex, ey, cwx, cwy, hvx, hvy);
+  const double norm_dist = signed_dist / ((double)w.wp_lane_width[crow] * 0.5);
+  const double angle_error = wrap_heading(cwh - eh);
+  std::vector<double> ttc_by(n, 1000.0), dist_by(n, 1.0);
+  for (int k = 0; k < nv; ++k) {
+    const size_t q = (size_t)ai * cap + k;
+    const int vlane = w.nbr_lane[q];
+    if (vlane < 0) continue;
+    const double vx = w.nbr_pos[q * 3 + 0], vy = w.nbr_pos[q * 3 + 1];
+    int bp = -1;
+    double bd = 0.0, bdist = 0.0;
+    for (int p = 0; p < n; ++p) {
+      double cum = 0.0, px = 0.0, py = 0.0;
+      for (int i = 0; i < plen(p); ++i) {
+        const double wx = w.wp_pos[(row(p) + i) * 3 + 0], wy = w.wp_pos[(row(p) + i) * 3 + 1];
+        if (i > 0) {
+          const double sx = wx - px, sy = wy - py;
+          cum += std::sqrt(sx * sx + sy * sy);
+        }
+        px = wx;
+        py = wy;
+        if (w.wp_lane[row(p) + i] != vlane) continue;
+        const double dx = wx - vx, dy = wy - vy;
+        const double d = std::sqrt(dx * dx + dy * dy);
+        if (bp < 0 || d < bd) {
+          bp = p;
+          bd = d;
+          bdist = cum;
+        }
+      }
+    }
+    if (bp < 0 || bd > 2.0) continue;
+    double rel = (espeed - (double)w.nbr_speed[q]) * 1000.0 / 3600.0;
+    if (std::fabs(rel) < 1e-5) rel = 1e-5;
+    double ttc = bdist / rel;
+    ttc /= 10.0;
+    if (ttc <= 0.0) continue;
+    const double ld = bdist / 100.0;
+    dist_by[bp] = std::min(dist_by[bp], ld);
+    ttc_by[bp] = std::min(ttc_by[bp], ttc);
+  }
+  for (int k = 0; k < 3; ++k) {
+    const int src = li - 1 + k;
+    if (src >= 0 && src < n) {
+      w.ttc_ttc[(size_t)ai * 3 + k] = (float)ttc_by[src];
+      w.ttc_dtc[(size_t)ai * 3 + k] = (float)dist_by[src];
+    }
+  }
+  if (li < 0 || li >= n) truncated = true;
+  w.ttc_valid[ai] = 1;
+  w.ttc_angle_error[ai] = (float)angle_error;
+  w.ttc_dist_center[ai] = (float)norm_dist;
+  if (truncated) w.status[ai] |= SB_STATUS_TTC_TRUNCATED;
+}
+
 void observe_agent(World& w, int e, int a) {
   const int ai = e * w.A + a, vi = e * w.V + a;
   // sensors.py:277-285, radius None -> max(10, 2 * default lane width) (sumo_road_network.py:679-680)
@@ -829,6 +922,7 @@ void observe_agent(World& w, int e, int a) {
     waypoint_paths(w.map, w.pos_x[vi], w.pos_y[vi], w.heading[vi], 1, w.length[vi], nullptr, -1, &ps);
     stash_trip_waypoint(w, ai, ps);
   }
+  if (w.cfg.ttc_enable) observe_ttc(w, e, a);
   if (w.cfg.lidar_enable) observe_lidar(w, e, a);
   if (w.cfg.ogm_enable) observe_ogm(w, e, a);
   if (w.cfg.dagm_enable) observe_dagm(w, e, a);
@@ -934,6 +1028,13 @@ void* or_create(const SbConfig* cfg, const SbMap* m, const double* base_rays, in
     w->path_cum.assign(na * w->ring, 0.0);
     for (auto* v : {&w->steps, &w->path_n, &w->ev_n_collisions, &w->ev_collidee, &w->ev_steps}) v->assign(na, 0);
     w->ev_events.assign(na, 0);
+  }
+  if (cfg->ttc_enable) {
+    w->ttc_angle_error.assign(na, 0.f);
+    w->ttc_dist_center.assign(na, 0.f);
+    w->ttc_dtc.assign(na * 3, 0.f);
+    w->ttc_ttc.assign(na * 3, 0.f);
+    w->ttc_valid.assign(na, 0);
   }
   if (cfg->ogm_enable) w->ogm.assign(na * cfg->ogm_width * cfg->ogm_height, 0);
   if (cfg->dagm_enable) w->dagm.assign(na * cfg->dagm_width * cfg->dagm_height, 0);
@@ -1099,6 +1200,8 @@ void or_get_obs(void* h, SbObsPtrs* o) {
   o->ev_events = w.ev_events.data(); o->ev_done = w.ev_done.data(); o->ev_n_collisions = w.ev_n_collisions.data();
   o->ev_collidee = w.ev_collidee.data(); o->ev_distance = w.ev_distance.data(); o->ev_reward = w.ev_reward.data();
   o->ev_steps = w.ev_steps.data();
+  o->ttc_angle_error = w.ttc_angle_error.data(); o->ttc_distance_from_center = w.ttc_dist_center.data();
+  o->ttc_dtc = w.ttc_dtc.data(); o->ttc_ttc = w.ttc_ttc.data(); o->ttc_valid = w.ttc_valid.data();
 }
 
 // ---- unit-level probes used to pin the oracle against the reference's golden vectors ----

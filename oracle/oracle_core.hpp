@@ -115,6 +115,8 @@ struct World {
       goal_y, goal_r, ev_distance, ev_reward;
   std::vector<int32_t> steps, path_n, ev_n_collisions, ev_collidee, ev_steps;
   std::vector<uint32_t> ev_events;
+  std::vector<float> ttc_angle_error, ttc_dist_center, ttc_dtc, ttc_ttc;
+  std::vector<uint8_t> ttc_valid;
   int ring = 1;
   bool stepped = false;
   int threads = 1;

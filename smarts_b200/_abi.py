@@ -6,7 +6,7 @@ from typing import Dict
 
 import numpy as np
 
-SB_ABI_VERSION = 2
+SB_ABI_VERSION = 3
 
 SB_ACTION_CONTINUOUS = 0
 SB_ACTION_LANE = 1
@@ -23,6 +23,7 @@ SB_CTRL_STATE = 12
 SB_STATUS_PATH_OVERFLOW = 1
 SB_STATUS_NO_WAYPOINTS = 2
 SB_STATUS_LIDAR_OVERFLOW = 4
+SB_STATUS_TTC_TRUNCATED = 8
 
 SB_EV_COLLISION, SB_EV_OFF_ROAD, SB_EV_OFF_ROUTE, SB_EV_ON_SHOULDER = 1, 2, 4, 8
 SB_EV_WRONG_WAY, SB_EV_NOT_MOVING, SB_EV_REACHED_GOAL, SB_EV_REACHED_MAX_STEPS = 16, 32, 64, 128
@@ -45,6 +46,7 @@ class SbConfig(C.Structure):
         ("dagm_enable", _i32), ("dagm_width", _i32), ("dagm_height", _i32), ("dagm_resolution", _f64),
         ("events_enable", _i32), ("done_mask", C.c_uint32), ("max_episode_steps", _i32),
         ("not_moving_time", _f64), ("not_moving_distance", _f64),
+        ("ttc_enable", _i32),
     ]
 
 
@@ -89,6 +91,8 @@ class SbObsPtrs(C.Structure):
         ("ogm", _pu8), ("dagm", _pu8),
         ("ev_events", _pu32), ("ev_done", _pu8), ("ev_n_collisions", _pi32), ("ev_collidee", _pi32),
         ("ev_distance", _pf64), ("ev_reward", _pf64), ("ev_steps", _pi32),
+        ("ttc_angle_error", _pf32), ("ttc_distance_from_center", _pf32), ("ttc_dtc", _pf32), ("ttc_ttc", _pf32),
+        ("ttc_valid", _pu8),
     ]
 
 
@@ -147,6 +151,9 @@ def obs_shapes(cfg: SbConfig) -> Dict[str, tuple]:
         out.update(ev_events=((), np.uint32), ev_done=((), np.uint8), ev_n_collisions=((), np.int32),
                    ev_collidee=((), np.int32), ev_distance=((), np.float64), ev_reward=((), np.float64),
                    ev_steps=((), np.int32))
+    if cfg.ttc_enable:
+        out.update(ttc_angle_error=((), np.float32), ttc_distance_from_center=((), np.float32),
+                   ttc_dtc=((3,), np.float32), ttc_ttc=((3,), np.float32), ttc_valid=((), np.uint8))
     return out
 
 

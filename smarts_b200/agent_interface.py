@@ -266,6 +266,8 @@ def compile_config(itf: AgentInterface, n_envs: int, n_agents: int, n_social: in
     if itf.drivable_area_grid_map:
         g = itf.drivable_area_grid_map
         c.dagm_enable, c.dagm_width, c.dagm_height, c.dagm_resolution = 1, g.width, g.height, g.resolution
+    if itf.waypoints and itf.neighborhood_vehicles:  # StdObs `ttc` (format_obs.py:387-388)
+        c.ttc_enable = 1
     if events:
         c.events_enable = 1
         c.done_mask = itf.done_criteria.mask()

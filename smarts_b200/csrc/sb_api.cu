@@ -31,6 +31,7 @@ struct SbHandle_ {
   DObs ob;
   DEvents ev{};
   DEvOut evo{};
+  DTtcOut ttc{};
   bool stepped = false;  // a sb_step since the last sb_observe (SensorState.step; `sim.resetting` otherwise)
   bool have_map = false, have_rays = false;
   double* d_rays = nullptr;
@@ -267,6 +268,8 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
   d.dagm_enable = c.dagm_enable; d.dagm_w = c.dagm_width; d.dagm_h = c.dagm_height; d.dagm_res = c.dagm_resolution;
   d.events_enable = c.events_enable; d.max_steps = c.max_episode_steps; d.done_mask = c.done_mask;
   d.nm_time = c.not_moving_time; d.nm_dist = c.not_moving_distance;
+  d.ttc_enable = c.ttc_enable;
+  if (c.ttc_enable && !(c.nbr_enable && c.wp_enable)) return fail(h, SB_EINVAL, "ttc needs the neighbour and waypoint sensors");
   if (c.events_enable && !(c.not_moving_time >= 0)) return fail(h, SB_EINVAL, "not_moving_time must be >= 0");
 
   const size_t nv = (size_t)d.E * d.V, na = (size_t)d.E * d.A;
@@ -320,6 +323,12 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
          dev_alloc(h, &q.reward, na) && dev_alloc(h, &q.steps, na);
     if (!ok) return SB_ENOMEM;
     k_fill<<<(unsigned)((na + 255) / 256), 256>>>(v.goal_r, na, -1.0);
+  }
+  if (c.ttc_enable) {
+    DTtcOut& q = h->ttc;
+    if (!(dev_alloc(h, &q.angle_error, na) && dev_alloc(h, &q.dist_center, na) && dev_alloc(h, &q.dtc, na * 3) &&
+          dev_alloc(h, &q.ttc, na * 3) && dev_alloc(h, &q.valid, na)))
+      return SB_ENOMEM;
   }
   if (!dev_alloc(h, &h->d_picks, na)) return SB_ENOMEM;
   if (!dev_alloc(h, &h->d_social, (size_t)d.E * (d.M ? d.M : 1) * 8)) return SB_ENOMEM;
@@ -673,6 +682,10 @@ int sb_observe(SbHandle h, void* stream) {
     k_observe<<<(na + SB_OBS_WARPS - 1) / SB_OBS_WARPS, SB_OBS_WARPS * 32, 0, st>>>(c, h->dmap, h->st, h->ob,
                                                                                     h->ev.trip_wp);
   }
+  if (c.ttc_enable) {
+    LaunchScope ls(h, SB_K_TTC, st);
+    k_ttc<<<(na + SB_TTC_WARPS - 1) / SB_TTC_WARPS, SB_TTC_WARPS * 32, 0, st>>>(c, h->st, h->ob, h->ttc);
+  }
   if (c.lidar_enable) {
     LaunchScope ls(h, SB_K_LIDAR, st);
     k_lidar<<<na, SB_LIDAR_THREADS, 0, st>>>(c, h->dmap, h->st, h->ob, h->d_rays,
@@ -823,6 +836,11 @@ int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs* dst) {
     cpy(dst->ev_collidee, q.collidee, na * 4); cpy(dst->ev_distance, q.distance, na * 8);
     cpy(dst->ev_reward, q.reward, na * 8); cpy(dst->ev_steps, q.steps, na * 4);
   }
+  if (c.ttc_enable) {
+    const DTtcOut& q = h->ttc;
+    cpy(dst->ttc_angle_error, q.angle_error, na * 4); cpy(dst->ttc_distance_from_center, q.dist_center, na * 4);
+    cpy(dst->ttc_dtc, q.dtc, na * 12); cpy(dst->ttc_ttc, q.ttc, na * 12); cpy(dst->ttc_valid, q.valid, na);
+  }
   if (n_packed < na) {  // the byte-image share, behind everything else on the link
     const size_t g0 = (size_t)c.ogm_width * c.ogm_height, g1 = (size_t)c.dagm_width * c.dagm_height;
     if (c.ogm_enable && dst->ogm) { cpy(dst->ogm + n_packed * g0, o.ogm + n_packed * g0, (na - n_packed) * g0); }
@@ -893,6 +911,8 @@ int sb_get_obs(SbHandle h, SbObsPtrs* out) {
   const DEvOut& q = h->evo;
   out->ev_events = q.events; out->ev_done = q.done; out->ev_n_collisions = q.n_collisions;
   out->ev_collidee = q.collidee; out->ev_distance = q.distance; out->ev_reward = q.reward; out->ev_steps = q.steps;
+  out->ttc_angle_error = h->ttc.angle_error; out->ttc_distance_from_center = h->ttc.dist_center;
+  out->ttc_dtc = h->ttc.dtc; out->ttc_ttc = h->ttc.ttc; out->ttc_valid = h->ttc.valid;
   return SB_OK;
 }
 

@@ -8,6 +8,7 @@
 //   k_lidar           LidarSensor ray casting                              (block per agent)
 //   k_raster          OGM + DrivableAreaGridMap                            (block per agent)
 //   k_events          Events / done / trip-meter reward / contacts         (warp per agent, sb_events.cuh)
+//   k_ttc             lane_ttc (StdObs ttc)                                (warp per agent, sb_ttc.cuh)
 #pragma once
 
 #include "sb_control.cuh"
@@ -43,7 +44,7 @@ struct DCfg {
   double ogm_res;
   int32_t dagm_enable, dagm_w, dagm_h;
   double dagm_res;
-  int32_t events_enable, max_steps;
+  int32_t events_enable, max_steps, ttc_enable;
   uint32_t done_mask;
   double nm_time, nm_dist;
 };
@@ -420,6 +421,7 @@ k_observe(DCfg c, DMap m, DState s, DObs o, double* __restrict__ trip_wp) {
 
 // --------------------------------------------------------------------------------- events
 #include "sb_events.cuh"
+#include "sb_ttc.cuh"
 
 // --------------------------------------------------------------------------------- lidar
 // k_lidar lives in sb_lidar.cuh (azimuth-sorted warps, sector / per-ray culls, exact binary64 tests).

@@ -315,6 +315,9 @@ class BatchedHiWayEnv:
         if itf.neighborhood_vehicles:
             out["neighbors"] = {"box": o["nbr_box"], "heading": o["nbr_heading"], "lane_index": o["nbr_lane_index"],
                                 "pos": o["nbr_pos"], "speed": o["nbr_speed"]}
+        if self.cfg.ttc_enable:  # zeros where the reference's _std_ttc returns None (o["ttc_valid"] == 0)
+            out["ttc"] = {"angle_error": o["ttc_angle_error"], "distance_from_center": o["ttc_distance_from_center"],
+                          "dtc": o["ttc_dtc"], "ttc": o["ttc_ttc"]}
         if itf.waypoints:
             out["waypoints"] = {"heading": o["wp_heading"], "lane_index": o["wp_lane_index"], "lane_width": o["wp_lane_width"],
                                 "pos": o["wp_pos"], "speed_limit": o["wp_speed_limit"]}

@@ -212,6 +212,10 @@ def test_std_obs_layout_matches_format_obs():
     assert tuple(nb["pos"].shape) == (E, A, 10, 3) and nb["pos"].dtype == torch.float64 and nb["lane_index"].dtype == torch.int8
     wp = so["waypoints"]
     assert tuple(wp["pos"].shape) == (E, A, 4, 20, 3) and tuple(wp["heading"].shape) == (E, A, 4, 20)
+    ttc = so["ttc"]  # enabled because both the waypoint and the neighbour sensor are on (format_obs.py:387-388)
+    assert set(ttc) == {"angle_error", "distance_from_center", "dtc", "ttc"}
+    assert tuple(ttc["dtc"].shape) == (E, A, 3) and tuple(ttc["angle_error"].shape) == (E, A)
+    assert all(v.dtype == torch.float32 for v in ttc.values())
     # agreement with the Observation objects
     o = obs[1]["A2"]
     assert np.allclose(so["ego"]["pos"][1, 2].cpu().numpy(), o.ego_vehicle_state.position)
