@@ -420,6 +420,18 @@ __device__ __forceinline__ int wp_rank(const DMap& m, const WarpPaths* wp, int k
   return rank;
 }
 
+// rise / run of one interpolation interval (run > 0: cum is strictly increasing across it).  A zero
+// rise -- y, heading, width and speed limit along any straight constant-width lane -- gives a zero
+// slope of the same sign, exactly what the division returns, without going through the division's
+// out-of-range slow path (ptxas sends a zero numerator there: ~75 instructions per quotient).
+__device__ __forceinline__ double wp_slope(double rise, double run) {
+  const bool flat = rise == 0.0;
+  double num = flat ? 1.0 : rise;
+  asm volatile("" : "+d"(num));  // opaque: otherwise nvcc folds the two selects back into rise / run
+  const double q = num / run;
+  return flat ? rise : q;
+}
+
 // First waypoint of wp_equally_spaced() for `path` without building the rest (find_current_lane,
 // lane_following_controller.py:367-374, only needs this one): the vehicle's projection on the
 // first lane point's heading line, or the lane point itself for a path of <= spacing points.
@@ -512,12 +524,12 @@ __device__ int wp_equally_spaced(const DMap& m, const int32_t* path, int n, doub
     } else {
       double den = cum[j + 1] - cum[j], ds = s - cum[j];
       int la = rlane[j], lb = rlane[j + 1];
-      w.x = ((rx[j + 1] - rx[j]) / den) * ds + rx[j];
-      w.y = ((ry[j + 1] - ry[j]) / den) * ds + ry[j];
-      w.heading = ((rh[j + 1] - rh[j]) / den) * ds + rh[j];
+      w.x = wp_slope(rx[j + 1] - rx[j], den) * ds + rx[j];
+      w.y = wp_slope(ry[j + 1] - ry[j], den) * ds + ry[j];
+      w.heading = wp_slope(rh[j + 1] - rh[j], den) * ds + rh[j];
       double wa = m.lane_width[la], wb = m.lane_width[lb], sa = m.lane_speed[la], sb_ = m.lane_speed[lb];
-      w.lane_width = ((wb - wa) / den) * ds + wa;
-      w.speed_limit = ((sb_ - sa) / den) * ds + sa;
+      w.lane_width = wp_slope(wb - wa, den) * ds + wa;
+      w.speed_limit = wp_slope(sb_ - sa, den) * ds + sa;
     }
     w.heading = d_wrap_heading(w.heading);
     while (jd + 1 < mm && s > cum[jd + 1]) ++jd;
