@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define SB_ABI_VERSION 3
+#define SB_ABI_VERSION 4
 
 /* error codes */
 #define SB_OK 0
@@ -72,6 +72,7 @@ extern "C" {
 #define SB_EV_REACHED_GOAL 64u          /* always ends the episode (sensors.py:464-474) */
 #define SB_EV_REACHED_MAX_STEPS 128u    /* always ends the episode */
 #define SB_EV_AGENTS_ALIVE_DONE 256u    /* multi-agent alive criteria: evaluated by the host layer */
+#define SB_MAX_VIAS 16                  /* via points per agent mission */
 #define SB_DRIVEN_PATH_MAX 500          /* DrivenPathSensor deque length, sensors.py:838-840 */
 
 typedef struct SbHandle_ *SbHandle;
@@ -117,6 +118,13 @@ typedef struct SbConfig {
   /* lane_ttc (smarts/env/custom_observations.py:148-290), the `ttc` member of StdObs (format_obs.py:546-556);
    * needs nbr_enable and wp_enable */
   int32_t ttc_enable;
+  /* AccelerometerSensor (sensors.py:1046-1084): linear / angular acceleration and jerk of the ego */
+  int32_t accel_enable;
+  /* ViaSensor (sensors.py:1090-1150): via points per agent mission (Mission.via, plan.py:180-188);
+   * via_cap = 0 disables.  Defaults of vehicle.py:552-558: range 40 m, speed accuracy 1.5 m/s */
+  int32_t via_cap;              /* <= SB_MAX_VIAS */
+  double via_acquisition_range;
+  double via_speed_accuracy;
 } SbConfig;
 
 /* Per-scenario constant road map (host pointers, copied once).  Built by
@@ -214,6 +222,16 @@ typedef struct SbObsPtrs {
   float *ttc_dtc;              /* [E*A, 3] right / current / left lane */
   float *ttc_ttc;              /* [E*A, 3] */
   uint8_t *ttc_valid;          /* [E*A] 0: no neighbours or no waypoint paths (the reference returns None) */
+  /* accelerometer (accel_enable): EgoVehicleObservation.linear_acceleration ... angular_jerk, sensors.py:94-101 */
+  double *acc_linear;          /* [E*A, 3] */
+  double *acc_angular;         /* [E*A, 3] */
+  double *acc_linear_jerk;     /* [E*A, 3] */
+  double *acc_angular_jerk;    /* [E*A, 3] */
+  /* vias (via_cap > 0): Observation.via_data (Vias, sensors.py:168-175) as indices into the agent's via list */
+  int32_t *via_near_count;     /* [E*A] */
+  int32_t *via_near_idx;       /* [E*A, via_cap] nearest first (stable), -1 padded */
+  int32_t *via_hit_count;      /* [E*A] points collected by this observation */
+  int32_t *via_hit_idx;        /* [E*A, via_cap] in mission order, -1 padded */
 } SbObsPtrs;
 
 /* Initial / reset state for a set of envs (host pointers).  Replaces SMARTS.reset ->
@@ -224,6 +242,10 @@ typedef struct SbResetState {
   const int32_t *route_len;  /* [n, A] or NULL */
   /* PositionalGoal (plan.py:95-124): goal_radius < 0 or NULL pointers = EndlessGoal */
   const double *goal_x, *goal_y, *goal_radius; /* [n, A] or NULL */
+  /* Mission.via (plan.py:180-188), used when via_cap > 0; NULL via_count = no vias */
+  const int32_t *via_count;  /* [n, A] 0..via_cap */
+  const int32_t *via_lane;   /* [n, A, via_cap] map lane index (Via.lane_id) */
+  const double *via_x, *via_y, *via_hit_distance, *via_required_speed; /* [n, A, via_cap] */
 } SbResetState;
 
 /* HiWayEnv.__init__ -> SMARTS.__init__ (smarts/env/hiway_env.py:166-173, smarts/core/smarts.py:96-185) */
@@ -272,7 +294,8 @@ int64_t sb_launch_count(SbHandle h);
 #define SB_K_EVENTS 5
 #define SB_K_PACK 6    /* k_pack_bits: grid transport of sb_copy_obs_to_host */
 #define SB_K_TTC 7
-#define SB_K_COUNT 8
+#define SB_K_EXTRAS 8   /* accelerometer + vias */
+#define SB_K_COUNT 9
 int sb_set_timing(SbHandle h, int on);
 int sb_collect_timing(SbHandle h, double *ms_sum /*[SB_K_COUNT]*/, int64_t *count /*[SB_K_COUNT]*/);
 const char *sb_last_error(SbHandle h);

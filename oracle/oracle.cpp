@@ -911,6 +911,76 @@ void observe_ttc(World& w, int e, int a) {
   if (truncated) w.status[ai] |= SB_STATUS_TTC_TRUNCATED;
 }
 
+// AccelerometerSensor.__call__, sensors.py:1053-1084, fed as sensors.py:294-299 with the ego's
+// linear velocity (radians_to_vec(heading) * speed, chassis.py:276-280) and angular velocity
+// (0, 0, yaw_rate); dt = sim.last_dt = the fixed time step (smarts.py:122, :261).
+void observe_accelerometer(World& w, int e, int a) {
+  const int ai = e * w.A + a, vi = e * w.V + a;
+  double hvx, hvy;
+  radians_to_vec(w.heading[vi], &hvx, &hvy);
+  auto& lv = w.acc_lin_hist[ai];
+  auto& av = w.acc_ang_hist[ai];
+  lv.push_back({hvx * w.speed[vi], hvy * w.speed[vi], 0.0});
+  if (lv.size() > 3) lv.pop_front();  // deque(maxlen=3)
+  av.push_back({0.0, 0.0, w.yaw_rate[vi]});
+  if (av.size() > 3) av.pop_front();
+  const double dt = w.cfg.dt;
+  std::array<double, 3> lin_acc{0, 0, 0}, ang_acc{0, 0, 0}, lin_jerk{0, 0, 0}, ang_jerk{0, 0, 0};
+  if (dt != 0.0) {
+    auto accel = [dt](const std::deque<std::array<double, 3>>& d, std::array<double, 3>* acc,
+                      std::array<double, 3>* jerk) {
+      const size_t n = d.size();
+      if (n < 2) return;
+      for (int k = 0; k < 3; ++k) (*acc)[k] = (d[n - 1][k] - d[n - 2][k]) / dt;
+      if (n < 3) return;
+      for (int k = 0; k < 3; ++k) (*jerk)[k] = (*acc)[k] - (d[n - 2][k] - d[n - 3][k]) / dt;  // sic: no / dt
+    };
+    accel(lv, &lin_acc, &lin_jerk);
+    accel(av, &ang_acc, &ang_jerk);
+  }
+  for (int k = 0; k < 3; ++k) {
+    w.acc_linear[(size_t)ai * 3 + k] = lin_acc[k];
+    w.acc_angular[(size_t)ai * 3 + k] = ang_acc[k];
+    w.acc_linear_jerk[(size_t)ai * 3 + k] = lin_jerk[k];
+    w.acc_angular_jerk[(size_t)ai * 3 + k] = ang_jerk[k];
+  }
+}
+
+// ViaSensor.__call__, sensors.py:1104-1147
+void observe_vias(World& w, int e, int a) {
+  const int ai = e * w.A + a, vi = e * w.V + a, C = w.cfg.via_cap;
+  const double px = w.pos_x[vi], py = w.pos_y[vi];
+  const double range = w.cfg.via_acquisition_range;
+  struct Near { int idx; double d2; };
+  std::vector<Near> near_points;
+  std::vector<int> hit_points;
+  const auto& vias = w.vias[ai];
+  for (int k = 0; k < (int)vias.size(); ++k) {
+    const World::ViaRec& via = vias[k];
+    // lane.center_at_point(position), road_map.py:357-360
+    double cx, cy;
+    from_lane_coord(w.map, via.lane, offset_along_lane(w.map, via.lane, px, py), &cx, &cy);
+    const double lx = cx - px, ly = cy - py;  // squared_dist, utils/math.py:152-160
+    if (lx * lx + ly * ly > range * range) continue;
+    const double dx = via.x - px, dy = via.y - py;
+    const double d2 = dx * dx + dy * dy;
+    near_points.push_back({k, d2});
+    const bool speed_ok = std::fabs(w.speed[vi] - via.required_speed) <=
+                          w.cfg.via_speed_accuracy + 1e-5 * std::fabs(via.required_speed);  // np.isclose
+    if (d2 <= via.hit_distance * via.hit_distance && !w.via_consumed[ai].count(k) && speed_ok) {
+      w.via_consumed[ai].insert(k);
+      hit_points.push_back(k);
+    }
+  }
+  std::stable_sort(near_points.begin(), near_points.end(), [](const Near& p, const Near& q) { return p.d2 < q.d2; });
+  for (int k = 0; k < C; ++k) {
+    w.via_near_idx[(size_t)ai * C + k] = k < (int)near_points.size() ? near_points[k].idx : -1;
+    w.via_hit_idx[(size_t)ai * C + k] = k < (int)hit_points.size() ? hit_points[k] : -1;
+  }
+  w.via_near_count[ai] = (int)near_points.size();
+  w.via_hit_count[ai] = (int)hit_points.size();
+}
+
 void observe_agent(World& w, int e, int a) {
   const int ai = e * w.A + a, vi = e * w.V + a;
   // sensors.py:277-285, radius None -> max(10, 2 * default lane width) (sumo_road_network.py:679-680)
@@ -923,6 +993,8 @@ void observe_agent(World& w, int e, int a) {
     stash_trip_waypoint(w, ai, ps);
   }
   if (w.cfg.ttc_enable) observe_ttc(w, e, a);
+  if (w.cfg.accel_enable) observe_accelerometer(w, e, a);
+  if (w.cfg.via_cap > 0) observe_vias(w, e, a);
   if (w.cfg.lidar_enable) observe_lidar(w, e, a);
   if (w.cfg.ogm_enable) observe_ogm(w, e, a);
   if (w.cfg.dagm_enable) observe_dagm(w, e, a);
@@ -1036,6 +1108,19 @@ void* or_create(const SbConfig* cfg, const SbMap* m, const double* base_rays, in
     w->ttc_ttc.assign(na * 3, 0.f);
     w->ttc_valid.assign(na, 0);
   }
+  if (cfg->accel_enable) {
+    w->acc_lin_hist.assign(na, {});
+    w->acc_ang_hist.assign(na, {});
+    for (auto* v : {&w->acc_linear, &w->acc_angular, &w->acc_linear_jerk, &w->acc_angular_jerk}) v->assign(na * 3, 0.0);
+  }
+  if (cfg->via_cap > 0) {
+    w->vias.assign(na, {});
+    w->via_consumed.assign(na, {});
+    w->via_near_count.assign(na, 0);
+    w->via_hit_count.assign(na, 0);
+    w->via_near_idx.assign(na * cfg->via_cap, -1);
+    w->via_hit_idx.assign(na * cfg->via_cap, -1);
+  }
   if (cfg->ogm_enable) w->ogm.assign(na * cfg->ogm_width * cfg->ogm_height, 0);
   if (cfg->dagm_enable) w->dagm.assign(na * cfg->dagm_width * cfg->dagm_height, 0);
   return w;
@@ -1084,6 +1169,21 @@ void or_reset(void* h, const int32_t* env_ids, int n, const SbResetState* init) 
         w.goal_x[ai] = goals ? init->goal_x[src] : 0.0;
         w.goal_y[ai] = goals ? init->goal_y[src] : 0.0;
         w.goal_r[ai] = goals ? init->goal_radius[src] : -1.0;
+      }
+      if (w.cfg.accel_enable) {  // a new vehicle carries a new AccelerometerSensor
+        w.acc_lin_hist[ai].clear();
+        w.acc_ang_hist[ai].clear();
+      }
+      if (w.cfg.via_cap > 0) {
+        w.vias[ai].clear();
+        w.via_consumed[ai].clear();
+        const int C = w.cfg.via_cap;
+        const int cnt = init->via_count ? init->via_count[src] : 0;
+        for (int k = 0; k < cnt && k < C; ++k) {
+          const size_t q = src * C + k;
+          w.vias[ai].push_back({init->via_lane[q], init->via_x[q], init->via_y[q], init->via_hit_distance[q],
+                                init->via_required_speed[q]});
+        }
       }
     }
     for (int j = w.A; j < w.V; ++j) {
@@ -1202,6 +1302,10 @@ void or_get_obs(void* h, SbObsPtrs* o) {
   o->ev_steps = w.ev_steps.data();
   o->ttc_angle_error = w.ttc_angle_error.data(); o->ttc_distance_from_center = w.ttc_dist_center.data();
   o->ttc_dtc = w.ttc_dtc.data(); o->ttc_ttc = w.ttc_ttc.data(); o->ttc_valid = w.ttc_valid.data();
+  o->acc_linear = w.acc_linear.data(); o->acc_angular = w.acc_angular.data();
+  o->acc_linear_jerk = w.acc_linear_jerk.data(); o->acc_angular_jerk = w.acc_angular_jerk.data();
+  o->via_near_count = w.via_near_count.data(); o->via_near_idx = w.via_near_idx.data();
+  o->via_hit_count = w.via_hit_count.data(); o->via_hit_idx = w.via_hit_idx.data();
 }
 
 // ---- unit-level probes used to pin the oracle against the reference's golden vectors ----

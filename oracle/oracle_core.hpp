@@ -20,7 +20,10 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
+#include <array>
 #include <cstring>
+#include <deque>
+#include <set>
 #include <limits>
 #include <vector>
 
@@ -117,6 +120,14 @@ struct World {
   std::vector<uint32_t> ev_events;
   std::vector<float> ttc_angle_error, ttc_dist_center, ttc_dtc, ttc_ttc;
   std::vector<uint8_t> ttc_valid;
+  // AccelerometerSensor (sensors.py:1046-1084): the two deques of each agent, and its outputs
+  std::vector<std::deque<std::array<double, 3>>> acc_lin_hist, acc_ang_hist;
+  std::vector<double> acc_linear, acc_angular, acc_linear_jerk, acc_angular_jerk;  // [E*A,3]
+  // ViaSensor (sensors.py:1090-1150): mission vias, the consumed set, and the outputs
+  struct ViaRec { int lane; double x, y, hit_distance, required_speed; };
+  std::vector<std::vector<ViaRec>> vias;
+  std::vector<std::set<int>> via_consumed;
+  std::vector<int32_t> via_near_count, via_near_idx, via_hit_count, via_hit_idx;
   int ring = 1;
   bool stepped = false;
   int threads = 1;

@@ -115,7 +115,7 @@ class OracleWorld:
         except Exception:
             pass
 
-    def reset(self, x, y, heading, speed, route=None, route_len=None, env_ids=None, goal=None):
+    def reset(self, x, y, heading, speed, route=None, route_len=None, env_ids=None, goal=None, vias=None):
         x, y, heading, speed = (np.ascontiguousarray(v, np.float64) for v in (x, y, heading, speed))
         rs = _abi.SbResetState()
         rs.agent_x, rs.agent_y, rs.agent_heading, rs.agent_speed = _dp(x), _dp(y), _dp(heading), _dp(speed)
@@ -129,6 +129,12 @@ class OracleWorld:
             goal = [np.ascontiguousarray(g, np.float64) for g in goal]
             keep += goal
             rs.goal_x, rs.goal_y, rs.goal_radius = (_dp(g) for g in goal)
+        if vias is not None:
+            vi = [np.ascontiguousarray(v, np.int32) for v in vias[:2]]
+            vf = [np.ascontiguousarray(v, np.float64) for v in vias[2:]]
+            keep += vi + vf
+            rs.via_count, rs.via_lane = _ip(vi[0]), _ip(vi[1])
+            rs.via_x, rs.via_y, rs.via_hit_distance, rs.via_required_speed = (_dp(v) for v in vf)
         ids = None
         n = self.E
         if env_ids is not None:

@@ -6,7 +6,7 @@ from typing import Dict
 
 import numpy as np
 
-SB_ABI_VERSION = 3
+SB_ABI_VERSION = 4
 
 SB_ACTION_CONTINUOUS = 0
 SB_ACTION_LANE = 1
@@ -47,6 +47,7 @@ class SbConfig(C.Structure):
         ("events_enable", _i32), ("done_mask", C.c_uint32), ("max_episode_steps", _i32),
         ("not_moving_time", _f64), ("not_moving_distance", _f64),
         ("ttc_enable", _i32),
+        ("accel_enable", _i32), ("via_cap", _i32), ("via_acquisition_range", _f64), ("via_speed_accuracy", _f64),
     ]
 
 
@@ -93,13 +94,17 @@ class SbObsPtrs(C.Structure):
         ("ev_distance", _pf64), ("ev_reward", _pf64), ("ev_steps", _pi32),
         ("ttc_angle_error", _pf32), ("ttc_distance_from_center", _pf32), ("ttc_dtc", _pf32), ("ttc_ttc", _pf32),
         ("ttc_valid", _pu8),
+        ("acc_linear", _pf64), ("acc_angular", _pf64), ("acc_linear_jerk", _pf64), ("acc_angular_jerk", _pf64),
+        ("via_near_count", _pi32), ("via_near_idx", _pi32), ("via_hit_count", _pi32), ("via_hit_idx", _pi32),
     ]
 
 
 class SbResetState(C.Structure):
     _fields_ = [("agent_x", _pf64), ("agent_y", _pf64), ("agent_heading", _pf64), ("agent_speed", _pf64),
                 ("route", _pi32), ("route_len", _pi32),
-                ("goal_x", _pf64), ("goal_y", _pf64), ("goal_radius", _pf64)]
+                ("goal_x", _pf64), ("goal_y", _pf64), ("goal_radius", _pf64),
+                ("via_count", _pi32), ("via_lane", _pi32),
+                ("via_x", _pf64), ("via_y", _pf64), ("via_hit_distance", _pf64), ("via_required_speed", _pf64)]
 
 
 _NP = {_pi32: np.int32, _pf64: np.float64, _pu8: np.uint8, _pf32: np.float32, _pi8: np.int8, _pu32: np.uint32}
@@ -154,6 +159,12 @@ def obs_shapes(cfg: SbConfig) -> Dict[str, tuple]:
     if cfg.ttc_enable:
         out.update(ttc_angle_error=((), np.float32), ttc_distance_from_center=((), np.float32),
                    ttc_dtc=((3,), np.float32), ttc_ttc=((3,), np.float32), ttc_valid=((), np.uint8))
+    if cfg.accel_enable:
+        out.update(acc_linear=((3,), np.float64), acc_angular=((3,), np.float64),
+                   acc_linear_jerk=((3,), np.float64), acc_angular_jerk=((3,), np.float64))
+    if cfg.via_cap > 0:
+        out.update(via_near_count=((), np.int32), via_near_idx=((cfg.via_cap,), np.int32),
+                   via_hit_count=((), np.int32), via_hit_idx=((cfg.via_cap,), np.int32))
     return out
 
 

@@ -224,7 +224,7 @@ class AgentInterface:
 def compile_config(itf: AgentInterface, n_envs: int, n_agents: int, n_social: int, dt: float, *, device: int = 0,
                    route_cap: int = 16, traj_len: int = 10, nbr_cap: int = 10, wp_out_paths: int = 4,
                    wp_out_len: Optional[int] = None, lidar_wall_height: float = 0.0, lidar_miss_inf: int = 1,
-                   events: bool = True) -> _abi.SbConfig:
+                   events: bool = True, via_cap: int = 0) -> _abi.SbConfig:
     """AgentInterface (+ HiWayEnv kwargs) -> SbConfig.  ``wp_out_len`` None keeps the sensor's full
     lookahead (what ``Observation.waypoint_paths`` holds); StdObs uses 4 x 20 (format_obs.py:41)."""
     if itf.action is None:
@@ -268,6 +268,10 @@ def compile_config(itf: AgentInterface, n_envs: int, n_agents: int, n_social: in
         c.dagm_enable, c.dagm_width, c.dagm_height, c.dagm_resolution = 1, g.width, g.height, g.resolution
     if itf.waypoints and itf.neighborhood_vehicles:  # StdObs `ttc` (format_obs.py:387-388)
         c.ttc_enable = 1
+    if itf.accelerometer:
+        c.accel_enable = 1
+    if via_cap > 0:  # ViaSensor is always attached (vehicle.py:552-558); it only does work for missions with vias
+        c.via_cap, c.via_acquisition_range, c.via_speed_accuracy = int(via_cap), 40.0, 1.5
     if events:
         c.events_enable = 1
         c.done_mask = itf.done_criteria.mask()

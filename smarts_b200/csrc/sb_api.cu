@@ -32,6 +32,7 @@ struct SbHandle_ {
   DEvents ev{};
   DEvOut evo{};
   DTtcOut ttc{};
+  DExtras ex{};
   bool stepped = false;  // a sb_step since the last sb_observe (SensorState.step; `sim.resetting` otherwise)
   bool have_map = false, have_rays = false;
   double* d_rays = nullptr;
@@ -269,6 +270,11 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
   d.events_enable = c.events_enable; d.max_steps = c.max_episode_steps; d.done_mask = c.done_mask;
   d.nm_time = c.not_moving_time; d.nm_dist = c.not_moving_distance;
   d.ttc_enable = c.ttc_enable;
+  d.accel_enable = c.accel_enable; d.via_cap = c.via_cap; d.via_range = c.via_acquisition_range;
+  d.via_speed_acc = c.via_speed_accuracy;
+  if (c.via_cap < 0 || c.via_cap > SB_MAX_VIAS) return fail(h, SB_EINVAL, "via_cap out of range");
+  if (c.via_cap > 0 && !(c.via_acquisition_range >= 0 && c.via_speed_accuracy >= 0))
+    return fail(h, SB_EINVAL, "via range / speed accuracy must be >= 0");
   if (c.ttc_enable && !(c.nbr_enable && c.wp_enable)) return fail(h, SB_EINVAL, "ttc needs the neighbour and waypoint sensors");
   if (c.events_enable && !(c.not_moving_time >= 0)) return fail(h, SB_EINVAL, "not_moving_time must be >= 0");
 
@@ -328,6 +334,22 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
     DTtcOut& q = h->ttc;
     if (!(dev_alloc(h, &q.angle_error, na) && dev_alloc(h, &q.dist_center, na) && dev_alloc(h, &q.dtc, na * 3) &&
           dev_alloc(h, &q.ttc, na * 3) && dev_alloc(h, &q.valid, na)))
+      return SB_ENOMEM;
+  }
+  if (c.accel_enable) {
+    DExtras& q = h->ex;
+    if (!(dev_alloc(h, &q.lin_hist, na * 4) && dev_alloc(h, &q.ang_hist, na * 2) && dev_alloc(h, &q.hist_n, na) &&
+          dev_alloc(h, &q.acc_lin, na * 3) && dev_alloc(h, &q.acc_ang, na * 3) && dev_alloc(h, &q.jerk_lin, na * 3) &&
+          dev_alloc(h, &q.jerk_ang, na * 3)))
+      return SB_ENOMEM;
+  }
+  if (c.via_cap > 0) {
+    DExtras& q = h->ex;
+    const size_t nc = na * c.via_cap;
+    if (!(dev_alloc(h, &q.via_count, na) && dev_alloc(h, &q.via_lane, nc) && dev_alloc(h, &q.via_x, nc) &&
+          dev_alloc(h, &q.via_y, nc) && dev_alloc(h, &q.via_hit, nc) && dev_alloc(h, &q.via_speed, nc) &&
+          dev_alloc(h, &q.via_consumed, na) && dev_alloc(h, &q.near_count, na) && dev_alloc(h, &q.near_idx, nc) &&
+          dev_alloc(h, &q.hit_count, na) && dev_alloc(h, &q.hit_idx, nc)))
       return SB_ENOMEM;
   }
   if (!dev_alloc(h, &h->d_picks, na)) return SB_ENOMEM;
@@ -581,6 +603,62 @@ int sb_upload_lidar_rays(SbHandle h, const double* base_rays, int32_t n_rays) {
   return SB_OK;
 }
 
+// second half of sb_reset: fresh AccelerometerSensor / ViaSensor state and the missions' via points
+static bool reset_extras(SbHandle h, const int32_t* env_ids, int n, const SbResetState* init) {
+  const DCfg& c = h->dc;
+  const size_t na = (size_t)n * c.A, nc = na * (c.via_cap > 0 ? c.via_cap : 0);
+  const bool vias = c.via_cap > 0 && init->via_count;
+  if (vias) {
+    if (!(init->via_lane && init->via_x && init->via_y && init->via_hit_distance && init->via_required_speed)) {
+      fail(h, SB_EINVAL, "via_count given without the via arrays");
+      return false;
+    }
+    for (size_t t = 0; t < na; ++t) {
+      const int cnt = init->via_count[t];
+      if (cnt < 0 || cnt > c.via_cap) {
+        fail(h, SB_EINVAL, "via_count out of range");
+        return false;
+      }
+      for (int k = 0; k < cnt; ++k) {
+        const int l = init->via_lane[t * c.via_cap + k];
+        if (l < 0 || l >= h->dmap.n_lanes) {
+          fail(h, SB_EINVAL, "via lane out of range");
+          return false;
+        }
+      }
+    }
+  }
+  const size_t off_ids = 0, off_cnt = ((size_t)n * 4 + 7) / 8 * 8, off_lane = off_cnt + (na * 4 + 7) / 8 * 8,
+               off_x = off_lane + (nc * 4 + 7) / 8 * 8, off_y = off_x + nc * 8, off_hit = off_y + nc * 8,
+               off_sp = off_hit + nc * 8, total = off_sp + nc * 8 + 8;
+  std::vector<unsigned char> host(total, 0);
+  if (env_ids) std::memcpy(&host[off_ids], env_ids, (size_t)n * 4);
+  if (vias) {
+    std::memcpy(&host[off_cnt], init->via_count, na * 4);
+    std::memcpy(&host[off_lane], init->via_lane, nc * 4);
+    std::memcpy(&host[off_x], init->via_x, nc * 8);
+    std::memcpy(&host[off_y], init->via_y, nc * 8);
+    std::memcpy(&host[off_hit], init->via_hit_distance, nc * 8);
+    std::memcpy(&host[off_sp], init->via_required_speed, nc * 8);
+  }
+  unsigned char* dev = nullptr;
+  if (!cuda_ok(h, cudaMalloc(&dev, total), "cudaMalloc(reset extras)")) return false;
+  bool ok = cuda_ok(h, cudaMemcpy(dev, host.data(), total, cudaMemcpyHostToDevice), "cudaMemcpy(reset extras)");
+  if (ok) {
+    const int threads = n * c.A;
+    k_reset_extras<<<(threads + 127) / 128, 128>>>(
+        c, h->ex, env_ids ? reinterpret_cast<const int32_t*>(dev + off_ids) : nullptr, n,
+        vias ? reinterpret_cast<const int32_t*>(dev + off_cnt) : nullptr,
+        reinterpret_cast<const int32_t*>(dev + off_lane), reinterpret_cast<const double*>(dev + off_x),
+        reinterpret_cast<const double*>(dev + off_y), reinterpret_cast<const double*>(dev + off_hit),
+        reinterpret_cast<const double*>(dev + off_sp));
+    h->launches++;
+    ok = cuda_ok(h, cudaDeviceSynchronize(), "k_reset_extras");
+  }
+  cudaFree(dev);
+  return ok;
+}
+
 int sb_reset(SbHandle h, const int32_t* env_ids, int32_t n, const SbResetState* init) {
   if (!h || !init || !init->agent_x || !init->agent_y || !init->agent_heading || !init->agent_speed) return SB_EINVAL;
   if (h->cuda_err) return SB_ECUDA;
@@ -629,6 +707,8 @@ int sb_reset(SbHandle h, const int32_t* env_ids, int32_t n, const SbResetState* 
     ok = cuda_ok(h, cudaDeviceSynchronize(), "k_reset");
   }
   cudaFree(dev);
+  if (ok && (c.accel_enable || c.via_cap > 0)) ok = reset_extras(h, env_ids, n, init);
+  if (!ok && !h->cuda_err) return SB_EINVAL;
   return ok ? SB_OK : SB_ECUDA;
 }
 
@@ -685,6 +765,10 @@ int sb_observe(SbHandle h, void* stream) {
   if (c.ttc_enable) {
     LaunchScope ls(h, SB_K_TTC, st);
     k_ttc<<<(na + SB_TTC_WARPS - 1) / SB_TTC_WARPS, SB_TTC_WARPS * 32, 0, st>>>(c, h->st, h->ob, h->ttc);
+  }
+  if (c.accel_enable || c.via_cap > 0) {
+    LaunchScope ls(h, SB_K_EXTRAS, st);
+    k_extras<<<(na + 127) / 128, 128, 0, st>>>(c, h->dmap, h->st, h->ex);
   }
   if (c.lidar_enable) {
     LaunchScope ls(h, SB_K_LIDAR, st);
@@ -836,6 +920,16 @@ int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs* dst) {
     cpy(dst->ev_collidee, q.collidee, na * 4); cpy(dst->ev_distance, q.distance, na * 8);
     cpy(dst->ev_reward, q.reward, na * 8); cpy(dst->ev_steps, q.steps, na * 4);
   }
+  if (c.accel_enable) {
+    const DExtras& q = h->ex;
+    cpy(dst->acc_linear, q.acc_lin, na * 24); cpy(dst->acc_angular, q.acc_ang, na * 24);
+    cpy(dst->acc_linear_jerk, q.jerk_lin, na * 24); cpy(dst->acc_angular_jerk, q.jerk_ang, na * 24);
+  }
+  if (c.via_cap > 0) {
+    const DExtras& q = h->ex;
+    cpy(dst->via_near_count, q.near_count, na * 4); cpy(dst->via_near_idx, q.near_idx, na * 4 * c.via_cap);
+    cpy(dst->via_hit_count, q.hit_count, na * 4); cpy(dst->via_hit_idx, q.hit_idx, na * 4 * c.via_cap);
+  }
   if (c.ttc_enable) {
     const DTtcOut& q = h->ttc;
     cpy(dst->ttc_angle_error, q.angle_error, na * 4); cpy(dst->ttc_distance_from_center, q.dist_center, na * 4);
@@ -913,6 +1007,10 @@ int sb_get_obs(SbHandle h, SbObsPtrs* out) {
   out->ev_collidee = q.collidee; out->ev_distance = q.distance; out->ev_reward = q.reward; out->ev_steps = q.steps;
   out->ttc_angle_error = h->ttc.angle_error; out->ttc_distance_from_center = h->ttc.dist_center;
   out->ttc_dtc = h->ttc.dtc; out->ttc_ttc = h->ttc.ttc; out->ttc_valid = h->ttc.valid;
+  out->acc_linear = h->ex.acc_lin; out->acc_angular = h->ex.acc_ang;
+  out->acc_linear_jerk = h->ex.jerk_lin; out->acc_angular_jerk = h->ex.jerk_ang;
+  out->via_near_count = h->ex.near_count; out->via_near_idx = h->ex.near_idx;
+  out->via_hit_count = h->ex.hit_count; out->via_hit_idx = h->ex.hit_idx;
   return SB_OK;
 }
 

@@ -9,6 +9,7 @@
 //   k_raster          OGM + DrivableAreaGridMap                            (block per agent)
 //   k_events          Events / done / trip-meter reward / contacts         (warp per agent, sb_events.cuh)
 //   k_ttc             lane_ttc (StdObs ttc)                                (warp per agent, sb_ttc.cuh)
+//   k_extras          accelerometer + via sensor                            (thread per agent, sb_extras.cuh)
 #pragma once
 
 #include "sb_control.cuh"
@@ -44,9 +45,9 @@ struct DCfg {
   double ogm_res;
   int32_t dagm_enable, dagm_w, dagm_h;
   double dagm_res;
-  int32_t events_enable, max_steps, ttc_enable;
+  int32_t events_enable, max_steps, ttc_enable, accel_enable, via_cap;
   uint32_t done_mask;
-  double nm_time, nm_dist;
+  double nm_time, nm_dist, via_range, via_speed_acc;
 };
 
 // --------------------------------------------------------------------------------- social
@@ -422,6 +423,7 @@ k_observe(DCfg c, DMap m, DState s, DObs o, double* __restrict__ trip_wp) {
 // --------------------------------------------------------------------------------- events
 #include "sb_events.cuh"
 #include "sb_ttc.cuh"
+#include "sb_extras.cuh"
 
 // --------------------------------------------------------------------------------- lidar
 // k_lidar lives in sb_lidar.cuh (azimuth-sorted warps, sector / per-ray culls, exact binary64 tests).

@@ -23,7 +23,7 @@ EXPORTS = [
     "sb_set_social", "sb_step", "sb_observe", "sb_step_host", "sb_copy_obs_to_host", "sb_get_obs",
     "sb_get_state", "sb_launch_count", "sb_last_error", "sb_set_timing", "sb_collect_timing",
 ]
-KERNEL_KINDS = ["k_set_social", "k_control", "k_observe", "k_lidar", "k_raster", "k_events", "k_pack_bits", "k_ttc"]
+KERNEL_KINDS = ["k_set_social", "k_control", "k_observe", "k_lidar", "k_raster", "k_events", "k_pack_bits", "k_ttc", "k_extras"]
 
 
 class SmartsB200Error(RuntimeError):
@@ -156,9 +156,10 @@ class Engine:
         return C.c_void_p(self._torch.cuda.current_stream(self.device).cuda_stream)
 
     # -- the step ------------------------------------------------------------------------
-    def reset(self, x, y, heading, speed, route=None, route_len=None, env_ids=None, goal=None):
+    def reset(self, x, y, heading, speed, route=None, route_len=None, env_ids=None, goal=None, vias=None):
         """Place agents (arrays [n, A]); ``route`` int32 [n, A, route_cap] road indices (-1 pad);
-        ``goal`` = (x, y, radius) arrays [n, A] of PositionalGoals (radius < 0: EndlessGoal)."""
+        ``goal`` = (x, y, radius) arrays [n, A] of PositionalGoals (radius < 0: EndlessGoal);
+        ``vias`` = (count [n, A], lane [n, A, via_cap], x, y, hit_distance, required_speed) of Mission.via."""
         f = lambda a: np.ascontiguousarray(a, np.float64)  # noqa: E731
         x, y, heading, speed = f(x), f(y), f(heading), f(speed)
         dp = lambda a: a.ctypes.data_as(C.POINTER(C.c_double))  # noqa: E731
@@ -173,6 +174,12 @@ class Engine:
             gx, gy, gr = (f(g) for g in goal)
             assert gx.size == gy.size == gr.size == x.size
             rs.goal_x, rs.goal_y, rs.goal_radius = dp(gx), dp(gy), dp(gr)
+        if vias is not None:
+            vc, vl = (np.ascontiguousarray(v, np.int32) for v in vias[:2])
+            vx, vy, vh, vs = (f(v) for v in vias[2:])
+            assert vl.size == vx.size == vy.size == vh.size == vs.size == vc.size * self.cfg.via_cap
+            rs.via_count, rs.via_lane = ip(vc), ip(vl)
+            rs.via_x, rs.via_y, rs.via_hit_distance, rs.via_required_speed = dp(vx), dp(vy), dp(vh), dp(vs)
         ids, n = None, self.E
         if env_ids is not None:
             env_ids = np.ascontiguousarray(env_ids, np.int32)

@@ -26,7 +26,7 @@ import numpy as np
 from . import _abi, lidar_params
 from .agent_interface import ActionSpaceType, AgentInterface, AgentSpec, compile_config
 from .observation import (Collision, Dimensions, DrivableAreaGridMap, EgoVehicleObservation, Events,
-                          GridMapMetadata, Mission, Observation, OccupancyGridMap, VehicleObservation, Vias,
+                          GridMapMetadata, Mission, Observation, OccupancyGridMap, VehicleObservation, Via, ViaPoint, Vias,
                           Waypoint)
 from .road_map import RoadMapData
 
@@ -133,7 +133,8 @@ class BatchedHiWayEnv:
         self._auto_reset = auto_reset
         self.cfg = compile_config(self.interface, self.E, self.A, self.M, self.dt, device=device,
                                   route_cap=route_cap, traj_len=traj_len, lidar_wall_height=lidar_wall_height,
-                                  wp_out_len=wp_out_len)
+                                  wp_out_len=wp_out_len,
+                                  via_cap=max([len(scenario.missions[a].via) for a in self.agent_ids] + [0]))
         rays = lidar_params.base_rays(self.interface.lidar.sensor_params) if self.interface.lidar else None
         self._base_rays = rays
         self._engine: Optional[Engine] = Engine(self.cfg, self.road_map, rays)
@@ -198,7 +199,26 @@ class BatchedHiWayEnv:
                 off = 0.5 * float(rm.lane_length[lane]) if m.end_offset is None else m.end_offset
                 px, py, _ = rm.lane_start_pose(m.end_road, m.end_lane, off)
                 gx[:, a], gy[:, a], gr[:, a] = px, py, m.goal_radius
-        return dict(x=x, y=y, h=h, v=v, route=route, rlen=rlen, goal=(gx, gy, gr))
+        return dict(x=x, y=y, h=h, v=v, route=route, rlen=rlen, goal=(gx, gy, gr), vias=self._build_vias())
+
+    def _build_vias(self):
+        """Scenario.to_scenario_via (scenario.py:652-676): sstudio vias -> lane, position, hit distance."""
+        C_ = self.cfg.via_cap
+        if C_ <= 0:
+            return None
+        rm, E, A = self.road_map, self.E, self.A
+        cnt = np.zeros((E, A), np.int32)
+        lane = np.full((E, A, C_), -1, np.int32)
+        vx = np.zeros((E, A, C_)); vy = np.zeros_like(vx); hit = np.zeros_like(vx); spd = np.zeros_like(vx)
+        for a, aid in enumerate(self.agent_ids):
+            for k, via in enumerate(self.scenario.missions[aid].via):
+                l = rm.lane_of_road(via.road_id, via.lane_index)
+                px, py, _ = rm.lane_start_pose(via.road_id, via.lane_index, float(via.lane_offset))
+                lane[:, a, k], vx[:, a, k], vy[:, a, k] = l, px, py
+                hit[:, a, k] = via.hit_distance if via.hit_distance > 0 else 0.5 * float(rm.lane_width[l])
+                spd[:, a, k] = via.required_speed
+            cnt[:, a] = len(self.scenario.missions[aid].via)
+        return cnt, lane, vx, vy, hit, spd
 
     def _social(self, t: int) -> Optional[np.ndarray]:
         tr = self.scenario.traffic
@@ -216,7 +236,8 @@ class BatchedHiWayEnv:
         s = self._start
         sel = slice(None) if env_ids is None else env_ids
         self.engine.reset(s["x"][sel], s["y"][sel], s["h"][sel], s["v"][sel], s["route"][sel], s["rlen"][sel],
-                          env_ids=env_ids, goal=tuple(g[sel] for g in s["goal"]))
+                          env_ids=env_ids, goal=tuple(g[sel] for g in s["goal"]),
+                          vias=None if s["vias"] is None else tuple(q[sel] for q in s["vias"]))
         self._tick[sel] = 0
         self._done_agents[sel] = False
 
@@ -279,10 +300,12 @@ class BatchedHiWayEnv:
         lane_idx = t.as_tensor(self.road_map.lane_idx_in_road, device=self.engine.device)
         ev = o["ev_events"]
         bit = lambda b: ((ev & b) != 0).to(t.int8)  # noqa: E731
+        acc = (lambda k: o[k].to(f32)) if self.cfg.accel_enable else (lambda k: zeros3)  # noqa: E731
         out: Dict[str, Any] = {
             "dist": o["ev_distance"].to(f32),
             "ego": {
-                "angular_acceleration": zeros3, "angular_jerk": zeros3, "linear_acceleration": zeros3, "linear_jerk": zeros3,
+                "angular_acceleration": acc("acc_angular"), "angular_jerk": acc("acc_angular_jerk"),
+                "linear_acceleration": acc("acc_linear"), "linear_jerk": acc("acc_linear_jerk"),
                 "angular_velocity": t.stack([t.zeros_like(ego["yaw_rate"]), t.zeros_like(ego["yaw_rate"]), ego["yaw_rate"]], -1).to(f32),
                 "box": t.stack([ego["length"], ego["width"], ego["height"]], -1).to(f32),
                 "heading": ego["heading"].to(f32),
@@ -346,7 +369,10 @@ class BatchedHiWayEnv:
             road_id=road_id, lane_id=lane_id, lane_index=lane_index, mission=self.scenario.missions[self.agent_ids[a]],
             linear_velocity=np.array([-math.sin(hd) * sp, math.cos(hd) * sp, 0.0]),
             angular_velocity=np.array([0.0, 0.0, float(s["yaw_rate"][e, a])]),
-            linear_acceleration=None, angular_acceleration=None, linear_jerk=None, angular_jerk=None)
+            linear_acceleration=o["acc_linear"][e, a].copy() if "acc_linear" in o else None,
+            angular_acceleration=o["acc_angular"][e, a].copy() if "acc_angular" in o else None,
+            linear_jerk=o["acc_linear_jerk"][e, a].copy() if "acc_linear_jerk" in o else None,
+            angular_jerk=o["acc_angular_jerk"][e, a].copy() if "acc_angular_jerk" in o else None)
         nbrs = None
         if itf.neighborhood_vehicles:
             nbrs = []
@@ -400,7 +426,22 @@ class BatchedHiWayEnv:
                            events=events, ego_vehicle_state=ego, neighborhood_vehicle_states=nbrs,
                            waypoint_paths=wps, distance_travelled=float(o["ev_distance"][e, a]),
                            lidar_point_cloud=lidar, drivable_area_grid_map=dagm, occupancy_grid_map=ogm,
-                           top_down_rgb=None, road_waypoints=None, via_data=Vias([], []))
+                           top_down_rgb=None, road_waypoints=None, via_data=self._vias(e, a))
+
+    def _vias(self, e: int, a: int) -> Vias:
+        """Observation.via_data (sensors.py:337-347) from the kernel's index lists."""
+        o = self._host
+        if "via_near_idx" not in o:
+            return Vias([], [])
+        mv = self.scenario.missions[self.agent_ids[a]].via
+        pos = self._start["vias"]
+
+        def point(k):
+            return ViaPoint((float(pos[2][e, a, k]), float(pos[3][e, a, k])), mv[k].lane_index, mv[k].road_id,
+                            mv[k].required_speed)
+        near = [point(int(k)) for k in o["via_near_idx"][e, a, :int(o["via_near_count"][e, a])]]
+        hit = [point(int(k)) for k in o["via_hit_idx"][e, a, :int(o["via_hit_count"][e, a])]]
+        return Vias(near, hit)
 
     def _env_observations(self, e: int) -> Dict[str, Observation]:
         return {aid: self._observation(e, a) for a, aid in enumerate(self.agent_ids) if not self._done_agents[e, a]}

@@ -94,6 +94,14 @@ class DrivableAreaGridMap(NamedTuple):
     data: np.ndarray
 
 
+class ViaPoint(NamedTuple):
+    """sensors.py:154-165."""
+    position: tuple
+    lane_index: float
+    road_id: str
+    required_speed: float
+
+
 class Vias(NamedTuple):
     near_via_points: List
     hit_via_points: List
@@ -134,6 +142,17 @@ class EndlessGoal:
 
 
 @dataclass(frozen=True)
+class Via:
+    """smarts/sstudio/types.py:423-435: a point on a lane the agent should pass at ``required_speed``;
+    a non-positive ``hit_distance`` means half the lane width (scenario.py:652-676)."""
+    road_id: str
+    lane_index: int
+    lane_offset: float
+    required_speed: float
+    hit_distance: float = -1
+
+
+@dataclass(frozen=True)
 class Mission:
     """What sstudio's ``Mission(Route(begin=(road, lane, offset), end=(road, lane, offset)))`` pins
     down for one agent (smarts/sstudio/types.py Route/Mission -> smarts/core/plan.py Mission)."""
@@ -146,3 +165,4 @@ class Mission:
     goal_radius: float = 1.0               # PositionalGoal default (plan.py:100)
     endless: bool = False
     start_speed: float = 0.0
+    via: tuple = ()                        # of Via (sstudio types.py:423-435)

@@ -10,7 +10,7 @@ from smarts_b200.agent_interface import (OGM, Agent, AgentInterface, AgentSpec, 
                                          compile_config)
 from smarts_b200.hiway_env import (BatchedHiWayEnv, HiWayEnv, Scenario, SMARTSDestroyedError, SMARTSNotSetupError,
                                    encode_actions, make)
-from smarts_b200.observation import Mission, Observation
+from smarts_b200.observation import Mission, Observation, Via
 
 MISSIONS = {"A0": Mission("edge-south-SN", 1, 10.0, "edge-west-EW", start_speed=5.0),
             "A1": Mission("edge-west-WE", 0, 10.0, "edge-east-WE", start_speed=5.0),
@@ -47,6 +47,9 @@ def test_compile_config_from_interface():
     assert c.dagm_enable == 0 and c.nbr_radius == 50.0 and c.nbr_cap == 10
     assert c.done_mask == _abi.SB_EV_COLLISION | _abi.SB_EV_OFF_ROAD | _abi.SB_EV_WRONG_WAY
     assert c.max_episode_steps == 100 and c.not_moving_time == 60.0
+    assert c.accel_enable == 1 and c.via_cap == 0          # accelerometer defaults to True (agent_interface.py:260)
+    cv = compile_config(itf, 8, 2, 20, 0.1, via_cap=3)
+    assert (cv.via_cap, cv.via_acquisition_range, cv.via_speed_accuracy) == (3, 40.0, 1.5)   # vehicle.py:552-558
     assert compile_config(AgentInterface.from_type(AgentType.Tagger), 1, 1, 0, 0.1).nbr_radius == -1.0  # radius=None
     for bad in (AgentType.Full, AgentType.MPCTracker, AgentType.Boid, AgentType.Buddha):
         with pytest.raises((NotImplementedError, ValueError)):
@@ -138,6 +141,51 @@ def test_hiway_env_step_contract():
     env.close(); env.close()
     with pytest.raises(SMARTSDestroyedError):
         env.step({})
+
+
+@pytest.mark.gpu
+def test_hiway_env_vias_and_accelerometer():
+    """Mission vias reach Observation.via_data (near sorted by distance, hit once at the required speed) and the
+    accelerometer members of the ego state are finite differences of its velocity vectors."""
+    rm = load_map("4lane")
+    itf = AgentInterface.from_type(AgentType.Laner, max_episode_steps=60)
+    specs = _specs(itf)
+    # a dry run without vias tells how fast A0 is at each point of its (straight) approach
+    env = make("smarts.env:hiway-v0", scenarios=[Scenario(rm, MISSIONS)], agent_specs=specs)
+    obs, track = env.reset(), []
+    for t in range(25):
+        obs, _, _, _ = env.step({i: "keep_lane" for i in obs})
+        track.append((obs["A0"].distance_travelled, obs["A0"].ego_vehicle_state.speed))
+    env.close()
+    (d1, v1), (d2, v2) = track[8], track[20]
+    assert d2 - d1 > 6.0
+    missions = dict(MISSIONS)
+    missions["A0"] = Mission("edge-south-SN", 1, 10.0, "edge-west-EW", start_speed=5.0,
+                             via=(Via("edge-south-SN", 1, 10.0 + d2, v2 + 1.0, hit_distance=2.0),
+                                  Via("edge-south-SN", 1, 10.0 + d1, v1 - 1.0),
+                                  Via("edge-south-SN", 0, 10.0 + d1, 30.0, hit_distance=5.0)))
+    env = make("smarts.env:hiway-v0", scenarios=[Scenario(rm, missions)], agent_specs=specs)
+    obs = env.reset()
+    near = obs["A0"].via_data.near_via_points
+    assert [p.required_speed for p in near] == [v1 - 1.0, 30.0, v2 + 1.0] and obs["A0"].via_data.hit_via_points == []
+    assert obs["A1"].via_data.near_via_points == []
+    assert np.array_equal(obs["A0"].ego_vehicle_state.linear_acceleration, np.zeros(3))
+    hits, prev_v, prev_a = [], obs["A0"].ego_vehicle_state.linear_velocity, None
+    for t in range(40):
+        obs, _, dones, _ = env.step({i: "keep_lane" for i in obs})
+        if "A0" not in obs:
+            break
+        ego = obs["A0"].ego_vehicle_state
+        acc = (ego.linear_velocity - prev_v) / 0.1
+        assert np.allclose(ego.linear_acceleration, acc, rtol=1e-9, atol=1e-9)
+        if prev_a is not None:
+            assert np.allclose(ego.linear_jerk, acc - prev_a, rtol=1e-9, atol=1e-9)
+        prev_v, prev_a = ego.linear_velocity, acc
+        hits += [p.required_speed for p in obs["A0"].via_data.hit_via_points]
+    assert sorted(hits) == sorted([v1 - 1.0, v2 + 1.0])   # each collected exactly once; the 30 m/s via never matches the speed
+    so = env.batched.std_obs()
+    assert so["ego"]["linear_acceleration"].dtype.is_floating_point and tuple(so["ego"]["linear_jerk"].shape) == (1, 4, 3)
+    env.close()
 
 
 @pytest.mark.gpu
