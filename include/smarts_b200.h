@@ -125,6 +125,12 @@ typedef struct SbConfig {
   int32_t via_cap;              /* <= SB_MAX_VIAS */
   double via_acquisition_range;
   double via_speed_accuracy;
+  /* ego_centric_observation_adapter (smarts/core/utils/adapters/ego_centric_adapters.py:62-178): 1 = sb_observe
+   * ends by rewriting the positional buffers in the ego frame (origin at the ego, +x along its heading):
+   * nbr_pos / nbr_heading, wp_pos / wp_heading, lidar_points.  Only filled entries are touched; a lidar miss
+   * stays (0,0,0) with lidar_miss_inf = 0 and becomes (NaN,NaN,NaN) with lidar_miss_inf = 1 (inf - x through
+   * the rotation, as in the reference). */
+  int32_t ego_frame;
 } SbConfig;
 
 /* Per-scenario constant road map (host pointers, copied once).  Built by
@@ -295,7 +301,8 @@ int64_t sb_launch_count(SbHandle h);
 #define SB_K_PACK 6    /* k_pack_bits: grid transport of sb_copy_obs_to_host */
 #define SB_K_TTC 7
 #define SB_K_EXTRAS 8   /* accelerometer + vias */
-#define SB_K_COUNT 9
+#define SB_K_EGO_FRAME 9
+#define SB_K_COUNT 10
 int sb_set_timing(SbHandle h, int on);
 int sb_collect_timing(SbHandle h, double *ms_sum /*[SB_K_COUNT]*/, int64_t *count /*[SB_K_COUNT]*/);
 const char *sb_last_error(SbHandle h);

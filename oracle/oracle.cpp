@@ -981,6 +981,68 @@ void observe_vias(World& w, int e, int a) {
   w.via_hit_count[ai] = (int)hit_points.size();
 }
 
+// ego_centric_observation_adapter, smarts/core/utils/adapters/ego_centric_adapters.py:62-178, on the
+// observation arrays of one agent: neighbours (:160-167), lidar points (:113-123), waypoints (:85-96).
+// wrap_value: utils/math.py:452-461; position_to_ego_frame / _gen_ego_frame_matrix: utils/math.py:464-487.
+double wrap_value(double value, double lo, double hi) {
+  double v = value;
+  const double diff = hi - lo;
+  if (value <= lo) v = hi - sb_pymod(lo - value, diff);
+  if (value > hi) v = lo + sb_pymod(value - hi, diff);
+  return v;
+}
+
+void position_to_ego_frame(double* pos, const double ego_position[3], double ego_heading) {
+  double m[3][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}};  // np.eye(3)
+  double sn, cs;
+  sb_sincos(-ego_heading, &sn, &cs);
+  m[0][0] = cs;
+  m[0][1] = -sn;
+  m[1][0] = sn;
+  m[1][1] = cs;
+  const double rel[3] = {pos[0] - ego_position[0], pos[1] - ego_position[1], pos[2] - ego_position[2]};
+  if (!(std::isfinite(rel[0]) && std::isfinite(rel[1]) && std::isfinite(rel[2]))) {
+    // a lidar miss (inf, inf, inf): every row of the product holds a 0 * inf
+    pos[0] = pos[1] = pos[2] = std::numeric_limits<double>::quiet_NaN();
+    return;
+  }
+  // the third column of rows 0-1 and the first two of row 2 are zero: their products add +-0
+  pos[0] = m[0][0] * rel[0] + m[0][1] * rel[1];
+  pos[1] = m[1][0] * rel[0] + m[1][1] * rel[1];
+  pos[2] = rel[2];
+}
+
+void ego_frame_agent(World& w, int e, int a) {
+  const int ai = e * w.A + a, vi = e * w.V + a;
+  const SbConfig& c = w.cfg;
+  const double position[3] = {w.pos_x[vi], w.pos_y[vi], w.pos_z[vi]};
+  const double heading = w.heading[vi];
+  if (c.lidar_enable)
+    for (int r = 0; r < c.lidar_rays; ++r) {
+      const size_t q = (size_t)ai * c.lidar_rays + r;
+      if (!w.lidar_hits[q] && !c.lidar_miss_inf) continue;  // zero-filled misses of StdObs are not points
+      position_to_ego_frame(&w.lidar_points[q * 3], position, heading);
+    }
+  if (c.nbr_enable)
+    for (int k = 0; k < std::min(w.nbr_count[ai], c.nbr_cap); ++k) {
+      const size_t q = (size_t)ai * c.nbr_cap + k;
+      position_to_ego_frame(&w.nbr_pos[q * 3], position, heading);
+      w.nbr_heading[q] = (float)wrap_value((double)w.nbr_heading[q] - heading, -SB_PI, SB_PI);
+    }
+  if (c.wp_enable) {
+    const int P = c.wp_out_paths, L = c.wp_out_len;
+    for (int p = 0; p < std::min(w.wp_n_paths[ai], P); ++p)
+      for (int i = 0; i < w.wp_len[(size_t)ai * P + p]; ++i) {
+        const size_t q = ((size_t)ai * P + p) * L + i;
+        double v[3] = {w.wp_pos[q * 3], w.wp_pos[q * 3 + 1], 0.0};  // np.append(wp.pos, [0])
+        position_to_ego_frame(v, position, heading);
+        w.wp_pos[q * 3] = v[0];
+        w.wp_pos[q * 3 + 1] = v[1];
+        w.wp_heading[q] = (float)wrap_value((double)w.wp_heading[q] - heading, -SB_PI, SB_PI);
+      }
+  }
+}
+
 void observe_agent(World& w, int e, int a) {
   const int ai = e * w.A + a, vi = e * w.V + a;
   // sensors.py:277-285, radius None -> max(10, 2 * default lane width) (sumo_road_network.py:679-680)
@@ -1271,6 +1333,7 @@ void or_observe(void* h) {
     parallel_for(w.E * w.A, w.threads, 1, [&](int i) { observe_events(w, i / w.A, i % w.A, ticked); });
     w.stepped = false;
   }
+  if (w.cfg.ego_frame) parallel_for(w.E * w.A, w.threads, 1, [&](int i) { ego_frame_agent(w, i / w.A, i % w.A); });
 }
 
 void or_get_state(void* h, SbStatePtrs* o) {

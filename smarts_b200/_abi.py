@@ -48,6 +48,7 @@ class SbConfig(C.Structure):
         ("not_moving_time", _f64), ("not_moving_distance", _f64),
         ("ttc_enable", _i32),
         ("accel_enable", _i32), ("via_cap", _i32), ("via_acquisition_range", _f64), ("via_speed_accuracy", _f64),
+        ("ego_frame", _i32),
     ]
 
 

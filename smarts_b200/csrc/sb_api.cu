@@ -272,6 +272,7 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
   d.ttc_enable = c.ttc_enable;
   d.accel_enable = c.accel_enable; d.via_cap = c.via_cap; d.via_range = c.via_acquisition_range;
   d.via_speed_acc = c.via_speed_accuracy;
+  d.ego_frame = c.ego_frame;
   if (c.via_cap < 0 || c.via_cap > SB_MAX_VIAS) return fail(h, SB_EINVAL, "via_cap out of range");
   if (c.via_cap > 0 && !(c.via_acquisition_range >= 0 && c.via_speed_accuracy >= 0))
     return fail(h, SB_EINVAL, "via range / speed accuracy must be >= 0");
@@ -784,6 +785,10 @@ int sb_observe(SbHandle h, void* stream) {
     k_events<<<(na + SB_EV_WARPS - 1) / SB_EV_WARPS, SB_EV_WARPS * 32, 0, st>>>(c, h->dmap, h->st, h->ev, h->evo,
                                                                               h->stepped ? 1 : 0);
     h->stepped = false;
+  }
+  if (c.ego_frame && (c.lidar_enable || c.nbr_enable || c.wp_enable)) {  // last: k_ttc / k_events read world-frame buffers
+    LaunchScope ls(h, SB_K_EGO_FRAME, st);
+    k_ego_frame<<<na, SB_EGO_THREADS, 0, st>>>(c, h->st, h->ob);
   }
   return cuda_ok(h, cudaGetLastError(), "k_observe") ? SB_OK : SB_ECUDA;
 }

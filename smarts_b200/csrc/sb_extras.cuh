@@ -142,3 +142,70 @@ __global__ void k_reset_extras(DCfg c, DExtras x, const int32_t* env_ids, int n,
     }
   }
 }
+
+// ---------------------------------------------------------------------------------------------
+// k_ego_frame: ego_centric_observation_adapter (smarts/core/utils/adapters/ego_centric_adapters.py:62-178)
+// on the observation buffers, in place, after every consumer of the world-frame values has run.
+//   transform(v)      = position_to_ego_frame(v, ego.position, ego.heading), utils/math.py:464-487:
+//                       rotation by -heading of (v - ego position), z kept
+//   adjust_heading(h) = wrap_value(h - ego.heading, -pi, pi), utils/math.py:452-461
+// One CTA per agent, threads stride over the agent's lidar points, neighbours and waypoints.
+#define SB_EGO_THREADS 128
+
+__device__ __forceinline__ double d_wrap_value_pi(double value) {
+  double v = value;
+  if (value <= -SB_PI) v = SB_PI - sb_pymod(-SB_PI - value, SB_TWO_PI);
+  if (value > SB_PI) v = -SB_PI + sb_pymod(value - SB_PI, SB_TWO_PI);
+  return v;
+}
+
+__device__ __forceinline__ void d_to_ego_frame(double* p, double ex, double ey, double ez, double cs, double sn) {
+  const double rx = p[0] - ex, ry = p[1] - ey, rz = p[2] - ez;
+  if (!(isfinite(rx) && isfinite(ry) && isfinite(rz))) {  // inf through the matrix product: 0 * inf
+    p[0] = p[1] = p[2] = __longlong_as_double(0x7ff8000000000000LL);
+    return;
+  }
+  // [[cos(-h), -sin(-h), 0], [sin(-h), cos(-h), 0], [0, 0, 1]] @ rel
+  p[0] = cs * rx + (-sn) * ry;
+  p[1] = sn * rx + cs * ry;
+  p[2] = rz;
+}
+
+__global__ void __launch_bounds__(SB_EGO_THREADS) k_ego_frame(DCfg c, DState s, DObs o) {
+  const int ai = blockIdx.x;
+  const int e = ai / c.A, a = ai - e * c.A, vi = e * c.V + a;
+  const double ex = s.pos_x[vi], ey = s.pos_y[vi], ez = s.pos_z[vi], eh = s.heading[vi];
+  double sn, cs;
+  sb_sincos(-eh, &sn, &cs);
+  if (c.lidar_enable) {
+    const int R = c.lidar_rays;
+    for (int r = threadIdx.x; r < R; r += SB_EGO_THREADS) {
+      const size_t q = (size_t)ai * R + r;
+      if (!o.lidar_hits[q] && !c.lidar_miss_inf) continue;  // StdObs zero fill (format_obs.py:437-443) stays
+      d_to_ego_frame(o.lidar_points + q * 3, ex, ey, ez, cs, sn);
+    }
+  }
+  if (c.nbr_enable) {
+    const int cnt = o.nbr_count[ai], n = cnt < c.nbr_cap ? cnt : c.nbr_cap;
+    for (int k = threadIdx.x; k < n; k += SB_EGO_THREADS) {
+      const size_t q = (size_t)ai * c.nbr_cap + k;
+      d_to_ego_frame(o.nbr_pos + q * 3, ex, ey, ez, cs, sn);
+      o.nbr_heading[q] = (float)d_wrap_value_pi((double)o.nbr_heading[q] - eh);
+    }
+  }
+  if (c.wp_enable) {
+    const int P = c.wp_out_paths, L = c.wp_out_len;
+    const int tp = o.wp_n_paths[ai], np_ = tp < P ? tp : P;
+    for (int t = threadIdx.x; t < np_ * L; t += SB_EGO_THREADS) {
+      const int p = t / L, i = t - p * L;
+      if (i >= o.wp_len[(size_t)ai * P + p]) continue;
+      const size_t q = ((size_t)ai * P + p) * L + i;
+      // transform(np.append(wp.pos, [0]))[:2]: the waypoint sits at z = 0, the stored z stays 0
+      double v[3] = {o.wp_pos[q * 3 + 0], o.wp_pos[q * 3 + 1], 0.0};
+      d_to_ego_frame(v, ex, ey, ez, cs, sn);
+      o.wp_pos[q * 3 + 0] = v[0];
+      o.wp_pos[q * 3 + 1] = v[1];
+      o.wp_heading[q] = (float)d_wrap_value_pi((double)o.wp_heading[q] - eh);
+    }
+  }
+}

@@ -45,7 +45,7 @@ struct DCfg {
   double ogm_res;
   int32_t dagm_enable, dagm_w, dagm_h;
   double dagm_res;
-  int32_t events_enable, max_steps, ttc_enable, accel_enable, via_cap;
+  int32_t events_enable, max_steps, ttc_enable, accel_enable, via_cap, ego_frame;
   uint32_t done_mask;
   double nm_time, nm_dist, via_range, via_speed_acc;
 };

@@ -23,7 +23,7 @@ EXPORTS = [
     "sb_set_social", "sb_step", "sb_observe", "sb_step_host", "sb_copy_obs_to_host", "sb_get_obs",
     "sb_get_state", "sb_launch_count", "sb_last_error", "sb_set_timing", "sb_collect_timing",
 ]
-KERNEL_KINDS = ["k_set_social", "k_control", "k_observe", "k_lidar", "k_raster", "k_events", "k_pack_bits", "k_ttc", "k_extras"]
+KERNEL_KINDS = ["k_set_social", "k_control", "k_observe", "k_lidar", "k_raster", "k_events", "k_pack_bits", "k_ttc", "k_extras", "k_ego_frame"]
 
 
 class SmartsB200Error(RuntimeError):

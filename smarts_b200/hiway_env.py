@@ -108,7 +108,7 @@ class BatchedHiWayEnv:
                  fixed_timestep_sec: float = 0.1, seed: int = 42, headless: bool = True, device: int = 0,
                  auto_reset: bool = True, start_jitter: float = 0.0, route_cap: int = 16, traj_len: int = 10,
                  lidar_wall_height: float = 0.0, wp_out_len: Optional[int] = None, sim_name: Optional[str] = None,
-                 **_ignored_reference_kwargs):
+                 ego_centric: bool = False, **_ignored_reference_kwargs):
         from .engine import Engine  # raises without the CUDA library / a GPU: no CPU fallback
         if not agent_specs:
             raise ValueError("agent_specs is empty")
@@ -135,6 +135,10 @@ class BatchedHiWayEnv:
                                   route_cap=route_cap, traj_len=traj_len, lidar_wall_height=lidar_wall_height,
                                   wp_out_len=wp_out_len,
                                   via_cap=max([len(scenario.missions[a].via) for a in self.agent_ids] + [0]))
+        # ego_centric: the tensor path (std_obs / step_tensor) hands out ego-frame buffers (k_ego_frame); the dict
+        # path keeps world-frame Observations -- use ego_centric.get_egocentric_adapters in the AgentSpec there
+        self.ego_centric = bool(ego_centric)
+        self.cfg.ego_frame = int(self.ego_centric)
         rays = lidar_params.base_rays(self.interface.lidar.sensor_params) if self.interface.lidar else None
         self._base_rays = rays
         self._engine: Optional[Engine] = Engine(self.cfg, self.road_map, rays)
@@ -334,7 +338,10 @@ class BatchedHiWayEnv:
             rays = t.as_tensor(self._base_rays, device=self.engine.device)
             n = rays.shape[0]
             org = origin.unsqueeze(2).expand(self.E, A, n, 3)
-            out["lidar"] = {"hit": o["lidar_hits"], "point_cloud": pc, "ray_origin": org, "ray_vector": org + rays}
+            end = org + rays
+            if self.ego_centric:  # transform(ray_start), transform(ray_end), ego_centric_adapters.py:118-122
+                org, end = self._to_ego_frame(org, ego), self._to_ego_frame(end, ego)
+            out["lidar"] = {"hit": o["lidar_hits"], "point_cloud": pc, "ray_origin": org, "ray_vector": end}
         if itf.neighborhood_vehicles:
             out["neighbors"] = {"box": o["nbr_box"], "heading": o["nbr_heading"], "lane_index": o["nbr_lane_index"],
                                 "pos": o["nbr_pos"], "speed": o["nbr_speed"]}
@@ -344,7 +351,22 @@ class BatchedHiWayEnv:
         if itf.waypoints:
             out["waypoints"] = {"heading": o["wp_heading"], "lane_index": o["wp_lane_index"], "lane_width": o["wp_lane_width"],
                                 "pos": o["wp_pos"], "speed_limit": o["wp_speed_limit"]}
+        if self.ego_centric:  # ego_centric_adapters.py:140-147: the ego sits at the origin, facing +x
+            g = out["ego"]
+            for k in ("linear_velocity", "linear_acceleration", "linear_jerk"):  # ego_frame_dynamics
+                v = g[k]
+                g[k] = t.stack([t.linalg.vector_norm(v[..., :2], dim=-1), t.zeros_like(v[..., 0]), v[..., 2]], -1)
+            g["pos"] = t.zeros_like(g["pos"])
+            g["heading"] = t.zeros_like(g["heading"])
         return out
+
+    def _to_ego_frame(self, pts, ego):
+        """position_to_ego_frame (utils/math.py:473-487) for [E, A, n, 3] points, on the device."""
+        t = self._torch
+        h = -ego["heading"]
+        c, s_ = t.cos(h)[..., None], t.sin(h)[..., None]
+        rel = pts - t.stack([ego["pos_x"], ego["pos_y"], ego["pos_z"]], -1)[:, :, None, :]
+        return t.stack([c * rel[..., 0] - s_ * rel[..., 1], s_ * rel[..., 0] + c * rel[..., 1], rel[..., 2]], -1)
 
     # -- host-side Observation objects ---------------------------------------------------------
     def _fetch(self):
