@@ -350,13 +350,19 @@ k_observe(DCfg c, DMap m, DState s, DObs o, double* __restrict__ trip_wp) {
     const int n = wp->n;
     double* tw = trip_wp + (size_t)ai * 4;
     if (n == 0 && lane == 0) tw[3] = -1.0;
-    if (lane < n && wp_rank(m, wp, lane) == 0)
-      wp_equally_spaced<SB_MAX_LOOKAHEAD + 1>(m, wp->lp[lane], wp->len[lane], x, y, 1, [&](int, const DWaypoint& w) {
-        tw[0] = w.x;
-        tw[1] = w.y;
-        tw[2] = w.heading;
-        tw[3] = (double)w.lane;
-      });
+    const unsigned first = __ballot_sync(SB_FULL_MASK, lane < n && wp_rank(m, wp, lane) == 0);
+    if (first) {
+      const int p = __ffs(first) - 1;
+      wp_equally_spaced_warp(
+          m, wp->lp[p], wp->len[p], x, y, 1,
+          [&](int, const DWaypoint& w) {
+            tw[0] = w.x;
+            tw[1] = w.y;
+            tw[2] = w.heading;
+            tw[3] = (double)w.lane;
+          },
+          wp, lane);
+    }
   }
 
   if (c.wp_enable) {  // sensors.py:972-988
@@ -371,12 +377,16 @@ k_observe(DCfg c, DMap m, DState s, DObs o, double* __restrict__ trip_wp) {
       if (wp->overflow) s.status[ai] |= SB_STATUS_PATH_OVERFLOW;
       if (c.events_enable && n == 0) trip_wp[(size_t)ai * 4 + 3] = -1.0;
     }
-    int rank = lane < n ? wp_rank(m, wp, lane) : 0x7fffffff;
-    if (rank < P) {
-      size_t row = ((size_t)ai * P + rank) * L;
+    // each path is interpolated by the whole warp (wp_equally_spaced_warp); lane k ranks path k
+    const int my_rank = lane < n ? wp_rank(m, wp, lane) : 0x7fffffff;
+    for (int p = 0; p < n; ++p) {
+      const int rank = __shfl_sync(SB_FULL_MASK, my_rank, p);
+      if (rank >= P) continue;
+      const size_t row = ((size_t)ai * P + rank) * L;
       const bool stash = c.events_enable && rank == 0;  // waypoint_paths[0][0] feeds the trip meter (sensors.py:340-341)
-      int got = wp_equally_spaced<SB_MAX_LOOKAHEAD + 1>(
-          m, wp->lp[lane], wp->len[lane], x, y, L, [&](int i, const DWaypoint& w) {
+      const int got = wp_equally_spaced_warp(
+          m, wp->lp[p], wp->len[p], x, y, L,
+          [&](int i, const DWaypoint& w) {
             if (stash && i == 0) {
               double* tw = trip_wp + (size_t)ai * 4;
               tw[0] = w.x;
@@ -393,10 +403,11 @@ k_observe(DCfg c, DMap m, DState s, DObs o, double* __restrict__ trip_wp) {
             o.wp_speed_limit[q] = (float)w.speed_limit;
             o.wp_lane[q] = w.lane;
             o.wp_lane_index[q] = (int8_t)w.lane_index;
-          });
-      int len = got < L ? got : L;
-      o.wp_len[(size_t)ai * P + rank] = len;
-      for (int i = len; i < L; ++i) {
+          },
+          wp, lane);
+      const int len = got < L ? got : L;
+      if (lane == 0) o.wp_len[(size_t)ai * P + rank] = len;
+      for (int i = len + lane; i < L; i += 32) {
         size_t q = row + i;
         o.wp_pos[q * 3 + 0] = o.wp_pos[q * 3 + 1] = o.wp_pos[q * 3 + 2] = 0.0;
         o.wp_heading[q] = o.wp_lane_width[q] = o.wp_speed_limit[q] = 0.f;

@@ -25,6 +25,9 @@ struct WarpPaths {
   // candidate set of wp_closest_with_pose (lane points within a small disc around the nearest one)
   double cand_d[SB_WP_CAND];
   int32_t cand_i[SB_WP_CAND];
+  // wp_equally_spaced_warp: arc length and heading-unwrap offset of the kept lane points, and their indices
+  double es_cum[SB_MAX_LOOKAHEAD + 1], es_acc[SB_MAX_LOOKAHEAD + 1];
+  int32_t es_kept[SB_MAX_LOOKAHEAD + 1];
 };
 
 struct DWaypoint {
@@ -534,6 +537,130 @@ __device__ int wp_equally_spaced(const DMap& m, const int32_t* path, int n, doub
     w.heading = d_wrap_heading(w.heading);
     while (jd + 1 < mm && s > cum[jd + 1]) ++jd;
     w.lane = rlane[jd];
+    w.lane_index = m.lane_idx_in_road[w.lane];
+    emit(i, w);
+  }
+  return n;
+}
+
+// The same function executed by a whole warp for ONE path (all arguments warp-uniform): the lane
+// points are filtered with a ballot, segment lengths and unwrap corrections are computed one per
+// lane, the two running sums (arc length, unwrap offset) are accumulated by lane 0 in the serial
+// order -- they are the only order-dependent roundings -- and each lane then interpolates and emits
+// its own output waypoints i = lane, lane + 32, ...  Every value is produced by the operations of
+// the serial version above in the same order, so the results are bit-identical:
+//   * j  (last kept point with cum[j] <= s) and jd (last with cum[jd] < s, else 0) do not depend on
+//     the previous waypoint because cum and s are both non-decreasing; they are found by bisection;
+//   * rh[i] = lp_heading + acc[i] is formed where it is used (same single addition).
+template <class Emit>
+__device__ int wp_equally_spaced_warp(const DMap& m, const int32_t* path, int n, double vx, double vy, int n_out,
+                                      Emit emit, WarpPaths* wp, int lane) {
+  double* cum = wp->es_cum;
+  double* acc = wp->es_acc;
+  int32_t* kept = wp->es_kept;
+  __syncwarp();  // scratch may still be read by the previous path's lanes
+  int mm = 0;
+  for (int base = 0; base < n; base += 32) {
+    const int i = base + lane;
+    bool keep = false;
+    int lp = 0;
+    if (i < n) {
+      lp = path[i];
+      keep = !(m.lp_inferred[lp] && 0 < i && i < n - 1);
+    }
+    const unsigned b = __ballot_sync(SB_FULL_MASK, keep);
+    if (keep) kept[mm + __popc(b & ((1u << lane) - 1u))] = lp;
+    mm += __popc(b);
+  }
+  __syncwarp();
+  const int lp0 = path[0];
+  const double lx = m.lp_x[lp0], ly = m.lp_y[lp0], rh0 = m.lp_heading[lp0];
+  double hvx, hvy;
+  d_radians_to_vec(rh0, &hvx, &hvy);
+  const double proj = (vx - lx) * hvx + (vy - ly) * hvy;
+  const double x0 = lx + proj * hvx, y0 = ly + proj * hvy;  // rx[0], ry[0]
+  // per kept point i >= 1: segment length to its predecessor and the inplace_unwrap correction
+  bool any_corr = false;
+  for (int i = lane; i < mm; i += 32) {
+    double d = 0.0, corr = 0.0;
+    if (i > 0) {
+      const int a = kept[i - 1], b = kept[i];
+      const double px = i == 1 ? x0 : m.lp_x[a], py = i == 1 ? y0 : m.lp_y[a];
+      const double dx = m.lp_x[b] - px, dy = m.lp_y[b] - py;
+      d = sqrt(dx * dx + dy * dy);
+      const double dd = m.lp_heading[b] - m.lp_heading[a];
+      double ddmod = sb_pymod(dd + SB_PI, SB_TWO_PI) - SB_PI;
+      if (ddmod == -SB_PI && dd > 0) ddmod = SB_PI;
+      corr = ddmod - dd;
+      if (fabs(dd) < SB_PI) corr = 0.0;
+    }
+    cum[i] = d;
+    acc[i] = corr;
+    any_corr |= corr != 0.0;
+  }
+  any_corr = __any_sync(SB_FULL_MASK, any_corr);
+  __syncwarp();
+  if (lane == 0) {
+    double c = 0.0;
+    for (int i = 1; i < mm; ++i) {
+      c = c + cum[i];
+      cum[i] = c;
+    }
+    if (any_corr) {
+      double a = 0.0;
+      for (int i = 1; i < mm; ++i) {
+        a += acc[i];
+        acc[i] = a;
+      }
+    }
+  }
+  __syncwarp();
+  if ((double)mm <= m.lanepoint_spacing) {  // sic (:1379)
+    if (lane == 0 && n_out > 0) {
+      const int l = m.lp_lane[lp0];
+      DWaypoint w{lx, ly, rh0, m.lane_width[l], m.lane_speed[l], l, m.lane_idx_in_road[l]};
+      emit(0, w);
+    }
+    return 1;
+  }
+  const double total = cum[mm - 1];
+  const double step = total / (double)(n - 1);
+  const int lim = n < n_out ? n : n_out;
+  // kept point k as the serial version holds it in rx / ry / rh
+  auto px = [&](int k) { return k == 0 ? x0 : m.lp_x[kept[k]]; };
+  auto py = [&](int k) { return k == 0 ? y0 : m.lp_y[kept[k]]; };
+  auto ph = [&](int k) { return k == 0 ? rh0 : m.lp_heading[kept[k]] + acc[k]; };
+  for (int i = lane; i < lim; i += 32) {
+    const double s = (i == n - 1) ? total : (double)i * step;
+    int lo = 0, hi = mm - 1;  // largest j with cum[j] <= s (cum[0] = 0 <= s)
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (cum[mid] <= s) lo = mid; else hi = mid - 1;
+    }
+    const int j = lo;
+    DWaypoint w;
+    if (j >= mm - 1 || cum[j] == s) {
+      const int l = m.lp_lane[kept[j]];
+      w.x = px(j);
+      w.y = py(j);
+      w.heading = ph(j);
+      w.lane_width = m.lane_width[l];
+      w.speed_limit = m.lane_speed[l];
+    } else {
+      const double den = cum[j + 1] - cum[j], ds = s - cum[j];
+      const int la = m.lp_lane[kept[j]], lb = m.lp_lane[kept[j + 1]];
+      const double xa = px(j), ya = py(j), ha = ph(j);
+      w.x = wp_slope(px(j + 1) - xa, den) * ds + xa;
+      w.y = wp_slope(py(j + 1) - ya, den) * ds + ya;
+      w.heading = wp_slope(ph(j + 1) - ha, den) * ds + ha;
+      const double wa = m.lane_width[la], wb = m.lane_width[lb], sa = m.lane_speed[la], sb_ = m.lane_speed[lb];
+      w.lane_width = wp_slope(wb - wa, den) * ds + wa;
+      w.speed_limit = wp_slope(sb_ - sa, den) * ds + sa;
+    }
+    w.heading = d_wrap_heading(w.heading);
+    int jd = j;  // largest jd with cum[jd] < s, else 0
+    while (jd > 0 && !(cum[jd] < s)) --jd;
+    w.lane = m.lp_lane[kept[jd]];
     w.lane_index = m.lane_idx_in_road[w.lane];
     emit(i, w);
   }
