@@ -84,9 +84,10 @@ __global__ void k_set_social(DCfg c, DState s, const double* __restrict__ in) {
 #define SB_CTRL_LAW_THREADS 32
 #define SB_CTRL_LOOKAHEAD 16
 
+// k_control_paths -> k_control_law: the waypoints of the path the controller follows
 struct CtrlPick {
-  int32_t lp[SB_CTRL_LOOKAHEAD + 1];
-  int32_t len;  // 0: no waypoints found
+  double wx[SB_CTRL_LOOKAHEAD + 1], wy[SB_CTRL_LOOKAHEAD + 1], wh[SB_CTRL_LOOKAHEAD + 1];
+  int32_t len;  // waypoints on the path; 0: no waypoints found
 };
 
 // controllers/__init__.py:125-152: Lane strings / LaneWithContinuousSpeed tuple -> (target speed, lane change)
@@ -141,12 +142,19 @@ k_control_paths(DCfg c, DMap m, DState s, const void* __restrict__ actions, Ctrl
   warp_argmin(dmin, cur);
   int sel = cur + lc;
   sel = sel < 0 ? 0 : (sel > n - 1 ? n - 1 : sel);
-  // the lane holding the selected path hands it to the others; all 32 write it out
+  // the selected path is interpolated by the whole warp, one waypoint per lane
   const unsigned who = __ballot_sync(SB_FULL_MASK, rank == sel);
   const int src = __ffs(who) - 1;
-  const int len = wp->len[src];
-  if (lane < len) picks[ai].lp[lane] = wp->lp[src][lane];
-  if (lane == 0) picks[ai].len = len;
+  CtrlPick* pk = &picks[ai];
+  const int L = wp_equally_spaced_warp(
+      m, wp->lp[src], wp->len[src], vx, vy, SB_CTRL_LOOKAHEAD + 1,
+      [&](int i, const DWaypoint& w) {
+        pk->wx[i] = w.x;
+        pk->wy[i] = w.y;
+        pk->wh[i] = w.heading;
+      },
+      wp, lane);
+  if (lane == 0) pk->len = L;
 }
 
 __global__ void __launch_bounds__(SB_CTRL_LAW_THREADS)
@@ -164,14 +172,7 @@ k_control_law(DCfg c, DMap m, DState s, const void* __restrict__ actions, const 
     double ts;
     int lc;
     d_lane_action(c, actions, ai, &ts, &lc);
-    double wx[SB_CTRL_LOOKAHEAD + 1], wy[SB_CTRL_LOOKAHEAD + 1], wh[SB_CTRL_LOOKAHEAD + 1];
-    const int L = wp_equally_spaced<SB_CTRL_LOOKAHEAD + 1>(m, pk.lp, pk.len, v.x, v.y, SB_CTRL_LOOKAHEAD + 1,
-                                                         [&](int i, const DWaypoint& w) {
-                                                           wx[i] = w.x;
-                                                           wy[i] = w.y;
-                                                           wh[i] = w.heading;
-                                                         });
-    d_lane_following_law(v, wx, wy, wh, L, ts, lc, c.dt, st, out3);
+    d_lane_following_law(v, pk.wx, pk.wy, pk.wh, pk.len, ts, lc, c.dt, st, out3);
   }
   d_chassis_step(s, ai, vi, c.dt, c.substeps);
 }
