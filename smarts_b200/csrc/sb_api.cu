@@ -429,6 +429,20 @@ int sb_upload_map(SbHandle h, const SbMap* mp) {
     }
     m.lp_chained = chained ? 1 : 0;
   }
+  {  // lane ranges tile the road range?  (lets one per-lane scan of a road serve as its road-level scan)
+    bool tiled = true;
+    for (int r = 0; r < mp->n_roads && tiled; ++r) {
+      int expect = mp->road_lp_start[r];
+      for (int l = mp->road_lane_start[r]; l < mp->road_lane_start[r] + mp->road_lane_count[r]; ++l) {
+        if (mp->lane_lp_count[l] <= 0) continue;
+        if (mp->lane_lp_start[l] != expect) tiled = false;
+        expect += mp->lane_lp_count[l];
+      }
+      if (mp->road_lp_count[r] > 0 && expect != mp->road_lp_start[r] + mp->road_lp_count[r]) tiled = false;
+      if (mp->road_lane_count[r] > SB_WP_CAND) tiled = false;
+    }
+    m.road_lp_tiled = tiled ? 1 : 0;
+  }
   // derived host tables: lane of every shape vertex; polygon AABBs (float, rounded outwards)
   std::vector<int32_t> shape_lane(mp->n_shape_pts);
   for (int l = 0; l < mp->n_lanes; ++l)

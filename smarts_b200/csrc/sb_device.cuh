@@ -17,6 +17,7 @@
 struct DMap {
   int32_t n_roads, n_lanes, n_lanepoints, n_shape_pts, n_polys, n_poly_verts, n_edges;
   int32_t lp_chained;  // every lane point but the last of its lane has the single successor index + 1
+  int32_t road_lp_tiled;  // a road's lane-point range is its lanes' ranges back to back, in lane order
   double lanepoint_spacing;
   const int32_t *road_lane_start, *road_lane_count, *road_lp_start, *road_lp_count, *road_first_out;
   const uint8_t* road_is_junction;
@@ -83,15 +84,17 @@ __device__ __forceinline__ double d_signed_dist_to_line(double px, double py, do
   return d * sg;
 }
 
-// lexicographic (value, index) minimum across the warp; every lane gets the result
+// lexicographic (value, index) minimum across the warp; every lane gets the result.  Values are distances
+// (>= 0, or the 1e300 "nothing" sentinel) and indices are >= 0, so both order like their bit patterns as
+// unsigned integers: three redux.sync minima (high word, low word among the high-word winners, index among
+// the value winners) replace fifteen shuffles with their compares.
 __device__ __forceinline__ void warp_argmin(double& d, int& i) {
-#pragma unroll
-  for (int off = 16; off > 0; off >>= 1) {
-    double od = __shfl_xor_sync(SB_FULL_MASK, d, off);
-    int oi = __shfl_xor_sync(SB_FULL_MASK, i, off);
-    if (od < d || (od == d && oi < i)) {
-      d = od;
-      i = oi;
-    }
-  }
+  const unsigned long long b = d == 0.0 ? 0ull : (unsigned long long)__double_as_longlong(d);
+  const unsigned hi = (unsigned)(b >> 32), lo = (unsigned)b;
+  const unsigned mhi = __reduce_min_sync(SB_FULL_MASK, hi);
+  const unsigned mlo = __reduce_min_sync(SB_FULL_MASK, hi == mhi ? lo : 0xffffffffu);
+  const bool win = hi == mhi && lo == mlo;
+  const unsigned mi = __reduce_min_sync(SB_FULL_MASK, win ? (unsigned)i : 0xffffffffu);
+  d = __longlong_as_double((long long)(((unsigned long long)mhi << 32) | mlo));
+  i = (int)mi;
 }

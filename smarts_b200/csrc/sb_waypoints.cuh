@@ -310,14 +310,39 @@ __device__ void wp_enumerate_chained(const DMap& m, int start, int lookahead, co
   }
 }
 
-// Lane._waypoint_paths_at for every lane of `road` (sumo_road_network.py:429-446, :838-839, :880-881)
+// Closest lane point of every lane of `road` -> per_lane[0 .. lanes) (-1 for a lane without points); returns
+// the closest of the whole road.  On a tiled map (DMap::road_lp_tiled) that is exactly the scan of the road's
+// own range: the lane ranges follow each other in index order, and ties keep the earlier (lower-index) lane.
+__device__ int wp_closest_per_lane(const DMap& m, int road, double x, double y, int lane, int32_t* per_lane) {
+  const int l0 = m.road_lane_start[road], l1 = l0 + m.road_lane_count[road];
+  int best = -1;
+  double bd = 0.0;
+  for (int l = l0; l < l1; ++l) {
+    const int cnt = m.lane_lp_count[l];
+    int lp = -1;
+    if (cnt > 0) {
+      lp = wp_closest_in_range(m, m.lane_lp_start[l], cnt, x, y, lane);
+      const double d = wp_sqdist(m, lp, x, y);
+      if (best < 0 || d < bd) {
+        best = lp;
+        bd = d;
+      }
+    }
+    if (lane == 0) per_lane[l - l0] = lp;
+  }
+  __syncwarp();
+  return best;
+}
+
+// Lane._waypoint_paths_at for every lane of `road` (sumo_road_network.py:429-446, :838-839, :880-881).
+// `per_lane`: closest lane point of each lane when the caller has already scanned this road, else null.
 __device__ void wp_paths_on_road(const DMap& m, int road, double x, double y, int lookahead, const int32_t* filt,
-                                 int nf, WarpPaths* wp, int lane) {
+                                 int nf, WarpPaths* wp, int lane, const int32_t* per_lane = nullptr) {
   int l0 = m.road_lane_start[road], l1 = l0 + m.road_lane_count[road];
   for (int l = l0; l < l1; ++l) {
     int cnt = m.lane_lp_count[l];
     if (cnt <= 0) continue;
-    int lp = wp_closest_in_range(m, m.lane_lp_start[l], cnt, x, y, lane);
+    int lp = per_lane ? per_lane[l - l0] : wp_closest_in_range(m, m.lane_lp_start[l], cnt, x, y, lane);
     if (m.lp_chained) {
       wp_enumerate_chained(m, lp, lookahead, filt, nf, wp, lane);
     } else if (lane == 0) {
@@ -363,6 +388,13 @@ __device__ void wp_waypoint_paths(const DMap& m, double x, double y, double h, i
     // with the smallest one is scanned first for an upper bound, then the roads are visited in order.
     double ub = 1e300;
     const bool prune = nr > 1 && nr <= SB_WP_CAND;
+    // the road scanned for the bound is scanned lane by lane and remembered: the loop below reuses its result
+    // and, when it wins, so does wp_paths_on_road -- one pass over its lane points instead of three
+    int cached_road = -1, cached_lp = -1;
+    if (!prune && nr == 1 && m.road_lp_tiled && m.road_lp_count[roads[0]] > 0) {
+      cached_road = roads[0];
+      cached_lp = wp_closest_per_lane(m, cached_road, x, y, lane, wp->cand_i);
+    }
     if (prune) {
       double lb_best = 1e300;
       int r_best = 0x7fffffff;
@@ -384,7 +416,14 @@ __device__ void wp_waypoint_paths(const DMap& m, double x, double y, double h, i
       __syncwarp();
       if (r_best != 0x7fffffff && lb_best < 1e299) {
         const int road = roads[r_best];
-        const int lp = wp_closest_in_range(m, m.road_lp_start[road], m.road_lp_count[road], x, y, lane);
+        int lp;
+        if (m.road_lp_tiled) {
+          lp = wp_closest_per_lane(m, road, x, y, lane, wp->cand_i);
+          cached_road = road;
+          cached_lp = lp;
+        } else {
+          lp = wp_closest_in_range(m, m.road_lp_start[road], m.road_lp_count[road], x, y, lane);
+        }
         ub = wp_sqdist(m, lp, x, y) * (1.0 + 1e-9);  // guard: bounds and distances round independently
       }
     }
@@ -395,7 +434,7 @@ __device__ void wp_waypoint_paths(const DMap& m, double x, double y, double h, i
       int cnt = m.road_lp_count[road];
       if (cnt <= 0) continue;
       if (prune && wp->cand_d[r] > ub) continue;
-      int lp = wp_closest_in_range(m, m.road_lp_start[road], cnt, x, y, lane);
+      int lp = road == cached_road ? cached_lp : wp_closest_in_range(m, m.road_lp_start[road], cnt, x, y, lane);
       double d = sqrt(wp_sqdist(m, lp, x, y));
       if (best < 0 || d < bd) {
         best = lp;
@@ -403,7 +442,8 @@ __device__ void wp_waypoint_paths(const DMap& m, double x, double y, double h, i
       }
     }
     if (best >= 0) {
-      wp_paths_on_road(m, m.lane_road[m.lp_lane[best]], x, y, lookahead, roads, nr, wp, lane);
+      const int on = m.lane_road[m.lp_lane[best]];
+      wp_paths_on_road(m, on, x, y, lookahead, roads, nr, wp, lane, on == cached_road ? wp->cand_i : nullptr);
       return;
     }
   }
