@@ -475,7 +475,7 @@ __device__ __forceinline__ double wp_slope(double rise, double run) {
   return flat ? rise : q;
 }
 
-// First waypoint of wp_equally_spaced() for `path` without building the rest (find_current_lane,
+// First waypoint of wp_equally_spaced_warp() for `path` without building the rest (find_current_lane,
 // lane_following_controller.py:367-374, only needs this one): the vehicle's projection on the
 // first lane point's heading line, or the lane point itself for a path of <= spacing points.
 __device__ void wp_first_point(const DMap& m, const int32_t* path, int n, double vx, double vy, double* x, double* y) {
@@ -496,101 +496,19 @@ __device__ void wp_first_point(const DMap& m, const int32_t* path, int n, double
   *y = ly + proj * hvy;
 }
 
-// sumo_road_network.py:1312-1437, one path, executed by a single lane.  Calls emit(i, waypoint)
-// for the first min(n_out, n) waypoints.  MAXN bounds the path length (lookahead + 1).
-template <int MAXN, class Emit>
-__device__ int wp_equally_spaced(const DMap& m, const int32_t* path, int n, double vx, double vy, int n_out,
-                                 Emit emit) {
-  double rx[MAXN], ry[MAXN], rh[MAXN], cum[MAXN];
-  int32_t rlane[MAXN];
-  int mm = 0;
-  for (int i = 0; i < n; ++i) {
-    int lp = path[i];
-    if (m.lp_inferred[lp] && 0 < i && i < n - 1) continue;
-    rx[mm] = m.lp_x[lp];
-    ry[mm] = m.lp_y[lp];
-    rh[mm] = m.lp_heading[lp];
-    rlane[mm] = m.lp_lane[lp];
-    ++mm;
-  }
-  {  // inplace_unwrap, utils/math.py:537-550
-    double acc = 0.0, prev = rh[0];
-    for (int i = 1; i < mm; ++i) {
-      double cur = rh[i];
-      double dd = cur - prev;
-      double ddmod = sb_pymod(dd + SB_PI, SB_TWO_PI) - SB_PI;
-      if (ddmod == -SB_PI && dd > 0) ddmod = SB_PI;
-      double corr = ddmod - dd;
-      if (fabs(dd) < SB_PI) corr = 0.0;
-      acc += corr;
-      prev = cur;
-      rh[i] = cur + acc;
-    }
-  }
-  double hvx, hvy;
-  d_radians_to_vec(rh[0], &hvx, &hvy);
-  int lp0 = path[0];
-  double lx = m.lp_x[lp0], ly = m.lp_y[lp0];
-  double proj = (vx - lx) * hvx + (vy - ly) * hvy;
-  rx[0] = lx + proj * hvx;
-  ry[0] = ly + proj * hvy;
-  cum[0] = 0.0;
-  for (int i = 1; i < mm; ++i) {
-    double dx = rx[i] - rx[i - 1], dy = ry[i] - ry[i - 1];
-    cum[i] = cum[i - 1] + sqrt(dx * dx + dy * dy);
-  }
-  if ((double)mm <= m.lanepoint_spacing) {  // sic (:1379)
-    int lane = m.lp_lane[lp0];
-    DWaypoint w{lx, ly, m.lp_heading[lp0], m.lane_width[lane], m.lane_speed[lane], lane, m.lane_idx_in_road[lane]};
-    if (n_out > 0) emit(0, w);
-    return 1;
-  }
-  double total = cum[mm - 1];
-  double step = total / (double)(n - 1);
-  int jd = 0, j = 0;
-  int lim = n < n_out ? n : n_out;
-  for (int i = 0; i < lim; ++i) {
-    double s = (i == n - 1) ? total : (double)i * step;
-    if (s > cum[mm - 1]) {
-      j = mm - 1;
-    } else {
-      while (j + 1 < mm && cum[j + 1] <= s) ++j;  // s is non-decreasing in i
-    }
-    DWaypoint w;
-    if (j >= mm - 1 || cum[j] == s) {
-      int l = rlane[j];
-      w.x = rx[j];
-      w.y = ry[j];
-      w.heading = rh[j];
-      w.lane_width = m.lane_width[l];
-      w.speed_limit = m.lane_speed[l];
-    } else {
-      double den = cum[j + 1] - cum[j], ds = s - cum[j];
-      int la = rlane[j], lb = rlane[j + 1];
-      w.x = wp_slope(rx[j + 1] - rx[j], den) * ds + rx[j];
-      w.y = wp_slope(ry[j + 1] - ry[j], den) * ds + ry[j];
-      w.heading = wp_slope(rh[j + 1] - rh[j], den) * ds + rh[j];
-      double wa = m.lane_width[la], wb = m.lane_width[lb], sa = m.lane_speed[la], sb_ = m.lane_speed[lb];
-      w.lane_width = wp_slope(wb - wa, den) * ds + wa;
-      w.speed_limit = wp_slope(sb_ - sa, den) * ds + sa;
-    }
-    w.heading = d_wrap_heading(w.heading);
-    while (jd + 1 < mm && s > cum[jd + 1]) ++jd;
-    w.lane = rlane[jd];
-    w.lane_index = m.lane_idx_in_road[w.lane];
-    emit(i, w);
-  }
-  return n;
-}
-
-// The same function executed by a whole warp for ONE path (all arguments warp-uniform): the lane
-// points are filtered with a ballot, segment lengths and unwrap corrections are computed one per
-// lane, the two running sums (arc length, unwrap offset) are accumulated by lane 0 in the serial
-// order -- they are the only order-dependent roundings -- and each lane then interpolates and emits
-// its own output waypoints i = lane, lane + 32, ...  Every value is produced by the operations of
-// the serial version above in the same order, so the results are bit-identical:
+// _equally_spaced_path (sumo_road_network.py:1312-1437) for ONE path, executed by the whole warp (all
+// arguments warp-uniform).  Calls emit(i, waypoint) for the first min(n_out, n) waypoints, each from the
+// lane that computed it, and returns the path's waypoint count.
+//   reference (serial)                                  here
+//   drop inferred interior lane points                  ballot compaction of the kept indices
+//   inplace_unwrap of the headings (utils/math.py:537)  per-lane correction; lane 0 sums the offsets in order
+//   cumulative arc length                               per-lane segment length; lane 0 sums in order
+//   np.interp at i * step for x, y, heading, width,     lane i interpolates waypoint i (i + 32, ...): the
+//   speed; lane of the last point with cum < s          interval is found by bisection on the arc lengths
+// The two running sums are the only order-dependent roundings, so they stay serial; everything else is the
+// reference's operation on the same operands, hence bit-identical to the oracle's serial restatement:
 //   * j  (last kept point with cum[j] <= s) and jd (last with cum[jd] < s, else 0) do not depend on
-//     the previous waypoint because cum and s are both non-decreasing; they are found by bisection;
+//     the previous waypoint because cum and s are both non-decreasing;
 //   * rh[i] = lp_heading + acc[i] is formed where it is used (same single addition).
 template <class Emit>
 __device__ int wp_equally_spaced_warp(const DMap& m, const int32_t* path, int n, double vx, double vy, int n_out,
