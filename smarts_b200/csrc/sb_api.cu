@@ -553,6 +553,34 @@ int sb_upload_map(SbHandle h, const SbMap* mp) {
       }
     }
   }
+  m.lpg_nx = m.lpg_ny = 0;
+  m.lpg_x0 = m.lpg_y0 = m.lpg_cell = m.lpg_inv_cell = 0.0;
+  m.lpg_cell_start = m.lpg_items = nullptr;
+  if (mp->n_lanepoints > 64) {  // uniform grid over the lane points (unrouted closest-lane-point queries)
+    const double cell = 8.0, inv = 1.0 / cell;
+    double x0 = 1e300, y0 = 1e300, x1 = -1e300, y1 = -1e300;
+    for (int i = 0; i < mp->n_lanepoints; ++i) {
+      x0 = fmin(x0, mp->lp_x[i]); x1 = fmax(x1, mp->lp_x[i]);
+      y0 = fmin(y0, mp->lp_y[i]); y1 = fmax(y1, mp->lp_y[i]);
+    }
+    const int nx = (int)floor((x1 - x0) * inv) + 1, ny = (int)floor((y1 - y0) * inv) + 1;
+    if (std::isfinite(x0) && std::isfinite(y0) && (long long)nx * ny <= (1 << 22)) {
+      auto cell_of = [&](int i) {
+        const int cx = std::min(nx - 1, std::max(0, (int)floor((mp->lp_x[i] - x0) * inv)));
+        const int cy = std::min(ny - 1, std::max(0, (int)floor((mp->lp_y[i] - y0) * inv)));
+        return (size_t)cy * nx + cx;
+      };
+      std::vector<int32_t> start((size_t)nx * ny + 1, 0), items(mp->n_lanepoints);
+      for (int i = 0; i < mp->n_lanepoints; ++i) start[cell_of(i) + 1]++;
+      for (size_t c2 = 0; c2 < (size_t)nx * ny; ++c2) start[c2 + 1] += start[c2];
+      std::vector<int32_t> fill(start.begin(), start.end() - 1);
+      for (int i = 0; i < mp->n_lanepoints; ++i) items[fill[cell_of(i)]++] = i;
+      if (!dev_upload(h, &m.lpg_cell_start, start.data(), start.size()) ||
+          !dev_upload(h, &m.lpg_items, items.data(), items.size()))
+        return SB_ECUDA;
+      m.lpg_nx = nx; m.lpg_ny = ny; m.lpg_x0 = x0; m.lpg_y0 = y0; m.lpg_cell = cell; m.lpg_inv_cell = inv;
+    }
+  }
   h->raster_dims.n_src = h->raster_dims.n_veh + (h->cfg.dagm_enable ? mp->n_polys : 0);
   h->have_map = true;
   return SB_OK;

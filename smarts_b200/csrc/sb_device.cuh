@@ -18,6 +18,11 @@ struct DMap {
   int32_t n_roads, n_lanes, n_lanepoints, n_shape_pts, n_polys, n_poly_verts, n_edges;
   int32_t lp_chained;  // every lane point but the last of its lane has the single successor index + 1
   int32_t road_lp_tiled;  // a road's lane-point range is its lanes' ranges back to back, in lane order
+  // uniform grid over the lane points (wp_closest_with_pose): row-major cells of lpg_cell metres, items = lane
+  // point indices sorted by cell (ascending inside a cell); lpg_nx == 0: no grid
+  double lpg_x0, lpg_y0, lpg_cell, lpg_inv_cell;
+  int32_t lpg_nx, lpg_ny;
+  const int32_t *lpg_cell_start, *lpg_items;
   double lanepoint_spacing;
   const int32_t *road_lane_start, *road_lane_count, *road_lp_start, *road_lp_count, *road_first_out;
   const uint8_t* road_is_junction;

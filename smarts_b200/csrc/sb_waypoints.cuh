@@ -10,6 +10,7 @@
 #include "sb_device.cuh"
 
 #define SB_WP_CAND 64
+#define SB_LPG_RINGS 3  // lane-point grid: squares of up to 3 cells around the query before falling back to the table
 
 struct WarpPaths {
   int32_t lp[SB_MAX_PATHS][SB_MAX_LOOKAHEAD + 1];  // lane-point indices of each path
@@ -69,7 +70,73 @@ __device__ int wp_closest_with_pose(const DMap& m, double x, double y, double h,
   double d2[10];
   int n = 0;
   int n_cand = -1;  // < 0: scan the table
-  {
+  bool gathered = false;
+  if (m.lpg_nx > 0) {
+    // Lane-point grid: the nearest point is final once it is closer than the scanned square's margin (every
+    // unscanned point is at least r cells away); the gather then visits the cells the reach disc can touch.
+    // Same candidate set as the two table scans below -- which remain the path for far-away queries.
+    const double gx = (x - m.lpg_x0) * m.lpg_inv_cell, gy = (y - m.lpg_y0) * m.lpg_inv_cell;
+    if (fabs(gx) < 1e6 && fabs(gy) < 1e6) {
+      const int qx = (int)floor(gx), qy = (int)floor(gy);
+      bool have = false;
+      double bd = 0.0;
+      for (int r = 1; r <= SB_LPG_RINGS && !have; ++r) {
+        double d = 1e300;
+        int bi = 0x7fffffff;
+        const int cx0 = max(qx - r, 0), cx1 = min(qx + r, m.lpg_nx - 1);
+        if (cx0 <= cx1)
+          for (int cy = max(qy - r, 0); cy <= min(qy + r, m.lpg_ny - 1); ++cy) {
+            const int a = m.lpg_cell_start[cy * m.lpg_nx + cx0], b = m.lpg_cell_start[cy * m.lpg_nx + cx1 + 1];
+            for (int t = a + lane; t < b; t += 32) {
+              const int i = m.lpg_items[t];
+              const double dd = wp_sqdist(m, i, x, y);
+              if (dd < d || (dd == d && i < bi)) {
+                d = dd;
+                bi = i;
+              }
+            }
+          }
+        warp_argmin(d, bi);
+        const double lim = (double)r * m.lpg_cell;
+        if (bi != 0x7fffffff && d < lim * lim * (1.0 - 1e-9)) {
+          have = true;
+          bd = d;
+        }
+      }
+      const double reach = sqrt(bd) + 4.0, T = reach * reach;
+      const int R2 = (int)floor((reach * (1.0 + 1e-9) + 1e-9) * m.lpg_inv_cell) + 1;
+      if (have && R2 <= 2 * SB_LPG_RINGS) {
+        int cnt = 0;
+        const int cx0 = max(qx - R2, 0), cx1 = min(qx + R2, m.lpg_nx - 1);
+        if (cx0 <= cx1)
+          for (int cy = max(qy - R2, 0); cy <= min(qy + R2, m.lpg_ny - 1); ++cy) {
+            const int a = m.lpg_cell_start[cy * m.lpg_nx + cx0], b = m.lpg_cell_start[cy * m.lpg_nx + cx1 + 1];
+            for (int t0 = a; t0 < b; t0 += 32) {
+              const int t = t0 + lane;
+              double d = 0.0;
+              int i = 0;
+              bool in = false;
+              if (t < b) {
+                i = m.lpg_items[t];
+                d = wp_sqdist(m, i, x, y);
+                in = d <= T;
+              }
+              const unsigned bal = __ballot_sync(SB_FULL_MASK, in);
+              const int pos = cnt + __popc(bal & ((1u << lane) - 1u));
+              if (in && pos < SB_WP_CAND) {
+                wp->cand_d[pos] = d;
+                wp->cand_i[pos] = i;
+              }
+              cnt += __popc(bal);
+            }
+          }
+        __syncwarp();
+        if (cnt >= k && cnt <= SB_WP_CAND) n_cand = cnt;
+        gathered = true;
+      }
+    }
+  }
+  if (!gathered) {
     double bd = 1e300;
     int bi = 0x7fffffff;
     for (int i = lane; i < P; i += 32) {
