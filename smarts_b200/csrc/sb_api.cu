@@ -556,6 +556,7 @@ int sb_upload_map(SbHandle h, const SbMap* mp) {
   m.lpg_nx = m.lpg_ny = 0;
   m.lpg_x0 = m.lpg_y0 = m.lpg_cell = m.lpg_inv_cell = 0.0;
   m.lpg_cell_start = m.lpg_items = nullptr;
+  m.lpg_px = m.lpg_py = nullptr;
   if (mp->n_lanepoints > 64) {  // uniform grid over the lane points (unrouted closest-lane-point queries)
     const double cell = 8.0, inv = 1.0 / cell;
     double x0 = 1e300, y0 = 1e300, x1 = -1e300, y1 = -1e300;
@@ -575,8 +576,14 @@ int sb_upload_map(SbHandle h, const SbMap* mp) {
       for (size_t c2 = 0; c2 < (size_t)nx * ny; ++c2) start[c2 + 1] += start[c2];
       std::vector<int32_t> fill(start.begin(), start.end() - 1);
       for (int i = 0; i < mp->n_lanepoints; ++i) items[fill[cell_of(i)]++] = i;
+      std::vector<double> px(items.size()), py(items.size());
+      for (size_t t = 0; t < items.size(); ++t) {
+        px[t] = mp->lp_x[items[t]];
+        py[t] = mp->lp_y[items[t]];
+      }
       if (!dev_upload(h, &m.lpg_cell_start, start.data(), start.size()) ||
-          !dev_upload(h, &m.lpg_items, items.data(), items.size()))
+          !dev_upload(h, &m.lpg_items, items.data(), items.size()) || !dev_upload(h, &m.lpg_px, px.data(), px.size()) ||
+          !dev_upload(h, &m.lpg_py, py.data(), py.size()))
         return SB_ECUDA;
       m.lpg_nx = nx; m.lpg_ny = ny; m.lpg_x0 = x0; m.lpg_y0 = y0; m.lpg_cell = cell; m.lpg_inv_cell = inv;
     }

@@ -23,6 +23,7 @@ struct DMap {
   double lpg_x0, lpg_y0, lpg_cell, lpg_inv_cell;
   int32_t lpg_nx, lpg_ny;
   const int32_t *lpg_cell_start, *lpg_items;
+  const double *lpg_px, *lpg_py;  // lp_x / lp_y of the items, in item order (no dependent gather)
   double lanepoint_spacing;
   const int32_t *road_lane_start, *road_lane_count, *road_lp_start, *road_lp_count, *road_first_out;
   const uint8_t* road_is_junction;

@@ -66,8 +66,8 @@ __device__ int wp_closest_with_pose(const DMap& m, double x, double y, double h,
                                     WarpPaths* wp) {
   const int P = m.n_lanepoints;
   const int k = P < 10 ? P : 10;
-  int idx[10];
-  double d2[10];
+  int my_idx = -1;
+  double my_d2 = 0.0;
   int n = 0;
   int n_cand = -1;  // < 0: scan the table
   bool gathered = false;
@@ -89,7 +89,8 @@ __device__ int wp_closest_with_pose(const DMap& m, double x, double y, double h,
             const int a = m.lpg_cell_start[cy * m.lpg_nx + cx0], b = m.lpg_cell_start[cy * m.lpg_nx + cx1 + 1];
             for (int t = a + lane; t < b; t += 32) {
               const int i = m.lpg_items[t];
-              const double dd = wp_sqdist(m, i, x, y);
+              const double ddx = m.lpg_px[t] - x, ddy = m.lpg_py[t] - y;  // lp_x / lp_y in item order
+              const double dd = ddx * ddx + ddy * ddy;
               if (dd < d || (dd == d && i < bi)) {
                 d = dd;
                 bi = i;
@@ -118,7 +119,8 @@ __device__ int wp_closest_with_pose(const DMap& m, double x, double y, double h,
               bool in = false;
               if (t < b) {
                 i = m.lpg_items[t];
-                d = wp_sqdist(m, i, x, y);
+                const double ddx = m.lpg_px[t] - x, ddy = m.lpg_py[t] - y;
+                d = ddx * ddx + ddy * ddy;
                 in = d <= T;
               }
               const unsigned bal = __ballot_sync(SB_FULL_MASK, in);
@@ -198,27 +200,28 @@ __device__ int wp_closest_with_pose(const DMap& m, double x, double y, double h,
     }
     warp_argmin(bd, bi);
     if (bi == 0x7fffffff) break;
-    idx[n] = bi;
-    d2[n] = bd;
+    if (lane == n) {  // lane r keeps the r-th nearest point
+      my_idx = bi;
+      my_d2 = bd;
+    }
     ++n;
     last_d = bd;
     last_i = bi;
   }
   __syncwarp();
-  // every lane holds the same list; finish redundantly (tiny)
-  int best = -1;
-  double bk = 0.0;
-  double r2 = within_radius * within_radius;
-  for (int i = 0; i < n; ++i) {
-    if (within_radius >= 0.0 && !(d2[i] <= r2 || i == 0)) continue;
-    double rel = d_wrap_heading(h - m.lp_heading[idx[i]]);
-    double key = d2[i] + fabs(rel);
-    if (best < 0 || key < bk) {
-      best = idx[i];
-      bk = key;
-    }
+  // min over the kept points of (squared distance + |heading difference|), the first one on ties
+  // (the sort key of lanepoints.py:582-589): lane r scores the r-th nearest, one (key, rank) arg-min picks
+  const double r2 = within_radius * within_radius;
+  double key = 1e300;
+  int rank = 0x7fffffff;
+  if (lane < n && !(within_radius >= 0.0 && !(my_d2 <= r2 || lane == 0))) {
+    const double rel = d_wrap_heading(h - m.lp_heading[my_idx]);
+    key = my_d2 + fabs(rel);
+    rank = lane;
   }
-  return best;
+  warp_argmin(key, rank);
+  if (rank == 0x7fffffff) return -1;
+  return __shfl_sync(SB_FULL_MASK, my_idx, rank);
 }
 
 __device__ __forceinline__ bool wp_in_route(const int32_t* route, int n, int road) {
