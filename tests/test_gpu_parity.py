@@ -211,6 +211,36 @@ def test_off_map_and_no_route_agents():
         assert_same(eng.obs_numpy(), ora.obs())
 
 
+@pytest.mark.parametrize("name,wp", [("figure_eight", True), ("loop", True), ("minicity", True), ("minicity", False)])
+def test_unrouted_queries_at_random_positions(name, wp):
+    """Closest-lane-point queries without a route at positions anywhere on and around the map: on a lane, a few
+    metres off, and beyond the lane-point grid's three rings (the table scan takes over there); with and without
+    the waypoint sensor (without it the events pass makes the lookahead-1 trip-meter query)."""
+    import torch
+    rm = load_map(name)
+    E, A = 64, 4
+    cfg = make_cfg(E=E, A=A, M=0, nbr=False, wp=wp, wp_lookahead=16, wp_paths=8, wp_len=17, route_cap=16, events=True)
+    rng = np.random.default_rng(21)
+    on = rng.integers(0, len(rm.lp_x), (E, A))
+    spread = np.where(rng.random((E, A)) < 0.6, rng.normal(0, 2.0, (E, A)), rng.uniform(-60, 60, (E, A)))
+    ang = rng.uniform(-np.pi, np.pi, (E, A))
+    x = rm.lp_x[on] + spread * np.cos(ang); y = rm.lp_y[on] + spread * np.sin(ang)
+    x[0, 0], y[0, 0] = rm.lp_x.min() - 400.0, rm.lp_y.max() + 400.0      # far outside the grid
+    h = rng.uniform(-3.1, 3.1, (E, A)); v = np.zeros((E, A))
+    eng, ora = engine(rm, cfg), oracle_world(rm, cfg, threads=8)
+    for w in (eng, ora):
+        w.reset(x, y, h, v, None, None)
+    act = np.zeros((E, A), np.int32)
+    for t in range(2):
+        eng.step(torch.from_numpy(act).cuda()); ora.step(act)
+        eng.observe(); ora.observe()
+        assert_same(eng.state_numpy(), ora.state())
+        assert_same(eng.obs_numpy(), ora.obs())
+    if wp:
+        n = ora.obs()["wp_n_paths"]
+        assert (n > 0).mean() > 0.5
+
+
 def test_full_size_grid_properties():
     """At BASELINE's full grid size the oracle is too slow for many envs, so check size-independent
     properties on a larger batch: determinism (two runs bit-identical), OGM == 255 at the ego's
