@@ -88,6 +88,13 @@ k_lidar(DCfg c, DMap m, DState s, DObs o, const double* __restrict__ rays, const
     n_boxes = 0;
     n_edges = 0;
   }
+  // this thread's first ray: its table entries are requested before the staging below, so that their
+  // latency is paid together with the vehicle / edge loads instead of after the barrier
+  const int R = c.lidar_rays;
+  const int si_first = threadIdx.x < R ? (int)threadIdx.x : R - 1;
+  int r = order[si_first];
+  LSector sec = sectors[si_first >> 5];
+  double dx = rays[r * 3 + 0], dy = rays[r * 3 + 1], dz = rays[r * 3 + 2];
   __syncthreads();
   // stage the env's other vehicles (order is irrelevant: the result is a minimum); every field is
   // loaded before the cull decision so that the block pays one round of global-load latency
@@ -138,15 +145,18 @@ k_lidar(DCfg c, DMap m, DState s, DObs o, const double* __restrict__ rays, const
   if (threadIdx.x == 0 && (n_boxes > SB_LIDAR_MAX_BOXES || n_edges > SB_LIDAR_MAX_EDGES))
     s.status[ai] |= SB_STATUS_LIDAR_OVERFLOW;
   const double inf = __longlong_as_double(0x7ff0000000000000LL);
-  const int R = c.lidar_rays;
   const double miss = c.lidar_miss_inf ? inf : 0.0;
 
   for (int base = 0; base < R; base += blockDim.x) {  // blockDim is a multiple of 32: chunks stay warp-aligned
     const int si = base + threadIdx.x;
     const bool act = si < R;
-    const int r = order[act ? si : R - 1];
-    const LSector sec = sectors[(act ? si : R - 1) >> 5];
-    const double dx = rays[r * 3 + 0], dy = rays[r * 3 + 1], dz = rays[r * 3 + 2];
+    if (base > 0) {  // (the first chunk's entries were loaded above)
+      r = order[act ? si : R - 1];
+      sec = sectors[(act ? si : R - 1) >> 5];
+      dx = rays[r * 3 + 0];
+      dy = rays[r * 3 + 1];
+      dz = rays[r * 3 + 2];
+    }
     // unit horizontal direction of this ray (float); a vertical ray takes no per-ray cull
     const float fdx = (float)dx, fdy = (float)dy;
     const float len = sqrtf(fdx * fdx + fdy * fdy);

@@ -549,8 +549,8 @@ __device__ __forceinline__ double wp_slope(double rise, double run) {
 // lane_following_controller.py:367-374, only needs this one): the vehicle's projection on the
 // first lane point's heading line, or the lane point itself for a path of <= spacing points.
 __device__ void wp_first_point(const DMap& m, const int32_t* path, int n, double vx, double vy, double* x, double* y) {
-  int mm = 0;
-  for (int i = 0; i < n; ++i)
+  int mm = 0;  // kept lane points, counted only until the test below is decided
+  for (int i = 0; i < n && (double)mm <= m.lanepoint_spacing; ++i)
     if (!(m.lp_inferred[path[i]] && 0 < i && i < n - 1)) ++mm;
   const int lp0 = path[0];
   const double lx = m.lp_x[lp0], ly = m.lp_y[lp0];
