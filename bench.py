@@ -341,11 +341,11 @@ def main():
         torch.cuda.synchronize()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        for t in range(10):
+        for t in range(K):  # the same ticks as the timed region above: the scene gets denser as agents converge
             tick_e(W_ + t)
         e1.record()
         torch.cuda.synchronize()
-        ms_events = e0.elapsed_time(e1) / 10
+        ms_events = e0.elapsed_time(e1) / K
         eng_e.close()
 
     if rank == 0:
