@@ -226,6 +226,7 @@ def main():
     ap.add_argument("--workload", default="4lane_lidar_ogm_dagm_256", choices=sorted(WORKLOADS))
     ap.add_argument("--envs", type=int, default=0, help="override envs per GPU")
     ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--e2e-full-rewrite", action="store_true", help="e2e with the default transport only (every grid byte rewritten per call)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--events", action="store_true", help="also compute Events / dones / trip-meter rewards (k_events)")
     ap.add_argument("--no-kernel-timing", action="store_true",
@@ -310,20 +311,29 @@ def main():
     # bytes that cross PCIe: the 0/255 grids travel as 1 bit per pixel (sb_copy_obs_to_host) and are widened
     # to the uint8 StdObs layout by host threads inside the call; every other buffer is copied as is
     d2h = sum(t.numel() * t.element_size() // (8 if k in ("ogm", "dagm") else 1) for k, t in host_obs.items())
-    eng.step_host(act_host.numpy(), soc_host[0].numpy()); eng.copy_obs_to_host(host_obs)  # warm
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    t0 = time.perf_counter()
-    for t in range(Ke):
-        eng.step_host(act_host.numpy(), soc_host[(t + 1) % T].numpy())
-        eng.copy_obs_to_host(host_obs)
-    torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
-    e2e_t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
-    e2e_value = world * E * A * Ke / float(e2e_t.item())
+    def e2e_run(t_base):
+        eng.step_host(act_host.numpy(), soc_host[t_base % T].numpy()); eng.copy_obs_to_host(host_obs)  # warm
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        for t in range(Ke):
+            eng.step_host(act_host.numpy(), soc_host[(t_base + t + 1) % T].numpy())
+            eng.copy_obs_to_host(host_obs)
+        torch.cuda.synchronize()
+        e2e_t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
+        return world * E * A * Ke / float(e2e_t.item())
+    # first with every grid byte rewritten per call (the default of sb_copy_obs_to_host), then the way a
+    # vectorised env that keeps its pinned staging buffers would run it: sb_set_incremental_host_grids, only the
+    # 64-pixel words that changed since the previous call are rewritten (the buffers hold the full images either way)
+    e2e_full = e2e_run(0)
+    e2e_value = e2e_full
+    if not args.e2e_full_rewrite:
+        eng.set_incremental_host_grids(True)
+        e2e_value = e2e_run(Ke + 1)
+        eng.set_incremental_host_grids(False)
 
     # ---- informational: the same step with Events / dones / trip-meter rewards also computed (k_events)
     ms_events = None
@@ -383,7 +393,12 @@ def main():
                          "bytes_per_launch": per_launch, "ms_per_launch": d_ms / max(d_n, 1)},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "host_obs_bytes_per_step": obs_host_bytes, "steps": Ke,
-                    "transport": "grids bit-packed over PCIe, widened to uint8 in host memory by the library"},
+                    "value_full_rewrite": e2e_full,
+                    "transport": "grids bit-packed over PCIe, widened to uint8 in host memory by the library; "
+                                 + ("every byte rewritten per call" if args.e2e_full_rewrite else
+                                    "persistent pinned destination buffers, only the 64-pixel words that changed since "
+                                    "the previous call are rewritten (sb_set_incremental_host_grids); "
+                                    "value_full_rewrite = the default mode")},
             "gpu_launches": int(launches), "clocks": clocks,
         }
         if world == 1 and not args.no_cpu_baseline:

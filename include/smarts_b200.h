@@ -284,6 +284,14 @@ int sb_step_host(SbHandle h, const void *host_actions, int64_t action_bytes,
  * The grids (0 / 255 pixels) cross PCIe as 1 bit per pixel and are widened to uint8 by a pool of
  * host threads while later chunks are still in flight; every other buffer is a plain copy. */
 int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs *host_dst);
+/* Opt-in for callers that reuse their host grid buffers: on = 1 promises that the ogm / dagm pointers given to
+ * sb_copy_obs_to_host are the ones of the previous call and that nothing else wrote to them in between.  The
+ * library then rewrites only the 64-pixel words that changed since that call (an ego-centred road image changes
+ * along its edges only), which takes the host-memory write volume -- the bound of the call -- down by an order of
+ * magnitude.  The buffers hold the complete uint8 images after every call either way.  A new pointer, a new size
+ * or on = 0 -> 1 makes the next call a full write.  (hiway_env.py:216-263: the reference allocates fresh arrays
+ * per step; a vectorised env that keeps its pinned staging buffers is the use case.) */
+int sb_set_incremental_host_grids(SbHandle h, int on);
 int sb_get_obs(SbHandle h, SbObsPtrs *out);
 int sb_get_state(SbHandle h, SbStatePtrs *out);
 /* number of kernel launches issued by this handle so far (bench gpu_launches) */

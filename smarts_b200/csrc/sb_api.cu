@@ -19,6 +19,7 @@ extern "C" {
 void* sbx_pool_create(int threads);
 void sbx_pool_destroy(void* p);
 void sbx_pool_submit(void* p, const uint8_t* bits, uint8_t* out, size_t n_bytes_in, size_t piece);
+void sbx_pool_submit_diff(void* p, const uint8_t* bits, uint8_t* prev, uint8_t* out, size_t n_bytes_in, size_t piece);
 void sbx_pool_wait(void* p);
 int sbx_pool_threads(void* p);
 }
@@ -62,6 +63,14 @@ struct SbHandle_ {
   void* pool = nullptr;
   std::vector<cudaEvent_t> xfer_ev;
   double xfer_frac = 1.0;  // share of the agents whose grids take the bit-packed path (SB_XFER_PACKED_SHARE)
+  // incremental grid writes (sb_set_incremental_host_grids): the bit image the destination was last written from
+  bool incremental = false, prev_valid = false;
+  uint8_t* h_prev = nullptr;
+  size_t prev_bytes = 0;
+  const void* prev_dst[2] = {nullptr, nullptr};
+  size_t prev_len[2] = {0, 0};
+  bool xfer_diff = false;
+  size_t xfer_bits = 0;
 };
 
 namespace {
@@ -401,6 +410,7 @@ void sb_destroy(SbHandle h) {
   for (void* p : h->allocs) cudaFree(p);
   if (h->pool) sbx_pool_destroy(h->pool);
   if (h->h_bits) cudaFreeHost(h->h_bits);
+  std::free(h->h_prev);
   for (auto e : h->xfer_ev) cudaEventDestroy(e);
   for (auto e : h->ev_pool) cudaEventDestroy(e);
   delete h;
@@ -913,6 +923,25 @@ int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs* dst) {
       h->h_bits = static_cast<uint8_t*>(q);
       h->bits_bytes = need;
     }
+    bool diff = false;  // incremental: same destinations and sizes as the previous call, written by this library
+    if (h->incremental) {
+      if (h->prev_bytes < need) {
+        std::free(h->h_prev);
+        h->h_prev = static_cast<uint8_t*>(std::malloc(need));
+        if (!h->h_prev) return SB_ENOMEM;
+        h->prev_bytes = need;
+        h->prev_valid = false;
+      }
+      diff = h->prev_valid;
+      for (int j = 0; j < 2; ++j) {
+        const void* d = j < nj ? jobs[j].host : nullptr;
+        const size_t len = j < nj ? jobs[j].bytes : 0;
+        if (h->prev_dst[j] != d || h->prev_len[j] != len) diff = false;
+        h->prev_dst[j] = d;
+        h->prev_len[j] = len;
+      }
+    }
+    h->xfer_diff = diff;
     if (!h->pool) {  // host threads: the cores of this box shared by the ranks of a torchrun launch
       unsigned hc = std::thread::hardware_concurrency();
       const char* lws = getenv("LOCAL_WORLD_SIZE");
@@ -1001,10 +1030,22 @@ int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs* dst) {
     for (size_t k = 0; k < sent.size() && ok; ++k) {
       ok = cuda_ok(h, cudaEventSynchronize(h->xfer_ev[k]), "D2H grid bits wait");
       if (k == 0) t_first = ms_since();
-      if (ok) sbx_pool_submit(h->pool, h->h_bits + sent[k].off, sent[k].host, sent[k].len, (size_t)128 << 10);
+      if (!ok) break;
+      if (h->xfer_diff)
+        sbx_pool_submit_diff(h->pool, h->h_bits + sent[k].off, h->h_prev + sent[k].off, sent[k].host, sent[k].len,
+                             (size_t)128 << 10);
+      else
+        sbx_pool_submit(h->pool, h->h_bits + sent[k].off, sent[k].host, sent[k].len, (size_t)128 << 10);
     }
     t_last = ms_since();
     sbx_pool_wait(h->pool);
+    if (ok && h->incremental && !h->xfer_diff) {  // a full write: remember what the destination now holds
+      size_t total = 0;
+      for (const Sent& q : sent) total = std::max(total, q.off + q.len);
+      std::memcpy(h->h_prev, h->h_bits, total);
+      h->prev_valid = true;
+    }
+    if (!ok) h->prev_valid = false;
     t_pool = ms_since();
   }
   if (!ok) return SB_ECUDA;
@@ -1014,6 +1055,13 @@ int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs* dst) {
             "(%d threads, %.1f MB over the link, packed share %.2f)\n",
             t_first, t_last, t_pool, ms_since(), h->pool ? sbx_pool_threads(h->pool) : 0, link_total / 1e6, h->xfer_frac);
   return ok ? SB_OK : SB_ECUDA;
+}
+
+int sb_set_incremental_host_grids(SbHandle h, int on) {
+  if (!h) return SB_EINVAL;
+  h->incremental = on != 0;
+  h->prev_valid = false;  // the next call writes everything
+  return SB_OK;
 }
 
 int sb_set_timing(SbHandle h, int on) {

@@ -64,6 +64,48 @@ __attribute__((target("avx512f,avx512bw"))) void expand_avx512(const uint8_t* bi
 }
 #endif
 
+// Incremental variants: `prev` holds the bit image this destination was last written from; only the
+// 64-pixel words that differ are rewritten (and recorded in prev).  A road surface or an empty film that
+// did not move writes nothing.
+typedef void (*ExpandDiffFn)(const uint8_t* bits, uint8_t* prev, uint8_t* out, size_t n_bytes_in);
+
+void expand_diff_lut(const uint8_t* bits, uint8_t* prev, uint8_t* out, size_t n) {
+  uint64_t* o = reinterpret_cast<uint64_t*>(out);
+  for (size_t i = 0; i < n; ++i)
+    if (bits[i] != prev[i]) {
+      o[i] = g_lut[bits[i]];
+      prev[i] = bits[i];
+    }
+}
+
+#if defined(__x86_64__)
+__attribute__((target("avx512f,avx512bw"))) void expand_diff_avx512(const uint8_t* bits, uint8_t* prev, uint8_t* out,
+                                                                     size_t n) {
+  size_t i = 0;
+  const bool aligned = (reinterpret_cast<uintptr_t>(out) & 63) == 0;
+  for (; i + 8 <= n; i += 8) {
+    uint64_t m, p;
+    std::memcpy(&m, bits + i, 8);
+    std::memcpy(&p, prev + i, 8);
+    if (m == p) continue;
+    const __m512i v = _mm512_movm_epi8((__mmask64)m);
+    if (aligned) _mm512_stream_si512(reinterpret_cast<__m512i*>(out + i * 8), v);
+    else _mm512_storeu_si512(out + i * 8, v);
+    std::memcpy(prev + i, &m, 8);
+  }
+  if (aligned) _mm_sfence();
+  if (i < n) expand_diff_lut(bits + i, prev + i, out + i * 8, n - i);
+}
+#endif
+
+ExpandDiffFn pick_expand_diff() {
+  std::call_once(g_lut_once, init_lut);
+#if defined(__x86_64__)
+  if (__builtin_cpu_supports("avx512bw") && __builtin_cpu_supports("avx512f")) return expand_diff_avx512;
+#endif
+  return expand_diff_lut;
+}
+
 ExpandFn pick_expand() {
   std::call_once(g_lut_once, init_lut);
 #if defined(__x86_64__)
@@ -76,6 +118,7 @@ struct Piece {
   const uint8_t* bits;
   uint8_t* out;
   size_t n;
+  uint8_t* prev;  // null: full write
 };
 
 }  // namespace
@@ -83,7 +126,7 @@ struct Piece {
 // A fixed pool; submit() queues pieces, wait() blocks until every queued piece is done.
 class SbExpandPool {
  public:
-  explicit SbExpandPool(int threads) : fn_(pick_expand()) {
+  explicit SbExpandPool(int threads) : fn_(pick_expand()), diff_fn_(pick_expand_diff()) {
     if (threads < 1) threads = 1;
     for (int i = 0; i < threads; ++i) workers_.emplace_back([this] { run(); });
   }
@@ -95,10 +138,10 @@ class SbExpandPool {
     cv_.notify_all();
     for (auto& t : workers_) t.join();
   }
-  void submit(const uint8_t* bits, uint8_t* out, size_t n, size_t piece) {
+  void submit(const uint8_t* bits, uint8_t* out, size_t n, size_t piece, uint8_t* prev = nullptr) {
     std::lock_guard<std::mutex> lk(mu_);
     for (size_t off = 0; off < n; off += piece) {
-      queue_.push_back(Piece{bits + off, out + off * 8, n - off < piece ? n - off : piece});
+      queue_.push_back(Piece{bits + off, out + off * 8, n - off < piece ? n - off : piece, prev ? prev + off : nullptr});
       ++pending_;
     }
     cv_.notify_all();
@@ -119,7 +162,8 @@ class SbExpandPool {
         if (stop_ && head_ >= queue_.size()) return;
         p = queue_[head_++];
       }
-      fn_(p.bits, p.out, p.n);
+      if (p.prev) diff_fn_(p.bits, p.prev, p.out, p.n);
+      else fn_(p.bits, p.out, p.n);
       {
         std::lock_guard<std::mutex> lk(mu_);
         if (--pending_ == 0) {
@@ -131,6 +175,7 @@ class SbExpandPool {
     }
   }
   ExpandFn fn_;
+  ExpandDiffFn diff_fn_;
   std::vector<std::thread> workers_;
   std::vector<Piece> queue_;
   size_t head_ = 0, pending_ = 0;
@@ -145,12 +190,17 @@ extern "C" {
 SBX_LOCAL void* sbx_pool_create(int threads);
 SBX_LOCAL void sbx_pool_destroy(void* p);
 SBX_LOCAL void sbx_pool_submit(void* p, const uint8_t* bits, uint8_t* out, size_t n_bytes_in, size_t piece);
+SBX_LOCAL void sbx_pool_submit_diff(void* p, const uint8_t* bits, uint8_t* prev, uint8_t* out, size_t n_bytes_in,
+                                    size_t piece);
 SBX_LOCAL void sbx_pool_wait(void* p);
 SBX_LOCAL int sbx_pool_threads(void* p);
 void* sbx_pool_create(int threads) { return new SbExpandPool(threads); }
 void sbx_pool_destroy(void* p) { delete static_cast<SbExpandPool*>(p); }
 void sbx_pool_submit(void* p, const uint8_t* bits, uint8_t* out, size_t n_bytes_in, size_t piece) {
   static_cast<SbExpandPool*>(p)->submit(bits, out, n_bytes_in, piece);
+}
+void sbx_pool_submit_diff(void* p, const uint8_t* bits, uint8_t* prev, uint8_t* out, size_t n_bytes_in, size_t piece) {
+  static_cast<SbExpandPool*>(p)->submit(bits, out, n_bytes_in, piece, prev);
 }
 void sbx_pool_wait(void* p) { static_cast<SbExpandPool*>(p)->wait(); }
 int sbx_pool_threads(void* p) { return static_cast<SbExpandPool*>(p)->threads(); }

@@ -22,6 +22,7 @@ EXPORTS = [
     "sb_abi_version", "sb_create", "sb_destroy", "sb_upload_map", "sb_upload_lidar_rays", "sb_reset",
     "sb_set_social", "sb_step", "sb_observe", "sb_step_host", "sb_copy_obs_to_host", "sb_get_obs",
     "sb_get_state", "sb_launch_count", "sb_last_error", "sb_set_timing", "sb_collect_timing",
+    "sb_set_incremental_host_grids",
 ]
 KERNEL_KINDS = ["k_set_social", "k_control", "k_observe", "k_lidar", "k_raster", "k_events", "k_pack_bits", "k_ttc", "k_extras", "k_ego_frame"]
 
@@ -64,6 +65,8 @@ def load_library(path: Optional[str] = None):
     L.sb_set_timing.restype = C.c_int
     L.sb_collect_timing.argtypes = [H, C.POINTER(C.c_double), C.POINTER(C.c_int64)]
     L.sb_collect_timing.restype = C.c_int
+    L.sb_set_incremental_host_grids.argtypes = [H, C.c_int]
+    L.sb_set_incremental_host_grids.restype = C.c_int
     for f in ("sb_create", "sb_upload_map", "sb_upload_lidar_rays", "sb_reset", "sb_set_social", "sb_step",
               "sb_observe", "sb_step_host", "sb_copy_obs_to_host", "sb_get_obs", "sb_get_state"):
         getattr(L, f).restype = C.c_int
@@ -221,6 +224,11 @@ class Engine:
             t = self._torch.empty(full, dtype=getattr(self._torch, np.dtype(dt).name), pin_memory=pinned)
             out[name] = t
         return out
+
+    def set_incremental_host_grids(self, on: bool = True):
+        """Promise that the same host grid buffers are passed to ``copy_obs_to_host`` every time and are not
+        written to in between: only the 64-pixel words that changed are rewritten (smarts_b200.h)."""
+        self._check(self._lib.sb_set_incremental_host_grids(self._h, int(on)), "sb_set_incremental_host_grids")
 
     def copy_obs_to_host(self, bufs: Dict[str, "object"]):
         p = _abi.SbObsPtrs()

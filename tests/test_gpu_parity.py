@@ -392,6 +392,49 @@ def test_host_buffer_call_matches_device_views(pinned, share, monkeypatch):
     assert got["ogm"].any() and got["dagm"].any()
 
 
+@pytest.mark.parametrize("pinned", [True, False])
+def test_incremental_host_grids_hold_the_full_images(pinned):
+    """sb_set_incremental_host_grids: with the same destination buffers call after call only the changed 64-pixel
+    words are rewritten -- the buffers must still equal the device images after every call, including after a
+    reset (large change), a switch to other buffers and back, and turning the mode off and on."""
+    import torch
+    rm = load_map("4lane")
+    E, A, M = 21, 4, 9
+    cfg = make_cfg(E=E, A=A, M=M, ogm=(96, 40, 0.3), dagm=(160, 72, 0.2), route_cap=16)
+    x, y, h, v, route, rlen = scenario_gen.agent_starts(rm, E, MISSIONS_4LANE, cfg.route_cap, 51, jitter=30.0, speed=6.0)
+    traffic = scenario_gen.SocialTraffic(rm, E, M, 52)
+    eng = engine(rm, cfg)
+    eng.reset(x, y, h, v, route, rlen)
+    eng.set_incremental_host_grids(True)
+
+    def buffers():
+        b = eng.host_obs_buffers(pinned=pinned)
+        if not pinned:
+            for k in ("ogm", "dagm"):
+                raw = torch.empty(b[k].numel() + 1, dtype=torch.uint8)
+                b[k] = raw[1:].view(b[k].shape)
+        for k in ("ogm", "dagm"):
+            b[k].fill_(0x5a)  # garbage: the first call into a buffer must write all of it
+        return b
+    bufs, other = buffers(), buffers()
+    act = np.random.default_rng(53).integers(0, 4, (E, A)).astype(np.int32)
+    changed = 0
+    for t in range(14):
+        if t == 5:
+            eng.reset(x[:7], y[:7], h[:7], v[:7], route[:7], rlen[:7], env_ids=np.arange(7, dtype=np.int32))
+        if t == 11:
+            eng.set_incremental_host_grids(False); eng.set_incremental_host_grids(True)
+        dst = other if t in (7, 8) else bufs      # other buffers for two calls, then back to the stale first pair
+        before = dst["dagm"].numpy().copy()
+        eng.step_host(act, traffic.states(t))
+        eng.copy_obs_to_host(dst)
+        dev = eng.obs_numpy()
+        for k in ("ogm", "dagm"):
+            assert np.array_equal(dst[k].numpy(), dev[k]), (t, k)
+        changed += int((before != dst["dagm"].numpy()).any())
+    assert changed >= 10 and dev["ogm"].any() and dev["dagm"].any()
+
+
 def test_config4_minicity_trajectory_tracking_100_social():
     """BASELINE configs[3] shape: minicity (52 k lane points), 32 TrajectoryTracking agents per env with
     100 BoxChassis social vehicles; action = first 10 waypoints of path 0 at 50/3.6 m/s
