@@ -83,6 +83,22 @@ __attribute__((target("avx512f,avx512bw"))) void expand_diff_avx512(const uint8_
                                                                      size_t n) {
   size_t i = 0;
   const bool aligned = (reinterpret_cast<uintptr_t>(out) & 63) == 0;
+  // eight words (512 pixels) per compare: an unchanged stretch costs two loads and one predictable branch
+  for (; i + 64 <= n; i += 64) {
+    const __m512i mv = _mm512_loadu_si512(bits + i), pv = _mm512_loadu_si512(prev + i);
+    unsigned ne = _mm512_cmpneq_epu64_mask(mv, pv);
+    if (!ne) continue;
+    _mm512_storeu_si512(prev + i, mv);
+    alignas(64) uint64_t w[8];
+    _mm512_store_si512(w, mv);
+    while (ne) {
+      const int k = __builtin_ctz(ne);
+      ne &= ne - 1;
+      const __m512i v = _mm512_movm_epi8((__mmask64)w[k]);
+      if (aligned) _mm512_stream_si512(reinterpret_cast<__m512i*>(out + (i + 8 * (size_t)k) * 8), v);
+      else _mm512_storeu_si512(out + (i + 8 * (size_t)k) * 8, v);
+    }
+  }
   for (; i + 8 <= n; i += 8) {
     uint64_t m, p;
     std::memcpy(&m, bits + i, 8);
