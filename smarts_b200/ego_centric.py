@@ -67,7 +67,9 @@ def _replace(obj: Any, **kwargs):
 
 def ego_centric_observation_adapter(obs: Observation, *args: Any, **kwargs: Any) -> Observation:
     """ego_centric_adapters.py:62-178.  Members this framework never fills (top_down_rgb, road_waypoints) pass
-    through as ``None``; the reference would raise on a missing camera, this mirror skips it."""
+    through as ``None``; the reference would raise on a missing camera, this mirror skips it.  The ego's
+    ``mission`` is passed through unchanged: this framework's ``Mission`` record holds road / lane / offset,
+    not world poses, so there is nothing to rotate (the reference rotates mission.start / via / goal)."""
     ego = obs.ego_vehicle_state
     position, heading = np.asarray(ego.position, np.float64), float(ego.heading)
 
