@@ -24,15 +24,14 @@ from .agent_interface import ActionSpaceType
 from .observation import Observation
 
 
-def wrap_value(value: float, _min: float, _max: float) -> float:
-    """utils/math.py:452-461."""
-    v = value
-    diff = _max - _min
-    if value <= _min:
-        v = _max - (_min - value) % diff
-    if value > _max:
-        v = _min + (value - _max) % diff
-    return v
+def wrap_value(value: float, lo: float, hi: float) -> float:
+    """Fold ``value`` into (lo, hi] (utils/math.py:452-461; Python's float ``%``, so lo itself maps to hi)."""
+    span = hi - lo
+    if value <= lo:
+        return hi - (lo - value) % span
+    if value > hi:
+        return lo + (value - hi) % span
+    return value
 
 
 def _ego_frame_matrix(ego_heading: float) -> np.ndarray:
@@ -151,23 +150,24 @@ def _target_pose_adapter(act, last_obs: Optional[Observation] = None):
     return np.array([*out[:2], wrap_value(float(ego.heading) + act[2], -math.pi, math.pi), act[3]])
 
 
-def _pair_adapters(obs_adapter: Callable, act_adapter: Callable) -> Tuple[Callable, Callable]:
-    """ego_centric_adapters.py:280-299: the action adapter sees the last *unmodified* observation."""
-    last_obs = None
+class _AdapterPair:
+    """ego_centric_adapters.py:280-299: the action adapter converts with the last observation the observation
+    adapter saw *before* it was moved into the ego frame."""
 
-    def oa_wrapper(obs: Observation):
-        nonlocal last_obs
-        last_obs = obs
-        return obs_adapter(obs)
+    def __init__(self, to_ego: Callable, to_world: Callable):
+        self._to_ego, self._to_world, self._seen = to_ego, to_world, None
 
-    def aa_wrapper(act: Any):
-        return act_adapter(act, last_obs)
+    def observe(self, obs: Observation):
+        self._seen = obs
+        return self._to_ego(obs)
 
-    return oa_wrapper, aa_wrapper
+    def act(self, action: Any):
+        return self._to_world(action, self._seen)
 
 
 def get_egocentric_adapters(action_space: ActionSpaceType):
     """ego_centric_adapters.py:302-325 -> (observation adapter, action adapter)."""
     m = {ActionSpaceType.Trajectory: _trajectory_adapter, ActionSpaceType.TrajectoryWithTime: _trajectory_adapter,
          ActionSpaceType.MPC: _trajectory_adapter, ActionSpaceType.TargetPose: _target_pose_adapter}
-    return _pair_adapters(ego_centric_observation_adapter, m.get(action_space, _identity))
+    pair = _AdapterPair(ego_centric_observation_adapter, m.get(action_space, _identity))
+    return pair.observe, pair.act

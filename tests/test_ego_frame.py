@@ -98,7 +98,7 @@ def test_gpu_ego_frame_matches_oracle(name):
 
 
 def test_host_adapters_round_trip():
-    """ego_centric.py mirrors utils/math.py:452-505 and the adapter pairing of ego_centric_adapters.py:280-325."""
+    """ego_centric.py mirrors utils/math.py:452-505 and the adapter pairing of ego_centric_adapters.py:280-325 (`_AdapterPair`)."""
     from smarts_b200 import ego_centric as ec
     from smarts_b200.agent_interface import ActionSpaceType
     from smarts_b200.observation import (EgoVehicleObservation, Dimensions, Events, Observation, VehicleObservation, Vias,
