@@ -16,7 +16,7 @@ from __future__ import annotations
 import math
 from dataclasses import is_dataclass
 from dataclasses import replace as dc_replace
-from typing import Any, Callable, Optional, Tuple
+from typing import Any, Callable, Optional
 
 import numpy as np
 
