@@ -34,6 +34,7 @@ struct SbHandle_ {
   DEvOut evo{};
   DTtcOut ttc{};
   DExtras ex{};
+  int32_t* d_veh_lane = nullptr;  // k_vehicle_lanes -> k_observe (only when V <= A * nbr_cap)
   bool stepped = false;  // a sb_step since the last sb_observe (SensorState.step; `sim.resetting` otherwise)
   bool have_map = false, have_rays = false;
   double* d_rays = nullptr;
@@ -362,6 +363,7 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
           dev_alloc(h, &q.hit_count, na) && dev_alloc(h, &q.hit_idx, nc)))
       return SB_ENOMEM;
   }
+  if (c.nbr_enable && d.V <= d.A * d.nbr_cap && !dev_alloc(h, &h->d_veh_lane, nv)) return SB_ENOMEM;
   if (!dev_alloc(h, &h->d_picks, na)) return SB_ENOMEM;
   if (!dev_alloc(h, &h->d_social, (size_t)d.E * (d.M ? d.M : 1) * 8)) return SB_ENOMEM;
   h->actions_cap = action_bytes(c);
@@ -819,8 +821,14 @@ int sb_observe(SbHandle h, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   {
     LaunchScope ls(h, SB_K_OBSERVE, st);
+    if (h->d_veh_lane) {  // fewer vehicles than neighbour slots: one lane lookup per vehicle, shared by the agents
+      const int nvs = c.E * c.V;
+      k_vehicle_lanes<<<(nvs + SB_OBS_WARPS - 1) / SB_OBS_WARPS, SB_OBS_WARPS * 32, 0, st>>>(c, h->dmap, h->st,
+                                                                                          h->d_veh_lane);
+      h->launches++;
+    }
     k_observe<<<(na + SB_OBS_WARPS - 1) / SB_OBS_WARPS, SB_OBS_WARPS * 32, 0, st>>>(c, h->dmap, h->st, h->ob,
-                                                                                    h->ev.trip_wp);
+                                                                                    h->ev.trip_wp, h->d_veh_lane);
   }
   if (c.ttc_enable) {
     LaunchScope ls(h, SB_K_TTC, st);

@@ -269,8 +269,21 @@ __device__ int d_nearest_lane_warp(const DMap& m, double px, double py, double r
 
 #define SB_OBS_WARPS 4
 
+// nearest_lane(vehicle position, radius = sedan length) of every alive vehicle slot, once per env instead of once
+// per (agent, neighbour) pair (sensors.py:243-266); warp per vehicle.
+#define SB_AGENT_LENGTH 3.68
+__global__ void __launch_bounds__(SB_OBS_WARPS * 32) k_vehicle_lanes(DCfg c, DMap m, DState s, int32_t* veh_lane) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int vj = blockIdx.x * SB_OBS_WARPS + warp;
+  if (vj >= c.E * c.V) return;
+  int nl = -1;
+  if (s.alive[vj]) nl = d_nearest_lane_warp(m, s.pos_x[vj], s.pos_y[vj], SB_AGENT_LENGTH, lane);
+  if (lane == 0) veh_lane[vj] = nl;
+}
+
+
 __global__ void __launch_bounds__(SB_OBS_WARPS * 32)
-k_observe(DCfg c, DMap m, DState s, DObs o, double* __restrict__ trip_wp) {
+k_observe(DCfg c, DMap m, DState s, DObs o, double* __restrict__ trip_wp, const int32_t* __restrict__ veh_lane) {
   __shared__ WarpPaths wps[SB_OBS_WARPS];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int ai = blockIdx.x * SB_OBS_WARPS + warp;
@@ -322,7 +335,10 @@ k_observe(DCfg c, DMap m, DState s, DObs o, double* __restrict__ trip_wp) {
     for (int k = 0; k < nw; ++k) {
       size_t q = (size_t)ai * cap + k;
       int vj = e * c.V + o.nbr_id[q];
-      int nl = d_nearest_lane_warp(m, s.pos_x[vj], s.pos_y[vj], ego_len, lane);
+      // the lane of a vehicle does not depend on who looks at it (the radius is the sedan's length for every
+      // agent): k_vehicle_lanes has it when the env has fewer vehicles than neighbour slots to fill
+      int nl = (veh_lane && ego_len == SB_AGENT_LENGTH) ? veh_lane[vj]
+                                                        : d_nearest_lane_warp(m, s.pos_x[vj], s.pos_y[vj], ego_len, lane);
       if (lane == 0) {
         o.nbr_lane[q] = nl;
         o.nbr_lane_index[q] = nl >= 0 ? (int8_t)m.lane_idx_in_road[nl] : 0;
