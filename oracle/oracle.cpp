@@ -386,6 +386,28 @@ void observe_waypoints(World& w, int e, int a) {
 // (plane.urdf), every other alive vehicle's box (agents z in [0.1, 1.1] above their base,
 // vehicle.urdf:12-16; social boxes z in [0.2, 0.2 + height], utils/bullet.py:169-177) and,
 // when lidar_wall_height > 0, vertical walls on the road boundary segments.
+//
+// Hit contract (DESIGN.md "LiDAR"): the ray table is factored into azimuth groups by
+// include/sb_lidar_table.h; a ray is  origin + s (ux, uy, slope),  0 <= s <= hlen.  Against a box the
+// horizontal slab interval [s0, s1] is found in the box frame with one reciprocal per axis, the
+// height slab with the ray's inv_slope; the hit is the entry of the intersection of the two.  A wall
+// is the degenerate interval s0 = s1 at the 2-D ray / segment intersection with heights [0, wall].
+namespace {
+inline void lidar_entry(double s0, double s1, double zlo, double zhi, double oz, const SbRayRec& q, double* sbest) {
+  double e0 = s0, e1 = s1;
+  if (q.dz == 0.0) {
+    if (oz < zlo || oz > zhi) return;
+  } else {
+    double za = (zlo - oz) * q.inv_slope, zb = (zhi - oz) * q.inv_slope;
+    if (za > zb) std::swap(za, zb);
+    if (za > e0) e0 = za;
+    if (zb < e1) e1 = zb;
+  }
+  if (e0 > e1 || e0 < 0.0 || e0 > q.hlen) return;  // origin inside the box: no hit
+  if (e0 < *sbest) *sbest = e0;
+}
+}  // namespace
+
 void observe_lidar(World& w, int e, int a) {
   const int R = w.cfg.lidar_rays, V = w.V;
   const int ai = e * w.A + a, vi = e * V + a;
@@ -393,11 +415,30 @@ void observe_lidar(World& w, int e, int a) {
   const double inf = std::numeric_limits<double>::infinity();
   const double miss = w.cfg.lidar_miss_inf ? inf : 0.0;
   for (int r = 0; r < R; ++r) {
-    const double dx = w.rays[r * 3 + 0], dy = w.rays[r * 3 + 1], dz = w.rays[r * 3 + 2];
-    double tbest = 2.0;
-    if (dz < 0.0) {
-      double t = (0.0 - oz) / dz;
-      if (t >= 0.0 && t <= 1.0) tbest = t;
+    const SbRayRec& q = w.ray_rec[r];
+    const size_t o = (size_t)ai * R + r;
+    if (q.group < 0) {  // straight up / down: the ground plane only
+      double t = 2.0;
+      if (q.dz < 0.0) {
+        t = (0.0 - oz) / q.dz;
+        if (!(t >= 0.0 && t <= 1.0)) t = 2.0;
+      }
+      if (t <= 1.0) {
+        w.lidar_hits[o] = 1;
+        w.lidar_points[o * 3 + 0] = ox;
+        w.lidar_points[o * 3 + 1] = oy;
+        w.lidar_points[o * 3 + 2] = oz + t * q.dz;
+      } else {
+        w.lidar_hits[o] = 0;
+        w.lidar_points[o * 3 + 0] = w.lidar_points[o * 3 + 1] = w.lidar_points[o * 3 + 2] = miss;
+      }
+      continue;
+    }
+    const double ux = w.ray_group_u[2 * q.group], uy = w.ray_group_u[2 * q.group + 1];
+    double sbest = inf;
+    if (q.dz < 0.0) {
+      const double sg = (0.0 - oz) * q.inv_slope;
+      if (sg >= 0.0 && sg <= q.hlen) sbest = sg;
     }
     for (int j = 0; j < V; ++j) {
       if (j == a) continue;
@@ -405,56 +446,48 @@ void observe_lidar(World& w, int e, int a) {
       if (!w.alive[vj]) continue;
       double c = w.cos_h[vj], s = w.sin_h[vj];
       double rx = ox - w.pos_x[vj], ry = oy - w.pos_y[vj];
-      // box frame: u = right (width), f = forward (length)
-      double lo_[3], ld_[3], mn[3], mx[3];
-      lo_[0] = rx * c + ry * s;
-      lo_[1] = ry * c - rx * s;
-      lo_[2] = oz;
-      ld_[0] = dx * c + dy * s;
-      ld_[1] = dy * c - dx * s;
-      ld_[2] = dz;
+      // box frame: axis 0 = right (width), axis 1 = forward (length)
+      double lo_[2] = {rx * c + ry * s, ry * c - rx * s};
+      double ld_[2] = {ux * c + uy * s, uy * c - ux * s};
       double hw = 0.5 * w.width[vj], hl = 0.5 * w.length[vj];
-      double z0 = w.pos_z[vj] + (j < w.A ? 0.1 : 0.2);
-      mn[0] = -hw; mx[0] = hw;
-      mn[1] = -hl; mx[1] = hl;
-      mn[2] = z0;  mx[2] = z0 + w.height[vj];
-      double t0 = -inf, t1 = inf;
+      double mn[2] = {-hw, -hl}, mx[2] = {hw, hl};
+      double s0 = -inf, s1 = inf;
       bool ok = true;
-      for (int k = 0; k < 3 && ok; ++k) {
+      for (int k = 0; k < 2 && ok; ++k) {
         if (ld_[k] == 0.0) {
           if (lo_[k] < mn[k] || lo_[k] > mx[k]) ok = false;
         } else {
-          double ta = (mn[k] - lo_[k]) / ld_[k], tb = (mx[k] - lo_[k]) / ld_[k];
-          if (ta > tb) std::swap(ta, tb);
-          if (ta > t0) t0 = ta;
-          if (tb < t1) t1 = tb;
+          double inv = 1.0 / ld_[k];
+          double sa = (mn[k] - lo_[k]) * inv, sb = (mx[k] - lo_[k]) * inv;
+          if (sa > sb) std::swap(sa, sb);
+          if (sa > s0) s0 = sa;
+          if (sb < s1) s1 = sb;
         }
       }
-      if (!ok || t0 > t1 || t0 < 0.0 || t0 > 1.0) continue;  // origin inside a box: no hit
-      if (t0 < tbest) tbest = t0;
+      if (!ok || s0 > s1) continue;
+      double z0 = w.pos_z[vj] + (j < w.A ? 0.1 : 0.2);
+      lidar_entry(s0, s1, z0, z0 + w.height[vj], oz, q, &sbest);
     }
     if (w.cfg.lidar_wall_height > 0.0) {
       const int NE = w.map.m.n_edges;
       for (int k = 0; k < NE; ++k) {
         const double* ed = &w.map.road_edges[(size_t)k * 4];
         double ex = ed[2] - ed[0], ey = ed[3] - ed[1];
-        double den = dx * ey - dy * ex;
+        double den = ux * ey - uy * ex;
         if (den == 0.0) continue;
         double qx = ed[0] - ox, qy = ed[1] - oy;
-        double t = (qx * ey - qy * ex) / den;
-        double u = (qx * dy - qy * dx) / den;
-        if (t < 0.0 || t > 1.0 || u < 0.0 || u > 1.0) continue;
-        double z = oz + t * dz;
-        if (z < 0.0 || z > w.cfg.lidar_wall_height) continue;
-        if (t < tbest) tbest = t;
+        double inv = 1.0 / den;
+        double sw = (qx * ey - qy * ex) * inv;
+        double u = (qx * uy - qy * ux) * inv;
+        if (sw < 0.0 || u < 0.0 || u > 1.0) continue;
+        lidar_entry(sw, sw, 0.0, w.cfg.lidar_wall_height, oz, q, &sbest);
       }
     }
-    size_t o = (size_t)ai * R + r;
-    if (tbest <= 1.0) {
+    if (sbest <= q.hlen) {
       w.lidar_hits[o] = 1;
-      w.lidar_points[o * 3 + 0] = ox + tbest * dx;
-      w.lidar_points[o * 3 + 1] = oy + tbest * dy;
-      w.lidar_points[o * 3 + 2] = oz + tbest * dz;
+      w.lidar_points[o * 3 + 0] = ox + sbest * ux;
+      w.lidar_points[o * 3 + 1] = oy + sbest * uy;
+      w.lidar_points[o * 3 + 2] = oz + sbest * q.slope;
     } else {
       w.lidar_hits[o] = 0;
       w.lidar_points[o * 3 + 0] = w.lidar_points[o * 3 + 1] = w.lidar_points[o * 3 + 2] = miss;
@@ -1101,7 +1134,12 @@ void* or_create(const SbConfig* cfg, const SbMap* m, const double* base_rays, in
   cp(mp.poly_x, m->poly_x, m->n_poly_verts);
   cp(mp.poly_y, m->poly_y, m->n_poly_verts);
   cp(mp.road_edges, m->road_edges, (size_t)m->n_edges * 4);
-  if (base_rays && n_rays > 0) w->rays.assign(base_rays, base_rays + (size_t)n_rays * 3);
+  if (base_rays && n_rays > 0) {
+    w->rays.assign(base_rays, base_rays + (size_t)n_rays * 3);
+    w->ray_rec.resize(n_rays);
+    w->ray_group_u.assign((size_t)n_rays * 2, 0.0);
+    sb_lidar_factor(base_rays, n_rays, w->ray_rec.data(), w->ray_group_u.data());
+  }
   w->E = cfg->n_envs;
   w->A = cfg->n_agents;
   w->M = cfg->n_social;

@@ -28,6 +28,7 @@
 #include <vector>
 
 #include "../include/sb_detmath.h"
+#include "../include/sb_lidar_table.h"
 #include "../include/smarts_b200.h"
 
 namespace {
@@ -98,6 +99,8 @@ struct World {
   SbConfig cfg;
   Map map;
   std::vector<double> rays;  // [R,3]
+  std::vector<SbRayRec> ray_rec;      // include/sb_lidar_table.h
+  std::vector<double> ray_group_u;    // [groups,2]
   int E, A, M, V;
   int substeps;
   // state

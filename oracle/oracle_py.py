@@ -23,7 +23,7 @@ _LIB = None
 def build(force: bool = False) -> str:
     so = os.path.join(_HERE, "_build", "liboracle.so")
     srcs = [os.path.join(_HERE, f) for f in ("oracle.cpp", "oracle_core.hpp")] + [
-        os.path.join(_HERE, "..", "include", f) for f in ("smarts_b200.h", "sb_detmath.h")]
+        os.path.join(_HERE, "..", "include", f) for f in ("smarts_b200.h", "sb_detmath.h", "sb_lidar_table.h")]
     stale = force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs)
     if stale:
         subprocess.check_call(["make", "-s", "-C", _HERE], stdout=subprocess.DEVNULL)

@@ -16,7 +16,7 @@ OUT = os.path.join(HERE, "libsmartsb200.so")
 SOURCES = ["sb_api.cu"]
 HOST_SOURCES = ["sb_hostxfer.cpp"]  # g++ (AVX-512 target attributes), linked into the same library
 DEPS = ["sb_api.cu", "sb_hostxfer.cpp", "sb_events.cuh", "sb_ttc.cuh", "sb_extras.cuh", "sb_lidar.cuh", "sb_kernels.cuh", "sb_control.cuh", "sb_waypoints.cuh", "sb_device.cuh", "sb_raster.cuh",
-        os.path.join("..", "..", "include", "smarts_b200.h"), os.path.join("..", "..", "include", "sb_detmath.h")]
+        os.path.join("..", "..", "include", "smarts_b200.h"), os.path.join("..", "..", "include", "sb_detmath.h"), os.path.join("..", "..", "include", "sb_lidar_table.h")]
 
 
 def nvcc_path() -> str:
@@ -47,7 +47,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         objs.append(obj)
     cmd = [
         nvcc_path(), "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
-        "-fmad=false", "--expt-extended-lambda", "-Xcompiler", "-fPIC", "-shared",
+        "-fmad=false", "--expt-extended-lambda", "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off", "-shared",
         "-Xptxas", "-v" if verbose else "-O3",
         "-o", OUT,
     ] + [os.path.join(CSRC, s) for s in SOURCES] + objs

@@ -37,9 +37,7 @@ struct SbHandle_ {
   int32_t* d_veh_lane = nullptr;  // k_vehicle_lanes -> k_observe (only when V <= A * nbr_cap)
   bool stepped = false;  // a sb_step since the last sb_observe (SensorState.step; `sim.resetting` otherwise)
   bool have_map = false, have_rays = false;
-  double* d_rays = nullptr;
-  int32_t* d_ray_order = nullptr;   // rays in azimuth order (k_lidar's thread -> ray map)
-  LSector* d_ray_sectors = nullptr; // bounding sector of every 32 consecutive rays of that order
+  LTable ray_table{};   // factored ray table (include/sb_lidar_table.h), sorted by azimuth group
   float ray_reach = 0.f;
   std::vector<void*> allocs;
   CtrlPick* d_picks = nullptr;  // k_control_paths -> k_control_law
@@ -611,56 +609,37 @@ int sb_upload_lidar_rays(SbHandle h, const double* base_rays, int32_t n_rays) {
   if (n_rays != h->cfg.lidar_rays) return fail(h, SB_EINVAL, "n_rays != cfg.lidar_rays");
   cudaSetDevice(h->cfg.device);
   if (n_rays > SB_LIDAR_MAX_RAYS) return fail(h, SB_EINVAL, "lidar: too many rays");
-  const double* d = nullptr;
-  if (!dev_upload(h, &d, base_rays, (size_t)n_rays * 3)) return SB_ECUDA;
-  h->d_rays = const_cast<double*>(d);
+  // Factor the table into azimuth groups (include/sb_lidar_table.h; the oracle runs the same function) and
+  // sort the records by group, vertical rays last: a warp's 32 rays then walk the same interval list.
+  std::vector<SbRayRec> rec(n_rays);
+  std::vector<double> gu((size_t)n_rays * 2, 0.0);
+  const int n_groups = sb_lidar_factor(base_rays, n_rays, rec.data(), gu.data());
+  std::stable_sort(rec.begin(), rec.end(), [&](const SbRayRec& p, const SbRayRec& q) {
+    const int gp = p.group < 0 ? n_groups : p.group, gq = q.group < 0 ? n_groups : q.group;
+    return gp < gq;
+  });
+  std::vector<int32_t> gstart(n_groups + 1, n_rays);
+  for (int i = n_rays - 1; i >= 0; --i)
+    if (rec[i].group >= 0) gstart[rec[i].group] = i;
+  {  // first vertical ray (or R)
+    int nv = n_rays;
+    for (int i = n_rays - 1; i >= 0 && rec[i].group < 0; --i) nv = i;
+    gstart[n_groups] = nv;
+  }
   double reach = 0.0;
-  for (int i = 0; i < n_rays; ++i)
-    reach = fmax(reach, sqrt(base_rays[i * 3] * base_rays[i * 3] + base_rays[i * 3 + 1] * base_rays[i * 3 + 1]));
+  for (int i = 0; i < n_rays; ++i) reach = fmax(reach, rec[i].hlen);
   h->ray_reach = (float)(reach * 1.0001 + 0.01);
-  // Thread -> ray map of k_lidar: rays sorted by azimuth (vertical rays last) so that a warp's 32
-  // rays fan a narrow sector, and the bounding sector of every chunk of 32.  Used for culling
-  // only (conservative: a chunk that is not narrow is marked "wide" and culls nothing).
-  std::vector<int32_t> order(n_rays);
-  std::vector<double> az(n_rays);
-  for (int i = 0; i < n_rays; ++i) {
-    order[i] = i;
-    double hx = base_rays[i * 3], hy = base_rays[i * 3 + 1];
-    az[i] = (hx * hx + hy * hy > 1e-18) ? atan2(hy, hx) : 1e9;
-  }
-  std::stable_sort(order.begin(), order.end(), [&](int32_t p, int32_t q) { return az[p] < az[q]; });
-  const int n_chunks = (n_rays + 31) / 32;
-  std::vector<LSector> sectors(n_chunks);
-  for (int ch = 0; ch < n_chunks; ++ch) {
-    double sx = 0, sy = 0;
-    int cnt = 0;
-    for (int i = ch * 32; i < n_rays && i < ch * 32 + 32; ++i) {
-      int r = order[i];
-      if (az[r] > 1e8) continue;
-      sx += cos(az[r]);
-      sy += sin(az[r]);
-      ++cnt;
-    }
-    LSector q{1.f, 0.f, -2.f, 0.f};  // wide
-    double nrm = sqrt(sx * sx + sy * sy);
-    if (cnt > 0 && nrm > 0.5 * cnt) {
-      double ucx = sx / nrm, ucy = sy / nrm, cmin = 1.0;
-      for (int i = ch * 32; i < n_rays && i < ch * 32 + 32; ++i) {
-        int r = order[i];
-        if (az[r] > 1e8) continue;
-        cmin = fmin(cmin, cos(az[r]) * ucx + sin(az[r]) * ucy);
-      }
-      double half = acos(fmax(-1.0, fmin(1.0, cmin))) + 1e-3;  // margin for the float arithmetic of the cull
-      if (half < 1.3) q = LSector{(float)ucx, (float)ucy, (float)cos(half), (float)sin(half)};
-    }
-    sectors[ch] = q;
-  }
-  const int32_t* d_order = nullptr;
-  const LSector* d_sec = nullptr;
-  if (!dev_upload(h, &d_order, order.data(), order.size()) || !dev_upload(h, &d_sec, sectors.data(), sectors.size()))
+  const SbRayRec* d_rec = nullptr;
+  const double* d_gu = nullptr;
+  const int32_t* d_gs = nullptr;
+  if (!dev_upload(h, &d_rec, rec.data(), rec.size()) || !dev_upload(h, &d_gu, gu.data(), (size_t)(n_groups > 0 ? n_groups : 1) * 2) ||
+      !dev_upload(h, &d_gs, gstart.data(), gstart.size()))
     return SB_ECUDA;
-  h->d_ray_order = const_cast<int32_t*>(d_order);
-  h->d_ray_sectors = const_cast<LSector*>(d_sec);
+  h->ray_table.rec = d_rec;
+  h->ray_table.group_u = reinterpret_cast<const double2*>(d_gu);
+  h->ray_table.group_start = d_gs;
+  h->ray_table.n_groups = n_groups;
+  h->ray_table.max_hlen = reach;
   h->have_rays = true;
   return SB_OK;
 }
@@ -840,8 +819,7 @@ int sb_observe(SbHandle h, void* stream) {
   }
   if (c.lidar_enable) {
     LaunchScope ls(h, SB_K_LIDAR, st);
-    k_lidar<<<na, SB_LIDAR_THREADS, 0, st>>>(c, h->dmap, h->st, h->ob, h->d_rays,
-                                                                                     h->d_ray_order, h->d_ray_sectors, h->ray_reach);
+    k_lidar<<<na, SB_LIDAR_THREADS, 0, st>>>(c, h->dmap, h->st, h->ob, h->ray_table, h->ray_reach);
   }
   if (c.ogm_enable || c.dagm_enable) {
     LaunchScope ls(h, SB_K_RASTER, st);

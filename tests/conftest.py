@@ -63,7 +63,8 @@ def make_cfg(E=1, A=1, M=0, dt=0.1, action_space=_abi.SB_ACTION_LANE, traj_len=1
     return c
 
 
-def oracle_world(rm: RoadMapData, cfg, threads=1):
+def oracle_world(rm: RoadMapData, cfg, threads=1, rays=None):
     from oracle import oracle_py
-    rays = lidar_params.base_rays(lidar_params.BasicLidar)
+    if rays is None:
+        rays = lidar_params.base_rays(lidar_params.BasicLidar)
     return oracle_py.OracleWorld(cfg, rm.arrays(), rm.spacing, rays, threads=threads)

@@ -18,9 +18,9 @@ MISSIONS_F8 = [("gneE20", 0, 5.0, "gneE27"), ("gneE36", 1, 5.0, "gneE25"), ("gne
                ("gneE36", 0, 30.0, "gneE25")]
 
 
-def engine(rm, cfg):
+def engine(rm, cfg, rays=None):
     from smarts_b200.engine import Engine
-    return Engine(cfg, rm, lidar_params.base_rays(lidar_params.BasicLidar))
+    return Engine(cfg, rm, lidar_params.base_rays(lidar_params.BasicLidar) if rays is None else rays)
 
 
 def assert_same(got: dict, want: dict, keys=None):
@@ -36,13 +36,13 @@ def assert_same(got: dict, want: dict, keys=None):
             raise AssertionError(f"{k}: {len(bad)} mismatches, first at {bad[0]}: got {g[tuple(bad[0])]} want {w[tuple(bad[0])]}")
 
 
-def run_pair(rm, cfg, missions, ticks, seed, action_fn, jitter=20.0, check_every=1, social_alive=0.9):
+def run_pair(rm, cfg, missions, ticks, seed, action_fn, jitter=20.0, check_every=1, social_alive=0.9, rays=None):
     import torch
     E, M = cfg.n_envs, cfg.n_social
     x, y, h, v, route, rlen = scenario_gen.agent_starts(rm, E, missions, cfg.route_cap, seed, jitter=jitter, speed=5.0)
     traffic = scenario_gen.SocialTraffic(rm, E, M, seed + 1, p_alive=social_alive) if M else None
-    eng = engine(rm, cfg)
-    ora = oracle_world(rm, cfg, threads=8)
+    eng = engine(rm, cfg, rays)
+    ora = oracle_world(rm, cfg, threads=8, rays=rays)
     eng.reset(x, y, h, v, route, rlen)
     ora.reset(x, y, h, v, route, rlen)
     for t in range(ticks):
@@ -86,6 +86,29 @@ def test_config3_4lane_lidar_ogm_dagm():
     o = ora.obs()
     assert o["ogm"].max() == 255 and o["dagm"].max() == 255 and o["lidar_hits"].sum() > 0
     assert 0.05 < (o["dagm"] == 255).mean() < 0.95
+
+
+@pytest.mark.parametrize("table", ["hdl32e", "ring"])
+def test_lidar_other_ray_tables(table):
+    """Ray tables other than BasicLidar: VelodyneHDL32E (36 azimuth groups x 24 laser angles, 100 m reach: the
+    interval lists are rebuilt per chunk of groups) and a flat ring of 250 distinct azimuths x 2 laser angles
+    plus straight-up / straight-down rays (every group holds two rays; vertical rays take the ground-only path)."""
+    rm = load_map("4lane")
+    E, A, M = 4, 4, 20
+    if table == "hdl32e":
+        rays = lidar_params.base_rays(lidar_params.VelodyneHDL32E)
+    else:
+        az = np.linspace(0.0, 2 * np.pi, 250, endpoint=False)
+        rays = np.concatenate([
+            np.stack([30 * np.cos(az), 30 * np.sin(az), np.zeros_like(az)], 1),
+            np.stack([25 * np.cos(az), 25 * np.sin(az), np.full_like(az, -2.0)], 1),
+            np.array([[0.0, 0.0, -5.0], [0.0, 0.0, 5.0], [0.0, 0.0, -0.5]])])
+    cfg = make_cfg(E=E, A=A, M=M, lidar=True, lidar_miss_inf=1, wall=1.5, route_cap=16)
+    cfg.lidar_rays = len(rays)
+    eng, ora = run_pair(rm, cfg, MISSIONS_4LANE, ticks=12, seed=23, action_fn=lane_actions(E, A, 9), check_every=3,
+                        rays=rays)
+    o = ora.obs()
+    assert 0 < o["lidar_hits"].mean() < 1
 
 
 def test_config1_loop_laner_full_suite():
