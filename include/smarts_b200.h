@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define SB_ABI_VERSION 4
+#define SB_ABI_VERSION 5
 
 /* error codes */
 #define SB_OK 0
@@ -252,6 +252,9 @@ typedef struct SbResetState {
   const int32_t *via_count;  /* [n, A] 0..via_cap */
   const int32_t *via_lane;   /* [n, A, via_cap] map lane index (Via.lane_id) */
   const double *via_x, *via_y, *via_hit_distance, *via_required_speed; /* [n, A, via_cap] */
+  /* 0: the envs' social slots are emptied (a fresh SMARTS.setup, smarts.py:440-460);  1: they are left as the last
+   * sb_set_social wrote them -- the auto-reset of a batched env whose injected traffic keeps running */
+  int32_t keep_social;
 } SbResetState;
 
 /* HiWayEnv.__init__ -> SMARTS.__init__ (smarts/env/hiway_env.py:166-173, smarts/core/smarts.py:96-185) */
@@ -275,6 +278,11 @@ int sb_set_social(SbHandle h, const double *dev_states, void *stream);
 int sb_step(SbHandle h, const void *dev_actions, void *stream);
 /* AgentManager.observe -> Sensors.observe for every agent (agent_manager.py:161-240, sensors.py:238-396) */
 int sb_observe(SbHandle h, void *stream);
+/* The same for the agents of the listed envs only (host env_ids [n]; NULL = every env): the reset observation of
+ * an auto-reset.  Every env of the reference is its own SMARTS instance (ParallelEnv, parallel_env.py:96-127), so
+ * observing the envs that were just reset must not touch the sensor state (driven path, trip meter,
+ * accelerometer history, vias, step counters) or the observation buffers of the others. */
+int sb_observe_envs(SbHandle h, const int32_t *env_ids, int32_t n, void *stream);
 /* Convenience: the reference-facing call with HOST buffers (hiway_env.py:216-263 step()):
  * copies actions and social states in, runs sb_set_social + sb_step + sb_observe, synchronises. */
 int sb_step_host(SbHandle h, const void *host_actions, int64_t action_bytes,

@@ -1286,7 +1286,7 @@ void or_reset(void* h, const int32_t* env_ids, int n, const SbResetState* init) 
         }
       }
     }
-    for (int j = w.A; j < w.V; ++j) {
+    for (int j = w.A; j < w.V && !init->keep_social; ++j) {
       int vj = e * w.V + j;
       w.alive[vj] = 0;
       w.pos_x[vj] = w.pos_y[vj] = w.pos_z[vj] = w.heading[vj] = w.speed[vj] = w.yaw_rate[vj] = 0.0;
@@ -1363,16 +1363,23 @@ void or_step(void* h, const void* actions) {
   w.stepped = true;
 }
 
-void or_observe(void* h) {
+// Sensors.observe for the agents of the listed envs (env_ids == nullptr: every env).  Envs are independent
+// simulations in the reference (one SMARTS instance each, parallel_env.py:96-127): observing one never touches
+// the sensor state of another.
+void or_observe_envs(void* h, const int32_t* env_ids, int n) {
   World& w = *static_cast<World*>(h);
-  parallel_for(w.E * w.A, w.threads, 1, [&](int i) { observe_agent(w, i / w.A, i % w.A); });
+  const int ne = env_ids ? n : w.E;
+  auto env_of = [&](int i) { return env_ids ? env_ids[i / w.A] : i / w.A; };
+  parallel_for(ne * w.A, w.threads, 1, [&](int i) { observe_agent(w, env_of(i), i % w.A); });
   if (w.cfg.events_enable) {
     const bool ticked = w.stepped;
-    parallel_for(w.E * w.A, w.threads, 1, [&](int i) { observe_events(w, i / w.A, i % w.A, ticked); });
+    parallel_for(ne * w.A, w.threads, 1, [&](int i) { observe_events(w, env_of(i), i % w.A, ticked); });
     w.stepped = false;
   }
-  if (w.cfg.ego_frame) parallel_for(w.E * w.A, w.threads, 1, [&](int i) { ego_frame_agent(w, i / w.A, i % w.A); });
+  if (w.cfg.ego_frame) parallel_for(ne * w.A, w.threads, 1, [&](int i) { ego_frame_agent(w, env_of(i), i % w.A); });
 }
+
+void or_observe(void* h) { or_observe_envs(h, nullptr, 0); }
 
 void or_get_state(void* h, SbStatePtrs* o) {
   World& w = *static_cast<World*>(h);

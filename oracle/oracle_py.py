@@ -42,6 +42,7 @@ def lib():
         L.or_set_social.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
         L.or_step.argtypes = [C.c_void_p, C.c_void_p]
         L.or_observe.argtypes = [C.c_void_p]
+        L.or_observe_envs.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.c_int]
         L.or_get_state.argtypes = [C.c_void_p, C.POINTER(_abi.SbStatePtrs)]
         L.or_get_obs.argtypes = [C.c_void_p, C.POINTER(_abi.SbObsPtrs)]
         L.or_waypoint_paths.restype = C.c_int
@@ -115,9 +116,11 @@ class OracleWorld:
         except Exception:
             pass
 
-    def reset(self, x, y, heading, speed, route=None, route_len=None, env_ids=None, goal=None, vias=None):
+    def reset(self, x, y, heading, speed, route=None, route_len=None, env_ids=None, goal=None, vias=None,
+              keep_social=False):
         x, y, heading, speed = (np.ascontiguousarray(v, np.float64) for v in (x, y, heading, speed))
         rs = _abi.SbResetState()
+        rs.keep_social = int(keep_social)
         rs.agent_x, rs.agent_y, rs.agent_heading, rs.agent_speed = _dp(x), _dp(y), _dp(heading), _dp(speed)
         keep = []
         if route is not None:
@@ -152,8 +155,12 @@ class OracleWorld:
         a = np.ascontiguousarray(actions)
         lib().or_step(self._h, a.ctypes.data_as(C.c_void_p))
 
-    def observe(self):
-        lib().or_observe(self._h)
+    def observe(self, env_ids=None):
+        if env_ids is None:
+            lib().or_observe(self._h)
+        else:
+            ids = np.ascontiguousarray(env_ids, np.int32)
+            lib().or_observe_envs(self._h, _ip(ids), len(ids))
 
     def obs(self) -> Dict[str, np.ndarray]:
         p = _abi.SbObsPtrs()

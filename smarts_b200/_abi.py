@@ -6,7 +6,7 @@ from typing import Dict
 
 import numpy as np
 
-SB_ABI_VERSION = 4
+SB_ABI_VERSION = 5
 
 SB_ACTION_CONTINUOUS = 0
 SB_ACTION_LANE = 1
@@ -105,7 +105,8 @@ class SbResetState(C.Structure):
                 ("route", _pi32), ("route_len", _pi32),
                 ("goal_x", _pf64), ("goal_y", _pf64), ("goal_radius", _pf64),
                 ("via_count", _pi32), ("via_lane", _pi32),
-                ("via_x", _pf64), ("via_y", _pf64), ("via_hit_distance", _pf64), ("via_required_speed", _pf64)]
+                ("via_x", _pf64), ("via_y", _pf64), ("via_hit_distance", _pf64), ("via_required_speed", _pf64),
+                ("keep_social", C.c_int32)]
 
 
 _NP = {_pi32: np.int32, _pf64: np.float64, _pu8: np.uint8, _pf32: np.float32, _pi8: np.int8, _pu32: np.uint32}

@@ -35,6 +35,8 @@ struct SbHandle_ {
   DTtcOut ttc{};
   DExtras ex{};
   int32_t* d_veh_lane = nullptr;  // k_vehicle_lanes -> k_observe (only when V <= A * nbr_cap)
+  int32_t *h_env_list = nullptr, *d_env_list = nullptr;  // sb_observe_envs: pinned staging + device copy of the env list
+  cudaStream_t env_list_stream = nullptr;
   bool stepped = false;  // a sb_step since the last sb_observe (SensorState.step; `sim.resetting` otherwise)
   bool have_map = false, have_rays = false;
   LTable ray_table{};   // factored ray table (include/sb_lidar_table.h), sorted by azimuth group
@@ -128,7 +130,8 @@ __global__ void k_fill(double* p, size_t n, double v) {
 // (models/vehicle.urdf:12-16), social slots cleared.
 __global__ void k_reset(DCfg c, DState s, DEvents ev, const int32_t* env_ids, int n, const double* ax,
                         const double* ay, const double* ah, const double* av, const int32_t* route,
-                        const int32_t* route_len, const double* gx, const double* gy, const double* gr) {
+                        const int32_t* route_len, const double* gx, const double* gy, const double* gr,
+                        int keep_social) {
   int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= n * c.V) return;
   int i = t / c.V, slot = t - i * c.V;
@@ -170,7 +173,7 @@ __global__ void k_reset(DCfg c, DState s, DEvents ev, const int32_t* env_ids, in
       ev.goal_y[ai] = gy ? gy[src] : 0.0;
       ev.goal_r[ai] = gr ? gr[src] : -1.0;
     }
-  } else {
+  } else if (!keep_social) {
     s.alive[vi] = 0;
     s.pos_x[vi] = s.pos_y[vi] = s.pos_z[vi] = s.heading[vi] = s.speed[vi] = s.yaw_rate[vi] = 0.0;
     s.length[vi] = s.width[vi] = s.height[vi] = 0.0;
@@ -281,6 +284,9 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
   d.accel_enable = c.accel_enable; d.via_cap = c.via_cap; d.via_range = c.via_acquisition_range;
   d.via_speed_acc = c.via_speed_accuracy;
   d.ego_frame = c.ego_frame;
+  d.env_list = nullptr;
+  d.n_list = 0;
+  d.a_magic = ((uint64_t)c.n_envs * c.n_agents * c.n_agents < (1ull << 32)) ? (uint32_t)((1ull << 32) / c.n_agents) + 1u : 0u;
   if (c.via_cap < 0 || c.via_cap > SB_MAX_VIAS) return fail(h, SB_EINVAL, "via_cap out of range");
   if (c.via_cap > 0 && !(c.via_acquisition_range >= 0 && c.via_speed_accuracy >= 0))
     return fail(h, SB_EINVAL, "via range / speed accuracy must be >= 0");
@@ -410,6 +416,7 @@ void sb_destroy(SbHandle h) {
   for (void* p : h->allocs) cudaFree(p);
   if (h->pool) sbx_pool_destroy(h->pool);
   if (h->h_bits) cudaFreeHost(h->h_bits);
+  if (h->h_env_list) cudaFreeHost(h->h_env_list);
   std::free(h->h_prev);
   for (auto e : h->xfer_ev) cudaEventDestroy(e);
   for (auto e : h->ev_pool) cudaEventDestroy(e);
@@ -743,7 +750,7 @@ int sb_reset(SbHandle h, const int32_t* env_ids, int32_t n, const SbResetState* 
         init->route_len ? reinterpret_cast<const int32_t*>(dev + off_rl) : nullptr,
         goals ? reinterpret_cast<const double*>(dev + off_gx) : nullptr,
         goals ? reinterpret_cast<const double*>(dev + off_gy) : nullptr,
-        goals ? reinterpret_cast<const double*>(dev + off_gr) : nullptr);
+        goals ? reinterpret_cast<const double*>(dev + off_gr) : nullptr, init->keep_social);
     h->launches++;
     ok = cuda_ok(h, cudaDeviceSynchronize(), "k_reset");
   }
@@ -790,18 +797,40 @@ int sb_step(SbHandle h, const void* dev_actions, void* stream) {
   return cuda_ok(h, cudaGetLastError(), "k_control") ? SB_OK : SB_ECUDA;
 }
 
-int sb_observe(SbHandle h, void* stream) {
+int sb_observe(SbHandle h, void* stream) { return sb_observe_envs(h, nullptr, 0, stream); }
+
+int sb_observe_envs(SbHandle h, const int32_t* env_ids, int32_t n, void* stream) {
   if (!h) return SB_EINVAL;
   if (h->cuda_err) return SB_ECUDA;
   if (!h->have_map) return fail(h, SB_ESTATE, "sb_observe before sb_upload_map");
-  const DCfg& c = h->dc;
-  if (c.lidar_enable && !h->have_rays) return fail(h, SB_ESTATE, "lidar enabled but no ray table uploaded");
-  int na = c.E * c.A;
+  if (h->dc.lidar_enable && !h->have_rays) return fail(h, SB_ESTATE, "lidar enabled but no ray table uploaded");
   cudaStream_t st = (cudaStream_t)stream;
+  DCfg c = h->dc;  // this call's copy: the env list rides in it
+  if (env_ids) {
+    if (n < 1 || n > c.E) return fail(h, SB_EINVAL, "n out of range");
+    for (int i = 0; i < n; ++i)
+      if (env_ids[i] < 0 || env_ids[i] >= c.E) return fail(h, SB_EINVAL, "env id out of range");
+    // staged through a pinned buffer owned by the handle so that the copy is stream-ordered like the kernels
+    if (!h->h_env_list) {
+      if (!cuda_ok(h, cudaHostAlloc(&h->h_env_list, (size_t)c.E * sizeof(int32_t), cudaHostAllocDefault), "cudaHostAlloc(env list)") ||
+          !dev_alloc(h, &h->d_env_list, (size_t)c.E))
+        return SB_ENOMEM;
+    } else {
+      cudaStreamSynchronize(h->env_list_stream);  // the previous list's copy has left the pinned buffer
+    }
+    std::memcpy(h->h_env_list, env_ids, (size_t)n * sizeof(int32_t));
+    if (!cuda_ok(h, cudaMemcpyAsync(h->d_env_list, h->h_env_list, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, st),
+                 "H2D env list"))
+      return SB_ECUDA;
+    h->env_list_stream = st;
+    c.env_list = h->d_env_list;
+    c.n_list = n;
+  }
+  const int na = (env_ids ? n : c.E) * c.A;
   {
     LaunchScope ls(h, SB_K_OBSERVE, st);
     if (h->d_veh_lane) {  // fewer vehicles than neighbour slots: one lane lookup per vehicle, shared by the agents
-      const int nvs = c.E * c.V;
+      const int nvs = (env_ids ? n : c.E) * c.V;
       k_vehicle_lanes<<<(nvs + SB_OBS_WARPS - 1) / SB_OBS_WARPS, SB_OBS_WARPS * 32, 0, st>>>(c, h->dmap, h->st,
                                                                                           h->d_veh_lane);
       h->launches++;

@@ -165,9 +165,9 @@ __device__ __forceinline__ bool ev_boxes_touch(double ax, double ay, double ac, 
 __global__ void __launch_bounds__(SB_EV_WARPS * 32)
 k_events(DCfg c, DMap m, DState s, DEvents ev, DEvOut o, int ticked) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int ai = blockIdx.x * SB_EV_WARPS + warp;
-  if (ai >= c.E * c.A) return;
-  const int e = ai / c.A, a = ai - e * c.A, vi = e * c.V + a;
+  int e, a;
+  if (!d_work_agent(c, blockIdx.x * SB_EV_WARPS + warp, &e, &a)) return;
+  const int ai = e * c.A + a, vi = e * c.V + a;
   const double px = s.pos_x[vi], py = s.pos_y[vi], ph = s.heading[vi];
   const double len = s.length[vi], wid = s.width[vi];
   const double ch = s.cos_h[vi], sh = s.sin_h[vi];

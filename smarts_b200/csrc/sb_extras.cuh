@@ -27,9 +27,9 @@ struct DExtras {
 };
 
 __global__ void __launch_bounds__(128) k_extras(DCfg c, DMap m, DState s, DExtras x) {
-  const int ai = blockIdx.x * blockDim.x + threadIdx.x;
-  if (ai >= c.E * c.A) return;
-  const int e = ai / c.A, a = ai - e * c.A, vi = e * c.V + a;
+  int e, a;
+  if (!d_work_agent(c, blockIdx.x * blockDim.x + threadIdx.x, &e, &a)) return;
+  const int ai = e * c.A + a, vi = e * c.V + a;
   if (c.accel_enable) {
     double hvx, hvy;
     d_radians_to_vec(s.heading[vi], &hvx, &hvy);
@@ -172,8 +172,9 @@ __device__ __forceinline__ void d_to_ego_frame(double* p, double ex, double ey, 
 }
 
 __global__ void __launch_bounds__(SB_EGO_THREADS) k_ego_frame(DCfg c, DState s, DObs o) {
-  const int ai = blockIdx.x;
-  const int e = ai / c.A, a = ai - e * c.A, vi = e * c.V + a;
+  int e, a;
+  if (!d_work_agent(c, blockIdx.x, &e, &a)) return;
+  const int ai = e * c.A + a, vi = e * c.V + a;
   const double ex = s.pos_x[vi], ey = s.pos_y[vi], ez = s.pos_z[vi], eh = s.heading[vi];
   double sn, cs;
   sb_sincos(-eh, &sn, &cs);

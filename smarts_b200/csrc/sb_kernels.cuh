@@ -48,7 +48,21 @@ struct DCfg {
   int32_t events_enable, max_steps, ttc_enable, accel_enable, via_cap, ego_frame;
   uint32_t done_mask;
   double nm_time, nm_dist, via_range, via_speed_acc;
+  // sb_observe_envs: the envs the observation kernels work on (device array; nullptr = every env, in order)
+  const int32_t* env_list;
+  int32_t n_list;
+  uint32_t a_magic;  // floor(2^32 / A) + 1 when idx / A == umulhi(idx, a_magic) for every work index, else 0
 };
+
+// work item idx -> (env, agent) of an observation kernel; false past the last one
+__device__ __forceinline__ bool d_work_agent(const DCfg& c, int idx, int* e, int* a) {
+  const int ne = c.env_list ? c.n_list : c.E;
+  if (idx >= ne * c.A) return false;
+  const int q = c.a_magic ? (int)__umulhi((uint32_t)idx, c.a_magic) : idx / c.A;
+  *a = idx - q * c.A;
+  *e = c.env_list ? c.env_list[q] : q;
+  return true;
+}
 
 // --------------------------------------------------------------------------------- social
 __global__ void k_set_social(DCfg c, DState s, const double* __restrict__ in) {
@@ -274,8 +288,10 @@ __device__ int d_nearest_lane_warp(const DMap& m, double px, double py, double r
 #define SB_AGENT_LENGTH 3.68
 __global__ void __launch_bounds__(SB_OBS_WARPS * 32) k_vehicle_lanes(DCfg c, DMap m, DState s, int32_t* veh_lane) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int vj = blockIdx.x * SB_OBS_WARPS + warp;
-  if (vj >= c.E * c.V) return;
+  const int idx = blockIdx.x * SB_OBS_WARPS + warp;
+  if (idx >= (c.env_list ? c.n_list : c.E) * c.V) return;
+  const int q = idx / c.V;
+  const int vj = (c.env_list ? c.env_list[q] : q) * c.V + (idx - q * c.V);
   int nl = -1;
   if (s.alive[vj]) nl = d_nearest_lane_warp(m, s.pos_x[vj], s.pos_y[vj], SB_AGENT_LENGTH, lane);
   if (lane == 0) veh_lane[vj] = nl;
@@ -286,9 +302,9 @@ __global__ void __launch_bounds__(SB_OBS_WARPS * 32)
 k_observe(DCfg c, DMap m, DState s, DObs o, double* __restrict__ trip_wp, const int32_t* __restrict__ veh_lane) {
   __shared__ WarpPaths wps[SB_OBS_WARPS];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int ai = blockIdx.x * SB_OBS_WARPS + warp;
-  if (ai >= c.E * c.A) return;
-  const int e = ai / c.A, a = ai - e * c.A, vi = e * c.V + a;
+  int e, a;
+  if (!d_work_agent(c, blockIdx.x * SB_OBS_WARPS + warp, &e, &a)) return;
+  const int ai = e * c.A + a, vi = e * c.V + a;
   const double x = s.pos_x[vi], y = s.pos_y[vi], z = s.pos_z[vi], h = s.heading[vi];
 
   // ego lane, sensors.py:277-285 (radius None -> max(10, 2 * 3.2))

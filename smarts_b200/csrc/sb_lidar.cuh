@@ -56,8 +56,9 @@ k_lidar(DCfg c, DMap m, DState s, DObs o, LTable tab, float reach_xy) {
   __shared__ LEntry entries[SB_LIDAR_ENTRIES];
   __shared__ int cnt[SB_LIDAR_CHUNK_GROUPS];
   __shared__ int n_boxes, n_edges;
-  const int ai = blockIdx.x;
-  const int e = ai / c.A, a = ai - e * c.A, vi = e * c.V + a;
+  int e, a;
+  if (!d_work_agent(c, blockIdx.x, &e, &a)) return;
+  const int ai = e * c.A + a, vi = e * c.V + a;
   const double ox = s.pos_x[vi], oy = s.pos_y[vi], oz = s.pos_z[vi] + 1.0;
   if (threadIdx.x == 0) {
     n_boxes = 0;

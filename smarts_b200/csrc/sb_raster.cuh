@@ -404,8 +404,9 @@ k_raster(DCfg c, DMap m, DState s, DObs o, RasterDims g) {
   extern __shared__ __align__(16) unsigned char smem[];
   uint2* lut = reinterpret_cast<uint2*>(smem);
   RasterStage* st = reinterpret_cast<RasterStage*>(smem + SB_RASTER_LUT_BYTES);
-  const int ai = blockIdx.x;
-  const int e = ai / c.A, a = ai - e * c.A, vi = e * c.V + a;
+  int e, a;
+  if (!d_work_agent(c, blockIdx.x, &e, &a)) return;
+  const int ai = e * c.A + a, vi = e * c.V + a;
   const double px = s.pos_x[vi], py = s.pos_y[vi], ch = s.cos_h[vi], sh = s.sin_h[vi];
   // the job record is indexed by image at run time: it lives in shared memory (a per-thread copy
   // would go to local memory -- 144 B x 256 threads x 16 384 CTAs of extra DRAM write traffic)

@@ -18,9 +18,9 @@ struct DTtcOut {
 
 __global__ void __launch_bounds__(SB_TTC_WARPS * 32) k_ttc(DCfg c, DState s, DObs o, DTtcOut out) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int ai = blockIdx.x * SB_TTC_WARPS + warp;
-  if (ai >= c.E * c.A) return;
-  const int e = ai / c.A, a = ai - e * c.A, vi = e * c.V + a;
+  int e, a;
+  if (!d_work_agent(c, blockIdx.x * SB_TTC_WARPS + warp, &e, &a)) return;
+  const int ai = e * c.A + a, vi = e * c.V + a;
   const int P = c.wp_out_paths, L = c.wp_out_len, cap = c.nbr_cap;
   const double ex = s.pos_x[vi], ey = s.pos_y[vi], eh = s.heading[vi], espeed = s.speed[vi];
   const int total_paths = o.wp_n_paths[ai];

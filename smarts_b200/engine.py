@@ -20,7 +20,7 @@ _LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libsmartsb
 
 EXPORTS = [
     "sb_abi_version", "sb_create", "sb_destroy", "sb_upload_map", "sb_upload_lidar_rays", "sb_reset",
-    "sb_set_social", "sb_step", "sb_observe", "sb_step_host", "sb_copy_obs_to_host", "sb_get_obs",
+    "sb_set_social", "sb_step", "sb_observe", "sb_observe_envs", "sb_step_host", "sb_copy_obs_to_host", "sb_get_obs",
     "sb_get_state", "sb_launch_count", "sb_last_error", "sb_set_timing", "sb_collect_timing",
     "sb_set_incremental_host_grids",
 ]
@@ -53,6 +53,7 @@ def load_library(path: Optional[str] = None):
     L.sb_set_social.argtypes = [H, C.c_void_p, C.c_void_p]
     L.sb_step.argtypes = [H, C.c_void_p, C.c_void_p]
     L.sb_observe.argtypes = [H, C.c_void_p]
+    L.sb_observe_envs.argtypes = [H, C.POINTER(C.c_int32), C.c_int32, C.c_void_p]
     L.sb_step_host.argtypes = [H, C.c_void_p, C.c_int64, C.c_void_p]
     L.sb_copy_obs_to_host.argtypes = [H, C.POINTER(_abi.SbObsPtrs)]
     L.sb_get_obs.argtypes = [H, C.POINTER(_abi.SbObsPtrs)]
@@ -68,7 +69,7 @@ def load_library(path: Optional[str] = None):
     L.sb_set_incremental_host_grids.argtypes = [H, C.c_int]
     L.sb_set_incremental_host_grids.restype = C.c_int
     for f in ("sb_create", "sb_upload_map", "sb_upload_lidar_rays", "sb_reset", "sb_set_social", "sb_step",
-              "sb_observe", "sb_step_host", "sb_copy_obs_to_host", "sb_get_obs", "sb_get_state"):
+              "sb_observe", "sb_observe_envs", "sb_step_host", "sb_copy_obs_to_host", "sb_get_obs", "sb_get_state"):
         getattr(L, f).restype = C.c_int
     if L.sb_abi_version() != _abi.SB_ABI_VERSION:
         raise SmartsB200Error("libsmartsb200.so ABI version mismatch; rebuild")
@@ -159,7 +160,8 @@ class Engine:
         return C.c_void_p(self._torch.cuda.current_stream(self.device).cuda_stream)
 
     # -- the step ------------------------------------------------------------------------
-    def reset(self, x, y, heading, speed, route=None, route_len=None, env_ids=None, goal=None, vias=None):
+    def reset(self, x, y, heading, speed, route=None, route_len=None, env_ids=None, goal=None, vias=None,
+              keep_social=False):
         """Place agents (arrays [n, A]); ``route`` int32 [n, A, route_cap] road indices (-1 pad);
         ``goal`` = (x, y, radius) arrays [n, A] of PositionalGoals (radius < 0: EndlessGoal);
         ``vias`` = (count [n, A], lane [n, A, via_cap], x, y, hit_distance, required_speed) of Mission.via."""
@@ -168,6 +170,7 @@ class Engine:
         dp = lambda a: a.ctypes.data_as(C.POINTER(C.c_double))  # noqa: E731
         ip = lambda a: a.ctypes.data_as(C.POINTER(C.c_int32))  # noqa: E731
         rs = _abi.SbResetState()
+        rs.keep_social = int(keep_social)
         rs.agent_x, rs.agent_y, rs.agent_heading, rs.agent_speed = dp(x), dp(y), dp(heading), dp(speed)
         if route is not None:
             route = np.ascontiguousarray(route, np.int32)
@@ -203,8 +206,15 @@ class Engine:
         assert actions.is_cuda and actions.is_contiguous()
         self._check(self._lib.sb_step(self._h, C.c_void_p(actions.data_ptr()), self._stream_ptr()), "sb_step")
 
-    def observe(self):
-        self._check(self._lib.sb_observe(self._h, self._stream_ptr()), "sb_observe")
+    def observe(self, env_ids=None):
+        """Sensors.observe for every agent, or for the agents of ``env_ids`` only (the reset observation of an
+        auto-reset: the other envs' sensor state and observation buffers stay untouched)."""
+        if env_ids is None:
+            self._check(self._lib.sb_observe(self._h, self._stream_ptr()), "sb_observe")
+            return
+        ids = np.ascontiguousarray(env_ids, np.int32)
+        self._check(self._lib.sb_observe_envs(self._h, ids.ctypes.data_as(C.POINTER(C.c_int32)), len(ids),
+                                              self._stream_ptr()), "sb_observe_envs")
 
     def step_host(self, actions: np.ndarray, social: Optional[np.ndarray]):
         """The reference-facing call with HOST buffers: H2D copies + set_social + step + observe + sync."""

@@ -16,6 +16,8 @@ CPU fallback: constructing either class without the CUDA library or a GPU raises
 """
 from __future__ import annotations
 
+import copy
+import dataclasses
 import math
 import os
 from dataclasses import dataclass, field
@@ -114,6 +116,11 @@ class BatchedHiWayEnv:
             raise ValueError("agent_specs is empty")
         self._agent_specs = dict(agent_specs)
         self.agent_ids = list(agent_specs.keys())
+        # ParallelEnv gives every env process its own copy of the AgentSpecs (parallel_env.py:96-127), so adapters
+        # that remember something between observe and act (the ego-centric pair keeps the last ego pose) never mix
+        # envs up.  Same here: one deep copy of the four adapters per env (the agent builder / params are shared).
+        self._env_specs: List[Dict[str, AgentSpec]] = [dict(agent_specs)] if int(n_envs) == 1 else [
+            {aid: self._own_adapters(s) for aid, s in agent_specs.items()} for _ in range(int(n_envs))]
         itfs = [s.interface for s in agent_specs.values()]
         if any(i is None for i in itfs):
             raise ValueError("every AgentSpec needs an interface")
@@ -149,6 +156,12 @@ class BatchedHiWayEnv:
         self._global_tick = 0
         self._done_agents = np.zeros((self.E, self.A), bool)
         self._host: Dict[str, np.ndarray] = {}
+
+    @staticmethod
+    def _own_adapters(spec: AgentSpec) -> AgentSpec:
+        memo: Dict[int, Any] = {}  # shared: bound methods of one object stay bound to one (new) object
+        return dataclasses.replace(spec, **{k: copy.deepcopy(getattr(spec, k), memo) for k in
+                                            ("observation_adapter", "action_adapter", "reward_adapter", "info_adapter")})
 
     # -- gym-ish surface -------------------------------------------------------------------
     @property
@@ -237,11 +250,15 @@ class BatchedHiWayEnv:
         return np.ascontiguousarray(s, np.float64)
 
     def _reset_envs(self, env_ids: Optional[np.ndarray]):
+        """SMARTS.reset of the listed envs (None: all).  An auto-reset (env_ids given) leaves the envs' social
+        slots as the last injection wrote them: the recorded traffic is driven by the global tick and keeps
+        running, so the reset observation still sees it."""
         s = self._start
         sel = slice(None) if env_ids is None else env_ids
         self.engine.reset(s["x"][sel], s["y"][sel], s["h"][sel], s["v"][sel], s["route"][sel], s["rlen"][sel],
                           env_ids=env_ids, goal=tuple(g[sel] for g in s["goal"]),
-                          vias=None if s["vias"] is None else tuple(q[sel] for q in s["vias"]))
+                          vias=None if s["vias"] is None else tuple(q[sel] for q in s["vias"]),
+                          keep_social=env_ids is not None)
         self._tick[sel] = 0
         self._done_agents[sel] = False
 
@@ -274,7 +291,11 @@ class BatchedHiWayEnv:
         eng.observe()
         self._global_tick += 1
         self._tick += 1
-        return eng.obs()
+        obs = eng.obs()
+        if "ev_done" in obs:  # done agents leave the simulation after this observation (agent_manager teardown):
+            alive = eng.state()["alive"]  # a device-side op on the zero-copy views, no synchronisation
+            alive[:, :self.A] &= (obs["ev_done"] == 0).to(alive.dtype)
+        return obs
 
     def auto_reset_done_envs(self) -> np.ndarray:
         """Reset every env whose agents are all done (parallel_env.py:300-326); returns their ids."""
@@ -285,7 +306,7 @@ class BatchedHiWayEnv:
         ids = np.nonzero(d.all(axis=1))[0].astype(np.int32)
         if len(ids) and self._auto_reset:
             self._reset_envs(ids)
-            self.engine.observe()
+            self.engine.observe(ids)  # only the reset envs: the others' sensor state and buffers stay as they are
         return ids
 
     # -- StdObs: the dense, batched observation of format_obs.py, on the device -------------------
@@ -472,8 +493,11 @@ class BatchedHiWayEnv:
     def reset(self) -> List[Dict[str, Any]]:
         self.reset_tensor()
         self._fetch()
-        return [{aid: self._agent_specs[aid].observation_adapter(ob) for aid, ob in self._env_observations(e).items()}
+        return [{aid: self._spec(e, aid).observation_adapter(ob) for aid, ob in self._env_observations(e).items()}
                 for e in range(self.E)]
+
+    def _spec(self, e: int, aid: str) -> AgentSpec:
+        return self._env_specs[e if self.E > 1 else 0][aid]
 
     def step(self, actions: Sequence[Dict[str, Any]]):
         """actions: one ``{agent_id: action}`` dict per env.  Returns (observations, rewards, dones, infos),
@@ -493,7 +517,7 @@ class BatchedHiWayEnv:
             assert isinstance(env_act, dict) and all(isinstance(k, str) for k in env_act), "Expected Dict[str, any]"
             for a, aid in enumerate(self.agent_ids):
                 if aid in env_act:
-                    flat.append(self._agent_specs[aid].action_adapter(env_act[aid]))
+                    flat.append(self._spec(e, aid).action_adapter(env_act[aid]))
                 elif self._done_agents[e, a] or default is not None:
                     flat.append(default if default is not None else self._neutral_action())
                 else:
@@ -512,7 +536,7 @@ class BatchedHiWayEnv:
             for a, aid in enumerate(self.agent_ids):
                 if self._done_agents[e, a]:
                     continue
-                spec = self._agent_specs[aid]
+                spec = self._spec(e, aid)
                 ob = self._observation(e, a)
                 r = float(self._host["ev_reward"][e, a])
                 info = {"score": float(self._host["ev_distance"][e, a]), "env_obs": ob}
@@ -523,19 +547,14 @@ class BatchedHiWayEnv:
             self._done_agents[e] |= newly[e]
             done_e["__all__"] = bool(self._done_agents[e].all())
             obs_l.append(obs_e); rew_l.append(rew_e); done_l.append(done_e); info_l.append(info_e)
-        # done agents leave the simulation (vehicle removed, agent_manager teardown)
-        if newly.any():
-            alive = self.engine.state()["alive"]
-            idx = np.argwhere(newly)
-            dev = self.engine.device
-            alive[self._torch.as_tensor(idx[:, 0]).to(dev), self._torch.as_tensor(idx[:, 1]).to(dev)] = 0
+        # (done agents left the simulation inside step_tensor: vehicle removed, agent_manager teardown)
         finished = np.nonzero(self._done_agents.all(axis=1))[0].astype(np.int32)
         if len(finished) and self._auto_reset:
             self._reset_envs(finished)
-            self.engine.observe()
+            self.engine.observe(finished)  # the reset envs only (ParallelEnv envs are independent)
             self._fetch()
             for e in finished:
-                obs_l[e] = {aid: self._agent_specs[aid].observation_adapter(ob)
+                obs_l[e] = {aid: self._spec(int(e), aid).observation_adapter(ob)
                             for aid, ob in self._env_observations(int(e)).items()}
         return obs_l, rew_l, done_l, info_l
 

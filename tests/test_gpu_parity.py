@@ -355,6 +355,54 @@ def test_events_rewards_dones_match_oracle(wp):
         assert seen & bit, f"rollout never raised event bit {bit}"
 
 
+def test_partial_reset_observes_only_the_reset_envs():
+    """sb_observe_envs: after a partial reset only the reset envs are observed (ParallelEnv envs are independent,
+    parallel_env.py:96-127).  CUDA == oracle bit for bit through the reset, and every env that was NOT reset holds
+    exactly what a run without any reset holds -- stateful sensors included (driven path / not_moving window, trip
+    meter, accelerometer history, vias' consumed set, step counters) and the ev_* outputs of the last tick."""
+    import torch
+    rm = load_map("4lane")
+    E, A, M = 8, 4, 10
+    cfg = make_cfg(E=E, A=A, M=M, nbr=True, wp=True, lidar=True, wall=1.5, ogm=(64, 64, 0.4), dagm=(64, 64, 0.4),
+                   route_cap=16, events=True, max_episode_steps=0, not_moving_time=1.0, not_moving_distance=0.5,
+                   ttc=True, accel=True, ego_frame=True)
+    x, y, h, v, route, rlen = scenario_gen.agent_starts(rm, E, MISSIONS_4LANE, cfg.route_cap, 61, jitter=30.0, speed=6.0)
+    traffic = scenario_gen.SocialTraffic(rm, E, M, 62)
+    ids = np.array([1, 4, 6], np.int32)
+    keep = np.setdiff1d(np.arange(E), ids)
+    runs = {}
+    for name in ("reset", "plain"):
+        eng, ora = engine(rm, cfg), oracle_world(rm, cfg, threads=8)
+        for w in (eng, ora):
+            w.reset(x, y, h, v, route, rlen)
+            w.observe()
+        rng = np.random.default_rng(63)
+        hist = []
+        for t in range(24):
+            act = rng.integers(0, 4, (E, A)).astype(np.int32)
+            act[:, 2] = _abi.SB_LANE_SLOW_DOWN  # agent 2 stops: not_moving depends on the driven-path window
+            soc = traffic.states(t)
+            eng.set_social(torch.from_numpy(soc).cuda()); ora.set_social(soc)
+            eng.step(torch.from_numpy(act).cuda()); ora.step(act)
+            eng.observe(); ora.observe()
+            if name == "reset" and t in (7, 15):
+                for w in (eng, ora):
+                    w.reset(x[ids], y[ids], h[ids], v[ids], route[ids], rlen[ids], env_ids=ids, keep_social=True)
+                    w.observe(ids)
+            got, want = eng.obs_numpy(), ora.obs()
+            assert_same(got, want)
+            assert_same(eng.state_numpy(), ora.state())
+            hist.append(got)
+        runs[name] = hist
+        eng.close()
+    for t, (a, b) in enumerate(zip(runs["reset"], runs["plain"])):
+        for k in a:
+            assert np.array_equal(a[k][keep], b[k][keep], equal_nan=a[k].dtype.kind == "f"), (t, k)
+    last = runs["reset"][-1]
+    assert last["ev_steps"][ids].max() == 24 - 16 and last["ev_steps"][keep].min() == 24
+    assert (last["ev_events"][keep][:, 2] & _abi.SB_EV_NOT_MOVING).all()
+
+
 def test_events_off_road_and_wrong_way_poses():
     """Hand-placed poses: on the lane, on the shoulder, off the road, facing against the lane."""
     rm = load_map("4lane")

@@ -222,6 +222,76 @@ def test_batched_env_auto_reset_and_tensor_path_agree():
 
 
 @pytest.mark.gpu
+def test_staggered_auto_reset_leaves_running_envs_alone():
+    """Envs that finish on different ticks: an env that is auto-reset must not disturb the others (in the reference
+    every ParallelEnv env is its own process).  Env 1 stands still and is ended by `not_moving` every few ticks
+    while envs 0 and 2 drive on; their observations equal those of a run without auto-reset."""
+    rm = load_map("4lane")
+    from smarts_b200.agent_interface import EventConfiguration
+    itf = AgentInterface.from_type(AgentType.LanerWithSpeed, neighborhood_vehicles=True,
+                                   done_criteria=DoneCriteria(not_moving=True, off_route=False),
+                                   event_configuration=EventConfiguration(not_moving_time=0.5, not_moving_distance=0.5))
+    E, M = 3, 6
+    sc = Scenario(rm, MISSIONS, scenario_gen.SocialTraffic(rm, E, M, 17), n_social=M)
+    hist = {}
+    for auto in (True, False):
+        env = BatchedHiWayEnv(sc, _specs(itf), n_envs=E, start_jitter=15.0, seed=9, auto_reset=auto)
+        obs = env.reset()
+        rows, resets = [], 0
+        for t in range(20):
+            acts = [{i: ((0.0, 0) if e == 1 else (9.0, 0)) for i in MISSIONS} for e in range(E)]
+            obs, rew, dones, infos = env.step([{i: a for i, a in acts[e].items() if i in obs[e]} for e in range(E)])
+            resets += int(dones[1]["__all__"])
+            row = {}
+            for e in (0, 2):
+                for i in infos[e]:
+                    o = infos[e][i]["env_obs"]
+                    eg = o.ego_vehicle_state
+                    row[e, i] = (eg.position.copy(), o.distance_travelled, o.events, eg.linear_acceleration.copy(),
+                                 eg.linear_jerk.copy(), [n.id for n in o.neighborhood_vehicle_states], rew[e][i])
+            rows.append(row)
+        hist[auto] = rows
+        if auto:
+            assert resets >= 2          # env 1 was ended by not_moving and restarted more than once
+            assert any(n.id.startswith("social") for o in obs[1].values() for n in o.neighborhood_vehicle_states), \
+                "the reset observation still sees the injected traffic"
+        env.close()
+    for t, (a, b) in enumerate(zip(hist[True], hist[False])):
+        assert a.keys() == b.keys() and len(a) == 8
+        for key in a:
+            for u, w in zip(a[key], b[key]):
+                assert np.array_equal(u, w) if isinstance(u, np.ndarray) else u == w, (t, key)
+
+
+@pytest.mark.gpu
+def test_ego_centric_adapters_are_per_env():
+    """get_egocentric_adapters keeps the last observation between observe and act (ego_centric_adapters.py:280-299);
+    with E > 1 every env must convert its ego-frame trajectory with ITS OWN ego pose."""
+    from smarts_b200 import ego_centric
+    rm = load_map("4lane")
+    itf = AgentInterface.from_type(AgentType.Tracker)
+    oa, aa = ego_centric.get_egocentric_adapters(ActionSpaceType.Trajectory)
+    spec = AgentSpec(interface=itf, observation_adapter=oa, action_adapter=aa)
+    E = 3
+    env = BatchedHiWayEnv(Scenario(rm, {"A0": MISSIONS["A0"]}, None, 0), {"A0": spec}, n_envs=E, start_jitter=40.0, seed=3)
+    obs = env.reset()
+    assert all(np.allclose(o["A0"].ego_vehicle_state.position, 0) for o in obs)      # ego frame
+    world = env._host_state
+    ego_traj = [np.array([2.0, 4.0, 6.0]), np.zeros(3), np.zeros(3), np.full(3, 8.0)]  # straight ahead, ego frame
+    xs = []
+    for e in range(E):
+        tx, ty, th, tv = env._spec(e, "A0").action_adapter(ego_traj)
+        hd = world["heading"][e, 0]
+        pos = np.array([world["pos_x"][e, 0], world["pos_y"][e, 0], world["pos_z"][e, 0]])
+        ex, ey = ego_centric.world_position_from_ego_frame([2.0, 0.0, 0.0], pos, hd)[:2]   # with env e's own pose
+        assert np.allclose([tx[0], ty[0]], [ex, ey], atol=1e-9) and np.allclose(th, hd)
+        xs.append((tx[0], ty[0]))
+    assert len({(round(a, 3), round(b, 3)) for a, b in xs}) == E                          # the envs differ
+    obs, _, _, _ = env.step([{"A0": ego_traj}] * E)
+    env.close()
+
+
+@pytest.mark.gpu
 def test_std_obs_layout_matches_format_obs():
     """StdObs keys / dtypes / trailing shapes (format_obs.py:45-197, :313-376) on the device, and agreement
     with the per-agent Observation objects of the dict path."""
