@@ -148,4 +148,27 @@ SB_HD double sb_atan2(double y, double x) {
   return 0.0;
 }
 
+/* The simulation clock.  SMARTS advances it as  t <- round(t + dt, d)  with d the number of decimals of dt
+ * (smarts.py:262, utils/math.py:553-569): the value after k ticks is the binary64 nearest to the decimal k * dt,
+ * which is the correctly rounded quotient below (k * dt_num and dt_den = 10^d are exact).  Time-window tests
+ * (DrivenPathSensor.distance_travelled, sensors.py:866-871) compare such clock values after a floating-point
+ * subtraction, so they must be reproduced to the bit, not approximated by tick counts. */
+SB_HD double sb_clock(long long ticks, long long dt_num, double dt_den) { return (double)(ticks * dt_num) / dt_den; }
+
+/* d of the above for a given dt: the digits after the point in its shortest decimal form (<= 12). */
+static inline int sb_clock_decimals(double dt, long long *dt_num, double *dt_den) {
+  double den = 1.0;
+  for (int d = 0; d <= 12; ++d, den *= 10.0) {
+    const double num = rint(dt * den);
+    if (num / den == dt) {
+      *dt_num = (long long)num;
+      *dt_den = den;
+      return d;
+    }
+  }
+  *dt_num = (long long)rint(dt * 1e12);
+  *dt_den = 1e12;
+  return 12;
+}
+
 #endif /* SB_DETMATH_H */

@@ -334,8 +334,8 @@ void observe_neighbors(World& w, int e, int a) {
 }
 
 // waypoint_paths[0][0] feeds TripMeterSensor.append_waypoint_if_new (sensors.py:340-341)
-void stash_trip_waypoint(World& w, int ai, const PathSet& ps) {
-  double* tw = &w.trip_wp[(size_t)ai * 4];
+void stash_trip_waypoint(World& w, int ai, const PathSet& ps, int slot = 0) {
+  double* tw = &w.trip_wp[(size_t)ai * 8 + slot * 4];
   if (ps.n == 0 || ps.len[0] == 0) {
     tw[3] = -1.0;
     return;
@@ -714,17 +714,20 @@ void observe_events(World& w, int e, int a, bool ticked) {
   w.steps[ai] = steps;
   w.ev_steps[ai] = steps;
   {  // TripMeterSensor, sensors.py:880-947
-    const double* tw = &w.trip_wp[(size_t)ai * 4];
+    const double* tw = &w.trip_wp[(size_t)ai * 8];
     const int tlane = (int)tw[3];
     double dist = w.trip_dist[ai], last = w.trip_last[ai];
-    if (tlane >= 0) {
-      if (!w.trip_init[ai]) {
-        w.trip_init[ai] = 1;
+    if (!w.trip_init[ai]) {  // TripMeterSensor.__init__ (sensors.py:885-898): its own unrouted query
+      w.trip_init[ai] = 1;
+      const double* cw = w.cfg.wp_enable ? tw + 4 : tw;
+      if ((int)cw[3] >= 0) {
         w.trip_has[ai] = 1;
-        w.trip_x[ai] = tw[0];
-        w.trip_y[ai] = tw[1];
-        w.trip_h[ai] = tw[2];
+        w.trip_x[ai] = cw[0];
+        w.trip_y[ai] = cw[1];
+        w.trip_h[ai] = cw[2];
       }
+    }
+    if (tlane >= 0) {
       last = dist;
       const bool fixed_route = w.goal_r[ai] >= 0.0;
       const bool count = !fixed_route || in_route(route, route_len, mp.lane_road[tlane]);
@@ -749,8 +752,6 @@ void observe_events(World& w, int e, int a, bool ticked) {
           w.trip_h[ai] = tw[2];
         }
       }
-    } else if (!w.trip_init[ai]) {
-      w.trip_init[ai] = 1;
     }
     w.trip_dist[ai] = dist;
     w.trip_last[ai] = last;
@@ -769,8 +770,14 @@ void observe_events(World& w, int e, int a, bool ticked) {
     w.path_n[ai] = n + 1;
     w.last_px[ai] = px;
     w.last_py[ai] = py;
-    if (!((double)steps * w.cfg.dt < w.cfg.not_moving_time)) {
-      int back = std::min(w.ring - 1, n);
+    // _vehicle_is_not_moving (sensors.py:509-524) over the entries whose timestamp >= now - not_moving_time
+    // (sensors.py:866-871); entry j was recorded at clock value sb_clock(j): the comparison is made on those
+    // binary64 values exactly as the reference makes it (0.1-second clocks do not subtract exactly)
+    const double now = sb_clock(steps, w.dt_num, w.dt_den);
+    if (!(now < w.cfg.not_moving_time)) {
+      const double threshold = now - w.cfg.not_moving_time;
+      int back = std::min(std::min(w.ring - 1, n), steps);
+      while (back > 0 && !(sb_clock(steps - back, w.dt_num, w.dt_den) >= threshold)) --back;
       double moved = cum - ring[(n - back) % w.ring];
       if (moved < w.cfg.not_moving_distance) bits |= SB_EV_NOT_MOVING;
     }
@@ -1082,10 +1089,13 @@ void observe_agent(World& w, int e, int a) {
   w.ego_lane[ai] = nearest_lane(w.map, w.pos_x[vi], w.pos_y[vi], std::max(10.0, 2 * 3.2));
   if (w.cfg.nbr_enable) observe_neighbors(w, e, a);
   if (w.cfg.wp_enable) observe_waypoints(w, e, a);
-  if (!w.cfg.wp_enable && w.cfg.events_enable) {  // sensors.py:289-295
+  if (w.cfg.events_enable && (!w.cfg.wp_enable || !w.trip_init[ai])) {
+    // the lookahead-1 query within the vehicle's length, no route: every observation of an agent without a
+    // waypoint sensor (sensors.py:289-295), and TripMeterSensor.__init__ of every agent (sensors.py:885-898;
+    // slot 1: the first observation after a reset stands at the pose the vehicle was created with)
     static thread_local PathSet ps;
     waypoint_paths(w.map, w.pos_x[vi], w.pos_y[vi], w.heading[vi], 1, w.length[vi], nullptr, -1, &ps);
-    stash_trip_waypoint(w, ai, ps);
+    stash_trip_waypoint(w, ai, ps, w.cfg.wp_enable ? 1 : 0);
   }
   if (w.cfg.ttc_enable) observe_ttc(w, e, a);
   if (w.cfg.accel_enable) observe_accelerometer(w, e, a);
@@ -1188,7 +1198,8 @@ void* or_create(const SbConfig* cfg, const SbMap* m, const double* base_rays, in
   }
   if (cfg->events_enable) {
     double win = std::floor(cfg->not_moving_time / cfg->dt + 1e-9);
-    w->ring = (int)(win < SB_DRIVEN_PATH_MAX - 1 ? win : SB_DRIVEN_PATH_MAX - 1) + 1;
+    w->ring = (int)(win + 1 < SB_DRIVEN_PATH_MAX - 1 ? win + 1 : SB_DRIVEN_PATH_MAX - 1) + 1;  // one spare interval
+    sb_clock_decimals(cfg->dt, &w->dt_num, &w->dt_den);
     w->trip_init.assign(na, 0);
     w->trip_has.assign(na, 0);
     w->ev_done.assign(na, 0);
@@ -1196,7 +1207,7 @@ void* or_create(const SbConfig* cfg, const SbMap* m, const double* base_rays, in
                     &w->goal_x, &w->goal_y, &w->ev_distance, &w->ev_reward})
       v->assign(na, 0.0);
     w->goal_r.assign(na, -1.0);
-    w->trip_wp.assign(na * 4, 0.0);
+    w->trip_wp.assign(na * 8, 0.0);
     w->path_cum.assign(na * w->ring, 0.0);
     for (auto* v : {&w->steps, &w->path_n, &w->ev_n_collisions, &w->ev_collidee, &w->ev_steps}) v->assign(na, 0);
     w->ev_events.assign(na, 0);
@@ -1262,7 +1273,8 @@ void or_reset(void* h, const int32_t* env_ids, int n, const SbResetState* init) 
       if (w.cfg.events_enable) {
         w.trip_init[ai] = w.trip_has[ai] = 0;
         w.trip_x[ai] = w.trip_y[ai] = w.trip_h[ai] = w.trip_dist[ai] = w.trip_last[ai] = 0.0;
-        w.trip_wp[(size_t)ai * 4 + 3] = -1.0;
+        w.trip_wp[(size_t)ai * 8 + 3] = -1.0;
+        w.trip_wp[(size_t)ai * 8 + 7] = -1.0;
         w.steps[ai] = w.path_n[ai] = 0;
         w.last_px[ai] = w.last_py[ai] = 0.0;
         const bool goals = init->goal_x && init->goal_y && init->goal_radius;

@@ -98,6 +98,8 @@ struct Waypoint {
 struct World {
   SbConfig cfg;
   Map map;
+  long long dt_num = 1;  // the simulation clock after k ticks is sb_clock(k, dt_num, dt_den) (include/sb_detmath.h)
+  double dt_den = 10.0;
   std::vector<double> rays;  // [R,3]
   std::vector<SbRayRec> ray_rec;      // include/sb_lidar_table.h
   std::vector<double> ray_group_u;    // [groups,2]

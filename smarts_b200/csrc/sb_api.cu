@@ -165,7 +165,8 @@ __global__ void k_reset(DCfg c, DState s, DEvents ev, const int32_t* env_ids, in
       ev.trip_init[ai] = 0;
       ev.trip_has[ai] = 0;
       ev.trip_x[ai] = ev.trip_y[ai] = ev.trip_h[ai] = ev.trip_dist[ai] = ev.trip_last[ai] = 0.0;
-      ev.trip_wp[(size_t)ai * 4 + 3] = -1.0;
+      ev.trip_wp[(size_t)ai * 8 + 3] = -1.0;
+      ev.trip_wp[(size_t)ai * 8 + 7] = -1.0;
       ev.steps[ai] = 0;
       ev.path_n[ai] = 0;
       ev.last_px[ai] = ev.last_py[ai] = 0.0;
@@ -333,10 +334,11 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
     // DrivenPathSensor keeps 500 entries (sensors.py:838-840); the not-moving window needs
     // floor(not_moving_time / dt) intervals of them
     double win = floor(c.not_moving_time / c.dt + 1e-9);
-    v.ring = (int)(win < SB_DRIVEN_PATH_MAX - 1 ? win : SB_DRIVEN_PATH_MAX - 1) + 1;
+    v.ring = (int)(win + 1 < SB_DRIVEN_PATH_MAX - 1 ? win + 1 : SB_DRIVEN_PATH_MAX - 1) + 1;  // one spare interval
+    sb_clock_decimals(c.dt, &v.dt_num, &v.dt_den);
     ok = dev_alloc(h, &v.trip_init, na) && dev_alloc(h, &v.trip_has, na) && dev_alloc(h, &v.trip_x, na) &&
          dev_alloc(h, &v.trip_y, na) && dev_alloc(h, &v.trip_h, na) && dev_alloc(h, &v.trip_dist, na) &&
-         dev_alloc(h, &v.trip_last, na) && dev_alloc(h, &v.trip_wp, na * 4) && dev_alloc(h, &v.steps, na) &&
+         dev_alloc(h, &v.trip_last, na) && dev_alloc(h, &v.trip_wp, na * 8) && dev_alloc(h, &v.steps, na) &&
          dev_alloc(h, &v.path_n, na) && dev_alloc(h, &v.path_cum, na * v.ring) && dev_alloc(h, &v.last_px, na) &&
          dev_alloc(h, &v.last_py, na) && dev_alloc(h, &v.goal_x, na) && dev_alloc(h, &v.goal_y, na) &&
          dev_alloc(h, &v.goal_r, na) && dev_alloc(h, &q.events, na) && dev_alloc(h, &q.done, na) &&
@@ -836,7 +838,7 @@ int sb_observe_envs(SbHandle h, const int32_t* env_ids, int32_t n, void* stream)
       h->launches++;
     }
     k_observe<<<(na + SB_OBS_WARPS - 1) / SB_OBS_WARPS, SB_OBS_WARPS * 32, 0, st>>>(c, h->dmap, h->st, h->ob,
-                                                                                    h->ev.trip_wp, h->d_veh_lane);
+                                                                                    h->ev.trip_wp, h->ev.trip_init, h->d_veh_lane);
   }
   if (c.ttc_enable) {
     LaunchScope ls(h, SB_K_TTC, st);

@@ -19,12 +19,16 @@ struct DEvents {
   // per agent [E*A]
   uint8_t *trip_init, *trip_has;
   double *trip_x, *trip_y, *trip_h, *trip_dist, *trip_last;
-  double* trip_wp;  // [E*A,4] x, y, heading, lane (-1: no waypoint) -- written by k_observe
+  // [E*A,2,4] x, y, heading, lane (-1: no waypoint), written by k_observe: [0] waypoint_paths[0][0] of this
+  // observation, [1] the waypoint of TripMeterSensor.__init__'s own unrouted query (first observation after a reset)
+  double* trip_wp;
   int32_t *steps, *path_n;
   double *path_cum;  // [E*A, ring] cumulative driven distance, ring buffer
   double *last_px, *last_py;
   double *goal_x, *goal_y, *goal_r;
-  int32_t ring;      // entries in the ring = not-moving window steps + 1 (<= SB_DRIVEN_PATH_MAX)
+  int32_t ring;      // entries in the ring = not-moving window steps + 2 (<= SB_DRIVEN_PATH_MAX)
+  long long dt_num;  // the simulation clock after k ticks is sb_clock(k, dt_num, dt_den) (include/sb_detmath.h)
+  double dt_den;
 };
 
 struct DEvOut {
@@ -183,18 +187,21 @@ k_events(DCfg c, DMap m, DState s, DEvents ev, DEvOut o, int ticked) {
     steps = ev.steps[ai] + (ticked ? 1 : 0);
     ev.steps[ai] = steps;
     o.steps[ai] = steps;
-    const double* tw = ev.trip_wp + (size_t)ai * 4;
+    const double* tw = ev.trip_wp + (size_t)ai * 8;
     const int tlane = (int)tw[3];
     double dist = ev.trip_dist[ai], last = ev.trip_last[ai];
+    if (!ev.trip_init[ai]) {  // TripMeterSensor.__init__ (sensors.py:885-898): its own unrouted lookahead-1 query
+      ev.trip_init[ai] = 1;
+      const double* cw = c.wp_enable ? tw + 4 : tw;
+      if ((int)cw[3] >= 0) {
+        ev.trip_has[ai] = 1;
+        ev.trip_x[ai] = cw[0];
+        ev.trip_y[ai] = cw[1];
+        ev.trip_h[ai] = cw[2];
+      }
+    }
     if (tlane >= 0) {
       const double wx = tw[0], wy = tw[1], wh = tw[2];
-      if (!ev.trip_init[ai]) {  // TripMeterSensor.__init__, sensors.py:885-898
-        ev.trip_init[ai] = 1;
-        ev.trip_has[ai] = 1;
-        ev.trip_x[ai] = wx;
-        ev.trip_y[ai] = wy;
-        ev.trip_h[ai] = wh;
-      }
       // append_waypoint_if_new, sensors.py:900-930
       last = dist;
       const bool fixed_route = ev.goal_r[ai] >= 0.0;
@@ -221,8 +228,6 @@ k_events(DCfg c, DMap m, DState s, DEvents ev, DEvOut o, int ticked) {
           ev.trip_h[ai] = wh;
         }
       }
-    } else if (!ev.trip_init[ai]) {
-      ev.trip_init[ai] = 1;
     }
     ev.trip_dist[ai] = dist;
     ev.trip_last[ai] = last;
@@ -241,10 +246,15 @@ k_events(DCfg c, DMap m, DState s, DEvents ev, DEvOut o, int ticked) {
     ev.path_n[ai] = n + 1;
     ev.last_px[ai] = px;
     ev.last_py[ai] = py;
-    // _vehicle_is_not_moving, sensors.py:509-524: window of the last not_moving_time seconds
-    if (!((double)steps * c.dt < c.nm_time)) {
-      int back = ev.ring - 1;
-      if (back > n) back = n;
+    // _vehicle_is_not_moving (sensors.py:509-524) over the entries whose timestamp >= now - not_moving_time
+    // (sensors.py:866-871).  Entry j carries the clock value sb_clock(j); the comparison is made on those binary64
+    // values as the reference makes it (a 0.1-second clock does not subtract exactly, so the window is one entry
+    // shorter on some ticks than not_moving_time / dt)
+    const double now = sb_clock(steps, ev.dt_num, ev.dt_den);
+    if (!(now < c.nm_time)) {
+      const double threshold = now - c.nm_time;
+      int back = min(min(ev.ring - 1, n), steps);
+      while (back > 0 && !(sb_clock(steps - back, ev.dt_num, ev.dt_den) >= threshold)) --back;
       nm_dist = cum - ring[(n - back) % ev.ring];
       nm_valid = true;
     }

@@ -299,7 +299,8 @@ __global__ void __launch_bounds__(SB_OBS_WARPS * 32) k_vehicle_lanes(DCfg c, DMa
 
 
 __global__ void __launch_bounds__(SB_OBS_WARPS * 32)
-k_observe(DCfg c, DMap m, DState s, DObs o, double* __restrict__ trip_wp, const int32_t* __restrict__ veh_lane) {
+k_observe(DCfg c, DMap m, DState s, DObs o, double* __restrict__ trip_wp, const uint8_t* __restrict__ trip_init,
+          const int32_t* __restrict__ veh_lane) {
   __shared__ WarpPaths wps[SB_OBS_WARPS];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   int e, a;
@@ -374,14 +375,16 @@ k_observe(DCfg c, DMap m, DState s, DObs o, double* __restrict__ trip_wp, const 
     }
   }
 
-  if (!c.wp_enable && c.events_enable) {
-    // TripMeterSensor without a waypoints sensor (sensors.py:289-295): lookahead 1, within the
-    // vehicle's length, no route; only path 0's first waypoint is needed.
+  if (c.events_enable && (!c.wp_enable || !trip_init[ai])) {
+    // The lookahead-1 query within the vehicle's length, no route; only path 0's first waypoint is needed.
+    // Every observation of an agent without a waypoint sensor (sensors.py:289-295), and TripMeterSensor.__init__
+    // of every agent (sensors.py:885-898; slot 1: the first observation after a reset stands at the pose the
+    // vehicle was created with).
     WarpPaths* wp = &wps[warp];
     wp_waypoint_paths(m, x, y, h, 1, s.length[vi], nullptr, -1, wp, lane);
     __syncwarp();
     const int n = wp->n;
-    double* tw = trip_wp + (size_t)ai * 4;
+    double* tw = trip_wp + (size_t)ai * 8 + (c.wp_enable ? 4 : 0);
     if (n == 0 && lane == 0) tw[3] = -1.0;
     const unsigned first = __ballot_sync(SB_FULL_MASK, lane < n && wp_rank(m, wp, lane) == 0);
     if (first) {
@@ -408,7 +411,7 @@ k_observe(DCfg c, DMap m, DState s, DObs o, double* __restrict__ trip_wp, const 
     if (lane == 0) {
       o.wp_n_paths[ai] = wp->total;
       if (wp->overflow) s.status[ai] |= SB_STATUS_PATH_OVERFLOW;
-      if (c.events_enable && n == 0) trip_wp[(size_t)ai * 4 + 3] = -1.0;
+      if (c.events_enable && n == 0) trip_wp[(size_t)ai * 8 + 3] = -1.0;
     }
     // each path is interpolated by the whole warp (wp_equally_spaced_warp); lane k ranks path k
     const int my_rank = lane < n ? wp_rank(m, wp, lane) : 0x7fffffff;
@@ -421,7 +424,7 @@ k_observe(DCfg c, DMap m, DState s, DObs o, double* __restrict__ trip_wp, const 
           m, wp->lp[p], wp->len[p], x, y, L,
           [&](int i, const DWaypoint& w) {
             if (stash && i == 0) {
-              double* tw = trip_wp + (size_t)ai * 4;
+              double* tw = trip_wp + (size_t)ai * 8;
               tw[0] = w.x;
               tw[1] = w.y;
               tw[2] = w.heading;

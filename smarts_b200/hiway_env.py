@@ -327,7 +327,9 @@ class BatchedHiWayEnv:
         bit = lambda b: ((ev & b) != 0).to(t.int8)  # noqa: E731
         acc = (lambda k: o[k].to(f32)) if self.cfg.accel_enable else (lambda k: zeros3)  # noqa: E731
         out: Dict[str, Any] = {
-            "dist": o["ev_distance"].to(f32),
+            # Observation.distance_travelled as the reference fills it: sensors.py:351 calls the trip meter with `sim`
+            # in the `increment` position, so the member is this observation's INCREMENT (= the reward), not the total
+            "dist": o["ev_reward"].to(f32),
             "ego": {
                 "angular_acceleration": acc("acc_angular"), "angular_jerk": acc("acc_angular_jerk"),
                 "linear_acceleration": acc("acc_linear"), "linear_jerk": acc("acc_linear_jerk"),
@@ -467,7 +469,10 @@ class BatchedHiWayEnv:
                         reached_max_episode_steps=bool(bits & _abi.SB_EV_REACHED_MAX_STEPS), agents_alive_done=False)
         return Observation(dt=self.dt, step_count=int(self._tick[e]), elapsed_sim_time=float(self._tick[e]) * self.dt,
                            events=events, ego_vehicle_state=ego, neighborhood_vehicle_states=nbrs,
-                           waypoint_paths=wps, distance_travelled=float(o["ev_distance"][e, a]),
+                           waypoint_paths=wps,
+                           # sensors.py:351 `vehicle.trip_meter_sensor(sim)`: `sim` lands in `increment`, so the
+                           # reference's Observation holds the increment; the total is infos["score"] (agent_manager.py:234)
+                           distance_travelled=float(o["ev_reward"][e, a]),
                            lidar_point_cloud=lidar, drivable_area_grid_map=dagm, occupancy_grid_map=ogm,
                            top_down_rgb=None, road_waypoints=None, via_data=self._vias(e, a))
 

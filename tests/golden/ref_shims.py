@@ -137,6 +137,64 @@ def install():
     sys.modules["smarts.sstudio.types"] = sstt
 
 
+def canonical_kd_ties():
+    """scipy's cKDTree returns equidistant neighbours in an order that depends on the tree's internal partition
+    (not on anything the reference specifies); lane maps are full of exactly coincident lane points -- the last
+    point of a lane and the first of its successor -- so which of the two comes first decides which lane a vehicle
+    standing there is "on".  The fixtures canonicalise that one third-party degree of freedom: among neighbours at
+    exactly the same distance the lower index comes first (the rule of the oracle and the kernels).
+    Everything else about the query, and all of the reference's own code around it, runs unchanged."""
+    import numpy as np
+    lp_mod = importlib.import_module("smarts.core.lanepoints")
+    base = lp_mod.KDTree
+    if getattr(base, "_sb_canonical", False):
+        return
+
+    class CanonicalKDTree(base):
+        _sb_canonical = True
+
+        def query(self, x, k=1, *a, **kw):
+            x = np.asarray(x, float)
+            kk = int(min(self.n, k + 8))
+            d, i = super().query(x.reshape(-1, self.m), kk, *a, **kw)
+            d, i = np.asarray(d).reshape(len(d), -1), np.asarray(i).reshape(len(i), -1)
+            rank = getattr(self, "_sb_rank", None)        # set_tie_ranks: index of the point in the flattened map
+            order = np.lexsort((i if rank is None else rank[np.minimum(i, self.n - 1)], d), axis=1)  # distance, then rank
+            d, i = np.take_along_axis(d, order, 1)[:, :k], np.take_along_axis(i, order, 1)[:, :k]
+            if k == 1:
+                d, i = d[:, 0], i[:, 0]
+            if x.ndim == 1:
+                d, i = d[0], i[0]
+            return d, i
+
+    lp_mod.KDTree = CanonicalKDTree
+
+
+def set_tie_ranks(ref_rm, mine):
+    """Give every KD-tree of the reference map the rank that breaks distance ties: the index of the lane point in
+    the flattened map `mine` (lanes in net.xml order, points along the lane), i.e. "lowest index wins" in the
+    numbering the oracle and the kernels use.  The reference's own global order is the traversal order of its
+    lane-point builder and plays no role in its results except through scipy's arbitrary tie order."""
+    import numpy as np
+    lps = ref_rm._lanepoints
+    lane_index = {lid: i for i, lid in enumerate(mine.lane_ids)}
+    rank_of = {}
+    for lane_id, llps in lps._lanepoints_by_lane_id.items():
+        start = int(mine.lane_lp_start[lane_index[lane_id]])
+        assert len(llps) == int(mine.lane_lp_count[lane_index[lane_id]]), lane_id
+        for k, llp in enumerate(llps):
+            p = llp.lp.pose.as_position2d()
+            assert abs(p[0] - mine.lp_x[start + k]) < 1e-9 and abs(p[1] - mine.lp_y[start + k]) < 1e-9, (lane_id, k)
+            rank_of[id(llp)] = start + k
+    def attach(tree, llps):
+        tree._sb_rank = np.array([rank_of[id(l)] for l in llps], np.int64)
+    attach(lps._lanepoints_kd_tree, lps._linked_lanepoints)
+    for lane_id, tree in lps._lanepoints_kd_tree_by_lane_id.items():
+        attach(tree, lps._lanepoints_by_lane_id[lane_id])
+    for edge_id, tree in lps._lanepoints_kd_tree_by_edge_id.items():
+        attach(tree, lps._lanepoints_by_edge_id[edge_id])
+
+
 class RefGraph:
     """``sumolib.net.Net`` stand-in over ``smarts_b200.sumo_net.SumoNet`` for the reference's
     ``SumoRoadNetwork``; ``getNeighboringLanes`` restates sumolib's rtree + distance filter with
@@ -165,6 +223,7 @@ def reference_road_map(net_file: str, spacing: float = 1.0):
     """The reference ``SumoRoadNetwork`` (its own lane points, KD-trees, waypoint code) over a
     map parsed by ``smarts_b200.sumo_net``."""
     install()
+    canonical_kd_ties()
     sys.path.insert(0, "/root/repo")
     from smarts_b200.sumo_net import SumoNet
     from smarts.core.sumo_road_network import SumoRoadNetwork

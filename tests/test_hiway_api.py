@@ -154,8 +154,8 @@ def test_hiway_env_vias_and_accelerometer():
     env = make("smarts.env:hiway-v0", scenarios=[Scenario(rm, MISSIONS)], agent_specs=specs)
     obs, track = env.reset(), []
     for t in range(25):
-        obs, _, _, _ = env.step({i: "keep_lane" for i in obs})
-        track.append((obs["A0"].distance_travelled, obs["A0"].ego_vehicle_state.speed))
+        obs, _, _, infos = env.step({i: "keep_lane" for i in obs})
+        track.append((infos["A0"]["score"], obs["A0"].ego_vehicle_state.speed))   # score = the trip meter's total
     env.close()
     (d1, v1), (d2, v2) = track[8], track[20]
     assert d2 - d1 > 6.0
