@@ -37,6 +37,15 @@ constexpr double kWheelRadius = 0.31265, kMaxTorque = 1600.0, kMaxBrakeTorque = 
 // 1 + 2356 + 2*1 + 4*15 kg (vehicle.urdf) plus the wheels' rotational inertia 4*Izz/r^2
 constexpr double kEffMass = 2419.0 + 4.0 * 2.0 / (kWheelRadius * kWheelRadius);
 constexpr double kRearAxleToCg = 1.5;  // wheels at y = +-1.5 (vehicle.urdf:96-135)
+// single-track model constants (DESIGN.md "Vehicle model")
+constexpr double kMass = 2356.0 + 4.0 * 15.0;                  // vehicle.urdf:19, :40 (chassis + wheels)
+constexpr double kIzz = 2681.95008628 + 4.0 * 15.0 * (1.5 * 1.5 + 0.5 * 0.5);  // vehicle.urdf:21 + wheels as point masses
+constexpr double kCornerStiffness = 100000.0;  // N/rad per axle: the stiffness the reference's own lateral-gain design
+                                               // linearises with (lane_following_controller.py:392-422, plane.urdf:26)
+constexpr double kTyreForceMax = 3.0 * kMass * 9.8 / 2.0;  // per axle: plane.urdf:24 lateral_friction 3 against a wheel
+                                                           // friction of 1 (plane.urdf:5-17), gravity 9.8 (smarts.py:600)
+constexpr double kSteerJointGain = 0.1;  // POSITION_CONTROL default positionGain: 10 % of the error per sub-step
+constexpr double kDynSpeed = 1.0;        // m/s: below it the tyres roll without slip (the slip angles divide by speed)
 
 struct Ego {
   double x, y, h, speed, yaw_rate, v_long, v_lat;
@@ -248,42 +257,53 @@ void trajectory_tracking(const Ego& v, const double* traj, int N, double dt, dou
   apply_control(v, thr, brake, st[5], out3);
 }
 
-// Kinematic stand-in for the pybullet AckermannChassis step (DESIGN.md
-// "Vehicle model"): CG-referenced kinematic bicycle, `substeps` explicit Euler sub-steps.
+// Stand-in for the pybullet AckermannChassis step (DESIGN.md "Vehicle model"): a single-track
+// ("bicycle") model with yaw inertia and linear, friction-limited tyres above kDynSpeed, the kinematic bicycle
+// below it, and a first-order steering joint; `substeps` explicit Euler sub-steps (240 Hz, smarts.py:607-615).
+// Body frame: x forward, y left, yaw counter-clockwise; delta = steering joint angle, left positive.
 void chassis_step(World& w, int ai, int vi) {
   const double* c = &w.last_control[(size_t)ai * 3];
-  double delta = -c[2] * kMaxSteeringWheel;  // chassis.py:790-793 (joint angle, left positive)
-  delta = clipd(delta, -kSteerLimit, kSteerLimit);
-  double acc = 4.0 * (c[0] * kMaxTorque - c[1] * kMaxBrakeTorque) / kWheelRadius / kEffMass;
-  double sd, cd;
-  sb_sincos(delta, &sd, &cd);
-  double beta = sb_atan2(0.5 * sd, cd);
-  double sbeta, cbeta;
-  sb_sincos(beta, &sbeta, &cbeta);
+  double target = -c[2] * kMaxSteeringWheel;  // chassis.py:790-793 (joint angle, left positive)
+  target = clipd(target, -kSteerLimit, kSteerLimit);
+  const double ax = 4.0 * (c[0] * kMaxTorque - c[1] * kMaxBrakeTorque) / kWheelRadius / kEffMass;
   const int n = w.substeps;
   const double hdt = w.cfg.dt / (double)n;
-  double x = w.pos_x[vi], y = w.pos_y[vi], h = w.heading[vi], v = w.speed[vi];
-  double omega = 0.0;
+  double x = w.pos_x[vi], y = w.pos_y[vi], h = w.heading[vi];
+  double vx = w.v_long[ai], vy = -w.v_lat[ai], om = w.yaw_rate[vi], delta = -w.steering[ai];
   for (int k = 0; k < n; ++k) {
-    v = v + acc * hdt;
-    if (v < 0) v = 0;
-    double s, cc;
-    sb_sincos(h + beta, &s, &cc);
-    x = x - (v * s) * hdt;
-    y = y + (v * cc) * hdt;
-    omega = (v / kRearAxleToCg) * sbeta;
-    h = h + omega * hdt;
+    delta = delta + kSteerJointGain * (target - delta);
+    double sd, cd;
+    sb_sincos(delta, &sd, &cd);
+    if (vx > kDynSpeed) {
+      const double af = (vy + kRearAxleToCg * om) / vx - delta, ar = (vy - kRearAxleToCg * om) / vx;
+      const double fyf = clipd(-kCornerStiffness * af, -kTyreForceMax, kTyreForceMax) * cd;
+      const double fyr = clipd(-kCornerStiffness * ar, -kTyreForceMax, kTyreForceMax);
+      const double ay = (fyf + fyr) / kMass - vx * om;
+      const double dom = (kRearAxleToCg * fyf - kRearAxleToCg * fyr) / kIzz;
+      vy = vy + ay * hdt;
+      om = om + dom * hdt;
+    } else {  // rolling without slip
+      om = vx * (sd / cd) / (2.0 * kRearAxleToCg);
+      vy = om * kRearAxleToCg;
+    }
+    vx = vx + (ax + vy * om) * hdt;
+    if (vx < 0) vx = 0;
+    double sn, cs;
+    sb_sincos(h, &sn, &cs);
+    x = x + (-(vx * sn) - vy * cs) * hdt;
+    y = y + (vx * cs - vy * sn) * hdt;
+    h = h + om * hdt;
   }
   h = wrap_heading(h);
   w.pos_x[vi] = x;
   w.pos_y[vi] = y;
   w.heading[vi] = h;
-  w.speed[vi] = v;
-  w.yaw_rate[vi] = omega;
+  w.speed[vi] = std::sqrt(vx * vx + vy * vy);
+  w.yaw_rate[vi] = om;
   sb_sincos(h, &w.sin_h[vi], &w.cos_h[vi]);
   w.steering[ai] = -delta;  // chassis.py:513-528
-  w.v_long[ai] = v * cbeta; // chassis.py:558-566
-  w.v_lat[ai] = -(v * sbeta);
+  w.v_long[ai] = vx;        // chassis.py:558-566
+  w.v_lat[ai] = -vy;
 }
 
 // ---------------------------------------------------------------- sensors
@@ -1450,6 +1470,17 @@ int or_waypoint_paths(void* h, double x, double y, double heading, int lookahead
 
 int or_nearest_lane(void* h, double x, double y, double radius, double* dist) {
   return nearest_lane(static_cast<World*>(h)->map, x, y, radius, dist);
+}
+
+// lane-coordinate probes (RoadMap.Lane.offset_along_lane / vector_at_offset / from_lane_coord, road_map.py:346-417;
+// SumoRoadNetwork.road_with_point, sumo_road_network.py:703-709): out = {s of (x, y), vector at `off` x, y,
+// point at `off` x, y, on-road flag of (x, y)}
+void or_lane_probe(void* h, int lane, double x, double y, double off, double* out) {
+  const Map& mp = static_cast<World*>(h)->map;
+  out[0] = offset_along_lane(mp, lane, x, y);
+  vector_at_offset(mp, lane, off, &out[1], &out[2]);
+  from_lane_coord(mp, lane, off, &out[3], &out[4]);
+  out[5] = road_with_point(mp, x, y) ? 1.0 : 0.0;
 }
 
 void or_lateral_gains(double target_speed, double* heading_gain, double* lateral_gain) {

@@ -50,6 +50,7 @@ def lib():
                                         C.POINTER(C.c_int32), C.c_int, C.POINTER(C.c_int32), C.POINTER(C.c_double)]
         L.or_nearest_lane.restype = C.c_int
         L.or_nearest_lane.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_double, C.POINTER(C.c_double)]
+        L.or_lane_probe.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_double, C.POINTER(C.c_double)]
         L.or_lateral_gains.argtypes = [C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.or_lane_following.restype = C.c_uint32
         L.or_lane_following.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int32), C.c_int,
@@ -203,6 +204,12 @@ class OracleWorld:
         d = C.c_double()
         l = lib().or_nearest_lane(self._h, x, y, radius, C.byref(d))
         return l, d.value
+
+    def lane_probe(self, lane, x, y, off):
+        """(offset of (x, y) along `lane`, lane vector at `off`, lane point at `off`, (x, y) on a road?)"""
+        out = np.zeros(6)
+        lib().or_lane_probe(self._h, int(lane), float(x), float(y), float(off), _dp(out))
+        return out[0], out[1:3].copy(), out[3:5].copy(), bool(out[5])
 
     def lane_following(self, veh7, route, target_speed, lane_change, dt, st):
         veh7 = np.ascontiguousarray(veh7, np.float64)

@@ -15,6 +15,13 @@
 #define SB_MAX_BTORQUE 1400.0
 #define SB_EFF_MASS (2419.0 + 4.0 * 2.0 / (SB_WHEEL_RADIUS * SB_WHEEL_RADIUS))
 #define SB_REAR_AXLE_TO_CG 1.5
+// single-track model (DESIGN.md "Vehicle model"; the oracle's chassis_step holds the same constants)
+#define SB_MASS (2356.0 + 4.0 * 15.0)                                      // vehicle.urdf:19, :40
+#define SB_IZZ (2681.95008628 + 4.0 * 15.0 * (1.5 * 1.5 + 0.5 * 0.5))       // vehicle.urdf:21 + wheels as point masses
+#define SB_CORNER_STIFFNESS 100000.0                                        // N/rad per axle (plane.urdf:26)
+#define SB_TYRE_FORCE_MAX (3.0 * SB_MASS * 9.8 / 2.0)                       // per axle: plane.urdf:24, gravity 9.8
+#define SB_STEER_JOINT_GAIN 0.1                                             // POSITION_CONTROL default positionGain
+#define SB_DYN_SPEED 1.0                                                    // m/s: below it the tyres roll without slip
 
 struct DEgo {
   double x, y, h, speed, yaw_rate, v_long, v_lat;
@@ -266,35 +273,44 @@ __device__ void d_trajectory_tracking(const DEgo& v, const double* traj, int N, 
 // Kinematic stand-in for the Bullet AckermannChassis step (DESIGN.md "Vehicle model").
 __device__ void d_chassis_step(const DState& s, int ai, int vi, double dt, int substeps) {
   const double* c = &s.last_control[(size_t)ai * 3];
-  double delta = -c[2] * SB_MAX_STEERING_WHEEL;
-  delta = d_clip(delta, -SB_STEER_LIMIT, SB_STEER_LIMIT);
-  double acc = 4.0 * (c[0] * SB_MAX_TORQUE - c[1] * SB_MAX_BTORQUE) / SB_WHEEL_RADIUS / SB_EFF_MASS;
-  double sd, cd;
-  sb_sincos(delta, &sd, &cd);
-  double beta = sb_atan2(0.5 * sd, cd);
-  double sbeta, cbeta;
-  sb_sincos(beta, &sbeta, &cbeta);
+  double target = -c[2] * SB_MAX_STEERING_WHEEL;  // joint angle, left positive (chassis.py:790-793)
+  target = d_clip(target, -SB_STEER_LIMIT, SB_STEER_LIMIT);
+  const double ax = 4.0 * (c[0] * SB_MAX_TORQUE - c[1] * SB_MAX_BTORQUE) / SB_WHEEL_RADIUS / SB_EFF_MASS;
   const double hdt = dt / (double)substeps;
-  double x = s.pos_x[vi], y = s.pos_y[vi], h = s.heading[vi], v = s.speed[vi];
-  double omega = 0.0;
+  double x = s.pos_x[vi], y = s.pos_y[vi], h = s.heading[vi];
+  double vx = s.v_long[ai], vy = -s.v_lat[ai], om = s.yaw_rate[vi], delta = -s.steering[ai];
   for (int k = 0; k < substeps; ++k) {
-    v = v + acc * hdt;
-    if (v < 0) v = 0;
+    delta = delta + SB_STEER_JOINT_GAIN * (target - delta);
+    double sd, cd;
+    sb_sincos(delta, &sd, &cd);
+    if (vx > SB_DYN_SPEED) {
+      const double af = (vy + SB_REAR_AXLE_TO_CG * om) / vx - delta, ar = (vy - SB_REAR_AXLE_TO_CG * om) / vx;
+      const double fyf = d_clip(-SB_CORNER_STIFFNESS * af, -SB_TYRE_FORCE_MAX, SB_TYRE_FORCE_MAX) * cd;
+      const double fyr = d_clip(-SB_CORNER_STIFFNESS * ar, -SB_TYRE_FORCE_MAX, SB_TYRE_FORCE_MAX);
+      const double ay = (fyf + fyr) / SB_MASS - vx * om;
+      const double dom = (SB_REAR_AXLE_TO_CG * fyf - SB_REAR_AXLE_TO_CG * fyr) / SB_IZZ;
+      vy = vy + ay * hdt;
+      om = om + dom * hdt;
+    } else {  // rolling without slip
+      om = vx * (sd / cd) / (2.0 * SB_REAR_AXLE_TO_CG);
+      vy = om * SB_REAR_AXLE_TO_CG;
+    }
+    vx = vx + (ax + vy * om) * hdt;
+    if (vx < 0) vx = 0;
     double sn, cs;
-    sb_sincos(h + beta, &sn, &cs);
-    x = x - (v * sn) * hdt;
-    y = y + (v * cs) * hdt;
-    omega = (v / SB_REAR_AXLE_TO_CG) * sbeta;
-    h = h + omega * hdt;
+    sb_sincos(h, &sn, &cs);
+    x = x + (-(vx * sn) - vy * cs) * hdt;
+    y = y + (vx * cs - vy * sn) * hdt;
+    h = h + om * hdt;
   }
   h = d_wrap_heading(h);
   s.pos_x[vi] = x;
   s.pos_y[vi] = y;
   s.heading[vi] = h;
-  s.speed[vi] = v;
-  s.yaw_rate[vi] = omega;
+  s.speed[vi] = sqrt(vx * vx + vy * vy);
+  s.yaw_rate[vi] = om;
   sb_sincos(h, &s.sin_h[vi], &s.cos_h[vi]);
-  s.steering[ai] = -delta;
-  s.v_long[ai] = v * cbeta;
-  s.v_lat[ai] = -(v * sbeta);
+  s.steering[ai] = -delta;  // chassis.py:513-528
+  s.v_long[ai] = vx;        // chassis.py:558-566
+  s.v_lat[ai] = -vy;
 }

@@ -238,15 +238,31 @@ class RoadMapData:
                      for i in range(nv - 1)]
             curr = add(shape[0][0], shape[0][1], seg_h[0], 0, li)
             lane_first[li] = curr
+            shape_lp = {(float(shape[0][0]), float(shape[0][1]), seg_h[0]): curr}
+            merged = False
             for i in range(nv - 1):
                 curr = interp(shape[i][0], shape[i][1], shape[i + 1][0], shape[i + 1][1], curr, li)
                 h = seg_h[i + 1] if i + 1 < nv - 1 else seg_h[nv - 2]
+                key = (float(shape[i + 1][0]), float(shape[i + 1][1]), h)
+                if key in shape_lp:
+                    # The reference memoises interpolation per LanePoint *value* (lane, pose, width: frozen dataclass,
+                    # lanepoints.py:396-401), so a shape point equal to an earlier one of its lane is not created
+                    # again: the chain links back to the earlier point and whatever followed the duplicate is not
+                    # linked from here.  Happens for lanes whose last two vertices coincide (zero-length internal
+                    # lanes of minicity): ONE lane point whose only successor is itself, no link to the outgoing lanes.
+                    if i + 1 != nv - 1:
+                        raise ValueError(f"lane {lane.getID()}: repeated interior shape vertex (not restated)")
+                    nexts[curr].append(shape_lp[key])
+                    merged = True
+                    break
                 n = add(shape[i + 1][0], shape[i + 1][1], h, 0, li)
+                shape_lp[key] = n
                 nexts[curr].append(n)
                 curr = n
             lane_last[li] = curr
-            for lo in self.outgoing_lanes(li):
-                pending_links.append((li, lo))
+            if not merged:
+                for lo in self.outgoing_lanes(li):
+                    pending_links.append((li, lo))
             lane_lp_count[li] = len(xs) - lane_lp_start[li]
 
         # cross-lane links (gap interpolation keeps lane points contiguous only when there is

@@ -14,10 +14,9 @@ What runs as the reference wrote it (behind the import shims of ``ref_shims.py``
     of smarts/core/tests/test_sensors.py:39-99
   * ``Lidar._compute_rays`` (lidar.py:89-113)
   * ``scipy.signal.place_poles`` gains (lane_following_controller.py:376-437)
-  * ``SMARTS.neighborhood_vehicles_around_vehicle`` (smarts.py:1191-1208)
 Maps are the reference's own: scenarios/{loop,figure_eight,intersections/4lane,straight} and
-smarts/core/tests/maps/6lane.net.xml, flattened by smarts_b200.road_map (lane points verified
-identical to the reference's, test_lanepoints_match_reference).
+smarts/core/tests/maps/6lane.net.xml, flattened by smarts_b200.road_map (every lane's points are checked against
+the reference's, coordinate by coordinate, in ref_shims.set_tie_ranks).
 """
 from __future__ import annotations
 
@@ -90,12 +89,15 @@ def sample_poses(mine: RoadMapData, rng, n):
     return x, y, np.array([float(Heading(v)) for v in h])
 
 
-def gen_map_queries(name, rel, rng, n=60):
+def gen_map_queries(name, rel, rng, n=60, tie_ranks=False, save_map=True):
     rm, net = ref_shims.reference_road_map(REF + rel)
     mine = RoadMapData(net)
-    mine.save(os.path.join(ROOT, "maps", name + ".npz"))
-    if name == "minicity":
-        return None, mine
+    if save_map:
+        mine.save(os.path.join(ROOT, "maps", name + ".npz"))
+    if name == "minicity" and not tie_ranks:
+        return None, mine  # queried by gen_minicity_golden.py (canonical order among coincident lane points)
+    if tie_ranks:
+        ref_shims.set_tie_ranks(rm, mine)
     routes = []
     for a, b in ROUTES.get(name, []):
         r = mine.generate_route(a, b)
@@ -270,12 +272,6 @@ def gen_gains():
         K = signal.place_poles(A, B, np.array([-35, -15, -2, -3]), method="KNV0").gain_matrix[0]
         out.append([v, K[0], K[1], np.clip(K[1], 0.02, 0.04), np.clip(K[0], 3.4, 4.1)])
     return np.array(out)
-
-
-def gen_neighbors(rng):
-    """SMARTS.neighborhood_vehicles_around_vehicle on mock vehicle states."""
-    from smarts.core.smarts import SMARTS  # noqa: F401  (import check only; method restated below if it fails)
-    raise NotImplementedError
 
 
 def main():

@@ -10,7 +10,7 @@ from conftest import GOLDEN, load_map, make_cfg, oracle_world
 from oracle import oracle_py
 from smarts_b200 import lidar_params
 
-MAPS = ["loop", "figure_eight", "4lane", "straight", "6lane"]
+MAPS = ["loop", "figure_eight", "4lane", "straight", "6lane", "minicity"]
 
 
 def test_detmath_sincos_matches_libm():
@@ -164,3 +164,43 @@ def test_neighbors_match_cdist():
             n = obs["nbr_count"][e, a]
             assert n == len(want)
             assert list(obs["nbr_id"][e, a, :n]) == want
+
+
+def test_map_known_answers_of_the_reference():
+    """smarts/core/tests/test_map.py:48-141 (`test_sumo_map`, scenarios/intersections/4lane): the numbers the
+    reference's own test asserts.  That test runs on the netconvert-shifted map (origin at the bounding-box corner,
+    sumo_road_network.py:117-143); the committed map keeps the net.xml coordinates, so its points are moved by the
+    convBoundary minimum (20, -130) of the file."""
+    rm = load_map("4lane")
+    w = oracle_world(rm, make_cfg(E=1, A=1, M=0))
+    sx, sy = 20.0, -130.0
+    px, py = 125.20 + sx, 139.0 + sy
+    lane, _ = w.nearest_lane(px, py, max(10.0, 2 * 3.2))        # RoadMap.nearest_lane default radius
+    assert rm.lane_ids[lane] == "edge-north-NS_0" and rm.lane_idx_in_road[lane] == 0        # :52-55
+    assert rm.road_ids[rm.lane_road[lane]] == "edge-north-NS"
+    assert rm.lane_length[lane] == 55.6                                                      # :59
+    road = rm.lane_road[lane]
+    assert rm.road_lane_count[road] == 2                       # :61-73: no lane to the right, one to the left
+    left = rm.road_lane_start[road] + 1
+    assert rm.lane_ids[left] == "edge-north-NS_1" and rm.lane_idx_in_road[left] == 1
+    s, _, at_s, on_road = w.lane_probe(lane, px, py, 1.0)
+    assert on_road                                                                           # :56 contains_point
+    assert s == 1.0                                                                          # :81 reflinept.s
+    assert np.allclose(at_s, [px, py], atol=1e-12)                                           # :82 reflinept.t == 0
+    assert rm.lane_width[lane] == 3.2                                                        # :85
+    _, vec, _, _ = w.lane_probe(lane, px, py, 55.7)
+    assert np.array_equal(vec, [0.0, -1.0])                                                  # :112-113
+    outs = [rm.lane_ids[l] for l in rm.outgoing_lanes(lane)]
+    assert outs == [":junction-intersection_0_0", ":junction-intersection_1_0"]              # :96-100
+    assert not [l for l in range(len(rm.lane_ids)) if lane in rm.outgoing_lanes(l)]          # :93-94 no incoming
+    route = rm.generate_route("edge-north-NS", "edge-east-WE")
+    assert len(route.road_indices) == 4                                                      # :124-126
+    # Route.distance_between (sumo_road_network.py:917-957): rest of the start lane + the roads between + the
+    # offset on the end lane
+    ex, ey = 198.0 + sx, 65.20 + sy
+    end_lane, _ = w.nearest_lane(ex, ey, 30.0)
+    assert rm.lane_road[end_lane] == route.road_indices[-1]
+    s_end, _, _, _ = w.lane_probe(end_lane, ex, ey, 0.0)
+    between = sum(float(rm.road_length[r]) for r in route.road_indices[1:-1])
+    assert round((rm.lane_length[lane] - s) + between + s_end, 2) == 134.01                  # :129-130
+    assert round(s_end, 2) == 53.6                                                           # :132-134 project_along
