@@ -35,7 +35,7 @@ METRIC = "agent-steps/sec incl. LiDAR+OGM obs"
 UNIT = "agent-steps/s"
 
 WORKLOADS = {
-    # BASELINE.json configs[2]
+    # BASELINE.json configs[2] -- the configuration the metric is quoted on
     "4lane_lidar_ogm_dagm_256": dict(
         map="4lane", E=4096, A=4, M=20, seed=11,
         missions=[("edge-south-SN", 1, 10.0, "edge-west-EW"), ("edge-west-WE", 0, 10.0, "edge-east-WE"),
@@ -43,26 +43,36 @@ WORKLOADS = {
         cfg=dict(lidar=True, wall=1.5, ogm=(256, 256, 0.1), dagm=(256, 256, 0.1), route_cap=16),
         desc="scenarios/intersections/4lane, 4 agents x 4096 envs, LiDAR 300 rays + OGM + DAGM 256x256 @0.1 m/px, "
              "20 synthetic social vehicles/env, Lane action keep_lane"),
+    # BASELINE.json configs[0], batched: the reference runs ONE such env on the CPU
+    "loop_laner_lidar_ogm64": dict(
+        map="loop", E=4096, A=1, M=20, seed=5, missions=[("445633931", 0, 20.0, "445633932")],
+        cfg=dict(lidar=True, wall=1.5, ogm=(64, 64, 50 / 64), route_cap=8),
+        desc="scenarios/loop, 1 Laner agent keep_lane x 4096 envs, LiDAR 300 rays + OGM 64x64, "
+             "20 synthetic social vehicles/env"),
     # BASELINE.json configs[1]
     "figure_eight_nbr_wp": dict(
         map="figure_eight", E=256, A=4, M=20, seed=7,
         missions=[("gneE20", 0, 5.0, "gneE27"), ("gneE36", 1, 5.0, "gneE25"), ("gneE20", 2, 25.0, "gneE27"),
                   ("gneE36", 0, 30.0, "gneE25")],
         cfg=dict(nbr=True, nbr_radius=50.0, wp=True, wp_lookahead=32, route_cap=24),
-        desc="scenarios/figure_eight, 4 agents x 256 envs, NeighborhoodVehicles + Waypoints"),
-    # BASELINE.json configs[3] (Lane action here: the Trajectory policy needs the previous observation on the host)
-    "minicity_wp_100_social": dict(
-        map="minicity", E=1024, A=32, M=100, seed=13, missions="random",
-        cfg=dict(wp=True, wp_lookahead=32, route_cap=32),
-        desc="scenarios/minicity, 32 agents x 1024 envs, Waypoints obs, 100 synthetic BoxChassis social vehicles/env"),
-    # BASELINE.json configs[4], one point of the sweep
+        desc="scenarios/figure_eight, 4 agents x 256 envs, NeighborhoodVehicles + Waypoints, Lane action keep_lane"),
+    # BASELINE.json configs[3]: the action of examples/trajectory_tracking_agent.py:16-37, built on the device
+    # every tick from the previous observation (first 10 waypoints of path 0 at 50 km/h)
+    "minicity_trajectory_100_social": dict(
+        map="minicity", E=1024, A=32, M=100, seed=13, missions="random", action="trajectory",
+        cfg=dict(wp=True, wp_lookahead=32, route_cap=32, action_space=_abi.SB_ACTION_TRAJECTORY, traj_len=10),
+        desc="scenarios/minicity, 32 TrajectoryTracking agents x 1024 envs, Waypoints obs, 100 synthetic BoxChassis "
+             "social vehicles/env, trajectory = 10 waypoints of path 0 at 50 km/h"),
+    # BASELINE.json configs[4], one point of the sweep (--envs moves along it)
     "straight_full_suite_64": dict(
         map="straight", E=4096, A=16, M=16, seed=17,
         missions=[("west", k % 3, 4.0 + 5.5 * k, "east") for k in range(16)],
         cfg=dict(nbr=True, nbr_radius=50.0, wp=True, wp_lookahead=32, lidar=True, wall=1.5, ogm=(64, 64, 50 / 64),
                  dagm=(64, 64, 50 / 64), route_cap=4),
-        desc="synthetic straight road, 16 agents x 4096 envs + 16 social/env, nbr + wp + LiDAR + OGM + DAGM 64x64"),
+        desc="synthetic straight road, 16 agents x 4096 envs + 16 social/env, nbr + wp + LiDAR + OGM + DAGM 64x64, "
+             "Lane action keep_lane"),
 }
+HEADLINE = "4lane_lidar_ogm_dagm_256"
 
 
 def make_cfg(E, A, M, device, **kw):
@@ -71,8 +81,8 @@ def make_cfg(E, A, M, device, **kw):
     c.device = device
     c.n_envs, c.n_agents, c.n_social = E, A, M
     c.dt = 0.1
-    c.action_space = _abi.SB_ACTION_LANE
-    c.traj_len = 10
+    c.action_space = kw.get("action_space", _abi.SB_ACTION_LANE)
+    c.traj_len = kw.get("traj_len", 10)
     c.route_cap = kw.get("route_cap", 16)
     c.nbr_enable, c.nbr_cap, c.nbr_radius = int(kw.get("nbr", False)), 10, kw.get("nbr_radius", 50.0)
     c.wp_enable, c.wp_lookahead, c.wp_out_paths, c.wp_out_len = int(kw.get("wp", False)), kw.get("wp_lookahead", 32), 4, 20
@@ -167,6 +177,24 @@ def build_inputs(w, E, seed_shift=0):
     return rm, (x, y, h, v, route, rlen), traffic
 
 
+def host_actions(w, E):
+    if w.get("action") == "trajectory":
+        return np.zeros((E, w["A"], 4, 10), np.float64)
+    return np.zeros((E, w["A"]), np.int32)  # keep_lane
+
+
+def trajectory_from_obs_numpy(o, out):
+    """examples/trajectory_tracking_agent.py:16-37 on arrays: 10 waypoints of path 0, 50 km/h.  (A path shorter than
+    10 waypoints repeats its last one -- the example would hand a shorter list.)"""
+    n = np.clip(o["wp_len"][:, :, 0], 1, 10)
+    idx = np.minimum(np.arange(10)[None, None, :], (n - 1)[:, :, None])
+    out[:, :, 0] = np.take_along_axis(o["wp_pos"][:, :, 0, :, 0], idx, 2)
+    out[:, :, 1] = np.take_along_axis(o["wp_pos"][:, :, 0, :, 1], idx, 2)
+    out[:, :, 2] = np.take_along_axis(o["wp_heading"][:, :, 0, :], idx, 2)
+    out[:, :, 3] = 50 / 3.6
+    return out
+
+
 def cpu_run(w, E_s, ticks, threads):
     """Oracle (restated reference path) on `threads` host threads: E_s envs x `ticks` ticks."""
     from oracle import oracle_py
@@ -174,17 +202,30 @@ def cpu_run(w, E_s, ticks, threads):
     cfg = make_cfg(E_s, w["A"], w["M"], 0, **w["cfg"])
     ora = oracle_py.OracleWorld(cfg, rm.arrays(), rm.spacing, lidar_params.base_rays(lidar_params.BasicLidar), threads)
     ora.reset(*init)
-    act = np.zeros((E_s, w["A"]), np.int32)
+    act = host_actions(w, E_s)
+    traj = w.get("action") == "trajectory"
     socs = [traffic.states(t) for t in range(ticks + 1)]
+    ora.observe()
+    if traj:
+        trajectory_from_obs_numpy(ora.obs(), act)
     ora.set_social(socs[0]); ora.step(act); ora.observe()  # warm
     t0 = time.perf_counter()
     for t in range(ticks):
+        if traj:
+            trajectory_from_obs_numpy(ora.obs(), act)
         ora.set_social(socs[t + 1])
         ora.step(act)
         ora.observe()
     dt = time.perf_counter() - t0
     ora.close()
     return E_s * w["A"] * ticks / dt, dt
+
+
+def describe(w, E, W_, K):
+    """The `config` object: what is run, nothing measured -- both arms print the same one."""
+    return {"workload": w["desc"], "envs_per_gpu": E, "agents_per_env": w["A"], "social_per_env": w["M"],
+            "tick_window": [W_, W_ + K], "dt": 0.1,
+            "l2": "every tick rewrites all observation buffers; with more than 126 MB of them per GPU no flush is needed"}
 
 
 def run_reference(args, w):
@@ -195,26 +236,201 @@ def run_reference(args, w):
     if rank != 0:
         return
     threads = os.cpu_count() or 1
+    W_, K = max(args.warmup, 3), args.steps
     # each step = the whole workload (every env of the per-GPU batch, one tick) unless that would not fit a
     # few minutes on this host, in which case the per-step sample is halved until it does
     E_s = w["E"]
     rate, _ = cpu_run(w, max(threads, 16), 2, threads)
-    budget = 150.0 / max(args.steps + args.warmup, 1)
+    budget = 150.0 / max(K + W_, 1)
     while E_s * w["A"] / rate > budget and E_s > threads:
         E_s //= 2
-    cpu_run(w, E_s, max(args.warmup, 1), threads)
-    value, dt = cpu_run(w, E_s, args.steps, threads)
-    sample = f"{E_s} envs x {w['A']} agents per step, {args.steps} steps, oracle port on {threads} threads"
+    cpu_run(w, E_s, W_, threads)
+    value, dt = cpu_run(w, E_s, K, threads)
+    sample = f"{E_s} of the {w['E']} envs x {w['A']} agents per step, {K} steps, oracle port on {threads} threads"
     line = {
-        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": K,
+        "warmup": W_, "ms_per_step": 1e3 * dt / K, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": w["desc"], "sample": sample},
+        "config": describe(w, w["E"], W_, K),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+class GpuWorkload:
+    """One workload resident on this rank's GPU: engine, recorded traffic and actions in HBM."""
+
+    T = 8  # ticks of recorded social traffic, cycled
+
+    def __init__(self, w, E, local, rank, events=False):
+        import torch
+        from smarts_b200.engine import Engine
+        self.torch, self.w, self.E, self.A, self.M = torch, w, E, w["A"], w["M"]
+        self.rm, self.init, self.traffic = build_inputs(w, E, seed_shift=1000 * rank)
+        self.cfg = make_cfg(E, self.A, self.M, local, **dict(w["cfg"], events=events or w["cfg"].get("events", False)))
+        self.eng = Engine(self.cfg, self.rm, lidar_params.base_rays(lidar_params.BasicLidar))
+        self.eng.reset(*self.init)
+        self.rec_host = self.traffic.recording(self.T)              # [T, E, M, 8] recorded social traffic
+        self.rec = torch.from_numpy(self.rec_host).cuda()           # resident in HBM before timing
+        self.traj = w.get("action") == "trajectory"
+        if self.traj:
+            self.actions = torch.zeros((E, self.A, 4, 10), dtype=torch.float64, device="cuda")
+            self.actions[:, :, 3] = 50 / 3.6
+            self.idx = torch.arange(10, device="cuda")[None, None, :]
+            self.eng.observe()                                       # the policy reads the reset observation
+        else:
+            self.actions = torch.zeros((E, self.A), dtype=torch.int32, device="cuda")  # keep_lane
+
+    def policy(self):
+        """examples/trajectory_tracking_agent.py:16-37 as tensor ops on the device-resident observation."""
+        torch, o = self.torch, self.eng.obs()
+        n = o["wp_len"][:, :, 0].clamp(1, 10).long()
+        idx = torch.minimum(self.idx, (n - 1)[:, :, None])
+        self.actions[:, :, 0] = torch.gather(o["wp_pos"][:, :, 0, :, 0], 2, idx)
+        self.actions[:, :, 1] = torch.gather(o["wp_pos"][:, :, 0, :, 1], 2, idx)
+        self.actions[:, :, 2] = torch.gather(o["wp_heading"][:, :, 0, :], 2, idx).double()
+
+    def tick(self, t):
+        if self.traj:
+            self.policy()
+        self.eng.set_social(self.rec[t % self.T])
+        self.eng.step(self.actions)
+        self.eng.observe()
+
+    def timed(self, first, K, dist=None, kernel_timing=False, sampler=None):
+        """K ticks from tick `first`, CUDA events on the launching stream; returns (ms, launches, kernel times)."""
+        torch = self.torch
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+        if sampler is not None:
+            sampler.start()
+        self.eng.set_timing(kernel_timing)
+        l0 = self.eng.launch_count
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        for t in range(K):
+            self.tick(first + t)
+        ev1.record()
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        ms = ev0.elapsed_time(ev1)
+        kt = self.eng.collect_timing() if kernel_timing else None
+        self.eng.set_timing(False)
+        return ms, self.eng.launch_count - l0, kt
+
+    def close(self):
+        self.eng.close()
+
+
+def hbm_peak():
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        return float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def measure(w, E, W_, K, local, rank, world, dist):
+    """Warm-up, the timed region (no per-kernel events inside it), then the same ticks again with every kernel
+    bracketed by CUDA events for the roofline.  Returns this workload's numbers (rank 0 uses them)."""
+    import torch
+    g = GpuWorkload(w, E, local, rank)
+    for t in range(W_):
+        g.tick(t)
+    sampler = ClockSampler(local)
+    ms, launches, _ = g.timed(W_, K, dist if world > 1 else None, False, sampler)
+    clocks = sampler.stop()
+    ms_kt, _, ktimes = g.timed(W_ + K, K, None, True)
+    stats = torch.tensor([ms, float(E * g.A * K)], dtype=torch.float64, device="cuda")
+    total = float(E * g.A * K)
+    if world > 1:  # max time over ranks; episode statistics (agent-steps) summed -- the only collectives
+        tmax, tot = stats[:1].clone(), stats[1:].clone()
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        ms, total = float(tmax.item()), float(tot.item())
+    peak, peak_src = hbm_peak()
+    step_bytes = algorithmic_bytes_per_agent_step(g.cfg, g.M, g.A)
+    step_gbs = step_bytes * (E * g.A * K) / (ms * 1e-3) / 1e9  # per GPU (weak scaling)
+    kms = {k: v[0] / max(v[1], 1) for k, v in ktimes.items() if v[1]}
+    dom = max(kms, key=kms.get)
+    if dom == "k_raster":
+        per_launch = raster_bytes_per_agent(g.cfg, g.A + g.M) * E * g.A
+    else:
+        per_launch = step_bytes * E * g.A
+    achieved = per_launch / (kms[dom] * 1e-3) / 1e9
+    out = dict(g=g, ms=ms, K=K, launches=launches, clocks=clocks, value=total / (ms * 1e-3),
+               step_bytes=step_bytes, step_gbs=step_gbs, step_frac=step_gbs / peak, kernel_ms=kms,
+               ms_per_step_kernel_timed=ms_kt / K, dom=dom, per_launch=per_launch, achieved=achieved, peak=peak,
+               peak_src=peak_src)
+    return out
+
+
+def measure_e2e(g, Ke, world, dist):
+    """The same metric through the host-buffer calls a reference-side binding makes (include/smarts_b200.h:
+    sb_step_host + sb_copy_obs_to_host): every step copies actions + social states H2D from pinned memory and
+    delivers EVERY observation buffer to host memory.  `value` rewrites every grid byte per call (the default
+    contract); `value_incremental` keeps persistent destination buffers and rewrites only the 64-pixel words that
+    changed (sb_set_incremental_host_grids)."""
+    import torch
+    eng, E, A = g.eng, g.E, g.A
+    host_obs = eng.host_obs_buffers(pinned=True)
+    act_host = torch.from_numpy(host_actions(g.w, E)).pin_memory()
+    soc_host = torch.from_numpy(g.rec_host).pin_memory()
+    h2d = act_host.numel() * act_host.element_size() + soc_host[0].numel() * 8
+    obs_host_bytes = sum(t.numel() * t.element_size() for t in host_obs.values())
+    # bytes that cross PCIe: the 0/255 grids travel as 1 bit per pixel and are widened to the uint8 StdObs layout
+    # by host threads inside the call; every other buffer is copied as is
+    d2h = sum(t.numel() * t.element_size() // (8 if k in ("ogm", "dagm") else 1) for k, t in host_obs.items())
+
+    def policy_host():
+        if g.traj:
+            trajectory_from_obs_numpy({k: host_obs[k].numpy().reshape((E, A) + tuple(host_obs[k].shape[1:]))
+                                       for k in ("wp_len", "wp_pos", "wp_heading")}, act_host.numpy())
+
+    def run(t_base):
+        eng.step_host(act_host.numpy(), soc_host[t_base % g.T].numpy()); eng.copy_obs_to_host(host_obs)  # warm
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        for t in range(Ke):
+            policy_host()
+            eng.step_host(act_host.numpy(), soc_host[(t_base + t + 1) % g.T].numpy())
+            eng.copy_obs_to_host(host_obs)
+        torch.cuda.synchronize()
+        e2e_t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
+        return world * E * A * Ke / float(e2e_t.item())
+
+    full = run(0)
+    eng.set_incremental_host_grids(True)
+    inc = run(Ke + 1)
+    eng.set_incremental_host_grids(False)
+    return {"value": full, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+            "host_obs_bytes_per_step": obs_host_bytes, "steps": Ke, "value_incremental": inc,
+            "transport": "grids bit-packed over PCIe, widened to uint8 in host memory by the library; value = every "
+                         "byte of every buffer rewritten per call; value_incremental = persistent pinned destination "
+                         "buffers, only the 64-pixel words that changed since the previous call rewritten"}
+
+
+def cpu_baseline(w, A):
+    """The oracle port on this box's host cores, bounded to ~15 s + a single-thread figure on a smaller sample."""
+    threads = os.cpu_count() or 1
+    rate, _ = cpu_run(w, max(threads, 16), 2, threads)
+    ticks = 20
+    E_s = int(min(max(15.0 * rate / (A * ticks), threads), w["E"]))
+    v, dt = cpu_run(w, E_s, ticks, threads)
+    E_1 = int(max(1, min(E_s, 5.0 * (rate / threads) / (A * ticks))))
+    v1, dt1 = cpu_run(w, E_1, ticks, 1)
+    return {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": f"{E_s} envs x {A} agents x {ticks} ticks of the same workload ({dt:.1f} s), CPU oracle on "
+                      f"{threads} threads",
+            "value_1_thread": v1, "sample_1_thread": f"{E_1} envs x {A} agents x {ticks} ticks ({dt1:.1f} s)"}
 
 
 def main():
@@ -223,16 +439,15 @@ def main():
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="smarts_b200", choices=["smarts_b200", "reference"])
-    ap.add_argument("--workload", default="4lane_lidar_ogm_dagm_256", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="all", choices=sorted(WORKLOADS) + ["all"],
+                    help="all = the headline line (BASELINE configs[2]) + an other_workloads object with the rest")
     ap.add_argument("--envs", type=int, default=0, help="override envs per GPU")
-    ap.add_argument("--e2e-steps", type=int, default=3)
-    ap.add_argument("--e2e-full-rewrite", action="store_true", help="e2e with the default transport only (every grid byte rewritten per call)")
+    ap.add_argument("--e2e-steps", type=int, default=20)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--events", action="store_true", help="also compute Events / dones / trip-meter rewards (k_events)")
-    ap.add_argument("--no-kernel-timing", action="store_true",
-                    help="do not bracket every kernel with CUDA events inside the timed region (no roofline object)")
     args = ap.parse_args()
-    w = dict(WORKLOADS[args.workload])
+    name = HEADLINE if args.workload == "all" else args.workload
+    w = dict(WORKLOADS[name])
     if args.envs:
         w["E"] = args.envs
     if args.events:
@@ -243,7 +458,6 @@ def main():
 
     import torch
     import torch.distributed as dist
-    from smarts_b200.engine import Engine
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -251,169 +465,63 @@ def main():
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    E, A, M = w["E"], w["A"], w["M"]
     W_, K = max(args.warmup, 3), args.steps
-    rm, init, traffic = build_inputs(w, E, seed_shift=1000 * rank)
-    cfg = make_cfg(E, A, M, local, **w["cfg"])
-    eng = Engine(cfg, rm, lidar_params.base_rays(lidar_params.BasicLidar))
-    eng.reset(*init)
-    T = 8
-    rec_host = traffic.recording(T)                      # [T, E, M, 8] recorded social traffic
-    rec = torch.from_numpy(rec_host).cuda()              # resident in HBM before timing
-    actions = torch.zeros((E, A), dtype=torch.int32, device="cuda")  # keep_lane
+    m = measure(w, w["E"], W_, K, local, rank, world, dist)
+    g = m["g"]
+    e2e = measure_e2e(g, max(1, args.e2e_steps), world, dist)
+    g.close()
 
-    def tick(t):
-        eng.set_social(rec[t % T])
-        eng.step(actions)
-        eng.observe()
-
-    for t in range(W_):
-        tick(t)
-    torch.cuda.synchronize()
-    sampler = ClockSampler(local)
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
-    sampler.start()
-    eng.set_timing(not args.no_kernel_timing)
-    l0 = eng.launch_count
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record()
-    for t in range(K):
-        tick(W_ + t)
-    ev1.record()
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    clocks = sampler.stop()
-    ms = ev0.elapsed_time(ev1)
-    launches = eng.launch_count - l0
-    ktimes = eng.collect_timing()
-    eng.set_timing(False)
-    stats = torch.tensor([ms, float(E * A * K)], dtype=torch.float64, device="cuda")
-    if world > 1:  # max time over ranks; episode statistics (agent-steps) summed -- the only collectives
-        tmax = stats[:1].clone()
-        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-        tot = stats[1:].clone()
-        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
-        ms, total_agent_steps = float(tmax.item()), float(tot.item())
-    else:
-        total_agent_steps = float(E * A * K)
-    value = total_agent_steps / (ms * 1e-3)
-
-    # ---- end-to-end through the host-buffer call: H2D actions + social, D2H every observation
-    Ke = max(1, args.e2e_steps)
-    host_obs = eng.host_obs_buffers(pinned=True)
-    act_host = torch.zeros((E, A), dtype=torch.int32).pin_memory()
-    soc_host = torch.from_numpy(rec_host).pin_memory()
-    h2d = act_host.numel() * 4 + soc_host[0].numel() * 8
-    obs_host_bytes = sum(t.numel() * t.element_size() for t in host_obs.values())
-    # bytes that cross PCIe: the 0/255 grids travel as 1 bit per pixel (sb_copy_obs_to_host) and are widened
-    # to the uint8 StdObs layout by host threads inside the call; every other buffer is copied as is
-    d2h = sum(t.numel() * t.element_size() // (8 if k in ("ogm", "dagm") else 1) for k, t in host_obs.items())
-    def e2e_run(t_base):
-        eng.step_host(act_host.numpy(), soc_host[t_base % T].numpy()); eng.copy_obs_to_host(host_obs)  # warm
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        t0 = time.perf_counter()
-        for t in range(Ke):
-            eng.step_host(act_host.numpy(), soc_host[(t_base + t + 1) % T].numpy())
-            eng.copy_obs_to_host(host_obs)
-        torch.cuda.synchronize()
-        e2e_t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
-        return world * E * A * Ke / float(e2e_t.item())
-    # first with every grid byte rewritten per call (the default of sb_copy_obs_to_host), then the way a
-    # vectorised env that keeps its pinned staging buffers would run it: sb_set_incremental_host_grids, only the
-    # 64-pixel words that changed since the previous call are rewritten (the buffers hold the full images either way)
-    e2e_full = e2e_run(0)
-    e2e_value = e2e_full
-    if not args.e2e_full_rewrite:
-        eng.set_incremental_host_grids(True)
-        e2e_value = e2e_run(Ke + 1)
-        eng.set_incremental_host_grids(False)
-
-    # ---- informational: the same step with Events / dones / trip-meter rewards also computed (k_events)
+    # informational: the same step with Events / dones / trip-meter rewards also computed (k_events)
     ms_events = None
     if not args.events and world == 1:
-        cfg_e = make_cfg(E, A, M, local, **dict(w["cfg"], events=True))
-        eng_e = Engine(cfg_e, rm, lidar_params.base_rays(lidar_params.BasicLidar))
-        eng_e.reset(*init)
-
-        def tick_e(t):
-            eng_e.set_social(rec[t % T])
-            eng_e.step(actions)
-            eng_e.observe()
+        ge = GpuWorkload(w, w["E"], local, rank, events=True)
         for t in range(W_):
-            tick_e(t)
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for t in range(K):  # the same ticks as the timed region above: the scene gets denser as agents converge
-            tick_e(W_ + t)
-        e1.record()
-        torch.cuda.synchronize()
-        ms_events = e0.elapsed_time(e1) / K
-        eng_e.close()
+            ge.tick(t)
+        ms_events = ge.timed(W_, K)[0] / K
+        ge.close()
+
+    others = {}
+    if args.workload == "all" and not args.envs:
+        for oname in sorted(WORKLOADS):
+            if oname == HEADLINE:
+                continue
+            ow = dict(WORKLOADS[oname])
+            Ko = min(K, 10)
+            om = measure(ow, ow["E"], W_, Ko, local, rank, world, dist)
+            om["g"].close()
+            others[oname] = {"config": describe(ow, ow["E"], W_, Ko), "ms_per_step": om["ms"] / Ko,
+                             "value": om["value"], "unit": UNIT, "steps": Ko,
+                             "algorithmic_bytes_per_agent_step": om["step_bytes"],
+                             "step_frac_of_peak": om["step_frac"], "dominant_kernel": om["dom"],
+                             "dominant_kernel_frac_of_peak": om["achieved"] / om["peak"],
+                             "kernel_ms_per_step": om["kernel_ms"], "gpu_launches": int(om["launches"])}
 
     if rank == 0:
-        peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
-        if os.path.exists(peaks_path):
-            peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
-        else:
-            peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
-        r_ms, r_n = ktimes["k_raster"]
-        dom = "k_raster" if r_n else max(ktimes, key=lambda k: ktimes[k][0])
-        d_ms, d_n = ktimes[dom]
-        if dom == "k_raster":
-            per_launch = raster_bytes_per_agent(cfg, A + M) * E * A
-        else:
-            per_launch = algorithmic_bytes_per_agent_step(cfg, M, A) * E * A
-        achieved = per_launch / (d_ms / d_n * 1e-3) / 1e9 if d_n and d_ms > 0 else float('nan')
         traffic = None  # dram__bytes_read + write per launch of that kernel, from the last committed ncu capture
         cur = os.path.join(ROOT, "profiles", "current.json")
-        if os.path.exists(cur) and args.workload == "4lane_lidar_ogm_dagm_256" and not args.envs:
-            traffic = json.load(open(cur)).get("kernels", {}).get(dom, {}).get("dram_bytes")
-        step_bytes = algorithmic_bytes_per_agent_step(cfg, M, A)
-        step_gbs = step_bytes * (E * A * K) / (ms * 1e-3) / 1e9  # this rank's share (weak scaling: per GPU)
+        if os.path.exists(cur) and name == HEADLINE and not args.envs:
+            traffic = json.load(open(cur)).get("kernels", {}).get(m["dom"], {}).get("dram_bytes")
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W_,
-            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "metric": METRIC, "value": m["value"], "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W_,
+            "ms_per_step": m["ms"] / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
-            "config": {"workload": w["desc"], "envs_per_gpu": E, "agents_per_env": A, "social_per_env": M,
-                       "l2": "outputs (%.2f GB/step/GPU) exceed the 126 MB L2, no flush needed" % (obs_host_bytes / 1e9),
-                       "algorithmic_bytes_per_agent_step": step_bytes,
-                       "step_hbm_gbs_per_gpu": step_gbs, "step_frac_of_peak": step_gbs / peak,
-                       "kernel_ms_per_step": {k: v[0] / max(v[1], 1) for k, v in ktimes.items() if v[1]},
-                       "ms_per_step_with_events_and_rewards": ms_events},
-            "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                         "bytes_per_launch": per_launch, "ms_per_launch": d_ms / max(d_n, 1)},
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "host_obs_bytes_per_step": obs_host_bytes, "steps": Ke,
-                    "value_full_rewrite": e2e_full,
-                    "transport": "grids bit-packed over PCIe, widened to uint8 in host memory by the library; "
-                                 + ("every byte rewritten per call" if args.e2e_full_rewrite else
-                                    "persistent pinned destination buffers, only the 64-pixel words that changed since "
-                                    "the previous call are rewritten (sb_set_incremental_host_grids); "
-                                    "value_full_rewrite = the default mode")},
-            "gpu_launches": int(launches), "clocks": clocks,
+            "config": describe(w, w["E"], W_, K),
+            "detail": {"algorithmic_bytes_per_agent_step": m["step_bytes"], "step_hbm_gbs_per_gpu": m["step_gbs"],
+                       "step_frac_of_peak": m["step_frac"], "kernel_ms_per_step": m["kernel_ms"],
+                       "ms_per_step_kernel_timed_pass": m["ms_per_step_kernel_timed"],
+                       "ms_per_step_with_events_and_rewards": ms_events,
+                       "note": "value / ms_per_step: timed without per-kernel CUDA events; kernel_ms_per_step and "
+                               "roofline: the same ticks run again with every kernel bracketed by events"},
+            "roofline": {"bound": "hbm", "kernel": m["dom"], "achieved": m["achieved"], "peak": m["peak"],
+                         "unit": "GB/s", "frac": m["achieved"] / m["peak"], "traffic": traffic,
+                         "peak_source": m["peak_src"], "bytes_per_launch": m["per_launch"],
+                         "ms_per_launch": m["kernel_ms"][m["dom"]]},
+            "e2e": e2e, "gpu_launches": int(m["launches"]), "clocks": m["clocks"],
         }
-        if world == 1 and not args.no_cpu_baseline:
-            threads = os.cpu_count() or 1
-            rate, _ = cpu_run(w, max(threads, 16), 2, threads)
-            ticks = 20  # ~15 s of CPU work: as many envs of the workload as that allows, 20 ticks each
-            E_s = int(min(max(15.0 * rate / (A * ticks), threads), E))
-            v, dt = cpu_run(w, E_s, ticks, threads)
-            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
-                                    "sample": f"{E_s} envs x {A} agents x {ticks} ticks of the same workload "
-                                              f"({dt:.1f} s), CPU oracle on {threads} threads"}
-        else:
-            line["cpu_baseline"] = None
+        if others:
+            line["other_workloads"] = others
+        line["cpu_baseline"] = cpu_baseline(w, w["A"]) if world == 1 and not args.no_cpu_baseline else None
         print(json.dumps(line), flush=True)
-    eng.close()
     if world > 1:
         dist.destroy_process_group()
 

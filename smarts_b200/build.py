@@ -33,9 +33,11 @@ def is_stale() -> bool:
     return any(os.path.getmtime(os.path.join(CSRC, d)) > t for d in DEPS)
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    if not force and not is_stale():
-        return OUT
+def build(force: bool = False, verbose: bool = False, out: str = None, defines=()) -> str:
+    """``out`` / ``defines`` build a variant next to the product library (kernel A/B experiments under profiles/;
+    loaded with SMARTS_B200_LIB=<path>)."""
+    if out is None and not force and not is_stale():
+        return out or OUT
     objs = []
     for src in HOST_SOURCES:
         obj = os.path.join(CSRC, os.path.splitext(src)[0] + ".o")
@@ -49,15 +51,15 @@ def build(force: bool = False, verbose: bool = False) -> str:
         nvcc_path(), "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
         "-fmad=false", "--expt-extended-lambda", "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off", "-shared",
         "-Xptxas", "-v" if verbose else "-O3",
-        "-o", OUT,
-    ] + [os.path.join(CSRC, s) for s in SOURCES] + objs
+        "-o", out or OUT,
+    ] + ["-D" + d for d in defines] + [os.path.join(CSRC, s) for s in SOURCES] + objs
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:
         sys.stderr.write(res.stdout + res.stderr)
         raise RuntimeError("nvcc failed")
     if verbose:
         sys.stderr.write(res.stderr)
-    return OUT
+    return out or OUT
 
 
 if __name__ == "__main__":

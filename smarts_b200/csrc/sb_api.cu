@@ -379,14 +379,15 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
   h->d_actions = da;
   {  // k_raster shared memory: table | staging area | bit image 0 | bit image 1
     auto rows256 = [](int hh) { return (size_t)(hh < SB_RASTER_THREADS ? hh : SB_RASTER_THREADS); };
-    size_t b0 = c.ogm_enable ? ((size_t)c.ogm_width / 32 + 1) * 4 * rows256(c.ogm_height) : 0;
-    size_t b1 = c.dagm_enable ? ((size_t)c.dagm_width / 32 + 1) * 4 * rows256(c.dagm_height) : 0;
+    auto row_words = [](int ww) { return (size_t)((ww / 32 + 7) / 8 * 8 + 1); };
+    size_t b0 = c.ogm_enable ? row_words(c.ogm_width) * 4 * rows256(c.ogm_height) : 0;
+    size_t b1 = c.dagm_enable ? row_words(c.dagm_width) * 4 * rows256(c.dagm_height) : 0;
     int wmax = 0;
     if (c.ogm_enable) wmax = c.ogm_width;
     if (c.dagm_enable && c.dagm_width > wmax) wmax = c.dagm_width;
     size_t stage = (sizeof(RasterStage) + 15) / 16 * 16;
     (void)wmax;
-    h->raster_smem = SB_RASTER_LUT_BYTES + stage + b0 + b1;
+    h->raster_smem = SB_RASTER_LUT_BYTES + stage + (b0 + b1 + 15) / 16 * 16;
     RasterDims& g = h->raster_dims;
     g.W0 = c.ogm_enable ? c.ogm_width : 0;
     g.H0 = c.ogm_enable ? c.ogm_height : 0;
@@ -399,7 +400,9 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
     g.n_veh = c.ogm_enable ? d.V : 0;
     g.n_src = g.n_veh;  // + map polygons once the map is uploaded (sb_upload_map)
     g.bits_off = (int)(SB_RASTER_LUT_BYTES + stage);
-    g.n_bit_words = g.rows0 * (g.wpr0 + 1) + g.rows1 * (g.wpr1 + 1);
+    g.stride0 = g.W0 ? (int)row_words(g.W0) : 0;
+    g.stride1 = g.W1 ? (int)row_words(g.W1) : 0;
+    g.n_bit_words = g.rows0 * g.stride0 + g.rows1 * g.stride1;
     g.rad0 = 0.5f * (float)c.ogm_resolution * sqrtf((float)g.W0 * g.W0 + (float)g.H0 * g.H0) + 1.0f;
     g.rad1 = 0.5f * (float)c.dagm_resolution * sqrtf((float)g.W1 * g.W1 + (float)g.H1 * g.H1) + 1.0f;
     if (h->raster_smem > 200 * 1024) return fail(h, SB_EINVAL, "grid too large for the shared-memory bit image");

@@ -479,3 +479,4 @@ k_observe(DCfg c, DMap m, DState s, DObs o, double* __restrict__ trip_wp, const 
 // --------------------------------------------------------------------------------- raster
 // k_raster lives in sb_raster.cuh (row-per-thread exact integer spans).
 #include "sb_raster.cuh"
+

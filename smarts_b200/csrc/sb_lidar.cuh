@@ -48,16 +48,25 @@ struct LTable {
   double max_hlen;             // longest horizontal reach of any ray
 };
 
-__global__ void __launch_bounds__(SB_LIDAR_THREADS, 4)
-k_lidar(DCfg c, DMap m, DState s, DObs o, LTable tab, float reach_xy) {
+// shared-memory working set of one agent's cast (k_sense carves it out of the raster kernel's dynamic buffer)
+struct __align__(16) LidarSmem {
+  LBox boxes[SB_LIDAR_MAX_BOXES];
+  double edges[SB_LIDAR_MAX_EDGES][4];
+  LEntry entries[SB_LIDAR_ENTRIES];
+  int cnt[SB_LIDAR_CHUNK_GROUPS];
+  int n_boxes, n_edges;
+};
+
+// One agent's cast by the whole block (any blockDim.x >= SB_LIDAR_CHUNK_GROUPS).
+__device__ __forceinline__ void d_lidar_agent(const DCfg& c, const DMap& m, const DState& s, const DObs& o,
+                                              const LTable& tab, float reach_xy, int e, int a, LidarSmem* sm) {
   // reach_xy: max_hlen + margin as a float, for the block-level cull
-  __shared__ LBox boxes[SB_LIDAR_MAX_BOXES];
-  __shared__ __align__(16) double edges[SB_LIDAR_MAX_EDGES][4];
-  __shared__ LEntry entries[SB_LIDAR_ENTRIES];
-  __shared__ int cnt[SB_LIDAR_CHUNK_GROUPS];
-  __shared__ int n_boxes, n_edges;
-  int e, a;
-  if (!d_work_agent(c, blockIdx.x, &e, &a)) return;
+  LBox* boxes = sm->boxes;
+  double(*edges)[4] = sm->edges;
+  LEntry* entries = sm->entries;
+  int* cnt = sm->cnt;
+  int& n_boxes = sm->n_boxes;
+  int& n_edges = sm->n_edges;
   const int ai = e * c.A + a, vi = e * c.V + a;
   const double ox = s.pos_x[vi], oy = s.pos_y[vi], oz = s.pos_z[vi] + 1.0;
   if (threadIdx.x == 0) {
@@ -246,4 +255,12 @@ k_lidar(DCfg c, DMap m, DState s, DObs o, LTable tab, float reach_xy) {
       o.lidar_points[w * 3 + 2] = miss;
     }
   }
+}
+
+__global__ void __launch_bounds__(SB_LIDAR_THREADS, 4)
+k_lidar(DCfg c, DMap m, DState s, DObs o, LTable tab, float reach_xy) {
+  __shared__ LidarSmem sm;
+  int e, a;
+  if (!d_work_agent(c, blockIdx.x, &e, &a)) return;
+  d_lidar_agent(c, m, s, o, tab, reach_xy, e, a, &sm);
 }

@@ -31,7 +31,12 @@
 #include "sb_device.cuh"
 
 #define SB_RASTER_THREADS 256
-#define SB_RASTER_ROUND 96  // polygons staged per round: one round in the common case
+#ifndef SB_RASTER_ROUND
+#define SB_RASTER_ROUND 64  // polygons staged per round: one round in the common case
+#endif
+#ifndef SB_RASTER_BLOCKS
+#define SB_RASTER_BLOCKS 4  // resident blocks per SM the register budget is set for
+#endif
 #define SB_RASTER_LIST (SB_RASTER_THREADS + SB_RASTER_ROUND)
 #define SB_RASTER_SMALL_ROWS 64  // polygons up to this many rows go warp-per-polygon, taller ones row-per-thread
 #define SB_RASTER_CLAMP 16777216.0        // 2^24 units = 65536 px
@@ -59,6 +64,7 @@ struct Cam {
 struct RasterDims {
   int32_t W0, H0, W1, H1;        // 0 when the grid is disabled
   int32_t wpr0, wpr1;            // 32-pixel words per row
+  int32_t stride0, stride1;      // words per bit-image row in shared memory: wpr rounded up to 8, + 1 (bank skew)
   int32_t rows0, rows1;          // rows per pass: min(H, 256)
   int32_t n_veh, n_src;          // OGM sources (vehicle slots), all sources (+ map polygons)
   int32_t bits_off, n_bit_words; // byte offset of bit image 0 in dynamic shared memory; words of both images
@@ -71,7 +77,6 @@ struct RasterStage {
   RPolyI hdr[SB_RASTER_ROUND];
   int32_t list[SB_RASTER_LIST];
   int32_t big[SB_RASTER_ROUND];  // staged polygons tall enough for the row-per-thread pass
-  int32_t pre[SB_RASTER_ROUND + 1];  // exclusive prefix of the short polygons' row counts ((polygon, row) pairs)
   int32_t n_list;
   int32_t n_big[2];  // by round parity: the other one is zeroed while a round is being rasterised
   int32_t wide;      // a kept polygon has more than 4 vertices: stage with 8 lanes per polygon instead of 4
@@ -203,11 +208,6 @@ __device__ __forceinline__ void d_stage_phase(const DCfg& c, const DMap& m, cons
   }
 }
 
-// low `t` bits set, t clamped to [0, 32]
-__device__ __forceinline__ uint32_t d_ones_below(int t) {
-  return __funnelshift_lc(0xffffffffu, 0u, (uint32_t)max(t, 0));
-}
-
 // Column span [c0, c1] of staged polygon `li` on row r (c0 > c1: empty).
 __device__ __forceinline__ void d_poly_span(const RasterStage* st, int li, const RPolyI P, int r, int W, int* c0o,
                                             int* c1o) {
@@ -244,92 +244,53 @@ __device__ __forceinline__ void d_poly_span(const RasterStage* st, int li, const
   *c1o = c1;
 }
 
-__device__ __forceinline__ void d_or_span(uint32_t (&w)[8], int lo, int hi1) {
-#pragma unroll
-  for (int j = 0; j < 8; ++j) w[j] |= d_ones_below(hi1 - 32 * j) & ~d_ones_below(lo - 32 * j);
+// OR columns [lo, hi1) (lo < hi1) into a bit-image row in shared memory.  Only the words the span touches are
+// visited (a lane strip is one or two of a row's eight); atomicOr because the short-polygon pass of another warp
+// may be writing the same word.
+__device__ __forceinline__ void d_or_span(uint32_t* row, int lo, int hi1) {
+  const int j0 = lo >> 5, j1 = (hi1 - 1) >> 5;
+  const uint32_t m0 = 0xffffffffu << (lo & 31), m1 = 0xffffffffu >> (31 - ((hi1 - 1) & 31));
+  atomicOr(&row[j0], j0 == j1 ? (m0 & m1) : m0);
+  for (int j = j0 + 1; j <= j1; ++j) atomicOr(&row[j], j == j1 ? m1 : 0xffffffffu);
 }
 
-// Tall polygons: OR their spans on row `r` (columns [cb, cb+256)) into the row's bit words held
-// in registers (every thread owns a row: no atomics).  Returns the images touched (bit per image;
-// uniform over the block).
-__device__ __forceinline__ int d_big_rows(const RasterJob& job, const RasterStage* st, int par, int r, int cb,
-                                          uint32_t (&w0)[8], uint32_t (&w1)[8]) {
+// Tall polygons: OR their spans on row `r` (columns [cb, cb+256)) into the row of the shared-memory bit image
+// (every thread owns a row).
+__device__ __forceinline__ void d_big_rows(const RasterJob& job, const RasterStage* st, int par, int r, int cb,
+                                           uint32_t* row0, uint32_t* row1) {
   const int nbig = st->n_big[par];
-  int touched = 0;
   for (int i = 0; i < nbig; ++i) {
     const int p = st->big[i];
     const RPolyI P = st->hdr[p];
-    touched |= 1 << P.img;
     if (r < P.r0 || r > P.r1) continue;
     int c0, c1;
     d_poly_span(st, p, P, r, job.W[P.img], &c0, &c1);
-    const int lo = max(c0 - cb, 0), hi1 = min(c1 - cb, 255) + 1;
+    const int lo = max(c0, cb), hi1 = min(c1, cb + 255) + 1;
     if (lo >= hi1) continue;
-    if (P.img == 0) d_or_span(w0, lo, hi1);  // warp-uniform
-    else d_or_span(w1, lo, hi1);
+    d_or_span(P.img == 0 ? row0 : row1, lo, hi1);
   }
-  return touched;
 }
 
-// Short polygons (vehicles, junction slivers) are flattened into (polygon, row) pairs so that
-// every lane has a row to do: each warp builds the exclusive prefix of the row counts (all warps
-// write the same values: no block barrier), takes a contiguous chunk of the pairs and walks the
-// prefix forward as its pair index grows.  A span goes into the shared-memory bit image with
-// atomicOr (1-2 words for a vehicle).  Rows [rg, rg+256), columns [cb, cb+256).
-__device__ __forceinline__ void d_small_pairs(const RasterJob& job, RasterStage* st, int count, int rg, int cb,
+// Short polygons (vehicles, junction slivers): a warp per polygon, a lane per row, 32 rows at a time (a car is 19 to
+// 47 rows at 0.1 m per pixel).  The span goes into the shared-memory bit image with atomicOr (one or two words
+// for a vehicle).  Rows [rg, rg+256), columns [cb, cb+256).
+__device__ __forceinline__ void d_small_polys(const RasterJob& job, const RasterStage* st, int count, int rg, int cb,
                                               uint32_t* bits0, uint32_t* bits1, int stride0, int stride1) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  int total = 0;
-  for (int b = 0; b < count; b += 32) {
-    const int li = b + lane;
-    int rows = 0;
-    if (li < count) {
-      const RPolyI P = st->hdr[li];
-      if (P.r1 >= P.r0 && P.r1 - P.r0 + 1 <= SB_RASTER_SMALL_ROWS)
-        rows = max(min((int)P.r1, rg + SB_RASTER_THREADS - 1) - max((int)P.r0, rg) + 1, 0);
-    }
-    int inc = rows;
-#pragma unroll
-    for (int off = 1; off < 32; off <<= 1) {
-      const int t = __shfl_up_sync(SB_FULL_MASK, inc, off);
-      if (lane >= off) inc += t;
-    }
-    if (li < count) st->pre[li] = total + inc - rows;
-    total += __shfl_sync(SB_FULL_MASK, inc, 31);
-  }
-  if (lane == 0) st->pre[count] = total;
-  __syncwarp();
-  if (total == 0) return;
-  const int chunk = (((total + SB_RASTER_THREADS / 32 - 1) / (SB_RASTER_THREADS / 32)) + 31) & ~31;
-  const int t_begin = warp * chunk, t_end = min(total, t_begin + chunk);
-  if (t_begin >= t_end) return;
-  int cursor = 0;  // largest li with pre[li] <= t_begin
-  for (int step = 64; step >= 1; step >>= 1) {
-    const int q = cursor + step;
-    if (q < count && st->pre[q] <= t_begin) cursor = q;
-  }
-  for (int t0 = t_begin; t0 < t_end; t0 += 32) {
-    const int t = t0 + lane;
-    const bool act = t < t_end;
-    int li = cursor;
-    if (act) {
-      while (st->pre[li + 1] <= t) ++li;  // t < total = pre[count]: stops at li <= count - 1
-      const RPolyI P = st->hdr[li];
-      const int r = max((int)P.r0, rg) + (t - st->pre[li]);
+  for (int li = warp; li < count; li += SB_RASTER_THREADS / 32) {
+    const RPolyI P = st->hdr[li];
+    if (P.r1 < P.r0 || P.r1 - P.r0 + 1 > SB_RASTER_SMALL_ROWS) continue;  // (same for the whole warp)
+    const int ra = max((int)P.r0, rg), rb = min((int)P.r1, rg + SB_RASTER_THREADS - 1);
+    const int W = job.W[P.img];
+    uint32_t* img = P.img == 0 ? bits0 - rg * stride0 : bits1 - rg * stride1;
+    const int stride = P.img == 0 ? stride0 : stride1;
+    for (int r = ra + lane; r <= rb; r += 32) {
       int c0, c1;
-      d_poly_span(st, li, P, r, job.W[P.img], &c0, &c1);
+      d_poly_span(st, li, P, r, W, &c0, &c1);
       c0 = max(c0, cb);
       c1 = min(c1, cb + 255);
-      if (c0 <= c1) {
-        uint32_t* row = (P.img == 0 ? bits0 + (r - rg) * stride0 : bits1 + (r - rg) * stride1);
-        const int j0 = c0 >> 5, j1 = c1 >> 5;
-        for (int j = j0; j <= j1; ++j) {
-          const uint32_t mk = d_ones_below(c1 + 1 - 32 * j) & ~d_ones_below(c0 - 32 * j);
-          atomicOr(&row[j], mk);
-        }
-      }
+      if (c0 <= c1) d_or_span(img + r * stride, c0, c1 + 1);
     }
-    cursor = __shfl_sync(SB_FULL_MASK, li, 31);
   }
 }
 
@@ -398,14 +359,11 @@ __device__ __forceinline__ void d_store_rows(const uint32_t* bits, const uint2* 
 #define SB_RASTER_LUT_BYTES 2048
 
 // Dynamic shared memory: [byte-expansion table | staging area | bit image 0 | bit image 1]
-// (bit images: min(H, 256) rows of W/32 + 1 words).  Sized by sb_create in sb_api.cu.
-__global__ void __launch_bounds__(SB_RASTER_THREADS, 4)
-k_raster(DCfg c, DMap m, DState s, DObs o, RasterDims g) {
-  extern __shared__ __align__(16) unsigned char smem[];
+// (bit images: min(H, 256) rows of RasterDims::stride words).  Sized by sb_create in sb_api.cu.
+__device__ __forceinline__ void d_raster_agent(const DCfg& c, const DMap& m, const DState& s, const DObs& o,
+                                               const RasterDims& g, int e, int a, unsigned char* smem) {
   uint2* lut = reinterpret_cast<uint2*>(smem);
   RasterStage* st = reinterpret_cast<RasterStage*>(smem + SB_RASTER_LUT_BYTES);
-  int e, a;
-  if (!d_work_agent(c, blockIdx.x, &e, &a)) return;
   const int ai = e * c.A + a, vi = e * c.V + a;
   const double px = s.pos_x[vi], py = s.pos_y[vi], ch = s.cos_h[vi], sh = s.sin_h[vi];
   // the job record is indexed by image at run time: it lives in shared memory (a per-thread copy
@@ -429,7 +387,8 @@ k_raster(DCfg c, DMap m, DState s, DObs o, RasterDims g) {
   const int Hmax = max(H0, H1), Wmax = max(W0, W1);
   const int wpr0 = g.wpr0, wpr1 = g.wpr1;
   uint32_t* bits0 = reinterpret_cast<uint32_t*>(smem + g.bits_off);
-  uint32_t* bits1 = bits0 + g.rows0 * (wpr0 + 1);
+  const int stride0 = g.stride0, stride1 = g.stride1;
+  uint32_t* bits1 = bits0 + g.rows0 * stride0;
   const int n_bit_words = g.n_bit_words;
   const float rad0 = g.rad0, rad1 = g.rad1;
   const float fx = (float)px, fy = (float)py;
@@ -437,16 +396,16 @@ k_raster(DCfg c, DMap m, DState s, DObs o, RasterDims g) {
 
   for (int rg = 0; rg < Hmax; rg += SB_RASTER_THREADS) {
     const int r = rg + threadIdx.x;
-    for (int i = threadIdx.x; i < n_bit_words; i += SB_RASTER_THREADS) bits0[i] = 0u;
+    for (int i = threadIdx.x; i * 4 < n_bit_words; i += SB_RASTER_THREADS)  // (the buffer is padded to 16 bytes)
+      reinterpret_cast<uint4*>(bits0)[i] = make_uint4(0u, 0u, 0u, 0u);
     for (int cb = 0; cb < Wmax; cb += 256) {
-      uint32_t w0[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u}, w1[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
       if (threadIdx.x == 0) {
         st->n_list = 0;
         st->n_big[0] = 0;
         st->wide = 0;
       }
       __syncthreads();
-      int par = 0, touched = 0;
+      int par = 0;
       for (int base = 0; base < n_src; base += SB_RASTER_THREADS) {
         const int p = base + threadIdx.x;
         bool keep = false;
@@ -476,8 +435,8 @@ k_raster(DCfg c, DMap m, DState s, DObs o, RasterDims g) {
           else d_stage_phase<4>(c, m, s, e, job, st, n_list - count, count, par);
           __syncthreads();
           if (threadIdx.x == 0) st->n_big[par ^ 1] = 0;
-          d_small_pairs(job, st, count, rg, cb, bits0, bits1, wpr0 + 1, wpr1 + 1);
-          touched |= d_big_rows(job, st, par, r, cb, w0, w1);
+          d_small_polys(job, st, count, rg, cb, bits0, bits1, stride0, stride1);
+          d_big_rows(job, st, par, r, cb, bits0 + threadIdx.x * stride0, bits1 + threadIdx.x * stride1);
           n_list -= count;
           par ^= 1;
           __syncthreads();
@@ -487,29 +446,22 @@ k_raster(DCfg c, DMap m, DState s, DObs o, RasterDims g) {
           __syncthreads();
         }
       }
-      // merge the register rows of the tall polygons (all atomics are behind the last barrier)
-      if ((touched & 1) && r < H0 && cb < W0) {
-        uint32_t* row = bits0 + threadIdx.x * (wpr0 + 1) + (cb >> 5);
-        const int nw = min(8, wpr0 - (cb >> 5));
-#pragma unroll
-        for (int k = 0; k < 8; ++k)
-          if (k < nw && w0[k]) row[k] |= w0[k];
-      }
-      if ((touched & 2) && r < H1 && cb < W1) {
-        uint32_t* row = bits1 + threadIdx.x * (wpr1 + 1) + (cb >> 5);
-        const int nw = min(8, wpr1 - (cb >> 5));
-#pragma unroll
-        for (int k = 0; k < 8; ++k)
-          if (k < nw && w1[k]) row[k] |= w1[k];
-      }
     }
     __syncthreads();
     if (rg < H0)
       d_store_rows(bits0, lut, o.ogm + (size_t)ai * W0 * H0 + (size_t)rg * W0, min(H0 - rg, SB_RASTER_THREADS), wpr0,
-                   wpr0 + 1);
+                   stride0);
     if (rg < H1)
       d_store_rows(bits1, lut, o.dagm + (size_t)ai * W1 * H1 + (size_t)rg * W1, min(H1 - rg, SB_RASTER_THREADS), wpr1,
-                   wpr1 + 1);
+                   stride1);
     if (rg + SB_RASTER_THREADS < Hmax) __syncthreads();
   }
+}
+
+__global__ void __launch_bounds__(SB_RASTER_THREADS, SB_RASTER_BLOCKS)
+k_raster(DCfg c, DMap m, DState s, DObs o, RasterDims g) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  int e, a;
+  if (!d_work_agent(c, blockIdx.x, &e, &a)) return;
+  d_raster_agent(c, m, s, o, g, e, a, smem);
 }

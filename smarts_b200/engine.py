@@ -16,7 +16,8 @@ from . import _abi
 from .road_map import RoadMapData
 
 _LIB = None
-_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libsmartsb200.so")
+# SMARTS_B200_LIB: a variant build of the same sources (kernel A/B experiments, profiles/README.md)
+_LIB_PATH = os.environ.get("SMARTS_B200_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "libsmartsb200.so")
 
 EXPORTS = [
     "sb_abi_version", "sb_create", "sb_destroy", "sb_upload_map", "sb_upload_lidar_rays", "sb_reset",
