@@ -344,7 +344,13 @@ def measure(w, E, W_, K, local, rank, world, dist):
     sampler = ClockSampler(local)
     ms, launches, _ = g.timed(W_, K, dist if world > 1 else None, False, sampler)
     clocks = sampler.stop()
-    ms_kt, _, ktimes = g.timed(W_ + K, K, None, True)
+    # the same ticks again (reset, warm-up, K ticks) with per-kernel events: the scene of tick t is the same scene
+    g.eng.reset(*g.init)
+    if g.traj:
+        g.eng.observe()
+    for t in range(W_):
+        g.tick(t)
+    ms_kt, _, ktimes = g.timed(W_, K, None, True)
     stats = torch.tensor([ms, float(E * g.A * K)], dtype=torch.float64, device="cuda")
     total = float(E * g.A * K)
     if world > 1:  # max time over ranks; episode statistics (agent-steps) summed -- the only collectives
@@ -386,13 +392,15 @@ def measure_e2e(g, Ke, world, dist):
     # by host threads inside the call; every other buffer is copied as is
     d2h = sum(t.numel() * t.element_size() // (8 if k in ("ogm", "dagm") else 1) for k, t in host_obs.items())
 
+    copy_kw = {}
+
     def policy_host():
         if g.traj:
             trajectory_from_obs_numpy({k: host_obs[k].numpy().reshape((E, A) + tuple(host_obs[k].shape[1:]))
                                        for k in ("wp_len", "wp_pos", "wp_heading")}, act_host.numpy())
 
     def run(t_base):
-        eng.step_host(act_host.numpy(), soc_host[t_base % g.T].numpy()); eng.copy_obs_to_host(host_obs)  # warm
+        eng.step_host(act_host.numpy(), soc_host[t_base % g.T].numpy()); eng.copy_obs_to_host(host_obs, **copy_kw)  # warm
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
@@ -400,7 +408,7 @@ def measure_e2e(g, Ke, world, dist):
         for t in range(Ke):
             policy_host()
             eng.step_host(act_host.numpy(), soc_host[(t_base + t + 1) % g.T].numpy())
-            eng.copy_obs_to_host(host_obs)
+            eng.copy_obs_to_host(host_obs, **copy_kw)
         torch.cuda.synchronize()
         e2e_t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
         if world > 1:
@@ -411,11 +419,20 @@ def measure_e2e(g, Ke, world, dist):
     eng.set_incremental_host_grids(True)
     inc = run(Ke + 1)
     eng.set_incremental_host_grids(False)
+    packed = None
+    if "ogm" in host_obs or "dagm" in host_obs:  # the same call with the grids left as 1-bit images
+        host_obs = eng.host_obs_buffers(pinned=True, packed_grids=True)
+        copy_kw["packed"] = True
+        packed = run(2 * Ke + 2)
+        packed_bytes = sum(t.numel() * t.element_size() for t in host_obs.values())
     return {"value": full, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
             "host_obs_bytes_per_step": obs_host_bytes, "steps": Ke, "value_incremental": inc,
+            "value_packed": packed, "host_obs_bytes_per_step_packed": packed_bytes if packed else None,
             "transport": "grids bit-packed over PCIe, widened to uint8 in host memory by the library; value = every "
                          "byte of every buffer rewritten per call; value_incremental = persistent pinned destination "
-                         "buffers, only the 64-pixel words that changed since the previous call rewritten"}
+                         "buffers, only the 64-pixel words that changed since the previous call rewritten; "
+                         "value_packed = sb_copy_obs_to_host_packed, the grids delivered as 1-bit images "
+                         "(numpy.unpackbits layout), everything else identical"}
 
 
 def cpu_baseline(w, A):

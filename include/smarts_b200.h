@@ -300,6 +300,15 @@ int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs *host_dst);
  * or on = 0 -> 1 makes the next call a full write.  (hiway_env.py:216-263: the reference allocates fresh arrays
  * per step; a vectorised env that keeps its pinned staging buffers is the use case.) */
 int sb_set_incremental_host_grids(SbHandle h, int on);
+/* sb_copy_obs_to_host with the grids delivered as the 1-bit image instead of uint8: host_dst->ogm / ->dagm point to
+ * W*H/8 bytes per agent, row-major, bit (i & 7) of byte (i >> 3) = pixel i of the [H, W] image (set = 255), i.e.
+ * numpy.unpackbits(buf.reshape(n, H, W // 8), axis=-1, bitorder="little") * 255 is the uint8 image
+ * sb_copy_obs_to_host delivers (widths are multiples of 32).  The uint8 widening is 8x the host-memory write
+ * volume of everything else in the call and is its bound (profiles/README.md); a consumer that keeps grids
+ * packed (a frame stack, a replay buffer, a policy whose first layer unpacks on its own device) should not
+ * pay for it.  Every other member as in sb_copy_obs_to_host.  (Replaces the np.array(...) conversions of
+ * smarts/core/sensors.py:706-716, :748-758 on the delivery side.) */
+int sb_copy_obs_to_host_packed(SbHandle h, const SbObsPtrs *host_dst);
 int sb_get_obs(SbHandle h, SbObsPtrs *out);
 int sb_get_state(SbHandle h, SbStatePtrs *out);
 /* number of kernel launches issued by this handle so far (bench gpu_launches) */

@@ -378,16 +378,24 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
   h->allocs.push_back(da);
   h->d_actions = da;
   {  // k_raster shared memory: table | staging area | bit image 0 | bit image 1
-    auto rows256 = [](int hh) { return (size_t)(hh < SB_RASTER_THREADS ? hh : SB_RASTER_THREADS); };
+    // grids of at most 128 rows: 256 / T agents per block, T threads each (k_raster_slices)
+    int hmax = 0;
+    if (c.ogm_enable) hmax = c.ogm_height;
+    if (c.dagm_enable && c.dagm_height > hmax) hmax = c.dagm_height;
+    const int T = hmax <= 32 ? 32 : hmax <= 64 ? 64 : hmax <= 128 ? 128 : SB_RASTER_THREADS;
+    auto rows256 = [T](int hh) { return (size_t)(hh < T ? hh : T); };
     auto row_words = [](int ww) { return (size_t)((ww / 32 + 7) / 8 * 8 + 1); };
     size_t b0 = c.ogm_enable ? row_words(c.ogm_width) * 4 * rows256(c.ogm_height) : 0;
     size_t b1 = c.dagm_enable ? row_words(c.dagm_width) * 4 * rows256(c.dagm_height) : 0;
     int wmax = 0;
     if (c.ogm_enable) wmax = c.ogm_width;
     if (c.dagm_enable && c.dagm_width > wmax) wmax = c.dagm_width;
-    size_t stage = (sizeof(RasterStage) + 15) / 16 * 16;
+    size_t stage = T == 32 ? sizeof(RasterStageT<32, SB_RASTER_SLICE_ROUND>) : T == 64 ? sizeof(RasterStageT<64, SB_RASTER_SLICE_ROUND>)
+                   : T == 128 ? sizeof(RasterStageT<128, SB_RASTER_SLICE_ROUND>) : sizeof(RasterStage);
+    stage = (stage + 15) / 16 * 16;
     (void)wmax;
-    h->raster_smem = SB_RASTER_LUT_BYTES + stage + (b0 + b1 + 15) / 16 * 16;
+    const size_t slice_bytes = stage + (b0 + b1 + 15) / 16 * 16;
+    h->raster_smem = SB_RASTER_LUT_BYTES + (SB_RASTER_THREADS / T) * slice_bytes;
     RasterDims& g = h->raster_dims;
     g.W0 = c.ogm_enable ? c.ogm_width : 0;
     g.H0 = c.ogm_enable ? c.ogm_height : 0;
@@ -399,14 +407,18 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
     g.rows1 = (int)rows256(g.H1);
     g.n_veh = c.ogm_enable ? d.V : 0;
     g.n_src = g.n_veh;  // + map polygons once the map is uploaded (sb_upload_map)
-    g.bits_off = (int)(SB_RASTER_LUT_BYTES + stage);
+    g.bits_off = (int)stage;
+    g.slice_threads = T;
+    g.slice_bytes = (int)slice_bytes;
     g.stride0 = g.W0 ? (int)row_words(g.W0) : 0;
     g.stride1 = g.W1 ? (int)row_words(g.W1) : 0;
     g.n_bit_words = g.rows0 * g.stride0 + g.rows1 * g.stride1;
     g.rad0 = 0.5f * (float)c.ogm_resolution * sqrtf((float)g.W0 * g.W0 + (float)g.H0 * g.H0) + 1.0f;
     g.rad1 = 0.5f * (float)c.dagm_resolution * sqrtf((float)g.W1 * g.W1 + (float)g.H1 * g.H1) + 1.0f;
     if (h->raster_smem > 200 * 1024) return fail(h, SB_EINVAL, "grid too large for the shared-memory bit image");
-    if (!cuda_ok(h, cudaFuncSetAttribute(k_raster, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->raster_smem),
+    const void* fn = T == 32 ? (const void*)k_raster_slices<32> : T == 64 ? (const void*)k_raster_slices<64>
+                     : T == 128 ? (const void*)k_raster_slices<128> : (const void*)k_raster;
+    if (!cuda_ok(h, cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->raster_smem),
                  "cudaFuncSetAttribute"))
       return SB_ECUDA;
   }
@@ -857,7 +869,16 @@ int sb_observe_envs(SbHandle h, const int32_t* env_ids, int32_t n, void* stream)
   }
   if (c.ogm_enable || c.dagm_enable) {
     LaunchScope ls(h, SB_K_RASTER, st);
-    k_raster<<<na, SB_RASTER_THREADS, h->raster_smem, st>>>(c, h->dmap, h->st, h->ob, h->raster_dims);
+    const RasterDims& g = h->raster_dims;
+    const int per = SB_RASTER_THREADS / g.slice_threads, nb = (na + per - 1) / per;
+    if (g.slice_threads == 32)
+      k_raster_slices<32><<<nb, SB_RASTER_THREADS, h->raster_smem, st>>>(c, h->dmap, h->st, h->ob, g, na);
+    else if (g.slice_threads == 64)
+      k_raster_slices<64><<<nb, SB_RASTER_THREADS, h->raster_smem, st>>>(c, h->dmap, h->st, h->ob, g, na);
+    else if (g.slice_threads == 128)
+      k_raster_slices<128><<<nb, SB_RASTER_THREADS, h->raster_smem, st>>>(c, h->dmap, h->st, h->ob, g, na);
+    else
+      k_raster<<<na, SB_RASTER_THREADS, h->raster_smem, st>>>(c, h->dmap, h->st, h->ob, g);
   }
   if (c.events_enable) {
     LaunchScope ls(h, SB_K_EVENTS, st);
@@ -895,7 +916,13 @@ int sb_step_host(SbHandle h, const void* host_actions, int64_t n_bytes, const do
   return cuda_ok(h, cudaStreamSynchronize(0), "sb_step_host sync") ? SB_OK : SB_ECUDA;
 }
 
-int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs* dst) {
+static int copy_obs_to_host(SbHandle h, const SbObsPtrs* dst, bool packed_dst);
+
+int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs* dst) { return copy_obs_to_host(h, dst, false); }
+
+int sb_copy_obs_to_host_packed(SbHandle h, const SbObsPtrs* dst) { return copy_obs_to_host(h, dst, true); }
+
+static int copy_obs_to_host(SbHandle h, const SbObsPtrs* dst, bool packed_dst) {
   if (!h || !dst) return SB_EINVAL;
   if (h->cuda_err) return SB_ECUDA;
   const SbConfig& c = h->cfg;
@@ -925,7 +952,7 @@ int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs* dst) {
     const double v = atof(sh);
     h->xfer_frac = v < 0.0 ? 0.0 : (v > 1.0 ? 1.0 : v);
   }
-  const size_t n_packed = std::min(na, (size_t)llround(h->xfer_frac * (double)na));
+  const size_t n_packed = packed_dst ? na : std::min(na, (size_t)llround(h->xfer_frac * (double)na));
   if (c.ogm_enable && dst->ogm) jobs[nj++] = {o.ogm, dst->ogm, n_packed * c.ogm_width * c.ogm_height};
   if (c.dagm_enable && dst->dagm) jobs[nj++] = {o.dagm, dst->dagm, n_packed * c.dagm_width * c.dagm_height};
   const auto t0 = std::chrono::steady_clock::now();
@@ -944,7 +971,7 @@ int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs* dst) {
       h->bits_bytes = need;
     }
     bool diff = false;  // incremental: same destinations and sizes as the previous call, written by this library
-    if (h->incremental) {
+    if (h->incremental && !packed_dst) {
       if (h->prev_bytes < need) {
         std::free(h->h_prev);
         h->h_prev = static_cast<uint8_t*>(std::malloc(need));
@@ -962,7 +989,7 @@ int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs* dst) {
       }
     }
     h->xfer_diff = diff;
-    if (!h->pool) {  // host threads: the cores of this box shared by the ranks of a torchrun launch
+    if (!h->pool && !packed_dst) {  // host threads: the cores of this box shared by the ranks of a torchrun launch
       unsigned hc = std::thread::hardware_concurrency();
       const char* lws = getenv("LOCAL_WORLD_SIZE");
       const int ranks = lws && atoi(lws) > 0 ? atoi(lws) : 1;
@@ -980,6 +1007,11 @@ int sb_copy_obs_to_host(SbHandle h, const SbObsPtrs* dst) {
       {
         LaunchScope ls(h, SB_K_PACK, 0);
         k_pack_bits<<<(unsigned)((words + 255) / 256), 256>>>(jobs[j].dev, h->d_bits + off / 4, words);
+      }
+      if (packed_dst) {  // the bit image is the delivery: one copy into the caller's buffer, nothing to widen
+        cpy(jobs[j].host, reinterpret_cast<const uint8_t*>(h->d_bits) + off, words * 4);
+        off += words * 4;
+        continue;
       }
       for (size_t c0 = 0; c0 < words * 4 && ok; c0 += chunk) {
         const size_t len = words * 4 - c0 < chunk ? words * 4 - c0 : chunk;

@@ -37,7 +37,7 @@
 #ifndef SB_RASTER_BLOCKS
 #define SB_RASTER_BLOCKS 4  // resident blocks per SM the register budget is set for
 #endif
-#define SB_RASTER_LIST (SB_RASTER_THREADS + SB_RASTER_ROUND)
+#define SB_RASTER_SLICE_ROUND 32  // ... per round of a slice of k_raster_slices (small grids: four staging areas per block)
 #define SB_RASTER_SMALL_ROWS 64  // polygons up to this many rows go warp-per-polygon, taller ones row-per-thread
 #define SB_RASTER_CLAMP 16777216.0        // 2^24 units = 65536 px
 #define SB_RASTER_FAST_LIMIT 536870912.0  // 2^29
@@ -65,22 +65,27 @@ struct RasterDims {
   int32_t W0, H0, W1, H1;        // 0 when the grid is disabled
   int32_t wpr0, wpr1;            // 32-pixel words per row
   int32_t stride0, stride1;      // words per bit-image row in shared memory: wpr rounded up to 8, + 1 (bank skew)
-  int32_t rows0, rows1;          // rows per pass: min(H, 256)
+  int32_t rows0, rows1;          // rows per pass: min(H, slice_threads)
   int32_t n_veh, n_src;          // OGM sources (vehicle slots), all sources (+ map polygons)
-  int32_t bits_off, n_bit_words; // byte offset of bit image 0 in dynamic shared memory; words of both images
+  int32_t bits_off, n_bit_words; // byte offset of bit image 0 in a slice's buffer; words of both images
+  int32_t slice_threads, slice_bytes;  // threads per agent (256: block per agent) and bytes of one slice's buffer
   float rad0, rad1;              // world-space cull radii: the film's half diagonal + 1 m
 };
 
 // staging area of one round of polygons
-struct RasterStage {
-  REdgeI edges[SB_RASTER_ROUND][SB_MAX_POLY_VERTS];
-  RPolyI hdr[SB_RASTER_ROUND];
-  int32_t list[SB_RASTER_LIST];
-  int32_t big[SB_RASTER_ROUND];  // staged polygons tall enough for the row-per-thread pass
+template <int T, int R>  // T threads cull into the list, R polygons are staged per round
+struct RasterStageT {
+  static constexpr int ROUND = R;
+  REdgeI edges[R][SB_MAX_POLY_VERTS];
+  RPolyI hdr[R];
+  int32_t list[T + R];
+  int32_t big[R];  // staged polygons tall enough for the row-per-thread pass
   int32_t n_list;
   int32_t n_big[2];  // by round parity: the other one is zeroed while a round is being rasterised
   int32_t wide;      // a kept polygon has more than 4 vertices: stage with 8 lanes per polygon instead of 4
 };
+
+using RasterStage = RasterStageT<SB_RASTER_THREADS, SB_RASTER_ROUND>;
 
 __device__ __forceinline__ void d_to_pixel(const Cam& cam, double x, double y, double* U, double* V) {
   double dx = x - cam.px, dy = y - cam.py;
@@ -107,12 +112,13 @@ struct RasterJob {
 // consecutive lanes of one warp, so the polygon never leaves the register file: world -> snapped pixel coordinates
 // per lane, neighbour vertex / signed area / bounding box by shuffles inside the group of 8, then
 // each lane writes the record of edge k -> k+1 (integer edge function + 32.32 crossing line).
-template <int G>
+template <int G, int T, class ST>
 __device__ __forceinline__ void d_stage_phase(const DCfg& c, const DMap& m, const DState& s, int e,
-                                              const RasterJob& job, RasterStage* st, int first, int count, int par) {
-  const int lane = threadIdx.x & 31, gbase = lane & ~(G - 1);
-  for (int it = 0; it * SB_RASTER_THREADS < count * G; ++it) {
-    const int slot = threadIdx.x + it * SB_RASTER_THREADS;
+                                              const RasterJob& job, ST* st, int first, int count, int par,
+                                              int tid) {
+  const int lane = tid & 31, gbase = lane & ~(G - 1);
+  for (int it = 0; it * T < count * G; ++it) {
+    const int slot = tid + it * T;
     const int li = slot / G, k = slot % G;
     int n = 0, img = 0;
     double x = 0.0, y = 0.0;
@@ -209,7 +215,8 @@ __device__ __forceinline__ void d_stage_phase(const DCfg& c, const DMap& m, cons
 }
 
 // Column span [c0, c1] of staged polygon `li` on row r (c0 > c1: empty).
-__device__ __forceinline__ void d_poly_span(const RasterStage* st, int li, const RPolyI P, int r, int W, int* c0o,
+template <class ST>
+__device__ __forceinline__ void d_poly_span(const ST* st, int li, const RPolyI P, int r, int W, int* c0o,
                                             int* c1o) {
   const int r256 = r << 8;
   const REdgeI* e = st->edges[li];
@@ -256,7 +263,8 @@ __device__ __forceinline__ void d_or_span(uint32_t* row, int lo, int hi1) {
 
 // Tall polygons: OR their spans on row `r` (columns [cb, cb+256)) into the row of the shared-memory bit image
 // (every thread owns a row).
-__device__ __forceinline__ void d_big_rows(const RasterJob& job, const RasterStage* st, int par, int r, int cb,
+template <class ST>
+__device__ __forceinline__ void d_big_rows(const RasterJob& job, const ST* st, int par, int r, int cb,
                                            uint32_t* row0, uint32_t* row1) {
   const int nbig = st->n_big[par];
   for (int i = 0; i < nbig; ++i) {
@@ -271,20 +279,21 @@ __device__ __forceinline__ void d_big_rows(const RasterJob& job, const RasterSta
   }
 }
 
-// Short polygons (vehicles, junction slivers): a warp per polygon, a lane per row, 32 rows at a time (a car is 19 to
-// 47 rows at 0.1 m per pixel).  The span goes into the shared-memory bit image with atomicOr (one or two words
-// for a vehicle).  Rows [rg, rg+256), columns [cb, cb+256).
-__device__ __forceinline__ void d_small_polys(const RasterJob& job, const RasterStage* st, int count, int rg, int cb,
-                                              uint32_t* bits0, uint32_t* bits1, int stride0, int stride1) {
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int li = warp; li < count; li += SB_RASTER_THREADS / 32) {
+// Short polygons (vehicles, junction slivers): GS lanes per polygon, a lane per row, GS rows at a time (a car is
+// 19 to 47 rows at 0.1 m per pixel: a warp per polygon; 3 to 7 rows on a 64 x 64 grid over 50 m: eight lanes).  The span goes into the
+// shared-memory bit image with atomicOr (one or two words for a vehicle).  Rows [rg, rg+T), columns [cb, cb+256).
+template <int T, class ST>
+__device__ __forceinline__ void d_small_polys(const RasterJob& job, const ST* st, int count, int rg, int cb,
+                                              uint32_t* bits0, uint32_t* bits1, int stride0, int stride1, int tid) {
+  constexpr int GS = T == SB_RASTER_THREADS ? 32 : 8;
+  for (int li = tid / GS; li < count; li += T / GS) {
     const RPolyI P = st->hdr[li];
-    if (P.r1 < P.r0 || P.r1 - P.r0 + 1 > SB_RASTER_SMALL_ROWS) continue;  // (same for the whole warp)
-    const int ra = max((int)P.r0, rg), rb = min((int)P.r1, rg + SB_RASTER_THREADS - 1);
+    if (P.r1 < P.r0 || P.r1 - P.r0 + 1 > SB_RASTER_SMALL_ROWS) continue;
+    const int ra = max((int)P.r0, rg), rb = min((int)P.r1, rg + T - 1);
     const int W = job.W[P.img];
     uint32_t* img = P.img == 0 ? bits0 - rg * stride0 : bits1 - rg * stride1;
     const int stride = P.img == 0 ? stride0 : stride1;
-    for (int r = ra + lane; r <= rb; r += 32) {
+    for (int r = ra + (tid & (GS - 1)); r <= rb; r += GS) {
       int c0, c1;
       d_poly_span(st, li, P, r, W, &c0, &c1);
       c0 = max(c0, cb);
@@ -301,22 +310,23 @@ __device__ __forceinline__ uint32_t d_expand4(uint32_t b) {  // low 4 bits -> 4 
 // rows x W bit image (stride words per row in shared memory) -> byte image; one 32-pixel word
 // per thread per step, written with a single 256-bit store.  A warp whose 32 words are all
 // 0 or all ~0 (most of an occupancy grid) skips the table.
+template <int T>
 __device__ __forceinline__ void d_store_rows(const uint32_t* bits, const uint2* lut, uint8_t* dst, int rows, int wpr,
-                                             int stride) {
+                                             int stride, int tid) {
   const int n_words = rows * wpr;
-  if ((wpr & (wpr - 1)) == 0 && wpr <= SB_RASTER_THREADS && (n_words & (SB_RASTER_THREADS - 1)) == 0) {
+  if ((wpr & (wpr - 1)) == 0 && wpr <= T && (n_words & (T - 1)) == 0) {
     // Common shapes (W a power of two up to 8192 px, rows * W/32 a multiple of 256): this thread's word keeps
     // its column and moves 256 / wpr rows per step, every thread is active in every step -- no index
     // carry, no tail predicate, and four steps' shared-memory loads are issued before their stores.
     const int sh = __ffs(wpr) - 1;
-    const uint32_t* src = bits + (threadIdx.x >> sh) * stride + (threadIdx.x & (wpr - 1));
-    const int dsrc = (SB_RASTER_THREADS >> sh) * stride;
-    uint8_t* p = dst + (size_t)threadIdx.x * 32;
-    const int iters = n_words / SB_RASTER_THREADS;
+    const uint32_t* src = bits + (tid >> sh) * stride + (tid & (wpr - 1));
+    const int dsrc = (T >> sh) * stride;
+    uint8_t* p = dst + (size_t)tid * 32;
+    const int iters = n_words / T;
 #pragma unroll 4
     for (int k = 0; k < iters; ++k) {
       const uint32_t word = src[k * dsrc];
-      uint8_t* q = p + (size_t)k * (SB_RASTER_THREADS * 32);
+      uint8_t* q = p + (size_t)k * (T * 32);
       if (__all_sync(SB_FULL_MASK, word + 1u <= 1u)) {
         asm volatile("st.global.v8.b32 [%0], {%1,%1,%1,%1,%1,%1,%1,%1};" ::"l"(q), "r"(word) : "memory");
       } else {
@@ -329,12 +339,12 @@ __device__ __forceinline__ void d_store_rows(const uint32_t* bits, const uint2* 
     return;
   }
   // running (row, word-in-row) of this thread's word: 256 words further every step
-  int row = threadIdx.x / wpr, j = threadIdx.x - row * wpr;
-  const int drow = SB_RASTER_THREADS / wpr, dj = SB_RASTER_THREADS - drow * wpr;
+  int row = tid / wpr, j = tid - row * wpr;
+  const int drow = T / wpr, dj = T - drow * wpr;
   const uint32_t* src = bits + row * stride + j;
   const int dsrc = drow * stride + dj;
-  uint8_t* p = dst + (size_t)threadIdx.x * 32;
-  for (int i = threadIdx.x; i - (int)threadIdx.x < n_words; i += SB_RASTER_THREADS) {
+  uint8_t* p = dst + (size_t)tid * 32;
+  for (int i = tid; i - tid < n_words; i += T) {
     const bool act = i < n_words;
     const uint32_t word = act ? *src : 0u;
     if (__all_sync(SB_FULL_MASK, word + 1u <= 1u)) {
@@ -346,7 +356,7 @@ __device__ __forceinline__ void d_store_rows(const uint32_t* bits, const uint2* 
                    "r"(b.y), "r"(c.x), "r"(c.y), "r"(d.x), "r"(d.y)
                    : "memory");
     }
-    p += SB_RASTER_THREADS * 32;
+    p += T * 32;
     j += dj;
     src += dsrc;
     if (j >= wpr) {  // carry into the next row (never taken when wpr divides 256)
@@ -360,16 +370,25 @@ __device__ __forceinline__ void d_store_rows(const uint32_t* bits, const uint2* 
 
 // Dynamic shared memory: [byte-expansion table | staging area | bit image 0 | bit image 1]
 // (bit images: min(H, 256) rows of RasterDims::stride words).  Sized by sb_create in sb_api.cu.
+// T threads (a whole block, or one of its 256 / T slices for grids of at most 128 rows: barrier `bar` is the
+// slice's own) rasterise both grids of agent (e, a).  `lut` is the block's byte-expansion table, `buf` the
+// slice's [staging area | bit image 0 | bit image 1].
+template <int T>
+__device__ __forceinline__ void d_slice_sync(int bar) {
+  if (T == SB_RASTER_THREADS) __syncthreads();
+  else asm volatile("bar.sync %0, %1;" ::"r"(bar), "n"(T) : "memory");
+}
+
+template <int T, class ST>
 __device__ __forceinline__ void d_raster_agent(const DCfg& c, const DMap& m, const DState& s, const DObs& o,
-                                               const RasterDims& g, int e, int a, unsigned char* smem) {
-  uint2* lut = reinterpret_cast<uint2*>(smem);
-  RasterStage* st = reinterpret_cast<RasterStage*>(smem + SB_RASTER_LUT_BYTES);
+                                               const RasterDims& g, int e, int a, const uint2* lut, unsigned char* buf,
+                                               RasterJob& sjob, int tid, int bar) {
+  ST* st = reinterpret_cast<ST*>(buf);
   const int ai = e * c.A + a, vi = e * c.V + a;
   const double px = s.pos_x[vi], py = s.pos_y[vi], ch = s.cos_h[vi], sh = s.sin_h[vi];
   // the job record is indexed by image at run time: it lives in shared memory (a per-thread copy
   // would go to local memory -- 144 B x 256 threads x 16 384 CTAs of extra DRAM write traffic)
-  __shared__ RasterJob sjob;
-  if (threadIdx.x == 0) {
+  if (tid == 0) {
     RasterJob& j = sjob;
     j.on[0] = g.W0 != 0;  // sensors.py:719-758: vehicles only, ego included
     j.on[1] = g.W1 != 0;  // sensors.py:675-716: road surface only
@@ -386,28 +405,27 @@ __device__ __forceinline__ void d_raster_agent(const DCfg& c, const DMap& m, con
   const int W0 = g.W0, H0 = g.H0, W1 = g.W1, H1 = g.H1, n_veh = g.n_veh, n_src = g.n_src;
   const int Hmax = max(H0, H1), Wmax = max(W0, W1);
   const int wpr0 = g.wpr0, wpr1 = g.wpr1;
-  uint32_t* bits0 = reinterpret_cast<uint32_t*>(smem + g.bits_off);
+  uint32_t* bits0 = reinterpret_cast<uint32_t*>(buf + g.bits_off);
   const int stride0 = g.stride0, stride1 = g.stride1;
   uint32_t* bits1 = bits0 + g.rows0 * stride0;
   const int n_bit_words = g.n_bit_words;
   const float rad0 = g.rad0, rad1 = g.rad1;
   const float fx = (float)px, fy = (float)py;
-  lut[threadIdx.x] = make_uint2(d_expand4(threadIdx.x & 15u), d_expand4(threadIdx.x >> 4));
 
-  for (int rg = 0; rg < Hmax; rg += SB_RASTER_THREADS) {
-    const int r = rg + threadIdx.x;
-    for (int i = threadIdx.x; i * 4 < n_bit_words; i += SB_RASTER_THREADS)  // (the buffer is padded to 16 bytes)
+  for (int rg = 0; rg < Hmax; rg += T) {
+    const int r = rg + tid;
+    for (int i = tid; i * 4 < n_bit_words; i += T)  // (the buffer is padded to 16 bytes)
       reinterpret_cast<uint4*>(bits0)[i] = make_uint4(0u, 0u, 0u, 0u);
     for (int cb = 0; cb < Wmax; cb += 256) {
-      if (threadIdx.x == 0) {
+      if (tid == 0) {
         st->n_list = 0;
         st->n_big[0] = 0;
         st->wide = 0;
       }
-      __syncthreads();
+      d_slice_sync<T>(bar);
       int par = 0;
-      for (int base = 0; base < n_src; base += SB_RASTER_THREADS) {
-        const int p = base + threadIdx.x;
+      for (int base = 0; base < n_src; base += T) {
+        const int p = base + tid;
         bool keep = false;
         if (p < n_veh) {
           const int vj = e * c.V + p;
@@ -425,43 +443,66 @@ __device__ __forceinline__ void d_raster_agent(const DCfg& c, const DMap& m, con
         }
         if (keep) st->list[atomicAdd(&st->n_list, 1)] = p;
         if (keep && p >= n_veh && m.poly_start[p - n_veh + 1] - m.poly_start[p - n_veh] > 4) st->wide = 1;
-        __syncthreads();
+        d_slice_sync<T>(bar);
         // stage + rasterise in rounds; a remainder < ROUND waits for the next cull pass
-        const bool last = base + SB_RASTER_THREADS >= n_src;
+        const bool last = base + T >= n_src;
         int n_list = st->n_list;
-        while (n_list >= SB_RASTER_ROUND || (last && n_list > 0)) {
-          const int count = min(n_list, SB_RASTER_ROUND);
-          if (st->wide) d_stage_phase<8>(c, m, s, e, job, st, n_list - count, count, par);
-          else d_stage_phase<4>(c, m, s, e, job, st, n_list - count, count, par);
-          __syncthreads();
-          if (threadIdx.x == 0) st->n_big[par ^ 1] = 0;
-          d_small_polys(job, st, count, rg, cb, bits0, bits1, stride0, stride1);
-          d_big_rows(job, st, par, r, cb, bits0 + threadIdx.x * stride0, bits1 + threadIdx.x * stride1);
+        while (n_list >= ST::ROUND || (last && n_list > 0)) {
+          const int count = min(n_list, ST::ROUND);
+          if (st->wide) d_stage_phase<8, T, ST>(c, m, s, e, job, st, n_list - count, count, par, tid);
+          else d_stage_phase<4, T, ST>(c, m, s, e, job, st, n_list - count, count, par, tid);
+          d_slice_sync<T>(bar);
+          if (tid == 0) st->n_big[par ^ 1] = 0;
+          d_small_polys<T, ST>(job, st, count, rg, cb, bits0, bits1, stride0, stride1, tid);
+          d_big_rows(job, st, par, r, cb, bits0 + tid * stride0, bits1 + tid * stride1);
           n_list -= count;
           par ^= 1;
-          __syncthreads();
+          d_slice_sync<T>(bar);
         }
         if (!last) {  // carry the remainder over to the next cull pass
-          if (threadIdx.x == 0) st->n_list = n_list;
-          __syncthreads();
+          if (tid == 0) st->n_list = n_list;
+          d_slice_sync<T>(bar);
         }
       }
     }
-    __syncthreads();
+    d_slice_sync<T>(bar);
     if (rg < H0)
-      d_store_rows(bits0, lut, o.ogm + (size_t)ai * W0 * H0 + (size_t)rg * W0, min(H0 - rg, SB_RASTER_THREADS), wpr0,
-                   stride0);
+      d_store_rows<T>(bits0, lut, o.ogm + (size_t)ai * W0 * H0 + (size_t)rg * W0, min(H0 - rg, T), wpr0,
+                      stride0, tid);
     if (rg < H1)
-      d_store_rows(bits1, lut, o.dagm + (size_t)ai * W1 * H1 + (size_t)rg * W1, min(H1 - rg, SB_RASTER_THREADS), wpr1,
-                   stride1);
-    if (rg + SB_RASTER_THREADS < Hmax) __syncthreads();
+      d_store_rows<T>(bits1, lut, o.dagm + (size_t)ai * W1 * H1 + (size_t)rg * W1, min(H1 - rg, T), wpr1,
+                      stride1, tid);
+    if (rg + T < Hmax) d_slice_sync<T>(bar);
   }
 }
 
+// One agent per block (grids taller than 128 rows) ...
 __global__ void __launch_bounds__(SB_RASTER_THREADS, SB_RASTER_BLOCKS)
 k_raster(DCfg c, DMap m, DState s, DObs o, RasterDims g) {
   extern __shared__ __align__(16) unsigned char smem[];
+  __shared__ RasterJob sjob;
+  uint2* lut = reinterpret_cast<uint2*>(smem);
+  lut[threadIdx.x] = make_uint2(d_expand4(threadIdx.x & 15u), d_expand4(threadIdx.x >> 4));
   int e, a;
   if (!d_work_agent(c, blockIdx.x, &e, &a)) return;
-  d_raster_agent(c, m, s, o, g, e, a, smem);
+  d_raster_agent<SB_RASTER_THREADS, RasterStage>(c, m, s, o, g, e, a, lut, smem + SB_RASTER_LUT_BYTES, sjob, threadIdx.x, 0);
+}
+
+// ... or 256 / T agents per block, each rasterised by its own slice of T = 32 / 64 / 128 threads (T >= rows) with
+// its own staging area, bit images and named barrier: a 64 x 64 grid is 4 KB of output, and a block per agent
+// would leave three quarters of its threads without a row and the SM without enough stores in flight.
+template <int T>
+__global__ void __launch_bounds__(SB_RASTER_THREADS)
+k_raster_slices(DCfg c, DMap m, DState s, DObs o, RasterDims g, int n_work) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  __shared__ RasterJob sjob[SB_RASTER_THREADS / T];
+  uint2* lut = reinterpret_cast<uint2*>(smem);
+  lut[threadIdx.x] = make_uint2(d_expand4(threadIdx.x & 15u), d_expand4(threadIdx.x >> 4));
+  __syncthreads();
+  const int slice = threadIdx.x / T, tid = threadIdx.x - slice * T;
+  const int work = blockIdx.x * (SB_RASTER_THREADS / T) + slice;
+  int e, a;
+  if (work >= n_work || !d_work_agent(c, work, &e, &a)) return;
+  d_raster_agent<T, RasterStageT<T, SB_RASTER_SLICE_ROUND>>(c, m, s, o, g, e, a, lut, smem + SB_RASTER_LUT_BYTES + (size_t)slice * g.slice_bytes, sjob[slice],
+                    tid, 1 + slice);
 }

@@ -23,7 +23,7 @@ EXPORTS = [
     "sb_abi_version", "sb_create", "sb_destroy", "sb_upload_map", "sb_upload_lidar_rays", "sb_reset",
     "sb_set_social", "sb_step", "sb_observe", "sb_observe_envs", "sb_step_host", "sb_copy_obs_to_host", "sb_get_obs",
     "sb_get_state", "sb_launch_count", "sb_last_error", "sb_set_timing", "sb_collect_timing",
-    "sb_set_incremental_host_grids",
+    "sb_set_incremental_host_grids", "sb_copy_obs_to_host_packed",
 ]
 KERNEL_KINDS = ["k_set_social", "k_control", "k_observe", "k_lidar", "k_raster", "k_events", "k_pack_bits", "k_ttc", "k_extras", "k_ego_frame"]
 
@@ -57,6 +57,8 @@ def load_library(path: Optional[str] = None):
     L.sb_observe_envs.argtypes = [H, C.POINTER(C.c_int32), C.c_int32, C.c_void_p]
     L.sb_step_host.argtypes = [H, C.c_void_p, C.c_int64, C.c_void_p]
     L.sb_copy_obs_to_host.argtypes = [H, C.POINTER(_abi.SbObsPtrs)]
+    L.sb_copy_obs_to_host_packed.argtypes = [H, C.POINTER(_abi.SbObsPtrs)]
+    L.sb_copy_obs_to_host_packed.restype = C.c_int
     L.sb_get_obs.argtypes = [H, C.POINTER(_abi.SbObsPtrs)]
     L.sb_get_state.argtypes = [H, C.POINTER(_abi.SbStatePtrs)]
     L.sb_launch_count.argtypes = [H]
@@ -227,10 +229,13 @@ class Engine:
         self._check(self._lib.sb_step_host(self._h, a.ctypes.data_as(C.c_void_p), a.nbytes,
                                            s.ctypes.data_as(C.c_void_p) if s is not None else None), "sb_step_host")
 
-    def host_obs_buffers(self, pinned: bool = True) -> Dict[str, "np.ndarray"]:
-        """Allocate host destination buffers (pinned by default) for ``copy_obs_to_host``."""
+    def host_obs_buffers(self, pinned: bool = True, packed_grids: bool = False) -> Dict[str, "np.ndarray"]:
+        """Allocate host destination buffers (pinned by default) for ``copy_obs_to_host``; with ``packed_grids``
+        the grids are [E, A, H, W // 8] uint8 bit images for ``copy_obs_to_host(..., packed=True)``."""
         out = {}
         for name, (shape, dt) in _abi.obs_shapes(self.cfg).items():
+            if packed_grids and name in ("ogm", "dagm"):
+                shape = (shape[0], shape[1] // 8)
             full = (self.E, self.A) + tuple(shape)
             t = self._torch.empty(full, dtype=getattr(self._torch, np.dtype(dt).name), pin_memory=pinned)
             out[name] = t
@@ -241,12 +246,21 @@ class Engine:
         written to in between: only the 64-pixel words that changed are rewritten (smarts_b200.h)."""
         self._check(self._lib.sb_set_incremental_host_grids(self._h, int(on)), "sb_set_incremental_host_grids")
 
-    def copy_obs_to_host(self, bufs: Dict[str, "object"]):
+    @staticmethod
+    def unpack_grid(bits: np.ndarray) -> np.ndarray:
+        """[..., H, W // 8] bit image of ``copy_obs_to_host(packed=True)`` -> the [..., H, W] 0 / 255 uint8 image."""
+        return np.unpackbits(np.asarray(bits), axis=-1, bitorder="little") * np.uint8(255)
+
+    def copy_obs_to_host(self, bufs: Dict[str, "object"], packed: bool = False):
+        """``packed``: the grids are delivered as 1-bit images (sb_copy_obs_to_host_packed; ``unpack_grid`` widens)."""
         p = _abi.SbObsPtrs()
         for name, t in bufs.items():
             field_t = dict(_abi.SbObsPtrs._fields_)[name]
             setattr(p, name, C.cast(C.c_void_p(t.data_ptr()), field_t))
-        self._check(self._lib.sb_copy_obs_to_host(self._h, C.byref(p)), "sb_copy_obs_to_host")
+        if packed:
+            self._check(self._lib.sb_copy_obs_to_host_packed(self._h, C.byref(p)), "sb_copy_obs_to_host_packed")
+        else:
+            self._check(self._lib.sb_copy_obs_to_host(self._h, C.byref(p)), "sb_copy_obs_to_host")
 
     # -- zero-copy views -----------------------------------------------------------------
     def obs(self) -> Dict[str, "object"]:

@@ -464,6 +464,33 @@ def test_host_buffer_call_matches_device_views(pinned, share, monkeypatch):
 
 
 @pytest.mark.parametrize("pinned", [True, False])
+def test_packed_host_grids_unpack_to_the_uint8_images(pinned):
+    """sb_copy_obs_to_host_packed: the grids arrive as 1-bit images in the layout smarts_b200.h documents
+    (numpy.unpackbits(..., bitorder="little") * 255 is the uint8 image); every other member as in the uint8 call."""
+    rm = load_map("4lane")
+    E, A, M = 19, 4, 9
+    cfg = make_cfg(E=E, A=A, M=M, nbr=True, lidar=True, wall=1.5, ogm=(96, 40, 0.3), dagm=(160, 72, 0.2), route_cap=16)
+    x, y, h, v, route, rlen = scenario_gen.agent_starts(rm, E, MISSIONS_4LANE, cfg.route_cap, 61, jitter=30.0, speed=6.0)
+    traffic = scenario_gen.SocialTraffic(rm, E, M, 62)
+    eng = engine(rm, cfg)
+    eng.reset(x, y, h, v, route, rlen)
+    bufs = eng.host_obs_buffers(pinned=pinned, packed_grids=True)
+    assert tuple(bufs["ogm"].shape) == (E, A, 40, 96 // 8) and tuple(bufs["dagm"].shape) == (E, A, 72, 160 // 8)
+    full = eng.host_obs_buffers(pinned=pinned)
+    act = np.random.default_rng(63).integers(0, 4, (E, A)).astype(np.int32)
+    for t in range(3):
+        eng.step_host(act, traffic.states(t))
+        eng.copy_obs_to_host(bufs, packed=True)
+        eng.copy_obs_to_host(full)
+        for k, t_full in full.items():
+            got = bufs[k].numpy()
+            if k in ("ogm", "dagm"):
+                got = eng.unpack_grid(got)
+            assert np.array_equal(got, t_full.numpy(), equal_nan=got.dtype.kind == "f"), k
+    assert full["ogm"].numpy().any() and full["dagm"].numpy().any()
+
+
+@pytest.mark.parametrize("pinned", [True, False])
 def test_incremental_host_grids_hold_the_full_images(pinned):
     """sb_set_incremental_host_grids: with the same destination buffers call after call only the changed 64-pixel
     words are rewritten -- the buffers must still equal the device images after every call, including after a
