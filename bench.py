@@ -28,7 +28,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-from smarts_b200 import _abi, lidar_params, scenario_gen  # noqa: E402
+from smarts_b200 import _abi, lidar_params, scenario_gen, sharding  # noqa: E402
 from smarts_b200.road_map import RoadMapData  # noqa: E402
 
 METRIC = "agent-steps/sec incl. LiDAR+OGM obs"
@@ -268,7 +268,8 @@ class GpuWorkload:
         import torch
         from smarts_b200.engine import Engine
         self.torch, self.w, self.E, self.A, self.M = torch, w, E, w["A"], w["M"]
-        self.rm, self.init, self.traffic = build_inputs(w, E, seed_shift=1000 * rank)
+        self.shard = sharding.weak_shard(E, rank, int(os.environ.get("WORLD_SIZE", "1")))  # every rank its own envs
+        self.rm, self.init, self.traffic = build_inputs(w, E, seed_shift=1000 * self.shard.rank)
         self.cfg = make_cfg(E, self.A, self.M, local, **dict(w["cfg"], events=events or w["cfg"].get("events", False)))
         self.eng = Engine(self.cfg, self.rm, lidar_params.base_rays(lidar_params.BasicLidar))
         self.eng.reset(*self.init)
@@ -351,13 +352,10 @@ def measure(w, E, W_, K, local, rank, world, dist):
     for t in range(W_):
         g.tick(t)
     ms_kt, _, ktimes = g.timed(W_, K, None, True)
-    stats = torch.tensor([ms, float(E * g.A * K)], dtype=torch.float64, device="cuda")
-    total = float(E * g.A * K)
-    if world > 1:  # max time over ranks; episode statistics (agent-steps) summed -- the only collectives
-        tmax, tot = stats[:1].clone(), stats[1:].clone()
-        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
-        ms, total = float(tmax.item()), float(tot.item())
+    # max time over ranks; episode statistics (agent-steps) summed -- the only collectives of the job
+    red = sharding.reduce_stats({"elapsed_ms": ms, "agent_steps": float(E * g.A * K)}, max_keys=("elapsed_ms",),
+                                device=torch.device("cuda", local))
+    ms, total = red["elapsed_ms"], red["agent_steps"]
     peak, peak_src = hbm_peak()
     step_bytes = algorithmic_bytes_per_agent_step(g.cfg, g.M, g.A)
     step_gbs = step_bytes * (E * g.A * K) / (ms * 1e-3) / 1e9  # per GPU (weak scaling)

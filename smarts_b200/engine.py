@@ -92,6 +92,29 @@ class _DevArray:
         }
 
 
+class TickGraph:
+    """See ``Engine.capture_tick``."""
+
+    def __init__(self, eng: "Engine", actions, social):
+        torch = eng._torch
+        if eng.M and social is None:
+            raise ValueError("this engine has social vehicles: pass the tensor their states are written to")
+        self.eng, self.actions, self.social = eng, actions, social
+        before = int(eng._lib.sb_launch_count(eng._h))
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            if social is not None:
+                eng.set_social(social)
+            eng.step(actions)
+            eng.observe()
+        self.launches = int(eng._lib.sb_launch_count(eng._h)) - before
+        eng._graph_launches -= self.launches  # the capture itself launched nothing
+
+    def replay(self):
+        self.graph.replay()
+        self.eng._graph_launches += self.launches
+
+
 class Engine:
     """One handle = E batched environments on one GPU."""
 
@@ -120,6 +143,7 @@ class Engine:
                         "sb_upload_lidar_rays")
         self._obs = None
         self._state = None
+        self._graph_launches = 0
 
     # -- plumbing ------------------------------------------------------------------------
     def _check(self, rc: int, what: str):
@@ -147,7 +171,7 @@ class Engine:
 
     @property
     def launch_count(self) -> int:
-        return int(self._lib.sb_launch_count(self._h))
+        return int(self._lib.sb_launch_count(self._h)) + self._graph_launches
 
     def set_timing(self, on: bool):
         self._check(self._lib.sb_set_timing(self._h, int(on)), "sb_set_timing")
@@ -218,6 +242,14 @@ class Engine:
         ids = np.ascontiguousarray(env_ids, np.int32)
         self._check(self._lib.sb_observe_envs(self._h, ids.ctypes.data_as(C.POINTER(C.c_int32)), len(ids),
                                               self._stream_ptr()), "sb_observe_envs")
+
+    def capture_tick(self, actions, social=None) -> "TickGraph":
+        """One tick (set_social + step + observe) captured into a CUDA graph over the given device tensors: the
+        graph reads ``actions`` / ``social`` at replay time, so write the next tick's values into the same
+        tensors and call ``.replay()``.  For small batches the tick is launch-bound (figure_eight x 256 envs:
+        three kernels of ~0.04 ms); the graph removes the per-launch host cost.  Run one eager tick first so
+        that every kernel's module is loaded outside the capture."""
+        return TickGraph(self, actions, social)
 
     def step_host(self, actions: np.ndarray, social: Optional[np.ndarray]):
         """The reference-facing call with HOST buffers: H2D copies + set_social + step + observe + sync."""

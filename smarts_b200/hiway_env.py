@@ -110,7 +110,7 @@ class BatchedHiWayEnv:
                  fixed_timestep_sec: float = 0.1, seed: int = 42, headless: bool = True, device: int = 0,
                  auto_reset: bool = True, start_jitter: float = 0.0, route_cap: int = 16, traj_len: int = 10,
                  lidar_wall_height: float = 0.0, wp_out_len: Optional[int] = None, sim_name: Optional[str] = None,
-                 ego_centric: bool = False, **_ignored_reference_kwargs):
+                 ego_centric: bool = False, shard=None, **_ignored_reference_kwargs):
         from .engine import Engine  # raises without the CUDA library / a GPU: no CPU fallback
         if not agent_specs:
             raise ValueError("agent_specs is empty")
@@ -133,7 +133,17 @@ class BatchedHiWayEnv:
         missing = [a for a in self.agent_ids if a not in scenario.missions]
         if missing:
             raise ValueError(f"scenario has no mission for agents {missing}")
+        # shard (sharding.EnvShard): this process owns envs [shard.start, shard.stop) of a job of shard.total envs --
+        # one process per GPU, no data-path collective; start jitter and seeds are functions of the GLOBAL env index,
+        # so a job gives the same episodes whatever the number of GPUs it is split over
+        self.shard = shard
+        if shard is not None:
+            if int(n_envs) != shard.count:
+                raise ValueError(f"n_envs {n_envs} != shard.count {shard.count}")
+            if not shard.total:
+                raise ValueError("shard.total is not set (use sharding.shard_envs / weak_shard)")
         self.E, self.A, self.M = int(n_envs), len(self.agent_ids), int(scenario.n_social)
+        self._stats = {"agent_steps": 0.0, "episodes_done": 0.0}
         self.dt = float(fixed_timestep_sec)
         self._seed = int(seed)
         self._jitter = float(start_jitter)
@@ -172,7 +182,8 @@ class BatchedHiWayEnv:
         """parallel_env.py:246-256: env i gets seed + i."""
         self._seed = int(seed)
         self._start = self._build_starts(self._seed)
-        return [seed + i for i in range(self.E)]
+        first = self.shard.start if self.shard is not None else 0
+        return [seed + first + i for i in range(self.E)]
 
     def close(self, terminate: bool = False):
         if self._engine is not None:
@@ -207,7 +218,11 @@ class BatchedHiWayEnv:
                 raise ValueError(f"route of {aid}: {len(r.road_indices)} roads (route_cap {rc})")
             route[:, a, :len(r.road_indices)] = r.road_indices
             rlen[:, a] = len(r.road_indices)
-            offs = m.begin_offset + (rng.uniform(0, self._jitter, E) if self._jitter > 0 else np.zeros(E))
+            if self._jitter > 0 and self.shard is not None:  # drawn for the whole job, this shard's slice kept
+                jit = rng.uniform(0, self._jitter, self.shard.total)[self.shard.start:self.shard.stop]
+            else:
+                jit = rng.uniform(0, self._jitter, E) if self._jitter > 0 else np.zeros(E)
+            offs = m.begin_offset + jit
             for e in range(E):
                 x[e, a], y[e, a], h[e, a] = rm.lane_start_pose(m.begin_road, m.begin_lane, float(offs[e]))
             v[:, a] = m.start_speed
@@ -291,6 +306,7 @@ class BatchedHiWayEnv:
         eng.observe()
         self._global_tick += 1
         self._tick += 1
+        self._stats["agent_steps"] += float(self.E * self.A - int(self._done_agents.sum()))
         obs = eng.obs()
         if "ev_done" in obs:  # done agents leave the simulation after this observation (agent_manager teardown):
             alive = eng.state()["alive"]  # a device-side op on the zero-copy views, no synchronisation
@@ -304,10 +320,28 @@ class BatchedHiWayEnv:
         d = done.cpu().numpy().astype(bool) | self._done_agents
         self._done_agents = d
         ids = np.nonzero(d.all(axis=1))[0].astype(np.int32)
+        self._stats["episodes_done"] += float(len(ids))
         if len(ids) and self._auto_reset:
             self._reset_envs(ids)
             self.engine.observe(ids)  # only the reset envs: the others' sensor state and buffers stay as they are
         return ids
+
+    @classmethod
+    def sharded(cls, scenario: Scenario, agent_specs: Dict[str, AgentSpec], n_envs_total: int, **kw):
+        """One process per GPU under torchrun: this rank's contiguous share of ``n_envs_total`` envs on
+        ``cuda:LOCAL_RANK`` (sharding.shard_from_env; ParallelEnv's analogue is one process per env)."""
+        import os
+        from . import sharding
+        sh = sharding.shard_from_env(int(n_envs_total))
+        return cls(scenario, agent_specs, sh.count, device=int(os.environ.get("LOCAL_RANK", "0")), shard=sh, **kw)
+
+    def episode_stats(self, reduce: bool = True) -> Dict[str, float]:
+        """Agent-steps taken and episodes finished so far, summed over the ranks of the job (the one collective:
+        a small all-reduce, sharding.reduce_stats)."""
+        from . import sharding
+        if not reduce:
+            return dict(self._stats)
+        return sharding.reduce_stats(self._stats, max_keys=(), device=self._torch.device("cuda", self.cfg.device))
 
     # -- StdObs: the dense, batched observation of format_obs.py, on the device -------------------
     def std_obs(self) -> Dict[str, Any]:
@@ -554,6 +588,7 @@ class BatchedHiWayEnv:
             obs_l.append(obs_e); rew_l.append(rew_e); done_l.append(done_e); info_l.append(info_e)
         # (done agents left the simulation inside step_tensor: vehicle removed, agent_manager teardown)
         finished = np.nonzero(self._done_agents.all(axis=1))[0].astype(np.int32)
+        self._stats["episodes_done"] += float(len(finished))
         if len(finished) and self._auto_reset:
             self._reset_envs(finished)
             self.engine.observe(finished)  # the reset envs only (ParallelEnv envs are independent)

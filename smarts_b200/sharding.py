@@ -20,6 +20,7 @@ class EnvShard:
     world: int
     start: int   # first global env index owned by this rank
     count: int   # envs owned
+    total: int = 0   # envs of the whole job (0: not recorded)
 
     @property
     def stop(self) -> int:
@@ -39,12 +40,18 @@ def shard_envs(n_envs: int, rank: int, world: int) -> EnvShard:
     base, extra = divmod(n_envs, world)
     count = base + (1 if rank < extra else 0)
     start = rank * base + min(rank, extra)
-    return EnvShard(rank, world, start, count)
+    return EnvShard(rank, world, start, count, n_envs)
 
 
 def weak_shard(envs_per_gpu: int, rank: int, world: int) -> EnvShard:
     """Weak-scaling layout used by bench.py: every rank owns `envs_per_gpu` envs of its own."""
-    return EnvShard(rank, world, rank * envs_per_gpu, envs_per_gpu)
+    return EnvShard(rank, world, rank * envs_per_gpu, envs_per_gpu, world * envs_per_gpu)
+
+
+def shard_from_env(n_envs: int) -> EnvShard:
+    """The shard of this process under torchrun (RANK / WORLD_SIZE; a single process owns everything)."""
+    import os
+    return shard_envs(n_envs, int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")))
 
 
 def owner_of(global_env: int, n_envs: int, world: int) -> int:

@@ -604,3 +604,37 @@ def test_maximum_grid_sizes_and_multi_pass_rows():
         assert_same(got, want)
         assert want["dagm"].any()
         eng.close(); ora.close()
+
+
+def test_captured_tick_replays_bit_identically():
+    """Engine.capture_tick: the tick as a CUDA graph over fixed action / social tensors gives the states and
+    observations of the eager calls, tick for tick."""
+    import torch
+    rm = load_map("4lane")
+    E, A, M = 33, 4, 9
+    cfg = make_cfg(E=E, A=A, M=M, nbr=True, wp=True, lidar=True, wall=1.5, ogm=(64, 64, 0.5), dagm=(96, 72, 0.3),
+                   route_cap=16, events=True)
+    x, y, h, v, route, rlen = scenario_gen.agent_starts(rm, E, MISSIONS_4LANE, cfg.route_cap, 71, jitter=30.0, speed=6.0)
+    traffic = scenario_gen.SocialTraffic(rm, E, M, 72)
+    acts = np.random.default_rng(73).integers(0, 4, (8, E, A)).astype(np.int32)
+    eager, graphed = engine(rm, cfg), engine(rm, cfg)
+    for w in (eager, graphed):
+        w.reset(x, y, h, v, route, rlen)
+    act_buf = torch.zeros((E, A), dtype=torch.int32, device="cuda")
+    soc_buf = torch.zeros((E, M, 8), dtype=torch.float64, device="cuda")
+    tick = None
+    for t in range(8):
+        a, s = torch.from_numpy(acts[t]).cuda(), torch.from_numpy(traffic.states(t)).cuda()
+        eager.set_social(s); eager.step(a); eager.observe()
+        act_buf.copy_(a); soc_buf.copy_(s)
+        if t == 0:      # modules loaded by an eager tick, then the capture
+            graphed.set_social(soc_buf); graphed.step(act_buf); graphed.observe()
+            tick = graphed.capture_tick(act_buf, soc_buf)
+            assert tick.launches >= 5
+        else:
+            n0 = graphed.launch_count
+            tick.replay()
+            assert graphed.launch_count - n0 == tick.launches
+        torch.cuda.synchronize()
+        assert_same(graphed.obs_numpy(), eager.obs_numpy())
+        assert_same(graphed.state_numpy(), eager.state_numpy())

@@ -222,6 +222,42 @@ def test_batched_env_auto_reset_and_tensor_path_agree():
 
 
 @pytest.mark.gpu
+def test_sharded_envs_reproduce_the_unsharded_job():
+    """BatchedHiWayEnv(shard=...): the two halves of a 7-env job (as two ranks would own them) start and run
+    exactly like envs [0, 4) and [4, 7) of the unsharded job, and count their agent-steps / episodes."""
+    import torch
+    from smarts_b200 import sharding
+    rm = load_map("4lane")
+    itf = AgentInterface.from_type(AgentType.LanerWithSpeed, max_episode_steps=4)
+    sc = Scenario(rm, MISSIONS, None, 0)
+    whole = BatchedHiWayEnv(sc, _specs(itf), n_envs=7, start_jitter=20.0, seed=5, shard=sharding.shard_envs(7, 0, 1))
+    parts = [BatchedHiWayEnv(sc, _specs(itf), n_envs=sharding.shard_envs(7, r, 2).count, start_jitter=20.0, seed=5,
+                             shard=sharding.shard_envs(7, r, 2)) for r in range(2)]
+    assert [p.E for p in parts] == [4, 3] and parts[1].seed(5) == [9, 10, 11]
+    for env in [whole] + parts:
+        env.seed(5)
+        env.reset_tensor()
+    for t in range(4):
+        outs = []
+        for env in [whole] + parts:
+            act = torch.tensor([[8.0, 0.0]], dtype=torch.float64, device="cuda").repeat(env.E * 4, 1)
+            o = env.step_tensor(act)
+            torch.cuda.synchronize()
+            outs.append({k: o[k].cpu().numpy() for k in ("ev_reward", "ev_distance", "wp_pos")})
+        for k in outs[0]:
+            assert np.array_equal(outs[0][k], np.concatenate([outs[1][k], outs[2][k]]), equal_nan=True), (t, k)
+    done = [len(env.auto_reset_done_envs()) for env in [whole] + parts]
+    assert done == [7, 4, 3]
+    st = [env.episode_stats() for env in [whole] + parts]
+    assert st[0] == {"agent_steps": 7 * 4 * 4.0, "episodes_done": 7.0}
+    assert st[1]["agent_steps"] + st[2]["agent_steps"] == st[0]["agent_steps"]
+    with pytest.raises(ValueError):
+        BatchedHiWayEnv(sc, _specs(itf), n_envs=5, shard=sharding.shard_envs(7, 0, 2))
+    for env in [whole] + parts:
+        env.close()
+
+
+@pytest.mark.gpu
 def test_staggered_auto_reset_leaves_running_envs_alone():
     """Envs that finish on different ticks: an env that is auto-reset must not disturb the others (in the reference
     every ParallelEnv env is its own process).  Env 1 stands still and is ended by `not_moving` every few ticks

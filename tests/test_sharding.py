@@ -40,6 +40,15 @@ def test_shard_envs_partitions_exactly():
 def test_weak_shard_layout():
     s = sharding.weak_shard(4096, 3, 8)
     assert (s.start, s.count, s.stop) == (3 * 4096, 4096, 4 * 4096)
+    assert s.total == 8 * 4096 and sharding.shard_envs(9, 1, 2).total == 9
+
+
+def test_shard_from_env_reads_the_torchrun_variables(monkeypatch):
+    monkeypatch.setenv("RANK", "1"); monkeypatch.setenv("WORLD_SIZE", "4")
+    s = sharding.shard_from_env(10)
+    assert (s.rank, s.world, s.start, s.count, s.total) == (1, 4, 3, 3, 10)
+    monkeypatch.delenv("RANK"); monkeypatch.delenv("WORLD_SIZE")
+    assert sharding.shard_from_env(10).count == 10
 
 
 def _free_port():
