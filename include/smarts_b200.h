@@ -261,7 +261,11 @@ typedef struct SbResetState {
 int sb_create(const SbConfig *cfg, SbHandle *out);
 /* HiWayEnv.close / SMARTS.destroy (hiway_env.py:287-291, smarts.py:688-703) */
 void sb_destroy(SbHandle h);
-/* SMARTS.setup -> road map load (smarts.py:440-460; SumoRoadNetwork.from_spec, sumo_road_network.py:145-176) */
+/* SMARTS.setup -> road map load (smarts.py:440-460; SumoRoadNetwork.from_spec, sumo_road_network.py:145-176).
+ * Calling it again replaces the map (the scenario iterator of HiWayEnv.reset, hiway_env.py:265-285, hands
+ * SMARTS.reset the next scenario and SMARTS.setup reloads the road map when it differs, smarts.py:411-460): the
+ * device is synchronised, the old map's arrays are freed, and every later call except a full sb_reset
+ * (env_ids = NULL) answers SB_ESTATE until that reset has placed the agents on the new map. */
 int sb_upload_map(SbHandle h, const SbMap *map);
 /* Lidar._compute_rays base table (smarts/core/lidar.py:89-106); host [R,3] direction*max_distance */
 int sb_upload_lidar_rays(SbHandle h, const double *base_rays, int32_t n_rays);

@@ -16,7 +16,7 @@
 
 // sb_hostxfer.cpp (g++): host threads that widen bit-packed grids back to uint8
 extern "C" {
-void* sbx_pool_create(int threads);
+void* sbx_pool_create(int threads, int first_cpu);
 void sbx_pool_destroy(void* p);
 void sbx_pool_submit(void* p, const uint8_t* bits, uint8_t* out, size_t n_bytes_in, size_t piece);
 void sbx_pool_submit_diff(void* p, const uint8_t* bits, uint8_t* prev, uint8_t* out, size_t n_bytes_in, size_t piece);
@@ -39,6 +39,8 @@ struct SbHandle_ {
   cudaStream_t env_list_stream = nullptr;
   bool stepped = false;  // a sb_step since the last sb_observe (SensorState.step; `sim.resetting` otherwise)
   bool have_map = false, have_rays = false;
+  bool stale_agents = false;          // a new map was uploaded: routes / lanes of the old one are meaningless until a full reset
+  std::vector<void*> map_allocs;      // device arrays of the current map (freed when another one replaces it)
   LTable ray_table{};   // factored ray table (include/sb_lidar_table.h), sorted by azimuth group
   float ray_reach = 0.f;
   std::vector<void*> allocs;
@@ -258,11 +260,11 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
                       c.wp_out_paths > SB_MAX_PATHS || c.wp_out_len < 1 || c.wp_out_len > SB_MAX_LOOKAHEAD + 1))
     return fail(h, SB_EINVAL, "waypoint sensor limits");
   if (c.lidar_enable && (c.lidar_rays < 1 || c.lidar_rays > SB_LIDAR_MAX_RAYS)) return fail(h, SB_EINVAL, "lidar_rays");
-  auto grid_ok = [](int w, int hh, double r) { return w >= 32 && hh >= 1 && (w % 32) == 0 && r > 0 && w <= 1024 && hh <= 1024; };
+  auto grid_ok = [](int w, int hh, double r) { return w >= 1 && hh >= 1 && r > 0 && w <= 1024 && hh <= 1024; };
   if (c.ogm_enable && !grid_ok(c.ogm_width, c.ogm_height, c.ogm_resolution))
-    return fail(h, SB_EINVAL, "ogm: width must be a multiple of 32, <= 1024; resolution > 0");
+    return fail(h, SB_EINVAL, "ogm: width and height must be in 1..1024, resolution > 0");
   if (c.dagm_enable && !grid_ok(c.dagm_width, c.dagm_height, c.dagm_resolution))
-    return fail(h, SB_EINVAL, "dagm: width must be a multiple of 32, <= 1024; resolution > 0");
+    return fail(h, SB_EINVAL, "dagm: width and height must be in 1..1024, resolution > 0");
   if (c.n_agents + c.n_social > SB_LIDAR_MAX_BOXES + 1 && c.lidar_enable)
     return fail(h, SB_EINVAL, "lidar: too many vehicles per env");
 
@@ -384,7 +386,7 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
     if (c.dagm_enable && c.dagm_height > hmax) hmax = c.dagm_height;
     const int T = hmax <= 32 ? 32 : hmax <= 64 ? 64 : hmax <= 128 ? 128 : SB_RASTER_THREADS;
     auto rows256 = [T](int hh) { return (size_t)(hh < T ? hh : T); };
-    auto row_words = [](int ww) { return (size_t)((ww / 32 + 7) / 8 * 8 + 1); };
+    auto row_words = [](int ww) { return (size_t)(((ww + 31) / 32 + 7) / 8 * 8 + 1); };
     size_t b0 = c.ogm_enable ? row_words(c.ogm_width) * 4 * rows256(c.ogm_height) : 0;
     size_t b1 = c.dagm_enable ? row_words(c.dagm_width) * 4 * rows256(c.dagm_height) : 0;
     int wmax = 0;
@@ -401,8 +403,8 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
     g.H0 = c.ogm_enable ? c.ogm_height : 0;
     g.W1 = c.dagm_enable ? c.dagm_width : 0;
     g.H1 = c.dagm_enable ? c.dagm_height : 0;
-    g.wpr0 = g.W0 / 32;
-    g.wpr1 = g.W1 / 32;
+    g.wpr0 = (g.W0 + 31) / 32;
+    g.wpr1 = (g.W1 + 31) / 32;
     g.rows0 = (int)rows256(g.H0);
     g.rows1 = (int)rows256(g.H1);
     g.n_veh = c.ogm_enable ? d.V : 0;
@@ -431,6 +433,7 @@ void sb_destroy(SbHandle h) {
   cudaSetDevice(h->cfg.device);
   cudaDeviceSynchronize();
   for (void* p : h->allocs) cudaFree(p);
+  for (void* p : h->map_allocs) cudaFree(p);
   if (h->pool) sbx_pool_destroy(h->pool);
   if (h->h_bits) cudaFreeHost(h->h_bits);
   if (h->h_env_list) cudaFreeHost(h->h_env_list);
@@ -443,9 +446,25 @@ void sb_destroy(SbHandle h) {
 int sb_upload_map(SbHandle h, const SbMap* mp) {
   if (!h || !mp) return SB_EINVAL;
   if (h->cuda_err) return SB_ECUDA;
-  if (h->have_map) return fail(h, SB_ESTATE, "map already uploaded");
   if (mp->n_lanes < 1 || mp->n_lanepoints < 1) return fail(h, SB_EINVAL, "empty map");
   cudaSetDevice(h->cfg.device);
+  if (h->have_map) {  // scenario cycling (hiway_env.py:265-285 draws the next scenario on reset): replace the map
+    if (!cuda_ok(h, cudaDeviceSynchronize(), "sync before map replacement")) return SB_ECUDA;
+    for (void* q : h->map_allocs) cudaFree(q);
+    h->map_allocs.clear();
+    h->dmap = DMap{};
+    h->have_map = false;
+    h->stale_agents = true;
+  }
+  const size_t alloc_mark = h->allocs.size();
+  struct Claim {  // whatever this call allocated belongs to the map, also when it fails half-way
+    SbHandle h;
+    size_t mark;
+    ~Claim() {
+      h->map_allocs.insert(h->map_allocs.end(), h->allocs.begin() + (long)mark, h->allocs.end());
+      h->allocs.resize(mark);
+    }
+  } claim{h, alloc_mark};
   DMap& m = h->dmap;
   m.n_roads = mp->n_roads; m.n_lanes = mp->n_lanes; m.n_lanepoints = mp->n_lanepoints;
   m.n_shape_pts = mp->n_shape_pts; m.n_polys = mp->n_polys; m.n_poly_verts = mp->n_poly_verts;
@@ -730,6 +749,7 @@ int sb_reset(SbHandle h, const int32_t* env_ids, int32_t n, const SbResetState* 
   if (!h->have_map) return fail(h, SB_ESTATE, "sb_reset before sb_upload_map");
   const DCfg& c = h->dc;
   if (!env_ids) n = c.E;
+  if (h->stale_agents && env_ids) return fail(h, SB_ESTATE, "the map was replaced: the first reset must cover every env");
   if (n < 1 || n > c.E) return fail(h, SB_EINVAL, "n out of range");
   if (env_ids)
     for (int i = 0; i < n; ++i)
@@ -774,6 +794,7 @@ int sb_reset(SbHandle h, const int32_t* env_ids, int32_t n, const SbResetState* 
   cudaFree(dev);
   if (ok && (c.accel_enable || c.via_cap > 0)) ok = reset_extras(h, env_ids, n, init);
   if (!ok && !h->cuda_err) return SB_EINVAL;
+  if (ok && !env_ids) h->stale_agents = false;
   return ok ? SB_OK : SB_ECUDA;
 }
 
@@ -795,6 +816,7 @@ int sb_step(SbHandle h, const void* dev_actions, void* stream) {
   if (!h || !dev_actions) return SB_EINVAL;
   if (h->cuda_err) return SB_ECUDA;
   if (!h->have_map) return fail(h, SB_ESTATE, "sb_step before sb_upload_map");
+  if (h->stale_agents) return fail(h, SB_ESTATE, "the map was replaced: reset every env (sb_reset with env_ids = NULL) first");
   const DCfg& c = h->dc;
   int na = c.E * c.A;
   cudaStream_t st = (cudaStream_t)stream;
@@ -820,6 +842,7 @@ int sb_observe_envs(SbHandle h, const int32_t* env_ids, int32_t n, void* stream)
   if (!h) return SB_EINVAL;
   if (h->cuda_err) return SB_ECUDA;
   if (!h->have_map) return fail(h, SB_ESTATE, "sb_observe before sb_upload_map");
+  if (h->stale_agents) return fail(h, SB_ESTATE, "the map was replaced: reset every env (sb_reset with env_ids = NULL) first");
   if (h->dc.lidar_enable && !h->have_rays) return fail(h, SB_ESTATE, "lidar enabled but no ray table uploaded");
   cudaStream_t st = (cudaStream_t)stream;
   DCfg c = h->dc;  // this call's copy: the env list rides in it
@@ -953,8 +976,13 @@ static int copy_obs_to_host(SbHandle h, const SbObsPtrs* dst, bool packed_dst) {
     h->xfer_frac = v < 0.0 ? 0.0 : (v > 1.0 ? 1.0 : v);
   }
   const size_t n_packed = packed_dst ? na : std::min(na, (size_t)llround(h->xfer_frac * (double)na));
-  if (c.ogm_enable && dst->ogm) jobs[nj++] = {o.ogm, dst->ogm, n_packed * c.ogm_width * c.ogm_height};
-  if (c.dagm_enable && dst->dagm) jobs[nj++] = {o.dagm, dst->dagm, n_packed * c.dagm_width * c.dagm_height};
+  // (the bit image is 32 pixels per word over the flat [n, H, W] byte array: a grid whose W * H is not a multiple of
+  // 32 travels as plain bytes, and cannot be delivered packed)
+  const bool pk0 = ((size_t)c.ogm_width * c.ogm_height) % 32 == 0, pk1 = ((size_t)c.dagm_width * c.dagm_height) % 32 == 0;
+  if (packed_dst && ((c.ogm_enable && dst->ogm && !pk0) || (c.dagm_enable && dst->dagm && !pk1)))
+    return fail(h, SB_EINVAL, "packed delivery needs width * height to be a multiple of 32");
+  if (c.ogm_enable && dst->ogm && pk0) jobs[nj++] = {o.ogm, dst->ogm, n_packed * c.ogm_width * c.ogm_height};
+  if (c.dagm_enable && dst->dagm && pk1) jobs[nj++] = {o.dagm, dst->dagm, n_packed * c.dagm_width * c.dagm_height};
   const auto t0 = std::chrono::steady_clock::now();
   if (ok && nj && n_packed) {
     size_t need = 0;
@@ -998,7 +1026,12 @@ static int copy_obs_to_host(SbHandle h, const SbObsPtrs* dst, bool packed_dst) {
       int nt = (int)(hc == 0 ? 4 : hc) / ranks;
       const char* forced = getenv("SB_XFER_THREADS");
       if (forced && atoi(forced) > 0) nt = atoi(forced);
-      h->pool = sbx_pool_create(nt < 2 ? 2 : (nt > 32 ? 32 : nt));
+      nt = nt < 2 ? 2 : (nt > 32 ? 32 : nt);
+      // several ranks on the box: rank r's workers on its own nt cores (SB_XFER_PIN=0: leave it to the scheduler)
+      const char* lr = getenv("LOCAL_RANK");
+      const char* pin = getenv("SB_XFER_PIN");
+      const bool do_pin = ranks > 1 && lr && !(pin && pin[0] == '0');
+      h->pool = sbx_pool_create(nt, do_pin ? atoi(lr) * nt : -1);
     }
     const size_t chunk = (size_t)8 << 20;  // bytes of bits per D2H chunk (64 MB of pixels)
     size_t off = 0, n_ev = 0;
@@ -1072,9 +1105,11 @@ static int copy_obs_to_host(SbHandle h, const SbObsPtrs* dst, bool packed_dst) {
   }
   if (n_packed < na) {  // the byte-image share, behind everything else on the link
     const size_t g0 = (size_t)c.ogm_width * c.ogm_height, g1 = (size_t)c.dagm_width * c.dagm_height;
-    if (c.ogm_enable && dst->ogm) { cpy(dst->ogm + n_packed * g0, o.ogm + n_packed * g0, (na - n_packed) * g0); }
-    if (c.dagm_enable && dst->dagm) { cpy(dst->dagm + n_packed * g1, o.dagm + n_packed * g1, (na - n_packed) * g1); }
+    if (c.ogm_enable && dst->ogm && pk0) { cpy(dst->ogm + n_packed * g0, o.ogm + n_packed * g0, (na - n_packed) * g0); }
+    if (c.dagm_enable && dst->dagm && pk1) { cpy(dst->dagm + n_packed * g1, o.dagm + n_packed * g1, (na - n_packed) * g1); }
   }
+  if (c.ogm_enable && dst->ogm && !pk0) cpy(dst->ogm, o.ogm, na * c.ogm_width * c.ogm_height);
+  if (c.dagm_enable && dst->dagm && !pk1) cpy(dst->dagm, o.dagm, na * c.dagm_width * c.dagm_height);
   static const bool debug = getenv("SB_DEBUG_XFER") != nullptr;
   auto ms_since = [&] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); };
   double t_first = 0, t_last = 0, t_pool = 0;

@@ -13,6 +13,8 @@
 #include <cstring>
 #include <mutex>
 #include <thread>
+#include <pthread.h>
+#include <sched.h>
 #include <vector>
 
 #if defined(__x86_64__)
@@ -142,9 +144,27 @@ struct Piece {
 // A fixed pool; submit() queues pieces, wait() blocks until every queued piece is done.
 class SbExpandPool {
  public:
-  explicit SbExpandPool(int threads) : fn_(pick_expand()), diff_fn_(pick_expand_diff()) {
+  // first_cpu >= 0: worker i is pinned to the (first_cpu + i)-th CPU this process may run on (wrapping), so the
+  // pools of the ranks of one box (one process per GPU) sit on disjoint cores instead of migrating over each other
+  explicit SbExpandPool(int threads, int first_cpu = -1) : fn_(pick_expand()), diff_fn_(pick_expand_diff()) {
     if (threads < 1) threads = 1;
-    for (int i = 0; i < threads; ++i) workers_.emplace_back([this] { run(); });
+    std::vector<int> cpus;
+    if (first_cpu >= 0) {
+      cpu_set_t set;
+      CPU_ZERO(&set);
+      if (sched_getaffinity(0, sizeof(set), &set) == 0)
+        for (int c = 0; c < CPU_SETSIZE; ++c)
+          if (CPU_ISSET(c, &set)) cpus.push_back(c);
+    }
+    for (int i = 0; i < threads; ++i) {
+      workers_.emplace_back([this] { run(); });
+      if (!cpus.empty()) {
+        cpu_set_t one;
+        CPU_ZERO(&one);
+        CPU_SET(cpus[(size_t)(first_cpu + i) % cpus.size()], &one);
+        pthread_setaffinity_np(workers_.back().native_handle(), sizeof(one), &one);
+      }
+    }
   }
   ~SbExpandPool() {
     {
@@ -203,14 +223,14 @@ class SbExpandPool {
 // C-linkage handles for sb_api.cu (which nvcc compiles)
 #define SBX_LOCAL __attribute__((visibility("hidden")))
 extern "C" {
-SBX_LOCAL void* sbx_pool_create(int threads);
+SBX_LOCAL void* sbx_pool_create(int threads, int first_cpu);
 SBX_LOCAL void sbx_pool_destroy(void* p);
 SBX_LOCAL void sbx_pool_submit(void* p, const uint8_t* bits, uint8_t* out, size_t n_bytes_in, size_t piece);
 SBX_LOCAL void sbx_pool_submit_diff(void* p, const uint8_t* bits, uint8_t* prev, uint8_t* out, size_t n_bytes_in,
                                     size_t piece);
 SBX_LOCAL void sbx_pool_wait(void* p);
 SBX_LOCAL int sbx_pool_threads(void* p);
-void* sbx_pool_create(int threads) { return new SbExpandPool(threads); }
+void* sbx_pool_create(int threads, int first_cpu) { return new SbExpandPool(threads, first_cpu); }
 void sbx_pool_destroy(void* p) { delete static_cast<SbExpandPool*>(p); }
 void sbx_pool_submit(void* p, const uint8_t* bits, uint8_t* out, size_t n_bytes_in, size_t piece) {
   static_cast<SbExpandPool*>(p)->submit(bits, out, n_bytes_in, piece);

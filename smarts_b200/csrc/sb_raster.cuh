@@ -311,8 +311,15 @@ __device__ __forceinline__ uint32_t d_expand4(uint32_t b) {  // low 4 bits -> 4 
 // per thread per step, written with a single 256-bit store.  A warp whose 32 words are all
 // 0 or all ~0 (most of an occupancy grid) skips the table.
 template <int T>
-__device__ __forceinline__ void d_store_rows(const uint32_t* bits, const uint2* lut, uint8_t* dst, int rows, int wpr,
+__device__ __forceinline__ void d_store_rows(const uint32_t* bits, const uint2* lut, uint8_t* dst, int rows, int W, int wpr,
                                              int stride, int tid) {
+  if (W & 31) {  // a width that is not a multiple of 32 pixels: rows are not 32-byte aligned -- byte stores, cropped
+    for (int i = tid; i < rows * W; i += T) {
+      const int row = i / W, col = i - row * W;
+      dst[i] = ((bits[row * stride + (col >> 5)] >> (col & 31)) & 1u) ? 255 : 0;
+    }
+    return;
+  }
   const int n_words = rows * wpr;
   if ((wpr & (wpr - 1)) == 0 && wpr <= T && (n_words & (T - 1)) == 0) {
     // Common shapes (W a power of two up to 8192 px, rows * W/32 a multiple of 256): this thread's word keeps
@@ -467,10 +474,10 @@ __device__ __forceinline__ void d_raster_agent(const DCfg& c, const DMap& m, con
     }
     d_slice_sync<T>(bar);
     if (rg < H0)
-      d_store_rows<T>(bits0, lut, o.ogm + (size_t)ai * W0 * H0 + (size_t)rg * W0, min(H0 - rg, T), wpr0,
+      d_store_rows<T>(bits0, lut, o.ogm + (size_t)ai * W0 * H0 + (size_t)rg * W0, min(H0 - rg, T), W0, wpr0,
                       stride0, tid);
     if (rg < H1)
-      d_store_rows<T>(bits1, lut, o.dagm + (size_t)ai * W1 * H1 + (size_t)rg * W1, min(H1 - rg, T), wpr1,
+      d_store_rows<T>(bits1, lut, o.dagm + (size_t)ai * W1 * H1 + (size_t)rg * W1, min(H1 - rg, T), W1, wpr1,
                       stride1, tid);
     if (rg + T < Hmax) d_slice_sync<T>(bar);
   }

@@ -132,9 +132,7 @@ class Engine:
         self._h = C.c_void_p()
         rc = self._lib.sb_create(C.byref(cfg), C.byref(self._h))
         self._check(rc, "sb_create")
-        m, keep = _abi.make_map_struct(road_map.arrays(), road_map.spacing)
-        self._check(self._lib.sb_upload_map(self._h, C.byref(m)), "sb_upload_map")
-        del keep
+        self.upload_map(road_map)
         if cfg.lidar_enable:
             if base_rays is None:
                 raise SmartsB200Error("lidar enabled but no base ray table given")
@@ -146,6 +144,14 @@ class Engine:
         self._graph_launches = 0
 
     # -- plumbing ------------------------------------------------------------------------
+    def upload_map(self, road_map: RoadMapData):
+        """Load (or, on a live handle, replace) the road map.  After a replacement every env must be reset
+        (``reset`` without ``env_ids``) before the next step / observe -- the library refuses anything else."""
+        m, keep = _abi.make_map_struct(road_map.arrays(), road_map.spacing)
+        self._check(self._lib.sb_upload_map(self._h, C.byref(m)), "sb_upload_map")
+        del keep
+        self.road_map = road_map
+
     def _check(self, rc: int, what: str):
         if rc != 0:
             msg = self._lib.sb_last_error(self._h)
@@ -267,6 +273,8 @@ class Engine:
         out = {}
         for name, (shape, dt) in _abi.obs_shapes(self.cfg).items():
             if packed_grids and name in ("ogm", "dagm"):
+                if (shape[0] * shape[1]) % 32 or shape[1] % 8:
+                    raise SmartsB200Error("packed grids need a width that is a multiple of 8 and W * H a multiple of 32")
                 shape = (shape[0], shape[1] // 8)
             full = (self.E, self.A) + tuple(shape)
             t = self._torch.empty(full, dtype=getattr(self._torch, np.dtype(dt).name), pin_memory=pinned)

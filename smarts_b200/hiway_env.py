@@ -18,6 +18,7 @@ from __future__ import annotations
 
 import copy
 import dataclasses
+import itertools
 import math
 import os
 from dataclasses import dataclass, field
@@ -110,7 +111,7 @@ class BatchedHiWayEnv:
                  fixed_timestep_sec: float = 0.1, seed: int = 42, headless: bool = True, device: int = 0,
                  auto_reset: bool = True, start_jitter: float = 0.0, route_cap: int = 16, traj_len: int = 10,
                  lidar_wall_height: float = 0.0, wp_out_len: Optional[int] = None, sim_name: Optional[str] = None,
-                 ego_centric: bool = False, shard=None, **_ignored_reference_kwargs):
+                 ego_centric: bool = False, shard=None, min_via_cap: int = 0, **_ignored_reference_kwargs):
         from .engine import Engine  # raises without the CUDA library / a GPU: no CPU fallback
         if not agent_specs:
             raise ValueError("agent_specs is empty")
@@ -124,10 +125,11 @@ class BatchedHiWayEnv:
         itfs = [s.interface for s in agent_specs.values()]
         if any(i is None for i in itfs):
             raise ValueError("every AgentSpec needs an interface")
-        if any(i is not itfs[0] and repr(i) != repr(itfs[0]) for i in itfs[1:]):
-            raise NotImplementedError("one AgentInterface per batch (SbConfig is per handle); "
-                                      "use one env per interface")
-        self.interface: AgentInterface = itfs[0]
+        # One SbConfig per handle: the handle computes the UNION of the agents' sensors for every agent and each
+        # agent's Observation shows what its own interface subscribes to (vehicle.py:470-560 attaches sensors per
+        # agent).  Everything that is not an on/off sensor choice must agree.
+        self.interface: AgentInterface = self._union_interface(itfs)
+        self._own_itf: List[AgentInterface] = itfs
         self.scenario = scenario
         self.road_map = scenario.road_map()
         missing = [a for a in self.agent_ids if a not in scenario.missions]
@@ -151,7 +153,7 @@ class BatchedHiWayEnv:
         self.cfg = compile_config(self.interface, self.E, self.A, self.M, self.dt, device=device,
                                   route_cap=route_cap, traj_len=traj_len, lidar_wall_height=lidar_wall_height,
                                   wp_out_len=wp_out_len,
-                                  via_cap=max([len(scenario.missions[a].via) for a in self.agent_ids] + [0]))
+                                  via_cap=max([len(scenario.missions[a].via) for a in self.agent_ids] + [int(min_via_cap)]))
         # ego_centric: the tensor path (std_obs / step_tensor) hands out ego-frame buffers (k_ego_frame); the dict
         # path keeps world-frame Observations -- use ego_centric.get_egocentric_adapters in the AgentSpec there
         self.ego_centric = bool(ego_centric)
@@ -165,7 +167,49 @@ class BatchedHiWayEnv:
         self._tick = np.zeros(self.E, np.int64)           # per-env step_count
         self._global_tick = 0
         self._done_agents = np.zeros((self.E, self.A), bool)
+        self._aad = None                                  # [E] bool on the device: agents_alive criterion of the last tick
         self._host: Dict[str, np.ndarray] = {}
+
+    _MASKABLE = ("neighborhood_vehicles", "lidar", "ogm", "drivable_area_grid_map", "accelerometer")
+
+    @classmethod
+    def _union_interface(cls, itfs: Sequence[AgentInterface]) -> AgentInterface:
+        first = itfs[0]
+        if all(i is first or repr(i) == repr(first) for i in itfs[1:]):
+            return first
+        union = {}
+        for name in cls._MASKABLE:
+            on = [getattr(i, name) for i in itfs if getattr(i, name)]
+            if any(repr(c) != repr(on[0]) for c in on[1:]):
+                raise NotImplementedError(f"agents enable {name} with different parameters: one configuration per "
+                                          f"sensor and handle (use one env per interface)")
+            union[name] = on[0] if on else getattr(first, name)
+        rest = [dataclasses.replace(i, **union) for i in itfs]
+        if any(repr(r) != repr(rest[0]) for r in rest[1:]):
+            # (the waypoint sensor is not maskable: without it the trip meter reads another query, sensors.py:337-345)
+            raise NotImplementedError("agent interfaces may differ in which of " + ", ".join(cls._MASKABLE) +
+                                      " they enable, nothing else (use one env per interface)")
+        return rest[0]
+
+    def set_scenario(self, scenario: Scenario):
+        """The next scenario of a scenario cycle (hiway_env.py:265-285 -> SMARTS.reset(scenario) -> SMARTS.setup,
+        smarts.py:411-460): same agents and social-slot count (both are sizes of the handle), possibly another map,
+        other missions and traffic.  Takes effect with the next ``reset`` -- which the library insists on when the
+        map changed."""
+        missing = [a for a in self.agent_ids if a not in scenario.missions]
+        if missing:
+            raise ValueError(f"scenario has no mission for agents {missing}")
+        if int(scenario.n_social) != self.M:
+            raise ValueError(f"scenario has {scenario.n_social} social slots, the handle was built for {self.M}")
+        if max([len(scenario.missions[a].via) for a in self.agent_ids] + [0]) > self.cfg.via_cap:
+            raise ValueError("scenario has more vias per mission than the handle was built for")
+        rm = scenario.road_map()
+        if rm is not self.road_map:
+            self.engine.upload_map(rm)
+            self.road_map = rm
+            self._setup = False
+        self.scenario = scenario
+        self._start = self._build_starts(self._seed)
 
     @staticmethod
     def _own_adapters(spec: AgentSpec) -> AgentSpec:
@@ -276,6 +320,11 @@ class BatchedHiWayEnv:
                           keep_social=env_ids is not None)
         self._tick[sel] = 0
         self._done_agents[sel] = False
+        if self._aad is not None:
+            if env_ids is None:
+                self._aad = None
+            else:
+                self._aad[self._torch.from_numpy(np.asarray(env_ids, np.int64)).to(self._aad.device)] = False
 
     # -- device-resident step (the scalable API) ----------------------------------------------
     def reset_tensor(self) -> Dict[str, Any]:
@@ -310,8 +359,32 @@ class BatchedHiWayEnv:
         obs = eng.obs()
         if "ev_done" in obs:  # done agents leave the simulation after this observation (agent_manager teardown):
             alive = eng.state()["alive"]  # a device-side op on the zero-copy views, no synchronisation
+            crit = self.interface.done_criteria.agents_alive
+            if crit:  # DoneCriteria.agents_alive: a host-layer criterion over the agents that entered this tick alive
+                before = alive[:, :self.A] != 0
+                self._aad = self._agents_alive_done(before, crit)
+                obs["ev_done"] |= (self._aad[:, None] & before).to(obs["ev_done"].dtype)
             alive[:, :self.A] &= (obs["ev_done"] == 0).to(alive.dtype)
         return obs
+
+    def _agents_alive_done(self, alive, crit):
+        """Sensors._agents_alive_done_check (sensors.py:404-441) per env, on the device: ``alive`` [E, A] bool =
+        agent_manager.agent_ids at observation time.  Every agent here is an ego agent, so the ego and total
+        minima read the same count.  Returns [E] bool (the criterion is the shared interface's: the same for every
+        agent of an env)."""
+        n = alive.sum(1)
+        res = self._torch.zeros_like(n, dtype=self._torch.bool)
+        if crit.minimum_ego_agents_alive:
+            res |= n < int(crit.minimum_ego_agents_alive)
+        if crit.minimum_total_agents_alive:
+            res |= n < int(crit.minimum_total_agents_alive)
+        for lst in crit.agent_lists_alive or ():
+            assert isinstance(lst.agents_list, (list, set, tuple)), "Please specify a list of agent ids to watch"
+            assert isinstance(lst.minimum_agents_alive_in_list, int) and lst.minimum_agents_alive_in_list >= 0
+            idx = [self.agent_ids.index(i) for i in lst.agents_list if i in self.agent_ids]
+            cnt = alive[:, idx].sum(1) if idx else self._torch.zeros_like(n)
+            res |= cnt < lst.minimum_agents_alive_in_list
+        return res
 
     def auto_reset_done_envs(self) -> np.ndarray:
         """Reset every env whose agents are all done (parallel_env.py:300-326); returns their ids."""
@@ -376,7 +449,8 @@ class BatchedHiWayEnv:
                 "pos": t.stack([ego["pos_x"], ego["pos_y"], ego["pos_z"]], -1),
                 "speed": ego["speed"].to(f32), "steering": s["steering"].to(f32), "yaw_rate": ego["yaw_rate"].to(f32),
             },
-            "events": {"agents_alive_done": t.zeros_like(ev, dtype=t.int8), "collisions": bit(_abi.SB_EV_COLLISION),
+            "events": {"agents_alive_done": (t.zeros_like(ev, dtype=t.int8) if self._aad is None
+                                             else self._aad[:, None].expand_as(ev).to(t.int8)), "collisions": bit(_abi.SB_EV_COLLISION),
                        "not_moving": bit(_abi.SB_EV_NOT_MOVING), "off_road": bit(_abi.SB_EV_OFF_ROAD),
                        "off_route": bit(_abi.SB_EV_OFF_ROUTE), "on_shoulder": bit(_abi.SB_EV_ON_SHOULDER),
                        "reached_goal": bit(_abi.SB_EV_REACHED_GOAL),
@@ -429,12 +503,13 @@ class BatchedHiWayEnv:
     def _fetch(self):
         self._host = self.engine.obs_numpy()
         self._host_state = self.engine.state_numpy()
+        self._host_aad = self._aad.cpu().numpy() if self._aad is not None else np.zeros(self.E, bool)
 
     def _vehicle_id(self, e: int, slot: int) -> str:
         return self.agent_ids[slot] if slot < self.A else f"social-{slot - self.A}"
 
     def _observation(self, e: int, a: int) -> Observation:
-        o, s, itf, rm = self._host, self._host_state, self.interface, self.road_map
+        o, s, itf, rm = self._host, self._host_state, self._own_itf[a], self.road_map
         px, py, pz = s["pos_x"][e, a], s["pos_y"][e, a], s["pos_z"][e, a]
         hd, sp = float(s["heading"][e, a]), float(s["speed"][e, a])
         el = int(o["ego_lane"][e, a])
@@ -448,10 +523,10 @@ class BatchedHiWayEnv:
             road_id=road_id, lane_id=lane_id, lane_index=lane_index, mission=self.scenario.missions[self.agent_ids[a]],
             linear_velocity=np.array([-math.sin(hd) * sp, math.cos(hd) * sp, 0.0]),
             angular_velocity=np.array([0.0, 0.0, float(s["yaw_rate"][e, a])]),
-            linear_acceleration=o["acc_linear"][e, a].copy() if "acc_linear" in o else None,
-            angular_acceleration=o["acc_angular"][e, a].copy() if "acc_angular" in o else None,
-            linear_jerk=o["acc_linear_jerk"][e, a].copy() if "acc_linear_jerk" in o else None,
-            angular_jerk=o["acc_angular_jerk"][e, a].copy() if "acc_angular_jerk" in o else None)
+            linear_acceleration=o["acc_linear"][e, a].copy() if itf.accelerometer else None,
+            angular_acceleration=o["acc_angular"][e, a].copy() if itf.accelerometer else None,
+            linear_jerk=o["acc_linear_jerk"][e, a].copy() if itf.accelerometer else None,
+            angular_jerk=o["acc_angular_jerk"][e, a].copy() if itf.accelerometer else None)
         nbrs = None
         if itf.neighborhood_vehicles:
             nbrs = []
@@ -500,7 +575,8 @@ class BatchedHiWayEnv:
                         off_route=bool(bits & _abi.SB_EV_OFF_ROUTE), on_shoulder=bool(bits & _abi.SB_EV_ON_SHOULDER),
                         wrong_way=bool(bits & _abi.SB_EV_WRONG_WAY), not_moving=bool(bits & _abi.SB_EV_NOT_MOVING),
                         reached_goal=bool(bits & _abi.SB_EV_REACHED_GOAL),
-                        reached_max_episode_steps=bool(bits & _abi.SB_EV_REACHED_MAX_STEPS), agents_alive_done=False)
+                        reached_max_episode_steps=bool(bits & _abi.SB_EV_REACHED_MAX_STEPS),
+                        agents_alive_done=bool(self._host_aad[e]))
         return Observation(dt=self.dt, step_count=int(self._tick[e]), elapsed_sim_time=float(self._tick[e]) * self.dt,
                            events=events, ego_vehicle_state=ego, neighborhood_vehicle_states=nbrs,
                            waypoint_paths=wps,
@@ -614,12 +690,17 @@ class HiWayEnv:
                  seed: int = 42, timestep_sec: Optional[float] = None, **kwargs):
         if not scenarios:
             raise ValueError("scenarios is empty")
-        if len(scenarios) > 1:
-            raise NotImplementedError("one scenario per env (the map is uploaded once per handle)")
         dt = fixed_timestep_sec or timestep_sec or 0.1  # hiway_env.py:112-113
         self._agent_specs = agent_specs
+        # Scenario.scenario_variations (scenario.py:137-166): the roots shuffled once, then cycled; reset() takes the next
+        order = list(scenarios)
+        if shuffle_scenarios:
+            np.random.default_rng(seed).shuffle(order)
+        self._scenarios_iterator = itertools.cycle(order)
+        via_cap = max(len(m.via) for sc in order for m in sc.missions.values()) if any(sc.missions for sc in order) else 0
         self._batched: Optional[BatchedHiWayEnv] = BatchedHiWayEnv(
-            scenarios[0], agent_specs, n_envs=1, fixed_timestep_sec=dt, seed=seed, auto_reset=False, **kwargs)
+            order[0], agent_specs, n_envs=1, fixed_timestep_sec=dt, seed=seed, auto_reset=False,
+            min_via_cap=via_cap, **kwargs)
         self._dones_registered = 0
 
     @property
@@ -637,6 +718,10 @@ class HiWayEnv:
         return seed
 
     def reset(self) -> Dict[str, Any]:
+        """hiway_env.py:265-285: the next scenario of the cycle, then SMARTS.reset."""
+        scenario = next(self._scenarios_iterator)
+        if scenario is not self.batched.scenario:
+            self.batched.set_scenario(scenario)
         self._dones_registered = 0
         return self.batched.reset()[0]
 

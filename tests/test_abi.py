@@ -69,7 +69,7 @@ def test_error_paths_without_a_device():
     cfg = make_cfg(E=0, A=1)
     assert lib.sb_create(C.byref(cfg), C.byref(h)) == -1
     lib.sb_destroy(h)
-    cfg = make_cfg(E=1, A=1, ogm=(100, 64, 0.5))  # width must be a multiple of 32
+    cfg = make_cfg(E=1, A=1, ogm=(1025, 64, 0.5))  # width 1 .. 1024 (any width in that range is accepted)
     assert lib.sb_create(C.byref(cfg), C.byref(h)) == -1 and b"ogm" in lib.sb_last_error(h)
     lib.sb_destroy(h)
     lib.sb_destroy(None)

@@ -606,6 +606,32 @@ def test_maximum_grid_sizes_and_multi_pass_rows():
         eng.close(); ora.close()
 
 
+def test_grid_widths_that_are_not_multiples_of_32():
+    """Any width from 1 to 1024 (AgentInterface takes what the user asks for, agent_interface.py:62-79): the bit image
+    is padded to whole words, the byte image is cropped -- bit-exact against the oracle, on the device views and
+    through the host-buffer call (such a grid travels as plain bytes unless W * H is a multiple of 32)."""
+    import torch
+    rm = load_map("4lane")
+    E, A, M = 3, 4, 20
+    x, y, h, v, route, rlen = scenario_gen.agent_starts(rm, E, MISSIONS_4LANE, 16, 81, jitter=40.0, speed=7.0)
+    soc = scenario_gen.SocialTraffic(rm, E, M, 82).states(2)
+    act = np.zeros((E, A), np.int32)
+    for ogm, dagm in (((100, 75, 0.3), (50, 33, 0.6)), ((1, 5, 3.0), (333, 64, 0.15)), ((257, 300, 0.1), (96, 31, 0.4))):
+        cfg = make_cfg(E=E, A=A, M=M, ogm=ogm, dagm=dagm, route_cap=16)
+        eng, ora = engine(rm, cfg), oracle_world(rm, cfg, threads=8)
+        for w in (eng, ora):
+            w.reset(x, y, h, v, route, rlen)
+        ora.set_social(soc); ora.step(act); ora.observe()
+        bufs = eng.host_obs_buffers()
+        eng.step_host(act, soc)
+        eng.copy_obs_to_host(bufs)
+        got, want = eng.obs_numpy(), ora.obs()
+        assert_same(got, want)
+        assert_same({k: t.numpy() for k, t in bufs.items()}, want)
+        assert want["dagm"].any() and tuple(got["ogm"].shape[-2:]) == (ogm[1], ogm[0])
+        eng.close(); ora.close()
+
+
 def test_captured_tick_replays_bit_identically():
     """Engine.capture_tick: the tick as a CUDA graph over fixed action / social tensors gives the states and
     observations of the eager calls, tick for tick."""

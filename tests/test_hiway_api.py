@@ -258,6 +258,127 @@ def test_sharded_envs_reproduce_the_unsharded_job():
 
 
 @pytest.mark.gpu
+def test_scenario_cycle_replaces_the_map_on_reset():
+    """hiway_env.py:265-285: reset() takes the next scenario of the cycle; here that means another road map on the
+    same handle (sb_upload_map again), and the library refuses to step until every env was reset onto it."""
+    from smarts_b200.engine import SmartsB200Error
+    fe = {"A0": Mission("gneE20", 0, 5.0, "gneE27", start_speed=4.0), "A1": Mission("gneE36", 1, 5.0, "gneE25", start_speed=4.0)}
+    fl = {"A0": MISSIONS["A0"], "A1": MISSIONS["A1"]}
+    itf = AgentInterface.from_type(AgentType.Laner, neighborhood_vehicles=True)
+    specs = _specs(itf, ("A0", "A1"))
+    scs = [Scenario("4lane", fl, None, 0), Scenario("figure_eight", fe, None, 0)]
+    env = HiWayEnv(scs, specs, shuffle_scenarios=False)
+    seen = []
+    for k in range(4):                      # 4lane, figure_eight, 4lane, figure_eight
+        obs = env.reset()
+        for t in range(3):
+            obs, rew, dones, infos = env.step({i: "keep_lane" for i in obs})
+        seen.append({i: (o.ego_vehicle_state.road_id, o.ego_vehicle_state.position.copy(),
+                         o.waypoint_paths[0][-1].pos.copy()) for i, o in obs.items()})
+    assert seen[0]["A0"][0] == "edge-south-SN" and seen[1]["A0"][0] == "gneE20"
+    for i in ("A0", "A1"):                  # a cycle later the same scenario gives the same episode
+        for a, b in ((0, 2), (1, 3)):
+            assert seen[a][i][0] == seen[b][i][0] and np.array_equal(seen[a][i][1], seen[b][i][1])
+            assert np.array_equal(seen[a][i][2], seen[b][i][2])
+    fresh = HiWayEnv([scs[1]], specs)       # and the same as a handle that only ever saw that map
+    obs = fresh.reset()
+    for t in range(3):
+        obs, _, _, _ = fresh.step({i: "keep_lane" for i in obs})
+    for i in ("A0", "A1"):
+        assert np.array_equal(obs[i].ego_vehicle_state.position, seen[1][i][1])
+        assert np.array_equal(obs[i].waypoint_paths[0][-1].pos, seen[1][i][2])
+    fresh.close()
+    eng = env.batched.engine                # the C-ABI's guard
+    eng.upload_map(load_map("4lane"))
+    with pytest.raises(SmartsB200Error):
+        eng.observe()
+    env.close()
+    with pytest.raises(ValueError):         # social-slot count is a size of the handle
+        e2 = HiWayEnv([scs[0]], specs)
+        try:
+            e2.batched.set_scenario(Scenario("4lane", fl, None, 3))
+        finally:
+            e2.close()
+
+
+@pytest.mark.gpu
+def test_agents_with_different_sensor_sets_share_a_handle():
+    """vehicle.py:470-560 attaches sensors per agent: A0 asks for lidar + OGM, A1 for neighbours only.  The handle
+    computes the union; each Observation carries what its own interface subscribes to, with the values a
+    single-interface env gives."""
+    rm = load_map("4lane")
+    base = AgentInterface.from_type(AgentType.Laner, accelerometer=False)
+    i0 = base.replace(lidar=True, ogm=OGM(64, 64, 0.5))
+    i1 = base.replace(neighborhood_vehicles=NeighborhoodVehicles(radius=400), accelerometer=True)
+    fl = {"A0": MISSIONS["A0"], "A1": MISSIONS["A1"]}
+    specs = {"A0": AgentSpec(interface=i0), "A1": AgentSpec(interface=i1)}
+    env = HiWayEnv([Scenario(rm, fl, None, 0)], specs)
+    both = i0.replace(neighborhood_vehicles=NeighborhoodVehicles(radius=400), accelerometer=True)
+    ref = HiWayEnv([Scenario(rm, fl, None, 0)], {"A0": AgentSpec(interface=both), "A1": AgentSpec(interface=both)})
+    obs, want = env.reset(), ref.reset()
+    for t in range(3):
+        obs, _, _, _ = env.step({i: "keep_lane" for i in obs})
+        want, _, _, _ = ref.step({i: "keep_lane" for i in want})
+    a0, a1 = obs["A0"], obs["A1"]
+    assert a0.lidar_point_cloud is not None and a0.occupancy_grid_map is not None
+    assert a0.neighborhood_vehicle_states is None and a0.ego_vehicle_state.linear_acceleration is None
+    assert a1.lidar_point_cloud is None and a1.occupancy_grid_map is None
+    assert len(a1.neighborhood_vehicle_states) == len(want["A1"].neighborhood_vehicle_states) == 1
+    assert np.array_equal(a1.ego_vehicle_state.linear_acceleration, want["A1"].ego_vehicle_state.linear_acceleration)
+    assert np.array_equal(a0.occupancy_grid_map.data, want["A0"].occupancy_grid_map.data)
+    assert np.array_equal(np.asarray(a0.lidar_point_cloud[0]), np.asarray(want["A0"].lidar_point_cloud[0]))
+    assert np.array_equal(a0.waypoint_paths[0][0].pos, want["A0"].waypoint_paths[0][0].pos)
+    env.close(); ref.close()
+    with pytest.raises(NotImplementedError):    # same sensor, other parameters
+        HiWayEnv([Scenario(rm, fl, None, 0)], {"A0": AgentSpec(interface=i0),
+                                               "A1": AgentSpec(interface=base.replace(ogm=OGM(32, 32, 1.0)))})
+    with pytest.raises(NotImplementedError):    # not a sensor choice
+        HiWayEnv([Scenario(rm, fl, None, 0)], {"A0": AgentSpec(interface=i0),
+                                               "A1": AgentSpec(interface=base.replace(max_episode_steps=7))})
+
+
+@pytest.mark.gpu
+def test_agents_alive_done_criteria():
+    """DoneCriteria.agents_alive (sensors.py:404-441): once A0 has reached its goal and left, the tick after it the
+    watch list [A0] has no agent alive -> every remaining agent is done with events.agents_alive_done."""
+    from smarts_b200.agent_interface import AgentsAliveDoneCriteria, AgentsListAlive
+    rm = load_map("4lane")
+    crit = DoneCriteria(agents_alive=AgentsAliveDoneCriteria(agent_lists_alive=[AgentsListAlive(["A0"], 1)]))
+    itf = AgentInterface.from_type(AgentType.LanerWithSpeed, done_criteria=crit)
+    missions = dict(MISSIONS, A0=Mission("edge-south-SN", 1, 10.0, "edge-south-SN", end_lane=1, end_offset=22.0,
+                                         goal_radius=2.0, start_speed=5.0))
+    env = BatchedHiWayEnv(Scenario(rm, missions, None, 0), _specs(itf), n_envs=3, auto_reset=False)
+    obs = env.reset()
+    left_at = None
+    for t in range(60):
+        obs, rew, dones, infos = env.step([{i: (8.0, 0) for i in ob} for ob in obs])
+        if left_at is None:
+            assert not any(o.events.agents_alive_done for ob in obs for o in ob.values())
+            if dones[0].get("A0"):
+                assert obs[0]["A0"].events.reached_goal and not dones[0]["__all__"]
+                left_at = t
+        else:
+            assert t == left_at + 1
+            for e in range(3):
+                assert set(obs[e]) == {"A1", "A2", "A3"} and dones[e]["__all__"]
+                assert all(o.events.agents_alive_done for o in obs[e].values()) and all(dones[e][i] for i in obs[e])
+            so = env.std_obs()
+            assert so["events"]["agents_alive_done"].cpu().numpy().all()
+            break
+    assert left_at is not None
+    env.close()
+    # minimum_total_agents_alive: four agents enter the first tick alive, the minimum is five
+    itf5 = AgentInterface.from_type(AgentType.LanerWithSpeed, done_criteria=DoneCriteria(
+        agents_alive=AgentsAliveDoneCriteria(minimum_total_agents_alive=5)))
+    env = BatchedHiWayEnv(Scenario(rm, MISSIONS, None, 0), _specs(itf5), n_envs=2, auto_reset=False)
+    obs = env.reset()
+    assert not obs[0]["A0"].events.agents_alive_done
+    obs, rew, dones, infos = env.step([{i: (8.0, 0) for i in ob} for ob in obs])
+    assert all(d["__all__"] for d in dones) and obs[1]["A3"].events.agents_alive_done
+    env.close()
+
+
+@pytest.mark.gpu
 def test_staggered_auto_reset_leaves_running_envs_alone():
     """Envs that finish on different ticks: an env that is auto-reset must not disturb the others (in the reference
     every ParallelEnv env is its own process).  Env 1 stands still and is ended by `not_moving` every few ticks
