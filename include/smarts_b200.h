@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define SB_ABI_VERSION 5
+#define SB_ABI_VERSION 6
 
 /* error codes */
 #define SB_OK 0
@@ -60,6 +60,10 @@ extern "C" {
 #define SB_STATUS_LIDAR_OVERFLOW 4u  /* more candidate boxes / edges near one agent than the kernel stages */
 #define SB_STATUS_TTC_TRUNCATED 8u   /* lane_ttc saw a capped neighbour / path / waypoint block (or a lane index
                                         beyond the path list, an IndexError in the reference) */
+#define SB_STATUS_RW_TRUNCATED 16u   /* RoadWaypoints: more lanes / paths / nearby roads than the caps below, or the
+                                        walk back through incoming lanes went deeper than SB_RW_MAX_DEPTH */
+#define SB_RW_MAX_DEPTH 8            /* nesting of RoadWaypointsSensor.paths_for_lane (sensors.py:1020-1027) */
+#define SB_RW_MAX_ROADS 64           /* the road + its parallel roads + oncoming roads (sensors.py:1008-1010) */
 
 /* Events bits (smarts/core/events.py:23-34) in SbObsPtrs.ev_events and SbConfig.done_mask
  * (DoneCriteria, smarts/core/agent_interface.py:185-206). */
@@ -131,6 +135,14 @@ typedef struct SbConfig {
    * stays (0,0,0) with lidar_miss_inf = 0 and becomes (NaN,NaN,NaN) with lidar_miss_inf = 1 (inf - x through
    * the rotation, as in the reference). */
   int32_t ego_frame;
+  /* RoadWaypoints (agent_interface.py:81-91, sensors.py:991-1043): waypoint paths along every lane of the road
+   * the ego is on, its parallel roads and the oncoming roads next to it, from `horizon` metres behind the ego over
+   * 2 * horizon lane points.  rw_lanes_cap lanes and rw_paths_cap paths (over all lanes) are written per agent;
+   * 2 * rw_horizon <= SB_MAX_LOOKAHEAD. */
+  int32_t rw_enable;
+  int32_t rw_horizon;      /* RoadWaypoints.horizon (default 20) */
+  int32_t rw_lanes_cap;
+  int32_t rw_paths_cap;
 } SbConfig;
 
 /* Per-scenario constant road map (host pointers, copied once).  Built by
@@ -139,6 +151,7 @@ typedef struct SbConfig {
 typedef struct SbMap {
   int32_t n_roads, n_lanes, n_lanepoints, n_shape_pts, n_polys, n_poly_verts, n_edges;
   int32_t n_lane_out, n_lp_next;
+  int32_t n_lane_in, n_road_par;
   double lanepoint_spacing;
   /* roads */
   const int32_t *road_lane_start, *road_lane_count;   /* [n_roads] lanes of a road are contiguous */
@@ -164,6 +177,11 @@ typedef struct SbMap {
   const int32_t *poly_start;                           /* [n_polys+1] CSR into poly_x/y */
   const double *poly_x, *poly_y;                       /* [n_poly_verts] */
   const double *road_edges;                            /* [n_edges,4] ax,ay,bx,by */
+  /* RoadWaypoints tables */
+  const int32_t *lane_in_start;                        /* [n_lanes+1] CSR into lane_in */
+  const int32_t *lane_in;                              /* [n_lane_in] Lane.incoming_lanes, sumo_road_network.py:342-348 */
+  const int32_t *road_par_start;                       /* [n_roads+1] CSR into road_par */
+  const int32_t *road_par;                             /* [n_road_par] Road.parallel_roads, sumo_road_network.py:607-618 */
 } SbMap;
 
 /* Device pointers owned by the library (valid until sb_destroy). */
@@ -238,6 +256,22 @@ typedef struct SbObsPtrs {
   int32_t *via_near_idx;       /* [E*A, via_cap] nearest first (stable), -1 padded */
   int32_t *via_hit_count;      /* [E*A] points collected by this observation */
   int32_t *via_hit_idx;        /* [E*A, via_cap] in mission order, -1 padded */
+  /* road waypoints (rw_enable): Observation.road_waypoints (RoadWaypoints.lanes, sensors.py:104-107) as a lane
+   * list in the reference's dict insertion order plus one flat path list; path p belongs to lane slot
+   * rw_path_slot[p]; the paths of one lane are consecutive and in the reference's list order (the lane groups
+   * themselves follow the order in which the sensor last computed each lane, which is the slot order unless a
+   * road is listed twice).  Lc = rw_lanes_cap, Pc = rw_paths_cap, Hz = 2 * rw_horizon + 1. */
+  int32_t *rw_n_lanes;         /* [E*A] lanes found (uncapped) */
+  int32_t *rw_lane;            /* [E*A, Lc] map lane index (the dict key), -1 padded */
+  int32_t *rw_n_paths;         /* [E*A] paths found (uncapped) */
+  int32_t *rw_path_slot;       /* [E*A, Pc] index into rw_lane, -1 padded */
+  int32_t *rw_len;             /* [E*A, Pc] waypoints of the path */
+  double *rw_pos;              /* [E*A, Pc, Hz, 2] */
+  double *rw_heading;          /* [E*A, Pc, Hz] */
+  float *rw_lane_width;        /* [E*A, Pc, Hz] */
+  float *rw_speed_limit;       /* [E*A, Pc, Hz] */
+  int32_t *rw_wp_lane;         /* [E*A, Pc, Hz] Waypoint.lane_id as a map lane index */
+  int8_t *rw_lane_index;       /* [E*A, Pc, Hz] */
 } SbObsPtrs;
 
 /* Initial / reset state for a set of envs (host pointers).  Replaces SMARTS.reset ->
@@ -331,7 +365,8 @@ int64_t sb_launch_count(SbHandle h);
 #define SB_K_TTC 7
 #define SB_K_EXTRAS 8   /* accelerometer + vias */
 #define SB_K_EGO_FRAME 9
-#define SB_K_COUNT 10
+#define SB_K_ROAD_WP 10  /* k_road_waypoints */
+#define SB_K_COUNT 11
 int sb_set_timing(SbHandle h, int on);
 int sb_collect_timing(SbHandle h, double *ms_sum /*[SB_K_COUNT]*/, int64_t *count /*[SB_K_COUNT]*/);
 const char *sb_last_error(SbHandle h);

@@ -1041,6 +1041,190 @@ void observe_vias(World& w, int e, int a) {
   w.via_hit_count[ai] = (int)hit_points.size();
 }
 
+// ---------------------------------------------------------------- RoadWaypointsSensor
+// nearest_lanes(point, radius) as the sorted list (sumo_road_network.py:675-701); equal distances by lane index
+std::vector<int> nearest_lanes_sorted(const Map& mp, double px, double py, double radius) {
+  std::vector<std::pair<double, int>> c;
+  for (int l = 0; l < mp.m.n_lanes; ++l) {
+    double d = dist_point_to_polyline(mp, l, px, py);
+    if (d < 0.0 || !(d < radius)) continue;
+    c.emplace_back(d, l);
+  }
+  std::sort(c.begin(), c.end());
+  std::vector<int> out;
+  for (auto& q : c) out.push_back(q.second);
+  return out;
+}
+
+// Lane.oncoming_lanes_at_offset, sumo_road_network.py:370-396
+std::vector<int> oncoming_lanes_at_offset(const Map& mp, int lane, double off) {
+  std::vector<int> result;
+  const double radius = 1.1 * mp.lane_width[lane];
+  double cx, cy, mvx, mvy;
+  from_lane_coord(mp, lane, off, &cx, &cy);
+  std::vector<int> nearby = nearest_lanes_sorted(mp, cx, cy, radius);
+  if (nearby.empty()) return result;
+  vector_at_offset(mp, lane, off, &mvx, &mvy);
+  const double my_norm = std::sqrt(mvx * mvx + mvy * mvy);
+  if (my_norm == 0.0) return result;
+  for (int l : nearby) {
+    if (l == lane) continue;
+    double sl = offset_along_lane(mp, l, cx, cy), lvx, lvy;
+    vector_at_offset(mp, l, sl, &lvx, &lvy);
+    const double lv_norm = std::sqrt(lvx * lvx + lvy * lvy);
+    if (lv_norm == 0.0) continue;
+    const double ang = (mvx * lvx + mvy * lvy) / (my_norm * lv_norm);
+    if (ang < -0.995562) result.push_back(l);
+  }
+  return result;
+}
+
+// `cache_*`: SumoRoadNetwork._WaypointsCache (sumo_road_network.py:1229-1276) as it acts inside one sensor call.  The
+// reference keeps the paths of the last query point keyed by the start lane's INDEX IN ITS ROAD, so two lanes of
+// different roads that have the same index and start the query from exactly the same point (internal lanes fanning
+// out of one approach lane) share an entry: the second one is answered with the first one's paths -- which are
+// lane_paths_at(first lane, point), so only the lane that filled an entry needs remembering.  The cache is taken
+// as empty when the call begins (what other vehicles left in it is not modelled).
+struct RwOut {
+  World& w;
+  int ai, n_paths = 0;
+  bool truncated = false;
+  bool cache_valid = false;
+  double cache_x = 0.0, cache_y = 0.0;
+  std::vector<std::array<int, 2>> cache_starts;  // lane index in road, lane that filled the entry
+};
+
+// RoadWaypointsSensor.paths_for_lane, sensors.py:1013-1040.  Every visit moves the cache; only a lane's last visit
+// is what the dict keeps (`emit`), written as the paths of lane slot `slot`.
+void rw_paths_for_lane(RwOut& o, int slot, bool emit, int lane, double px, double py, bool have_overflow,
+                       double overflow, int depth) {
+  World& w = o.w;
+  const Map& mp = w.map;
+  const int horizon = w.cfg.rw_horizon;
+  double start;
+  if (!have_overflow) {
+    start = offset_along_lane(mp, lane, px, py) - (double)horizon;
+  } else {
+    start = mp.lane_length[lane] + overflow;
+  }
+  const int i0 = mp.lane_in_start[lane], i1 = mp.lane_in_start[lane + 1];
+  if (start < 0 && i1 > i0) {
+    if (depth + 1 >= SB_RW_MAX_DEPTH) {
+      o.truncated = true;
+      return;
+    }
+    for (int i = i0; i < i1; ++i) rw_paths_for_lane(o, slot, emit, mp.lane_in[i], px, py, true, start, depth + 1);
+    return;
+  }
+  start = std::max(0.0, start);
+  double sx, sy;
+  from_lane_coord(mp, lane, start, &sx, &sy);
+  if (mp.lane_lp_count[lane] <= 0) return;
+  const int key = mp.lane_idx_in_road[lane];  // llp.lp.lane.index of the closest lane point ON this lane
+  int source = lane;
+  bool hit = false;
+  if (o.cache_valid && sx == o.cache_x && sy == o.cache_y) {
+    for (auto& c : o.cache_starts)
+      if (c[0] == key) {
+        source = c[1];
+        hit = true;
+      }
+  } else {
+    o.cache_valid = true;
+    o.cache_x = sx;
+    o.cache_y = sy;
+    o.cache_starts.clear();
+  }
+  if (!hit) o.cache_starts.push_back({key, lane});
+  if (!emit) return;
+  static thread_local PathSet ps;
+  ps.n = ps.total = 0;
+  ps.overflow = false;
+  const int rl = w.route_len[o.ai];
+  lane_paths_at(mp, source, sx, sy, 2 * horizon, rl > 0 ? &w.route[(size_t)o.ai * w.cfg.route_cap] : nullptr,
+                rl > 0 ? rl : 0, &ps);
+  if (ps.overflow) o.truncated = true;
+  const int Pc = w.cfg.rw_paths_cap, Hz = 2 * horizon + 1;
+  for (int k = 0; k < ps.n; ++k) {
+    const int p = o.n_paths++;
+    if (p >= Pc) {
+      o.truncated = true;
+      continue;
+    }
+    const size_t q = (size_t)o.ai * Pc + p;
+    w.rw_path_slot[q] = slot;
+    w.rw_len[q] = ps.len[k];
+    for (int i = 0; i < ps.len[k] && i < Hz; ++i) {
+      const Waypoint& wp = ps.wp[k][i];
+      const size_t t = q * Hz + i;
+      w.rw_pos[t * 2] = wp.x;
+      w.rw_pos[t * 2 + 1] = wp.y;
+      w.rw_heading[t] = wp.heading;
+      w.rw_lane_width[t] = (float)wp.lane_width;
+      w.rw_speed_limit[t] = (float)wp.speed_limit;
+      w.rw_wp_lane[t] = wp.lane;
+      w.rw_lane_index[t] = (int8_t)wp.lane_index;
+    }
+  }
+}
+
+// RoadWaypointsSensor.__call__, sensors.py:1000-1011
+void observe_road_waypoints(World& w, int e, int a) {
+  const int ai = e * w.A + a, vi = e * w.V + a;
+  const Map& mp = w.map;
+  const int Lc = w.cfg.rw_lanes_cap, Pc = w.cfg.rw_paths_cap, Hz = 2 * w.cfg.rw_horizon + 1;
+  for (int i = 0; i < Lc; ++i) w.rw_lane[(size_t)ai * Lc + i] = -1;
+  for (int p = 0; p < Pc; ++p) {
+    const size_t q = (size_t)ai * Pc + p;
+    w.rw_path_slot[q] = -1;
+    w.rw_len[q] = 0;
+    for (int i = 0; i < Hz; ++i) {
+      const size_t t = q * Hz + i;
+      w.rw_pos[t * 2] = w.rw_pos[t * 2 + 1] = w.rw_heading[t] = 0.0;
+      w.rw_lane_width[t] = w.rw_speed_limit[t] = 0.f;
+      w.rw_wp_lane[t] = -1;
+      w.rw_lane_index[t] = 0;
+    }
+  }
+  w.rw_n_lanes[ai] = w.rw_n_paths[ai] = 0;
+  const double px = w.pos_x[vi], py = w.pos_y[vi];
+  const int nl = nearest_lane(mp, px, py, std::max(10.0, 2 * 3.2));
+  if (nl < 0) return;
+  const int road = mp.lane_road[nl];
+  std::vector<int> croads(1, road);
+  for (int i = mp.road_par_start[road]; i < mp.road_par_start[road + 1]; ++i) croads.push_back(mp.road_par[i]);
+  // Road.oncoming_roads_at_point, sumo_road_network.py:595-605
+  for (int l = mp.road_lane_start[road]; l < mp.road_lane_start[road] + mp.road_lane_count[road]; ++l) {
+    const double off = offset_along_lane(mp, l, px, py);  // lane.to_lane_coord(point).s
+    for (int ol : oncoming_lanes_at_offset(mp, l, off))
+      if (mp.lane_road[ol] != road) croads.push_back(mp.lane_road[ol]);
+  }
+  RwOut out{w, ai};
+  if ((int)croads.size() > SB_RW_MAX_ROADS) {
+    croads.resize(SB_RW_MAX_ROADS);
+    out.truncated = true;
+  }
+  // lane_paths[lane.lane_id] = paths_for_lane(lane) over every lane of every road of the list: a road listed twice
+  // has its lanes computed twice; the dict keeps the first position and the last value of a key
+  std::vector<int> visits, lanes;
+  for (int r : croads)
+    for (int l = mp.road_lane_start[r]; l < mp.road_lane_start[r] + mp.road_lane_count[r]; ++l) {
+      visits.push_back(l);
+      if (std::find(lanes.begin(), lanes.end(), l) == lanes.end()) lanes.push_back(l);
+    }
+  w.rw_n_lanes[ai] = (int)lanes.size();
+  if ((int)lanes.size() > Lc) out.truncated = true;
+  for (int s = 0; s < std::min((int)lanes.size(), Lc); ++s) w.rw_lane[(size_t)ai * Lc + s] = lanes[s];
+  for (size_t v = 0; v < visits.size(); ++v) {
+    const int l = visits[v];
+    const bool last = std::find(visits.begin() + v + 1, visits.end(), l) == visits.end();
+    const int slot = (int)(std::find(lanes.begin(), lanes.end(), l) - lanes.begin());
+    rw_paths_for_lane(out, slot, last && slot < Lc, l, px, py, false, 0.0, 0);
+  }
+  w.rw_n_paths[ai] = out.n_paths;
+  if (out.truncated) w.status[ai] |= SB_STATUS_RW_TRUNCATED;
+}
+
 // ego_centric_observation_adapter, smarts/core/utils/adapters/ego_centric_adapters.py:62-178, on the
 // observation arrays of one agent: neighbours (:160-167), lidar points (:113-123), waypoints (:85-96).
 // wrap_value: utils/math.py:452-461; position_to_ego_frame / _gen_ego_frame_matrix: utils/math.py:464-487.
@@ -1101,6 +1285,18 @@ void ego_frame_agent(World& w, int e, int a) {
         w.wp_heading[q] = (float)wrap_value((double)w.wp_heading[q] - heading, -SB_PI, SB_PI);
       }
   }
+  if (c.rw_enable) {  // :98-108
+    const int Pc = c.rw_paths_cap, Hz = 2 * c.rw_horizon + 1;
+    for (int p = 0; p < std::min(w.rw_n_paths[ai], Pc); ++p)
+      for (int i = 0; i < std::min(w.rw_len[(size_t)ai * Pc + p], Hz); ++i) {
+        const size_t q = ((size_t)ai * Pc + p) * Hz + i;
+        double v[3] = {w.rw_pos[q * 2], w.rw_pos[q * 2 + 1], 0.0};
+        position_to_ego_frame(v, position, heading);
+        w.rw_pos[q * 2] = v[0];
+        w.rw_pos[q * 2 + 1] = v[1];
+        w.rw_heading[q] = wrap_value(w.rw_heading[q] - heading, -SB_PI, SB_PI);
+      }
+  }
 }
 
 void observe_agent(World& w, int e, int a) {
@@ -1120,6 +1316,7 @@ void observe_agent(World& w, int e, int a) {
   if (w.cfg.ttc_enable) observe_ttc(w, e, a);
   if (w.cfg.accel_enable) observe_accelerometer(w, e, a);
   if (w.cfg.via_cap > 0) observe_vias(w, e, a);
+  if (w.cfg.rw_enable) observe_road_waypoints(w, e, a);
   if (w.cfg.lidar_enable) observe_lidar(w, e, a);
   if (w.cfg.ogm_enable) observe_ogm(w, e, a);
   if (w.cfg.dagm_enable) observe_dagm(w, e, a);
@@ -1164,6 +1361,10 @@ void* or_create(const SbConfig* cfg, const SbMap* m, const double* base_rays, in
   cp(mp.poly_x, m->poly_x, m->n_poly_verts);
   cp(mp.poly_y, m->poly_y, m->n_poly_verts);
   cp(mp.road_edges, m->road_edges, (size_t)m->n_edges * 4);
+  cp(mp.lane_in_start, m->lane_in_start, m->n_lanes + 1);
+  cp(mp.lane_in, m->lane_in, std::max(m->n_lane_in, 1));
+  cp(mp.road_par_start, m->road_par_start, m->n_roads + 1);
+  cp(mp.road_par, m->road_par, std::max(m->n_road_par, 1));
   if (base_rays && n_rays > 0) {
     w->rays.assign(base_rays, base_rays + (size_t)n_rays * 3);
     w->ray_rec.resize(n_rays);
@@ -1251,6 +1452,20 @@ void* or_create(const SbConfig* cfg, const SbMap* m, const double* base_rays, in
     w->via_hit_count.assign(na, 0);
     w->via_near_idx.assign(na * cfg->via_cap, -1);
     w->via_hit_idx.assign(na * cfg->via_cap, -1);
+  }
+  if (cfg->rw_enable) {
+    const size_t np = na * cfg->rw_paths_cap, n = np * (2 * cfg->rw_horizon + 1);
+    w->rw_n_lanes.assign(na, 0);
+    w->rw_n_paths.assign(na, 0);
+    w->rw_lane.assign(na * cfg->rw_lanes_cap, -1);
+    w->rw_path_slot.assign(np, -1);
+    w->rw_len.assign(np, 0);
+    w->rw_pos.assign(n * 2, 0.0);
+    w->rw_heading.assign(n, 0.0);
+    w->rw_lane_width.assign(n, 0.f);
+    w->rw_speed_limit.assign(n, 0.f);
+    w->rw_wp_lane.assign(n, -1);
+    w->rw_lane_index.assign(n, 0);
   }
   if (cfg->ogm_enable) w->ogm.assign(na * cfg->ogm_width * cfg->ogm_height, 0);
   if (cfg->dagm_enable) w->dagm.assign(na * cfg->dagm_width * cfg->dagm_height, 0);
@@ -1446,6 +1661,11 @@ void or_get_obs(void* h, SbObsPtrs* o) {
   o->acc_linear_jerk = w.acc_linear_jerk.data(); o->acc_angular_jerk = w.acc_angular_jerk.data();
   o->via_near_count = w.via_near_count.data(); o->via_near_idx = w.via_near_idx.data();
   o->via_hit_count = w.via_hit_count.data(); o->via_hit_idx = w.via_hit_idx.data();
+  o->rw_n_lanes = w.rw_n_lanes.data(); o->rw_lane = w.rw_lane.data(); o->rw_n_paths = w.rw_n_paths.data();
+  o->rw_path_slot = w.rw_path_slot.data(); o->rw_len = w.rw_len.data(); o->rw_pos = w.rw_pos.data();
+  o->rw_heading = w.rw_heading.data(); o->rw_lane_width = w.rw_lane_width.data();
+  o->rw_speed_limit = w.rw_speed_limit.data(); o->rw_wp_lane = w.rw_wp_lane.data();
+  o->rw_lane_index = w.rw_lane_index.data();
 }
 
 // ---- unit-level probes used to pin the oracle against the reference's golden vectors ----

@@ -82,6 +82,7 @@ struct Map {
   std::vector<int32_t> lp_lane, lp_next_start, lp_next;
   std::vector<double> shape_x, shape_y, poly_x, poly_y, road_edges;
   std::vector<int32_t> poly_start;
+  std::vector<int32_t> lane_in_start, lane_in, road_par_start, road_par;  // RoadWaypoints tables
 };
 
 template <class T>
@@ -133,6 +134,11 @@ struct World {
   std::vector<std::vector<ViaRec>> vias;
   std::vector<std::set<int>> via_consumed;
   std::vector<int32_t> via_near_count, via_near_idx, via_hit_count, via_hit_idx;
+  // RoadWaypointsSensor (sensors.py:991-1043)
+  std::vector<int32_t> rw_n_lanes, rw_lane, rw_n_paths, rw_path_slot, rw_len, rw_wp_lane;
+  std::vector<double> rw_pos, rw_heading;
+  std::vector<float> rw_lane_width, rw_speed_limit;
+  std::vector<int8_t> rw_lane_index;
   int ring = 1;
   bool stepped = false;
   int threads = 1;

@@ -6,7 +6,7 @@ from typing import Dict
 
 import numpy as np
 
-SB_ABI_VERSION = 5
+SB_ABI_VERSION = 6
 
 SB_ACTION_CONTINUOUS = 0
 SB_ACTION_LANE = 1
@@ -24,6 +24,7 @@ SB_STATUS_PATH_OVERFLOW = 1
 SB_STATUS_NO_WAYPOINTS = 2
 SB_STATUS_LIDAR_OVERFLOW = 4
 SB_STATUS_TTC_TRUNCATED = 8
+SB_STATUS_RW_TRUNCATED = 16
 
 SB_EV_COLLISION, SB_EV_OFF_ROAD, SB_EV_OFF_ROUTE, SB_EV_ON_SHOULDER = 1, 2, 4, 8
 SB_EV_WRONG_WAY, SB_EV_NOT_MOVING, SB_EV_REACHED_GOAL, SB_EV_REACHED_MAX_STEPS = 16, 32, 64, 128
@@ -49,6 +50,7 @@ class SbConfig(C.Structure):
         ("ttc_enable", _i32),
         ("accel_enable", _i32), ("via_cap", _i32), ("via_acquisition_range", _f64), ("via_speed_accuracy", _f64),
         ("ego_frame", _i32),
+        ("rw_enable", _i32), ("rw_horizon", _i32), ("rw_lanes_cap", _i32), ("rw_paths_cap", _i32),
     ]
 
 
@@ -63,6 +65,7 @@ _MAP_PTRS = [
     ("lp_next_start", _pi32), ("lp_next", _pi32),
     ("shape_x", _pf64), ("shape_y", _pf64),
     ("poly_start", _pi32), ("poly_x", _pf64), ("poly_y", _pf64), ("road_edges", _pf64),
+    ("lane_in_start", _pi32), ("lane_in", _pi32), ("road_par_start", _pi32), ("road_par", _pi32),
 ]
 
 
@@ -70,6 +73,7 @@ class SbMap(C.Structure):
     _fields_ = [
         ("n_roads", _i32), ("n_lanes", _i32), ("n_lanepoints", _i32), ("n_shape_pts", _i32),
         ("n_polys", _i32), ("n_poly_verts", _i32), ("n_edges", _i32), ("n_lane_out", _i32), ("n_lp_next", _i32),
+        ("n_lane_in", _i32), ("n_road_par", _i32),
         ("lanepoint_spacing", _f64),
     ] + _MAP_PTRS
 
@@ -97,6 +101,9 @@ class SbObsPtrs(C.Structure):
         ("ttc_valid", _pu8),
         ("acc_linear", _pf64), ("acc_angular", _pf64), ("acc_linear_jerk", _pf64), ("acc_angular_jerk", _pf64),
         ("via_near_count", _pi32), ("via_near_idx", _pi32), ("via_hit_count", _pi32), ("via_hit_idx", _pi32),
+        ("rw_n_lanes", _pi32), ("rw_lane", _pi32), ("rw_n_paths", _pi32), ("rw_path_slot", _pi32), ("rw_len", _pi32),
+        ("rw_pos", _pf64), ("rw_heading", _pf64), ("rw_lane_width", _pf32), ("rw_speed_limit", _pf32),
+        ("rw_wp_lane", _pi32), ("rw_lane_index", _pi8),
     ]
 
 
@@ -129,6 +136,8 @@ def make_map_struct(arrays: Dict[str, np.ndarray], spacing: float):
     m.n_edges = len(arrays["road_edges"])
     m.n_lane_out = int(arrays["lane_out_start"][-1])
     m.n_lp_next = int(arrays["lp_next_start"][-1])
+    m.n_lane_in = int(arrays["lane_in_start"][-1])
+    m.n_road_par = int(arrays["road_par_start"][-1])
     m.lanepoint_spacing = float(spacing)
     return m, keep
 
@@ -167,6 +176,13 @@ def obs_shapes(cfg: SbConfig) -> Dict[str, tuple]:
     if cfg.via_cap > 0:
         out.update(via_near_count=((), np.int32), via_near_idx=((cfg.via_cap,), np.int32),
                    via_hit_count=((), np.int32), via_hit_idx=((cfg.via_cap,), np.int32))
+    if cfg.rw_enable:
+        lc, pc, hz = cfg.rw_lanes_cap, cfg.rw_paths_cap, 2 * cfg.rw_horizon + 1
+        out.update(rw_n_lanes=((), np.int32), rw_lane=((lc,), np.int32), rw_n_paths=((), np.int32),
+                   rw_path_slot=((pc,), np.int32), rw_len=((pc,), np.int32), rw_pos=((pc, hz, 2), np.float64),
+                   rw_heading=((pc, hz), np.float64), rw_lane_width=((pc, hz), np.float32),
+                   rw_speed_limit=((pc, hz), np.float32), rw_wp_lane=((pc, hz), np.int32),
+                   rw_lane_index=((pc, hz), np.int8))
     return out
 
 

@@ -7,7 +7,7 @@ Mirrors (field names, defaults, presets; no code shared):
   /root/reference/smarts/zoo/agent_spec.py:36-119, smarts/core/agent.py:31-58   AgentSpec, Agent
 
 ``compile_config`` turns one AgentInterface into the ``SbConfig`` the C-ABI takes
-(include/smarts_b200.h); sensors the hot path does not cover (RGB camera, RoadWaypoints, the
+(include/smarts_b200.h); sensors the hot path does not cover (RGB camera, the
 MPC / TrajectoryWithTime / MultiTargetPose / Imitation action spaces) raise ``NotImplementedError``
 instead of being silently dropped.
 """
@@ -224,7 +224,8 @@ class AgentInterface:
 def compile_config(itf: AgentInterface, n_envs: int, n_agents: int, n_social: int, dt: float, *, device: int = 0,
                    route_cap: int = 16, traj_len: int = 10, nbr_cap: int = 10, wp_out_paths: int = 4,
                    wp_out_len: Optional[int] = None, lidar_wall_height: float = 0.0, lidar_miss_inf: int = 1,
-                   events: bool = True, via_cap: int = 0) -> _abi.SbConfig:
+                   events: bool = True, via_cap: int = 0, rw_lanes_cap: int = 32,
+                   rw_paths_cap: int = 64) -> _abi.SbConfig:
     """AgentInterface (+ HiWayEnv kwargs) -> SbConfig.  ``wp_out_len`` None keeps the sensor's full
     lookahead (what ``Observation.waypoint_paths`` holds); StdObs uses 4 x 20 (format_obs.py:41)."""
     if itf.action is None:
@@ -234,8 +235,6 @@ def compile_config(itf: AgentInterface, n_envs: int, n_agents: int, n_social: in
                                   f"(supported: {[a.name for a in _SUPPORTED_ACTIONS]})")
     if itf.rgb:
         raise NotImplementedError("RGB camera needs the Panda3D renderer: unavailable on this box (DESIGN.md 9)")
-    if itf.road_waypoints:
-        raise NotImplementedError("RoadWaypoints sensor is outside the B200 hot path (SURVEY.md 8)")
     if itf.vehicle_type != "sedan":
         raise NotImplementedError("only the sedan chassis parameters are built in")
     c = _abi.SbConfig()
@@ -270,6 +269,11 @@ def compile_config(itf: AgentInterface, n_envs: int, n_agents: int, n_social: in
         c.ttc_enable = 1
     if itf.accelerometer:
         c.accel_enable = 1
+    if itf.road_waypoints:  # sensors.py:991-1043; a path holds 2 * horizon + 1 waypoints
+        hz = int(itf.road_waypoints.horizon)
+        if not 1 <= hz <= _abi.SB_MAX_LOOKAHEAD // 2:
+            raise ValueError(f"RoadWaypoints.horizon {hz} outside 1 .. {_abi.SB_MAX_LOOKAHEAD // 2}")
+        c.rw_enable, c.rw_horizon, c.rw_lanes_cap, c.rw_paths_cap = 1, hz, int(rw_lanes_cap), int(rw_paths_cap)
     if via_cap > 0:  # ViaSensor is always attached (vehicle.py:552-558); it only does work for missions with vias
         c.via_cap, c.via_acquisition_range, c.via_speed_accuracy = int(via_cap), 40.0, 1.5
     if events:

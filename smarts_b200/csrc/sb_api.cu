@@ -34,6 +34,7 @@ struct SbHandle_ {
   DEvOut evo{};
   DTtcOut ttc{};
   DExtras ex{};
+  DRoadWp rw{};
   int32_t* d_veh_lane = nullptr;  // k_vehicle_lanes -> k_observe (only when V <= A * nbr_cap)
   int32_t *h_env_list = nullptr, *d_env_list = nullptr;  // sb_observe_envs: pinned staging + device copy of the env list
   cudaStream_t env_list_stream = nullptr;
@@ -287,6 +288,7 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
   d.accel_enable = c.accel_enable; d.via_cap = c.via_cap; d.via_range = c.via_acquisition_range;
   d.via_speed_acc = c.via_speed_accuracy;
   d.ego_frame = c.ego_frame;
+  d.rw_enable = c.rw_enable; d.rw_horizon = c.rw_horizon; d.rw_lanes_cap = c.rw_lanes_cap; d.rw_paths_cap = c.rw_paths_cap;
   d.env_list = nullptr;
   d.n_list = 0;
   d.a_magic = ((uint64_t)c.n_envs * c.n_agents * c.n_agents < (1ull << 32)) ? (uint32_t)((1ull << 32) / c.n_agents) + 1u : 0u;
@@ -294,6 +296,9 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
   if (c.via_cap > 0 && !(c.via_acquisition_range >= 0 && c.via_speed_accuracy >= 0))
     return fail(h, SB_EINVAL, "via range / speed accuracy must be >= 0");
   if (c.ttc_enable && !(c.nbr_enable && c.wp_enable)) return fail(h, SB_EINVAL, "ttc needs the neighbour and waypoint sensors");
+  if (c.rw_enable && !(c.rw_horizon >= 1 && 2 * c.rw_horizon <= SB_MAX_LOOKAHEAD))
+    return fail(h, SB_EINVAL, "rw_horizon must be in 1 .. SB_MAX_LOOKAHEAD / 2");
+  if (c.rw_enable && !(c.rw_lanes_cap >= 1 && c.rw_paths_cap >= 1)) return fail(h, SB_EINVAL, "rw_lanes_cap / rw_paths_cap must be >= 1");
   if (c.events_enable && !(c.not_moving_time >= 0)) return fail(h, SB_EINVAL, "not_moving_time must be >= 0");
 
   const size_t nv = (size_t)d.E * d.V, na = (size_t)d.E * d.A;
@@ -369,6 +374,15 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
           dev_alloc(h, &q.via_y, nc) && dev_alloc(h, &q.via_hit, nc) && dev_alloc(h, &q.via_speed, nc) &&
           dev_alloc(h, &q.via_consumed, na) && dev_alloc(h, &q.near_count, na) && dev_alloc(h, &q.near_idx, nc) &&
           dev_alloc(h, &q.hit_count, na) && dev_alloc(h, &q.hit_idx, nc)))
+      return SB_ENOMEM;
+  }
+  if (c.rw_enable) {
+    DRoadWp& q = h->rw;
+    const size_t np = na * c.rw_paths_cap, n = np * (2 * c.rw_horizon + 1);
+    if (!(dev_alloc(h, &q.n_lanes, na) && dev_alloc(h, &q.lane, na * c.rw_lanes_cap) && dev_alloc(h, &q.n_paths, na) &&
+          dev_alloc(h, &q.path_slot, np) && dev_alloc(h, &q.len, np) && dev_alloc(h, &q.pos, n * 2) &&
+          dev_alloc(h, &q.heading, n) && dev_alloc(h, &q.lane_width, n) && dev_alloc(h, &q.speed_limit, n) &&
+          dev_alloc(h, &q.wp_lane, n) && dev_alloc(h, &q.lane_index, n)))
       return SB_ENOMEM;
   }
   if (c.nbr_enable && d.V <= d.A * d.nbr_cap && !dev_alloc(h, &h->d_veh_lane, nv)) return SB_ENOMEM;
@@ -541,7 +555,11 @@ int sb_upload_map(SbHandle h, const SbMap* mp) {
             dev_upload(h, &m.poly_x, mp->poly_x, (size_t)mp->n_poly_verts) &&
             dev_upload(h, &m.poly_y, mp->poly_y, (size_t)mp->n_poly_verts) &&
             dev_upload(h, &m.poly_bbox, bbox.data(), bbox.size()) &&
-            dev_upload(h, &m.road_edges, mp->road_edges, (size_t)mp->n_edges * 4);
+            dev_upload(h, &m.road_edges, mp->road_edges, (size_t)mp->n_edges * 4) &&
+            dev_upload(h, &m.lane_in_start, mp->lane_in_start, L + 1) &&
+            dev_upload(h, &m.lane_in, mp->lane_in, (size_t)(mp->n_lane_in > 0 ? mp->n_lane_in : 1)) &&
+            dev_upload(h, &m.road_par_start, mp->road_par_start, R + 1) &&
+            dev_upload(h, &m.road_par, mp->road_par, (size_t)(mp->n_road_par > 0 ? mp->n_road_par : 1));
   if (!ok) return SB_ECUDA;
   {  // bounding box of every road's lane points: lower bound for the "closest lane point per route road" search
     std::vector<double> rb((size_t)mp->n_roads * 4);
@@ -886,6 +904,10 @@ int sb_observe_envs(SbHandle h, const int32_t* env_ids, int32_t n, void* stream)
     LaunchScope ls(h, SB_K_EXTRAS, st);
     k_extras<<<(na + 127) / 128, 128, 0, st>>>(c, h->dmap, h->st, h->ex);
   }
+  if (c.rw_enable) {
+    LaunchScope ls(h, SB_K_ROAD_WP, st);
+    k_road_waypoints<<<(na + SB_RW_WARPS - 1) / SB_RW_WARPS, SB_RW_WARPS * 32, 0, st>>>(c, h->dmap, h->st, h->rw);
+  }
   if (c.lidar_enable) {
     LaunchScope ls(h, SB_K_LIDAR, st);
     k_lidar<<<na, SB_LIDAR_THREADS, 0, st>>>(c, h->dmap, h->st, h->ob, h->ray_table, h->ray_reach);
@@ -909,9 +931,9 @@ int sb_observe_envs(SbHandle h, const int32_t* env_ids, int32_t n, void* stream)
                                                                               h->stepped ? 1 : 0);
     h->stepped = false;
   }
-  if (c.ego_frame && (c.lidar_enable || c.nbr_enable || c.wp_enable)) {  // last: k_ttc / k_events read world-frame buffers
+  if (c.ego_frame && (c.lidar_enable || c.nbr_enable || c.wp_enable || c.rw_enable)) {  // last: k_ttc / k_events read world-frame buffers
     LaunchScope ls(h, SB_K_EGO_FRAME, st);
-    k_ego_frame<<<na, SB_EGO_THREADS, 0, st>>>(c, h->st, h->ob);
+    k_ego_frame<<<na, SB_EGO_THREADS, 0, st>>>(c, h->st, h->ob, h->rw);
   }
   return cuda_ok(h, cudaGetLastError(), "k_observe") ? SB_OK : SB_ECUDA;
 }
@@ -1098,6 +1120,15 @@ static int copy_obs_to_host(SbHandle h, const SbObsPtrs* dst, bool packed_dst) {
     cpy(dst->via_near_count, q.near_count, na * 4); cpy(dst->via_near_idx, q.near_idx, na * 4 * c.via_cap);
     cpy(dst->via_hit_count, q.hit_count, na * 4); cpy(dst->via_hit_idx, q.hit_idx, na * 4 * c.via_cap);
   }
+  if (c.rw_enable) {
+    const DRoadWp& q = h->rw;
+    const size_t np = na * c.rw_paths_cap, n = np * (2 * c.rw_horizon + 1);
+    cpy(dst->rw_n_lanes, q.n_lanes, na * 4); cpy(dst->rw_lane, q.lane, na * c.rw_lanes_cap * 4);
+    cpy(dst->rw_n_paths, q.n_paths, na * 4); cpy(dst->rw_path_slot, q.path_slot, np * 4); cpy(dst->rw_len, q.len, np * 4);
+    cpy(dst->rw_pos, q.pos, n * 16); cpy(dst->rw_heading, q.heading, n * 8); cpy(dst->rw_lane_width, q.lane_width, n * 4);
+    cpy(dst->rw_speed_limit, q.speed_limit, n * 4); cpy(dst->rw_wp_lane, q.wp_lane, n * 4);
+    cpy(dst->rw_lane_index, q.lane_index, n);
+  }
   if (c.ttc_enable) {
     const DTtcOut& q = h->ttc;
     cpy(dst->ttc_angle_error, q.angle_error, na * 4); cpy(dst->ttc_distance_from_center, q.dist_center, na * 4);
@@ -1200,6 +1231,10 @@ int sb_get_obs(SbHandle h, SbObsPtrs* out) {
   out->acc_linear_jerk = h->ex.jerk_lin; out->acc_angular_jerk = h->ex.jerk_ang;
   out->via_near_count = h->ex.near_count; out->via_near_idx = h->ex.near_idx;
   out->via_hit_count = h->ex.hit_count; out->via_hit_idx = h->ex.hit_idx;
+  out->rw_n_lanes = h->rw.n_lanes; out->rw_lane = h->rw.lane; out->rw_n_paths = h->rw.n_paths;
+  out->rw_path_slot = h->rw.path_slot; out->rw_len = h->rw.len; out->rw_pos = h->rw.pos; out->rw_heading = h->rw.heading;
+  out->rw_lane_width = h->rw.lane_width; out->rw_speed_limit = h->rw.speed_limit; out->rw_wp_lane = h->rw.wp_lane;
+  out->rw_lane_index = h->rw.lane_index;
   return SB_OK;
 }
 

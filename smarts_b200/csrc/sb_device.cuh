@@ -46,6 +46,7 @@ struct DMap {
   int32_t seg_nx, seg_ny;
   const int32_t *seg_cell_start, *seg_items;
   const double* road_lp_bbox;  // [n_roads,4] xmin, ymin, xmax, ymax of the road's lane points
+  const int32_t *lane_in_start, *lane_in, *road_par_start, *road_par;  // RoadWaypoints tables (SbMap)
 };
 
 struct DState {

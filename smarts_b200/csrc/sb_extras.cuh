@@ -171,7 +171,7 @@ __device__ __forceinline__ void d_to_ego_frame(double* p, double ex, double ey, 
   p[2] = rz;
 }
 
-__global__ void __launch_bounds__(SB_EGO_THREADS) k_ego_frame(DCfg c, DState s, DObs o) {
+__global__ void __launch_bounds__(SB_EGO_THREADS) k_ego_frame(DCfg c, DState s, DObs o, DRoadWp rw) {
   int e, a;
   if (!d_work_agent(c, blockIdx.x, &e, &a)) return;
   const int ai = e * c.A + a, vi = e * c.V + a;
@@ -207,6 +207,20 @@ __global__ void __launch_bounds__(SB_EGO_THREADS) k_ego_frame(DCfg c, DState s, 
       o.wp_pos[q * 3 + 0] = v[0];
       o.wp_pos[q * 3 + 1] = v[1];
       o.wp_heading[q] = (float)d_wrap_value_pi((double)o.wp_heading[q] - eh);
+    }
+  }
+  if (c.rw_enable) {  // ego_centric_adapters.py:98-108
+    const int Pc = c.rw_paths_cap, Hz = 2 * c.rw_horizon + 1;
+    const int tp = rw.n_paths[ai], np_ = tp < Pc ? tp : Pc;
+    for (int t = threadIdx.x; t < np_ * Hz; t += SB_EGO_THREADS) {
+      const int p = t / Hz, i = t - p * Hz;
+      if (i >= rw.len[(size_t)ai * Pc + p]) continue;
+      const size_t q = ((size_t)ai * Pc + p) * Hz + i;
+      double v[3] = {rw.pos[q * 2 + 0], rw.pos[q * 2 + 1], 0.0};
+      d_to_ego_frame(v, ex, ey, ez, cs, sn);
+      rw.pos[q * 2 + 0] = v[0];
+      rw.pos[q * 2 + 1] = v[1];
+      rw.heading[q] = d_wrap_value_pi(rw.heading[q] - eh);
     }
   }
 }

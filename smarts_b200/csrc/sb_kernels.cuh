@@ -10,6 +10,7 @@
 //   k_events          Events / done / trip-meter reward / contacts         (warp per agent, sb_events.cuh)
 //   k_ttc             lane_ttc (StdObs ttc)                                (warp per agent, sb_ttc.cuh)
 //   k_extras          accelerometer + via sensor                            (thread per agent, sb_extras.cuh)
+//   k_road_waypoints  RoadWaypoints sensor                                 (warp per agent, sb_roadwp.cuh)
 #pragma once
 
 #include "sb_control.cuh"
@@ -46,6 +47,7 @@ struct DCfg {
   int32_t dagm_enable, dagm_w, dagm_h;
   double dagm_res;
   int32_t events_enable, max_steps, ttc_enable, accel_enable, via_cap, ego_frame;
+  int32_t rw_enable, rw_horizon, rw_lanes_cap, rw_paths_cap;
   uint32_t done_mask;
   double nm_time, nm_dist, via_range, via_speed_acc;
   // sb_observe_envs: the envs the observation kernels work on (device array; nullptr = every env, in order)
@@ -469,6 +471,7 @@ k_observe(DCfg c, DMap m, DState s, DObs o, double* __restrict__ trip_wp, const 
 
 // --------------------------------------------------------------------------------- events
 #include "sb_events.cuh"
+#include "sb_roadwp.cuh"
 #include "sb_ttc.cuh"
 #include "sb_extras.cuh"
 

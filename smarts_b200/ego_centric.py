@@ -65,7 +65,7 @@ def _replace(obj: Any, **kwargs):
 
 
 def ego_centric_observation_adapter(obs: Observation, *args: Any, **kwargs: Any) -> Observation:
-    """ego_centric_adapters.py:62-178.  Members this framework never fills (top_down_rgb, road_waypoints) pass
+    """ego_centric_adapters.py:62-178.  Members this framework never fills (top_down_rgb) pass
     through as ``None``; the reference would raise on a missing camera, this mirror skips it.  The ego's
     ``mission`` is passed through unchanged: this framework's ``Mission`` record holds road / lane / offset,
     not world poses, so there is nothing to rotate (the reference rotates mission.start / via / goal)."""
@@ -121,6 +121,8 @@ def ego_centric_observation_adapter(obs: Observation, *args: Any, **kwargs: Any)
         drivable_area_grid_map=replace_metadata(obs.drivable_area_grid_map),
         occupancy_grid_map=replace_metadata(obs.occupancy_grid_map),
         top_down_rgb=replace_metadata(obs.top_down_rgb),
+        road_waypoints=None if not obs.road_waypoints else _replace(
+            obs.road_waypoints, lanes={l_id: replace_wps(wps) for l_id, wps in obs.road_waypoints.lanes.items()}),
         via_data=vd,
     )
 

@@ -25,7 +25,7 @@ EXPORTS = [
     "sb_get_state", "sb_launch_count", "sb_last_error", "sb_set_timing", "sb_collect_timing",
     "sb_set_incremental_host_grids", "sb_copy_obs_to_host_packed",
 ]
-KERNEL_KINDS = ["k_set_social", "k_control", "k_observe", "k_lidar", "k_raster", "k_events", "k_pack_bits", "k_ttc", "k_extras", "k_ego_frame"]
+KERNEL_KINDS = ["k_set_social", "k_control", "k_observe", "k_lidar", "k_raster", "k_events", "k_pack_bits", "k_ttc", "k_extras", "k_ego_frame", "k_road_waypoints"]
 
 
 class SmartsB200Error(RuntimeError):

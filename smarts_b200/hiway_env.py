@@ -29,8 +29,8 @@ import numpy as np
 from . import _abi, lidar_params
 from .agent_interface import ActionSpaceType, AgentInterface, AgentSpec, compile_config
 from .observation import (Collision, Dimensions, DrivableAreaGridMap, EgoVehicleObservation, Events,
-                          GridMapMetadata, Mission, Observation, OccupancyGridMap, VehicleObservation, Via, ViaPoint, Vias,
-                          Waypoint)
+                          GridMapMetadata, Mission, Observation, OccupancyGridMap, RoadWaypoints, VehicleObservation, Via,
+                          ViaPoint, Vias, Waypoint)
 from .road_map import RoadMapData
 
 _MAPS_DIR = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "maps")
@@ -170,7 +170,7 @@ class BatchedHiWayEnv:
         self._aad = None                                  # [E] bool on the device: agents_alive criterion of the last tick
         self._host: Dict[str, np.ndarray] = {}
 
-    _MASKABLE = ("neighborhood_vehicles", "lidar", "ogm", "drivable_area_grid_map", "accelerometer")
+    _MASKABLE = ("neighborhood_vehicles", "lidar", "ogm", "drivable_area_grid_map", "accelerometer", "road_waypoints")
 
     @classmethod
     def _union_interface(cls, itfs: Sequence[AgentInterface]) -> AgentInterface:
@@ -551,6 +551,19 @@ class BatchedHiWayEnv:
                                      lane_width=float(o["wp_lane_width"][e, a, p, i]),
                                      speed_limit=float(o["wp_speed_limit"][e, a, p, i]),
                                      lane_index=int(o["wp_lane_index"][e, a, p, i])) for i in range(n)])
+        rwps = None
+        if itf.road_waypoints:  # sensors.py:1000-1011: {lane_id: [[Waypoint]]} in the sensor's insertion order
+            lanes = {rm.lane_ids[int(l)]: [] for l in o["rw_lane"][e, a, :min(int(o["rw_n_lanes"][e, a]), self.cfg.rw_lanes_cap)]}
+            keys = list(lanes)
+            for p in range(min(int(o["rw_n_paths"][e, a]), self.cfg.rw_paths_cap)):
+                n = int(o["rw_len"][e, a, p])
+                lanes[keys[int(o["rw_path_slot"][e, a, p])]].append(
+                    [Waypoint(pos=o["rw_pos"][e, a, p, i].copy(), heading=float(o["rw_heading"][e, a, p, i]),
+                              lane_id=rm.lane_ids[int(o["rw_wp_lane"][e, a, p, i])],
+                              lane_width=float(o["rw_lane_width"][e, a, p, i]),
+                              speed_limit=float(o["rw_speed_limit"][e, a, p, i]),
+                              lane_index=int(o["rw_lane_index"][e, a, p, i])) for i in range(n)])
+            rwps = RoadWaypoints(lanes=lanes)
         lidar = None
         if itf.lidar:  # (points, hits, [(origin, end)]) as lidar.py:115-134
             origin = np.array([px, py, pz + 1.0])
@@ -584,7 +597,7 @@ class BatchedHiWayEnv:
                            # reference's Observation holds the increment; the total is infos["score"] (agent_manager.py:234)
                            distance_travelled=float(o["ev_reward"][e, a]),
                            lidar_point_cloud=lidar, drivable_area_grid_map=dagm, occupancy_grid_map=ogm,
-                           top_down_rgb=None, road_waypoints=None, via_data=self._vias(e, a))
+                           top_down_rgb=None, road_waypoints=rwps, via_data=self._vias(e, a))
 
     def _vias(self, e: int, a: int) -> Vias:
         """Observation.via_data (sensors.py:337-347) from the kernel's index lists."""

@@ -107,6 +107,11 @@ class Vias(NamedTuple):
     hit_via_points: List
 
 
+class RoadWaypoints(NamedTuple):
+    """sensors.py:104-107: lane id -> waypoint paths along that lane."""
+    lanes: dict
+
+
 @dataclass
 class Observation:
     dt: float
@@ -121,7 +126,7 @@ class Observation:
     drivable_area_grid_map: Optional[DrivableAreaGridMap]
     occupancy_grid_map: Optional[OccupancyGridMap]
     top_down_rgb: Optional[Any]
-    road_waypoints: Optional[Any]
+    road_waypoints: Optional[RoadWaypoints]
     via_data: Vias
 
 

@@ -63,6 +63,7 @@ class RoadMapData:
     (``sb_upload_map``) and, unchanged, to the CPU oracle."""
 
     _SAVE_KEYS = ["road_length", "conn_from", "conn_to", "conn_via"]
+    _RW_KEYS = ["lane_in_start", "lane_in", "road_par_start", "road_par"]  # RoadWaypoints tables (ABI 6)
 
     def __init__(self, net: Optional[SumoNet], lanepoint_spacing: float = 1.0):
         self.net = net
@@ -107,6 +108,19 @@ class RoadMapData:
         self._road_ids = [str(s) for s in z["road_ids"]]
         self.lane_index = {s: i for i, s in enumerate(self._lane_ids)}
         self.road_index = {s: i for i, s in enumerate(self._road_ids)}
+        if not hasattr(self, "lane_in_start"):
+            # a map saved before the RoadWaypoints tables existed: incoming lanes follow from the connection table
+            # (from-lanes of the connections that end on the lane, file order); parallel roads need the node ids of
+            # the net.xml, which such a file does not hold -- none are listed
+            nl = len(self._lane_ids)
+            inc = [[] for _ in range(nl)]
+            for f, t in zip(self.conn_from, self.conn_to):
+                inc[int(t)].append(int(f))
+            self.lane_in_start = np.asarray(np.cumsum([0] + [len(v) for v in inc]), np.int32)
+            flat = [f for v in inc for f in v]
+            self.lane_in = np.asarray(flat if flat else [0], np.int32)
+            self.road_par_start = np.zeros(len(self._road_ids) + 1, np.int32)
+            self.road_par = np.zeros(1, np.int32)
         return self
 
     # ------------------------------------------------------------------ tables
@@ -144,6 +158,22 @@ class RoadMapData:
         self.lane_out_start = np.asarray(out_start, np.int32)
         self.lane_out = np.asarray(out_flat if out_flat else [0], np.int32)
         assert nl == len(self.lane_width)
+        # incoming lanes (Lane.incoming_lanes, sumo_road_network.py:342-348: sumolib Lane.getIncoming()) and
+        # parallel roads (Road.parallel_roads, :607-618: other edges between the same two nodes) -- RoadWaypoints
+        in_start, in_flat = [0], []
+        for l in self.lanes:
+            in_flat.extend(self.lane_index[i.getID()] for i in l.getIncoming())
+            in_start.append(len(in_flat))
+        self.lane_in_start = np.asarray(in_start, np.int32)
+        self.lane_in = np.asarray(in_flat if in_flat else [0], np.int32)
+        par_start, par_flat = [0], []
+        for e in self.roads:
+            to_id = e.getToNode().getID()
+            par_flat.extend(self.road_index[o.getID()] for o in e.getFromNode().getOutgoing()
+                            if o.getID() != e.getID() and o.getToNode().getID() == to_id)
+            par_start.append(len(par_flat))
+        self.road_par_start = np.asarray(par_start, np.int32)
+        self.road_par = np.asarray(par_flat if par_flat else [0], np.int32)
         # <connection> table in file order (from lane, to lane, via lane or -1): all the routing
         # code needs, so a map saved with ``save()`` can route without the net.xml.
         cf, ct, cv = [], [], []
@@ -500,6 +530,7 @@ class RoadMapData:
             "lane_out_start", "lane_out", "lane_lp_start", "lane_lp_count", "lane_shape_start",
             "lp_x", "lp_y", "lp_heading", "lp_inferred", "lp_lane", "lp_next_start", "lp_next",
             "shape_x", "shape_y", "poly_x", "poly_y", "poly_start", "road_edges",
+            "lane_in_start", "lane_in", "road_par_start", "road_par",
         ]
         return {k: np.ascontiguousarray(getattr(self, k)) for k in keys}
 

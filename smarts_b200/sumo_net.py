@@ -111,6 +111,8 @@ class NetEdge:
     # insertion-ordered like sumolib's dict: to-edge -> [Connection]
     outgoing: Dict["NetEdge", List[Connection]] = field(default_factory=dict)
     incoming: Dict["NetEdge", List[Connection]] = field(default_factory=dict)
+    from_node_obj: "NetNode" = None
+    to_node_obj: "NetNode" = None
 
     def getID(self):
         return self.edge_id
@@ -140,6 +142,12 @@ class NetEdge:
     def getConnections(self, to_edge):
         return self.outgoing.get(to_edge, [])
 
+    def getFromNode(self):
+        return self.from_node_obj
+
+    def getToNode(self):
+        return self.to_node_obj
+
 
 @dataclass(eq=False)
 class NetNode:
@@ -147,9 +155,17 @@ class NetNode:
     node_type: str
     coord: Tuple[float, float]
     shape: List[Tuple[float, float]]
+    outgoing: List[NetEdge] = field(default_factory=list)  # edges leaving / entering, in edge file order
+    incoming: List[NetEdge] = field(default_factory=list)
 
     def getID(self):
         return self.node_id
+
+    def getOutgoing(self):
+        return self.outgoing
+
+    def getIncoming(self):
+        return self.incoming
 
     def getType(self):
         return self.node_type
@@ -222,6 +238,21 @@ class SumoNet:
             tl.incoming_lanes.append(fl)
             fe.outgoing.setdefault(te, []).append(c)
             te.incoming.setdefault(fe, []).append(c)
+
+        # Edge.getFromNode / getToNode and Node.getOutgoing / getIncoming (Road.parallel_roads,
+        # sumo_road_network.py:607-618).  sumolib's reader gives an internal edge ":<junction>_<k>" the junction
+        # itself as both end nodes, and links every edge to its nodes as it is added (file order).
+        node_by_id = {n.node_id: n for n in self.nodes}
+        for e in self.edges:
+            f_id, t_id = e.from_node, e.to_node
+            if e.function in ("internal", "crossing", "walkingarea"):
+                f_id = t_id = e.edge_id[1:e.edge_id.rfind("_")]
+            for attr, nid, lst in (("from_node_obj", f_id, "outgoing"), ("to_node_obj", t_id, "incoming")):
+                n = node_by_id.get(nid)
+                if n is None:  # sumolib's addNode creates a bare node for an id the file never declares
+                    n = node_by_id[nid] = NetNode(nid, "", (0.0, 0.0), [])
+                setattr(e, attr, n)
+                getattr(n, lst).append(e)
 
     # -- sumolib.net.Net surface ---------------------------------------------------------
     def getEdges(self, withInternal: bool = True) -> List[NetEdge]:
