@@ -46,6 +46,7 @@ struct SbHandle_ {
   float ray_reach = 0.f;
   std::vector<void*> allocs;
   CtrlPick* d_picks = nullptr;  // k_control_paths -> k_control_law
+  double* d_edge_inv = nullptr;  // LTable::edge_inv (rebuilt when the map or the ray table changes)
   void* d_actions = nullptr;  // staging for sb_step_host
   size_t actions_cap = 0;
   double* d_social = nullptr;
@@ -438,6 +439,10 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
                  "cudaFuncSetAttribute"))
       return SB_ECUDA;
   }
+  if (c.lidar_enable &&
+      !cuda_ok(h, cudaFuncSetAttribute((const void*)k_lidar_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)sizeof(LidarShared)), "cudaFuncSetAttribute(k_lidar_tiles)"))
+    return SB_ECUDA;
   if (!cuda_ok(h, cudaDeviceSynchronize(), "sb_create sync")) return SB_ECUDA;
   return SB_OK;
 }
@@ -454,8 +459,11 @@ void sb_destroy(SbHandle h) {
   std::free(h->h_prev);
   for (auto e : h->xfer_ev) cudaEventDestroy(e);
   for (auto e : h->ev_pool) cudaEventDestroy(e);
+  if (h->d_edge_inv) cudaFree(h->d_edge_inv);
   delete h;
 }
+
+static bool build_lidar_edge_inv(SbHandle h);
 
 int sb_upload_map(SbHandle h, const SbMap* mp) {
   if (!h || !mp) return SB_EINVAL;
@@ -469,6 +477,7 @@ int sb_upload_map(SbHandle h, const SbMap* mp) {
     h->dmap = DMap{};
     h->have_map = false;
     h->stale_agents = true;
+    build_lidar_edge_inv(h);  // (no map: drops the table built on the old one)
   }
   const size_t alloc_mark = h->allocs.size();
   struct Claim {  // whatever this call allocated belongs to the map, also when it fails half-way
@@ -661,7 +670,26 @@ int sb_upload_map(SbHandle h, const SbMap* mp) {
   }
   h->raster_dims.n_src = h->raster_dims.n_veh + (h->cfg.dagm_enable ? mp->n_polys : 0);
   h->have_map = true;
+  if (!build_lidar_edge_inv(h)) return SB_ECUDA;
   return SB_OK;
+}
+
+// LTable::edge_inv: needs the map's road edges and the ray table's groups, whichever arrives second builds it
+static bool build_lidar_edge_inv(SbHandle h) {
+  if (h->d_edge_inv) {
+    cudaFree(h->d_edge_inv);
+    h->d_edge_inv = nullptr;
+  }
+  h->ray_table.edge_inv = nullptr;
+  if (!(h->have_map && h->have_rays && h->cfg.lidar_enable && h->cfg.lidar_wall_height > 0.0)) return true;
+  const int n = h->ray_table.n_groups * h->dmap.n_edges;
+  if (n <= 0) return true;
+  if (!cuda_ok(h, cudaMalloc(&h->d_edge_inv, (size_t)n * sizeof(double)), "cudaMalloc(edge_inv)")) return false;
+  k_lidar_edge_inv<<<(n + 255) / 256, 256>>>(h->dmap.road_edges, h->dmap.n_edges, h->ray_table.group_u,
+                                             h->ray_table.n_groups, h->d_edge_inv);
+  if (!cuda_ok(h, cudaDeviceSynchronize(), "k_lidar_edge_inv")) return false;
+  h->ray_table.edge_inv = h->d_edge_inv;
+  return true;
 }
 
 int sb_upload_lidar_rays(SbHandle h, const double* base_rays, int32_t n_rays) {
@@ -702,6 +730,7 @@ int sb_upload_lidar_rays(SbHandle h, const double* base_rays, int32_t n_rays) {
   h->ray_table.n_groups = n_groups;
   h->ray_table.max_hlen = reach;
   h->have_rays = true;
+  if (!build_lidar_edge_inv(h)) return SB_ECUDA;
   return SB_OK;
 }
 
@@ -910,7 +939,15 @@ int sb_observe_envs(SbHandle h, const int32_t* env_ids, int32_t n, void* stream)
   }
   if (c.lidar_enable) {
     LaunchScope ls(h, SB_K_LIDAR, st);
-    k_lidar<<<na, SB_LIDAR_THREADS, 0, st>>>(c, h->dmap, h->st, h->ob, h->ray_table, h->ray_reach);
+    const int G = h->ray_table.n_groups;
+    if (c.A >= 2 && c.V <= SB_LIDAR_MAX_BOXES && G <= SB_LIDAR_MAX_GROUPS && G * c.V <= SB_LIDAR_RECIP) {
+      // several agents of an env per block: vehicles staged and (group, vehicle) reciprocals computed once
+      const int tiles = (c.A + SB_LIDAR_TILE - 1) / SB_LIDAR_TILE;
+      k_lidar_tiles<<<(env_ids ? n : c.E) * tiles, SB_LIDAR_THREADS, sizeof(LidarShared), st>>>(
+          c, h->dmap, h->st, h->ob, h->ray_table, h->ray_reach, tiles);
+    } else {
+      k_lidar<<<na, SB_LIDAR_THREADS, 0, st>>>(c, h->dmap, h->st, h->ob, h->ray_table, h->ray_reach);
+    }
   }
   if (c.ogm_enable || c.dagm_enable) {
     LaunchScope ls(h, SB_K_RASTER, st);

@@ -46,6 +46,7 @@ struct LTable {
   const int32_t* group_start;  // [G + 1]; rays [group_start[G], R) are vertical
   int32_t n_groups;
   double max_hlen;             // longest horizontal reach of any ray
+  const double* edge_inv;      // [G, n_edges] 1 / (u x edge) or NaN (k_lidar_edge_inv); null: divide in the kernel
 };
 
 // shared-memory working set of one agent's cast (k_sense carves it out of the raster kernel's dynamic buffer)
@@ -263,4 +264,302 @@ k_lidar(DCfg c, DMap m, DState s, DObs o, LTable tab, float reach_xy) {
   int e, a;
   if (!d_work_agent(c, blockIdx.x, &e, &a)) return;
   d_lidar_agent(c, m, s, o, tab, reach_xy, e, a, &sm);
+}
+
+// ---------------------------------------------------------------------------------------------
+// k_lidar_tiles: one block casts for up to SB_LIDAR_TILE agents of ONE env.
+//
+// The rays are fixed in the world frame (lidar.py:108-113 only moves the origin), so what a (group, vehicle)
+// pair needs a division for -- the reciprocals of the group direction's components in the box frame -- is the
+// same for every agent of the env; and the one of a (group, road edge) pair never changes at all
+// (LTable::edge_inv, built when both the map and the ray table are on the device).  The block therefore
+//   P0  stages the env's alive vehicles once,
+//   P1  computes the (group, vehicle) reciprocals once, and culls vehicles / edges per agent into index lists,
+//   P2  turns every (agent, group, near primitive) into its horizontal interval with multiplications only and
+//       links the survivors (about one pair in sixteen) into a list per (agent, group),
+//   P3  casts tile x R rays, each walking the list of its (agent, group),
+// with three barriers for the whole tile instead of two per agent plus a staging round.  The arithmetic of an
+// interval and of a hit is, operation for operation, the one of d_lidar_agent (a hit distance is a minimum:
+// the order in which intervals are met does not matter), so results stay bit-identical to the oracle.
+// A tile whose intervals do not fit SB_LIDAR_LIST falls back to d_lidar_agent, agent after agent.
+#define SB_LIDAR_TILE 4
+#define SB_LIDAR_LIST 640        // intervals held per block
+#define SB_LIDAR_RECIP 768       // (group, vehicle) reciprocal pairs held per block
+#define SB_LIDAR_MAX_GROUPS 64
+
+struct __align__(16) LidarTile {
+  LBox boxes[SB_LIDAR_MAX_BOXES];
+  double2 recip[SB_LIDAR_RECIP];           // 1 / ld0, 1 / ld1 (NaN: the component is zero)
+  LEntry entries[SB_LIDAR_LIST];
+  int32_t next[SB_LIDAR_LIST];
+  int32_t head[SB_LIDAR_TILE][SB_LIDAR_MAX_GROUPS];
+  uint16_t near_box[SB_LIDAR_TILE][SB_LIDAR_MAX_BOXES];
+  uint16_t near_edge[SB_LIDAR_TILE][SB_LIDAR_MAX_EDGES];
+  int16_t box_slot[SB_LIDAR_MAX_BOXES];    // vehicle slot of a staged box
+  double org[SB_LIDAR_TILE][3];
+  int32_t nb[SB_LIDAR_TILE], ne[SB_LIDAR_TILE];
+  int32_t total, n_boxes;
+};
+
+union LidarShared {
+  LidarTile tile;
+  LidarSmem one;
+};
+
+static_assert(SB_LIDAR_TILE == 4, "the flattened item index of k_lidar_tiles is written out for four agents");
+
+__global__ void __launch_bounds__(SB_LIDAR_THREADS, 4)
+k_lidar_tiles(DCfg c, DMap m, DState s, DObs o, LTable tab, float reach_xy, int tiles_per_env) {
+  extern __shared__ __align__(16) unsigned char lidar_raw[];
+  LidarShared* sh = reinterpret_cast<LidarShared*>(lidar_raw);
+  LidarTile& t = sh->tile;
+  const int ne_envs = c.env_list ? c.n_list : c.E;
+  const int qe = blockIdx.x / tiles_per_env;
+  if (qe >= ne_envs) return;
+  const int e = c.env_list ? c.env_list[qe] : qe;
+  const int a0 = (blockIdx.x - qe * tiles_per_env) * SB_LIDAR_TILE;
+  const int na = min(SB_LIDAR_TILE, c.A - a0);
+  const int tid = threadIdx.x, T = blockDim.x;
+  const int R = c.lidar_rays, G = tab.n_groups;
+  const double inf = __longlong_as_double(0x7ff0000000000000LL);
+  const double nan = __longlong_as_double(0x7ff8000000000000LL);
+
+  // ---- P0: the env's alive vehicles, the tile's origins
+  if (tid == 0) {
+    t.total = 0;
+    t.n_boxes = 0;
+  }
+  if (tid < SB_LIDAR_TILE) {
+    t.nb[tid] = 0;
+    t.ne[tid] = 0;
+    if (tid < na) {
+      const int vi = e * c.V + a0 + tid;
+      t.org[tid][0] = s.pos_x[vi];
+      t.org[tid][1] = s.pos_y[vi];
+      t.org[tid][2] = s.pos_z[vi] + 1.0;
+    }
+  }
+  for (int i = tid; i < SB_LIDAR_TILE * SB_LIDAR_MAX_GROUPS; i += T) (&t.head[0][0])[i] = -1;
+  __syncthreads();
+  for (int j = tid; j < c.V; j += T) {
+    const int vj = e * c.V + j;
+    const bool alive = s.alive[vj] != 0;
+    const double vx = s.pos_x[vj], vy = s.pos_y[vj], vz = s.pos_z[vj], vc = s.cos_h[vj], vs = s.sin_h[vj];
+    const double vw = s.width[vj], vl = s.length[vj], vhh = s.height[vj];
+    if (!alive) continue;
+    const int k = atomicAdd(&t.n_boxes, 1);  // V <= SB_LIDAR_MAX_BOXES on this path
+    const double z0 = vz + (j < c.A ? 0.1 : 0.2);
+    t.boxes[k] = LBox{vx, vy, vc, vs, 0.5 * vw, 0.5 * vl, z0, z0 + vhh};
+    t.box_slot[k] = (int16_t)j;
+  }
+  __syncthreads();
+
+  // ---- P1: reciprocals per (group, vehicle); near lists per agent
+  const int nbx = t.n_boxes;
+  for (int p = tid; p < G * nbx; p += T) {
+    const int g = p / nbx, k = p - g * nbx;
+    const double2 u = tab.group_u[g];
+    const LBox& b = t.boxes[k];
+    const double ld0 = u.x * b.c + u.y * b.s, ld1 = u.y * b.c - u.x * b.s;
+    t.recip[p] = make_double2(ld0 == 0.0 ? nan : 1.0 / ld0, ld1 == 0.0 ? nan : 1.0 / ld1);
+  }
+  for (int p = tid; p < na * nbx; p += T) {
+    const int al = p / nbx, k = p - al * nbx;
+    if (t.box_slot[k] == a0 + al) continue;  // the ego's own box
+    const LBox& b = t.boxes[k];
+    // a hit lies within reach_xy of the origin and within the half diagonal of the box centre
+    const float bx = (float)(b.x - t.org[al][0]), by = (float)(b.y - t.org[al][1]);
+    const float fw = (float)(2.0 * b.hw), fl = (float)(2.0 * b.hl);
+    const float hd = 0.5f * sqrtf(fw * fw + fl * fl);
+    const float lim = reach_xy + hd + 0.25f;
+    if (bx * bx + by * by > lim * lim) continue;
+    t.near_box[al][atomicAdd(&t.nb[al], 1)] = (uint16_t)k;
+  }
+  if (c.lidar_wall_height > 0.0) {
+    // segments whose bounding circle reaches an agent's disc; from the far end of the block, so that other
+    // warps than the ones above take them
+    for (int p = T - 1 - tid; p < na * m.n_edges; p += T) {
+      const int al = p / m.n_edges, k = p - al * m.n_edges;
+      const double4 ed = reinterpret_cast<const double4*>(m.road_edges)[k];
+      const double ox = t.org[al][0], oy = t.org[al][1];
+      const float ax = (float)(ed.x - ox), ay = (float)(ed.y - oy), bx = (float)(ed.z - ox), by = (float)(ed.w - oy);
+      const float mx = 0.5f * (ax + bx), my = 0.5f * (ay + by), hx = 0.5f * (bx - ax), hy = 0.5f * (by - ay);
+      const float hl = sqrtf(hx * hx + hy * hy);
+      const float reach = hl + reach_xy + 0.25f;
+      if (mx * mx + my * my > reach * reach) continue;
+      const int q = atomicAdd(&t.ne[al], 1);
+      if (q < SB_LIDAR_MAX_EDGES) t.near_edge[al][q] = (uint16_t)k;
+    }
+  }
+  __syncthreads();
+
+  // ---- P2: intervals of every (agent, group, near primitive), the tile's items flattened
+  int cnt_a[SB_LIDAR_TILE];  // near primitives of each agent (static indexing only: stays in registers)
+#pragma unroll
+  for (int al = 0; al < SB_LIDAR_TILE; ++al) {
+    cnt_a[al] = 0;
+    if (al < na) {
+      const int ne = t.ne[al] < SB_LIDAR_MAX_EDGES ? t.ne[al] : SB_LIDAR_MAX_EDGES;
+      cnt_a[al] = t.nb[al] + ne;
+      if (tid == 0 && t.ne[al] > SB_LIDAR_MAX_EDGES) s.status[e * c.A + a0 + al] |= SB_STATUS_LIDAR_OVERFLOW;
+    }
+  }
+  const int c1 = G * cnt_a[0], c2 = c1 + G * cnt_a[1], c3 = c2 + G * cnt_a[2], c4 = c3 + G * cnt_a[3];
+  for (int p = tid; p < c4; p += T) {
+    const int al = (p >= c1) + (p >= c2) + (p >= c3);
+    const int base = al == 0 ? 0 : al == 1 ? c1 : al == 2 ? c2 : c3;
+    const int nprim = al == 0 ? cnt_a[0] : al == 1 ? cnt_a[1] : al == 2 ? cnt_a[2] : cnt_a[3];
+    const int r = p - base;
+    const int nbl = t.nb[al];
+    const int g = r / nprim, k = r - g * nprim;
+    const double ox = t.org[al][0], oy = t.org[al][1];
+    LEntry en;
+    if (k < nbl) {
+      const int kb = t.near_box[al][k];
+      const LBox b = t.boxes[kb];
+      const double2 inv = t.recip[g * nbx + kb];
+      const double rx = ox - b.x, ry = oy - b.y;
+      const double lo0 = rx * b.c + ry * b.s, lo1 = ry * b.c - rx * b.s;  // box frame: right, forward
+      double s0 = -inf, s1 = inf;
+      bool ok = true;
+      if (inv.x != inv.x) {  // ld0 == 0
+        if (lo0 < -b.hw || lo0 > b.hw) ok = false;
+      } else {
+        double sa = (-b.hw - lo0) * inv.x, sb = (b.hw - lo0) * inv.x;
+        if (sa > sb) {
+          const double tmp = sa;
+          sa = sb;
+          sb = tmp;
+        }
+        if (sa > s0) s0 = sa;
+        if (sb < s1) s1 = sb;
+      }
+      if (inv.y != inv.y) {  // ld1 == 0
+        if (lo1 < -b.hl || lo1 > b.hl) ok = false;
+      } else {
+        double sa = (-b.hl - lo1) * inv.y, sb = (b.hl - lo1) * inv.y;
+        if (sa > sb) {
+          const double tmp = sa;
+          sa = sb;
+          sb = tmp;
+        }
+        if (sa > s0) s0 = sa;
+        if (sb < s1) s1 = sb;
+      }
+      if (!ok || s0 > s1 || s1 < 0.0 || s0 > tab.max_hlen) continue;
+      en = LEntry{s0, s1, b.z0, b.z1};
+    } else {
+      const int ke = t.near_edge[al][k - nbl];
+      const double4 ed = reinterpret_cast<const double4*>(m.road_edges)[ke];
+      const double2 u = tab.group_u[g];
+      const double ex = ed.z - ed.x, ey = ed.w - ed.y;
+      double inv;
+      if (tab.edge_inv) {
+        inv = tab.edge_inv[(size_t)g * m.n_edges + ke];
+        if (inv != inv) continue;  // den == 0
+      } else {
+        const double den = u.x * ey - u.y * ex;
+        if (den == 0.0) continue;
+        inv = 1.0 / den;
+      }
+      const double qx = ed.x - ox, qy = ed.y - oy;
+      const double sw = (qx * ey - qy * ex) * inv;
+      const double uu = (qx * u.y - qy * u.x) * inv;
+      if (sw < 0.0 || uu < 0.0 || uu > 1.0 || sw > tab.max_hlen) continue;
+      en = LEntry{sw, sw, 0.0, c.lidar_wall_height};
+    }
+    const int idx = atomicAdd(&t.total, 1);
+    if (idx < SB_LIDAR_LIST) {
+      t.entries[idx] = en;
+      t.next[idx] = atomicExch(&t.head[al][g], idx);
+    }
+  }
+  __syncthreads();
+  if (t.total > SB_LIDAR_LIST) {  // (uniform) too many intervals for the list: one agent at a time, chunked
+    __syncthreads();
+    for (int al = 0; al < na; ++al) {
+      d_lidar_agent(c, m, s, o, tab, reach_xy, e, a0 + al, &sh->one);
+      __syncthreads();
+    }
+    return;
+  }
+
+  // ---- P3: rays
+  const double miss = c.lidar_miss_inf ? inf : 0.0;
+  const int v0 = tab.group_start[G];  // first vertical ray of the sorted table
+  for (int al = 0; al < na; ++al) {
+    const double ox = t.org[al][0], oy = t.org[al][1], oz = t.org[al][2];
+    const size_t wbase = (size_t)(e * c.A + a0 + al) * R;
+    for (int si = tid; si < R; si += T) {
+      const SbRayRec q = tab.rec[si];
+      const size_t w = wbase + q.index;
+      if (si >= v0) {  // no horizontal extent: the ground plane only
+        double tt = 2.0;
+        if (q.dz < 0.0) {
+          tt = (0.0 - oz) / q.dz;
+          if (!(tt >= 0.0 && tt <= 1.0)) tt = 2.0;
+        }
+        if (tt <= 1.0) {
+          o.lidar_hits[w] = 1;
+          o.lidar_points[w * 3 + 0] = ox;
+          o.lidar_points[w * 3 + 1] = oy;
+          o.lidar_points[w * 3 + 2] = oz + tt * q.dz;
+        } else {
+          o.lidar_hits[w] = 0;
+          o.lidar_points[w * 3 + 0] = miss;
+          o.lidar_points[w * 3 + 1] = miss;
+          o.lidar_points[w * 3 + 2] = miss;
+        }
+        continue;
+      }
+      double sbest = inf;
+      if (q.dz < 0.0) {
+        const double sg = (0.0 - oz) * q.inv_slope;
+        if (sg >= 0.0 && sg <= q.hlen) sbest = sg;
+      }
+      for (int i = t.head[al][q.group]; i >= 0; i = t.next[i]) {
+        const LEntry en = t.entries[i];
+        double e0 = en.s0, e1 = en.s1;
+        if (q.dz == 0.0) {
+          if (oz < en.zlo || oz > en.zhi) continue;
+        } else {
+          double za = (en.zlo - oz) * q.inv_slope, zb = (en.zhi - oz) * q.inv_slope;
+          if (za > zb) {
+            const double tmp = za;
+            za = zb;
+            zb = tmp;
+          }
+          if (za > e0) e0 = za;
+          if (zb < e1) e1 = zb;
+        }
+        if (e0 > e1 || e0 < 0.0 || e0 > q.hlen) continue;  // e0 < 0: origin inside the box, no hit
+        if (e0 < sbest) sbest = e0;
+      }
+      if (sbest <= q.hlen) {
+        const double2 u = tab.group_u[q.group];
+        o.lidar_hits[w] = 1;
+        o.lidar_points[w * 3 + 0] = ox + sbest * u.x;
+        o.lidar_points[w * 3 + 1] = oy + sbest * u.y;
+        o.lidar_points[w * 3 + 2] = oz + sbest * q.slope;
+      } else {
+        o.lidar_hits[w] = 0;
+        o.lidar_points[w * 3 + 0] = miss;
+        o.lidar_points[w * 3 + 1] = miss;
+        o.lidar_points[w * 3 + 2] = miss;
+      }
+    }
+  }
+}
+
+// 1 / (u x edge) of every (group, road edge) pair, NaN where the cross product is zero
+__global__ void k_lidar_edge_inv(const double* __restrict__ road_edges, int n_edges, const double2* __restrict__ group_u,
+                                 int n_groups, double* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_groups * n_edges) return;
+  const int g = i / n_edges, k = i - g * n_edges;
+  const double4 ed = reinterpret_cast<const double4*>(road_edges)[k];
+  const double2 u = group_u[g];
+  const double ex = ed.z - ed.x, ey = ed.w - ed.y;
+  const double den = u.x * ey - u.y * ex;
+  out[i] = den == 0.0 ? __longlong_as_double(0x7ff8000000000000LL) : 1.0 / den;
 }
