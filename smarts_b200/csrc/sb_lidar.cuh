@@ -484,69 +484,66 @@ k_lidar_tiles(DCfg c, DMap m, DState s, DObs o, LTable tab, float reach_xy, int 
     return;
   }
 
-  // ---- P3: rays
+  // ---- P3: rays; a thread keeps its ray record for every agent of the tile
   const double miss = c.lidar_miss_inf ? inf : 0.0;
   const int v0 = tab.group_start[G];  // first vertical ray of the sorted table
-  for (int al = 0; al < na; ++al) {
-    const double ox = t.org[al][0], oy = t.org[al][1], oz = t.org[al][2];
-    const size_t wbase = (size_t)(e * c.A + a0 + al) * R;
-    for (int si = tid; si < R; si += T) {
-      const SbRayRec q = tab.rec[si];
-      const size_t w = wbase + q.index;
-      if (si >= v0) {  // no horizontal extent: the ground plane only
+  for (int si = tid; si < R; si += T) {
+    const SbRayRec q = tab.rec[si];
+    const bool vertical = si >= v0;
+    double2 u = make_double2(0.0, 0.0);
+    if (!vertical) u = tab.group_u[q.group];
+    for (int al = 0; al < na; ++al) {
+      const double ox = t.org[al][0], oy = t.org[al][1], oz = t.org[al][2];
+      const size_t w = (size_t)(e * c.A + a0 + al) * R + q.index;
+      double px = miss, py = miss, pz = miss;
+      bool hit = false;
+      if (vertical) {  // no horizontal extent: the ground plane only
         double tt = 2.0;
         if (q.dz < 0.0) {
           tt = (0.0 - oz) / q.dz;
           if (!(tt >= 0.0 && tt <= 1.0)) tt = 2.0;
         }
         if (tt <= 1.0) {
-          o.lidar_hits[w] = 1;
-          o.lidar_points[w * 3 + 0] = ox;
-          o.lidar_points[w * 3 + 1] = oy;
-          o.lidar_points[w * 3 + 2] = oz + tt * q.dz;
-        } else {
-          o.lidar_hits[w] = 0;
-          o.lidar_points[w * 3 + 0] = miss;
-          o.lidar_points[w * 3 + 1] = miss;
-          o.lidar_points[w * 3 + 2] = miss;
+          hit = true;
+          px = ox;
+          py = oy;
+          pz = oz + tt * q.dz;
         }
-        continue;
-      }
-      double sbest = inf;
-      if (q.dz < 0.0) {
-        const double sg = (0.0 - oz) * q.inv_slope;
-        if (sg >= 0.0 && sg <= q.hlen) sbest = sg;
-      }
-      for (int i = t.head[al][q.group]; i >= 0; i = t.next[i]) {
-        const LEntry en = t.entries[i];
-        double e0 = en.s0, e1 = en.s1;
-        if (q.dz == 0.0) {
-          if (oz < en.zlo || oz > en.zhi) continue;
-        } else {
-          double za = (en.zlo - oz) * q.inv_slope, zb = (en.zhi - oz) * q.inv_slope;
-          if (za > zb) {
-            const double tmp = za;
-            za = zb;
-            zb = tmp;
-          }
-          if (za > e0) e0 = za;
-          if (zb < e1) e1 = zb;
-        }
-        if (e0 > e1 || e0 < 0.0 || e0 > q.hlen) continue;  // e0 < 0: origin inside the box, no hit
-        if (e0 < sbest) sbest = e0;
-      }
-      if (sbest <= q.hlen) {
-        const double2 u = tab.group_u[q.group];
-        o.lidar_hits[w] = 1;
-        o.lidar_points[w * 3 + 0] = ox + sbest * u.x;
-        o.lidar_points[w * 3 + 1] = oy + sbest * u.y;
-        o.lidar_points[w * 3 + 2] = oz + sbest * q.slope;
       } else {
-        o.lidar_hits[w] = 0;
-        o.lidar_points[w * 3 + 0] = miss;
-        o.lidar_points[w * 3 + 1] = miss;
-        o.lidar_points[w * 3 + 2] = miss;
+        double sbest = inf;
+        if (q.dz < 0.0) {
+          const double sg = (0.0 - oz) * q.inv_slope;
+          if (sg >= 0.0 && sg <= q.hlen) sbest = sg;
+        }
+        for (int i = t.head[al][q.group]; i >= 0; i = t.next[i]) {
+          const LEntry en = t.entries[i];
+          double e0 = en.s0, e1 = en.s1;
+          if (q.dz == 0.0) {
+            if (oz < en.zlo || oz > en.zhi) continue;
+          } else {
+            double za = (en.zlo - oz) * q.inv_slope, zb = (en.zhi - oz) * q.inv_slope;
+            if (za > zb) {
+              const double tmp = za;
+              za = zb;
+              zb = tmp;
+            }
+            if (za > e0) e0 = za;
+            if (zb < e1) e1 = zb;
+          }
+          if (e0 > e1 || e0 < 0.0 || e0 > q.hlen) continue;  // e0 < 0: origin inside the box, no hit
+          if (e0 < sbest) sbest = e0;
+        }
+        if (sbest <= q.hlen) {
+          hit = true;
+          px = ox + sbest * u.x;
+          py = oy + sbest * u.y;
+          pz = oz + sbest * q.slope;
+        }
       }
+      o.lidar_hits[w] = hit ? 1 : 0;
+      o.lidar_points[w * 3 + 0] = px;
+      o.lidar_points[w * 3 + 1] = py;
+      o.lidar_points[w * 3 + 2] = pz;
     }
   }
 }
