@@ -664,3 +664,70 @@ def test_captured_tick_replays_bit_identically():
         torch.cuda.synchronize()
         assert_same(graphed.obs_numpy(), eager.obs_numpy())
         assert_same(graphed.state_numpy(), eager.state_numpy())
+
+
+def test_lane_action_strings_use_the_reference_dispatch_table():
+    """Controllers.perform_action for ActionSpaceType.Lane (/root/reference/smarts/core/controllers/__init__.py:125-144):
+    keep_lane -> (target_speed 15, lane_change 0), slow_down -> (0, 0), change_lane_left -> (12.5, +1),
+    change_lane_right -> (12.5, -1).  The Lane action space must move the vehicles exactly as
+    LaneWithContinuousSpeed does with those tuples (same controller behind both, :100-124)."""
+    import torch
+    from smarts_b200.agent_interface import ActionSpaceType
+    from smarts_b200.hiway_env import encode_actions
+    table = {"keep_lane": (15, 0), "slow_down": (0, 0), "change_lane_left": (12.5, 1), "change_lane_right": (12.5, -1)}
+    rm = load_map("4lane")
+    E, A = 6, 4
+    x, y, h, v, route, rlen = scenario_gen.agent_starts(rm, E, MISSIONS_4LANE, 16, 3, jitter=20.0, speed=5.0)
+    names = list(table)
+    rng = np.random.default_rng(5)
+    engs = [engine(rm, make_cfg(E=E, A=A, action_space=sp, route_cap=16))
+            for sp in (_abi.SB_ACTION_LANE, _abi.SB_ACTION_LANE_WITH_CONTINUOUS_SPEED)]
+    for g in engs:
+        g.reset(x, y, h, v, route, rlen)
+    for t in range(25):
+        pick = [names[i] for i in rng.integers(0, 4, E * A)]
+        a_lane = encode_actions(ActionSpaceType.Lane, pick, 10).reshape(E, A)
+        a_speed = encode_actions(ActionSpaceType.LaneWithContinuousSpeed, [table[p] for p in pick], 10).reshape(E, A, 2)
+        engs[0].step(torch.from_numpy(a_lane).cuda())
+        engs[1].step(torch.from_numpy(a_speed).cuda())
+    s0, s1 = engs[0].state_numpy(), engs[1].state_numpy()
+    assert_same(s0, s1, keys=("pos_x", "pos_y", "heading", "speed", "steering", "last_control"))
+    assert np.ptp(s0["speed"][:, :A]) > 1.0          # the four commands did drive the agents apart
+    for g in engs:
+        g.close()
+
+
+def test_headline_batch_at_full_size_matches_oracle():
+    """BASELINE configs[2] at its full size -- 4096 envs x 4 agents, 20 social vehicles, LiDAR 300 rays (road-edge
+    walls on) + OGM + DAGM 256 x 256 @ 0.1 m/px -- three ticks, every state and observation tensor bit for bit against
+    the oracle (16 384 agents, 2.27 GB of observations per tick; the oracle takes about half a second per tick on the
+    box's host cores).  Tick 2 is compared after the agents have moved off their reset poses."""
+    import os
+    import torch
+    rm = load_map("4lane")
+    E, A, M = 4096, 4, 20
+    cfg = make_cfg(E=E, A=A, M=M, lidar=True, wall=1.5, ogm=(256, 256, 0.1), dagm=(256, 256, 0.1), route_cap=16)
+    x, y, h, v, route, rlen = scenario_gen.agent_starts(rm, E, MISSIONS_4LANE, cfg.route_cap, 11, jitter=25.0, speed=8.0)
+    traffic = scenario_gen.SocialTraffic(rm, E, M, 12)
+    eng = engine(rm, cfg)
+    ora = oracle_world(rm, cfg, threads=os.cpu_count() or 8)
+    eng.reset(x, y, h, v, route, rlen)
+    ora.reset(x, y, h, v, route, rlen)
+    act = np.zeros((E, A), np.int32)
+    for t in range(3):
+        soc = traffic.states(t)
+        eng.set_social(torch.from_numpy(soc).cuda())
+        ora.set_social(soc)
+        eng.step(torch.from_numpy(act).cuda())
+        ora.step(act)
+    eng.observe()
+    ora.observe()
+    assert_same(eng.state_numpy(), ora.state())
+    want = ora.obs()
+    obs = eng.obs()                                     # device tensors: compared key by key to bound host memory
+    for k, wv in want.items():
+        got = obs[k].cpu().numpy()
+        assert_same({k: got}, {k: wv})
+        del got
+    assert want["ogm"].any() and want["dagm"].any() and want["lidar_hits"].any()
+    eng.close()
