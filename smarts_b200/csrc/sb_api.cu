@@ -38,6 +38,7 @@ struct SbHandle_ {
   int32_t* d_veh_lane = nullptr;  // k_vehicle_lanes -> k_observe (only when V <= A * nbr_cap)
   int32_t *h_env_list = nullptr, *d_env_list = nullptr;  // sb_observe_envs: pinned staging + device copy of the env list
   cudaStream_t env_list_stream = nullptr;
+  cudaStream_t last_stream = nullptr;  // stream of the last sb_set_social / sb_step / sb_observe (host-buffer calls order themselves after it)
   bool stepped = false;  // a sb_step since the last sb_observe (SensorState.step; `sim.resetting` otherwise)
   bool have_map = false, have_rays = false;
   bool stale_agents = false;          // a new map was uploaded: routes / lanes of the old one are meaningless until a full reset
@@ -218,6 +219,21 @@ struct LaunchScope {
   }
 };
 
+// Every entry point runs with the handle's device current and hands the caller's back (a process may hold handles on
+// several GPUs, or call from a thread whose current device is another one).
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = true;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    if (prev != dev) ok = cudaSetDevice(dev) == cudaSuccess;
+  }
+  ~DeviceGuard() {
+    int cur = -1;
+    if (prev >= 0 && cudaGetDevice(&cur) == cudaSuccess && cur != prev) cudaSetDevice(prev);
+  }
+};
+
 size_t action_bytes(const SbConfig& c) {
   size_t na = (size_t)c.n_envs * c.n_agents;
   switch (c.action_space) {
@@ -270,7 +286,8 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
   if (c.n_agents + c.n_social > SB_LIDAR_MAX_BOXES + 1 && c.lidar_enable)
     return fail(h, SB_EINVAL, "lidar: too many vehicles per env");
 
-  if (!cuda_ok(h, cudaSetDevice(c.device), "cudaSetDevice")) return SB_ECUDA;
+  DeviceGuard dg(c.device);  // (the caller's current device is restored on return)
+  if (!cuda_ok(h, dg.ok ? cudaSuccess : cudaErrorInvalidDevice, "cudaSetDevice")) return SB_ECUDA;
   DCfg& d = h->dc;
   d.E = c.n_envs; d.A = c.n_agents; d.M = c.n_social; d.V = d.A + d.M;
   d.dt = c.dt;
@@ -449,7 +466,7 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
 
 void sb_destroy(SbHandle h) {
   if (!h) return;
-  cudaSetDevice(h->cfg.device);
+  DeviceGuard dg(h->cfg.device);
   cudaDeviceSynchronize();
   for (void* p : h->allocs) cudaFree(p);
   for (void* p : h->map_allocs) cudaFree(p);
@@ -469,7 +486,7 @@ int sb_upload_map(SbHandle h, const SbMap* mp) {
   if (!h || !mp) return SB_EINVAL;
   if (h->cuda_err) return SB_ECUDA;
   if (mp->n_lanes < 1 || mp->n_lanepoints < 1) return fail(h, SB_EINVAL, "empty map");
-  cudaSetDevice(h->cfg.device);
+  DeviceGuard dg(h->cfg.device);
   if (h->have_map) {  // scenario cycling (hiway_env.py:265-285 draws the next scenario on reset): replace the map
     if (!cuda_ok(h, cudaDeviceSynchronize(), "sync before map replacement")) return SB_ECUDA;
     for (void* q : h->map_allocs) cudaFree(q);
@@ -696,7 +713,7 @@ int sb_upload_lidar_rays(SbHandle h, const double* base_rays, int32_t n_rays) {
   if (!h || !base_rays) return SB_EINVAL;
   if (h->cuda_err) return SB_ECUDA;
   if (n_rays != h->cfg.lidar_rays) return fail(h, SB_EINVAL, "n_rays != cfg.lidar_rays");
-  cudaSetDevice(h->cfg.device);
+  DeviceGuard dg(h->cfg.device);
   if (n_rays > SB_LIDAR_MAX_RAYS) return fail(h, SB_EINVAL, "lidar: too many rays");
   // Factor the table into azimuth groups (include/sb_lidar_table.h; the oracle runs the same function) and
   // sort the records by group, vertical rays last: a warp's 32 rays then walk the same interval list.
@@ -801,7 +818,7 @@ int sb_reset(SbHandle h, const int32_t* env_ids, int32_t n, const SbResetState* 
   if (env_ids)
     for (int i = 0; i < n; ++i)
       if (env_ids[i] < 0 || env_ids[i] >= c.E) return fail(h, SB_EINVAL, "env id out of range");
-  cudaSetDevice(h->cfg.device);
+  DeviceGuard dg(h->cfg.device);
   size_t na = (size_t)n * c.A;
   // one staging buffer: ids | x | y | h | v | route | route_len
   size_t off_ids = 0, off_x = ((size_t)n * 4 + 7) / 8 * 8, off_y = off_x + na * 8, off_h = off_y + na * 8,
@@ -851,6 +868,8 @@ int sb_set_social(SbHandle h, const double* dev_states, void* stream) {
   const DCfg& c = h->dc;
   if (c.M == 0) return SB_OK;
   if (!dev_states) return fail(h, SB_EINVAL, "dev_states is null");
+  DeviceGuard dg(h->cfg.device);
+  h->last_stream = (cudaStream_t)stream;
   int n = c.E * c.M;
   {
     LaunchScope ls(h, SB_K_SOCIAL, (cudaStream_t)stream);
@@ -867,6 +886,8 @@ int sb_step(SbHandle h, const void* dev_actions, void* stream) {
   const DCfg& c = h->dc;
   int na = c.E * c.A;
   cudaStream_t st = (cudaStream_t)stream;
+  DeviceGuard dg(h->cfg.device);
+  h->last_stream = st;
   {
     LaunchScope ls(h, SB_K_CONTROL, st);
     if (c.action_space == SB_ACTION_LANE || c.action_space == SB_ACTION_LANE_WITH_CONTINUOUS_SPEED) {
@@ -892,6 +913,8 @@ int sb_observe_envs(SbHandle h, const int32_t* env_ids, int32_t n, void* stream)
   if (h->stale_agents) return fail(h, SB_ESTATE, "the map was replaced: reset every env (sb_reset with env_ids = NULL) first");
   if (h->dc.lidar_enable && !h->have_rays) return fail(h, SB_ESTATE, "lidar enabled but no ray table uploaded");
   cudaStream_t st = (cudaStream_t)stream;
+  DeviceGuard dg(h->cfg.device);
+  h->last_stream = st;
   DCfg c = h->dc;  // this call's copy: the env list rides in it
   if (env_ids) {
     if (n < 1 || n > c.E) return fail(h, SB_EINVAL, "n out of range");
@@ -980,7 +1003,9 @@ int sb_step_host(SbHandle h, const void* host_actions, int64_t n_bytes, const do
   if (h->cuda_err) return SB_ECUDA;
   if ((size_t)n_bytes != h->actions_cap) return fail(h, SB_EINVAL, "action_bytes does not match the action space");
   const DCfg& c = h->dc;
-  cudaSetDevice(h->cfg.device);
+  DeviceGuard dg(h->cfg.device);
+  // this call works on the legacy stream; work queued by sb_step / sb_observe on another (non-blocking) stream comes first
+  if (h->last_stream && cudaStreamSynchronize(h->last_stream) != cudaSuccess) cudaGetLastError();  // (a stream the caller has since destroyed has nothing pending)
   if (!cuda_ok(h, cudaMemcpyAsync(h->d_actions, host_actions, h->actions_cap, cudaMemcpyHostToDevice, 0), "H2D actions"))
     return SB_ECUDA;
   if (c.M > 0) {
@@ -1010,7 +1035,9 @@ static int copy_obs_to_host(SbHandle h, const SbObsPtrs* dst, bool packed_dst) {
   const SbConfig& c = h->cfg;
   const DObs& o = h->ob;
   size_t na = (size_t)c.n_envs * c.n_agents;
-  cudaSetDevice(c.device);
+  DeviceGuard dg(c.device);
+  // copies run on the legacy stream: observations written on another (non-blocking) stream are waited for first
+  if (h->last_stream && cudaStreamSynchronize(h->last_stream) != cudaSuccess) cudaGetLastError();  // (a stream the caller has since destroyed has nothing pending)
   bool ok = true;
   size_t link_total = 0;  // bytes queued on the PCIe link by this call
   auto cpy = [&](void* d, const void* s, size_t bytes) {
@@ -1229,7 +1256,7 @@ int sb_set_timing(SbHandle h, int on) {
 
 int sb_collect_timing(SbHandle h, double* ms_sum, int64_t* count) {
   if (!h || !ms_sum || !count) return SB_EINVAL;
-  cudaSetDevice(h->cfg.device);
+  DeviceGuard dg(h->cfg.device);
   if (!cuda_ok(h, cudaDeviceSynchronize(), "sb_collect_timing sync")) return SB_ECUDA;
   for (int k = 0; k < SB_K_COUNT; ++k) {
     ms_sum[k] = 0.0;

@@ -731,3 +731,37 @@ def test_headline_batch_at_full_size_matches_oracle():
         del got
     assert want["ogm"].any() and want["dagm"].any() and want["lidar_hits"].any()
     eng.close()
+
+
+def test_host_buffer_copy_orders_itself_after_a_side_stream():
+    """sb_step / sb_observe queued on a non-blocking side stream, then sb_copy_obs_to_host (which copies on the legacy
+    stream): the copy must wait for the observation kernels of the side stream.  A long chain of ticks is queued first
+    so that the kernels are still running when the copy call is made."""
+    import torch
+    rm = load_map("4lane")
+    E, A, M = 64, 4, 20
+    cfg = make_cfg(E=E, A=A, M=M, lidar=True, wall=1.5, ogm=(256, 256, 0.1), dagm=(256, 256, 0.1), route_cap=16)
+    x, y, h, v, route, rlen = scenario_gen.agent_starts(rm, E, MISSIONS_4LANE, cfg.route_cap, 5, jitter=20.0, speed=6.0)
+    traffic = scenario_gen.SocialTraffic(rm, E, M, 6)
+    eng, ora = engine(rm, cfg), oracle_world(rm, cfg, threads=8)
+    eng.reset(x, y, h, v, route, rlen)
+    ora.reset(x, y, h, v, route, rlen)
+    act = np.zeros((E, A), np.int32)
+    side = torch.cuda.Stream()
+    socs = [torch.from_numpy(traffic.states(t)).cuda() for t in range(12)]
+    acts = torch.from_numpy(act).cuda()
+    torch.cuda.synchronize()
+    with torch.cuda.stream(side):
+        for t in range(12):
+            eng.set_social(socs[t])
+            eng.step(acts)
+            eng.observe()
+    bufs = eng.host_obs_buffers(pinned=True)
+    eng.copy_obs_to_host(bufs)                      # no torch-side synchronisation in between
+    for t in range(12):
+        ora.set_social(traffic.states(t))
+        ora.step(act)
+        ora.observe()
+    want = ora.obs()
+    assert_same({k: bufs[k].numpy() for k in want}, want)
+    eng.close()
