@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define SB_ABI_VERSION 6
+#define SB_ABI_VERSION 7
 
 /* error codes */
 #define SB_OK 0
@@ -143,6 +143,9 @@ typedef struct SbConfig {
   int32_t rw_horizon;      /* RoadWaypoints.horizon (default 20) */
   int32_t rw_lanes_cap;
   int32_t rw_paths_cap;
+  /* AgentInterface.vehicle_type (agent_interface.py:246-250; vehicle.py:393-406): SB_VEHICLE_SEDAN (0) or
+   * SB_VEHICLE_BUS (1) of include/sb_vehicle.h -- chassis box, masses, torques and controller gains of the agents */
+  int32_t vehicle_type;
 } SbConfig;
 
 /* Per-scenario constant road map (host pointers, copied once).  Built by

@@ -31,19 +31,7 @@ void parallel_for(int n, int threads, int chunk, F fn) {
   for (auto& th : pool) th.join();
 }
 
-constexpr double kMaxSteeringWheel = 12.56 / 17.4;  // chassis.py:628-631, controller_parameters.yaml:23-25
-constexpr double kSteerLimit = 0.8727;              // models/vehicle.urdf:101
-constexpr double kWheelRadius = 0.31265, kMaxTorque = 1600.0, kMaxBrakeTorque = 1400.0;
-// 1 + 2356 + 2*1 + 4*15 kg (vehicle.urdf) plus the wheels' rotational inertia 4*Izz/r^2
-constexpr double kEffMass = 2419.0 + 4.0 * 2.0 / (kWheelRadius * kWheelRadius);
-constexpr double kRearAxleToCg = 1.5;  // wheels at y = +-1.5 (vehicle.urdf:96-135)
-// single-track model constants (DESIGN.md "Vehicle model")
-constexpr double kMass = 2356.0 + 4.0 * 15.0;                  // vehicle.urdf:19, :40 (chassis + wheels)
-constexpr double kIzz = 2681.95008628 + 4.0 * 15.0 * (1.5 * 1.5 + 0.5 * 0.5);  // vehicle.urdf:21 + wheels as point masses
-constexpr double kCornerStiffness = 100000.0;  // N/rad per axle: the stiffness the reference's own lateral-gain design
-                                               // linearises with (lane_following_controller.py:392-422, plane.urdf:26)
-constexpr double kTyreForceMax = 3.0 * kMass * 9.8 / 2.0;  // per axle: plane.urdf:24 lateral_friction 3 against a wheel
-                                                           // friction of 1 (plane.urdf:5-17), gravity 9.8 (smarts.py:600)
+// vehicle-type constants: World::veh, filled by sb_vehicle() of include/sb_vehicle.h (the CUDA library holds the same record)
 constexpr double kSteerJointGain = 0.1;  // POSITION_CONTROL default positionGain: 10 % of the error per sub-step
 constexpr double kDynSpeed = 1.0;        // m/s: below it the tyres roll without slip (the slip angles divide by speed)
 
@@ -63,8 +51,8 @@ inline void apply_control(const Ego& v, double thr, double brake, double steer, 
 // [2] steering_state [3] throttle_state [4] speed_error [5,6] min_curvature_location [7] valid.
 // _update_target_lane_if_reached_end_of_lane (:439-473) only rewrites state.target_lane_id, which
 // feeds nothing but itself, so it is not restated.
-uint32_t lane_following(const Map& mp, const Ego& v, const int32_t* route, int route_len, double target_speed,
-                        int lane_change, double dt, double* st, double* out3) {
+uint32_t lane_following(const Map& mp, const SbVehicle& vp, const Ego& v, const int32_t* route, int route_len,
+                        double target_speed, int lane_change, double dt, double* st, double* out3) {
   static thread_local PathSet ps;
   waypoint_paths(mp, v.x, v.y, v.h, 16, 5.0, route, route_len, &ps);
   uint32_t status = ps.overflow ? SB_STATUS_PATH_OVERFLOW : 0u;
@@ -127,14 +115,14 @@ uint32_t lane_following(const Map& mp, const Ego& v, const int32_t* route, int r
   double damping = (speed_error - st[4]) / dt;
   double lfc = 1.5;
   if (v.speed < 8 || target_speed < 6) lfc = 0;
-  raw += (-0.2 * damping - 0.1 * st[1]) + std::fabs(lfc * sb_sin(st[2] * kMaxSteeringWheel));
+  raw += (-0.2 * damping - 0.1 * st[1]) + std::fabs(lfc * sb_sin(st[2] * vp.max_steering_wheel));
   st[4] = speed_error;
   if (st[7] != 0.0) {
     double mx = v.x - st[5], my = v.y - st[6];
     if (std::sqrt(mx * mx + my * my) < 2) ref_h = wp[la].heading;
   }
   double Kh, Kl;
-  lateral_gains(target_speed, &Kh, &Kl);
+  lateral_gains(target_speed, vp, &Kh, &Kl);
   double dvx, dvy;
   radians_to_vec(wp[la].heading, &dvx, &dvy);
   double lat_err = signed_dist_to_line(lx, ly, wp[la].x, wp[la].y, dvx, dvy);
@@ -180,17 +168,18 @@ uint32_t lane_following(const Map& mp, const Ego& v, const int32_t* route, int r
 // models/controller_parameters.yaml:3-16.  st: [0] heading_error [1] lateral_error
 // [2] velocity_error [3] integral_velocity_error [4] integral_windup_error [5] steering_state
 // [6] throttle_state.  traj = x[N], y[N], heading[N], speed[N].
-void trajectory_tracking(const Ego& v, const double* traj, int N, double dt, double* st, double* out3) {
+void trajectory_tracking(const SbVehicle& vp, const Ego& v, const double* traj, int N, double dt, double* st, double* out3) {
   const double* tx = traj;
   const double* ty = traj + N;
   const double* th = traj + 2 * N;
   const double* tv = traj + 3 * N;
-  const double final_steering_filter_constant = 23.5;
-  double throttle_filter_constant = 22.5;
-  const double velocity_gain = 5.1, velocity_integral_gain = 0, traction_gain = 6;
-  const double initial_look_ahead_distant = 6, derivative_activation = 1;
-  const bool speed_reduction = true;
-  const double velocity_damping_gain = 0.001, windup_gain = 0.01;
+  const double final_steering_filter_constant = vp.final_steering_filter_constant;
+  double throttle_filter_constant = vp.throttle_filter_constant;
+  const double velocity_gain = vp.velocity_gain, velocity_integral_gain = vp.velocity_integral_gain,
+               traction_gain = vp.traction_gain;
+  const double initial_look_ahead_distant = vp.initial_look_ahead_distant, derivative_activation = vp.derivative_activation;
+  const bool speed_reduction = vp.speed_reduction_activation != 0;
+  const double velocity_damping_gain = vp.velocity_damping_gain, windup_gain = vp.windup_gain;
 
   double lateral_gain = 0.61, heading_gain = 0.01, led_gain = 0.15, hed_gain = 0.5;
   double ns = clipd((3.6 * tv[0] - 20) / (80 - 20), 0, 1);
@@ -262,6 +251,11 @@ void trajectory_tracking(const Ego& v, const double* traj, int N, double dt, dou
 // below it, and a first-order steering joint; `substeps` explicit Euler sub-steps (240 Hz, smarts.py:607-615).
 // Body frame: x forward, y left, yaw counter-clockwise; delta = steering joint angle, left positive.
 void chassis_step(World& w, int ai, int vi) {
+  const SbVehicle& vp = w.veh;
+  const double kMaxSteeringWheel = vp.max_steering_wheel, kSteerLimit = vp.steer_limit, kMaxTorque = vp.max_torque,
+               kMaxBrakeTorque = vp.max_btorque, kWheelRadius = vp.wheel_radius, kEffMass = vp.eff_mass,
+               kRearAxleToCg = vp.axle_to_cg, kCornerStiffness = vp.corner_stiffness, kTyreForceMax = vp.tyre_force_max,
+               kMass = vp.mass, kIzz = vp.izz;
   const double* c = &w.last_control[(size_t)ai * 3];
   double target = -c[2] * kMaxSteeringWheel;  // chassis.py:790-793 (joint angle, left positive)
   target = clipd(target, -kSteerLimit, kSteerLimit);
@@ -485,7 +479,7 @@ void observe_lidar(World& w, int e, int a) {
         }
       }
       if (!ok || s0 > s1) continue;
-      double z0 = w.pos_z[vj] + (j < w.A ? 0.1 : 0.2);
+      double z0 = w.pos_z[vj] + (j < w.A ? w.veh.box_z0 : 0.2);
       lidar_entry(s0, s1, z0, z0 + w.height[vj], oz, q, &sbest);
     }
     if (w.cfg.lidar_wall_height > 0.0) {
@@ -1330,6 +1324,7 @@ extern "C" {
 void* or_create(const SbConfig* cfg, const SbMap* m, const double* base_rays, int n_rays) {
   World* w = new World();
   w->cfg = *cfg;
+  sb_vehicle(cfg->vehicle_type, &w->veh);
   Map& mp = w->map;
   mp.m = *m;
   cp(mp.road_lane_start, m->road_lane_start, m->n_roads);
@@ -1491,9 +1486,9 @@ void or_reset(void* h, const int32_t* env_ids, int n, const SbResetState* init) 
       w.heading[vi] = wrap_heading(init->agent_heading[src]);
       w.speed[vi] = init->agent_speed[src];
       w.yaw_rate[vi] = 0.0;
-      w.length[vi] = 3.68;
-      w.width[vi] = 1.47;
-      w.height[vi] = 1.0;
+      w.length[vi] = w.veh.length;
+      w.width[vi] = w.veh.width;
+      w.height[vi] = w.veh.height;
       sb_sincos(w.heading[vi], &w.sin_h[vi], &w.cos_h[vi]);
       w.alive[vi] = 1;
       w.steering[ai] = 0.0;
@@ -1587,13 +1582,13 @@ void or_step(void* h, const void* actions) {
         if (cmd == SB_LANE_SLOW_DOWN) ts = 0;
         else if (cmd == SB_LANE_CHANGE_LEFT) { ts = 12.5; lc = 1; }
         else if (cmd == SB_LANE_CHANGE_RIGHT) { ts = 12.5; lc = -1; }
-        w.status[ai] |= lane_following(w.map, v, route, w.route_len[ai], ts, lc, w.cfg.dt, st, out3);
+        w.status[ai] |= lane_following(w.map, w.veh, v, route, w.route_len[ai], ts, lc, w.cfg.dt, st, out3);
       } else if (as == SB_ACTION_LANE_WITH_CONTINUOUS_SPEED) {
         const double* ac = static_cast<const double*>(actions) + (size_t)ai * 2;
-        w.status[ai] |= lane_following(w.map, v, route, w.route_len[ai], ac[0], (int)ac[1], w.cfg.dt, st, out3);
+        w.status[ai] |= lane_following(w.map, w.veh, v, route, w.route_len[ai], ac[0], (int)ac[1], w.cfg.dt, st, out3);
       } else if (as == SB_ACTION_TRAJECTORY) {
         const int N = w.cfg.traj_len;
-        trajectory_tracking(v, static_cast<const double*>(actions) + (size_t)ai * 4 * N, N, w.cfg.dt, st, out3);
+        trajectory_tracking(w.veh, v, static_cast<const double*>(actions) + (size_t)ai * 4 * N, N, w.cfg.dt, st, out3);
       } else if (as == SB_ACTION_CONTINUOUS) {
         const double* ac = static_cast<const double*>(actions) + (size_t)ai * 3;
         apply_control(v, clipd(ac[0], 0, 1), clipd(ac[1], 0, 1), clipd(ac[2], -1, 1), out3);
@@ -1703,20 +1698,32 @@ void or_lane_probe(void* h, int lane, double x, double y, double off, double* ou
   out[5] = road_with_point(mp, x, y) ? 1.0 : 0.0;
 }
 
+void or_lateral_gains_v(int vehicle_type, double target_speed, double* heading_gain, double* lateral_gain) {
+  SbVehicle vp;
+  sb_vehicle(vehicle_type, &vp);
+  lateral_gains(target_speed, vp, heading_gain, lateral_gain);
+}
 void or_lateral_gains(double target_speed, double* heading_gain, double* lateral_gain) {
-  lateral_gains(target_speed, heading_gain, lateral_gain);
+  or_lateral_gains_v(SB_VEHICLE_SEDAN, target_speed, heading_gain, lateral_gain);
 }
 
 // one controller call on an explicit vehicle state (golden checks vs the reference controllers)
 uint32_t or_lane_following(void* h, const double* veh7, const int32_t* route, int route_len, double target_speed,
                            int lane_change, double dt, double* st, double* out3) {
   Ego v{veh7[0], veh7[1], veh7[2], veh7[3], veh7[4], veh7[5], veh7[6]};
-  return lane_following(static_cast<World*>(h)->map, v, route, route_len, target_speed, lane_change, dt, st, out3);
+  World& w = *static_cast<World*>(h);
+  return lane_following(w.map, w.veh, v, route, route_len, target_speed, lane_change, dt, st, out3);
 }
 
-void or_trajectory_tracking(const double* veh7, const double* traj, int N, double dt, double* st, double* out3) {
+void or_trajectory_tracking_v(int vehicle_type, const double* veh7, const double* traj, int N, double dt, double* st,
+                               double* out3) {
   Ego v{veh7[0], veh7[1], veh7[2], veh7[3], veh7[4], veh7[5], veh7[6]};
-  trajectory_tracking(v, traj, N, dt, st, out3);
+  SbVehicle vp;
+  sb_vehicle(vehicle_type, &vp);
+  trajectory_tracking(vp, v, traj, N, dt, st, out3);
+}
+void or_trajectory_tracking(const double* veh7, const double* traj, int N, double dt, double* st, double* out3) {
+  or_trajectory_tracking_v(SB_VEHICLE_SEDAN, veh7, traj, N, dt, st, out3);
 }
 
 void or_sincos(const double* x, int n, double* s, double* c) {

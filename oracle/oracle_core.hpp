@@ -29,6 +29,7 @@
 
 #include "../include/sb_detmath.h"
 #include "../include/sb_lidar_table.h"
+#include "../include/sb_vehicle.h"
 #include "../include/smarts_b200.h"
 
 namespace {
@@ -98,6 +99,7 @@ struct Waypoint {
 
 struct World {
   SbConfig cfg;
+  SbVehicle veh;  // the agents' vehicle type (include/sb_vehicle.h)
   Map map;
   long long dt_num = 1;  // the simulation clock after k ticks is sb_clock(k, dt_num, dt_den) (include/sb_detmath.h)
   double dt_den = 10.0;
@@ -513,13 +515,13 @@ double curvature_calculation(const double* tx, const double* ty, const double* t
 // it is evaluated with Ackermann's formula K = e_n^T C^-1 phi(A) (tests pin it to
 // scipy.signal.place_poles).  Constants: vehicle.length/2 = 1.84, chassis link mass 2356,
 // Izz 2681.95008628 (models/vehicle.urdf:18-22), ground contact stiffness 1e5 (models/plane.urdf:26).
-void lateral_gains(double ts, double* heading_gain, double* lateral_gain) {
+void lateral_gains(double ts, const SbVehicle& vp, double* heading_gain, double* lateral_gain) {
   if (!(ts > 0)) {
     *heading_gain = 0.01;
     *lateral_gain = 0.36;
     return;
   }
-  const double lh = 1.84, mass = 2356.0, iz = 2681.95008628, c = 100000.0;
+  const double lh = vp.half_len, mass = vp.link_mass, iz = vp.link_izz, c = vp.road_stiffness;
   double Am[4][4] = {{0, ts, 0, ts},
                      {0, 0, 1, 0},
                      {0, 0, -(2 * c * (lh * lh)) / (ts * iz), 0},

@@ -23,7 +23,7 @@ _LIB = None
 def build(force: bool = False) -> str:
     so = os.path.join(_HERE, "_build", "liboracle.so")
     srcs = [os.path.join(_HERE, f) for f in ("oracle.cpp", "oracle_core.hpp")] + [
-        os.path.join(_HERE, "..", "include", f) for f in ("smarts_b200.h", "sb_detmath.h", "sb_lidar_table.h")]
+        os.path.join(_HERE, "..", "include", f) for f in ("smarts_b200.h", "sb_detmath.h", "sb_lidar_table.h", "sb_vehicle.h")]
     stale = force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs)
     if stale:
         subprocess.check_call(["make", "-s", "-C", _HERE], stdout=subprocess.DEVNULL)
@@ -52,11 +52,14 @@ def lib():
         L.or_nearest_lane.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_double, C.POINTER(C.c_double)]
         L.or_lane_probe.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_double, C.POINTER(C.c_double)]
         L.or_lateral_gains.argtypes = [C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        L.or_lateral_gains_v.argtypes = [C.c_int, C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.or_lane_following.restype = C.c_uint32
         L.or_lane_following.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_int32), C.c_int,
                                         C.c_double, C.c_int, C.c_double, C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.or_trajectory_tracking.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_int, C.c_double,
                                              C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        L.or_trajectory_tracking_v.argtypes = [C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_int, C.c_double,
+                                               C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.or_sincos.argtypes = [C.POINTER(C.c_double), C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
         L.or_atan2.argtypes = [C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_int, C.POINTER(C.c_double)]
         _LIB = L
@@ -86,9 +89,9 @@ def det_atan2(y, x):
     return o
 
 
-def lateral_gains(ts: float):
+def lateral_gains(ts: float, vehicle_type: int = 0):
     a, b = C.c_double(), C.c_double()
-    lib().or_lateral_gains(ts, C.byref(a), C.byref(b))
+    lib().or_lateral_gains_v(vehicle_type, ts, C.byref(a), C.byref(b))
     return a.value, b.value
 
 
@@ -221,10 +224,10 @@ class OracleWorld:
         return out, st, status
 
 
-def trajectory_tracking(veh7, traj, dt, st):
+def trajectory_tracking(veh7, traj, dt, st, vehicle_type: int = 0):
     veh7 = np.ascontiguousarray(veh7, np.float64)
     traj = np.ascontiguousarray(traj, np.float64)
     st = np.ascontiguousarray(st, np.float64)
     out = np.zeros(3)
-    lib().or_trajectory_tracking(_dp(veh7), _dp(traj), traj.shape[1], dt, _dp(st), _dp(out))
+    lib().or_trajectory_tracking_v(vehicle_type, _dp(veh7), _dp(traj), traj.shape[1], dt, _dp(st), _dp(out))
     return out, st

@@ -6,7 +6,7 @@ from typing import Dict
 
 import numpy as np
 
-SB_ABI_VERSION = 6
+SB_ABI_VERSION = 7
 
 SB_ACTION_CONTINUOUS = 0
 SB_ACTION_LANE = 1
@@ -25,6 +25,7 @@ SB_STATUS_NO_WAYPOINTS = 2
 SB_STATUS_LIDAR_OVERFLOW = 4
 SB_STATUS_TTC_TRUNCATED = 8
 SB_STATUS_RW_TRUNCATED = 16
+SB_VEHICLE_SEDAN, SB_VEHICLE_BUS = 0, 1
 
 SB_EV_COLLISION, SB_EV_OFF_ROAD, SB_EV_OFF_ROUTE, SB_EV_ON_SHOULDER = 1, 2, 4, 8
 SB_EV_WRONG_WAY, SB_EV_NOT_MOVING, SB_EV_REACHED_GOAL, SB_EV_REACHED_MAX_STEPS = 16, 32, 64, 128
@@ -51,6 +52,7 @@ class SbConfig(C.Structure):
         ("accel_enable", _i32), ("via_cap", _i32), ("via_acquisition_range", _f64), ("via_speed_accuracy", _f64),
         ("ego_frame", _i32),
         ("rw_enable", _i32), ("rw_horizon", _i32), ("rw_lanes_cap", _i32), ("rw_paths_cap", _i32),
+        ("vehicle_type", _i32),
     ]
 
 

@@ -235,13 +235,12 @@ def compile_config(itf: AgentInterface, n_envs: int, n_agents: int, n_social: in
                                   f"(supported: {[a.name for a in _SUPPORTED_ACTIONS]})")
     if itf.rgb:
         raise NotImplementedError("RGB camera needs the Panda3D renderer: unavailable on this box (DESIGN.md 9)")
-    if itf.vehicle_type != "sedan":
-        raise NotImplementedError("only the sedan chassis parameters are built in")
     c = _abi.SbConfig()
     c.abi_version = _abi.SB_ABI_VERSION
     c.device = device
     c.n_envs, c.n_agents, c.n_social = n_envs, n_agents, n_social
     c.dt = dt
+    c.vehicle_type = {"sedan": _abi.SB_VEHICLE_SEDAN, "bus": _abi.SB_VEHICLE_BUS}[itf.vehicle_type]  # vehicle.py:393-398
     c.action_space = _SUPPORTED_ACTIONS[itf.action]
     c.traj_len = traj_len
     c.route_cap = route_cap

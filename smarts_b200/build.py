@@ -16,7 +16,7 @@ OUT = os.path.join(HERE, "libsmartsb200.so")
 SOURCES = ["sb_api.cu"]
 HOST_SOURCES = ["sb_hostxfer.cpp"]  # g++ (AVX-512 target attributes), linked into the same library
 DEPS = ["sb_api.cu", "sb_hostxfer.cpp", "sb_events.cuh", "sb_roadwp.cuh", "sb_ttc.cuh", "sb_extras.cuh", "sb_lidar.cuh", "sb_kernels.cuh", "sb_control.cuh", "sb_waypoints.cuh", "sb_device.cuh", "sb_raster.cuh",
-        os.path.join("..", "..", "include", "smarts_b200.h"), os.path.join("..", "..", "include", "sb_detmath.h"), os.path.join("..", "..", "include", "sb_lidar_table.h")]
+        os.path.join("..", "..", "include", "smarts_b200.h"), os.path.join("..", "..", "include", "sb_detmath.h"), os.path.join("..", "..", "include", "sb_lidar_table.h"), os.path.join("..", "..", "include", "sb_vehicle.h")]
 
 
 def nvcc_path() -> str:

@@ -152,9 +152,9 @@ __global__ void k_reset(DCfg c, DState s, DEvents ev, const int32_t* env_ids, in
     s.heading[vi] = h;
     s.speed[vi] = av[src];
     s.yaw_rate[vi] = 0.0;
-    s.length[vi] = 3.68;
-    s.width[vi] = 1.47;
-    s.height[vi] = 1.0;
+    s.length[vi] = c.veh.length;
+    s.width[vi] = c.veh.width;
+    s.height[vi] = c.veh.height;
     sb_sincos(h, &s.sin_h[vi], &s.cos_h[vi]);
     s.alive[vi] = 1;
     s.steering[ai] = 0.0;
@@ -306,6 +306,8 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
   d.accel_enable = c.accel_enable; d.via_cap = c.via_cap; d.via_range = c.via_acquisition_range;
   d.via_speed_acc = c.via_speed_accuracy;
   d.ego_frame = c.ego_frame;
+  if (c.vehicle_type != SB_VEHICLE_SEDAN && c.vehicle_type != SB_VEHICLE_BUS) return fail(h, SB_EINVAL, "vehicle_type must be SB_VEHICLE_SEDAN or SB_VEHICLE_BUS");
+  sb_vehicle(c.vehicle_type, &d.veh);
   d.rw_enable = c.rw_enable; d.rw_horizon = c.rw_horizon; d.rw_lanes_cap = c.rw_lanes_cap; d.rw_paths_cap = c.rw_paths_cap;
   d.env_list = nullptr;
   d.n_list = 0;

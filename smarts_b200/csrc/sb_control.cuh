@@ -8,20 +8,12 @@
 
 #include "sb_device.cuh"
 
-#define SB_MAX_STEERING_WHEEL (12.56 / 17.4)  // controller_parameters.yaml:23-25
-#define SB_STEER_LIMIT 0.8727                 // models/vehicle.urdf:101
-#define SB_WHEEL_RADIUS 0.31265
-#define SB_MAX_TORQUE 1600.0
-#define SB_MAX_BTORQUE 1400.0
-#define SB_EFF_MASS (2419.0 + 4.0 * 2.0 / (SB_WHEEL_RADIUS * SB_WHEEL_RADIUS))
-#define SB_REAR_AXLE_TO_CG 1.5
-// single-track model (DESIGN.md "Vehicle model"; the oracle's chassis_step holds the same constants)
-#define SB_MASS (2356.0 + 4.0 * 15.0)                                      // vehicle.urdf:19, :40
-#define SB_IZZ (2681.95008628 + 4.0 * 15.0 * (1.5 * 1.5 + 0.5 * 0.5))       // vehicle.urdf:21 + wheels as point masses
-#define SB_CORNER_STIFFNESS 100000.0                                        // N/rad per axle (plane.urdf:26)
-#define SB_TYRE_FORCE_MAX (3.0 * SB_MASS * 9.8 / 2.0)                       // per axle: plane.urdf:24, gravity 9.8
-#define SB_STEER_JOINT_GAIN 0.1                                             // POSITION_CONTROL default positionGain
-#define SB_DYN_SPEED 1.0                                                    // m/s: below it the tyres roll without slip
+#include "../../include/sb_vehicle.h"
+
+// Vehicle-type constants (sedan / bus) arrive in DCfg::veh, filled on the host by sb_vehicle() of include/sb_vehicle.h
+// -- the oracle holds the same record.
+#define SB_STEER_JOINT_GAIN 0.1  // POSITION_CONTROL default positionGain
+#define SB_DYN_SPEED 1.0         // m/s: below it the tyres roll without slip
 
 struct DEgo {
   double x, y, h, speed, yaw_rate, v_long, v_lat;
@@ -50,13 +42,13 @@ __device__ double d_curvature(const double* tx, const double* ty, const double* 
 }
 
 // lane_following_controller.py:376-437: single-input pole placement == Ackermann's formula.
-__device__ void d_lateral_gains(double ts, double* heading_gain, double* lateral_gain) {
+__device__ void d_lateral_gains(double ts, const SbVehicle& vp, double* heading_gain, double* lateral_gain) {
   if (!(ts > 0)) {
     *heading_gain = 0.01;
     *lateral_gain = 0.36;
     return;
   }
-  const double lh = 1.84, mass = 2356.0, iz = 2681.95008628, c = 100000.0;
+  const double lh = vp.half_len, mass = vp.link_mass, iz = vp.link_izz, c = vp.road_stiffness;
   double Am[4][4] = {{0, ts, 0, ts},
                      {0, 0, 1, 0},
                      {0, 0, -(2 * c * (lh * lh)) / (ts * iz), 0},
@@ -123,8 +115,9 @@ __device__ void d_lateral_gains(double ts, double* heading_gain, double* lateral
 }
 
 // lane_following_controller.py:105-361 once the waypoint path (x, y, heading; L points) is known.
-__device__ void d_lane_following_law(const DEgo& v, const double* wx, const double* wy, const double* wh, int L,
-                                     double target_speed, int lane_change, double dt, double* st, double* out3) {
+__device__ void d_lane_following_law(const DEgo& v, const SbVehicle& vp, const double* wx, const double* wy,
+                                     const double* wh, int L, double target_speed, int lane_change, double dt,
+                                     double* st, double* out3) {
   double ewma = 0.0;
   for (int i = L - 2; i >= 0; --i) ewma = d_lerp(ewma, d_degrees(fabs(d_wrap_heading(wh[i] - wh[i + 1]))), 0.03);
   double curv = d_clip(ewma / 2.5, 0, 1);
@@ -156,14 +149,14 @@ __device__ void d_lane_following_law(const DEgo& v, const double* wx, const doub
   double damping = (speed_error - st[4]) / dt;
   double lfc = 1.5;
   if (v.speed < 8 || target_speed < 6) lfc = 0;
-  raw += (-0.2 * damping - 0.1 * st[1]) + fabs(lfc * sb_sin(st[2] * SB_MAX_STEERING_WHEEL));
+  raw += (-0.2 * damping - 0.1 * st[1]) + fabs(lfc * sb_sin(st[2] * vp.max_steering_wheel));
   st[4] = speed_error;
   if (st[7] != 0.0) {
     double mx = v.x - st[5], my = v.y - st[6];
     if (sqrt(mx * mx + my * my) < 2) ref_h = wh[la];
   }
   double Kh, Kl;
-  d_lateral_gains(target_speed, &Kh, &Kl);
+  d_lateral_gains(target_speed, vp, &Kh, &Kl);
   double dvx, dvy;
   d_radians_to_vec(wh[la], &dvx, &dvy);
   double lat_err = d_signed_dist_to_line(lx, ly, wx[la], wy[la], dvx, dvy);
@@ -204,20 +197,22 @@ __device__ void d_lane_following_law(const DEgo& v, const double* wx, const doub
   d_apply_control(v, st[3], brake, st[2], out3);
 }
 
-// trajectory_tracking_controller.py:176-441 (sedan parameters, controller_parameters.yaml:3-16)
-__device__ void d_trajectory_tracking(const DEgo& v, const double* traj, int N, double dt, double* st, double* out3) {
+// trajectory_tracking_controller.py:176-441 (the vehicle type's control block of controller_parameters.yaml)
+__device__ void d_trajectory_tracking(const DEgo& v, const SbVehicle& vp, const double* traj, int N, double dt,
+                                      double* st, double* out3) {
   const double* tx = traj;
   const double* ty = traj + N;
   const double* th = traj + 2 * N;
   const double* tv = traj + 3 * N;
-  double throttle_filter_constant = 22.5;
+  double throttle_filter_constant = vp.throttle_filter_constant;
+  const bool speed_reduction = vp.speed_reduction_activation != 0;
   double lateral_gain = 0.61, heading_gain = 0.01, led_gain = 0.15, hed_gain = 0.5;
   double ns = d_clip((3.6 * tv[0] - 20) / (80 - 20), 0, 1);
   if (v.speed > 70 / 3.6) {
     lateral_gain = 1.51;
     hed_gain = 0.1;
   }
-  double steering_filter_constant = d_lerp(12, 23.5, ns);
+  double steering_filter_constant = d_lerp(12, vp.final_steering_filter_constant, ns);
   if (fabs(d_angdiff(th[N - 1], th[0])) > 2) throttle_filter_constant = 2.5;
   if (fabs(d_curvature(tx, ty, th, N, 0, 3)) < 150) {
     heading_gain = 0.05;
@@ -225,10 +220,10 @@ __device__ void d_trajectory_tracking(const DEgo& v, const double* traj, int N, 
     hed_gain = 0.05;
   }
   double heading_error = d_angdiff(sb_pymod(v.h, SB_TWO_PI), th[0]);
-  double look_dist = 6;
-  int look_pts = 6;
+  double look_dist = vp.initial_look_ahead_distant;
+  int look_pts = (int)vp.initial_look_ahead_distant;
   double ahead_curv = fabs(d_curvature(tx, ty, th, N, 4, 5));
-  if (ahead_curv < 30) {
+  if (ahead_curv < 30 && speed_reduction) {
     look_dist = 1;
     look_pts = 1;
   }
@@ -243,19 +238,22 @@ __device__ void d_trajectory_tracking(const DEgo& v, const double* traj, int N, 
   double derivative_term = hed_gain * v.yaw_rate + led_gain * (lateral_error - st[1]) / dt;
   double ff = 0.1 * (1 / Rc) * (v.speed * v.speed);
   double steering_raw =
-      d_clip(1 * derivative_term + d_degrees(heading_gain * heading_error) + 1 * lateral_gain * lateral_error - ff, -1, 1);
+      d_clip(vp.derivative_activation * derivative_term + d_degrees(heading_gain * heading_error) +
+                 1 * lateral_gain * lateral_error - ff,
+             -1, 1);
   st[5] = d_low_pass(steering_raw, st[5], steering_filter_constant, dt, -1.0, 0.0);
   double desired_speed = tv[N - 1];
-  if (ahead_curv < 30)
+  if (ahead_curv < 30 && speed_reduction)
     desired_speed = d_clip(0.8 * desired_speed, 0, 8.3);
-  else if (ahead_curv < 100)
+  else if (ahead_curv < 100 && speed_reduction)
     desired_speed *= 0.8;
   double velocity_error = v.speed - desired_speed;
   double ved = (velocity_error - st[2]) / dt;
-  double raw_throttle = 3.6 * (-0.5 * 5.1 * velocity_error - 0 * (st[3] + 0.01 * st[4]) - 0.001 * ved);
+  double raw_throttle = 3.6 * (-0.5 * vp.velocity_gain * velocity_error -
+                               vp.velocity_integral_gain * (st[3] + vp.windup_gain * st[4]) - vp.velocity_damping_gain * ved);
   st[2] = velocity_error;
   st[4] = d_clip(raw_throttle, -1, 1) - raw_throttle;
-  st[6] = d_low_pass(raw_throttle, st[6], throttle_filter_constant, dt, -1.0, -6 * fabs(v.v_lat));
+  st[6] = d_low_pass(raw_throttle, st[6], throttle_filter_constant, dt, -1.0, -vp.traction_gain * fabs(v.v_lat));
   double thr, brake;
   if (st[6] > 0) {
     brake = 0;
@@ -271,11 +269,11 @@ __device__ void d_trajectory_tracking(const DEgo& v, const double* traj, int N, 
 }
 
 // Kinematic stand-in for the Bullet AckermannChassis step (DESIGN.md "Vehicle model").
-__device__ void d_chassis_step(const DState& s, int ai, int vi, double dt, int substeps) {
+__device__ void d_chassis_step(const DState& s, const SbVehicle& vp, int ai, int vi, double dt, int substeps) {
   const double* c = &s.last_control[(size_t)ai * 3];
-  double target = -c[2] * SB_MAX_STEERING_WHEEL;  // joint angle, left positive (chassis.py:790-793)
-  target = d_clip(target, -SB_STEER_LIMIT, SB_STEER_LIMIT);
-  const double ax = 4.0 * (c[0] * SB_MAX_TORQUE - c[1] * SB_MAX_BTORQUE) / SB_WHEEL_RADIUS / SB_EFF_MASS;
+  double target = -c[2] * vp.max_steering_wheel;  // joint angle, left positive (chassis.py:790-793)
+  target = d_clip(target, -vp.steer_limit, vp.steer_limit);
+  const double ax = 4.0 * (c[0] * vp.max_torque - c[1] * vp.max_btorque) / vp.wheel_radius / vp.eff_mass;
   const double hdt = dt / (double)substeps;
   double x = s.pos_x[vi], y = s.pos_y[vi], h = s.heading[vi];
   double vx = s.v_long[ai], vy = -s.v_lat[ai], om = s.yaw_rate[vi], delta = -s.steering[ai];
@@ -284,16 +282,16 @@ __device__ void d_chassis_step(const DState& s, int ai, int vi, double dt, int s
     double sd, cd;
     sb_sincos(delta, &sd, &cd);
     if (vx > SB_DYN_SPEED) {
-      const double af = (vy + SB_REAR_AXLE_TO_CG * om) / vx - delta, ar = (vy - SB_REAR_AXLE_TO_CG * om) / vx;
-      const double fyf = d_clip(-SB_CORNER_STIFFNESS * af, -SB_TYRE_FORCE_MAX, SB_TYRE_FORCE_MAX) * cd;
-      const double fyr = d_clip(-SB_CORNER_STIFFNESS * ar, -SB_TYRE_FORCE_MAX, SB_TYRE_FORCE_MAX);
-      const double ay = (fyf + fyr) / SB_MASS - vx * om;
-      const double dom = (SB_REAR_AXLE_TO_CG * fyf - SB_REAR_AXLE_TO_CG * fyr) / SB_IZZ;
+      const double af = (vy + vp.axle_to_cg * om) / vx - delta, ar = (vy - vp.axle_to_cg * om) / vx;
+      const double fyf = d_clip(-vp.corner_stiffness * af, -vp.tyre_force_max, vp.tyre_force_max) * cd;
+      const double fyr = d_clip(-vp.corner_stiffness * ar, -vp.tyre_force_max, vp.tyre_force_max);
+      const double ay = (fyf + fyr) / vp.mass - vx * om;
+      const double dom = (vp.axle_to_cg * fyf - vp.axle_to_cg * fyr) / vp.izz;
       vy = vy + ay * hdt;
       om = om + dom * hdt;
     } else {  // rolling without slip
-      om = vx * (sd / cd) / (2.0 * SB_REAR_AXLE_TO_CG);
-      vy = om * SB_REAR_AXLE_TO_CG;
+      om = vx * (sd / cd) / (2.0 * vp.axle_to_cg);
+      vy = om * vp.axle_to_cg;
     }
     vx = vx + (ax + vy * om) * hdt;
     if (vx < 0) vx = 0;

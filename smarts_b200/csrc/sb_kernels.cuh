@@ -48,6 +48,7 @@ struct DCfg {
   double dagm_res;
   int32_t events_enable, max_steps, ttc_enable, accel_enable, via_cap, ego_frame;
   int32_t rw_enable, rw_horizon, rw_lanes_cap, rw_paths_cap;
+  SbVehicle veh;  // the agents' vehicle type (include/sb_vehicle.h)
   uint32_t done_mask;
   double nm_time, nm_dist, via_range, via_speed_acc;
   // sb_observe_envs: the envs the observation kernels work on (device array; nullptr = every env, in order)
@@ -188,9 +189,9 @@ k_control_law(DCfg c, DMap m, DState s, const void* __restrict__ actions, const 
     double ts;
     int lc;
     d_lane_action(c, actions, ai, &ts, &lc);
-    d_lane_following_law(v, pk.wx, pk.wy, pk.wh, pk.len, ts, lc, c.dt, st, out3);
+    d_lane_following_law(v, c.veh, pk.wx, pk.wy, pk.wh, pk.len, ts, lc, c.dt, st, out3);
   }
-  d_chassis_step(s, ai, vi, c.dt, c.substeps);
+  d_chassis_step(s, c.veh, ai, vi, c.dt, c.substeps);
 }
 
 __global__ void k_control_simple(DCfg c, DState s, const double* __restrict__ actions) {
@@ -205,7 +206,7 @@ __global__ void k_control_simple(DCfg c, DState s, const double* __restrict__ ac
     double traj[4 * SB_MAX_TRAJ];
     const double* src = actions + (size_t)ai * 4 * N;
     for (int i = 0; i < 4 * N; ++i) traj[i] = src[i];
-    d_trajectory_tracking(v, traj, N, c.dt, st, out3);
+    d_trajectory_tracking(v, c.veh, traj, N, c.dt, st, out3);
   } else if (c.action_space == SB_ACTION_CONTINUOUS) {  // controllers/__init__.py:94-99
     const double* ac = actions + (size_t)ai * 3;
     d_apply_control(v, d_clip(ac[0], 0, 1), d_clip(ac[1], 0, 1), d_clip(ac[2], -1, 1), out3);
@@ -215,7 +216,7 @@ __global__ void k_control_simple(DCfg c, DState s, const double* __restrict__ ac
     d_apply_control(v, d_clip(ac[0], 0, 1), d_clip(ac[1], 0, 1), steering, out3);
     st[0] = steering;
   }
-  d_chassis_step(s, ai, vi, c.dt, c.substeps);
+  d_chassis_step(s, c.veh, ai, vi, c.dt, c.substeps);
 }
 
 // --------------------------------------------------------------------------------- observe
@@ -287,7 +288,6 @@ __device__ int d_nearest_lane_warp(const DMap& m, double px, double py, double r
 
 // nearest_lane(vehicle position, radius = sedan length) of every alive vehicle slot, once per env instead of once
 // per (agent, neighbour) pair (sensors.py:243-266); warp per vehicle.
-#define SB_AGENT_LENGTH 3.68
 __global__ void __launch_bounds__(SB_OBS_WARPS * 32) k_vehicle_lanes(DCfg c, DMap m, DState s, int32_t* veh_lane) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int idx = blockIdx.x * SB_OBS_WARPS + warp;
@@ -295,7 +295,7 @@ __global__ void __launch_bounds__(SB_OBS_WARPS * 32) k_vehicle_lanes(DCfg c, DMa
   const int q = idx / c.V;
   const int vj = (c.env_list ? c.env_list[q] : q) * c.V + (idx - q * c.V);
   int nl = -1;
-  if (s.alive[vj]) nl = d_nearest_lane_warp(m, s.pos_x[vj], s.pos_y[vj], SB_AGENT_LENGTH, lane);
+  if (s.alive[vj]) nl = d_nearest_lane_warp(m, s.pos_x[vj], s.pos_y[vj], c.veh.length, lane);
   if (lane == 0) veh_lane[vj] = nl;
 }
 
@@ -356,7 +356,7 @@ k_observe(DCfg c, DMap m, DState s, DObs o, double* __restrict__ trip_wp, const 
       int vj = e * c.V + o.nbr_id[q];
       // the lane of a vehicle does not depend on who looks at it (the radius is the sedan's length for every
       // agent): k_vehicle_lanes has it when the env has fewer vehicles than neighbour slots to fill
-      int nl = (veh_lane && ego_len == SB_AGENT_LENGTH) ? veh_lane[vj]
+      int nl = (veh_lane && ego_len == c.veh.length) ? veh_lane[vj]
                                                         : d_nearest_lane_warp(m, s.pos_x[vj], s.pos_y[vj], ego_len, lane);
       if (lane == 0) {
         o.nbr_lane[q] = nl;

@@ -92,7 +92,7 @@ __device__ __forceinline__ void d_lidar_agent(const DCfg& c, const DMap& m, cons
     if (bx * bx + by * by > lim * lim) continue;
     const int k = atomicAdd(&n_boxes, 1);
     if (k < SB_LIDAR_MAX_BOXES) {
-      const double z0 = vz + (j < c.A ? 0.1 : 0.2);
+      const double z0 = vz + (j < c.A ? c.veh.box_z0 : 0.2);  // agents: URDF collision box; social: utils/bullet.py:169-177
       boxes[k] = LBox{vx, vy, vc, vs, 0.5 * vw, 0.5 * vl, z0, z0 + vhh};
     }
   }
@@ -348,7 +348,7 @@ k_lidar_tiles(DCfg c, DMap m, DState s, DObs o, LTable tab, float reach_xy, int 
     const double vw = s.width[vj], vl = s.length[vj], vhh = s.height[vj];
     if (!alive) continue;
     const int k = atomicAdd(&t.n_boxes, 1);  // V <= SB_LIDAR_MAX_BOXES on this path
-    const double z0 = vz + (j < c.A ? 0.1 : 0.2);
+    const double z0 = vz + (j < c.A ? c.veh.box_z0 : 0.2);  // agents: URDF collision box; social: utils/bullet.py:169-177
     t.boxes[k] = LBox{vx, vy, vc, vs, 0.5 * vw, 0.5 * vl, z0, z0 + vhh};
     t.box_slot[k] = (int16_t)j;
   }

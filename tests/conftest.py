@@ -34,7 +34,7 @@ def make_cfg(E=1, A=1, M=0, dt=0.1, action_space=_abi.SB_ACTION_LANE, traj_len=1
              lidar=False, lidar_miss_inf=0, wall=0.0, ogm=None, dagm=None, device=0, substeps=0,
              events=False, done_mask=None, max_episode_steps=0, not_moving_time=60.0, not_moving_distance=1.0,
              ttc=False, accel=False, via_cap=0, via_range=40.0, via_speed_accuracy=1.5, ego_frame=False,
-             rw=False, rw_horizon=20, rw_lanes=32, rw_paths=64):
+             rw=False, rw_horizon=20, rw_lanes=32, rw_paths=64, vehicle_type=0):
     c = _abi.SbConfig()
     c.abi_version = _abi.SB_ABI_VERSION
     c.device = device
@@ -62,6 +62,7 @@ def make_cfg(E=1, A=1, M=0, dt=0.1, action_space=_abi.SB_ACTION_LANE, traj_len=1
     c.via_cap, c.via_acquisition_range, c.via_speed_accuracy = via_cap, via_range, via_speed_accuracy
     c.ego_frame = int(ego_frame)
     c.rw_enable, c.rw_horizon, c.rw_lanes_cap, c.rw_paths_cap = int(rw), rw_horizon, rw_lanes, rw_paths
+    c.vehicle_type = vehicle_type
     return c
 
 

@@ -140,7 +140,7 @@ def gen_map_queries(name, rel, rng, n=60, tie_ranks=False, save_map=True):
     return rec, (rm, mine, routes)
 
 
-def gen_lane_controller(rm, mine, routes, rng, n_steps=40):
+def gen_lane_controller(rm, mine, routes, rng, n_steps=40, length=3.68, mass_and_inertia=(2356.0, 2681.95008628)):
     """Drive the reference LaneFollowingController closed-loop on a mock vehicle whose state is
     scripted (so no chassis is involved) and record inputs, state and outputs every tick."""
     from smarts.core.chassis import AckermannChassis
@@ -166,12 +166,12 @@ def gen_lane_controller(rm, mine, routes, rng, n_steps=40):
             vlat = float(rng.normal(0, 0.1))
             vehicle.chassis.longitudinal_lateral_speed = (speed, vlat)
             vehicle.chassis.velocity_vectors = (np.array([speed, vlat, 0.0]), np.array([0.0, 0.0, yaw]))
-            vehicle.chassis.mass_and_inertia = (2356.0, 2681.95008628)
+            vehicle.chassis.mass_and_inertia = mass_and_inertia
             vehicle.pose = make_pose(x, y, h)
             vehicle.position = vehicle.pose.position
             vehicle.heading = vehicle.pose.heading
             vehicle.speed = speed
-            vehicle.length = 3.68
+            vehicle.length = length
             vehicle.max_steering_wheel = 12.56 / 17.4
             out = {}
             vehicle.control = lambda throttle, brake, steering: out.update(t=throttle, b=brake, s=steering)
@@ -203,12 +203,12 @@ def gen_lane_controller(rm, mine, routes, rng, n_steps=40):
     return np.array(recs, np.float64)
 
 
-def gen_traj_controller(rng, n=200):
+def gen_traj_controller(rng, n=200, vehicle_type="sedan"):
     from smarts.core.controllers.trajectory_tracking_controller import (
         TrajectoryTrackingController, TrajectoryTrackingControllerState)
     import yaml
     with open(REF + "smarts/core/models/controller_parameters.yaml") as f:
-        params = yaml.safe_load(f)["sedan"]["control"]
+        params = yaml.safe_load(f)[vehicle_type]["control"]
     recs, trajs = [], []
     N = 10
     for i in range(n):
@@ -261,11 +261,10 @@ def gen_lidar_rays():
     return out
 
 
-def gen_gains():
+def gen_gains(lh=3.68 / 2, m=2356.0, iz=2681.95008628, c=100000.0):
     from scipy import signal
     speeds = np.array([0.5, 1.0, 1.9, 2.0, 2.02, 2.05, 2.1, 3.0, 5.0, 8.0, 12.5, 15.0, 20.0, 30.0])
     out = []
-    lh, m, iz, c = 3.68 / 2, 2356.0, 2681.95008628, 100000.0
     for v in speeds:
         A = np.array([[0, v, 0, v], [0, 0, 1, 0], [0, 0, -(2 * c * lh ** 2) / (v * iz), 0], [0, 0, -1, -2 * c / (m * v)]])
         B = np.array([[0], [0], [lh * c / iz], [c / (m * v)]])
