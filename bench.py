@@ -394,8 +394,8 @@ def measure_e2e(g, Ke, world, dist):
 
     def policy_host():
         if g.traj:
-            trajectory_from_obs_numpy({k: host_obs[k].numpy().reshape((E, A) + tuple(host_obs[k].shape[1:]))
-                                       for k in ("wp_len", "wp_pos", "wp_heading")}, act_host.numpy())
+            trajectory_from_obs_numpy({k: host_obs[k].numpy() for k in ("wp_len", "wp_pos", "wp_heading")},
+                                      act_host.numpy())
 
     def run(t_base):
         eng.step_host(act_host.numpy(), soc_host[t_base % g.T].numpy()); eng.copy_obs_to_host(host_obs, **copy_kw)  # warm

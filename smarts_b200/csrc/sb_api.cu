@@ -47,6 +47,7 @@ struct SbHandle_ {
   float ray_reach = 0.f;
   std::vector<void*> allocs;
   CtrlPick* d_picks = nullptr;  // k_control_paths -> k_control_law
+  int lidar_list_cap = SB_LIDAR_LIST;  // intervals a k_lidar_tiles block holds (SB_LIDAR_LIST_CAP lowers it: tests of the fallback path)
   double* d_edge_inv = nullptr;  // LTable::edge_inv (rebuilt when the map or the ray table changes)
   void* d_actions = nullptr;  // staging for sb_step_host
   size_t actions_cap = 0;
@@ -311,7 +312,9 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
   d.rw_enable = c.rw_enable; d.rw_horizon = c.rw_horizon; d.rw_lanes_cap = c.rw_lanes_cap; d.rw_paths_cap = c.rw_paths_cap;
   d.env_list = nullptr;
   d.n_list = 0;
-  d.a_magic = ((uint64_t)c.n_envs * c.n_agents * c.n_agents < (1ull << 32)) ? (uint32_t)((1ull << 32) / c.n_agents) + 1u : 0u;
+  // (A = 1: the magic number would be 2^32 + 1 and wrap to 1 -- every work item would land in env 0; plain division there)
+  d.a_magic = (c.n_agents >= 2 && (uint64_t)c.n_envs * c.n_agents * c.n_agents < (1ull << 32))
+                  ? (uint32_t)((1ull << 32) / c.n_agents) + 1u : 0u;
   if (c.via_cap < 0 || c.via_cap > SB_MAX_VIAS) return fail(h, SB_EINVAL, "via_cap out of range");
   if (c.via_cap > 0 && !(c.via_acquisition_range >= 0 && c.via_speed_accuracy >= 0))
     return fail(h, SB_EINVAL, "via range / speed accuracy must be >= 0");
@@ -457,6 +460,10 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
     if (!cuda_ok(h, cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->raster_smem),
                  "cudaFuncSetAttribute"))
       return SB_ECUDA;
+  }
+  if (const char* cap = getenv("SB_LIDAR_LIST_CAP")) {
+    const int v = atoi(cap);
+    if (v >= 0 && v < SB_LIDAR_LIST) h->lidar_list_cap = v;
   }
   if (c.lidar_enable &&
       !cuda_ok(h, cudaFuncSetAttribute((const void*)k_lidar_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -947,8 +954,13 @@ int sb_observe_envs(SbHandle h, const int32_t* env_ids, int32_t n, void* stream)
                                                                                           h->d_veh_lane);
       h->launches++;
     }
-    k_observe<<<(na + SB_OBS_WARPS - 1) / SB_OBS_WARPS, SB_OBS_WARPS * 32, 0, st>>>(c, h->dmap, h->st, h->ob,
-                                                                                    h->ev.trip_wp, h->ev.trip_init, h->d_veh_lane);
+    if (!c.wp_enable || c.wp_lookahead <= 32) {
+      k_observe<32><<<(na + SB_OBS_WARPS - 1) / SB_OBS_WARPS, SB_OBS_WARPS * 32, 0, st>>>(c, h->dmap, h->st, h->ob,
+                                                                                      h->ev.trip_wp, h->ev.trip_init, h->d_veh_lane);
+    } else {
+      k_observe<SB_MAX_LOOKAHEAD><<<(na + SB_OBS_WARPS - 1) / SB_OBS_WARPS, SB_OBS_WARPS * 32, 0, st>>>(c, h->dmap, h->st, h->ob,
+                                                                                      h->ev.trip_wp, h->ev.trip_init, h->d_veh_lane);
+    }
   }
   if (c.ttc_enable) {
     LaunchScope ls(h, SB_K_TTC, st);
@@ -969,7 +981,7 @@ int sb_observe_envs(SbHandle h, const int32_t* env_ids, int32_t n, void* stream)
       // several agents of an env per block: vehicles staged and (group, vehicle) reciprocals computed once
       const int tiles = (c.A + SB_LIDAR_TILE - 1) / SB_LIDAR_TILE;
       k_lidar_tiles<<<(env_ids ? n : c.E) * tiles, SB_LIDAR_THREADS, sizeof(LidarShared), st>>>(
-          c, h->dmap, h->st, h->ob, h->ray_table, h->ray_reach, tiles);
+          c, h->dmap, h->st, h->ob, h->ray_table, h->ray_reach, tiles, h->lidar_list_cap);
     } else {
       k_lidar<<<na, SB_LIDAR_THREADS, 0, st>>>(c, h->dmap, h->st, h->ob, h->ray_table, h->ray_reach);
     }

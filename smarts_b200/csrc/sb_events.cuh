@@ -166,7 +166,10 @@ __device__ __forceinline__ bool ev_boxes_touch(double ax, double ay, double ac, 
 
 #define SB_EV_WARPS 4
 
-__global__ void __launch_bounds__(SB_EV_WARPS * 32)
+#ifndef SB_EV_MIN_BLOCKS
+#define SB_EV_MIN_BLOCKS 10  // 48 registers: 0.110 -> 0.087 ms on the headline with events (8: 0.091, 12: 0.087), profiles/README.md r2y
+#endif
+__global__ void __launch_bounds__(SB_EV_WARPS * 32, SB_EV_MIN_BLOCKS)
 k_events(DCfg c, DMap m, DState s, DEvents ev, DEvOut o, int ticked) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   int e, a;

@@ -123,13 +123,18 @@ __device__ __forceinline__ void d_lane_action(const DCfg& c, const void* actions
   }
 }
 
-__global__ void __launch_bounds__(SB_CTRL_WARPS * 32)
+#ifndef SB_CTRL_MIN_BLOCKS
+#define SB_CTRL_MIN_BLOCKS 12  // 40 registers (92 B of spills): 48 resident warps hide the L1 / L2 latency of the path search; 1 -> 12: 0.107 -> 0.095 ms on the headline, 0.319 -> 0.272 ms on the full suite at 65 k agents (profiles/README.md r2y)
+#endif
+using CtrlWarpPaths = WarpPathsT<SB_CTRL_LOOKAHEAD>;  // 2.6 KB per warp instead of 7.4 KB
+
+__global__ void __launch_bounds__(SB_CTRL_WARPS * 32, SB_CTRL_MIN_BLOCKS)
 k_control_paths(DCfg c, DMap m, DState s, const void* __restrict__ actions, CtrlPick* __restrict__ picks) {
-  __shared__ WarpPaths wps[SB_CTRL_WARPS];
+  __shared__ CtrlWarpPaths wps[SB_CTRL_WARPS];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int ai = blockIdx.x * SB_CTRL_WARPS + warp;
   if (ai >= c.E * c.A) return;
-  WarpPaths* wp = &wps[warp];
+  CtrlWarpPaths* wp = &wps[warp];
   const int e = ai / c.A, a = ai - e * c.A, vi = e * c.V + a;
   const double vx = s.pos_x[vi], vy = s.pos_y[vi], vh = s.heading[vi];
   double ts;
@@ -300,9 +305,15 @@ __global__ void __launch_bounds__(SB_OBS_WARPS * 32) k_vehicle_lanes(DCfg c, DMa
 }
 
 
-__global__ void __launch_bounds__(SB_OBS_WARPS * 32)
+#ifndef SB_OBS_MIN_BLOCKS
+#define SB_OBS_MIN_BLOCKS 8  // 64 registers: 0.628 -> 0.567 ms on the full suite at 65 k agents (10: 0.569, 12: 0.654 -- spills), profiles/README.md r2y
+#endif
+// LA: the per-warp path record is sized for lookaheads up to LA (32 covers the Waypoints sensor's default; 64 the cap)
+template <int LA>
+__global__ void __launch_bounds__(SB_OBS_WARPS * 32, SB_OBS_MIN_BLOCKS)
 k_observe(DCfg c, DMap m, DState s, DObs o, double* __restrict__ trip_wp, const uint8_t* __restrict__ trip_init,
           const int32_t* __restrict__ veh_lane) {
+  using WarpPaths = WarpPathsT<LA>;
   __shared__ WarpPaths wps[SB_OBS_WARPS];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   int e, a;

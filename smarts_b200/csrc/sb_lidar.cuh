@@ -309,7 +309,7 @@ union LidarShared {
 static_assert(SB_LIDAR_TILE == 4, "the flattened item index of k_lidar_tiles is written out for four agents");
 
 __global__ void __launch_bounds__(SB_LIDAR_THREADS, 4)
-k_lidar_tiles(DCfg c, DMap m, DState s, DObs o, LTable tab, float reach_xy, int tiles_per_env) {
+k_lidar_tiles(DCfg c, DMap m, DState s, DObs o, LTable tab, float reach_xy, int tiles_per_env, int list_cap) {
   extern __shared__ __align__(16) unsigned char lidar_raw[];
   LidarShared* sh = reinterpret_cast<LidarShared*>(lidar_raw);
   LidarTile& t = sh->tile;
@@ -469,13 +469,13 @@ k_lidar_tiles(DCfg c, DMap m, DState s, DObs o, LTable tab, float reach_xy, int 
       en = LEntry{sw, sw, 0.0, c.lidar_wall_height};
     }
     const int idx = atomicAdd(&t.total, 1);
-    if (idx < SB_LIDAR_LIST) {
+    if (idx < list_cap) {
       t.entries[idx] = en;
       t.next[idx] = atomicExch(&t.head[al][g], idx);
     }
   }
   __syncthreads();
-  if (t.total > SB_LIDAR_LIST) {  // (uniform) too many intervals for the list: one agent at a time, chunked
+  if (t.total > list_cap) {  // (uniform) too many intervals for the list: one agent at a time, chunked
     __syncthreads();
     for (int al = 0; al < na; ++al) {
       d_lidar_agent(c, m, s, o, tab, reach_xy, e, a0 + al, &sh->one);

@@ -12,24 +12,27 @@
 #define SB_WP_CAND 64
 #define SB_LPG_RINGS 3  // lane-point grid: squares of up to 3 cells around the query before falling back to the table
 
-struct WarpPaths {
-  int32_t lp[SB_MAX_PATHS][SB_MAX_LOOKAHEAD + 1];  // lane-point indices of each path
+// LA = the longest lookahead the kernel asks for: the per-warp record is sized by it (the controller's 16-point query
+// needs 2.6 KB where the sensors' 64-point one needs 7.4 KB, and the record's size bounds the resident blocks)
+template <int LA>
+struct WarpPathsT {
+  int32_t lp[SB_MAX_PATHS][LA + 1];  // lane-point indices of each path
   int32_t len[SB_MAX_PATHS];
   int32_t n;         // paths stored
   int32_t total;     // paths found
   int32_t overflow;  // more than SB_MAX_PATHS
   int32_t jr[2];     // junction route of _resolve_in_junction
   // lane-level walk stack of wp_enumerate_chained (depth counts lanes, not lane points)
-  int32_t seg_first[SB_MAX_LOOKAHEAD + 1], seg_cnt[SB_MAX_LOOKAHEAD + 1], seg_before[SB_MAX_LOOKAHEAD + 1],
-      seg_cursor[SB_MAX_LOOKAHEAD + 1];
-  uint8_t seg_had[SB_MAX_LOOKAHEAD + 1];
+  int32_t seg_first[LA + 1], seg_cnt[LA + 1], seg_before[LA + 1], seg_cursor[LA + 1];
+  uint8_t seg_had[LA + 1];
   // candidate set of wp_closest_with_pose (lane points within a small disc around the nearest one)
   double cand_d[SB_WP_CAND];
   int32_t cand_i[SB_WP_CAND];
   // wp_equally_spaced_warp: arc length and heading-unwrap offset of the kept lane points, and their indices
-  double es_cum[SB_MAX_LOOKAHEAD + 1], es_acc[SB_MAX_LOOKAHEAD + 1];
-  int32_t es_kept[SB_MAX_LOOKAHEAD + 1];
+  double es_cum[LA + 1], es_acc[LA + 1];
+  int32_t es_kept[LA + 1];
 };
+using WarpPaths = WarpPathsT<SB_MAX_LOOKAHEAD>;
 
 struct DWaypoint {
   double x, y, heading, lane_width, speed_limit;
@@ -62,8 +65,9 @@ __device__ int wp_closest_in_range(const DMap& m, int start, int count, double x
 // compaction); when that set holds at least k points the k smallest are among them, and the ten
 // selection rounds run on <= 64 candidates instead of the whole table.  Otherwise (sparse or very
 // dense neighbourhood) the rounds scan the table, as before.  Same distances, same ties: same result.
+template <class WP>
 __device__ int wp_closest_with_pose(const DMap& m, double x, double y, double h, double within_radius, int lane,
-                                    WarpPaths* wp) {
+                                    WP* wp) {
   const int P = m.n_lanepoints;
   const int k = P < 10 ? P : 10;
   int my_idx = -1;
@@ -231,8 +235,9 @@ __device__ __forceinline__ bool wp_in_route(const int32_t* route, int n, int roa
 }
 
 // lanepoints.py:646-692 as a depth-first walk (lane 0 only).  Appends to wpaths.
+template <class WP>
 __device__ void wp_enumerate_paths(const DMap& m, int start, int lookahead, const int32_t* filt, int nf,
-                                   WarpPaths* wp) {
+                                   WP* wp) {
   int32_t node[SB_MAX_LOOKAHEAD + 1];
   int32_t cursor[SB_MAX_LOOKAHEAD + 1];
   uint8_t had_child[SB_MAX_LOOKAHEAD + 1];
@@ -308,8 +313,9 @@ __device__ __forceinline__ bool wp_lane_ok(const DMap& m, const int32_t* filt, i
 // LANE (2-4 steps for a 16 m lookahead) instead of per lane point.  Leaf order and leaf rule are
 // those of the point-level walk above.  Executed by the whole warp uniformly; the lanes share
 // the work of writing a path out.
+template <class WP>
 __device__ void wp_enumerate_chained(const DMap& m, int start, int lookahead, const int32_t* filt, int nf,
-                                     WarpPaths* wp, int lane) {
+                                     WP* wp, int lane) {
   int n = wp->n, total = wp->total, overflow = wp->overflow;
   const int need = lookahead + 1;
   int d = 0;
@@ -406,8 +412,9 @@ __device__ int wp_closest_per_lane(const DMap& m, int road, double x, double y, 
 
 // Lane._waypoint_paths_at for every lane of `road` (sumo_road_network.py:429-446, :838-839, :880-881).
 // `per_lane`: closest lane point of each lane when the caller has already scanned this road, else null.
+template <class WP>
 __device__ void wp_paths_on_road(const DMap& m, int road, double x, double y, int lookahead, const int32_t* filt,
-                                 int nf, WarpPaths* wp, int lane, const int32_t* per_lane = nullptr) {
+                                 int nf, WP* wp, int lane, const int32_t* per_lane = nullptr) {
   int l0 = m.road_lane_start[road], l1 = l0 + m.road_lane_count[road];
   for (int l = l0; l < l1; ++l) {
     int cnt = m.lane_lp_count[l];
@@ -424,8 +431,9 @@ __device__ void wp_paths_on_road(const DMap& m, int road, double x, double y, in
 
 // RoadMap.waypoint_paths: fills wp (shared memory, one per warp).  route_len < 0: no route
 // object; == 0: empty Route (-> _resolve_in_junction).
+template <class WP>
 __device__ void wp_waypoint_paths(const DMap& m, double x, double y, double h, int lookahead, double within_radius,
-                                  const int32_t* route, int route_len, WarpPaths* wp, int lane) {
+                                  const int32_t* route, int route_len, WP* wp, int lane) {
   if (lane == 0) {
     wp->n = 0;
     wp->total = 0;
@@ -523,7 +531,8 @@ __device__ void wp_waypoint_paths(const DMap& m, double x, double y, double h, i
 }
 
 // rank of path k after sorted(paths, key=first waypoint's lane_index) (stable)
-__device__ __forceinline__ int wp_rank(const DMap& m, const WarpPaths* wp, int k) {
+template <class WP>
+__device__ __forceinline__ int wp_rank(const DMap& m, const WP* wp, int k) {
   int key = m.lane_idx_in_road[m.lp_lane[wp->lp[k][0]]];
   int rank = 0;
   for (int j = 0; j < wp->n; ++j) {
@@ -580,9 +589,9 @@ __device__ void wp_first_point(const DMap& m, const int32_t* path, int n, double
 //   * j  (last kept point with cum[j] <= s) and jd (last with cum[jd] < s, else 0) do not depend on
 //     the previous waypoint because cum and s are both non-decreasing;
 //   * rh[i] = lp_heading + acc[i] is formed where it is used (same single addition).
-template <class Emit>
+template <class Emit, class WP>
 __device__ int wp_equally_spaced_warp(const DMap& m, const int32_t* path, int n, double vx, double vy, int n_out,
-                                      Emit emit, WarpPaths* wp, int lane) {
+                                      Emit emit, WP* wp, int lane) {
   double* cum = wp->es_cum;
   double* acc = wp->es_acc;
   int32_t* kept = wp->es_kept;

@@ -765,3 +765,19 @@ def test_host_buffer_copy_orders_itself_after_a_side_stream():
     want = ora.obs()
     assert_same({k: bufs[k].numpy() for k in want}, want)
     eng.close()
+
+
+@pytest.mark.parametrize("A,cap", [(6, None), (5, "8"), (1, None)])
+def test_lidar_tile_remainders_and_list_overflow_fallback(A, cap, monkeypatch):
+    """k_lidar_tiles casts for four agents of an env per block: A = 6 leaves a tile of two, A = 5 a tile of one; with the
+    block's interval list capped at 8 entries (SB_LIDAR_LIST_CAP, read at sb_create) every tile overflows and falls back
+    to the one-agent chunked cast; A = 1 takes the one-agent kernel outright.  All bit-identical to the oracle."""
+    if cap is not None:
+        monkeypatch.setenv("SB_LIDAR_LIST_CAP", cap)
+    rm = load_map("4lane")
+    E, M = 5, 18
+    missions = (MISSIONS_4LANE + MISSIONS_4LANE)[:A]
+    cfg = make_cfg(E=E, A=A, M=M, lidar=True, lidar_miss_inf=1, wall=1.5, route_cap=16)
+    eng, ora = run_pair(rm, cfg, missions, ticks=16, seed=41 + A, action_fn=lane_actions(E, A, 3), check_every=4, jitter=30.0)
+    assert 0 < ora.obs()["lidar_hits"].mean() < 1
+    eng.close()
