@@ -47,6 +47,7 @@ struct SbHandle_ {
   float ray_reach = 0.f;
   std::vector<void*> allocs;
   CtrlPick* d_picks = nullptr;  // k_control_paths -> k_control_law
+  int lidar_tile_min_agents = 2;      // agents per env from which k_lidar_tiles is used (SB_LIDAR_TILE_MIN_A: A/B runs)
   int lidar_list_cap = SB_LIDAR_LIST;  // intervals a k_lidar_tiles block holds (SB_LIDAR_LIST_CAP lowers it: tests of the fallback path)
   double* d_edge_inv = nullptr;  // LTable::edge_inv (rebuilt when the map or the ray table changes)
   void* d_actions = nullptr;  // staging for sb_step_host
@@ -461,6 +462,7 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
                  "cudaFuncSetAttribute"))
       return SB_ECUDA;
   }
+  if (const char* ma = getenv("SB_LIDAR_TILE_MIN_A")) h->lidar_tile_min_agents = atoi(ma);
   if (const char* cap = getenv("SB_LIDAR_LIST_CAP")) {
     const int v = atoi(cap);
     if (v >= 0 && v < SB_LIDAR_LIST) h->lidar_list_cap = v;
@@ -977,7 +979,7 @@ int sb_observe_envs(SbHandle h, const int32_t* env_ids, int32_t n, void* stream)
   if (c.lidar_enable) {
     LaunchScope ls(h, SB_K_LIDAR, st);
     const int G = h->ray_table.n_groups;
-    if (c.A >= 2 && c.V <= SB_LIDAR_MAX_BOXES && G <= SB_LIDAR_MAX_GROUPS && G * c.V <= SB_LIDAR_RECIP) {
+    if (c.A >= h->lidar_tile_min_agents && c.V <= SB_LIDAR_MAX_BOXES && G <= SB_LIDAR_MAX_GROUPS && G * c.V <= SB_LIDAR_RECIP) {
       // several agents of an env per block: vehicles staged and (group, vehicle) reciprocals computed once
       const int tiles = (c.A + SB_LIDAR_TILE - 1) / SB_LIDAR_TILE;
       k_lidar_tiles<<<(env_ids ? n : c.E) * tiles, SB_LIDAR_THREADS, sizeof(LidarShared), st>>>(

@@ -161,3 +161,43 @@ def test_lane_following_envelope_gpu(turn, run):
                         obs=lambda w: w.obs_numpy(), state=lambda w: w.state_numpy())
     check_lane_envelope(*out, f"map{turn}/{run[0]}")
     eng.close()
+
+
+# ---------------------------------------------------------------------------------------- steering direction
+def steering_direction(world, to_dev=lambda a: a, state=lambda w: w.state()):
+    """smarts/core/tests/test_dynamics_backend.py:53-66: a chassis at rest, 100 Bullet steps (240 Hz) per phase -- here
+    5 ticks of 0.1 s = 120 sub-steps -- with steering 0, then +1, then -1 (throttle and brake 0): the steering value
+    read back is 0, then positive (a right turn), then negative."""
+    z = np.zeros((1, 1))
+    world.reset(z, z, z + math.pi * 0.5, z)
+    out = []
+    for steering in (0.0, 1.0, -1.0):
+        act = np.zeros((1, 1, 3))
+        act[..., 2] = steering
+        for _ in range(5):
+            world.step(to_dev(act))
+        out.append(float(state(world)["steering"][0, 0]))
+    return out
+
+
+def check_steering(s):
+    assert math.isclose(s[0], 0, rel_tol=1e-2, abs_tol=1e-12)
+    assert s[1] > 0 and s[2] < 0
+    # the joint settles on the commanded angle: steering * max_steering / steering_gear_ratio (chassis.py:790-793)
+    assert math.isclose(s[1], 12.56 / 17.4, rel_tol=1e-3) and math.isclose(s[2], -12.56 / 17.4, rel_tol=1e-2)
+
+
+def test_steering_direction_oracle():
+    cfg = make_cfg(E=1, A=1, action_space=_abi.SB_ACTION_CONTINUOUS)
+    check_steering(steering_direction(oracle_world(load_map("straight"), cfg)))
+
+
+@pytest.mark.gpu
+def test_steering_direction_gpu():
+    import torch
+    from smarts_b200 import lidar_params
+    from smarts_b200.engine import Engine
+    cfg = make_cfg(E=1, A=1, action_space=_abi.SB_ACTION_CONTINUOUS)
+    eng = Engine(cfg, load_map("straight"), lidar_params.base_rays(lidar_params.BasicLidar))
+    check_steering(steering_direction(eng, to_dev=lambda a: torch.from_numpy(a).cuda(), state=lambda w: w.state_numpy()))
+    eng.close()
