@@ -38,7 +38,12 @@
 #define SB_RASTER_BLOCKS 4  // resident blocks per SM the register budget is set for
 #endif
 #define SB_RASTER_SLICE_ROUND 32  // ... per round of a slice of k_raster_slices (small grids: four staging areas per block)
+#ifndef SB_RASTER_SMALL_ROWS
 #define SB_RASTER_SMALL_ROWS 64  // polygons up to this many rows go warp-per-polygon, taller ones row-per-thread
+#endif
+#ifndef SB_RASTER_STORE_UNROLL
+#define SB_RASTER_STORE_UNROLL 4  // steps of the bit -> byte store loop in flight
+#endif
 #define SB_RASTER_CLAMP 16777216.0        // 2^24 units = 65536 px
 #define SB_RASTER_FAST_LIMIT 536870912.0  // 2^29
 
@@ -330,7 +335,8 @@ __device__ __forceinline__ void d_store_rows(const uint32_t* bits, const uint2* 
     const int dsrc = (T >> sh) * stride;
     uint8_t* p = dst + (size_t)tid * 32;
     const int iters = n_words / T;
-#pragma unroll 4
+    constexpr int kStoreUnroll = SB_RASTER_STORE_UNROLL;
+#pragma unroll kStoreUnroll
     for (int k = 0; k < iters; ++k) {
       const uint32_t word = src[k * dsrc];
       uint8_t* q = p + (size_t)k * (T * 32);
