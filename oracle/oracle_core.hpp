@@ -324,6 +324,8 @@ int equally_spaced_path(const Map& mp, const int32_t* path, int n, double vx, do
   double rx[SB_MAX_LOOKAHEAD + 1], ry[SB_MAX_LOOKAHEAD + 1], rh[SB_MAX_LOOKAHEAD + 1], rw[SB_MAX_LOOKAHEAD + 1],
       rs[SB_MAX_LOOKAHEAD + 1];
   int32_t rlane[SB_MAX_LOOKAHEAD + 1];
+  if (n <= 0) return 0;
+  rh[0] = 0.0;  // (n >= 1 keeps path[0]; this only tells the compiler so)
   int m = 0;
   for (int i = 0; i < n; ++i) {
     int lp = path[i];
