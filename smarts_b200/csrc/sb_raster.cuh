@@ -32,10 +32,12 @@
 
 #define SB_RASTER_THREADS 256
 #ifndef SB_RASTER_ROUND
-#define SB_RASTER_ROUND 64  // polygons staged per round: one round in the common case
+#define SB_RASTER_ROUND 48  // polygons staged per round (with 5 blocks / SM: 32 / 40 / 48 / 56 / 64 -> 0.383 / 0.380 / 0.380 / 0.379 / 0.385 ms)
 #endif
 #ifndef SB_RASTER_BLOCKS
-#define SB_RASTER_BLOCKS 4  // resident blocks per SM the register budget is set for
+#define SB_RASTER_BLOCKS 5  // resident blocks per SM the register budget is set for: 48 registers, 32 B of spills; a block's life
+                           // is a latency chain (cull -> stage -> spans -> stores), so the SM wants many of them: 3 / 4 / 5 / 6
+                           // blocks -> 0.442 / 0.394 / 0.380 / 0.395 ms (6 needs 40 registers: 72 B of spills)
 #endif
 #define SB_RASTER_SLICE_ROUND 32  // ... per round of a slice of k_raster_slices (small grids: four staging areas per block)
 #ifndef SB_RASTER_SMALL_ROWS
@@ -504,8 +506,11 @@ k_raster(DCfg c, DMap m, DState s, DObs o, RasterDims g) {
 // ... or 256 / T agents per block, each rasterised by its own slice of T = 32 / 64 / 128 threads (T >= rows) with
 // its own staging area, bit images and named barrier: a 64 x 64 grid is 4 KB of output, and a block per agent
 // would leave three quarters of its threads without a row and the SM without enough stores in flight.
+#ifndef SB_RASTER_SLICE_BLOCKS
+#define SB_RASTER_SLICE_BLOCKS 4  // 64 registers (5 blocks at 48: 0.437 -> 0.452 ms on the full suite, 6 at 40: 0.508)
+#endif
 template <int T>
-__global__ void __launch_bounds__(SB_RASTER_THREADS)
+__global__ void __launch_bounds__(SB_RASTER_THREADS, SB_RASTER_SLICE_BLOCKS)
 k_raster_slices(DCfg c, DMap m, DState s, DObs o, RasterDims g, int n_work) {
   extern __shared__ __align__(16) unsigned char smem[];
   __shared__ RasterJob sjob[SB_RASTER_THREADS / T];
