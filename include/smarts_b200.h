@@ -350,6 +350,42 @@ int sb_set_incremental_host_grids(SbHandle h, int on);
  * pay for it.  Every other member as in sb_copy_obs_to_host.  (Replaces the np.array(...) conversions of
  * smarts/core/sensors.py:706-716, :748-758 on the delivery side.) */
 int sb_copy_obs_to_host_packed(SbHandle h, const SbObsPtrs *host_dst);
+/* The grid half of sb_copy_obs_to_host_packed for callers that cannot allocate.  (No counterpart in the
+ * reference: it is Python and never meets the problem.)
+ *
+ * sb_copy_obs_to_host_packed sizes its device bit image with cudaMalloc and its pinned staging with
+ * cudaHostAlloc on first use, and again whenever the grids grow.  That is no use to
+ *   - a trainer whose memory pool was handed all of HBM at start-up (cudaMalloc then answers out-of-memory),
+ *   - a control loop that must not stall: cudaMalloc / cudaFree synchronise the whole device,
+ *   - a thread that runs while another thread of the process has a stream capture open in the global capture mode,
+ *     where cudaMalloc is an error,
+ *   - an embedding that audits allocations and forbids them after initialisation.
+ * This call performs no cudaMalloc, cudaFree, cudaHostAlloc or any other allocating CUDA / library routine, on its
+ * first call or later.  Its scratch is a 256-byte-aligned `static __device__` array of SB_NOALLOC_BITS_MAX_BYTES
+ * (16 MiB) that is part of the library image: every GPU that loads libsmartsb200.so holds those 16 MiB until the
+ * process exits, whether or not this entry point is ever called.
+ *
+ * Inputs: the handle's ogm / dagm device images as the last sb_observe left them.  Outputs: host_ogm_bits /
+ * host_dagm_bits (HOST pointers, pinned or pageable; NULL skips that grid), E*A*H*W/8 bytes each, in exactly the bit
+ * layout sb_copy_obs_to_host_packed documents.  The call waits for the stream of the last sb_set_social / sb_step /
+ * sb_observe, works on the legacy default stream and returns after the host buffers are complete.
+ *
+ * Limit: the bit images of the requested grids together must fit the array: E*A*(ogm W*H + dagm W*H)/8 <=
+ * SB_NOALLOC_BITS_MAX_BYTES (e.g. 1024 agents with two 256 x 256 grids, or 16 384 agents with two 64 x 64 grids).
+ * Anything larger returns SB_EINVAL with the two numbers in sb_last_error; nothing is launched.  W*H must be a
+ * multiple of 32 as for the packed call.
+ *
+ * First call on a device: the library asks the runtime once for the device address of the array
+ * (cudaGetSymbolAddress with that device current; the host-side name of a __device__ array is not a device
+ * pointer).  Make that first call before opening any stream capture.
+ *
+ * Sharing: every handle on the same GPU uses the same array, and it keeps what the last call wrote.  Nothing has to
+ * start at zero -- the kernel overwrites every word that is copied out afterwards -- so nothing is cleared.  Two
+ * calls whose GPU work overlaps (two host threads, two handles on one GPU) race on the array and deliver garbage;
+ * serialise them.  sb_set_timing does not see this call's kernel (timing events are created on demand, which
+ * allocates); sb_launch_count does. */
+#define SB_NOALLOC_BITS_MAX_BYTES (16u << 20)
+int sb_copy_grids_to_host_packed_noalloc(SbHandle h, uint8_t *host_ogm_bits, uint8_t *host_dagm_bits);
 int sb_get_obs(SbHandle h, SbObsPtrs *out);
 int sb_get_state(SbHandle h, SbStatePtrs *out);
 /* number of kernel launches issued by this handle so far (bench gpu_launches) */

@@ -7,6 +7,8 @@ from typing import Dict
 import numpy as np
 
 SB_ABI_VERSION = 7
+SB_OK, SB_EINVAL, SB_ECUDA, SB_ESTATE, SB_ENOMEM = 0, -1, -2, -3, -4
+SB_NOALLOC_BITS_MAX_BYTES = 16 << 20  # static device staging of sb_copy_grids_to_host_packed_noalloc
 
 SB_ACTION_CONTINUOUS = 0
 SB_ACTION_LANE = 1

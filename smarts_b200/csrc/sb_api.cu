@@ -1330,3 +1330,85 @@ int sb_get_state(SbHandle h, SbStatePtrs* out) {
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------
+// sb_copy_grids_to_host_packed_noalloc: packed grid delivery for callers that must not allocate (smarts_b200.h).
+// The bit image lives in a file-scope device array instead of the cudaMalloc'ed SbHandle_::d_bits.
+// ---------------------------------------------------------------------------------------------------------------
+#include <mutex>
+
+// 16 MiB of every GPU that loads this library, for the life of the process.  In host code this NAME is only a handle
+// for the runtime's symbol table: a kernel launched with it as an argument would read or write host memory (or
+// fault).  The device address comes from cudaGetSymbolAddress, below.
+static __device__ __align__(256) uint32_t g_noalloc_bits[SB_NOALLOC_BITS_MAX_BYTES / sizeof(uint32_t)];
+
+namespace {
+
+constexpr int kNoallocMaxDevices = 64;
+std::mutex g_noalloc_mu;
+uint32_t* g_noalloc_dev_ptr[kNoallocMaxDevices] = {};  // device address of g_noalloc_bits on each GPU, once known
+
+// `device` must be the current device: a __device__ array exists once per GPU and the runtime resolves the symbol
+// for whichever one is current.
+cudaError_t noalloc_bits_address(int device, uint32_t** out) {
+  if (device < 0 || device >= kNoallocMaxDevices) return cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (!g_noalloc_dev_ptr[device]) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_bits);
+    if (e != cudaSuccess) return e;
+    g_noalloc_dev_ptr[device] = static_cast<uint32_t*>(p);
+  }
+  *out = g_noalloc_dev_ptr[device];
+  return cudaSuccess;
+}
+
+// k_pack_bits for up to two grids in one launch: words [0, n0) pack src0, words [n0, n0 + n1) pack src1, each word
+// written exactly once (so whatever an earlier call left in `bits` never reaches the host).
+__global__ void __launch_bounds__(256) k_pack_bits_noalloc(const uint8_t* __restrict__ src0, size_t n0,
+                                                           const uint8_t* __restrict__ src1, size_t n1,
+                                                           uint32_t* __restrict__ bits) {
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n0 + n1) return;
+  const uint4* p = t < n0 ? reinterpret_cast<const uint4*>(src0) + t * 2 : reinterpret_cast<const uint4*>(src1) + (t - n0) * 2;
+  const uint4 a = __ldcs(p), b = __ldcs(p + 1);
+  auto nib = [](uint32_t w) { return ((w & 0x01010101u) * 0x01020408u) >> 24; };
+  bits[t] = nib(a.x) | (nib(a.y) << 4) | (nib(a.z) << 8) | (nib(a.w) << 12) | (nib(b.x) << 16) | (nib(b.y) << 20) |
+            (nib(b.z) << 24) | (nib(b.w) << 28);
+}
+
+}  // namespace
+
+extern "C" int sb_copy_grids_to_host_packed_noalloc(SbHandle h, uint8_t* host_ogm_bits, uint8_t* host_dagm_bits) {
+  if (!h) return SB_EINVAL;
+  if (h->cuda_err) return SB_ECUDA;
+  const SbConfig& c = h->cfg;
+  const size_t na = (size_t)c.n_envs * c.n_agents;
+  const bool want0 = host_ogm_bits != nullptr, want1 = host_dagm_bits != nullptr;
+  if (!want0 && !want1) return fail(h, SB_EINVAL, "sb_copy_grids_to_host_packed_noalloc: both destinations are NULL");
+  if ((want0 && !c.ogm_enable) || (want1 && !c.dagm_enable))
+    return fail(h, SB_EINVAL, "sb_copy_grids_to_host_packed_noalloc: a destination was given for a grid the config does not enable");
+  const size_t px0 = want0 ? (size_t)c.ogm_width * c.ogm_height : 0, px1 = want1 ? (size_t)c.dagm_width * c.dagm_height : 0;
+  if (px0 % 32 || px1 % 32)
+    return fail(h, SB_EINVAL, "packed delivery needs width * height to be a multiple of 32");
+  const size_t words0 = na * px0 / 32, words1 = na * px1 / 32, need = (words0 + words1) * 4;
+  if (need > (size_t)SB_NOALLOC_BITS_MAX_BYTES)
+    return fail(h, SB_EINVAL, "sb_copy_grids_to_host_packed_noalloc: the bit images need " + std::to_string(need) +
+                              " bytes, the static staging array holds " + std::to_string((size_t)SB_NOALLOC_BITS_MAX_BYTES) +
+                              " (SB_NOALLOC_BITS_MAX_BYTES); use sb_copy_obs_to_host_packed, which allocates");
+  DeviceGuard dg(c.device);
+  if (!dg.ok) return fail(h, SB_ECUDA, "cudaSetDevice failed");
+  uint32_t* bits = nullptr;  // first call on this device: resolves the array's device address (before any capture)
+  if (!cuda_ok(h, noalloc_bits_address(c.device, &bits), "cudaGetSymbolAddress(g_noalloc_bits)")) return SB_ECUDA;
+  // the grids may have been written on another (non-blocking) stream: wait for it, as sb_copy_obs_to_host does
+  if (h->last_stream && cudaStreamSynchronize(h->last_stream) != cudaSuccess) cudaGetLastError();
+  h->launches++;
+  k_pack_bits_noalloc<<<(unsigned)((words0 + words1 + 255) / 256), 256>>>(h->ob.ogm, words0, h->ob.dagm, words1, bits);
+  if (!cuda_ok(h, cudaGetLastError(), "k_pack_bits_noalloc")) return SB_ECUDA;
+  const uint8_t* src = reinterpret_cast<const uint8_t*>(bits);
+  if (want0 && !cuda_ok(h, cudaMemcpyAsync(host_ogm_bits, src, words0 * 4, cudaMemcpyDeviceToHost, 0), "D2H ogm bits"))
+    return SB_ECUDA;
+  if (want1 && !cuda_ok(h, cudaMemcpyAsync(host_dagm_bits, src + words0 * 4, words1 * 4, cudaMemcpyDeviceToHost, 0), "D2H dagm bits"))
+    return SB_ECUDA;
+  return cuda_ok(h, cudaStreamSynchronize(0), "sb_copy_grids_to_host_packed_noalloc sync") ? SB_OK : SB_ECUDA;
+}

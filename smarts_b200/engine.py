@@ -23,7 +23,7 @@ EXPORTS = [
     "sb_abi_version", "sb_create", "sb_destroy", "sb_upload_map", "sb_upload_lidar_rays", "sb_reset",
     "sb_set_social", "sb_step", "sb_observe", "sb_observe_envs", "sb_step_host", "sb_copy_obs_to_host", "sb_get_obs",
     "sb_get_state", "sb_launch_count", "sb_last_error", "sb_set_timing", "sb_collect_timing",
-    "sb_set_incremental_host_grids", "sb_copy_obs_to_host_packed",
+    "sb_set_incremental_host_grids", "sb_copy_obs_to_host_packed", "sb_copy_grids_to_host_packed_noalloc",
 ]
 KERNEL_KINDS = ["k_set_social", "k_control", "k_observe", "k_lidar", "k_raster", "k_events", "k_pack_bits", "k_ttc", "k_extras", "k_ego_frame", "k_road_waypoints"]
 
@@ -59,6 +59,8 @@ def load_library(path: Optional[str] = None):
     L.sb_copy_obs_to_host.argtypes = [H, C.POINTER(_abi.SbObsPtrs)]
     L.sb_copy_obs_to_host_packed.argtypes = [H, C.POINTER(_abi.SbObsPtrs)]
     L.sb_copy_obs_to_host_packed.restype = C.c_int
+    L.sb_copy_grids_to_host_packed_noalloc.argtypes = [H, C.c_void_p, C.c_void_p]
+    L.sb_copy_grids_to_host_packed_noalloc.restype = C.c_int
     L.sb_get_obs.argtypes = [H, C.POINTER(_abi.SbObsPtrs)]
     L.sb_get_state.argtypes = [H, C.POINTER(_abi.SbStatePtrs)]
     L.sb_launch_count.argtypes = [H]
@@ -301,6 +303,17 @@ class Engine:
             self._check(self._lib.sb_copy_obs_to_host_packed(self._h, C.byref(p)), "sb_copy_obs_to_host_packed")
         else:
             self._check(self._lib.sb_copy_obs_to_host(self._h, C.byref(p)), "sb_copy_obs_to_host")
+
+    def copy_grids_to_host_packed_noalloc(self, ogm_bits=None, dagm_bits=None):
+        """The 1-bit grid images of ``copy_obs_to_host(packed=True)`` without a single allocation inside the library
+        (sb_copy_grids_to_host_packed_noalloc): for processes whose allocator already owns all of HBM, loops that
+        cannot afford cudaMalloc's device-wide synchronisation, or code running beside another thread's stream
+        capture.  ``ogm_bits`` / ``dagm_bits``: host uint8 tensors [E, A, H, W // 8] (``host_obs_buffers(packed_grids=
+        True)``); ``None`` skips that grid.  The staging array is 16 MiB per GPU and shared by every engine on it:
+        larger batches raise, and overlapping calls from two threads must be serialised by the caller."""
+        ptr = lambda t: None if t is None else C.c_void_p(t.data_ptr())
+        self._check(self._lib.sb_copy_grids_to_host_packed_noalloc(self._h, ptr(ogm_bits), ptr(dagm_bits)),
+                    "sb_copy_grids_to_host_packed_noalloc")
 
     # -- zero-copy views -----------------------------------------------------------------
     def obs(self) -> Dict[str, "object"]:
