@@ -322,7 +322,11 @@ int sb_observe(SbHandle h, void *stream);
 /* The same for the agents of the listed envs only (host env_ids [n]; NULL = every env): the reset observation of
  * an auto-reset.  Every env of the reference is its own SMARTS instance (ParallelEnv, parallel_env.py:96-127), so
  * observing the envs that were just reset must not touch the sensor state (driven path, trip meter,
- * accelerometer history, vias, step counters) or the observation buffers of the others. */
+ * accelerometer history, vias, step counters) or the observation buffers of the others.  Whether an observation
+ * follows a tick (step counter + 1, dones may be raised) or is the `sim.resetting` kind is kept per agent: sb_step
+ * marks every agent, the events pass of sb_observe / sb_observe_envs uses the mark up for the agents it covers, and
+ * sb_reset clears it for the envs it resets -- so any split of the envs over several sb_observe_envs calls after a
+ * sb_step gives what one sb_observe gives. */
 int sb_observe_envs(SbHandle h, const int32_t *env_ids, int32_t n, void *stream);
 /* Convenience: the reference-facing call with HOST buffers (hiway_env.py:216-263 step()):
  * copies actions and social states in, runs sb_set_social + sb_step + sb_observe, synchronises. */

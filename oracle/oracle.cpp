@@ -716,9 +716,11 @@ bool boxes_touch(double ax, double ay, double ac, double as, double al, double a
 }
 
 // Sensors.observe tail: trip meter, driven path, _is_done_with_events (sensors.py:340-396, :443-594)
-void observe_events(World& w, int e, int a, bool ticked) {
+void observe_events(World& w, int e, int a) {
   const Map& mp = w.map;
   const int ai = e * w.A + a, vi = e * w.V + a;
+  const bool ticked = w.ticked[ai] != 0;  // per agent: observing a subset of the envs leaves the others' tick pending
+  w.ticked[ai] = 0;
   const double px = w.pos_x[vi], py = w.pos_y[vi], ph = w.heading[vi];
   const double len = w.length[vi], wid = w.width[vi], ch = w.cos_h[vi], sh = w.sin_h[vi];
   const int32_t* route = &w.route[(size_t)ai * w.cfg.route_cap];
@@ -1385,6 +1387,7 @@ void* or_create(const SbConfig* cfg, const SbMap* m, const double* base_rays, in
   w->route.assign(na * std::max(cfg->route_cap, 1), -1);
   w->route_len.assign(na, 0);
   w->status.assign(na, 0);
+  w->ticked.assign(na, 0);
   w->ego_lane.assign(na, -1);
   if (cfg->nbr_enable) {
     size_t n = na * cfg->nbr_cap;
@@ -1497,6 +1500,7 @@ void or_reset(void* h, const int32_t* env_ids, int n, const SbResetState* init) 
       for (int k = 0; k < SB_CTRL_STATE; ++k) w.ctrl[(size_t)ai * SB_CTRL_STATE + k] = 0.0;
       for (int k = 0; k < 3; ++k) w.last_control[(size_t)ai * 3 + k] = 0.0;
       w.status[ai] = 0;
+      w.ticked[ai] = 0;
       int rc = w.cfg.route_cap;
       for (int k = 0; k < rc; ++k) w.route[(size_t)ai * rc + k] = init->route ? init->route[src * rc + k] : -1;
       w.route_len[ai] = init->route_len ? init->route_len[src] : 0;
@@ -1602,7 +1606,7 @@ void or_step(void* h, const void* actions) {
       chassis_step(w, ai, vi);
     }
   });
-  w.stepped = true;
+  std::fill(w.ticked.begin(), w.ticked.end(), (uint8_t)1);
 }
 
 // Sensors.observe for the agents of the listed envs (env_ids == nullptr: every env).  Envs are independent
@@ -1614,9 +1618,7 @@ void or_observe_envs(void* h, const int32_t* env_ids, int n) {
   auto env_of = [&](int i) { return env_ids ? env_ids[i / w.A] : i / w.A; };
   parallel_for(ne * w.A, w.threads, 1, [&](int i) { observe_agent(w, env_of(i), i % w.A); });
   if (w.cfg.events_enable) {
-    const bool ticked = w.stepped;
-    parallel_for(ne * w.A, w.threads, 1, [&](int i) { observe_events(w, env_of(i), i % w.A, ticked); });
-    w.stepped = false;
+    parallel_for(ne * w.A, w.threads, 1, [&](int i) { observe_events(w, env_of(i), i % w.A); });
   }
   if (w.cfg.ego_frame) parallel_for(ne * w.A, w.threads, 1, [&](int i) { ego_frame_agent(w, env_of(i), i % w.A); });
 }

@@ -142,7 +142,7 @@ struct World {
   std::vector<float> rw_lane_width, rw_speed_limit;
   std::vector<int8_t> rw_lane_index;
   int ring = 1;
-  bool stepped = false;
+  std::vector<uint8_t> ticked;  // [E*A] stepped since the agent's last events pass (SensorState.step is due)
   int threads = 1;
 };
 

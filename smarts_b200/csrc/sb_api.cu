@@ -39,7 +39,6 @@ struct SbHandle_ {
   int32_t *h_env_list = nullptr, *d_env_list = nullptr;  // sb_observe_envs: pinned staging + device copy of the env list
   cudaStream_t env_list_stream = nullptr;
   cudaStream_t last_stream = nullptr;  // stream of the last sb_set_social / sb_step / sb_observe (host-buffer calls order themselves after it)
-  bool stepped = false;  // a sb_step since the last sb_observe (SensorState.step; `sim.resetting` otherwise)
   bool have_map = false, have_rays = false;
   bool stale_agents = false;          // a new map was uploaded: routes / lanes of the old one are meaningless until a full reset
   std::vector<void*> map_allocs;      // device arrays of the current map (freed when another one replaces it)
@@ -165,6 +164,7 @@ __global__ void k_reset(DCfg c, DState s, DEvents ev, const int32_t* env_ids, in
     for (int k = 0; k < SB_CTRL_STATE; ++k) s.ctrl[(size_t)ai * SB_CTRL_STATE + k] = 0.0;
     for (int k = 0; k < 3; ++k) s.last_control[(size_t)ai * 3 + k] = 0.0;
     s.status[ai] = 0;
+    s.ticked[ai] = 0;  // the first observation of a new episode is the `sim.resetting` one
     for (int k = 0; k < c.route_cap; ++k)
       s.route[(size_t)ai * c.route_cap + k] = route ? route[src * c.route_cap + k] : -1;
     s.route_len[ai] = route_len ? route_len[src] : 0;
@@ -334,7 +334,7 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
             dev_alloc(h, &s.steering, na) && dev_alloc(h, &s.v_long, na) && dev_alloc(h, &s.v_lat, na) &&
             dev_alloc(h, &s.ctrl, na * SB_CTRL_STATE) && dev_alloc(h, &s.last_control, na * 3) &&
             dev_alloc(h, &s.route, na * c.route_cap) && dev_alloc(h, &s.route_len, na) &&
-            dev_alloc(h, &s.status, na);
+            dev_alloc(h, &s.status, na) && dev_alloc(h, &s.ticked, na);
   if (!ok) return SB_ENOMEM;
   k_fill<<<(unsigned)((nv + 255) / 256), 256>>>(s.cos_h, nv, 1.0);
   cudaMemset(s.route, 0xff, na * c.route_cap * sizeof(int32_t));
@@ -462,10 +462,27 @@ int sb_create(const SbConfig* cfg, SbHandle* out) {
                  "cudaFuncSetAttribute"))
       return SB_ECUDA;
   }
-  if (const char* ma = getenv("SB_LIDAR_TILE_MIN_A")) h->lidar_tile_min_agents = atoi(ma);
-  if (const char* cap = getenv("SB_LIDAR_LIST_CAP")) {
-    const int v = atoi(cap);
-    if (v >= 0 && v < SB_LIDAR_LIST) h->lidar_list_cap = v;
+  // Test / A-B hooks for the LiDAR kernel choice.  They exist for tests/ and profiles/ only, so they are dead unless
+  // SB_DEBUG_HOOKS=1 is set as well (a stray SB_LIDAR_* in a production environment changes nothing), and a value that
+  // is not a whole number in range fails sb_create instead of silently selecting the slow path.
+  if (const char* on = getenv("SB_DEBUG_HOOKS"); on && on[0] == '1' && on[1] == '\0') {
+    auto hook = [&](const char* name, long lo, long hi, int* dst) {
+      const char* v = getenv(name);
+      if (!v) return true;
+      char* end = nullptr;
+      const long x = strtol(v, &end, 10);
+      if (end == v || *end != '\0' || x < lo || x > hi) {
+        fail(h, SB_EINVAL, std::string(name) + "=\"" + v + "\": expected a whole number in [" + std::to_string(lo) + ", " +
+                               std::to_string(hi) + "]");
+        return false;
+      }
+      *dst = (int)x;
+      return true;
+    };
+    // agents per env from which k_lidar_tiles is used (1: always; A + 1 or more: never)
+    if (!hook("SB_LIDAR_TILE_MIN_A", 1, 1 << 20, &h->lidar_tile_min_agents)) return SB_EINVAL;
+    // intervals a k_lidar_tiles block may hold before it falls back to the one-agent cast (0: always fall back)
+    if (!hook("SB_LIDAR_LIST_CAP", 0, SB_LIDAR_LIST, &h->lidar_list_cap)) return SB_EINVAL;
   }
   if (c.lidar_enable &&
       !cuda_ok(h, cudaFuncSetAttribute((const void*)k_lidar_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -911,7 +928,6 @@ int sb_step(SbHandle h, const void* dev_actions, void* stream) {
       k_control_simple<<<(na + 127) / 128, 128, 0, st>>>(c, h->st, static_cast<const double*>(dev_actions));
     }
   }
-  h->stepped = true;
   return cuda_ok(h, cudaGetLastError(), "k_control") ? SB_OK : SB_ECUDA;
 }
 
@@ -1003,9 +1019,7 @@ int sb_observe_envs(SbHandle h, const int32_t* env_ids, int32_t n, void* stream)
   }
   if (c.events_enable) {
     LaunchScope ls(h, SB_K_EVENTS, st);
-    k_events<<<(na + SB_EV_WARPS - 1) / SB_EV_WARPS, SB_EV_WARPS * 32, 0, st>>>(c, h->dmap, h->st, h->ev, h->evo,
-                                                                              h->stepped ? 1 : 0);
-    h->stepped = false;
+    k_events<<<(na + SB_EV_WARPS - 1) / SB_EV_WARPS, SB_EV_WARPS * 32, 0, st>>>(c, h->dmap, h->st, h->ev, h->evo);
   }
   if (c.ego_frame && (c.lidar_enable || c.nbr_enable || c.wp_enable || c.rw_enable)) {  // last: k_ttc / k_events read world-frame buffers
     LaunchScope ls(h, SB_K_EGO_FRAME, st);

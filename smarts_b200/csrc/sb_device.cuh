@@ -55,6 +55,9 @@ struct DState {
   double *steering, *v_long, *v_lat, *ctrl, *last_control;
   int32_t *route, *route_len;
   uint32_t* status;
+  // [E*A] 1: a control kernel has moved this agent since its last events pass (SensorState.step is due); k_events
+  // consumes it.  Per agent, not per handle: observing some envs must not use up the tick of the others.
+  uint8_t* ticked;
 };
 
 // ---- scalar restatements (reference file:line in the comments) -------------------------------

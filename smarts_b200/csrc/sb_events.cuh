@@ -170,11 +170,19 @@ __device__ __forceinline__ bool ev_boxes_touch(double ax, double ay, double ac, 
 #define SB_EV_MIN_BLOCKS 10  // 48 registers: 0.110 -> 0.087 ms on the headline with events (8: 0.091, 12: 0.087), profiles/README.md r2y
 #endif
 __global__ void __launch_bounds__(SB_EV_WARPS * 32, SB_EV_MIN_BLOCKS)
-k_events(DCfg c, DMap m, DState s, DEvents ev, DEvOut o, int ticked) {
+k_events(DCfg c, DMap m, DState s, DEvents ev, DEvOut o) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   int e, a;
   if (!d_work_agent(c, blockIdx.x * SB_EV_WARPS + warp, &e, &a)) return;
   const int ai = e * c.A + a, vi = e * c.V + a;
+  // this agent's tick flag: read by lane 0, handed to the warp, used up (one warp per agent here and one thread
+  // per agent in the control kernels, so nobody else touches the byte)
+  int ticked = 0;
+  if (lane == 0) {
+    ticked = s.ticked[ai];
+    s.ticked[ai] = 0;
+  }
+  ticked = __shfl_sync(0xffffffffu, ticked, 0);
   const double px = s.pos_x[vi], py = s.pos_y[vi], ph = s.heading[vi];
   const double len = s.length[vi], wid = s.width[vi];
   const double ch = s.cos_h[vi], sh = s.sin_h[vi];

@@ -183,6 +183,7 @@ __global__ void __launch_bounds__(SB_CTRL_LAW_THREADS)
 k_control_law(DCfg c, DMap m, DState s, const void* __restrict__ actions, const CtrlPick* __restrict__ picks) {
   const int ai = blockIdx.x * SB_CTRL_LAW_THREADS + threadIdx.x;
   if (ai >= c.E * c.A) return;
+  s.ticked[ai] = 1;
   const int e = ai / c.A, a = ai - e * c.A, vi = e * c.V + a;
   DEgo v{s.pos_x[vi], s.pos_y[vi], s.heading[vi], s.speed[vi], s.yaw_rate[vi], s.v_long[ai], s.v_lat[ai]};
   double* st = s.ctrl + (size_t)ai * SB_CTRL_STATE;
@@ -202,6 +203,7 @@ k_control_law(DCfg c, DMap m, DState s, const void* __restrict__ actions, const 
 __global__ void k_control_simple(DCfg c, DState s, const double* __restrict__ actions) {
   int ai = blockIdx.x * blockDim.x + threadIdx.x;
   if (ai >= c.E * c.A) return;
+  s.ticked[ai] = 1;
   const int e = ai / c.A, a = ai - e * c.A, vi = e * c.V + a;
   DEgo v{s.pos_x[vi], s.pos_y[vi], s.heading[vi], s.speed[vi], s.yaw_rate[vi], s.v_long[ai], s.v_lat[ai]};
   double* st = s.ctrl + (size_t)ai * SB_CTRL_STATE;

@@ -149,6 +149,8 @@ class Engine:
     def upload_map(self, road_map: RoadMapData):
         """Load (or, on a live handle, replace) the road map.  After a replacement every env must be reset
         (``reset`` without ``env_ids``) before the next step / observe -- the library refuses anything else."""
+        if self.cfg.rw_enable:
+            road_map.require_road_waypoint_tables()
         m, keep = _abi.make_map_struct(road_map.arrays(), road_map.spacing)
         self._check(self._lib.sb_upload_map(self._h, C.byref(m)), "sb_upload_map")
         del keep

@@ -19,6 +19,7 @@ lanepoints.py:85-102) become three index ranges of the same arrays.
 from __future__ import annotations
 
 import math
+import warnings
 from dataclasses import dataclass
 from typing import Dict, List, Optional, Sequence, Tuple
 
@@ -121,7 +122,23 @@ class RoadMapData:
             self.lane_in = np.asarray(flat if flat else [0], np.int32)
             self.road_par_start = np.zeros(len(self._road_ids) + 1, np.int32)
             self.road_par = np.zeros(1, np.int32)
+            # ... so the RoadWaypoints sensor would see other lane sets than the reference (sensors.py:1007-1011):
+            # the map is flagged and `require_road_waypoint_tables` (called for rw_enable) refuses it
+            self.rw_tables_complete = False
+            warnings.warn(f"{path}: saved without the RoadWaypoints tables (lane_in / road_par); every sensor but "
+                          "RoadWaypoints works, rebuild the file from its net.xml to use that one", stacklevel=2)
         return self
+
+    rw_tables_complete = True
+
+    def require_road_waypoint_tables(self):
+        """Raise unless the incoming-lane and parallel-road tables come from the net itself (``Lane.incoming_lanes``
+        in getIncoming() order, ``Road.parallel_roads`` by node ids; sumo_road_network.py:342-348, :607-618).  An
+        old-format .npz only approximates the first and has none of the second."""
+        if not self.rw_tables_complete:
+            raise ValueError("this map was loaded from an .npz written before the RoadWaypoints tables existed: "
+                             "RoadWaypoints (rw_enable) would list other lanes than the reference; rebuild the file "
+                             "with RoadMapData.from_file(net_xml).save(path)")
 
     # ------------------------------------------------------------------ tables
     def _build_tables(self):

@@ -773,6 +773,7 @@ def test_lidar_tile_remainders_and_list_overflow_fallback(A, cap, monkeypatch):
     block's interval list capped at 8 entries (SB_LIDAR_LIST_CAP, read at sb_create) every tile overflows and falls back
     to the one-agent chunked cast; A = 1 takes the one-agent kernel outright.  All bit-identical to the oracle."""
     if cap is not None:
+        monkeypatch.setenv("SB_DEBUG_HOOKS", "1")
         monkeypatch.setenv("SB_LIDAR_LIST_CAP", cap)
     rm = load_map("4lane")
     E, M = 5, 18
@@ -781,3 +782,63 @@ def test_lidar_tile_remainders_and_list_overflow_fallback(A, cap, monkeypatch):
     eng, ora = run_pair(rm, cfg, missions, ticks=16, seed=41 + A, action_fn=lane_actions(E, A, 3), check_every=4, jitter=30.0)
     assert 0 < ora.obs()["lidar_hits"].mean() < 1
     eng.close()
+
+
+@pytest.mark.gpu
+def test_observing_the_envs_in_two_halves_ticks_every_env_once():
+    """sb_step, then sb_observe_envs on one half of the envs and on the other half: the tick belongs to each agent,
+    not to the handle, so the second half's step counters advance and its dones are raised exactly as in one
+    sb_observe over all envs (the first partial observe must not use up the others' tick; SensorState.step,
+    sensors.py:609-637).  A third observe without a step in between is the `sim.resetting` kind for everyone."""
+    import torch
+    rm = load_map("4lane")
+    E, A, M = 6, 4, 6
+    cfg = make_cfg(E=E, A=A, M=M, nbr=True, wp=True, route_cap=16, events=True, max_episode_steps=3)
+    x, y, h, v, route, rlen = scenario_gen.agent_starts(rm, E, MISSIONS_4LANE, cfg.route_cap, 91, jitter=30.0, speed=6.0)
+    traffic = scenario_gen.SocialTraffic(rm, E, M, 92)
+    first, second = np.array([0, 2, 5], np.int32), np.array([1, 3, 4], np.int32)
+    split, whole, ora = engine(rm, cfg), engine(rm, cfg), oracle_world(rm, cfg, threads=4)
+    for w in (split, whole, ora):
+        w.reset(x, y, h, v, route, rlen)
+        w.observe()
+    act = np.zeros((E, A), np.int32)
+    for t in range(3):
+        soc = traffic.states(t)
+        for w in (split, whole):
+            w.set_social(torch.from_numpy(soc).cuda())
+            w.step(torch.from_numpy(act).cuda())
+        ora.set_social(soc); ora.step(act)
+        whole.observe()
+        for w in (split, ora):
+            w.observe(first)
+            w.observe(second)
+        got = split.obs_numpy()
+        assert_same(got, whole.obs_numpy())
+        assert_same(got, ora.obs())
+        assert (got["ev_steps"] == t + 1).all()
+    assert got["ev_done"].all() and (got["ev_events"] & _abi.SB_EV_REACHED_MAX_STEPS).all()
+    for w in (split, ora):
+        w.observe(second)  # no step since: nothing advances, no done is raised
+    got = split.obs_numpy()
+    assert_same(got, ora.obs())
+    assert (got["ev_steps"] == 3).all() and not got["ev_done"][second].any() and got["ev_done"][first].all()
+    for w in (split, whole):
+        w.close()
+
+
+@pytest.mark.gpu
+def test_lidar_debug_hooks_are_gated_and_validated(monkeypatch):
+    """SB_LIDAR_* only count together with SB_DEBUG_HOOKS=1, and then garbage fails sb_create with the variable named
+    in the message instead of quietly selecting the per-agent LiDAR fallback."""
+    from smarts_b200.engine import SmartsB200Error
+    rm = load_map("4lane")
+    cfg = make_cfg(E=2, A=4, M=4, lidar=True, wall=1.5, route_cap=16)
+    monkeypatch.setenv("SB_LIDAR_LIST_CAP", "zero")
+    engine(rm, cfg).close()  # ignored: the hooks are off
+    monkeypatch.setenv("SB_DEBUG_HOOKS", "1")
+    with pytest.raises(SmartsB200Error, match="SB_LIDAR_LIST_CAP"):
+        engine(rm, cfg)
+    monkeypatch.setenv("SB_LIDAR_LIST_CAP", "8")
+    monkeypatch.setenv("SB_LIDAR_TILE_MIN_A", "-3")
+    with pytest.raises(SmartsB200Error, match="SB_LIDAR_TILE_MIN_A"):
+        engine(rm, cfg)

@@ -186,3 +186,23 @@ def test_hiway_env_road_waypoints_observation():
         d0 = np.linalg.norm(path[0].pos - ob.ego_vehicle_state.position[:2])
         assert d0 <= 20.0 + 2.0
     env.close()
+
+
+def test_old_format_map_is_flagged_and_refused_for_road_waypoints(tmp_path):
+    """An .npz written before the lane_in / road_par tables existed loads (with a warning) for every other sensor,
+    but is refused for RoadWaypoints: its parallel-road table is empty and its incoming lanes are not in
+    getIncoming() order, so the sensor's lane set would differ from the reference's (sensors.py:1007-1011)."""
+    from smarts_b200.road_map import RoadMapData
+    src = np.load(os.path.join(os.path.dirname(GOLDEN), "..", "maps", "4lane.npz"), allow_pickle=False)
+    old = {k: src[k] for k in src.files if k not in ("lane_in_start", "lane_in", "road_par_start", "road_par")}
+    path = str(tmp_path / "old.npz")
+    np.savez_compressed(path, **old)
+    with pytest.warns(UserWarning, match="RoadWaypoints tables"):
+        rm = RoadMapData.load(path)
+    assert not rm.rw_tables_complete
+    assert len(rm.lane_in_start) == len(rm.lane_road) + 1  # still a usable map for the other sensors
+    with pytest.raises(ValueError, match="RoadWaypoints"):
+        rm.require_road_waypoint_tables()
+    new = load_map("4lane")
+    assert new.rw_tables_complete
+    new.require_road_waypoint_tables()
