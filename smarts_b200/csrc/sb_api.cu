@@ -37,8 +37,12 @@ struct SbHandle_ {
   DRoadWp rw{};
   int32_t* d_veh_lane = nullptr;  // k_vehicle_lanes -> k_observe (only when V <= A * nbr_cap)
   int32_t *h_env_list = nullptr, *d_env_list = nullptr;  // sb_observe_envs: pinned staging + device copy of the env list
-  cudaStream_t env_list_stream = nullptr;
-  cudaStream_t last_stream = nullptr;  // stream of the last sb_set_social / sb_step / sb_observe (host-buffer calls order themselves after it)
+  // Ordering against the caller's streams is kept with events the handle owns, never with the caller's stream
+  // handles (a stream may be destroyed, or be under capture, by the time the next call looks at it).
+  cudaEvent_t work_ev = nullptr;      // recorded behind the last sb_set_social / sb_step / sb_observe on a non-legacy stream
+  bool work_pending = false;          // ... and not yet waited for by a host-buffer call
+  cudaEvent_t env_list_ev = nullptr;  // recorded behind the H2D copy of the sb_observe_envs list
+  bool env_list_pending = false;
   bool have_map = false, have_rays = false;
   bool stale_agents = false;          // a new map was uploaded: routes / lanes of the old one are meaningless until a full reset
   std::vector<void*> map_allocs;      // device arrays of the current map (freed when another one replaces it)
@@ -235,6 +239,32 @@ struct DeviceGuard {
     if (prev >= 0 && cudaGetDevice(&cur) == cudaSuccess && cur != prev) cudaSetDevice(prev);
   }
 };
+
+// Called at the end of sb_set_social / sb_step / sb_observe: remembers "everything queued on st so far" as an event
+// the host-buffer calls can wait for.  Work on the legacy stream needs no mark (those calls run on it), and a stream
+// under capture cannot be marked (the record would become a graph node and the event could not be waited on): after
+// replaying a captured tick on a non-blocking stream the caller synchronises it before a host-buffer call.
+void mark_work(SbHandle h, cudaStream_t st) {
+  if (st == nullptr || st == cudaStreamLegacy) return;  // (an earlier mark on another stream stays pending)
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(st, &cs) != cudaSuccess) {
+    cudaGetLastError();
+    return;
+  }
+  if (cs != cudaStreamCaptureStatusNone) return;
+  if (!h->work_ev && cudaEventCreateWithFlags(&h->work_ev, cudaEventDisableTiming) != cudaSuccess) {
+    cudaGetLastError();
+    h->work_ev = nullptr;
+    return;
+  }
+  h->work_pending = cudaEventRecord(h->work_ev, st) == cudaSuccess;
+}
+
+// The host-buffer calls work on the legacy stream: make it wait (on the device, no host stall) for the marked work.
+void wait_marked_work(SbHandle h) {
+  if (h->work_pending && cudaStreamWaitEvent(nullptr, h->work_ev, 0) != cudaSuccess) cudaGetLastError();
+  h->work_pending = false;
+}
 
 size_t action_bytes(const SbConfig& c) {
   size_t na = (size_t)c.n_envs * c.n_agents;
@@ -504,6 +534,8 @@ void sb_destroy(SbHandle h) {
   std::free(h->h_prev);
   for (auto e : h->xfer_ev) cudaEventDestroy(e);
   for (auto e : h->ev_pool) cudaEventDestroy(e);
+  if (h->work_ev) cudaEventDestroy(h->work_ev);
+  if (h->env_list_ev) cudaEventDestroy(h->env_list_ev);
   if (h->d_edge_inv) cudaFree(h->d_edge_inv);
   delete h;
 }
@@ -897,13 +929,14 @@ int sb_set_social(SbHandle h, const double* dev_states, void* stream) {
   if (c.M == 0) return SB_OK;
   if (!dev_states) return fail(h, SB_EINVAL, "dev_states is null");
   DeviceGuard dg(h->cfg.device);
-  h->last_stream = (cudaStream_t)stream;
   int n = c.E * c.M;
   {
     LaunchScope ls(h, SB_K_SOCIAL, (cudaStream_t)stream);
     k_set_social<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(c, h->st, dev_states);
   }
-  return cuda_ok(h, cudaGetLastError(), "k_set_social") ? SB_OK : SB_ECUDA;
+  if (!cuda_ok(h, cudaGetLastError(), "k_set_social")) return SB_ECUDA;
+  mark_work(h, (cudaStream_t)stream);
+  return SB_OK;
 }
 
 int sb_step(SbHandle h, const void* dev_actions, void* stream) {
@@ -915,7 +948,6 @@ int sb_step(SbHandle h, const void* dev_actions, void* stream) {
   int na = c.E * c.A;
   cudaStream_t st = (cudaStream_t)stream;
   DeviceGuard dg(h->cfg.device);
-  h->last_stream = st;
   {
     LaunchScope ls(h, SB_K_CONTROL, st);
     if (c.action_space == SB_ACTION_LANE || c.action_space == SB_ACTION_LANE_WITH_CONTINUOUS_SPEED) {
@@ -928,7 +960,9 @@ int sb_step(SbHandle h, const void* dev_actions, void* stream) {
       k_control_simple<<<(na + 127) / 128, 128, 0, st>>>(c, h->st, static_cast<const double*>(dev_actions));
     }
   }
-  return cuda_ok(h, cudaGetLastError(), "k_control") ? SB_OK : SB_ECUDA;
+  if (!cuda_ok(h, cudaGetLastError(), "k_control")) return SB_ECUDA;
+  mark_work(h, st);
+  return SB_OK;
 }
 
 int sb_observe(SbHandle h, void* stream) { return sb_observe_envs(h, nullptr, 0, stream); }
@@ -941,7 +975,6 @@ int sb_observe_envs(SbHandle h, const int32_t* env_ids, int32_t n, void* stream)
   if (h->dc.lidar_enable && !h->have_rays) return fail(h, SB_ESTATE, "lidar enabled but no ray table uploaded");
   cudaStream_t st = (cudaStream_t)stream;
   DeviceGuard dg(h->cfg.device);
-  h->last_stream = st;
   DCfg c = h->dc;  // this call's copy: the env list rides in it
   if (env_ids) {
     if (n < 1 || n > c.E) return fail(h, SB_EINVAL, "n out of range");
@@ -952,14 +985,21 @@ int sb_observe_envs(SbHandle h, const int32_t* env_ids, int32_t n, void* stream)
       if (!cuda_ok(h, cudaHostAlloc(&h->h_env_list, (size_t)c.E * sizeof(int32_t), cudaHostAllocDefault), "cudaHostAlloc(env list)") ||
           !dev_alloc(h, &h->d_env_list, (size_t)c.E))
         return SB_ENOMEM;
-    } else {
-      cudaStreamSynchronize(h->env_list_stream);  // the previous list's copy has left the pinned buffer
+    } else if (h->env_list_pending) {
+      cudaEventSynchronize(h->env_list_ev);  // the previous list's copy has left the pinned buffer
+      h->env_list_pending = false;
     }
     std::memcpy(h->h_env_list, env_ids, (size_t)n * sizeof(int32_t));
     if (!cuda_ok(h, cudaMemcpyAsync(h->d_env_list, h->h_env_list, (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, st),
                  "H2D env list"))
       return SB_ECUDA;
-    h->env_list_stream = st;
+    {  // (a stream under capture is not marked: the copy is then a graph node that reads the buffer at replay time)
+      cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+      if (cudaStreamIsCapturing(st, &cs) != cudaSuccess) cudaGetLastError();
+      else if (cs == cudaStreamCaptureStatusNone &&
+               (h->env_list_ev || cudaEventCreateWithFlags(&h->env_list_ev, cudaEventDisableTiming) == cudaSuccess))
+        h->env_list_pending = cudaEventRecord(h->env_list_ev, st) == cudaSuccess;
+    }
     c.env_list = h->d_env_list;
     c.n_list = n;
   }
@@ -1025,7 +1065,9 @@ int sb_observe_envs(SbHandle h, const int32_t* env_ids, int32_t n, void* stream)
     LaunchScope ls(h, SB_K_EGO_FRAME, st);
     k_ego_frame<<<na, SB_EGO_THREADS, 0, st>>>(c, h->st, h->ob, h->rw);
   }
-  return cuda_ok(h, cudaGetLastError(), "k_observe") ? SB_OK : SB_ECUDA;
+  if (!cuda_ok(h, cudaGetLastError(), "k_observe")) return SB_ECUDA;
+  mark_work(h, st);
+  return SB_OK;
 }
 
 int sb_step_host(SbHandle h, const void* host_actions, int64_t n_bytes, const double* host_social) {
@@ -1035,7 +1077,7 @@ int sb_step_host(SbHandle h, const void* host_actions, int64_t n_bytes, const do
   const DCfg& c = h->dc;
   DeviceGuard dg(h->cfg.device);
   // this call works on the legacy stream; work queued by sb_step / sb_observe on another (non-blocking) stream comes first
-  if (h->last_stream && cudaStreamSynchronize(h->last_stream) != cudaSuccess) cudaGetLastError();  // (a stream the caller has since destroyed has nothing pending)
+  wait_marked_work(h);
   if (!cuda_ok(h, cudaMemcpyAsync(h->d_actions, host_actions, h->actions_cap, cudaMemcpyHostToDevice, 0), "H2D actions"))
     return SB_ECUDA;
   if (c.M > 0) {
@@ -1067,7 +1109,7 @@ static int copy_obs_to_host(SbHandle h, const SbObsPtrs* dst, bool packed_dst) {
   size_t na = (size_t)c.n_envs * c.n_agents;
   DeviceGuard dg(c.device);
   // copies run on the legacy stream: observations written on another (non-blocking) stream are waited for first
-  if (h->last_stream && cudaStreamSynchronize(h->last_stream) != cudaSuccess) cudaGetLastError();  // (a stream the caller has since destroyed has nothing pending)
+  wait_marked_work(h);
   bool ok = true;
   size_t link_total = 0;  // bytes queued on the PCIe link by this call
   auto cpy = [&](void* d, const void* s, size_t bytes) {
@@ -1415,7 +1457,7 @@ extern "C" int sb_copy_grids_to_host_packed_noalloc(SbHandle h, uint8_t* host_og
   uint32_t* bits = nullptr;  // first call on this device: resolves the array's device address (before any capture)
   if (!cuda_ok(h, noalloc_bits_address(c.device, &bits), "cudaGetSymbolAddress(g_noalloc_bits)")) return SB_ECUDA;
   // the grids may have been written on another (non-blocking) stream: wait for it, as sb_copy_obs_to_host does
-  if (h->last_stream && cudaStreamSynchronize(h->last_stream) != cudaSuccess) cudaGetLastError();
+  wait_marked_work(h);
   h->launches++;
   k_pack_bits_noalloc<<<(unsigned)((words0 + words1 + 255) / 256), 256>>>(h->ob.ogm, words0, h->ob.dagm, words1, bits);
   if (!cuda_ok(h, cudaGetLastError(), "k_pack_bits_noalloc")) return SB_ECUDA;

@@ -767,6 +767,48 @@ def test_host_buffer_copy_orders_itself_after_a_side_stream():
     eng.close()
 
 
+def test_host_buffer_copy_after_the_callers_stream_is_gone():
+    """The library keeps no handle of the caller's stream: ticks are queued on a raw non-blocking stream through the
+    C-ABI, the stream is destroyed at once (CUDA lets its queued work finish), and sb_copy_obs_to_host still
+    delivers the last tick's observations -- it waits on an event the handle owns, recorded behind those kernels."""
+    import ctypes as C
+    import torch
+    try:
+        from cuda.bindings import runtime as cudart
+    except ImportError:
+        cudart = pytest.importorskip("cuda.cudart")
+    rm = load_map("4lane")
+    E, A, M = 64, 4, 20
+    cfg = make_cfg(E=E, A=A, M=M, lidar=True, wall=1.5, ogm=(256, 256, 0.1), dagm=(256, 256, 0.1), route_cap=16)
+    x, y, h, v, route, rlen = scenario_gen.agent_starts(rm, E, MISSIONS_4LANE, cfg.route_cap, 7, jitter=20.0, speed=6.0)
+    traffic = scenario_gen.SocialTraffic(rm, E, M, 8)
+    eng, ora = engine(rm, cfg), oracle_world(rm, cfg, threads=8)
+    eng.reset(x, y, h, v, route, rlen)
+    ora.reset(x, y, h, v, route, rlen)
+    act = np.zeros((E, A), np.int32)
+    socs = [torch.from_numpy(traffic.states(t)).cuda() for t in range(12)]
+    acts = torch.from_numpy(act).cuda()
+    torch.cuda.synchronize()
+    err, raw = cudart.cudaStreamCreateWithFlags(cudart.cudaStreamNonBlocking)
+    assert int(err) == 0
+    st = C.c_void_p(int(raw))
+    lib, hdl = eng._lib, eng._h
+    for t in range(12):
+        assert lib.sb_set_social(hdl, C.c_void_p(socs[t].data_ptr()), st) == 0
+        assert lib.sb_step(hdl, C.c_void_p(acts.data_ptr()), st) == 0
+        assert lib.sb_observe(hdl, st) == 0
+    assert int(cudart.cudaStreamDestroy(raw)[0]) == 0
+    bufs = eng.host_obs_buffers(pinned=True)
+    eng.copy_obs_to_host(bufs)
+    for t in range(12):
+        ora.set_social(traffic.states(t))
+        ora.step(act)
+        ora.observe()
+    want = ora.obs()
+    assert_same({k: bufs[k].numpy() for k in want}, want)
+    eng.close()
+
+
 @pytest.mark.parametrize("A,cap", [(6, None), (5, "8"), (1, None)])
 def test_lidar_tile_remainders_and_list_overflow_fallback(A, cap, monkeypatch):
     """k_lidar_tiles casts for four agents of an env per block: A = 6 leaves a tile of two, A = 5 a tile of one; with the
