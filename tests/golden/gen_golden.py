@@ -273,12 +273,20 @@ def gen_gains(lh=3.68 / 2, m=2356.0, iz=2681.95008628, c=100000.0):
     return np.array(out)
 
 
+SAVE_MAPS = True  # regen_check.py turns this off: it only compares
+
+
 def main():
     os.makedirs(os.path.join(ROOT, "maps"), exist_ok=True)
     rng = np.random.default_rng(20241104)
     keep = {}
     for name, rel in MAPS.items():
-        rec, extra = gen_map_queries(name, rel, rng)
+        # 4lane: lane ends and their successors' starts coincide exactly, scipy's order among such ties is not
+        # specified, and the committed queries_4lane.npz was generated under the canonical order (ref_shims.
+        # set_tie_ranks) the oracle and the kernels use.  Against scipy's own order 8 of the 1 246 sampled 4lane paths
+        # (0.6 %) start on the other of the two coincident lanes.  tests/golden/regen_check.py verifies that this
+        # main() reproduces every committed queries_*.npz.
+        rec, extra = gen_map_queries(name, rel, rng, tie_ranks=(name == "4lane"), save_map=SAVE_MAPS)
         if rec is None:
             continue
         np.savez_compressed(os.path.join(HERE, f"queries_{name}.npz"), **rec)
